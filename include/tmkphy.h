@@ -1,0 +1,196 @@
+/*
+ * tmkphy.h — C ABI of libtmkphy, the B200-native batched acoustic-modem PHY engine.
+ *
+ * Drop-in boundary for the PHY hot path of HeZeBang/TrackMaker-rs (reference paths are
+ * relative to the reference repository root):
+ *
+ *   tmk_modulate        replaces PhyEncoder::encode_frames      src/phy/encoder.rs:70-92
+ *                       (Frame::to_bytes src/phy/frame.rs:74-102,
+ *                        LineCode::encode src/phy/line_coding.rs:74-91,202-240)
+ *   tmk_decode_batch    replaces PhyDecoder::process_samples    src/phy/decoder.rs:68-112
+ *                       (search_for_preamble :123-238, decode_frame :242-356,
+ *                        LineCode::decode line_coding.rs:93-123,243-293,
+ *                        Frame::from_bits frame.rs:147-183, crc8 crc.rs:7-22)
+ *   tmk_correlate       parity probe for the normalised sliding correlation
+ *                                                              src/phy/decoder.rs:130-147
+ *   tmk_channel_busy    replaces mac::is_channel_busy           src/mac/mod.rs:18-27
+ *   tmk_phy_config      mirrors PhyDecoder::new / PhyEncoder::new arguments
+ *                                                              src/phy/decoder.rs:36-65
+ *   tmk_frame_desc      mirrors struct Frame                    src/phy/frame.rs:34-41
+ *
+ * Conventions: every call returns 0 (TMK_OK) or a negative error code; nothing unwinds
+ * across the boundary; all buffers are caller-allocated and caller-owned; sample / record /
+ * payload pointers may be HOST or DEVICE pointers (detected with cudaPointerGetAttributes);
+ * one engine per GPU, driven by one host thread at a time (like a PhyDecoder: Send, !Sync).
+ * There is no CPU fallback: every entry point that computes runs CUDA kernels on sm_100a.
+ */
+#ifndef TMKPHY_H
+#define TMKPHY_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define TMK_ABI_VERSION 1
+
+/* LineCodingKind (src/phy/line_coding.rs:26-30) */
+#define TMK_LINE_MANCHESTER 0
+#define TMK_LINE_4B5B 1
+
+/* FrameType (src/phy/frame.rs:12-16) */
+#define TMK_FRAME_TYPE_DATA 0x01
+#define TMK_FRAME_TYPE_ACK 0x02
+
+/* return codes */
+#define TMK_OK 0
+#define TMK_E_INVALID (-1)  /* bad argument (null pointer, bad config, misaligned stream) */
+#define TMK_E_CUDA (-2)     /* CUDA runtime error; see tmk_last_error */
+#define TMK_E_CAPACITY (-3) /* an output buffer was too small; counts are still returned */
+#define TMK_E_NOMEM (-4)
+
+/* per-candidate verdict: one record per preamble detection, in the order the reference
+ * decoder would have met them (src/phy/decoder.rs:266-355). Only TMK_FRAME_OK records
+ * correspond to Frames returned by PhyDecoder::process_samples. */
+#define TMK_FRAME_OK 0
+#define TMK_FRAME_HDR_PARSE 1    /* decoder.rs:266-273  consumes header_samples */
+#define TMK_FRAME_BAD_LEN 2      /* decoder.rs:277-286  consumes 1 sample */
+#define TMK_FRAME_SHORT_DECODE 3 /* decoder.rs:311-320  4B5B invalid symbol mid-frame */
+#define TMK_FRAME_NOT_FOR_US 4   /* decoder.rs:322-329  dst != local_addr */
+#define TMK_FRAME_CRC_FAIL 5     /* decoder.rs:347-354 */
+#define TMK_FRAME_TRUNCATED 6    /* capture ended while the decoder was waiting for samples
+                                    (decoder.rs:252-254,295-297 return None forever) */
+
+/* Reference defaults: src/utils/consts.rs:24-48 and src/phy/decoder.rs:57,61 */
+#define TMK_DEFAULT_SPL 3
+#define TMK_DEFAULT_PREAMBLE_BYTES 2
+#define TMK_DEFAULT_THRESHOLD 0.9f
+#define TMK_DEFAULT_MAX_FRAME_BYTES 256
+#define TMK_DEFAULT_GAP_SAMPLES 48
+#define TMK_PHY_HEADER_BYTES 7
+
+typedef struct tmk_engine tmk_engine;
+
+typedef struct tmk_phy_config {
+    int32_t line_code;        /* TMK_LINE_* */
+    uint32_t spl;             /* samples per level (3) */
+    uint32_t preamble_bytes;  /* 2 */
+    int32_t local_addr;       /* 0..255; -1 accepts every dst (extension) */
+    float threshold;          /* 0.9f */
+    uint32_t max_frame_bytes; /* 256 */
+    uint64_t chunk;           /* size of each simulated process_samples() call in samples;
+                                 0 = the whole capture in one call (src/main.rs:540).
+                                 The live receiver polls 1200 samples (src/mac/csma.rs:446). */
+} tmk_phy_config;
+
+/* one capture of a ragged batch; `offset` is in samples from the `samples` base pointer and
+ * must be a multiple of 4 (16-byte aligned float4 loads). */
+typedef struct tmk_stream {
+    uint64_t offset;
+    uint64_t n_samples;
+    tmk_phy_config cfg;
+} tmk_stream;
+
+typedef struct tmk_frame_rec {
+    uint32_t stream;         /* index into the streams array */
+    uint32_t status;         /* TMK_FRAME_* */
+    uint64_t preamble_start; /* absolute sample index of the first window with corr >= thr */
+    uint64_t frame_start;    /* first header sample after sync-word refinement */
+    uint64_t payload_off;    /* byte offset into the payload buffer (status OK / CRC_FAIL /
+                                NOT_FOR_US: `len` decoded payload bytes are stored there) */
+    float corr;              /* correlation of the detecting window */
+    uint32_t consumed;       /* samples consumed from preamble_start */
+    uint16_t len;            /* header fields (zero when fewer than 7 header bytes decoded) */
+    uint8_t crc;
+    uint8_t type;
+    uint8_t seq;
+    uint8_t src;
+    uint8_t dst;
+    uint8_t hdr_valid;       /* 1 if the header fields above were decoded */
+} tmk_frame_rec;
+
+/* struct Frame (src/phy/frame.rs:34-41) for the modulator */
+typedef struct tmk_frame_desc {
+    uint64_t payload_off; /* into the payload buffer */
+    uint32_t len;         /* payload bytes, <= 65535 */
+    uint8_t type;
+    uint8_t seq;
+    uint8_t src;
+    uint8_t dst;
+} tmk_frame_desc;
+
+/* counters returned by tmk_stats (accumulated since engine creation / tmk_stats_reset) */
+enum {
+    TMK_STAT_SAMPLES = 0,
+    TMK_STAT_DETECTIONS = 1,
+    TMK_STAT_FRAMES_OK = 2,
+    TMK_STAT_CRC_FAIL = 3,
+    TMK_STAT_HDR_FAIL = 4, /* HDR_PARSE + BAD_LEN + SHORT_DECODE */
+    TMK_STAT_NOT_FOR_US = 5,
+    TMK_STAT_EXACT_REPLAYS = 6, /* threshold decisions that needed the sequential replay */
+    TMK_STAT_CANDIDATES = 7,
+    TMK_STAT_COUNT = 8
+};
+
+int tmk_abi_version(void);
+int tmk_engine_create(int device, tmk_engine** out);
+void tmk_engine_destroy(tmk_engine* e);
+const char* tmk_last_error(const tmk_engine* e);
+void tmk_default_config(int32_t line_code, int32_t local_addr, tmk_phy_config* out);
+
+/* LineCode::samples_for_bits / preamble length (line_coding.rs:125-127,295-300,13-21) */
+uint64_t tmk_samples_for_bits(const tmk_phy_config* cfg, uint64_t n_bits);
+uint64_t tmk_preamble_len(const tmk_phy_config* cfg);
+/* number of samples tmk_modulate will produce */
+uint64_t tmk_modulated_len(const tmk_phy_config* cfg, const tmk_frame_desc* frames, uint32_t n_frames,
+                           uint32_t gap_samples);
+
+int tmk_modulate(tmk_engine* e, const tmk_phy_config* cfg, const tmk_frame_desc* frames, uint32_t n_frames,
+                 const uint8_t* payload, uint64_t payload_len, uint32_t gap_samples, float* out_samples,
+                 uint64_t out_cap, uint64_t* out_len);
+
+int tmk_decode_batch(tmk_engine* e, const float* samples, uint64_t total_samples, const tmk_stream* streams,
+                     uint32_t n_streams, tmk_frame_rec* recs, uint64_t rec_cap, uint64_t* n_recs,
+                     uint8_t* payload, uint64_t payload_cap, uint64_t* payload_len);
+
+/* corr_out[offset + i] = correlation of window i of each stream (n_samples - P + 1 windows),
+ * one-shot semantics, energy re-seeded at window 0 only. */
+int tmk_correlate(tmk_engine* e, const float* samples, uint64_t total_samples, const tmk_stream* streams,
+                  uint32_t n_streams, float* corr_out);
+
+/* busy[i] = -1 (fewer than 20 samples), 0 or 1 : mac::is_channel_busy per stream */
+int tmk_channel_busy(tmk_engine* e, const float* samples, uint64_t total_samples, const tmk_stream* streams,
+                     uint32_t n_streams, int8_t* busy);
+
+int tmk_stats(tmk_engine* e, uint64_t counters[TMK_STAT_COUNT]);
+int tmk_stats_reset(tmk_engine* e);
+
+/* plumbing for callers without a CUDA runtime of their own (tests, bench, the Rust shim) */
+int tmk_device_alloc(tmk_engine* e, uint64_t bytes, void** out);
+int tmk_device_free(tmk_engine* e, void* p);
+int tmk_host_alloc_pinned(tmk_engine* e, uint64_t bytes, void** out);
+int tmk_host_free_pinned(tmk_engine* e, void* p);
+int tmk_memcpy_h2d(tmk_engine* e, void* dst, const void* src, uint64_t bytes);
+int tmk_memcpy_d2h(tmk_engine* e, void* dst, const void* src, uint64_t bytes);
+int tmk_synchronize(tmk_engine* e);
+void* tmk_engine_stream(tmk_engine* e); /* the cudaStream_t every kernel is launched on */
+/* device time of the kernels of the last tmk_decode_batch call (CUDA events), ms */
+int tmk_last_kernel_ms(tmk_engine* e, float* ms);
+/* how many kernels this engine has launched so far */
+uint64_t tmk_launch_count(const tmk_engine* e);
+
+/* Synthetic capture generator (measurement harness): fills `samples` (device or
+ * host) with n_streams captures of n_per_stream samples each — random frames (payload
+ * 1..128 B, 10 % ACKs, 10 % foreign dst), random gaps, AWGN of the given SNR — generated on
+ * the GPU from counter-based hashes of (seed, stream). Ground truth (what was sent) is written
+ * to truth records (status = OK, preamble_start, len, seq, dst ...) when truth != NULL. */
+int tmk_synth_batch(tmk_engine* e, const tmk_phy_config* cfg, uint64_t seed, uint32_t n_streams,
+                    uint64_t n_per_stream, float snr_db, float amplitude, float* samples,
+                    tmk_frame_rec* truth, uint64_t truth_cap, uint64_t* n_truth);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* TMKPHY_H */

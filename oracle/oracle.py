@@ -1,0 +1,187 @@
+"""ORACLE — TEST INFRASTRUCTURE ONLY.
+
+ctypes loader for oracle/liboracle.so, the CPU restatement of the reference's src/phy
+(see phy_core.hpp / phy_decoder.hpp for the file:line citations). Imported only by tests/,
+__graft_entry__.smoke() and bench.py's cpu_baseline / --impl reference legs.
+"""
+import ctypes as C
+import os
+import subprocess
+import sys
+
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, os.path.join(os.path.dirname(_HERE), "trackmaker-rs_b200"))
+from tmkphy._abi import (CFG_DTYPE, DESC_DTYPE, REC_DTYPE, STREAM_DTYPE, FrameDesc, FrameRec,  # noqa: E402
+                         PhyConfig, Stream)
+
+LIB = os.path.join(_HERE, "liboracle.so")
+
+
+def build(force=False):
+    srcs = [os.path.join(_HERE, f) for f in ("oracle_capi.cpp", "phy_core.hpp", "phy_decoder.hpp")]
+    if force or not os.path.exists(LIB) or any(os.path.getmtime(s) > os.path.getmtime(LIB) for s in srcs):
+        subprocess.check_call(["make", "-C", _HERE, "-B", "liboracle.so"], stdout=subprocess.DEVNULL)
+
+
+_lib = None
+
+
+def lib():
+    global _lib
+    if _lib is None:
+        if not os.path.exists(LIB):
+            build()
+        L = C.CDLL(LIB)
+        vp, u64, u32 = C.c_void_p, C.c_uint64, C.c_uint32
+        pcfg = C.POINTER(PhyConfig)
+        sig = {
+            "orc_crc8": (C.c_uint8, [vp, u64]),
+            "orc_bytes_to_bits": (u64, [vp, u64, vp]),
+            "orc_bits_to_bytes": (u64, [vp, u64, vp]),
+            "orc_samples_for_bits": (u64, [C.c_int, u32, u64]),
+            "orc_line_encode": (u64, [C.c_int, u32, vp, u64, vp, u64]),
+            "orc_line_decode": (u64, [C.c_int, u32, vp, u64, vp, u64]),
+            "orc_preamble": (u64, [C.c_int, u32, u32, vp, u64]),
+            "orc_frame_to_bytes": (u64, [vp, vp, vp]),
+            "orc_modulate": (u64, [pcfg, vp, u32, vp, u32, vp, u64]),
+            "orc_decode_stream": (u64, [pcfg, vp, u64, u32, vp, u64, vp, u64, C.POINTER(u64)]),
+            "orc_decode_batch_mt": (u64, [vp, vp, u32, C.c_int, vp, u64, vp, u64, C.POINTER(u64),
+                                          C.POINTER(C.c_double)]),
+            "orc_correlate": (u64, [pcfg, vp, u64, vp]),
+            "orc_channel_busy": (C.c_int, [vp, u64]),
+            "orc_hardware_threads": (C.c_int, []),
+        }
+        for n, (r, a) in sig.items():
+            f = getattr(L, n)
+            f.restype, f.argtypes = r, a
+        _lib = L
+    return _lib
+
+
+def make_config(line_code, local_addr=1, spl=3, preamble_bytes=2, threshold=0.9, max_frame_bytes=256, chunk=0):
+    return PhyConfig(line_code, spl, preamble_bytes, local_addr, threshold, max_frame_bytes, chunk)
+
+
+def _ptr(a):
+    return a.ctypes.data_as(C.c_void_p)
+
+
+def crc8(data: bytes) -> int:
+    b = np.frombuffer(bytes(data), dtype=np.uint8)
+    return lib().orc_crc8(_ptr(b) if len(b) else None, len(b))
+
+
+def bytes_to_bits(data: bytes) -> np.ndarray:
+    b = np.frombuffer(bytes(data), dtype=np.uint8)
+    out = np.zeros(len(b) * 8, np.uint8)
+    lib().orc_bytes_to_bits(_ptr(b), len(b), _ptr(out))
+    return out
+
+
+def bits_to_bytes(bits) -> bytes:
+    b = np.ascontiguousarray(bits, dtype=np.uint8)
+    out = np.zeros((len(b) + 7) // 8, np.uint8)
+    lib().orc_bits_to_bytes(_ptr(b), len(b), _ptr(out))
+    return out.tobytes()
+
+
+def samples_for_bits(kind, spl, nbits):
+    return lib().orc_samples_for_bits(kind, spl, nbits)
+
+
+def line_encode(kind, spl, bits) -> np.ndarray:
+    b = np.ascontiguousarray(bits, dtype=np.uint8)
+    n = lib().orc_line_encode(kind, spl, _ptr(b), len(b), None, 0)
+    out = np.zeros(n, np.float32)
+    lib().orc_line_encode(kind, spl, _ptr(b), len(b), _ptr(out), n)
+    return out
+
+
+def line_decode(kind, spl, samples) -> np.ndarray:
+    s = np.ascontiguousarray(samples, dtype=np.float32)
+    out = np.zeros(len(s) + 8, np.uint8)
+    n = lib().orc_line_decode(kind, spl, _ptr(s), len(s), _ptr(out), len(out))
+    return out[:n]
+
+
+def preamble(kind, spl=3, pbytes=2) -> np.ndarray:
+    n = lib().orc_preamble(kind, spl, pbytes, None, 0)
+    out = np.zeros(n, np.float32)
+    lib().orc_preamble(kind, spl, pbytes, _ptr(out), n)
+    return out
+
+
+def make_descs(frames):
+    """frames: list of (type, seq, src, dst, payload bytes) -> (desc array, payload array)"""
+    d = np.zeros(len(frames), DESC_DTYPE)
+    blob = bytearray()
+    for i, (t, seq, src, dst, data) in enumerate(frames):
+        d[i] = (len(blob), len(data), t, seq, src, dst)
+        blob += bytes(data)
+    pl = np.frombuffer(bytes(blob) + b"\0", dtype=np.uint8).copy()
+    return d, pl
+
+
+def frame_to_bytes(t, seq, src, dst, data) -> bytes:
+    d, pl = make_descs([(t, seq, src, dst, data)])
+    out = np.zeros(7 + len(data), np.uint8)
+    n = lib().orc_frame_to_bytes(_ptr(d), _ptr(pl), _ptr(out))
+    return out[:n].tobytes()
+
+
+def modulate(cfg, frames, gap=48) -> np.ndarray:
+    d, pl = make_descs(frames)
+    n = lib().orc_modulate(C.byref(cfg), _ptr(d), len(d), _ptr(pl), gap, None, 0)
+    out = np.zeros(n, np.float32)
+    lib().orc_modulate(C.byref(cfg), _ptr(d), len(d), _ptr(pl), gap, _ptr(out), n)
+    return out
+
+
+def decode_stream(cfg, samples, stream_id=0):
+    """-> (records ndarray[REC_DTYPE], payload ndarray[u8])"""
+    s = np.ascontiguousarray(samples, dtype=np.float32)
+    cap = max(16, len(s) // 8 + 16)
+    recs = np.zeros(cap, REC_DTYPE)
+    pl = np.zeros(max(1024, len(s) // 4), np.uint8)
+    plen = C.c_uint64(0)
+    n = lib().orc_decode_stream(C.byref(cfg), _ptr(s), len(s), stream_id, _ptr(recs), cap, _ptr(pl), len(pl),
+                                C.byref(plen))
+    assert n <= cap and plen.value <= len(pl)
+    return recs[:n].copy(), pl[:plen.value].copy()
+
+
+def decode_batch(samples, streams, n_threads=0, rec_cap=None, payload_cap=None):
+    """-> (records, payload, seconds). streams: ndarray[STREAM_DTYPE]."""
+    s = np.ascontiguousarray(samples, dtype=np.float32)
+    st = np.ascontiguousarray(streams, dtype=STREAM_DTYPE)
+    if n_threads <= 0:
+        n_threads = os.cpu_count() or 1
+    total = int(st["n_samples"].sum())
+    rec_cap = rec_cap or max(1024, total // 64)
+    payload_cap = payload_cap or max(4096, total // 8)
+    recs = np.zeros(rec_cap, REC_DTYPE)
+    pl = np.zeros(payload_cap, np.uint8)
+    plen = C.c_uint64(0)
+    sec = C.c_double(0)
+    n = lib().orc_decode_batch_mt(_ptr(s), _ptr(st), len(st), n_threads, _ptr(recs), rec_cap, _ptr(pl),
+                                  payload_cap, C.byref(plen), C.byref(sec))
+    assert n <= rec_cap and plen.value <= payload_cap, "oracle output capacity too small"
+    return recs[:n].copy(), pl[:plen.value].copy(), sec.value
+
+
+def correlate(cfg, samples) -> np.ndarray:
+    s = np.ascontiguousarray(samples, dtype=np.float32)
+    out = np.zeros(len(s), np.float32)
+    n = lib().orc_correlate(C.byref(cfg), _ptr(s), len(s), _ptr(out))
+    return out[:n]
+
+
+def channel_busy(samples) -> int:
+    s = np.ascontiguousarray(samples, dtype=np.float32)
+    return lib().orc_channel_busy(_ptr(s), len(s))
+
+
+def hardware_threads() -> int:
+    return lib().orc_hardware_threads()

@@ -1,0 +1,174 @@
+// ORACLE — TEST INFRASTRUCTURE ONLY (see phy_core.hpp header). C entry points for ctypes.
+#include <algorithm>
+#include <atomic>
+#include <chrono>
+#include <thread>
+
+#include "phy_decoder.hpp"
+
+using namespace orc;
+
+extern "C" {
+
+uint8_t orc_crc8(const uint8_t* d, uint64_t n) { return crc8(d, n); }
+
+uint64_t orc_bytes_to_bits(const uint8_t* b, uint64_t n, uint8_t* bits) {
+    auto v = bytes_to_bits(b, n);
+    std::copy(v.begin(), v.end(), bits);
+    return v.size();
+}
+
+uint64_t orc_bits_to_bytes(const uint8_t* bits, uint64_t n, uint8_t* bytes) {
+    auto v = bits_to_bytes(bits, n);
+    std::copy(v.begin(), v.end(), bytes);
+    return v.size();
+}
+
+uint64_t orc_samples_for_bits(int kind, uint32_t spl, uint64_t nbits) {
+    return make_line_code(kind, spl)->samples_for_bits(nbits);
+}
+
+// LineCode::encode ; returns number of samples (writes at most cap)
+uint64_t orc_line_encode(int kind, uint32_t spl, const uint8_t* bits, uint64_t nbits, float* out, uint64_t cap) {
+    auto v = make_line_code(kind, spl)->encode(std::vector<uint8_t>(bits, bits + nbits));
+    std::copy(v.begin(), v.begin() + std::min<uint64_t>(cap, v.size()), out);
+    return v.size();
+}
+
+uint64_t orc_line_decode(int kind, uint32_t spl, const float* s, uint64_t n, uint8_t* bits, uint64_t cap) {
+    auto v = make_line_code(kind, spl)->decode(s, n);
+    std::copy(v.begin(), v.begin() + std::min<uint64_t>(cap, v.size()), bits);
+    return v.size();
+}
+
+uint64_t orc_preamble(int kind, uint32_t spl, uint32_t pbytes, float* out, uint64_t cap) {
+    auto v = make_line_code(kind, spl)->generate_preamble(pbytes);
+    std::copy(v.begin(), v.begin() + std::min<uint64_t>(cap, v.size()), out);
+    return v.size();
+}
+
+// Frame::to_bytes
+uint64_t orc_frame_to_bytes(const tmk_frame_desc* f, const uint8_t* payload, uint8_t* out) {
+    Frame fr;
+    fr.type = f->type;
+    fr.seq = f->seq;
+    fr.src = f->src;
+    fr.dst = f->dst;
+    fr.data.assign(payload + f->payload_off, payload + f->payload_off + f->len);
+    auto v = fr.to_bytes();
+    std::copy(v.begin(), v.end(), out);
+    return v.size();
+}
+
+// PhyEncoder::encode_frames
+uint64_t orc_modulate(const tmk_phy_config* cfg, const tmk_frame_desc* frames, uint32_t n_frames,
+                      const uint8_t* payload, uint32_t gap, float* out, uint64_t cap) {
+    Encoder enc(cfg->spl, cfg->preamble_bytes, cfg->line_code);
+    std::vector<Frame> fs(n_frames);
+    for (uint32_t i = 0; i < n_frames; ++i) {
+        fs[i].type = frames[i].type;
+        fs[i].seq = frames[i].seq;
+        fs[i].src = frames[i].src;
+        fs[i].dst = frames[i].dst;
+        fs[i].data.assign(payload + frames[i].payload_off, payload + frames[i].payload_off + frames[i].len);
+    }
+    auto v = enc.encode_frames(fs, gap);
+    std::copy(v.begin(), v.begin() + std::min<uint64_t>(cap, v.size()), out);
+    return v.size();
+}
+
+static void decode_one(const tmk_phy_config& cfg, const float* s, uint64_t n, uint32_t stream_id,
+                       std::vector<tmk_frame_rec>& recs, std::vector<uint8_t>& payload) {
+    Decoder d(cfg);
+    d.stream_id = stream_id;
+    d.recs = &recs;
+    d.payload = &payload;
+    if (cfg.chunk == 0 || cfg.chunk >= n) {
+        d.process_samples(s, n);
+    } else {
+        for (uint64_t p = 0; p < n; p += cfg.chunk) d.process_samples(s + p, std::min<uint64_t>(cfg.chunk, n - p));
+    }
+    d.finish();
+}
+
+// One capture through a fresh PhyDecoder, fed in cfg->chunk sized process_samples calls.
+// Returns the number of records (writes at most rec_cap); *payload_len receives payload bytes.
+uint64_t orc_decode_stream(const tmk_phy_config* cfg, const float* s, uint64_t n, uint32_t stream_id,
+                           tmk_frame_rec* recs, uint64_t rec_cap, uint8_t* payload, uint64_t payload_cap,
+                           uint64_t* payload_len) {
+    std::vector<tmk_frame_rec> r;
+    std::vector<uint8_t> p;
+    decode_one(*cfg, s, n, stream_id, r, p);
+    for (size_t i = 0; i < r.size() && i < rec_cap; ++i) recs[i] = r[i];
+    std::copy(p.begin(), p.begin() + std::min<uint64_t>(payload_cap, p.size()), payload);
+    if (payload_len) *payload_len = p.size();
+    return r.size();
+}
+
+// Ragged batch over a thread pool (one PhyDecoder per stream, like one decoder per MAC node,
+// src/mac/csma.rs:37-47). Records come back sorted by stream; payload offsets are global.
+// Returns records; *seconds receives the wall time of the decode region.
+uint64_t orc_decode_batch_mt(const float* samples, const tmk_stream* streams, uint32_t n_streams, int n_threads,
+                             tmk_frame_rec* recs, uint64_t rec_cap, uint8_t* payload, uint64_t payload_cap,
+                             uint64_t* payload_len, double* seconds) {
+    if (n_threads < 1) n_threads = 1;
+    std::vector<std::vector<tmk_frame_rec>> R(n_streams);
+    std::vector<std::vector<uint8_t>> Pl(n_streams);
+    std::atomic<uint32_t> next{0};
+    auto t0 = std::chrono::steady_clock::now();
+    auto work = [&] {
+        for (;;) {
+            uint32_t s = next.fetch_add(1);
+            if (s >= n_streams) return;
+            decode_one(streams[s].cfg, samples + streams[s].offset, streams[s].n_samples, s, R[s], Pl[s]);
+        }
+    };
+    std::vector<std::thread> th;
+    for (int t = 1; t < n_threads; ++t) th.emplace_back(work);
+    work();
+    for (auto& t : th) t.join();
+    auto t1 = std::chrono::steady_clock::now();
+    if (seconds) *seconds = std::chrono::duration<double>(t1 - t0).count();
+    uint64_t nr = 0, np = 0;
+    for (uint32_t s = 0; s < n_streams; ++s) {
+        for (auto r : R[s]) {
+            r.payload_off += np;
+            if (recs && nr < rec_cap) recs[nr] = r;
+            ++nr;
+        }
+        if (payload && np + Pl[s].size() <= payload_cap) std::copy(Pl[s].begin(), Pl[s].end(), payload + np);
+        np += Pl[s].size();
+    }
+    if (payload_len) *payload_len = np;
+    return nr;
+}
+
+// Correlation of every window in reference arithmetic (one search_for_preamble pass that
+// never stops: seed at window 0, rolling energy, AVX-order dot, energy gate).
+uint64_t orc_correlate(const tmk_phy_config* cfg, const float* s, uint64_t n, float* out) {
+    Decoder d(*cfg);
+    size_t P = d.preamble.size();
+    if (n < P) return 0;
+    size_t windows = n - P + 1;
+    float energy = seq_energy(s, P);
+    for (size_t i = 0; i < windows; ++i) {
+        out[i] = energy < 1e-6f ? 0.0f : dot_avx_order(s + i, d.preamble.data(), P) / (std::sqrt(energy) * d.preamble_energy);
+        if (i + 1 < windows) {
+            energy = energy - s[i] * s[i] + s[i + P] * s[i + P];
+            if (energy < 0.0f) energy = 0.0f;
+        }
+    }
+    return windows;
+}
+
+// mac::is_channel_busy (src/mac/mod.rs:18-27): -1 = None
+int orc_channel_busy(const float* s, uint64_t n) {
+    if (n < 20) return -1;
+    for (uint64_t i = 0; i < n; ++i)
+        if (std::fabs(s[i]) > 0.5f) return 1;
+    return 0;
+}
+
+int orc_hardware_threads(void) { return int(std::thread::hardware_concurrency()); }
+
+}  // extern "C"

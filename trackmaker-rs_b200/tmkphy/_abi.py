@@ -1,0 +1,119 @@
+"""ctypes view of include/tmkphy.h (struct layouts, constants, symbol table).
+
+The shared library is the product; this file is only the binding a Python caller needs.
+There is no fallback: if libtmkphy.so is missing, importing the library raises.
+"""
+import ctypes as C
+import os
+
+import numpy as np
+
+LINE_MANCHESTER = 0
+LINE_4B5B = 1
+FRAME_TYPE_DATA = 1
+FRAME_TYPE_ACK = 2
+
+OK, E_INVALID, E_CUDA, E_CAPACITY, E_NOMEM = 0, -1, -2, -3, -4
+(FRAME_OK, FRAME_HDR_PARSE, FRAME_BAD_LEN, FRAME_SHORT_DECODE, FRAME_NOT_FOR_US, FRAME_CRC_FAIL,
+ FRAME_TRUNCATED) = range(7)
+STATUS_NAMES = ["OK", "HDR_PARSE", "BAD_LEN", "SHORT_DECODE", "NOT_FOR_US", "CRC_FAIL", "TRUNCATED"]
+STAT_NAMES = ["samples", "detections", "frames_ok", "crc_fail", "hdr_fail", "not_for_us", "exact_replays",
+              "candidates"]
+STAT_COUNT = 8
+
+
+class PhyConfig(C.Structure):
+    _fields_ = [("line_code", C.c_int32), ("spl", C.c_uint32), ("preamble_bytes", C.c_uint32),
+                ("local_addr", C.c_int32), ("threshold", C.c_float), ("max_frame_bytes", C.c_uint32),
+                ("chunk", C.c_uint64)]
+
+
+class Stream(C.Structure):
+    _fields_ = [("offset", C.c_uint64), ("n_samples", C.c_uint64), ("cfg", PhyConfig)]
+
+
+class FrameRec(C.Structure):
+    _fields_ = [("stream", C.c_uint32), ("status", C.c_uint32), ("preamble_start", C.c_uint64),
+                ("frame_start", C.c_uint64), ("payload_off", C.c_uint64), ("corr", C.c_float),
+                ("consumed", C.c_uint32), ("len", C.c_uint16), ("crc", C.c_uint8), ("type", C.c_uint8),
+                ("seq", C.c_uint8), ("src", C.c_uint8), ("dst", C.c_uint8), ("hdr_valid", C.c_uint8)]
+
+
+class FrameDesc(C.Structure):
+    _fields_ = [("payload_off", C.c_uint64), ("len", C.c_uint32), ("type", C.c_uint8), ("seq", C.c_uint8),
+                ("src", C.c_uint8), ("dst", C.c_uint8)]
+
+
+assert C.sizeof(PhyConfig) == 32 and C.sizeof(Stream) == 48 and C.sizeof(FrameRec) == 48
+assert C.sizeof(FrameDesc) == 16
+
+# numpy mirrors (zero-copy views of record arrays)
+CFG_DTYPE = np.dtype([("line_code", "<i4"), ("spl", "<u4"), ("preamble_bytes", "<u4"), ("local_addr", "<i4"),
+                      ("threshold", "<f4"), ("max_frame_bytes", "<u4"), ("chunk", "<u8")])
+STREAM_DTYPE = np.dtype([("offset", "<u8"), ("n_samples", "<u8"), ("cfg", CFG_DTYPE)])
+REC_DTYPE = np.dtype([("stream", "<u4"), ("status", "<u4"), ("preamble_start", "<u8"), ("frame_start", "<u8"),
+                      ("payload_off", "<u8"), ("corr", "<f4"), ("consumed", "<u4"), ("len", "<u2"),
+                      ("crc", "u1"), ("type", "u1"), ("seq", "u1"), ("src", "u1"), ("dst", "u1"),
+                      ("hdr_valid", "u1")])
+DESC_DTYPE = np.dtype([("payload_off", "<u8"), ("len", "<u4"), ("type", "u1"), ("seq", "u1"), ("src", "u1"),
+                       ("dst", "u1")])
+assert STREAM_DTYPE.itemsize == 48 and REC_DTYPE.itemsize == 48 and DESC_DTYPE.itemsize == 16
+
+_vp, _u64, _u32, _i32 = C.c_void_p, C.c_uint64, C.c_uint32, C.c_int32
+_pu64 = C.POINTER(C.c_uint64)
+_pcfg = C.POINTER(PhyConfig)
+
+# every symbol include/tmkphy.h declares: name -> (restype, argtypes)
+SYMBOLS = {
+    "tmk_abi_version": (C.c_int, []),
+    "tmk_engine_create": (C.c_int, [C.c_int, C.POINTER(_vp)]),
+    "tmk_engine_destroy": (None, [_vp]),
+    "tmk_last_error": (C.c_char_p, [_vp]),
+    "tmk_default_config": (None, [_i32, _i32, _pcfg]),
+    "tmk_samples_for_bits": (_u64, [_pcfg, _u64]),
+    "tmk_preamble_len": (_u64, [_pcfg]),
+    "tmk_modulated_len": (_u64, [_pcfg, _vp, _u32, _u32]),
+    "tmk_modulate": (C.c_int, [_vp, _pcfg, _vp, _u32, _vp, _u64, _u32, _vp, _u64, _pu64]),
+    "tmk_decode_batch": (C.c_int, [_vp, _vp, _u64, _vp, _u32, _vp, _u64, _pu64, _vp, _u64, _pu64]),
+    "tmk_correlate": (C.c_int, [_vp, _vp, _u64, _vp, _u32, _vp]),
+    "tmk_channel_busy": (C.c_int, [_vp, _vp, _u64, _vp, _u32, _vp]),
+    "tmk_stats": (C.c_int, [_vp, _pu64]),
+    "tmk_stats_reset": (C.c_int, [_vp]),
+    "tmk_device_alloc": (C.c_int, [_vp, _u64, C.POINTER(_vp)]),
+    "tmk_device_free": (C.c_int, [_vp, _vp]),
+    "tmk_host_alloc_pinned": (C.c_int, [_vp, _u64, C.POINTER(_vp)]),
+    "tmk_host_free_pinned": (C.c_int, [_vp, _vp]),
+    "tmk_memcpy_h2d": (C.c_int, [_vp, _vp, _vp, _u64]),
+    "tmk_memcpy_d2h": (C.c_int, [_vp, _vp, _vp, _u64]),
+    "tmk_synchronize": (C.c_int, [_vp]),
+    "tmk_engine_stream": (_vp, [_vp]),
+    "tmk_last_kernel_ms": (C.c_int, [_vp, C.POINTER(C.c_float)]),
+    "tmk_launch_count": (_u64, [_vp]),
+    "tmk_synth_batch": (C.c_int, [_vp, _pcfg, _u64, _u32, _u64, C.c_float, C.c_float, _vp, _vp, _u64, _pu64]),
+}
+
+PKG_DIR = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+LIB_PATH = os.path.join(PKG_DIR, "libtmkphy.so")
+
+_lib = None
+
+
+def load_library(path=None):
+    """dlopen libtmkphy.so and bind every declared symbol. Raises if anything is missing."""
+    global _lib
+    if _lib is not None and path is None:
+        return _lib
+    p = path or LIB_PATH
+    if not os.path.exists(p):
+        raise ImportError(f"libtmkphy.so not found at {p}: run `python __graft_entry__.py build` "
+                          "(there is no CPU fallback)")
+    lib = C.CDLL(p)
+    for name, (res, args) in SYMBOLS.items():
+        fn = getattr(lib, name)  # AttributeError if the symbol is not exported
+        fn.restype = res
+        fn.argtypes = args
+    if lib.tmk_abi_version() != 1:
+        raise ImportError("libtmkphy ABI version mismatch")
+    if path is None:
+        _lib = lib
+    return lib
