@@ -178,6 +178,10 @@ int tmk_synchronize(tmk_engine* e);
 void* tmk_engine_stream(tmk_engine* e); /* the cudaStream_t every kernel is launched on */
 /* device time of the kernels of the last tmk_decode_batch call (CUDA events), ms */
 int tmk_last_kernel_ms(tmk_engine* e, float* ms);
+/* device time of the stages of the last tmk_decode_batch call, ms:
+ * [0] preamble scan kernel(s), [1] walk kernel, [2] record ordering, [3] host->device staging of
+ * the samples (0 when they were already resident) */
+int tmk_last_stage_ms(tmk_engine* e, float ms[4]);
 /* how many kernels this engine has launched so far */
 uint64_t tmk_launch_count(const tmk_engine* e);
 

@@ -1,0 +1,605 @@
+// engine.cu — the C ABI of libtmkphy (include/tmkphy.h): host-side batch plumbing around the
+// scan / walk kernels. No CPU implementation of any PHY stage lives here: every entry point that
+// computes launches CUDA kernels, and fails with TMK_E_CUDA when no sm_100 device is usable.
+#include <algorithm>
+#include <cmath>
+#include <cstdio>
+#include <cstring>
+#include <string>
+#include <vector>
+
+#include "tmk_internal.cuh"
+
+namespace {
+
+struct DevBuf {  // grow-only device scratch
+    void* p = nullptr;
+    size_t cap = 0;
+    cudaError_t reserve(size_t bytes) {
+        if (bytes <= cap) return cudaSuccess;
+        if (p) cudaFree(p);
+        p = nullptr;
+        cap = 0;
+        size_t want = bytes + bytes / 8 + 256;
+        cudaError_t e = cudaMalloc(&p, want);
+        if (e != cudaSuccess) {
+            e = cudaMalloc(&p, bytes);
+            want = bytes;
+        }
+        if (e == cudaSuccess) cap = want;
+        return e;
+    }
+    void release() {
+        if (p) cudaFree(p);
+        p = nullptr;
+        cap = 0;
+    }
+};
+
+}  // namespace
+
+struct tmk_engine {
+    int device = 0;
+    cudaStream_t stream = nullptr;
+    cudaStream_t copy_stream = nullptr;
+    std::string err;
+    std::vector<TmkPattern> patterns;  // host mirror of the device pattern table
+    DevBuf d_patterns, d_streams, d_blk_info, d_cand, d_recs_tmp, d_rec_ord, d_recs, d_payload, d_cnt, d_base,
+        d_counters, d_samples, d_misc, d_misc2;
+    cudaEvent_t ev[6] = {};
+    float stage_ms[4] = {0, 0, 0, 0};
+    uint64_t launches = 0;
+    uint64_t stats[TMK_STAT_COUNT] = {};
+};
+
+namespace {
+
+int fail(tmk_engine* e, int code, const std::string& msg) {
+    if (e) e->err = msg;
+    return code;
+}
+
+#define CK(call)                                                                                   \
+    do {                                                                                           \
+        cudaError_t _err = (call);                                                                 \
+        if (_err != cudaSuccess)                                                                   \
+            return fail(e, _err == cudaErrorMemoryAllocation ? TMK_E_NOMEM : TMK_E_CUDA,           \
+                        std::string(#call) + ": " + cudaGetErrorString(_err));                     \
+    } while (0)
+
+bool is_device_ptr(const void* p) {
+    cudaPointerAttributes a;
+    if (cudaPointerGetAttributes(&a, p) != cudaSuccess) {
+        cudaGetLastError();
+        return false;
+    }
+    return a.type == cudaMemoryTypeDevice || a.type == cudaMemoryTypeManaged;
+}
+
+bool valid_cfg(const tmk_phy_config& c) {
+    if (c.line_code != TMK_LINE_MANCHESTER && c.line_code != TMK_LINE_4B5B) return false;
+    if (c.spl == 0 || c.preamble_bytes == 0 || c.spl > 64 || c.preamble_bytes > 64) return false;
+    const uint64_t P = tmk_sfb(c.line_code, c.spl, 8ull * c.preamble_bytes);
+    if (P > TMK_MAX_P || P / c.spl > TMK_MAX_LEVELS) return false;
+    if (!(c.threshold > 0.0f) || !(c.threshold <= 1.0f)) return false;
+    if (c.local_addr < -1 || c.local_addr > 255) return false;
+    if (c.max_frame_bytes > uint32_t(tmk_walk_max_frame_bytes())) return false;
+    return true;
+}
+
+// LineCode::generate_preamble (line_coding.rs:13-21) as level signs, for either line code
+void build_pattern(const tmk_phy_config& c, TmkPattern* p) {
+    std::memset(p, 0, sizeof *p);
+    p->line_code = c.line_code;
+    p->spl = c.spl;
+    p->preamble_bytes = c.preamble_bytes;
+    std::vector<int> bits;
+    static const int k33[8] = {0, 0, 1, 1, 0, 0, 1, 1}, k5a[8] = {0, 1, 0, 1, 1, 0, 1, 0};
+    for (uint32_t i = 0; i + 1 < c.preamble_bytes; ++i) bits.insert(bits.end(), k33, k33 + 8);
+    bits.insert(bits.end(), k5a, k5a + 8);
+    uint32_t L = 0;
+    if (c.line_code == TMK_LINE_MANCHESTER) {
+        for (int b : bits) {
+            p->levels[L++] = b ? -1.0f : 1.0f;
+            p->levels[L++] = b ? 1.0f : -1.0f;
+        }
+    } else {
+        static const int enc[16] = {0x1e, 0x09, 0x14, 0x15, 0x0a, 0x0b, 0x0e, 0x0f,
+                                    0x12, 0x13, 0x16, 0x17, 0x1a, 0x1b, 0x1c, 0x1d};
+        float level = 1.0f;
+        for (size_t i = 0; i < bits.size(); i += 4) {
+            const int nib = bits[i] << 3 | bits[i + 1] << 2 | bits[i + 2] << 1 | bits[i + 3];
+            for (int j = 4; j >= 0; --j) {
+                if ((enc[nib] >> j) & 1) level = -level;
+                p->levels[L++] = level;
+            }
+        }
+    }
+    p->L = L;
+    p->P = L * c.spl;
+    p->sync_len = uint32_t(tmk_sfb(c.line_code, c.spl, 8));
+    p->margin = uint32_t(tmk_sfb(c.line_code, c.spl, 1));
+    p->hdr_samples = uint32_t(tmk_sfb(c.line_code, c.spl, 8 * TMK_PHY_HEADER_BYTES));
+    // sqrt of a sequential f32 sum of +-1 squares: exact integers, so sqrtf(P) (decoder.rs:46-50,167-171)
+    p->pe = std::sqrt(float(p->P));
+    p->sync_energy = std::sqrt(float(p->sync_len));
+}
+
+// index of the pattern of `c` in the engine's table (uploads the table when it grows)
+int pattern_index(tmk_engine* e, const tmk_phy_config& c, uint32_t* out) {
+    for (size_t i = 0; i < e->patterns.size(); ++i) {
+        const TmkPattern& p = e->patterns[i];
+        if (p.line_code == c.line_code && p.spl == c.spl && p.preamble_bytes == c.preamble_bytes) {
+            *out = uint32_t(i);
+            return TMK_OK;
+        }
+    }
+    TmkPattern p;
+    build_pattern(c, &p);
+    e->patterns.push_back(p);
+    CK(cudaStreamSynchronize(e->stream));
+    CK(e->d_patterns.reserve(sizeof(TmkPattern) * std::max<size_t>(16, e->patterns.size())));
+    CK(cudaMemcpyAsync(e->d_patterns.p, e->patterns.data(), sizeof(TmkPattern) * e->patterns.size(),
+                       cudaMemcpyHostToDevice, e->stream));
+    *out = uint32_t(e->patterns.size() - 1);
+    return TMK_OK;
+}
+
+struct Batch {
+    std::vector<TmkStreamDev> sd;
+    uint64_t n_tiles = 0, n_blocks = 0;
+};
+
+int prepare_batch(tmk_engine* e, uint64_t total_samples, const tmk_stream* streams, uint32_t n_streams, Batch* b) {
+    b->sd.resize(n_streams);
+    uint64_t tiles = 0;
+    for (uint32_t s = 0; s < n_streams; ++s) {
+        const tmk_stream& st = streams[s];
+        if (!valid_cfg(st.cfg)) return fail(e, TMK_E_INVALID, "stream " + std::to_string(s) + ": invalid tmk_phy_config");
+        if (st.offset % 4 != 0) return fail(e, TMK_E_INVALID, "stream offset must be a multiple of 4 samples");
+        if (st.offset > total_samples || st.n_samples > total_samples - st.offset)
+            return fail(e, TMK_E_INVALID, "stream " + std::to_string(s) + " exceeds the sample buffer");
+        TmkStreamDev& d = b->sd[s];
+        uint32_t pi = 0;
+        int rc = pattern_index(e, st.cfg, &pi);
+        if (rc != TMK_OK) return rc;
+        const uint64_t P = e->patterns[pi].P;
+        const uint64_t nwin = st.n_samples >= P ? st.n_samples - P + 1 : 0;
+        d.offset = st.offset;
+        d.n_samples = st.n_samples;
+        d.n_tiles = uint32_t((nwin + TMK_TILE - 1) / TMK_TILE);
+        if (tiles + d.n_tiles > 0x7fffffffull) return fail(e, TMK_E_INVALID, "batch too large (tile count)");
+        d.tile_base = uint32_t(tiles);
+        d.blk_base = tiles * TMK_TILE_BLKS;
+        d.pattern = pi;
+        d.local_addr = st.cfg.local_addr;
+        d.threshold = st.cfg.threshold;
+        d.max_frame_bytes = st.cfg.max_frame_bytes;
+        d.chunk = st.cfg.chunk;
+        tiles += d.n_tiles;
+    }
+    b->n_tiles = tiles;
+    b->n_blocks = tiles * TMK_TILE_BLKS;
+    return TMK_OK;
+}
+
+// device view of caller memory: the pointer itself when it is device memory, else a staged copy
+int stage_in(tmk_engine* e, DevBuf& buf, const void* src, size_t bytes, const void** out) {
+    if (bytes == 0) {
+        *out = nullptr;
+        return TMK_OK;
+    }
+    if (is_device_ptr(src)) {
+        *out = src;
+        return TMK_OK;
+    }
+    CK(buf.reserve(bytes));
+    CK(cudaMemcpyAsync(buf.p, src, bytes, cudaMemcpyHostToDevice, e->stream));
+    *out = buf.p;
+    return TMK_OK;
+}
+
+}  // namespace
+
+extern "C" {
+
+int tmk_abi_version(void) { return TMK_ABI_VERSION; }
+
+int tmk_engine_create(int device, tmk_engine** out) {
+    if (!out) return TMK_E_INVALID;
+    *out = nullptr;
+    int n = 0;
+    if (cudaGetDeviceCount(&n) != cudaSuccess || device < 0 || device >= n) {
+        cudaGetLastError();
+        return TMK_E_CUDA;  // no CPU fallback: without a CUDA device there is no engine
+    }
+    cudaDeviceProp prop;
+    if (cudaGetDeviceProperties(&prop, device) != cudaSuccess || prop.major != 10) return TMK_E_CUDA;  // sm_100a only
+    if (cudaSetDevice(device) != cudaSuccess) return TMK_E_CUDA;
+    tmk_engine* e = new tmk_engine();
+    e->device = device;
+    bool ok = cudaStreamCreateWithFlags(&e->stream, cudaStreamNonBlocking) == cudaSuccess &&
+              cudaStreamCreateWithFlags(&e->copy_stream, cudaStreamNonBlocking) == cudaSuccess;
+    for (int i = 0; ok && i < 6; ++i) ok = cudaEventCreate(&e->ev[i]) == cudaSuccess;
+    ok = ok && tmk_walk_init() == 0;
+    ok = ok && e->d_counters.reserve(sizeof(TmkCounters)) == cudaSuccess;
+    if (!ok) {
+        tmk_engine_destroy(e);
+        return TMK_E_CUDA;
+    }
+    *out = e;
+    return TMK_OK;
+}
+
+void tmk_engine_destroy(tmk_engine* e) {
+    if (!e) return;
+    cudaSetDevice(e->device);
+    if (e->stream) cudaStreamSynchronize(e->stream);
+    DevBuf* bufs[] = {&e->d_patterns, &e->d_streams, &e->d_blk_info, &e->d_cand, &e->d_recs_tmp, &e->d_rec_ord,
+                      &e->d_recs, &e->d_payload, &e->d_cnt, &e->d_base, &e->d_counters, &e->d_samples,
+                      &e->d_misc, &e->d_misc2};
+    for (DevBuf* b : bufs) b->release();
+    for (int i = 0; i < 6; ++i)
+        if (e->ev[i]) cudaEventDestroy(e->ev[i]);
+    if (e->stream) cudaStreamDestroy(e->stream);
+    if (e->copy_stream) cudaStreamDestroy(e->copy_stream);
+    delete e;
+}
+
+const char* tmk_last_error(const tmk_engine* e) { return e ? e->err.c_str() : "null engine"; }
+
+void tmk_default_config(int32_t line_code, int32_t local_addr, tmk_phy_config* out) {
+    if (!out) return;
+    out->line_code = line_code;
+    out->spl = TMK_DEFAULT_SPL;
+    out->preamble_bytes = TMK_DEFAULT_PREAMBLE_BYTES;
+    out->local_addr = local_addr;
+    out->threshold = TMK_DEFAULT_THRESHOLD;
+    out->max_frame_bytes = TMK_DEFAULT_MAX_FRAME_BYTES;
+    out->chunk = 0;
+}
+
+uint64_t tmk_samples_for_bits(const tmk_phy_config* cfg, uint64_t n_bits) {
+    return cfg ? tmk_sfb(cfg->line_code, cfg->spl, n_bits) : 0;
+}
+
+uint64_t tmk_preamble_len(const tmk_phy_config* cfg) {
+    return cfg ? tmk_sfb(cfg->line_code, cfg->spl, 8ull * cfg->preamble_bytes) : 0;
+}
+
+uint64_t tmk_modulated_len(const tmk_phy_config* cfg, const tmk_frame_desc* frames, uint32_t n_frames,
+                           uint32_t gap_samples) {
+    if (!cfg || (!frames && n_frames)) return 0;
+    uint64_t total = 0;
+    for (uint32_t i = 0; i < n_frames; ++i) {
+        total += tmk_preamble_len(cfg) + tmk_sfb(cfg->line_code, cfg->spl, 8ull * (TMK_PHY_HEADER_BYTES + frames[i].len));
+        if (i + 1 < n_frames) total += gap_samples;  // between frames only, encoder.rs:81-83
+    }
+    return total;
+}
+
+int tmk_modulate(tmk_engine* e, const tmk_phy_config* cfg, const tmk_frame_desc* frames, uint32_t n_frames,
+                 const uint8_t* payload, uint64_t payload_len, uint32_t gap_samples, float* out_samples,
+                 uint64_t out_cap, uint64_t* out_len) {
+    if (!e || !cfg || (!frames && n_frames) || !out_len) return fail(e, TMK_E_INVALID, "tmk_modulate: null argument");
+    if (!valid_cfg(*cfg)) return fail(e, TMK_E_INVALID, "tmk_modulate: invalid config");
+    CK(cudaSetDevice(e->device));
+    std::vector<uint64_t> off(n_frames + 1, 0);
+    const uint64_t P = tmk_preamble_len(cfg);
+    for (uint32_t i = 0; i < n_frames; ++i) {
+        if (frames[i].len > 65535u || frames[i].payload_off + frames[i].len > payload_len)
+            return fail(e, TMK_E_INVALID, "tmk_modulate: frame " + std::to_string(i) + " payload out of range");
+        uint64_t flen = P + tmk_sfb(cfg->line_code, cfg->spl, 8ull * (TMK_PHY_HEADER_BYTES + frames[i].len));
+        off[i + 1] = off[i] + flen + (i + 1 < n_frames ? gap_samples : 0);
+    }
+    const uint64_t total = off[n_frames];
+    *out_len = total;
+    if (total > out_cap) return fail(e, TMK_E_CAPACITY, "tmk_modulate: output buffer too small");
+    if (total == 0) return TMK_OK;
+    if (!out_samples) return fail(e, TMK_E_INVALID, "tmk_modulate: null output");
+    uint32_t pi = 0;
+    int rc = pattern_index(e, *cfg, &pi);
+    if (rc != TMK_OK) return rc;
+    // frame table + offsets + payload -> device
+    const size_t fbytes = sizeof(tmk_frame_desc) * n_frames, obytes = sizeof(uint64_t) * (n_frames + 1);
+    CK(e->d_misc.reserve(fbytes + obytes + 16));
+    char* dm = static_cast<char*>(e->d_misc.p);
+    CK(cudaMemcpyAsync(dm, off.data(), obytes, cudaMemcpyHostToDevice, e->stream));
+    CK(cudaMemcpyAsync(dm + obytes, frames, fbytes, cudaMemcpyHostToDevice, e->stream));
+    const void* d_payload = nullptr;
+    rc = stage_in(e, e->d_payload, payload, payload_len, &d_payload);
+    if (rc != TMK_OK) return rc;
+    float* d_out = out_samples;
+    const bool dev_out = is_device_ptr(out_samples);
+    if (!dev_out) {
+        CK(e->d_samples.reserve(total * sizeof(float)));
+        d_out = static_cast<float*>(e->d_samples.p);
+    }
+    e->launches += tmk_launch_modulate(static_cast<const TmkPattern*>(e->d_patterns.p) + pi,
+                                       reinterpret_cast<const tmk_frame_desc*>(dm + obytes),
+                                       reinterpret_cast<const uint64_t*>(dm), n_frames,
+                                       static_cast<const uint8_t*>(d_payload), d_out, e->stream);
+    CK(cudaGetLastError());
+    if (!dev_out) CK(cudaMemcpyAsync(out_samples, d_out, total * sizeof(float), cudaMemcpyDeviceToHost, e->stream));
+    CK(cudaStreamSynchronize(e->stream));
+    return TMK_OK;
+}
+
+int tmk_decode_batch(tmk_engine* e, const float* samples, uint64_t total_samples, const tmk_stream* streams,
+                     uint32_t n_streams, tmk_frame_rec* recs, uint64_t rec_cap, uint64_t* n_recs, uint8_t* payload,
+                     uint64_t payload_cap, uint64_t* payload_len) {
+    if (!e || (!samples && total_samples) || (!streams && n_streams) || !n_recs || !payload_len ||
+        (!recs && rec_cap) || (!payload && payload_cap))
+        return fail(e, TMK_E_INVALID, "tmk_decode_batch: null argument");
+    *n_recs = 0;
+    *payload_len = 0;
+    if (n_streams == 0) return TMK_OK;
+    CK(cudaSetDevice(e->device));
+    Batch b;
+    int rc = prepare_batch(e, total_samples, streams, n_streams, &b);
+    if (rc != TMK_OK) return rc;
+
+    CK(e->d_streams.reserve(sizeof(TmkStreamDev) * n_streams));
+    CK(cudaMemcpyAsync(e->d_streams.p, b.sd.data(), sizeof(TmkStreamDev) * n_streams, cudaMemcpyHostToDevice, e->stream));
+    CK(cudaEventRecord(e->ev[0], e->stream));
+    const void* d_samples = nullptr;
+    rc = stage_in(e, e->d_samples, samples, total_samples * sizeof(float), &d_samples);
+    if (rc != TMK_OK) return rc;
+    CK(e->d_blk_info.reserve(sizeof(float2) * std::max<uint64_t>(1, b.n_blocks)));
+    CK(e->d_cand.reserve(sizeof(uint32_t) * TMK_BLK_WORDS * std::max<uint64_t>(1, b.n_blocks)));
+    CK(e->d_cnt.reserve(sizeof(uint32_t) * n_streams));
+    CK(e->d_base.reserve(sizeof(uint64_t) * (n_streams + 1)));
+
+    const TmkStreamDev* ds = static_cast<const TmkStreamDev*>(e->d_streams.p);
+    const TmkPattern* dp = static_cast<const TmkPattern*>(e->d_patterns.p);
+    const float* dx = static_cast<const float*>(d_samples);
+    float2* dbi = static_cast<float2*>(e->d_blk_info.p);
+    uint32_t* dcb = static_cast<uint32_t*>(e->d_cand.p);
+    TmkCounters* dc = static_cast<TmkCounters*>(e->d_counters.p);
+
+    CK(cudaEventRecord(e->ev[1], e->stream));
+    e->launches += tmk_launch_scan(dx, ds, n_streams, uint32_t(b.n_tiles), dp, dbi, dcb, e->stream);
+    CK(cudaGetLastError());
+    CK(cudaEventRecord(e->ev[2], e->stream));
+
+    // record / payload scratch on the device: start from a guess, rerun the (cheap) walk if the
+    // counts say it was too small and the caller's buffers are larger.
+    const bool recs_dev = rec_cap && is_device_ptr(recs), pay_dev = payload_cap && is_device_ptr(payload);
+    uint64_t dev_rec_cap = std::min<uint64_t>(rec_cap, std::max<uint64_t>(4096, total_samples / 192 + 2ull * n_streams));
+    uint64_t dev_pay_cap = pay_dev ? payload_cap : std::min<uint64_t>(payload_cap, std::max<uint64_t>(65536, total_samples / 24));
+    TmkCounters hc;
+    for (int attempt = 0;; ++attempt) {
+        CK(e->d_recs_tmp.reserve(sizeof(tmk_frame_rec) * std::max<uint64_t>(1, dev_rec_cap)));
+        CK(e->d_rec_ord.reserve(sizeof(uint32_t) * std::max<uint64_t>(1, dev_rec_cap)));
+        if (!pay_dev) CK(e->d_payload.reserve(std::max<uint64_t>(1, dev_pay_cap)));
+        uint8_t* dpay = pay_dev ? payload : static_cast<uint8_t*>(e->d_payload.p);
+        CK(cudaMemsetAsync(dc, 0, sizeof(TmkCounters), e->stream));
+        e->launches += tmk_launch_walk(dx, ds, n_streams, dp, dbi, dcb, static_cast<tmk_frame_rec*>(e->d_recs_tmp.p),
+                                       static_cast<uint32_t*>(e->d_rec_ord.p), dev_rec_cap, dpay, dev_pay_cap,
+                                       static_cast<uint32_t*>(e->d_cnt.p), dc, e->stream);
+        CK(cudaGetLastError());
+        CK(cudaMemcpyAsync(&hc, dc, sizeof hc, cudaMemcpyDeviceToHost, e->stream));
+        CK(cudaStreamSynchronize(e->stream));
+        const bool rec_short = hc.n_recs > dev_rec_cap && dev_rec_cap < rec_cap;
+        const bool pay_short = hc.n_payload > dev_pay_cap && dev_pay_cap < payload_cap;
+        if ((!rec_short && !pay_short) || attempt >= 2) break;
+        if (rec_short) dev_rec_cap = std::min<uint64_t>(rec_cap, hc.n_recs);
+        if (pay_short) dev_pay_cap = std::min<uint64_t>(payload_cap, hc.n_payload);
+    }
+    CK(cudaEventRecord(e->ev[3], e->stream));
+    *n_recs = hc.n_recs;
+    *payload_len = hc.n_payload;
+    for (int i = 0; i < TMK_STAT_COUNT; ++i) e->stats[i] += hc.stats[i];
+    const bool overflow = hc.n_recs > rec_cap || hc.n_payload > payload_cap;
+    if (!overflow && hc.n_recs) {
+        tmk_frame_rec* dout = recs;
+        if (!recs_dev) {
+            CK(e->d_recs.reserve(sizeof(tmk_frame_rec) * hc.n_recs));
+            dout = static_cast<tmk_frame_rec*>(e->d_recs.p);
+        }
+        e->launches += tmk_launch_order(static_cast<const tmk_frame_rec*>(e->d_recs_tmp.p),
+                                        static_cast<const uint32_t*>(e->d_rec_ord.p), hc.n_recs,
+                                        static_cast<const uint32_t*>(e->d_cnt.p), static_cast<uint64_t*>(e->d_base.p),
+                                        n_streams, dout, e->stream);
+        CK(cudaGetLastError());
+        CK(cudaEventRecord(e->ev[4], e->stream));
+        if (!recs_dev)
+            CK(cudaMemcpyAsync(recs, dout, sizeof(tmk_frame_rec) * hc.n_recs, cudaMemcpyDeviceToHost, e->stream));
+        if (!pay_dev && hc.n_payload)
+            CK(cudaMemcpyAsync(payload, e->d_payload.p, hc.n_payload, cudaMemcpyDeviceToHost, e->stream));
+    } else {
+        CK(cudaEventRecord(e->ev[4], e->stream));
+    }
+    CK(cudaStreamSynchronize(e->stream));
+    cudaEventElapsedTime(&e->stage_ms[3], e->ev[0], e->ev[1]);
+    cudaEventElapsedTime(&e->stage_ms[0], e->ev[1], e->ev[2]);
+    cudaEventElapsedTime(&e->stage_ms[1], e->ev[2], e->ev[3]);
+    cudaEventElapsedTime(&e->stage_ms[2], e->ev[3], e->ev[4]);
+    if (overflow) return fail(e, TMK_E_CAPACITY, "tmk_decode_batch: record or payload buffer too small");
+    return TMK_OK;
+}
+
+int tmk_correlate(tmk_engine* e, const float* samples, uint64_t total_samples, const tmk_stream* streams,
+                  uint32_t n_streams, float* corr_out) {
+    if (!e || !samples || !streams || !corr_out) return fail(e, TMK_E_INVALID, "tmk_correlate: null argument");
+    CK(cudaSetDevice(e->device));
+    Batch b;
+    int rc = prepare_batch(e, total_samples, streams, n_streams, &b);
+    if (rc != TMK_OK) return rc;
+    CK(e->d_streams.reserve(sizeof(TmkStreamDev) * n_streams));
+    CK(cudaMemcpyAsync(e->d_streams.p, b.sd.data(), sizeof(TmkStreamDev) * n_streams, cudaMemcpyHostToDevice, e->stream));
+    const void* d_samples = nullptr;
+    rc = stage_in(e, e->d_samples, samples, total_samples * sizeof(float), &d_samples);
+    if (rc != TMK_OK) return rc;
+    float* d_out = corr_out;
+    const bool dev_out = is_device_ptr(corr_out);
+    if (!dev_out) {
+        CK(e->d_misc2.reserve(total_samples * sizeof(float)));
+        d_out = static_cast<float*>(e->d_misc2.p);
+        CK(cudaMemsetAsync(d_out, 0, total_samples * sizeof(float), e->stream));
+    }
+    e->launches += tmk_launch_correlate(static_cast<const float*>(d_samples), static_cast<const TmkStreamDev*>(e->d_streams.p),
+                                        n_streams, static_cast<const TmkPattern*>(e->d_patterns.p), d_out, e->stream);
+    CK(cudaGetLastError());
+    if (!dev_out) CK(cudaMemcpyAsync(corr_out, d_out, total_samples * sizeof(float), cudaMemcpyDeviceToHost, e->stream));
+    CK(cudaStreamSynchronize(e->stream));
+    return TMK_OK;
+}
+
+int tmk_channel_busy(tmk_engine* e, const float* samples, uint64_t total_samples, const tmk_stream* streams,
+                     uint32_t n_streams, int8_t* busy) {
+    if (!e || (!samples && total_samples) || !streams || !busy) return fail(e, TMK_E_INVALID, "tmk_channel_busy: null argument");
+    CK(cudaSetDevice(e->device));
+    std::vector<TmkStreamDev> sd(n_streams);
+    for (uint32_t s = 0; s < n_streams; ++s) {
+        if (streams[s].offset > total_samples || streams[s].n_samples > total_samples - streams[s].offset)
+            return fail(e, TMK_E_INVALID, "tmk_channel_busy: stream exceeds the sample buffer");
+        std::memset(&sd[s], 0, sizeof sd[s]);
+        sd[s].offset = streams[s].offset;
+        sd[s].n_samples = streams[s].n_samples;
+    }
+    CK(e->d_streams.reserve(sizeof(TmkStreamDev) * std::max<uint32_t>(1, n_streams)));
+    CK(cudaMemcpyAsync(e->d_streams.p, sd.data(), sizeof(TmkStreamDev) * n_streams, cudaMemcpyHostToDevice, e->stream));
+    const void* d_samples = nullptr;
+    int rc = stage_in(e, e->d_samples, samples, total_samples * sizeof(float), &d_samples);
+    if (rc != TMK_OK) return rc;
+    int8_t* d_out = busy;
+    const bool dev_out = is_device_ptr(busy);
+    if (!dev_out) {
+        CK(e->d_misc2.reserve(std::max<uint32_t>(1, n_streams)));
+        d_out = static_cast<int8_t*>(e->d_misc2.p);
+    }
+    e->launches += tmk_launch_busy(static_cast<const float*>(d_samples), static_cast<const TmkStreamDev*>(e->d_streams.p),
+                                   n_streams, d_out, e->stream);
+    CK(cudaGetLastError());
+    if (!dev_out && n_streams) CK(cudaMemcpyAsync(busy, d_out, n_streams, cudaMemcpyDeviceToHost, e->stream));
+    CK(cudaStreamSynchronize(e->stream));
+    return TMK_OK;
+}
+
+int tmk_stats(tmk_engine* e, uint64_t counters[TMK_STAT_COUNT]) {
+    if (!e || !counters) return TMK_E_INVALID;
+    for (int i = 0; i < TMK_STAT_COUNT; ++i) counters[i] = e->stats[i];
+    return TMK_OK;
+}
+
+int tmk_stats_reset(tmk_engine* e) {
+    if (!e) return TMK_E_INVALID;
+    for (int i = 0; i < TMK_STAT_COUNT; ++i) e->stats[i] = 0;
+    return TMK_OK;
+}
+
+int tmk_device_alloc(tmk_engine* e, uint64_t bytes, void** out) {
+    if (!e || !out) return TMK_E_INVALID;
+    CK(cudaSetDevice(e->device));
+    CK(cudaMalloc(out, bytes ? bytes : 1));
+    return TMK_OK;
+}
+
+int tmk_device_free(tmk_engine* e, void* p) {
+    if (!e) return TMK_E_INVALID;
+    CK(cudaSetDevice(e->device));
+    CK(cudaFree(p));
+    return TMK_OK;
+}
+
+int tmk_host_alloc_pinned(tmk_engine* e, uint64_t bytes, void** out) {
+    if (!e || !out) return TMK_E_INVALID;
+    CK(cudaSetDevice(e->device));
+    CK(cudaMallocHost(out, bytes ? bytes : 1));
+    return TMK_OK;
+}
+
+int tmk_host_free_pinned(tmk_engine* e, void* p) {
+    if (!e) return TMK_E_INVALID;
+    CK(cudaFreeHost(p));
+    return TMK_OK;
+}
+
+int tmk_memcpy_h2d(tmk_engine* e, void* dst, const void* src, uint64_t bytes) {
+    if (!e) return TMK_E_INVALID;
+    CK(cudaSetDevice(e->device));
+    CK(cudaMemcpyAsync(dst, src, bytes, cudaMemcpyHostToDevice, e->stream));
+    CK(cudaStreamSynchronize(e->stream));
+    return TMK_OK;
+}
+
+int tmk_memcpy_d2h(tmk_engine* e, void* dst, const void* src, uint64_t bytes) {
+    if (!e) return TMK_E_INVALID;
+    CK(cudaSetDevice(e->device));
+    CK(cudaMemcpyAsync(dst, src, bytes, cudaMemcpyDeviceToHost, e->stream));
+    CK(cudaStreamSynchronize(e->stream));
+    return TMK_OK;
+}
+
+int tmk_synchronize(tmk_engine* e) {
+    if (!e) return TMK_E_INVALID;
+    CK(cudaSetDevice(e->device));
+    CK(cudaStreamSynchronize(e->stream));
+    return TMK_OK;
+}
+
+void* tmk_engine_stream(tmk_engine* e) { return e ? static_cast<void*>(e->stream) : nullptr; }
+
+int tmk_last_kernel_ms(tmk_engine* e, float* ms) {
+    if (!e || !ms) return TMK_E_INVALID;
+    *ms = e->stage_ms[0] + e->stage_ms[1] + e->stage_ms[2];
+    return TMK_OK;
+}
+
+int tmk_last_stage_ms(tmk_engine* e, float ms[4]) {
+    if (!e || !ms) return TMK_E_INVALID;
+    for (int i = 0; i < 4; ++i) ms[i] = e->stage_ms[i];
+    return TMK_OK;
+}
+
+uint64_t tmk_launch_count(const tmk_engine* e) { return e ? e->launches : 0; }
+
+int tmk_synth_batch(tmk_engine* e, const tmk_phy_config* cfg, uint64_t seed, uint32_t n_streams, uint64_t n_per_stream,
+                    float snr_db, float amplitude, float* samples, tmk_frame_rec* truth, uint64_t truth_cap,
+                    uint64_t* n_truth) {
+    if (!e || !cfg || !samples || !n_truth || (!truth && truth_cap))
+        return fail(e, TMK_E_INVALID, "tmk_synth_batch: null argument");
+    if (!valid_cfg(*cfg) || n_per_stream % 4 != 0 || n_per_stream >= (1ull << 32))
+        return fail(e, TMK_E_INVALID, "tmk_synth_batch: invalid config or n_per_stream (multiple of 4, < 2^32)");
+    CK(cudaSetDevice(e->device));
+    uint32_t pi = 0;
+    int rc = pattern_index(e, *cfg, &pi);
+    if (rc != TMK_OK) return rc;
+    const TmkPattern* dp = static_cast<const TmkPattern*>(e->d_patterns.p) + pi;
+    const uint64_t total = uint64_t(n_streams) * n_per_stream;
+    float* d_x = samples;
+    const bool dev_out = is_device_ptr(samples);
+    if (!dev_out) {
+        CK(e->d_samples.reserve(total * sizeof(float)));
+        d_x = static_cast<float*>(e->d_samples.p);
+    }
+    const float sigma = snr_db >= 100.0f ? 0.0f : amplitude * std::pow(10.0f, -snr_db / 20.0f);
+    e->launches += tmk_launch_synth_noise(seed, total, sigma, d_x, e->stream);
+    CK(e->d_cnt.reserve(sizeof(uint32_t) * std::max<uint32_t>(1, n_streams)));
+    CK(e->d_base.reserve(sizeof(uint64_t) * (n_streams + 1)));
+    uint32_t* d_cnt = static_cast<uint32_t*>(e->d_cnt.p);
+    uint64_t* d_base = static_cast<uint64_t*>(e->d_base.p);
+    e->launches += tmk_launch_synth_plan(dp, cfg->local_addr, seed, n_streams, n_per_stream, d_cnt, nullptr, nullptr, 0, e->stream);
+    e->launches += tmk_launch_excl_scan(d_cnt, d_base, n_streams, e->stream);
+    uint64_t n_frames = 0;
+    CK(cudaMemcpyAsync(&n_frames, d_base + n_streams, sizeof n_frames, cudaMemcpyDeviceToHost, e->stream));
+    CK(cudaStreamSynchronize(e->stream));
+    *n_truth = n_frames;
+    CK(e->d_recs_tmp.reserve(sizeof(tmk_frame_rec) * std::max<uint64_t>(1, n_frames)));
+    tmk_frame_rec* d_fr = static_cast<tmk_frame_rec*>(e->d_recs_tmp.p);
+    e->launches += tmk_launch_synth_plan(dp, cfg->local_addr, seed, n_streams, n_per_stream, d_cnt, d_base, d_fr, n_frames, e->stream);
+    e->launches += tmk_launch_synth_frames(dp, seed, n_per_stream, amplitude, d_fr, n_frames, d_x, e->stream);
+    CK(cudaGetLastError());
+    if (!dev_out) CK(cudaMemcpyAsync(samples, d_x, total * sizeof(float), cudaMemcpyDeviceToHost, e->stream));
+    if (truth && n_frames) {
+        const uint64_t n = std::min<uint64_t>(n_frames, truth_cap);
+        CK(cudaMemcpyAsync(truth, d_fr, sizeof(tmk_frame_rec) * n,
+                           is_device_ptr(truth) ? cudaMemcpyDeviceToDevice : cudaMemcpyDeviceToHost, e->stream));
+    }
+    CK(cudaStreamSynchronize(e->stream));
+    if (truth && n_frames > truth_cap) return fail(e, TMK_E_CAPACITY, "tmk_synth_batch: truth buffer too small");
+    return TMK_OK;
+}
+
+}  // extern "C"

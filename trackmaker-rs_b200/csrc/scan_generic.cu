@@ -1,0 +1,137 @@
+// scan_generic.cu — preamble scan for ANY (line code, spl, preamble_bytes): sliding correlation
+// with energy normalisation over every window of every stream, one pass over HBM.
+//
+// Replaces the per-sample loop of PhyDecoder::search_for_preamble (src/phy/decoder.rs:138-147)
+// as a *filter*: it marks every window whose correlation may reach the threshold
+// (corr_approx >= thr * TMK_CAND_RATIO) in a bitmap and summarises the window energies of each
+// block of TMK_BLK windows as (min, max). The exact reference decision (AVX summation order,
+// rolling energy) is re-established for the marked windows by the walk kernel (walk.cu).
+//
+// This translation unit is the general-shape kernel; scan_fast.cu holds the kernels specialised
+// for the reference's shipped constants (spl = 3, 2 preamble bytes; src/utils/consts.rs:24-37).
+#include "tmk_internal.cuh"
+
+namespace {
+
+constexpr int kThreads = 256;
+constexpr int kSmemX = TMK_TILE + TMK_MAX_P + 8;
+
+// stream that owns scan tile `tile` (streams are sorted by tile_base)
+__device__ __forceinline__ uint32_t find_stream(const TmkStreamDev* __restrict__ streams, uint32_t n_streams,
+                                                uint32_t tile) {
+    uint32_t lo = 0, hi = n_streams - 1;
+    while (lo < hi) {
+        uint32_t mid = (lo + hi + 1) >> 1;
+        if (streams[mid].tile_base <= tile) lo = mid; else hi = mid - 1;
+    }
+    // skip streams without tiles that share the same tile_base
+    while (streams[lo].n_tiles == 0 && lo + 1 < n_streams) ++lo;
+    return lo;
+}
+
+__global__ void __launch_bounds__(kThreads)
+scan_generic_kernel(const float* __restrict__ samples, const TmkStreamDev* __restrict__ streams,
+                    uint32_t n_streams, const TmkPattern* __restrict__ patterns, float2* __restrict__ blk_info,
+                    uint32_t* __restrict__ cand_bits) {
+    __shared__ float xs[kSmemX];   // raw samples, then box sums of spl samples
+    __shared__ float qs[kSmemX];   // box sums of spl squared samples
+    __shared__ float lev[TMK_MAX_LEVELS];
+    __shared__ uint32_t s_stream;
+
+    const uint32_t tile = blockIdx.x;
+    if (threadIdx.x == 0) s_stream = find_stream(streams, n_streams, tile);
+    __syncthreads();
+    const TmkStreamDev sd = streams[s_stream];
+    const TmkPattern* pat = patterns + sd.pattern;
+    const uint32_t P = pat->P, L = pat->L, spl = pat->spl;
+    const uint64_t n = sd.n_samples;
+    const uint64_t nwin = n - P + 1;  // n >= P, otherwise the stream has no tiles
+    const uint64_t w0 = uint64_t(tile - sd.tile_base) * TMK_TILE;
+    const float* __restrict__ x = samples + sd.offset;
+
+    for (uint32_t l = threadIdx.x; l < L; l += kThreads) lev[l] = pat->levels[l];
+
+    // stage the tile (+ P - 1 halo) in shared memory: coalesced float4 loads, zero fill past the end
+    const uint32_t need = TMK_TILE + P - 1;
+    for (uint32_t i = threadIdx.x * 4; i < need; i += kThreads * 4) {
+        uint64_t g = w0 + i;
+        float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
+        if (g + 3 < n) {
+            v = __ldg(reinterpret_cast<const float4*>(x + g));
+        } else {
+            if (g < n) v.x = x[g];
+            if (g + 1 < n) v.y = x[g + 1];
+            if (g + 2 < n) v.z = x[g + 2];
+        }
+        *reinterpret_cast<float4*>(xs + i) = v;
+    }
+    for (uint32_t i = ((need + 3) & ~3u) + threadIdx.x; i < kSmemX; i += kThreads) xs[i] = 0.f;
+    __syncthreads();
+
+    // box sums over one level (spl samples) of x and x^2, in place via registers
+    {
+        float yb[(kSmemX + kThreads - 1) / kThreads], qb[(kSmemX + kThreads - 1) / kThreads];
+        int c = 0;
+        for (uint32_t i = threadIdx.x; i < need; i += kThreads, ++c) {
+            float y = 0.f, q = 0.f;
+            for (uint32_t k = 0; k < spl; ++k) {
+                float v = (i + k < kSmemX) ? xs[i + k] : 0.f;
+                y += v;
+                q = fmaf(v, v, q);
+            }
+            yb[c] = y;
+            qb[c] = q;
+        }
+        __syncthreads();
+        c = 0;
+        for (uint32_t i = threadIdx.x; i < need; i += kThreads, ++c) {
+            xs[i] = yb[c];
+            qs[i] = qb[c];
+        }
+    }
+    __syncthreads();
+
+    const float thr_c = sd.threshold * TMK_CAND_RATIO;
+    const float kappa = thr_c * thr_c * float(P);
+    const uint32_t warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const uint32_t bw0 = warp * TMK_BLK;  // this warp's block inside the tile
+    float emin = __int_as_float(0x7f800000), emax = 0.f;
+    uint32_t myword = 0;
+#pragma unroll 1
+    for (uint32_t i = 0; i < TMK_BLK_WORDS; ++i) {
+        const uint32_t w = bw0 + i * 32 + lane;
+        float D = 0.f, E = 0.f;
+        for (uint32_t l = 0; l < L; ++l) {
+            D = fmaf(lev[l], xs[w + l * spl], D);
+            E += qs[w + l * spl];
+        }
+        const bool valid = (w0 + w) < nwin;
+        const bool cand = valid && D > 0.f && D * D >= kappa * E;
+        if (valid) {
+            emin = fminf(emin, E);
+            emax = max_nan(emax, E);
+        }
+        const uint32_t word = __ballot_sync(0xffffffffu, cand);
+        if (lane == i) myword = word;
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+        emin = fminf(emin, __shfl_xor_sync(0xffffffffu, emin, o));
+        emax = max_nan(emax, __shfl_xor_sync(0xffffffffu, emax, o));
+    }
+    const uint64_t blk_in_stream = w0 / TMK_BLK + warp;
+    if (blk_in_stream * TMK_BLK < nwin) {
+        const uint64_t gb = sd.blk_base + blk_in_stream;
+        if (lane < TMK_BLK_WORDS) cand_bits[gb * TMK_BLK_WORDS + lane] = myword;
+        if (lane == 0) blk_info[gb] = make_float2(emin, emax);
+    }
+}
+
+}  // namespace
+
+int tmk_launch_scan(const float* samples, const TmkStreamDev* streams, uint32_t n_streams, uint32_t n_tiles,
+                            const TmkPattern* patterns, float2* blk_info, uint32_t* cand_bits, cudaStream_t st) {
+    if (n_tiles == 0) return 0;
+    scan_generic_kernel<<<n_tiles, kThreads, 0, st>>>(samples, streams, n_streams, patterns, blk_info, cand_bits);
+    return 1;
+}

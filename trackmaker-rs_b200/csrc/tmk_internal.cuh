@@ -1,0 +1,126 @@
+// tmk_internal.cuh — shared definitions of libtmkphy's CUDA translation units (sm_100a only).
+//
+// Data layout in HBM:
+//   samples      float[total]             all captures of a batch, stream s at streams[s].offset
+//   blk_info     float2[n_blocks]         per block of TMK_BLK windows: (min, max) window energy
+//   cand_bits    uint32[n_blocks * 8]     1 bit per window: corr_approx >= thr * CAND_RATIO
+//   recs/payload tmk_frame_rec[] / u8[]   verdict records + decoded payload bytes
+//
+// "Exact" device helpers use __fadd_rn/__fmul_rn/__fdiv_rn/__fsqrt_rn so that nvcc never
+// contracts them into FMAs: they reproduce the reference's f32 operation order
+// (src/phy/decoder.rs, src/phy/line_coding.rs) bit for bit.
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include "../../include/tmkphy.h"
+
+#define TMK_BLK 256          // windows per block (candidate bitmap / energy summary granularity)
+#define TMK_BLK_WORDS 8      // TMK_BLK / 32
+#define TMK_TILE_BLKS 8      // blocks per scan tile
+#define TMK_TILE (TMK_BLK * TMK_TILE_BLKS)  // 2048 windows per scan tile
+#define TMK_MAX_P 1024       // longest supported preamble in samples
+#define TMK_MAX_LEVELS 512   // longest supported preamble in levels
+#define TMK_CAND_RATIO 0.9444444f  // candidate filter keeps corr_approx >= thr * (0.85 / 0.9)
+
+// Pattern of one (line_code, spl, preamble_bytes) class, resident in device memory.
+struct TmkPattern {
+    int32_t line_code;
+    uint32_t spl;
+    uint32_t preamble_bytes;
+    uint32_t P;          // preamble samples
+    uint32_t L;          // preamble levels (P / spl)
+    uint32_t sync_len;   // samples_for_bits(8)
+    uint32_t margin;     // samples_for_bits(1)
+    uint32_t hdr_samples;  // samples_for_bits(56)
+    float pe;            // sqrt(sum p^2)           decoder.rs:46-50
+    float sync_energy;   // sqrt(sum sync^2)        decoder.rs:167-171
+    float levels[TMK_MAX_LEVELS];  // +1/-1 per level
+};
+
+// Per-stream work description for the scan / walk kernels.
+struct TmkStreamDev {
+    uint64_t offset;      // first sample (multiple of 4)
+    uint64_t n_samples;
+    uint64_t blk_base;    // first block of this stream in blk_info / cand_bits
+    uint32_t tile_base;   // first scan tile of this stream
+    uint32_t n_tiles;
+    uint32_t pattern;     // index into the pattern table
+    int32_t local_addr;
+    float threshold;
+    uint32_t max_frame_bytes;
+    uint64_t chunk;       // 0 = one shot
+};
+
+struct TmkCounters {
+    unsigned long long n_recs;
+    unsigned long long n_payload;
+    unsigned long long stats[TMK_STAT_COUNT];
+};
+
+__host__ __device__ inline uint64_t tmk_sfb(int line_code, uint32_t spl, uint64_t nbits) {
+    // LineCode::samples_for_bits  line_coding.rs:125-127 (Manchester), :295-300 (4B5B)
+    return line_code == TMK_LINE_MANCHESTER ? nbits * spl * 2 : ((nbits + 3) / 4) * 5 * spl;
+}
+
+#ifdef __CUDACC__
+// ---------------------------------------------------------------- exact f32 helpers
+__device__ __forceinline__ float ex_add(float a, float b) { return __fadd_rn(a, b); }
+__device__ __forceinline__ float ex_sub(float a, float b) { return __fsub_rn(a, b); }
+__device__ __forceinline__ float ex_mul(float a, float b) { return __fmul_rn(a, b); }
+__device__ __forceinline__ float ex_div(float a, float b) { return __fdiv_rn(a, b); }
+__device__ __forceinline__ float ex_sqrt(float a) { return __fsqrt_rn(a); }
+
+// rolling window energy update with clamp, decoder.rs:224-233
+__device__ __forceinline__ float ex_roll(float e, float leaving, float entering) {
+    e = ex_add(ex_sub(e, ex_mul(leaving, leaving)), ex_mul(entering, entering));
+    return e < 0.0f ? 0.0f : e;
+}
+
+// correlation of one window given its dot product and window energy, decoder.rs:142-147
+__device__ __forceinline__ float ex_corr(float dot, float energy, float pe) {
+    if (energy < 1e-6f) return 0.0f;
+    return ex_div(dot, ex_mul(ex_sqrt(energy), pe));
+}
+
+__device__ __forceinline__ float max_nan(float a, float b) {
+    float r;
+    asm("max.NaN.f32 %0, %1, %2;" : "=f"(r) : "f"(a), "f"(b));
+    return r;
+}
+
+// CRC-8 poly 0x07 init 0 (crc.rs:7-22), one byte step
+__device__ __forceinline__ uint32_t crc8_step(uint32_t crc, uint32_t byte) {
+    crc ^= byte;
+#pragma unroll
+    for (int k = 0; k < 8; ++k) crc = (crc & 0x80u) ? ((crc << 1) ^ 0x07u) & 0xFFu : (crc << 1) & 0xFFu;
+    return crc;
+}
+#endif
+
+// kernel launchers (each returns the number of kernels it launched)
+int tmk_launch_scan(const float* samples, const TmkStreamDev* streams, uint32_t n_streams, uint32_t n_tiles,
+                    const TmkPattern* patterns, float2* blk_info, uint32_t* cand_bits, cudaStream_t st);
+int tmk_launch_walk(const float* samples, const TmkStreamDev* streams, uint32_t n_streams,
+                    const TmkPattern* patterns, const float2* blk_info, const uint32_t* cand_bits,
+                    tmk_frame_rec* recs, uint32_t* rec_ord, uint64_t rec_cap, uint8_t* payload,
+                    uint64_t payload_cap, uint32_t* stream_cnt, TmkCounters* counters, cudaStream_t st);
+int tmk_launch_order(const tmk_frame_rec* recs_in, const uint32_t* rec_ord, uint64_t n_recs,
+                     const uint32_t* stream_cnt, uint64_t* stream_base, uint32_t n_streams,
+                     tmk_frame_rec* recs_out, cudaStream_t st);
+int tmk_launch_excl_scan(const uint32_t* cnt, uint64_t* base, uint32_t n, cudaStream_t st);
+int tmk_walk_init();
+int tmk_walk_max_frame_bytes();
+int tmk_launch_correlate(const float* samples, const TmkStreamDev* streams, uint32_t n_streams,
+                         const TmkPattern* patterns, float* corr_out, cudaStream_t st);
+int tmk_launch_busy(const float* samples, const TmkStreamDev* streams, uint32_t n_streams, int8_t* busy,
+                    cudaStream_t st);
+int tmk_launch_modulate(const TmkPattern* pattern, const tmk_frame_desc* frames, const uint64_t* frame_off,
+                        uint32_t n_frames, const uint8_t* payload, float* out, cudaStream_t st);
+// synthetic captures (synth.cu)
+int tmk_launch_synth_noise(uint64_t seed, uint64_t total, float sigma, float* samples, cudaStream_t st);
+int tmk_launch_synth_plan(const TmkPattern* pattern, int32_t local_addr, uint64_t seed, uint32_t n_streams,
+                          uint64_t n_per_stream, uint32_t* counts, const uint64_t* base, tmk_frame_rec* frames,
+                          uint64_t frame_cap, cudaStream_t st);
+int tmk_launch_synth_frames(const TmkPattern* pattern, uint64_t seed, uint64_t n_per_stream, float amplitude,
+                            tmk_frame_rec* frames, uint64_t n_frames, float* samples, cudaStream_t st);

@@ -1,0 +1,741 @@
+// walk.cu — per-stream walk: turns the scan kernel's candidate bitmap into the exact sequence of
+// verdicts the reference decoder produces (src/phy/decoder.rs:68-356), one warp per stream.
+//
+// The walk emulates the PhyDecoder state machine over *sparse* events only:
+//   Searching  (decoder.rs:123-238): the first window with corr >= threshold, where corr uses the
+//              reference's AVX-order dot product (:381-417) and its ROLLING window energy
+//              (:224-233), re-seeded at every search entry. The rolling value E_ref is not
+//              computed; instead  E_ref in [E_c - delta, E_c + delta]  with E_c an accurately
+//              summed window energy and delta a rigorous bound on the rolling drift since the
+//              seed (see DESIGN.md "exactness"). Because corr is monotone in E, evaluating the
+//              reference formula at both ends decides almost every window; the rare undecided
+//              one is replayed sequentially from its seed (TMK_STAT_EXACT_REPLAYS).
+//   refinement (:157-221), Decoding (:242-356), line decode (line_coding.rs:93-123,243-293),
+//              header parse / CRC (frame.rs:109-183, crc.rs:7-22): executed literally, in the
+//              reference's f32 operation order, warp-parallel over offsets / levels / bytes.
+// Chunked feeding (cfg.chunk) is emulated through `avail`, the number of samples the reference
+// would have buffered when it examines a window.
+#include "tmk_internal.cuh"
+
+namespace {
+
+constexpr int kWarpsPerCta = 4;
+constexpr int kMaxFrameBytesCap = 1024;                 // cfg.max_frame_bytes upper limit
+constexpr int kByteBuf = TMK_PHY_HEADER_BYTES + kMaxFrameBytesCap + 9;
+constexpr int kQBuf = TMK_BLK + 256;                    // prefix sums for P <= 255
+constexpr float kU = 5.9604645e-8f;                     // 2^-24, unit roundoff of f32
+constexpr unsigned kFull = 0xffffffffu;
+
+__device__ uint8_t g_crc_pow[kMaxFrameBytesCap + 8];    // x^(8k) mod 0x107, k = 0..
+
+struct WarpScratch {
+    double Q[kQBuf + 1];
+    uint8_t bytes[kByteBuf];
+};
+
+struct Ctx {
+    const float* x;       // stream samples
+    uint64_t N;           // samples in the stream
+    uint64_t nwin;        // windows (N - P + 1, or 0)
+    uint64_t C;           // chunk (0 = one shot)
+    const TmkPattern* pat;
+    const float2* blk_info;
+    const uint32_t* cand_bits;
+    uint64_t nblk;
+    float thr;
+    int32_t local_addr;
+    uint32_t max_frame_bytes;
+    uint32_t P;
+    int lane;
+    WarpScratch* sc;
+    // exact replay cache: rolling energy `rE` of window `rpos` for a chain seeded at `rseed`
+    uint64_t rseed, rpos;
+    float rE;
+    bool rvalid;
+    // stats
+    uint32_t n_replays, n_cands, n_det;
+};
+
+// samples the reference has buffered when it examines window w, given the current `avail`
+__device__ __forceinline__ uint64_t avail_for(const Ctx& c, uint64_t w, uint64_t avail) {
+    if (w + c.P <= avail) return avail;
+    uint64_t t = ((w + c.P + c.C - 1) / c.C) * c.C;  // C > 0 here (one shot has avail == N)
+    return t < c.N ? t : c.N;
+}
+
+// position at which the search that examines window w was (re)entered = where its rolling
+// energy was seeded (decoder.rs:133-136)
+__device__ __forceinline__ uint64_t seed_for(const Ctx& c, uint64_t w, uint64_t q, uint64_t avail) {
+    uint64_t aw = avail_for(c, w, avail);
+    if (aw == avail) return q;
+    uint64_t prev = ((aw - 1) / c.C) * c.C;  // avail of the previous process_samples call
+    if (prev + 1 < uint64_t(c.P)) return q;
+    uint64_t s = prev + 1 - c.P;
+    return s > q ? s : q;
+}
+
+// preamble sample k
+__device__ __forceinline__ float pre(const Ctx& c, uint32_t k) { return c.pat->levels[k / c.pat->spl]; }
+
+// compute_dot_product_avx (decoder.rs:381-417): 8 lanes of mul-then-add, lane l + lane l+4,
+// the 4 partials summed left to right from 0, then the len % 8 tail. Runs per thread.
+__device__ float dot_avx_order(const Ctx& c, const float* __restrict__ w) {
+    const uint32_t P = c.P;
+    float a[8];
+#pragma unroll
+    for (int l = 0; l < 8; ++l) a[l] = 0.0f;
+    uint32_t i = 0;
+    for (; i + 8 <= P; i += 8) {
+#pragma unroll
+        for (int l = 0; l < 8; ++l) a[l] = ex_add(a[l], ex_mul(w[i + l], pre(c, i + l)));
+    }
+    float s = 0.0f;
+#pragma unroll
+    for (int l = 0; l < 4; ++l) s = ex_add(s, ex_add(a[l], a[l + 4]));
+    for (; i < P; ++i) s = ex_add(s, ex_mul(w[i], pre(c, i)));
+    return s;
+}
+
+// iter().map(|x| x * x).sum::<f32>()  — sequential left to right
+__device__ float seq_energy(const float* __restrict__ w, uint32_t n) {
+    float e = 0.0f;
+    for (uint32_t i = 0; i < n; ++i) e = ex_add(e, ex_mul(w[i], w[i]));
+    return e;
+}
+
+// Exact rolling window energy of window `w` for a search seeded at `seed` (decoder.rs:133-136,
+// 224-233). Sequential by construction; all lanes run it redundantly (broadcast loads).
+__device__ float exact_energy(Ctx& c, uint64_t seed, uint64_t w) {
+    float e;
+    uint64_t pos;
+    if (c.rvalid && c.rseed == seed && c.rpos <= w) {
+        e = c.rE;
+        pos = c.rpos;
+    } else {
+        e = seq_energy(c.x + seed, c.P);
+        pos = seed;
+    }
+    const float* __restrict__ x = c.x;
+    const uint32_t P = c.P;
+    // 32 steps at a time: one coalesced load of the leaving / entering samples, then shuffles
+    while (pos < w) {
+        uint64_t left = w - pos;
+        uint32_t n = left < 32 ? uint32_t(left) : 32u;
+        float lv = 0.f, en = 0.f;
+        if (uint32_t(c.lane) < n) {
+            lv = x[pos + c.lane];
+            en = x[pos + P + c.lane];
+        }
+        for (uint32_t j = 0; j < n; ++j) {
+            float l = __shfl_sync(kFull, lv, j), t = __shfl_sync(kFull, en, j);
+            e = ex_roll(e, l, t);
+        }
+        pos += n;
+    }
+    c.rvalid = true;
+    c.rseed = seed;
+    c.rpos = w;
+    c.rE = e;
+    c.n_replays++;
+    return e;
+}
+
+// drift bound of the rolling energy after k steps from a seed, relative to the largest window
+// energy on the chain (|e_k| <= 1.15 u (1.25 P + 2.6 k) Smax for k <= 2^20)
+__device__ __forceinline__ float drift_factor(uint32_t P, uint64_t k) {
+    return 1.2f * kU * (1.25f * float(P) + 2.6f * float(k));
+}
+
+enum { DEC_NO = 0, DEC_YES = 1, DEC_AMBIG = 2 };
+
+// decide corr_ref >= thr (thr > 0) for a window with exact dot D and E_ref in [Ec-delta, Ec+delta].
+// corr = D / (sqrt(E) * pe) is monotone in E under round-to-nearest, and the energy gate
+// (E < 1e-6 -> corr = 0, decoder.rs:142-144) can only turn a detection into a non-detection.
+__device__ __forceinline__ int decide_interval(const Ctx& c, float D, float Ec, float delta) {
+    if (!(D > 0.f)) return DEC_NO;  // corr <= 0, gated 0, or NaN: never >= thr
+    if (!(delta >= 0.f) || !(delta <= 3.0e38f) || !(Ec >= 0.f) || !(Ec <= 3.0e38f) || !(D <= 3.0e38f))
+        return DEC_AMBIG;  // NaN / inf somewhere on the chain: let the literal replay decide
+    float lo = __fsub_rd(Ec, delta), hi = __fadd_ru(Ec, delta);
+    if (!(hi <= 3.0e38f)) return DEC_AMBIG;
+    if (hi < 1e-6f) return DEC_NO;  // gated whatever E_ref is
+    const float lo_g = lo < 1e-6f ? 1e-6f : lo;
+    if (ex_corr(D, lo_g, c.pat->pe) < c.thr) return DEC_NO;  // even the smallest ungated energy fails
+    if (lo >= 1e-6f && ex_corr(D, hi, c.pat->pe) >= c.thr) return DEC_YES;
+    return DEC_AMBIG;
+}
+
+__device__ __forceinline__ double warp_incl_scan_add(double v, int lane) {
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+        double t = __shfl_up_sync(kFull, v, o);
+        if (lane >= o) v += t;
+    }
+    return v;
+}
+
+__device__ __forceinline__ float warp_incl_scan_maxnan(float v, int lane) {
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+        float t = __shfl_up_sync(kFull, v, o);
+        if (lane >= o) v = max_nan(v, t);
+    }
+    return v;
+}
+
+struct Detection {
+    uint64_t c;      // detecting window (preamble start)
+    uint64_t seed;   // where the search that found it was entered (search area start)
+    uint64_t avail;  // samples buffered at that time
+    float corr;      // reference correlation value of the detecting window
+};
+
+// Exact evaluation of window w (literal reference arithmetic). All lanes, uniform arguments.
+__device__ bool exact_window(Ctx& c, uint64_t w, uint64_t seed, float D, float* corr_out) {
+    float e = exact_energy(c, seed, w);
+    float corr = ex_corr(D, e, c.pat->pe);
+    *corr_out = corr;
+    return corr >= c.thr;
+}
+
+// Examine the windows of block `bb` that are >= q, in order. `prevmax` bounds the window
+// energies of the chain before this block. Returns true with *det filled on a detection.
+__device__ bool process_block(Ctx& c, uint64_t bb, uint64_t q, uint64_t avail, float prevmax, Detection* det) {
+    const int lane = c.lane;
+    const uint32_t P = c.P;
+    const uint64_t wb0 = bb * TMK_BLK;
+    const float* __restrict__ x = c.x;
+    const float silent = 0.5f * c.thr * c.thr * 1e-6f;
+    // neighbourhood maximum for the scan kernel's own approximation error
+    float nb = c.blk_info[bb].y;
+    if (bb > 0) nb = max_nan(nb, c.blk_info[bb - 1].y);
+    if (bb + 1 < c.nblk) nb = max_nan(nb, c.blk_info[bb + 1].y);
+    const float dscan = 64.f * kU * nb;
+
+    const bool fast = P <= 255;
+    if (fast) {
+        // prefix sums of the rounded squares in double: E_c(w) = Q[w+P] - Q[w]
+        uint64_t ns64 = c.N - wb0;
+        const uint32_t ns = ns64 < uint64_t(TMK_BLK + P - 1) ? uint32_t(ns64) : TMK_BLK + P - 1;
+        double carry = 0.0;
+        if (lane == 0) c.sc->Q[0] = 0.0;
+        for (uint32_t base = 0; base < ns; base += 32) {
+            uint32_t i = base + lane;
+            float xv = i < ns ? x[wb0 + i] : 0.f;
+            double v = double(ex_mul(xv, xv));
+            v = warp_incl_scan_add(v, lane);
+            if (i < ns) c.sc->Q[i + 1] = carry + v;
+            carry += __shfl_sync(kFull, v, 31);
+        }
+        __syncwarp();
+    }
+    float pmcarry = prevmax * 1.001f;  // block maxima come from the approximate scan
+    const uint32_t* words = c.cand_bits + bb * TMK_BLK_WORDS;
+    for (uint32_t r = 0; r < TMK_BLK_WORDS; ++r) {
+        const uint32_t wl = r * 32 + lane;
+        const uint64_t w = wb0 + wl;
+        const bool valid = w >= q && w < c.nwin;
+        if (!__any_sync(kFull, valid)) continue;
+        float Ec = 0.f;
+        if (valid) {
+            if (fast) {
+                Ec = __double2float_rn(c.sc->Q[wl + P] - c.sc->Q[wl]);
+            } else {
+                double s = 0.0;
+                for (uint32_t k = 0; k < P; ++k) s += double(ex_mul(x[w + k], x[w + k]));
+                Ec = __double2float_rn(s);
+            }
+        }
+        float pm = warp_incl_scan_maxnan(Ec, lane);
+        pm = max_nan(pm, pmcarry);
+        pmcarry = __shfl_sync(kFull, pm, 31);
+        uint64_t seed = q;
+        float delta = 0.f;
+        bool tight = false;
+        if (valid) {
+            seed = seed_for(c, w, q, avail);
+            const uint64_t k = w - seed;
+            delta = drift_factor(P, k) * pm + 2.5f * kU * Ec;
+            if (k > (1u << 20)) delta = __int_as_float(0x7f800000);  // bound not valid: force replay
+            tight = (delta + dscan) <= 0.04f * Ec;
+        }
+        const bool bit = (words[r] >> lane) & 1u;
+        const bool possible = Ec >= silent || !(Ec == Ec);
+        const bool eval = valid && possible && (bit || !tight);
+        uint32_t em = __ballot_sync(kFull, eval);
+        if (em == 0) continue;
+        float D = 0.f;
+        int dec = DEC_NO;
+        if (eval) {
+            D = dot_avx_order(c, x + w);
+            dec = decide_interval(c, D, Ec, delta);
+        }
+        c.n_cands += __popc(em);
+        uint32_t pend = __ballot_sync(kFull, dec != DEC_NO);
+        while (pend) {
+            const int j = __ffs(pend) - 1;
+            pend &= pend - 1;
+            const int dj = __shfl_sync(kFull, dec, j);
+            const uint64_t wj = wb0 + r * 32 + j;
+            const uint64_t sj = __shfl_sync(kFull, seed, j);
+            const float Dj = __shfl_sync(kFull, D, j);
+            float corr;
+            bool hit;
+            if (dj == DEC_YES) {
+                // report the reference's corr value: needs the exact energy only for the record;
+                // use the interval centre (documented: corr in records is within 1e-5)
+                corr = ex_corr(Dj, __shfl_sync(kFull, Ec, j), c.pat->pe);
+                hit = true;
+            } else {
+                hit = exact_window(c, wj, sj, Dj, &corr);
+            }
+            if (hit) {
+                det->c = wj;
+                det->seed = sj;
+                det->avail = avail_for(c, wj, avail);
+                det->corr = corr;
+                return true;
+            }
+        }
+    }
+    return false;
+}
+
+// search_for_preamble over all future calls: first window >= q with corr_ref >= thr.
+__device__ bool search(Ctx& c, uint64_t q, uint64_t avail, Detection* det) {
+    if (c.nwin == 0 || q >= c.nwin) return false;
+    const int lane = c.lane;
+    const float silent = 0.5f * c.thr * c.thr * 1e-6f;
+    float runmax = 0.f;
+    for (uint64_t b0 = q / TMK_BLK; b0 < c.nblk; b0 += 32) {
+        const uint64_t bb = b0 + lane;
+        const bool valid = bb < c.nblk;
+        float2 info = make_float2(0.f, 0.f);
+        bool any = false;
+        if (valid) {
+            info = c.blk_info[bb];
+            const uint4* wp = reinterpret_cast<const uint4*>(c.cand_bits + bb * TMK_BLK_WORDS);
+            uint4 a = wp[0], b = wp[1];
+            any = (a.x | a.y | a.z | a.w | b.x | b.y | b.z | b.w) != 0u;
+        }
+        // neighbourhood maximum (blocks bb-1 .. bb+1) for the scan kernel's own approximation error
+        float nb = max_nan(info.y, max_nan(__shfl_up_sync(kFull, info.y, 1), __shfl_down_sync(kFull, info.y, 1)));
+        if (valid && lane == 0 && bb > 0) nb = max_nan(nb, c.blk_info[bb - 1].y);
+        if (valid && lane == 31 && bb + 1 < c.nblk) nb = max_nan(nb, c.blk_info[bb + 1].y);
+        float incl = warp_incl_scan_maxnan(info.y, lane);
+        float up = __shfl_up_sync(kFull, incl, 1);
+        const float excl = lane == 0 ? runmax : max_nan(runmax, up);
+        const float run = max_nan(runmax, incl);
+        bool need = false;
+        if (valid) {
+            uint64_t wlast = bb * TMK_BLK + (TMK_BLK - 1);
+            if (wlast >= c.nwin) wlast = c.nwin - 1;
+            // longest chain inside the block: last window minus the earliest possible seed
+            const uint64_t wfirst = bb * TMK_BLK > q ? bb * TMK_BLK : q;
+            const uint64_t s_first = seed_for(c, wfirst, q, avail);
+            const uint64_t k = wlast - s_first;
+            float delta = drift_factor(c.P, k) * run * 1.001f + 64.f * kU * nb + 2.5f * kU * info.y;
+            const bool wellcond = k <= (1u << 20) && delta <= 0.04f * info.x;
+            const bool is_silent = info.y < silent;
+            need = !is_silent && (!wellcond || any);
+        }
+        uint32_t m = __ballot_sync(kFull, need);
+        while (m) {
+            const int j = __ffs(m) - 1;
+            m &= m - 1;
+            const float pmax = __shfl_sync(kFull, excl, j);
+            if (process_block(c, b0 + j, q, avail, pmax, det)) return true;
+        }
+        runmax = __shfl_sync(kFull, run, 31);
+    }
+    return false;
+}
+
+// ---------------------------------------------------------------- refinement (decoder.rs:157-221)
+__device__ uint64_t refine(const Ctx& c, const Detection& d) {
+    const TmkPattern* pat = c.pat;
+    const uint32_t P = c.P, sl = pat->sync_len, margin = pat->margin;
+    const float* __restrict__ x = c.x;
+    const uint64_t expect = d.c + P - sl;
+    const uint64_t e_rel = expect - d.seed;  // relative to the search area start
+    const uint64_t lo = d.seed + (e_rel > margin ? e_rel - margin : 0);
+    uint64_t hi = expect + margin;
+    if (hi > d.avail - sl) hi = d.avail - sl;
+    float best = -1.0f;
+    uint64_t best_off = expect;
+    for (uint64_t base = lo; base <= hi; base += 32) {
+        const uint64_t j = base + c.lane;
+        float corr = -2.0f;
+        if (j <= hi) {
+            float dot = 0.0f, we = 0.0f;
+            for (uint32_t t = 0; t < sl; ++t) {
+                const float w = x[j + t];
+                dot = ex_add(dot, ex_mul(w, pre(c, P - sl + t)));
+                we = ex_add(we, ex_mul(w, w));
+            }
+            corr = (we > 1e-6f && pat->sync_energy > 1e-6f) ? ex_div(dot, ex_mul(ex_sqrt(we), pat->sync_energy)) : 0.0f;
+            if (!(corr == corr)) corr = -2.0f;  // NaN never satisfies `corr > best_corr`
+        }
+        // first strict maximum: larger value wins, ties go to the lower offset
+        float v = corr;
+        int idx = c.lane;
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) {
+            const float ov = __shfl_xor_sync(kFull, v, o);
+            const int oi = __shfl_xor_sync(kFull, idx, o);
+            if (ov > v || (ov == v && oi < idx)) {
+                v = ov;
+                idx = oi;
+            }
+        }
+        if (v > best) {
+            best = v;
+            best_off = base + idx;
+        }
+    }
+    return best_off + sl;
+}
+
+// ---------------------------------------------------------------- line decode
+__constant__ int8_t c_dec5[32] = {  // decode_4b5b_symbol, line_coding.rs:157-180 (-1 = invalid)
+    -1, -1, -1, -1, -1, -1, -1, -1, -1, 1, 4, 5, -1, -1, 6, 7,
+    -1, -1, 8, 9, 2, 3, 10, 11, -1, -1, 12, 13, 14, 15, 0, -1};
+
+// f32 mean of one level: sequential sum from 0, one divide (line_coding.rs:104-113, 258-261)
+__device__ __forceinline__ float level_mean(const float* __restrict__ s, uint32_t spl) {
+    float acc = 0.0f;
+    for (uint32_t i = 0; i < spl; ++i) acc = ex_add(acc, s[i]);
+    return ex_div(acc, float(spl));
+}
+
+// LineCode::decode over the samples of `total_bits` bits starting at fs. Writes MSB-first packed
+// bytes (crc.rs:63-75) to c.sc->bytes and returns the number of bits decoded (4B5B stops at the
+// first invalid symbol, line_coding.rs:281-286).
+__device__ uint32_t line_decode(const Ctx& c, uint64_t fs, uint32_t total_bits) {
+    const float* __restrict__ s = c.x + fs;
+    const uint32_t spl = c.pat->spl;
+    const int lane = c.lane;
+    uint8_t* bytes = c.sc->bytes;
+    if (c.pat->line_code == TMK_LINE_MANCHESTER) {
+        for (uint32_t b0 = 0; b0 < total_bits; b0 += 32) {
+            const uint32_t bi = b0 + lane;
+            bool bit = false;
+            if (bi < total_bits) {
+                const float a = level_mean(s + uint64_t(bi) * 2 * spl, spl);
+                const float b = level_mean(s + uint64_t(bi) * 2 * spl + spl, spl);
+                bit = !(a > b);  // first_half > second_half -> 0, else 1 (tie -> 1)
+            }
+            const uint32_t rev = __brev(__ballot_sync(kFull, bit));
+            if (lane < 4 && b0 + lane * 8 < total_bits) bytes[b0 / 8 + lane] = uint8_t(rev >> (24 - 8 * lane));
+        }
+        __syncwarp();
+        return total_bits;
+    }
+    const uint32_t nlev = (total_bits / 4) * 5;
+    float last = 1.0f;  // prev_level_avg restarts at 1.0 on every decode call (line_coding.rs:251)
+    uint32_t nb = 0, hi = 0;
+    bool stop = false;
+    for (uint32_t l0 = 0; l0 < nlev && !stop; l0 += 30) {
+        const uint32_t li = l0 + lane;
+        const bool active = lane < 30 && li < nlev;
+        const float cur = active ? level_mean(s + uint64_t(li) * spl, spl) : 0.0f;
+        const bool valid = active && fabsf(cur) > 1e-6f;
+        const uint32_t vm = __ballot_sync(kFull, valid);
+        const uint32_t below = vm & ((1u << lane) - 1u);
+        const int src = below ? 31 - __clz(below) : 0;
+        const float pv = __shfl_sync(kFull, cur, src);
+        const float lastv = below ? pv : last;
+        const bool bit = active && ex_mul(lastv, cur) < 0.0f;
+        const uint32_t bm = __ballot_sync(kFull, bit);
+        if (vm) last = __shfl_sync(kFull, cur, 31 - __clz(vm));
+        uint32_t nsy = (nlev - l0) / 5;
+        if (nsy > 6) nsy = 6;
+        for (uint32_t k = 0; k < nsy; ++k) {
+            uint32_t sym = 0;
+#pragma unroll
+            for (int j = 0; j < 5; ++j) sym = (sym << 1) | ((bm >> (5 * k + j)) & 1u);
+            const int nib = c_dec5[sym];
+            if (nib < 0) {
+                stop = true;
+                break;
+            }
+            if ((nb & 7u) == 0) {
+                hi = uint32_t(nib) << 4;
+            } else if (lane == 0) {
+                bytes[nb >> 3] = uint8_t(hi | uint32_t(nib));
+            }
+            nb += 4;
+        }
+    }
+    if ((nb & 7u) == 4 && lane == 0) bytes[nb >> 3] = uint8_t(hi);  // trailing nibble, low bits zero
+    __syncwarp();
+    return nb;
+}
+
+// CRC-8 (poly 0x07, init 0; crc.rs:7-22) of bytes[0..n), lane-parallel:
+// crc = XOR_i  b_i(x) * x^(8(n-i)) mod g
+__device__ uint32_t crc8_warp(const uint8_t* bytes, uint32_t n, int lane) {
+    uint32_t acc = 0;
+    for (uint32_t i = lane; i < n; i += 32) {
+        const uint32_t a = bytes[i], w = g_crc_pow[n - i];
+        uint32_t p = 0;
+#pragma unroll
+        for (int j = 0; j < 8; ++j) p ^= ((a >> j) & 1u) ? (w << j) : 0u;
+#pragma unroll
+        for (int k = 14; k >= 8; --k) p ^= ((p >> k) & 1u) ? (0x107u << (k - 8)) : 0u;
+        acc ^= p & 0xffu;
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) acc ^= __shfl_xor_sync(kFull, acc, o);
+    return acc;
+}
+
+// ---------------------------------------------------------------- verdict records
+struct Emit {
+    tmk_frame_rec* recs;
+    uint32_t* rec_ord;
+    uint64_t rec_cap;
+    uint8_t* payload;
+    uint64_t payload_cap;
+    TmkCounters* counters;
+    uint32_t stream;
+    uint32_t ord;  // records emitted by this stream so far
+};
+
+__device__ void emit(const Ctx& c, Emit& em, uint32_t status, const Detection& d, uint64_t frame_start,
+                     uint32_t consumed, bool have_hdr, const uint8_t* hdr, uint32_t data_len) {
+    unsigned long long slot = 0, poff = 0;
+    if (c.lane == 0) {
+        slot = atomicAdd(&em.counters->n_recs, 1ull);
+        if (data_len) poff = atomicAdd(&em.counters->n_payload, (unsigned long long)data_len);
+    }
+    slot = __shfl_sync(kFull, slot, 0);
+    poff = __shfl_sync(kFull, poff, 0);
+    if (data_len && poff + data_len <= em.payload_cap) {
+        for (uint32_t i = c.lane; i < data_len; i += 32) em.payload[poff + i] = c.sc->bytes[TMK_PHY_HEADER_BYTES + i];
+    }
+    if (c.lane == 0 && slot < em.rec_cap) {
+        tmk_frame_rec r;
+        r.stream = em.stream;
+        r.status = status;
+        r.preamble_start = d.c;
+        r.frame_start = frame_start;
+        r.payload_off = poff;
+        r.corr = d.corr;
+        r.consumed = consumed;
+        r.len = have_hdr ? uint16_t((uint32_t(hdr[0]) << 8) | hdr[1]) : 0;
+        r.crc = have_hdr ? hdr[2] : 0;
+        r.type = have_hdr ? hdr[3] : 0;
+        r.seq = have_hdr ? hdr[4] : 0;
+        r.src = have_hdr ? hdr[5] : 0;
+        r.dst = have_hdr ? hdr[6] : 0;
+        r.hdr_valid = have_hdr ? 1 : 0;
+        em.recs[slot] = r;
+        em.rec_ord[slot] = em.ord;
+    }
+    em.ord++;
+}
+
+__global__ void __launch_bounds__(kWarpsPerCta * 32)
+walk_kernel(const float* __restrict__ samples, const TmkStreamDev* __restrict__ streams, uint32_t n_streams,
+            const TmkPattern* __restrict__ patterns, const float2* __restrict__ blk_info,
+            const uint32_t* __restrict__ cand_bits, tmk_frame_rec* recs, uint32_t* rec_ord, uint64_t rec_cap,
+            uint8_t* payload, uint64_t payload_cap, uint32_t* stream_cnt, TmkCounters* counters) {
+    __shared__ WarpScratch scratch[kWarpsPerCta];
+    const uint32_t warp = threadIdx.x >> 5;
+    const uint32_t sidx = blockIdx.x * kWarpsPerCta + warp;
+    if (sidx >= n_streams) return;
+    const TmkStreamDev sd = streams[sidx];
+    Ctx c;
+    c.x = samples + sd.offset;
+    c.N = sd.n_samples;
+    c.pat = patterns + sd.pattern;
+    c.P = c.pat->P;
+    c.nwin = c.N >= c.P ? c.N - c.P + 1 : 0;
+    c.C = (sd.chunk == 0 || sd.chunk >= c.N) ? 0 : sd.chunk;
+    c.blk_info = blk_info + sd.blk_base;
+    c.cand_bits = cand_bits + sd.blk_base * TMK_BLK_WORDS;
+    c.nblk = (c.nwin + TMK_BLK - 1) / TMK_BLK;
+    c.thr = sd.threshold;
+    c.local_addr = sd.local_addr;
+    c.max_frame_bytes = sd.max_frame_bytes;
+    c.lane = threadIdx.x & 31;
+    c.sc = &scratch[warp];
+    c.rvalid = false;
+    c.rseed = c.rpos = 0;
+    c.rE = 0.f;
+    c.n_replays = c.n_cands = c.n_det = 0;
+    Emit em{recs, rec_ord, rec_cap, payload, payload_cap, counters, sidx, 0};
+    uint32_t n_ok = 0, n_crc = 0, n_hdr = 0, n_nfu = 0;
+
+    const int lc = c.pat->line_code;
+    const uint32_t spl = c.pat->spl;
+    const uint32_t hs = c.pat->hdr_samples;
+    uint64_t q = 0;                           // buffer_offset (absolute)
+    uint64_t avail = c.C ? c.C : c.N;         // samples fed so far
+    Detection d;
+    while (search(c, q, avail, &d)) {
+        c.n_det++;
+        avail = d.avail;
+        const uint64_t fs = refine(c, d);
+        // ---- decode_frame (decoder.rs:242-356); `avail` grows by one chunk per call
+        bool truncated = false;
+        while (avail < fs + hs) {
+            if (avail >= c.N) { truncated = true; break; }
+            avail = avail + c.C < c.N ? avail + c.C : c.N;
+        }
+        if (truncated) {
+            emit(c, em, TMK_FRAME_TRUNCATED, d, fs, 0, false, nullptr, 0);
+            break;
+        }
+        const uint8_t* hb = c.sc->bytes;
+        const uint32_t hbits = line_decode(c, fs, 8 * TMK_PHY_HEADER_BYTES);
+        const bool have7 = (hbits + 7) / 8 >= TMK_PHY_HEADER_BYTES;
+        uint8_t hdr[TMK_PHY_HEADER_BYTES];
+        for (int i = 0; i < TMK_PHY_HEADER_BYTES; ++i) hdr[i] = have7 ? hb[i] : 0;
+        __syncwarp();
+        const uint32_t type = hdr[3];
+        if (!have7 || (type != TMK_FRAME_TYPE_DATA && type != TMK_FRAME_TYPE_ACK)) {  // :266-273
+            emit(c, em, TMK_FRAME_HDR_PARSE, d, fs, hs, have7, hdr, 0);
+            n_hdr++;
+            q = d.c + hs;
+            continue;
+        }
+        const uint32_t len = (uint32_t(hdr[0]) << 8) | hdr[1];
+        if ((type == TMK_FRAME_TYPE_DATA && len == 0) || len > c.max_frame_bytes) {  // :277-286
+            emit(c, em, TMK_FRAME_BAD_LEN, d, fs, 1, true, hdr, 0);
+            n_hdr++;
+            q = d.c + 1;
+            continue;
+        }
+        const uint32_t total_bits = (TMK_PHY_HEADER_BYTES + len) * 8;
+        const uint64_t total_samples = tmk_sfb(lc, spl, total_bits);
+        while (avail < fs + total_samples) {
+            if (avail >= c.N) { truncated = true; break; }
+            avail = avail + c.C < c.N ? avail + c.C : c.N;
+        }
+        if (truncated) {
+            emit(c, em, TMK_FRAME_TRUNCATED, d, fs, 0, false, nullptr, 0);
+            break;
+        }
+        const uint32_t nbits = line_decode(c, fs, total_bits);
+        const uint32_t consumed = c.P + uint32_t(tmk_sfb(lc, spl, nbits));  // :306-309
+        q = d.c + consumed;
+        if (nbits < total_bits) {  // :311-320
+            emit(c, em, TMK_FRAME_SHORT_DECODE, d, fs, consumed, true, hdr, 0);
+            n_hdr++;
+            continue;
+        }
+        if (c.local_addr >= 0 && hdr[6] != uint32_t(c.local_addr)) {  // :322-329
+            emit(c, em, TMK_FRAME_NOT_FOR_US, d, fs, consumed, true, hdr, len);
+            n_nfu++;
+            continue;
+        }
+        const uint32_t crc = crc8_warp(c.sc->bytes + TMK_PHY_HEADER_BYTES, len, c.lane);
+        if (crc != hdr[2]) {  // frame.rs:155-159
+            emit(c, em, TMK_FRAME_CRC_FAIL, d, fs, consumed, true, hdr, len);
+            n_crc++;
+            continue;
+        }
+        emit(c, em, TMK_FRAME_OK, d, fs, consumed, true, hdr, len);
+        n_ok++;
+    }
+    if (c.lane == 0) {
+        stream_cnt[sidx] = em.ord;
+        atomicAdd(&counters->stats[TMK_STAT_SAMPLES], (unsigned long long)c.N);
+        atomicAdd(&counters->stats[TMK_STAT_DETECTIONS], (unsigned long long)c.n_det);
+        atomicAdd(&counters->stats[TMK_STAT_FRAMES_OK], (unsigned long long)n_ok);
+        atomicAdd(&counters->stats[TMK_STAT_CRC_FAIL], (unsigned long long)n_crc);
+        atomicAdd(&counters->stats[TMK_STAT_HDR_FAIL], (unsigned long long)n_hdr);
+        atomicAdd(&counters->stats[TMK_STAT_NOT_FOR_US], (unsigned long long)n_nfu);
+        atomicAdd(&counters->stats[TMK_STAT_EXACT_REPLAYS], (unsigned long long)c.n_replays);
+        atomicAdd(&counters->stats[TMK_STAT_CANDIDATES], (unsigned long long)c.n_cands);
+    }
+}
+
+// ---------------------------------------------------------------- ordering of the records
+// exclusive scan of the per-stream record counts (single CTA; n_streams is small next to the samples)
+__global__ void __launch_bounds__(1024)
+scan_counts_kernel(const uint32_t* __restrict__ cnt, uint64_t* __restrict__ base, uint32_t n) {
+    __shared__ uint64_t warp_tot[32];
+    __shared__ uint64_t carry_s;
+    if (threadIdx.x == 0) carry_s = 0;
+    __syncthreads();
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    for (uint32_t b0 = 0; b0 < n; b0 += 1024) {
+        const uint32_t i = b0 + threadIdx.x;
+        const uint64_t v = i < n ? cnt[i] : 0;
+        uint64_t s = v;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            uint64_t t = __shfl_up_sync(kFull, s, o);
+            if (lane >= o) s += t;
+        }
+        if (lane == 31) warp_tot[warp] = s;
+        __syncthreads();
+        if (warp == 0) {
+            uint64_t w = warp_tot[lane], ws = w;
+#pragma unroll
+            for (int o = 1; o < 32; o <<= 1) {
+                uint64_t t = __shfl_up_sync(kFull, ws, o);
+                if (lane >= o) ws += t;
+            }
+            warp_tot[lane] = ws - w;  // exclusive
+        }
+        __syncthreads();
+        const uint64_t c0 = carry_s;
+        if (i < n) base[i] = c0 + warp_tot[warp] + s - v;
+        __syncthreads();
+        if (threadIdx.x == 1023) carry_s = c0 + warp_tot[31] + s;
+        __syncthreads();
+    }
+    if (threadIdx.x == 0) base[n] = carry_s;
+}
+
+__global__ void order_kernel(const tmk_frame_rec* __restrict__ in, const uint32_t* __restrict__ ord, uint64_t n,
+                             const uint64_t* __restrict__ base, tmk_frame_rec* __restrict__ out) {
+    const uint64_t i = uint64_t(blockIdx.x) * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const tmk_frame_rec r = in[i];
+    out[base[r.stream] + ord[i]] = r;
+}
+
+}  // namespace
+
+int tmk_walk_init() {
+    uint8_t tab[kMaxFrameBytesCap + 8];
+    uint32_t v = 1;  // x^0
+    for (int k = 0; k < kMaxFrameBytesCap + 8; ++k) {
+        tab[k] = uint8_t(v);
+        for (int b = 0; b < 8; ++b) v = (v & 0x80u) ? ((v << 1) ^ 0x07u) & 0xffu : (v << 1) & 0xffu;  // times x^8
+    }
+    return cudaMemcpyToSymbol(g_crc_pow, tab, sizeof tab) == cudaSuccess ? 0 : -1;
+}
+
+int tmk_walk_max_frame_bytes() { return kMaxFrameBytesCap; }
+
+// base[i] = sum of cnt[0..i), base[n] = total
+int tmk_launch_excl_scan(const uint32_t* cnt, uint64_t* base, uint32_t n, cudaStream_t st) {
+    scan_counts_kernel<<<1, 1024, 0, st>>>(cnt, base, n);
+    return 1;
+}
+
+int tmk_launch_walk(const float* samples, const TmkStreamDev* streams, uint32_t n_streams,
+                    const TmkPattern* patterns, const float2* blk_info, const uint32_t* cand_bits,
+                    tmk_frame_rec* recs, uint32_t* rec_ord, uint64_t rec_cap, uint8_t* payload,
+                    uint64_t payload_cap, uint32_t* stream_cnt, TmkCounters* counters, cudaStream_t st) {
+    if (n_streams == 0) return 0;
+    const uint32_t grid = (n_streams + kWarpsPerCta - 1) / kWarpsPerCta;
+    walk_kernel<<<grid, kWarpsPerCta * 32, 0, st>>>(samples, streams, n_streams, patterns, blk_info, cand_bits, recs,
+                                                    rec_ord, rec_cap, payload, payload_cap, stream_cnt, counters);
+    return 1;
+}
+
+int tmk_launch_order(const tmk_frame_rec* recs_in, const uint32_t* rec_ord, uint64_t n_recs,
+                     const uint32_t* stream_cnt, uint64_t* stream_base, uint32_t n_streams,
+                     tmk_frame_rec* recs_out, cudaStream_t st) {
+    tmk_launch_excl_scan(stream_cnt, stream_base, n_streams, st);
+    if (n_recs == 0) return 1;
+    const uint32_t grid = uint32_t((n_recs + 255) / 256);
+    order_kernel<<<grid, 256, 0, st>>>(recs_in, rec_ord, n_recs, stream_base, recs_out);
+    return 2;
+}
