@@ -182,6 +182,9 @@ int tmk_last_kernel_ms(tmk_engine* e, float* ms);
  * [0] preamble scan kernel(s), [1] walk kernel, [2] record ordering, [3] host->device staging of
  * the samples (0 when they were already resident) */
 int tmk_last_stage_ms(tmk_engine* e, float ms[4]);
+/* CUDA-event stopwatch on the engine's stream (for callers without a CUDA runtime of their own) */
+int tmk_timer_start(tmk_engine* e);
+int tmk_timer_stop(tmk_engine* e, float* ms);
 /* how many kernels this engine has launched so far */
 uint64_t tmk_launch_count(const tmk_engine* e);
 

@@ -1,0 +1,106 @@
+"""The oracle against every literal / known answer the reference's own unit tests hold for the
+PHY path: src/phy/crc.rs:77-109, src/phy/line_coding.rs:335-377,
+src/phy/encoder.rs:100-128, plus the CRC-8/SMBUS check value and the derived loopback offsets
+of `trackmaker-rs test` (src/main.rs:480-589) on assets/think-different.txt."""
+import os
+
+import numpy as np
+import pytest
+
+GOLDEN = os.path.join(os.path.dirname(__file__), "golden")
+MAN, FB = 0, 1
+
+
+def test_bit_conversion(orc):  # crc.rs:94-99
+    assert list(orc.bytes_to_bits(bytes([0b10110011]))) == [1, 0, 1, 1, 0, 0, 1, 1]
+    assert orc.bits_to_bytes([1, 0, 1, 1, 0, 0, 1, 1]) == bytes([0b10110011])
+
+
+def test_bytes_bits_roundtrip(orc):  # crc.rs:102-108
+    b = bytes([0xAB, 0xCD, 0xEF])
+    bits = orc.bytes_to_bits(b)
+    assert len(bits) == 24 and orc.bits_to_bytes(bits) == b
+    assert orc.bits_to_bytes([1, 1, 1]) == bytes([0b11100000])  # partial byte zero padded low, crc.rs:63-75
+
+
+def test_crc8(orc):  # crc.rs:82-91 + CRC-8/SMBUS check value
+    data = b"Hello, World!"
+    c = orc.crc8(data)
+    assert c == orc.crc8(data) == 0x87
+    assert orc.crc8(b"Hallo, World!") != c
+    assert orc.crc8(b"123456789") == 0xF4
+    assert orc.crc8(b"") == 0
+
+
+def test_manchester_roundtrip_and_preamble(orc):  # line_coding.rs:340-355
+    bits = [0, 1, 0, 1, 1, 0, 1, 0]
+    s = orc.line_encode(MAN, 2, bits)
+    assert len(s) == 32 and list(orc.line_decode(MAN, 2, s)) == bits
+    assert list(s[:8]) == [1, 1, -1, -1, -1, -1, 1, 1]  # 0 -> high,low ; 1 -> low,high
+    assert len(orc.preamble(MAN, 2, 2)) == 64
+
+
+def test_4b5b_roundtrip_and_preamble(orc):  # line_coding.rs:358-376
+    bits = [1, 0, 1, 0, 0, 1, 1, 1, 0, 0, 0, 0, 1, 1, 1, 1]
+    s = orc.line_encode(FB, 4, bits)
+    assert len(s) == 4 * 5 * 4 and list(orc.line_decode(FB, 4, s)) == bits
+    assert len(orc.preamble(FB, 4, 2)) == 80
+    # partial nibble is zero padded on encode (line_coding.rs:204-215)
+    assert len(orc.line_encode(FB, 3, [1, 1])) == 15
+
+
+def test_preamble_levels(orc):  # SURVEY §3 table, derived from line_coding.rs:13-21
+    lv = lambda p: "".join("+" if v > 0 else "-" for v in p[::3])
+    assert lv(orc.preamble(FB)) == "--++-++--++--+-++-++" and len(orc.preamble(FB)) == 60
+    assert lv(orc.preamble(MAN)) == "+-+--+-++-+--+-++--++--+-++--++-" and len(orc.preamble(MAN)) == 96
+    assert orc.samples_for_bits(MAN, 3, 56) == 336 and orc.samples_for_bits(FB, 3, 56) == 210
+    assert orc.samples_for_bits(FB, 3, 1) == 15 and orc.samples_for_bits(MAN, 3, 1) == 6
+
+
+def test_frame_bytes(orc):  # frame.rs:74-102
+    b = orc.frame_to_bytes(1, 7, 3, 9, b"abc")
+    assert b == bytes([0, 3, orc.crc8(b"abc"), 1, 7, 3, 9]) + b"abc"
+    assert orc.frame_to_bytes(2, 1, 2, 3, b"") == bytes([0, 0, 0, 2, 1, 2, 3])  # ACK, empty payload CRC 0
+
+
+def test_encoder_lengths(orc):  # encoder.rs:106-128
+    for kind, P in ((MAN, 96), (FB, 60)):
+        cfg = orc.make_config(kind)
+        one = orc.modulate(cfg, [(1, 0, 0, 1, b"\x01\x02\x03")], 48)
+        assert len(one) == P + orc.samples_for_bits(kind, 3, 80)
+        two = orc.modulate(cfg, [(1, 0, 0, 1, b"\x01\x02\x03")] * 2, 48)
+        assert len(two) == 2 * len(one) + 48  # gap between frames only
+        assert set(np.unique(two)) <= {-1.0, 0.0, 1.0}
+
+
+@pytest.mark.parametrize("kind,total,stride,P", [(FB, 32136, 4158, 60), (MAN, 51216, 6624, 96)])
+def test_loopback_think_different(orc, kind, total, stride, P):
+    """`trackmaker-rs test` (src/main.rs:480-589) with local_addr == dst: 8 frames, derived offsets."""
+    text = open(os.path.join(GOLDEN, "think-different.txt"), "rb").read()
+    assert len(text) == 988
+    frames = [(1, i, 0, 1, text[o:o + 128]) for i, o in enumerate(range(0, len(text), 128))]
+    cfg = orc.make_config(kind, local_addr=1)
+    wave = orc.modulate(cfg, frames, 48)
+    assert len(wave) == total
+    recs, pl = orc.decode_stream(cfg, wave)
+    assert len(recs) == 8 and (recs["status"] == 0).all()
+    assert list(recs["preamble_start"]) == [i * stride for i in range(8)]
+    assert list(recs["frame_start"]) == [i * stride + P for i in range(8)]
+    assert np.allclose(recs["corr"], 1.0)
+    assert bytes(pl) == text
+    # the shipped driver's mismatch (local_addr 2, dst 1; main.rs:496-508) drops every frame
+    recs2, _ = orc.decode_stream(orc.make_config(kind, local_addr=2), wave)
+    assert len(recs2) == 8 and (recs2["status"] == 4).all()
+    # chunked feeding (25 ms polls, csma.rs:446) gives the same frames
+    recs3, pl3 = orc.decode_stream(orc.make_config(kind, local_addr=1, chunk=1200), wave)
+    assert list(recs3["frame_start"]) == list(recs["frame_start"]) and bytes(pl3) == text
+
+
+def test_channel_busy(orc):  # src/mac/mod.rs:18-27
+    assert orc.channel_busy(np.zeros(19, np.float32)) == -1
+    assert orc.channel_busy(np.zeros(20, np.float32)) == 0
+    x = np.zeros(64, np.float32)
+    x[40] = -0.51
+    assert orc.channel_busy(x) == 1
+    x[40] = 0.5
+    assert orc.channel_busy(x) == 0

@@ -47,6 +47,7 @@ struct tmk_engine {
     DevBuf d_patterns, d_streams, d_blk_info, d_cand, d_recs_tmp, d_rec_ord, d_recs, d_payload, d_cnt, d_base,
         d_counters, d_samples, d_misc, d_misc2;
     cudaEvent_t ev[6] = {};
+    cudaEvent_t tev[2] = {};
     float stage_ms[4] = {0, 0, 0, 0};
     uint64_t launches = 0;
     uint64_t stats[TMK_STAT_COUNT] = {};
@@ -221,6 +222,7 @@ int tmk_engine_create(int device, tmk_engine** out) {
     bool ok = cudaStreamCreateWithFlags(&e->stream, cudaStreamNonBlocking) == cudaSuccess &&
               cudaStreamCreateWithFlags(&e->copy_stream, cudaStreamNonBlocking) == cudaSuccess;
     for (int i = 0; ok && i < 6; ++i) ok = cudaEventCreate(&e->ev[i]) == cudaSuccess;
+    for (int i = 0; ok && i < 2; ++i) ok = cudaEventCreate(&e->tev[i]) == cudaSuccess;
     ok = ok && tmk_walk_init() == 0;
     ok = ok && e->d_counters.reserve(sizeof(TmkCounters)) == cudaSuccess;
     if (!ok) {
@@ -241,6 +243,8 @@ void tmk_engine_destroy(tmk_engine* e) {
     for (DevBuf* b : bufs) b->release();
     for (int i = 0; i < 6; ++i)
         if (e->ev[i]) cudaEventDestroy(e->ev[i]);
+    for (int i = 0; i < 2; ++i)
+        if (e->tev[i]) cudaEventDestroy(e->tev[i]);
     if (e->stream) cudaStreamDestroy(e->stream);
     if (e->copy_stream) cudaStreamDestroy(e->copy_stream);
     delete e;
@@ -550,6 +554,22 @@ int tmk_last_kernel_ms(tmk_engine* e, float* ms) {
 int tmk_last_stage_ms(tmk_engine* e, float ms[4]) {
     if (!e || !ms) return TMK_E_INVALID;
     for (int i = 0; i < 4; ++i) ms[i] = e->stage_ms[i];
+    return TMK_OK;
+}
+
+int tmk_timer_start(tmk_engine* e) {
+    if (!e) return TMK_E_INVALID;
+    CK(cudaSetDevice(e->device));
+    CK(cudaStreamSynchronize(e->stream));
+    CK(cudaEventRecord(e->tev[0], e->stream));
+    return TMK_OK;
+}
+
+int tmk_timer_stop(tmk_engine* e, float* ms) {
+    if (!e || !ms) return TMK_E_INVALID;
+    CK(cudaEventRecord(e->tev[1], e->stream));
+    CK(cudaEventSynchronize(e->tev[1]));
+    CK(cudaEventElapsedTime(ms, e->tev[0], e->tev[1]));
     return TMK_OK;
 }
 

@@ -1,0 +1,315 @@
+"""tmkphy — host-side mirror of the reference's PHY interface over libtmkphy's C ABI.
+
+Names, argument meaning and error behaviour follow src/phy/mod.rs:4-13 of the reference:
+  Frame / FrameType          src/phy/frame.rs:8-72
+  LineCodingKind             src/phy/line_coding.rs:26-49
+  PhyEncoder                 src/phy/encoder.rs:5-97
+  PhyDecoder                 src/phy/decoder.rs:16-119
+plus the batched entry point the reference does not have (decode_batch: many captures at once).
+
+Everything that computes goes through libtmkphy.so (CUDA, sm_100a). There is no CPU path: if the
+library is missing or no B200 is visible, constructing an Engine raises.
+"""
+import ctypes as C
+from dataclasses import dataclass
+from enum import IntEnum
+
+import numpy as np
+
+from . import _abi
+from ._abi import (DESC_DTYPE, REC_DTYPE, STREAM_DTYPE, FRAME_OK, LINE_4B5B, LINE_MANCHESTER,  # noqa: F401
+                   STATUS_NAMES, STAT_NAMES, PhyConfig)
+
+# src/utils/consts.rs:24-48
+SAMPLE_RATE = 48000
+SAMPLES_PER_LEVEL = 3
+PREAMBLE_PATTERN_BYTES = 2
+MAX_FRAME_DATA_SIZE = 128
+INTER_FRAME_GAP_SAMPLES = 48
+PHY_HEADER_BYTES = 7
+
+
+class TmkError(RuntimeError):
+    def __init__(self, code, msg):
+        super().__init__(f"libtmkphy error {code}: {msg}")
+        self.code = code
+
+
+class LineCodingKind(IntEnum):  # line_coding.rs:26-38
+    Manchester = LINE_MANCHESTER
+    FourBFiveB = LINE_4B5B
+
+    def display_name(self):
+        return "Manchester" if self == LineCodingKind.Manchester else "4B5B"
+
+
+class FrameType(IntEnum):  # frame.rs:12-32
+    Data = 0x01
+    Ack = 0x02
+
+
+@dataclass
+class Frame:  # frame.rs:34-41
+    frame_type: FrameType
+    sequence: int
+    src: int
+    dst: int
+    data: bytes = b""
+
+    @staticmethod
+    def new_data(sequence, src, dst, data):  # frame.rs:60-62
+        return Frame(FrameType.Data, sequence & 0xFF, src & 0xFF, dst & 0xFF, bytes(data))
+
+    @staticmethod
+    def new_ack(sequence, frm, to):  # frame.rs:64-66
+        return Frame(FrameType.Ack, sequence & 0xFF, frm & 0xFF, to & 0xFF, b"")
+
+
+def _ptr(a):
+    return a.ctypes.data_as(C.c_void_p) if a is not None and a.size else None
+
+
+class Engine:
+    """One engine per GPU (tmk_engine). Not thread-safe: one host thread drives it."""
+
+    def __init__(self, device=0):
+        self._lib = _abi.load_library()
+        h = C.c_void_p()
+        rc = self._lib.tmk_engine_create(int(device), C.byref(h))
+        if rc != 0:
+            raise TmkError(rc, "tmk_engine_create failed: no usable sm_100 CUDA device (there is no CPU fallback)")
+        self._h = h
+        self.device = device
+
+    def close(self):
+        if getattr(self, "_h", None):
+            self._lib.tmk_engine_destroy(self._h)
+            self._h = None
+
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *a):
+        self.close()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def _check(self, rc):
+        if rc != 0:
+            raise TmkError(rc, self._lib.tmk_last_error(self._h).decode())
+
+    # ---- plumbing
+    def device_alloc(self, nbytes):
+        p = C.c_void_p()
+        self._check(self._lib.tmk_device_alloc(self._h, int(nbytes), C.byref(p)))
+        return p.value
+
+    def device_free(self, p):
+        self._check(self._lib.tmk_device_free(self._h, C.c_void_p(p)))
+
+    def pinned_alloc(self, nbytes):
+        p = C.c_void_p()
+        self._check(self._lib.tmk_host_alloc_pinned(self._h, int(nbytes), C.byref(p)))
+        return p.value
+
+    def pinned_free(self, p):
+        self._check(self._lib.tmk_host_free_pinned(self._h, C.c_void_p(p)))
+
+    def pinned_array(self, shape, dtype):
+        """numpy array over pinned host memory (freed with pinned_free(arr.ctypes.data))"""
+        dtype = np.dtype(dtype)
+        n = int(np.prod(shape))
+        p = self.pinned_alloc(max(1, n * dtype.itemsize))
+        buf = (C.c_char * (n * dtype.itemsize)).from_address(p)
+        return np.frombuffer(buf, dtype=dtype, count=n).reshape(shape)
+
+    def h2d(self, dptr, arr):
+        arr = np.ascontiguousarray(arr)
+        self._check(self._lib.tmk_memcpy_h2d(self._h, C.c_void_p(dptr), _ptr(arr), arr.nbytes))
+
+    def d2h(self, arr, dptr):
+        self._check(self._lib.tmk_memcpy_d2h(self._h, _ptr(arr), C.c_void_p(dptr), arr.nbytes))
+
+    def synchronize(self):
+        self._check(self._lib.tmk_synchronize(self._h))
+
+    def stream_handle(self):
+        return self._lib.tmk_engine_stream(self._h)
+
+    def timer_start(self):
+        self._check(self._lib.tmk_timer_start(self._h))
+
+    def timer_stop(self):
+        ms = C.c_float(0)
+        self._check(self._lib.tmk_timer_stop(self._h, C.byref(ms)))
+        return ms.value
+
+    def launch_count(self):
+        return int(self._lib.tmk_launch_count(self._h))
+
+    def last_kernel_ms(self):
+        ms = C.c_float(0)
+        self._check(self._lib.tmk_last_kernel_ms(self._h, C.byref(ms)))
+        return ms.value
+
+    def last_stage_ms(self):
+        ms = (C.c_float * 4)()
+        self._check(self._lib.tmk_last_stage_ms(self._h, ms))
+        return {"scan": ms[0], "walk": ms[1], "order": ms[2], "h2d": ms[3]}
+
+    def stats(self):
+        c = (C.c_uint64 * _abi.STAT_COUNT)()
+        self._check(self._lib.tmk_stats(self._h, c))
+        return dict(zip(STAT_NAMES, [int(v) for v in c]))
+
+    def stats_reset(self):
+        self._check(self._lib.tmk_stats_reset(self._h))
+
+    # ---- the path
+    def modulate(self, cfg, frames, gap=INTER_FRAME_GAP_SAMPLES, out_device_ptr=None):
+        """PhyEncoder::encode_frames. frames: list of Frame. Returns float32 samples (host)."""
+        d = np.zeros(len(frames), DESC_DTYPE)
+        blob = bytearray()
+        for i, f in enumerate(frames):
+            d[i] = (len(blob), len(f.data), int(f.frame_type), f.sequence, f.src, f.dst)
+            blob += bytes(f.data)
+        pl = np.frombuffer(bytes(blob) + b"\0", dtype=np.uint8).copy()
+        n = self._lib.tmk_modulated_len(C.byref(cfg), _ptr(d), len(d), gap)
+        out_len = C.c_uint64(0)
+        if out_device_ptr is not None:
+            self._check(self._lib.tmk_modulate(self._h, C.byref(cfg), _ptr(d), len(d), _ptr(pl), len(blob), gap,
+                                               C.c_void_p(out_device_ptr), n, C.byref(out_len)))
+            return int(out_len.value)
+        out = np.zeros(n, np.float32)
+        self._check(self._lib.tmk_modulate(self._h, C.byref(cfg), _ptr(d), len(d), _ptr(pl), len(blob), gap,
+                                           _ptr(out), n, C.byref(out_len)))
+        assert out_len.value == n
+        return out
+
+    def decode_batch(self, samples, streams, rec_cap=None, payload_cap=None, total_samples=None):
+        """tmk_decode_batch. samples: float32 ndarray (host) or an int device pointer;
+        streams: ndarray[STREAM_DTYPE]. Returns (records ndarray[REC_DTYPE], payload ndarray[u8])."""
+        st = np.ascontiguousarray(streams, dtype=STREAM_DTYPE)
+        if isinstance(samples, np.ndarray):
+            s = np.ascontiguousarray(samples, dtype=np.float32)
+            sp, total = _ptr(s), s.size
+        else:
+            sp, total = C.c_void_p(int(samples)), int(total_samples)
+        tot = int(st["n_samples"].sum()) if len(st) else 0
+        rec_cap = int(rec_cap) if rec_cap is not None else max(1024, tot // 96 + 2 * len(st))
+        payload_cap = int(payload_cap) if payload_cap is not None else max(65536, tot // 12)
+        recs = np.zeros(rec_cap, REC_DTYPE)
+        pl = np.zeros(payload_cap, np.uint8)
+        nr, npl = C.c_uint64(0), C.c_uint64(0)
+        rc = self._lib.tmk_decode_batch(self._h, sp, total, _ptr(st), len(st), _ptr(recs), rec_cap, C.byref(nr),
+                                        _ptr(pl), payload_cap, C.byref(npl))
+        if rc == _abi.E_CAPACITY and (nr.value > rec_cap or npl.value > payload_cap):
+            return self.decode_batch(samples, streams, max(rec_cap, nr.value), max(payload_cap, npl.value),
+                                     total_samples)
+        self._check(rc)
+        return recs[:nr.value].copy(), pl[:npl.value].copy()
+
+    def correlate(self, samples, streams):
+        s = np.ascontiguousarray(samples, dtype=np.float32)
+        st = np.ascontiguousarray(streams, dtype=STREAM_DTYPE)
+        out = np.zeros(s.size, np.float32)
+        self._check(self._lib.tmk_correlate(self._h, _ptr(s), s.size, _ptr(st), len(st), _ptr(out)))
+        return out
+
+    def channel_busy(self, samples, streams):
+        s = np.ascontiguousarray(samples, dtype=np.float32)
+        st = np.ascontiguousarray(streams, dtype=STREAM_DTYPE)
+        out = np.zeros(len(st), np.int8)
+        self._check(self._lib.tmk_channel_busy(self._h, _ptr(s), s.size, _ptr(st), len(st), _ptr(out)))
+        return out
+
+    def synth_batch(self, cfg, seed, n_streams, n_per_stream, snr_db, amplitude=1.0, device_ptr=None,
+                    want_truth=True):
+        """Synthetic captures. Returns (samples or None when device_ptr is given, truth records)."""
+        total = n_streams * n_per_stream
+        cap = (total // 300 + n_streams + 16) if want_truth else 0
+        truth = np.zeros(cap, REC_DTYPE) if want_truth else None
+        nt = C.c_uint64(0)
+        if device_ptr is None:
+            out = np.zeros(total, np.float32)
+            sp = _ptr(out)
+        else:
+            out, sp = None, C.c_void_p(int(device_ptr))
+        self._check(self._lib.tmk_synth_batch(self._h, C.byref(cfg), seed, n_streams, n_per_stream, snr_db, amplitude,
+                                              sp, _ptr(truth) if want_truth else None, cap, C.byref(nt)))
+        return out, (truth[:nt.value].copy() if want_truth else int(nt.value))
+
+
+def make_config(kind, local_addr=1, spl=SAMPLES_PER_LEVEL, preamble_bytes=PREAMBLE_PATTERN_BYTES, threshold=0.9,
+                max_frame_bytes=2 * MAX_FRAME_DATA_SIZE, chunk=0):
+    return PhyConfig(int(kind), spl, preamble_bytes, local_addr, threshold, max_frame_bytes, chunk)
+
+
+def make_streams(lengths, cfg, align=4):
+    """Contiguous ragged layout: stream i starts at the next multiple of `align` samples."""
+    st = np.zeros(len(lengths), STREAM_DTYPE)
+    off = 0
+    for i, n in enumerate(lengths):
+        st[i]["offset"] = off
+        st[i]["n_samples"] = n
+        c = cfg[i] if isinstance(cfg, (list, tuple)) else cfg
+        st[i]["cfg"] = (c.line_code, c.spl, c.preamble_bytes, c.local_addr, c.threshold, c.max_frame_bytes, c.chunk)
+        off += (n + align - 1) // align * align
+    return st, off
+
+
+def records_to_frames(recs, payload):
+    """Only FRAME_OK records are Frames PhyDecoder::process_samples returns (decoder.rs:341-344)."""
+    out = []
+    for r in recs:
+        if r["status"] == FRAME_OK:
+            o = int(r["payload_off"])
+            out.append(Frame(FrameType(int(r["type"])), int(r["seq"]), int(r["src"]), int(r["dst"]),
+                             bytes(payload[o:o + int(r["len"])])))
+    return out
+
+
+class PhyEncoder:
+    """PhyEncoder::new(samples_per_level, preamble_bytes, line_coding_kind)  encoder.rs:18-39"""
+
+    def __init__(self, engine, samples_per_level, preamble_bytes, line_coding_kind):
+        self.engine = engine
+        self.cfg = make_config(line_coding_kind, spl=samples_per_level, preamble_bytes=preamble_bytes)
+
+    def preamble_len(self):  # encoder.rs:94-96
+        return int(self.engine._lib.tmk_preamble_len(C.byref(self.cfg)))
+
+    def encode_frame(self, frame):  # encoder.rs:43-63
+        return self.engine.modulate(self.cfg, [frame], 0)
+
+    def encode_frames(self, frames, inter_frame_gap_samples):  # encoder.rs:70-92
+        return self.engine.modulate(self.cfg, list(frames), inter_frame_gap_samples)
+
+
+class PhyDecoder:
+    """PhyDecoder::new(samples_per_level, preamble_bytes, line_coding_kind, local_addr)  decoder.rs:36-65
+
+    Offline use: every process_samples call decodes one whole capture with a fresh decoder state
+    (what src/main.rs:540 does); `chunk` reproduces the verdicts of feeding it in chunk-sized calls.
+    """
+
+    def __init__(self, engine, samples_per_level, preamble_bytes, line_coding_kind, local_addr, chunk=0):
+        self.engine = engine
+        self.cfg = make_config(line_coding_kind, local_addr=local_addr, spl=samples_per_level,
+                               preamble_bytes=preamble_bytes, chunk=chunk)
+        self.last_records = np.zeros(0, REC_DTYPE)
+        self.last_payload = np.zeros(0, np.uint8)
+
+    def process_samples(self, samples):
+        s = np.ascontiguousarray(samples, dtype=np.float32)
+        st, _ = make_streams([s.size], self.cfg)
+        self.last_records, self.last_payload = self.engine.decode_batch(s, st)
+        return records_to_frames(self.last_records, self.last_payload)
+
+    def reset(self):  # decoder.rs:114-119 — nothing is carried between calls
+        self.last_records = np.zeros(0, REC_DTYPE)
+        self.last_payload = np.zeros(0, np.uint8)

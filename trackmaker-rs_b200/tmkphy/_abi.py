@@ -89,6 +89,8 @@ SYMBOLS = {
     "tmk_engine_stream": (_vp, [_vp]),
     "tmk_last_kernel_ms": (C.c_int, [_vp, C.POINTER(C.c_float)]),
     "tmk_last_stage_ms": (C.c_int, [_vp, C.POINTER(C.c_float)]),
+    "tmk_timer_start": (C.c_int, [_vp]),
+    "tmk_timer_stop": (C.c_int, [_vp, C.POINTER(C.c_float)]),
     "tmk_launch_count": (_u64, [_vp]),
     "tmk_synth_batch": (C.c_int, [_vp, _pcfg, _u64, _u32, _u64, C.c_float, C.c_float, _vp, _vp, _u64, _pu64]),
 }
