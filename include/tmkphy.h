@@ -156,7 +156,9 @@ int tmk_decode_batch(tmk_engine* e, const float* samples, uint64_t total_samples
                      uint8_t* payload, uint64_t payload_cap, uint64_t* payload_len);
 
 /* corr_out[offset + i] = correlation of window i of each stream (n_samples - P + 1 windows),
- * one-shot semantics, energy re-seeded at window 0 only. */
+ * one-shot semantics: window energy seeded at window 0 and rolled (decoder.rs:133-136,224-233),
+ * AVX-order dot product; bit-exact with the reference arithmetic (sequential per stream: a
+ * parity probe, not the hot path). */
 int tmk_correlate(tmk_engine* e, const float* samples, uint64_t total_samples, const tmk_stream* streams,
                   uint32_t n_streams, float* corr_out);
 

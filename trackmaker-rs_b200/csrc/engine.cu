@@ -349,7 +349,7 @@ int tmk_decode_batch(tmk_engine* e, const float* samples, uint64_t total_samples
     const void* d_samples = nullptr;
     rc = stage_in(e, e->d_samples, samples, total_samples * sizeof(float), &d_samples);
     if (rc != TMK_OK) return rc;
-    CK(e->d_blk_info.reserve(sizeof(float2) * std::max<uint64_t>(1, b.n_blocks)));
+    CK(e->d_blk_info.reserve(sizeof(float4) * std::max<uint64_t>(1, b.n_blocks)));
     CK(e->d_cand.reserve(sizeof(uint32_t) * TMK_BLK_WORDS * std::max<uint64_t>(1, b.n_blocks)));
     CK(e->d_cnt.reserve(sizeof(uint32_t) * n_streams));
     CK(e->d_base.reserve(sizeof(uint64_t) * (n_streams + 1)));
@@ -357,7 +357,7 @@ int tmk_decode_batch(tmk_engine* e, const float* samples, uint64_t total_samples
     const TmkStreamDev* ds = static_cast<const TmkStreamDev*>(e->d_streams.p);
     const TmkPattern* dp = static_cast<const TmkPattern*>(e->d_patterns.p);
     const float* dx = static_cast<const float*>(d_samples);
-    float2* dbi = static_cast<float2*>(e->d_blk_info.p);
+    float4* dbi = static_cast<float4*>(e->d_blk_info.p);
     uint32_t* dcb = static_cast<uint32_t*>(e->d_cand.p);
     TmkCounters* dc = static_cast<TmkCounters*>(e->d_counters.p);
 

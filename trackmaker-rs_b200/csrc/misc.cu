@@ -102,8 +102,36 @@ modulate_kernel(const TmkPattern* __restrict__ pat, const tmk_frame_desc* __rest
 }
 
 // ---------------------------------------------------------------- correlation probe
-// corr[i] = dot_avx_order(window i) / (sqrt(E_i) * pe) with E_i summed directly (the reference
-// rolls it, decoder.rs:224-233; the two agree to ~1e-6 relative, the probe's contract is 1e-5).
+// One search_for_preamble pass that never stops (decoder.rs:130-147,224-233): window energy seeded
+// at window 0 by a sequential sum and ROLLED from there, AVX-order dot product. Bit-exact with the
+// reference arithmetic, so it is sequential per stream: kernel 1 rolls the energy chain (one warp
+// per stream, 32 steps per coalesced load), kernel 2 divides the dot products by it in place.
+__global__ void energy_chain_kernel(const float* __restrict__ samples, const TmkStreamDev* __restrict__ streams,
+                                    uint32_t n_streams, const TmkPattern* __restrict__ patterns,
+                                    float* __restrict__ corr_out) {
+    const uint32_t s = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
+    if (s >= n_streams) return;
+    const TmkStreamDev sd = streams[s];
+    const uint32_t P = patterns[sd.pattern].P;
+    if (sd.n_samples < P) return;
+    const uint64_t nwin = sd.n_samples - P + 1;
+    const float* __restrict__ x = samples + sd.offset;
+    float* __restrict__ out = corr_out + sd.offset;
+    float e = 0.0f;
+    for (uint32_t i = 0; i < P; ++i) e = ex_add(e, ex_mul(x[i], x[i]));
+    for (uint64_t w0 = 0; w0 < nwin; w0 += 32) {
+        const uint64_t w = w0 + lane;
+        const bool step_ok = w + 1 < nwin;  // the roll that produces window w + 1
+        const float lv = step_ok ? x[w] : 0.f, en = step_ok ? x[w + P] : 0.f;
+        float mine = 0.f;
+        for (int j = 0; j < 32; ++j) {
+            if (lane == j) mine = e;  // energy of window w0 + j
+            if (w0 + j + 1 < nwin) e = ex_roll(e, __shfl_sync(0xffffffffu, lv, j), __shfl_sync(0xffffffffu, en, j));
+        }
+        if (w < nwin) out[w] = mine;
+    }
+}
+
 __global__ void correlate_kernel(const float* __restrict__ samples, const TmkStreamDev* __restrict__ streams,
                                  const TmkPattern* __restrict__ patterns, float* __restrict__ corr_out) {
     const TmkStreamDev sd = streams[blockIdx.x];
@@ -116,25 +144,16 @@ __global__ void correlate_kernel(const float* __restrict__ samples, const TmkStr
         float a[8];
 #pragma unroll
         for (int l = 0; l < 8; ++l) a[l] = 0.0f;
-        double e = 0.0;
         uint32_t i = 0;
         for (; i + 8 <= P; i += 8) {
 #pragma unroll
-            for (int l = 0; l < 8; ++l) {
-                const float v = x[w + i + l];
-                a[l] = ex_add(a[l], ex_mul(v, pat->levels[(i + l) / spl]));
-                e += double(ex_mul(v, v));
-            }
+            for (int l = 0; l < 8; ++l) a[l] = ex_add(a[l], ex_mul(x[w + i + l], pat->levels[(i + l) / spl]));
         }
         float s = 0.0f;
 #pragma unroll
         for (int l = 0; l < 4; ++l) s = ex_add(s, ex_add(a[l], a[l + 4]));
-        for (; i < P; ++i) {
-            const float v = x[w + i];
-            s = ex_add(s, ex_mul(v, pat->levels[i / spl]));
-            e += double(ex_mul(v, v));
-        }
-        corr_out[sd.offset + w] = ex_corr(s, __double2float_rn(e), pat->pe);
+        for (; i < P; ++i) s = ex_add(s, ex_mul(x[w + i], pat->levels[i / spl]));
+        corr_out[sd.offset + w] = ex_corr(s, corr_out[sd.offset + w], pat->pe);
     }
 }
 
@@ -165,9 +184,10 @@ int tmk_launch_modulate(const TmkPattern* pattern, const tmk_frame_desc* frames,
 int tmk_launch_correlate(const float* samples, const TmkStreamDev* streams, uint32_t n_streams,
                          const TmkPattern* patterns, float* corr_out, cudaStream_t st) {
     if (n_streams == 0) return 0;
+    energy_chain_kernel<<<(n_streams + 3) / 4, 128, 0, st>>>(samples, streams, n_streams, patterns, corr_out);
     dim3 grid(n_streams, 64);
     correlate_kernel<<<grid, 256, 0, st>>>(samples, streams, patterns, corr_out);
-    return 1;
+    return 2;
 }
 
 int tmk_launch_busy(const float* samples, const TmkStreamDev* streams, uint32_t n_streams, int8_t* busy,

@@ -4,7 +4,7 @@
 // Replaces the per-sample loop of PhyDecoder::search_for_preamble (src/phy/decoder.rs:138-147)
 // as a *filter*: it marks every window whose correlation may reach the threshold
 // (corr_approx >= thr * TMK_CAND_RATIO) in a bitmap and summarises the window energies of each
-// block of TMK_BLK windows as (min, max). The exact reference decision (AVX summation order,
+// block of TMK_BLK windows as (min, max) plus the largest squared correlation of the block. The exact reference decision (AVX summation order,
 // rolling energy) is re-established for the marked windows by the walk kernel (walk.cu).
 //
 // This translation unit is the general-shape kernel; scan_fast.cu holds the kernels specialised
@@ -31,7 +31,7 @@ __device__ __forceinline__ uint32_t find_stream(const TmkStreamDev* __restrict__
 
 __global__ void __launch_bounds__(kThreads)
 scan_generic_kernel(const float* __restrict__ samples, const TmkStreamDev* __restrict__ streams,
-                    uint32_t n_streams, const TmkPattern* __restrict__ patterns, float2* __restrict__ blk_info,
+                    uint32_t n_streams, const TmkPattern* __restrict__ patterns, float4* __restrict__ blk_info,
                     uint32_t* __restrict__ cand_bits) {
     __shared__ float xs[kSmemX];   // raw samples, then box sums of spl samples
     __shared__ float qs[kSmemX];   // box sums of spl squared samples
@@ -95,7 +95,7 @@ scan_generic_kernel(const float* __restrict__ samples, const TmkStreamDev* __res
     const float kappa = thr_c * thr_c * float(P);
     const uint32_t warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const uint32_t bw0 = warp * TMK_BLK;  // this warp's block inside the tile
-    float emin = __int_as_float(0x7f800000), emax = 0.f;
+    float emin = __int_as_float(0x7f800000), emax = 0.f, dmax = 0.f;
     uint32_t myword = 0;
 #pragma unroll 1
     for (uint32_t i = 0; i < TMK_BLK_WORDS; ++i) {
@@ -110,6 +110,7 @@ scan_generic_kernel(const float* __restrict__ samples, const TmkStreamDev* __res
         if (valid) {
             emin = fminf(emin, E);
             emax = max_nan(emax, E);
+            if (D > 0.f) dmax = fmaxf(dmax, D * D / (float(P) * E));  // largest corr^2 of the block
         }
         const uint32_t word = __ballot_sync(0xffffffffu, cand);
         if (lane == i) myword = word;
@@ -118,19 +119,20 @@ scan_generic_kernel(const float* __restrict__ samples, const TmkStreamDev* __res
     for (int o = 16; o > 0; o >>= 1) {
         emin = fminf(emin, __shfl_xor_sync(0xffffffffu, emin, o));
         emax = max_nan(emax, __shfl_xor_sync(0xffffffffu, emax, o));
+        dmax = fmaxf(dmax, __shfl_xor_sync(0xffffffffu, dmax, o));
     }
     const uint64_t blk_in_stream = w0 / TMK_BLK + warp;
     if (blk_in_stream * TMK_BLK < nwin) {
         const uint64_t gb = sd.blk_base + blk_in_stream;
         if (lane < TMK_BLK_WORDS) cand_bits[gb * TMK_BLK_WORDS + lane] = myword;
-        if (lane == 0) blk_info[gb] = make_float2(emin, emax);
+        if (lane == 0) blk_info[gb] = make_float4(emin, emax, dmax, 0.f);
     }
 }
 
 }  // namespace
 
 int tmk_launch_scan(const float* samples, const TmkStreamDev* streams, uint32_t n_streams, uint32_t n_tiles,
-                            const TmkPattern* patterns, float2* blk_info, uint32_t* cand_bits, cudaStream_t st) {
+                            const TmkPattern* patterns, float4* blk_info, uint32_t* cand_bits, cudaStream_t st) {
     if (n_tiles == 0) return 0;
     scan_generic_kernel<<<n_tiles, kThreads, 0, st>>>(samples, streams, n_streams, patterns, blk_info, cand_bits);
     return 1;

@@ -2,7 +2,7 @@
 //
 // Data layout in HBM:
 //   samples      float[total]             all captures of a batch, stream s at streams[s].offset
-//   blk_info     float2[n_blocks]         per block of TMK_BLK windows: (min, max) window energy
+//   blk_info     float4[n_blocks]         per block of TMK_BLK windows: (min E, max E, max corr^2, 0)
 //   cand_bits    uint32[n_blocks * 8]     1 bit per window: corr_approx >= thr * CAND_RATIO
 //   recs/payload tmk_frame_rec[] / u8[]   verdict records + decoded payload bytes
 //
@@ -55,6 +55,8 @@ struct TmkStreamDev {
 struct TmkCounters {
     unsigned long long n_recs;
     unsigned long long n_payload;
+    unsigned int next_stream;  // persistent walk warps pull stream indices from here
+    unsigned int pad_;
     unsigned long long stats[TMK_STAT_COUNT];
 };
 
@@ -100,9 +102,9 @@ __device__ __forceinline__ uint32_t crc8_step(uint32_t crc, uint32_t byte) {
 
 // kernel launchers (each returns the number of kernels it launched)
 int tmk_launch_scan(const float* samples, const TmkStreamDev* streams, uint32_t n_streams, uint32_t n_tiles,
-                    const TmkPattern* patterns, float2* blk_info, uint32_t* cand_bits, cudaStream_t st);
+                    const TmkPattern* patterns, float4* blk_info, uint32_t* cand_bits, cudaStream_t st);
 int tmk_launch_walk(const float* samples, const TmkStreamDev* streams, uint32_t n_streams,
-                    const TmkPattern* patterns, const float2* blk_info, const uint32_t* cand_bits,
+                    const TmkPattern* patterns, const float4* blk_info, const uint32_t* cand_bits,
                     tmk_frame_rec* recs, uint32_t* rec_ord, uint64_t rec_cap, uint8_t* payload,
                     uint64_t payload_cap, uint32_t* stream_cnt, TmkCounters* counters, cudaStream_t st);
 int tmk_launch_order(const tmk_frame_rec* recs_in, const uint32_t* rec_ord, uint64_t n_recs,

@@ -25,11 +25,18 @@ constexpr int kByteBuf = TMK_PHY_HEADER_BYTES + kMaxFrameBytesCap + 9;
 constexpr int kQBuf = TMK_BLK + 256;                    // prefix sums for P <= 255
 constexpr float kU = 5.9604645e-8f;                     // 2^-24, unit roundoff of f32
 constexpr unsigned kFull = 0xffffffffu;
+// A window outside the candidate bitmap has corr_approx < thr * TMK_CAND_RATIO; the reference can
+// only detect it if its rolling energy sits below (TMK_CAND_RATIO)^2 = 0.892 of the true window
+// energy. kTight is the share of the window energy the drift bound may use up before such a
+// window has to be examined individually (0.09 < 1 - 0.892, the rest is margin for the scan
+// kernel's own rounding).
+constexpr float kTight = 0.09f;
 
 __device__ uint8_t g_crc_pow[kMaxFrameBytesCap + 8];    // x^(8k) mod 0x107, k = 0..
 
 struct WarpScratch {
     double Q[kQBuf + 1];
+    float pre[TMK_MAX_P];  // preamble samples (levels expanded by spl)
     uint8_t bytes[kByteBuf];
 };
 
@@ -39,7 +46,7 @@ struct Ctx {
     uint64_t nwin;        // windows (N - P + 1, or 0)
     uint64_t C;           // chunk (0 = one shot)
     const TmkPattern* pat;
-    const float2* blk_info;
+    const float4* blk_info;
     const uint32_t* cand_bits;
     uint64_t nblk;
     float thr;
@@ -52,6 +59,10 @@ struct Ctx {
     uint64_t rseed, rpos;
     float rE;
     bool rvalid;
+    // anchor: |E_ref(a_w) - S(a_w)| <= a_err for the chain seeded at a_seed (a_w == a_seed, a_err == 0
+    // right after a search entry; a measured value after an exact re-anchoring)
+    uint64_t a_seed, a_w;
+    float a_err;
     // stats
     uint32_t n_replays, n_cands, n_det;
 };
@@ -66,33 +77,31 @@ __device__ __forceinline__ uint64_t avail_for(const Ctx& c, uint64_t w, uint64_t
 // position at which the search that examines window w was (re)entered = where its rolling
 // energy was seeded (decoder.rs:133-136)
 __device__ __forceinline__ uint64_t seed_for(const Ctx& c, uint64_t w, uint64_t q, uint64_t avail) {
+    if (w + c.P <= avail) return q;
     uint64_t aw = avail_for(c, w, avail);
-    if (aw == avail) return q;
     uint64_t prev = ((aw - 1) / c.C) * c.C;  // avail of the previous process_samples call
     if (prev + 1 < uint64_t(c.P)) return q;
     uint64_t s = prev + 1 - c.P;
     return s > q ? s : q;
 }
 
-// preamble sample k
-__device__ __forceinline__ float pre(const Ctx& c, uint32_t k) { return c.pat->levels[k / c.pat->spl]; }
-
 // compute_dot_product_avx (decoder.rs:381-417): 8 lanes of mul-then-add, lane l + lane l+4,
 // the 4 partials summed left to right from 0, then the len % 8 tail. Runs per thread.
 __device__ float dot_avx_order(const Ctx& c, const float* __restrict__ w) {
     const uint32_t P = c.P;
+    const float* __restrict__ pre = c.sc->pre;
     float a[8];
 #pragma unroll
     for (int l = 0; l < 8; ++l) a[l] = 0.0f;
     uint32_t i = 0;
     for (; i + 8 <= P; i += 8) {
 #pragma unroll
-        for (int l = 0; l < 8; ++l) a[l] = ex_add(a[l], ex_mul(w[i + l], pre(c, i + l)));
+        for (int l = 0; l < 8; ++l) a[l] = ex_add(a[l], ex_mul(w[i + l], pre[i + l]));
     }
     float s = 0.0f;
 #pragma unroll
     for (int l = 0; l < 4; ++l) s = ex_add(s, ex_add(a[l], a[l + 4]));
-    for (; i < P; ++i) s = ex_add(s, ex_mul(w[i], pre(c, i)));
+    for (; i < P; ++i) s = ex_add(s, ex_mul(w[i], pre[i]));
     return s;
 }
 
@@ -104,7 +113,8 @@ __device__ float seq_energy(const float* __restrict__ w, uint32_t n) {
 }
 
 // Exact rolling window energy of window `w` for a search seeded at `seed` (decoder.rs:133-136,
-// 224-233). Sequential by construction; all lanes run it redundantly (broadcast loads).
+// 224-233). Sequential by construction: the squares are formed lane-parallel, 32 steps per
+// coalesced load, the dependent (sub, add, clamp) chain runs redundantly on every lane.
 __device__ float exact_energy(Ctx& c, uint64_t seed, uint64_t w) {
     float e;
     uint64_t pos;
@@ -117,18 +127,28 @@ __device__ float exact_energy(Ctx& c, uint64_t seed, uint64_t w) {
     }
     const float* __restrict__ x = c.x;
     const uint32_t P = c.P;
-    // 32 steps at a time: one coalesced load of the leaving / entering samples, then shuffles
     while (pos < w) {
-        uint64_t left = w - pos;
-        uint32_t n = left < 32 ? uint32_t(left) : 32u;
+        const uint64_t left = w - pos;
+        const uint32_t n = left < 32 ? uint32_t(left) : 32u;
         float lv = 0.f, en = 0.f;
         if (uint32_t(c.lane) < n) {
             lv = x[pos + c.lane];
             en = x[pos + P + c.lane];
         }
-        for (uint32_t j = 0; j < n; ++j) {
-            float l = __shfl_sync(kFull, lv, j), t = __shfl_sync(kFull, en, j);
-            e = ex_roll(e, l, t);
+        lv = ex_mul(lv, lv);
+        en = ex_mul(en, en);
+        // `if e < 0 { e = 0 }` equals max(e, 0) unless e is NaN (sign of zero never matters: the
+        // energy gate keeps zeros away from sqrt); NaN / inf batches take the literal form
+        const bool finite = __all_sync(kFull, fabsf(lv) <= 3.0e38f && fabsf(en) <= 3.0e38f) && fabsf(e) <= 3.0e38f;
+        if (n == 32 && finite) {
+#pragma unroll
+            for (int j = 0; j < 32; ++j)
+                e = fmaxf(ex_add(ex_sub(e, __shfl_sync(kFull, lv, j)), __shfl_sync(kFull, en, j)), 0.0f);
+        } else {
+            for (uint32_t j = 0; j < n; ++j) {
+                e = ex_add(ex_sub(e, __shfl_sync(kFull, lv, j)), __shfl_sync(kFull, en, j));
+                e = e < 0.0f ? 0.0f : e;
+            }
         }
         pos += n;
     }
@@ -140,10 +160,14 @@ __device__ float exact_energy(Ctx& c, uint64_t seed, uint64_t w) {
     return e;
 }
 
-// drift bound of the rolling energy after k steps from a seed, relative to the largest window
-// energy on the chain (|e_k| <= 1.15 u (1.25 P + 2.6 k) Smax for k <= 2^20)
-__device__ __forceinline__ float drift_factor(uint32_t P, uint64_t k) {
-    return 1.2f * kU * (1.25f * float(P) + 2.6f * float(k));
+// Bound on |E_ref(w) - S(w)|, S = exact sum of the rounded squares of window w, for a chain that
+// has run k rolling steps since a point where the error was at most e0, with every window energy
+// on the way at most smax (DESIGN.md "exactness"): each step adds at most 2.1 u S and multiplies
+// the error by at most (1 + 2.1 u). The 1.5 P u smax term covers the sequential seed sum.
+__device__ __forceinline__ float drift_bound(uint32_t P, uint64_t k, float e0, float smax) {
+    const float kf = float(k);
+    const float growth = kf < 65536.f ? 1.01f : __expf(2.2f * kU * kf) * 1.01f;
+    return (e0 + kU * (1.5f * float(P) + 2.2f * kf) * smax) * growth;
 }
 
 enum { DEC_NO = 0, DEC_YES = 1, DEC_AMBIG = 2 };
@@ -182,6 +206,18 @@ __device__ __forceinline__ float warp_incl_scan_maxnan(float v, int lane) {
     return v;
 }
 
+// accurately summed energy of window w (double accumulation of the rounded squares), warp-parallel
+__device__ float window_energy(const Ctx& c, uint64_t w) {
+    double s = 0.0;
+    for (uint32_t k = c.lane; k < c.P; k += 32) {
+        const float v = c.x[w + k];
+        s += double(ex_mul(v, v));
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) s += __shfl_xor_sync(kFull, s, o);
+    return __double2float_rn(s);
+}
+
 struct Detection {
     uint64_t c;      // detecting window (preamble start)
     uint64_t seed;   // where the search that found it was entered (search area start)
@@ -197,9 +233,11 @@ __device__ bool exact_window(Ctx& c, uint64_t w, uint64_t seed, float D, float* 
     return corr >= c.thr;
 }
 
-// Examine the windows of block `bb` that are >= q, in order. `prevmax` bounds the window
-// energies of the chain before this block. Returns true with *det filled on a detection.
-__device__ bool process_block(Ctx& c, uint64_t bb, uint64_t q, uint64_t avail, float prevmax, Detection* det) {
+// Examine the windows of block `bb` that are >= q, in order. `prevmax` bounds the window energies
+// of the chain between the anchor and this block; *pm_out receives the bound including this block.
+// Returns true with *det filled on a detection.
+__device__ bool process_block(Ctx& c, uint64_t bb, uint64_t q, uint64_t avail, float prevmax, Detection* det,
+                              float* pm_out) {
     const int lane = c.lane;
     const uint32_t P = c.P;
     const uint64_t wb0 = bb * TMK_BLK;
@@ -209,7 +247,7 @@ __device__ bool process_block(Ctx& c, uint64_t bb, uint64_t q, uint64_t avail, f
     float nb = c.blk_info[bb].y;
     if (bb > 0) nb = max_nan(nb, c.blk_info[bb - 1].y);
     if (bb + 1 < c.nblk) nb = max_nan(nb, c.blk_info[bb + 1].y);
-    const float dscan = 64.f * kU * nb;
+    const float dscan = 128.f * kU * nb;
 
     const bool fast = P <= 255;
     if (fast) {
@@ -253,10 +291,9 @@ __device__ bool process_block(Ctx& c, uint64_t bb, uint64_t q, uint64_t avail, f
         bool tight = false;
         if (valid) {
             seed = seed_for(c, w, q, avail);
-            const uint64_t k = w - seed;
-            delta = drift_factor(P, k) * pm + 2.5f * kU * Ec;
-            if (k > (1u << 20)) delta = __int_as_float(0x7f800000);  // bound not valid: force replay
-            tight = (delta + dscan) <= 0.04f * Ec;
+            const bool same = seed == c.a_seed && w >= c.a_w;
+            delta = drift_bound(P, same ? w - c.a_w : w - seed, same ? c.a_err : 0.f, pm) + 2.5f * kU * Ec;
+            tight = (delta + dscan) <= kTight * Ec;
         }
         const bool bit = (words[r] >> lane) & 1u;
         const bool possible = Ec >= silent || !(Ec == Ec);
@@ -281,8 +318,7 @@ __device__ bool process_block(Ctx& c, uint64_t bb, uint64_t q, uint64_t avail, f
             float corr;
             bool hit;
             if (dj == DEC_YES) {
-                // report the reference's corr value: needs the exact energy only for the record;
-                // use the interval centre (documented: corr in records is within 1e-5)
+                // the record's corr uses the accurately summed energy (within 1e-5 of the reference's)
                 corr = ex_corr(Dj, __shfl_sync(kFull, Ec, j), c.pat->pe);
                 hit = true;
             } else {
@@ -297,6 +333,7 @@ __device__ bool process_block(Ctx& c, uint64_t bb, uint64_t q, uint64_t avail, f
             }
         }
     }
+    *pm_out = pmcarry;
     return false;
 }
 
@@ -304,12 +341,20 @@ __device__ bool process_block(Ctx& c, uint64_t bb, uint64_t q, uint64_t avail, f
 __device__ bool search(Ctx& c, uint64_t q, uint64_t avail, Detection* det) {
     if (c.nwin == 0 || q >= c.nwin) return false;
     const int lane = c.lane;
+    const uint32_t P = c.P;
     const float silent = 0.5f * c.thr * c.thr * 1e-6f;
-    float runmax = 0.f;
-    for (uint64_t b0 = q / TMK_BLK; b0 < c.nblk; b0 += 32) {
+    c.a_seed = q;
+    c.a_w = q;
+    c.a_err = 0.f;
+    float runmax = 0.f;  // bound on the window energies in (a_w, first window of the group)
+    // the block that contains q is partial: its summary also covers windows before q
+    uint64_t b0 = q / TMK_BLK;
+    if (process_block(c, b0, q, avail, 0.f, det, &runmax)) return true;
+    ++b0;
+    while (b0 < c.nblk) {
         const uint64_t bb = b0 + lane;
         const bool valid = bb < c.nblk;
-        float2 info = make_float2(0.f, 0.f);
+        float4 info = make_float4(0.f, 0.f, 0.f, 0.f);
         bool any = false;
         if (valid) {
             info = c.blk_info[bb];
@@ -319,33 +364,64 @@ __device__ bool search(Ctx& c, uint64_t q, uint64_t avail, Detection* det) {
         }
         // neighbourhood maximum (blocks bb-1 .. bb+1) for the scan kernel's own approximation error
         float nb = max_nan(info.y, max_nan(__shfl_up_sync(kFull, info.y, 1), __shfl_down_sync(kFull, info.y, 1)));
-        if (valid && lane == 0 && bb > 0) nb = max_nan(nb, c.blk_info[bb - 1].y);
+        if (valid && lane == 0) nb = max_nan(nb, c.blk_info[bb - 1].y);
         if (valid && lane == 31 && bb + 1 < c.nblk) nb = max_nan(nb, c.blk_info[bb + 1].y);
-        float incl = warp_incl_scan_maxnan(info.y, lane);
-        float up = __shfl_up_sync(kFull, incl, 1);
+        const float incl = warp_incl_scan_maxnan(info.y, lane);
+        const float up = __shfl_up_sync(kFull, incl, 1);
         const float excl = lane == 0 ? runmax : max_nan(runmax, up);
         const float run = max_nan(runmax, incl);
-        bool need = false;
+        bool need = false, hist_loose = false;
+        uint64_t wfirst = bb * TMK_BLK, s_first = q, kk = 0;
         if (valid) {
-            uint64_t wlast = bb * TMK_BLK + (TMK_BLK - 1);
+            uint64_t wlast = wfirst + (TMK_BLK - 1);
             if (wlast >= c.nwin) wlast = c.nwin - 1;
-            // longest chain inside the block: last window minus the earliest possible seed
-            const uint64_t wfirst = bb * TMK_BLK > q ? bb * TMK_BLK : q;
-            const uint64_t s_first = seed_for(c, wfirst, q, avail);
-            const uint64_t k = wlast - s_first;
-            float delta = drift_factor(c.P, k) * run * 1.001f + 64.f * kU * nb + 2.5f * kU * info.y;
-            const bool wellcond = k <= (1u << 20) && delta <= 0.04f * info.x;
+            s_first = seed_for(c, wfirst, q, avail);  // earliest seed of any window in the block
+            const bool same = s_first == c.a_seed;
+            kk = wlast - (same ? c.a_w : s_first);
+            const float e0 = same ? c.a_err : 0.f;
+            const float delta = drift_bound(P, kk, e0, run * 1.001f) + 128.f * kU * nb + 2.5f * kU * info.y;
+            // (1) no window of the block can reach the threshold even with the lowest possible E_ref:
+            //     corr_ref^2 = corr_true^2 * S / E_ref  with  E_ref >= max(S - delta, 1e-6)
+            float gain;  // upper bound of S / E_ref over the block
+            if (delta < 0.5f * info.x) gain = 1.0f / (1.0f - delta / (info.x * 0.999f));
+            else gain = info.y * 1.001f * 1e6f;
+            const bool fine = info.x >= 1e-3f * nb;  // the scan's corr^2 is accurate for every window
+            const bool safe = fine && info.z * 1.003f * gain < c.thr * c.thr * 0.999f;
             const bool is_silent = info.y < silent;
-            need = !is_silent && (!wellcond || any);
+            need = !is_silent && (any || !safe);
+            // (2) is the drift accumulated BEFORE this block what makes its windows undecidable?
+            hist_loose = drift_bound(P, kk, e0, excl * 1.001f) > 0.25f * kTight * info.x;
         }
-        uint32_t m = __ballot_sync(kFull, need);
-        while (m) {
-            const int j = __ffs(m) - 1;
-            m &= m - 1;
-            const float pmax = __shfl_sync(kFull, excl, j);
-            if (process_block(c, b0 + j, q, avail, pmax, det)) return true;
+        const uint32_t m = __ballot_sync(kFull, need);
+        if (m == 0) {
+            runmax = __shfl_sync(kFull, run, 31);
+            b0 += 32;
+            continue;
         }
-        runmax = __shfl_sync(kFull, run, 31);
+        const int j = __ffs(m) - 1;
+        const uint64_t wf = __shfl_sync(kFull, wfirst, j), sf = __shfl_sync(kFull, s_first, j);
+        const uint64_t kj = __shfl_sync(kFull, kk, j);
+        const bool hl = __shfl_sync(kFull, int(hist_loose), j) != 0;
+        const bool one_seed = c.C == 0 || seed_for(c, wf + TMK_BLK - 1 < c.nwin ? wf + TMK_BLK - 1 : c.nwin - 1, q, avail) == sf;
+        if (hl && one_seed && kj > 1024) {
+            // re-anchor: roll the reference's chain up to this block once and measure its drift
+            const float eref = exact_energy(c, sf, wf);
+            const float ec = window_energy(c, wf);
+            float err = fabsf(eref - ec) + 1.2f * kU * ec;
+            if (!(err == err)) err = __int_as_float(0x7f800000);
+            c.a_seed = sf;
+            c.a_w = wf;
+            c.a_err = err;
+            runmax = 0.f;
+            b0 += j;
+            continue;  // re-evaluate from this block with the measured anchor
+        }
+        const float pmax = __shfl_sync(kFull, excl, j);
+        float pm_blk;
+        if (process_block(c, b0 + j, q, avail, pmax, det, &pm_blk)) return true;
+        // continue behind block j; the running maximum now covers it
+        runmax = max_nan(pmax, __shfl_sync(kFull, info.y, j));
+        b0 += j + 1;
     }
     return false;
 }
@@ -369,7 +445,7 @@ __device__ uint64_t refine(const Ctx& c, const Detection& d) {
             float dot = 0.0f, we = 0.0f;
             for (uint32_t t = 0; t < sl; ++t) {
                 const float w = x[j + t];
-                dot = ex_add(dot, ex_mul(w, pre(c, P - sl + t)));
+                dot = ex_add(dot, ex_mul(w, c.sc->pre[P - sl + t]));
                 we = ex_add(we, ex_mul(w, w));
             }
             corr = (we > 1e-6f && pat->sync_energy > 1e-6f) ? ex_div(dot, ex_mul(ex_sqrt(we), pat->sync_energy)) : 0.0f;
@@ -415,58 +491,73 @@ __device__ uint32_t line_decode(const Ctx& c, uint64_t fs, uint32_t total_bits) 
     const uint32_t spl = c.pat->spl;
     const int lane = c.lane;
     uint8_t* bytes = c.sc->bytes;
+    constexpr int U = 8;  // iterations whose loads are issued together (the walk is latency bound)
     if (c.pat->line_code == TMK_LINE_MANCHESTER) {
-        for (uint32_t b0 = 0; b0 < total_bits; b0 += 32) {
-            const uint32_t bi = b0 + lane;
-            bool bit = false;
-            if (bi < total_bits) {
-                const float a = level_mean(s + uint64_t(bi) * 2 * spl, spl);
-                const float b = level_mean(s + uint64_t(bi) * 2 * spl + spl, spl);
-                bit = !(a > b);  // first_half > second_half -> 0, else 1 (tie -> 1)
+        for (uint32_t b0 = 0; b0 < total_bits; b0 += 32 * U) {
+            float a[U], b[U];
+#pragma unroll
+            for (int u = 0; u < U; ++u) {
+                const uint32_t bi = b0 + u * 32 + lane;
+                a[u] = b[u] = 0.f;
+                if (bi < total_bits) {
+                    a[u] = level_mean(s + uint64_t(bi) * 2 * spl, spl);
+                    b[u] = level_mean(s + uint64_t(bi) * 2 * spl + spl, spl);
+                }
             }
-            const uint32_t rev = __brev(__ballot_sync(kFull, bit));
-            if (lane < 4 && b0 + lane * 8 < total_bits) bytes[b0 / 8 + lane] = uint8_t(rev >> (24 - 8 * lane));
+#pragma unroll
+            for (int u = 0; u < U; ++u) {
+                const uint32_t bb = b0 + u * 32;
+                if (bb >= total_bits) break;
+                const bool bit = (bb + lane < total_bits) && !(a[u] > b[u]);  // first > second -> 0, else 1 (tie -> 1)
+                const uint32_t rev = __brev(__ballot_sync(kFull, bit));
+                if (lane < 4 && bb + lane * 8 < total_bits) bytes[bb / 8 + lane] = uint8_t(rev >> (24 - 8 * lane));
+            }
         }
         __syncwarp();
         return total_bits;
     }
     const uint32_t nlev = (total_bits / 4) * 5;
     float last = 1.0f;  // prev_level_avg restarts at 1.0 on every decode call (line_coding.rs:251)
-    uint32_t nb = 0, hi = 0;
+    uint32_t nb = 0;
     bool stop = false;
-    for (uint32_t l0 = 0; l0 < nlev && !stop; l0 += 30) {
-        const uint32_t li = l0 + lane;
-        const bool active = lane < 30 && li < nlev;
-        const float cur = active ? level_mean(s + uint64_t(li) * spl, spl) : 0.0f;
-        const bool valid = active && fabsf(cur) > 1e-6f;
-        const uint32_t vm = __ballot_sync(kFull, valid);
-        const uint32_t below = vm & ((1u << lane) - 1u);
-        const int src = below ? 31 - __clz(below) : 0;
-        const float pv = __shfl_sync(kFull, cur, src);
-        const float lastv = below ? pv : last;
-        const bool bit = active && ex_mul(lastv, cur) < 0.0f;
-        const uint32_t bm = __ballot_sync(kFull, bit);
-        if (vm) last = __shfl_sync(kFull, cur, 31 - __clz(vm));
-        uint32_t nsy = (nlev - l0) / 5;
-        if (nsy > 6) nsy = 6;
-        for (uint32_t k = 0; k < nsy; ++k) {
-            uint32_t sym = 0;
+    for (uint32_t g0 = 0; g0 < nlev && !stop; g0 += 30 * U) {
+        float curs[U];
 #pragma unroll
-            for (int j = 0; j < 5; ++j) sym = (sym << 1) | ((bm >> (5 * k + j)) & 1u);
+        for (int u = 0; u < U; ++u) {
+            const uint32_t li = g0 + u * 30 + lane;
+            curs[u] = (lane < 30 && li < nlev) ? level_mean(s + uint64_t(li) * spl, spl) : 0.0f;
+        }
+#pragma unroll
+        for (int u = 0; u < U; ++u) {
+            const uint32_t l0 = g0 + u * 30;
+            if (l0 >= nlev || stop) break;
+            const uint32_t li = l0 + lane;
+            const bool active = lane < 30 && li < nlev;
+            const float cur = curs[u];
+            const bool valid = active && fabsf(cur) > 1e-6f;
+            const uint32_t vm = __ballot_sync(kFull, valid);
+            const uint32_t below = vm & ((1u << lane) - 1u);
+            const int src = below ? 31 - __clz(below) : 0;
+            const float pv = __shfl_sync(kFull, cur, src);
+            const float lastv = below ? pv : last;
+            const bool bit = active && ex_mul(lastv, cur) < 0.0f;
+            const uint32_t bm = __ballot_sync(kFull, bit);
+            if (vm) last = __shfl_sync(kFull, cur, 31 - __clz(vm));
+            uint32_t nsy = (nlev - l0) / 5;
+            if (nsy > 6) nsy = 6;
+            // lane k decodes symbol k (levels 5k..5k+4, first level = MSB); an iteration always
+            // starts on a byte boundary (6 symbols = 3 bytes)
+            const uint32_t sym = __brev((bm >> (5 * (lane < 6 ? lane : 0))) & 31u) >> 27;
             const int nib = c_dec5[sym];
-            if (nib < 0) {
-                stop = true;
-                break;
-            }
-            if ((nb & 7u) == 0) {
-                hi = uint32_t(nib) << 4;
-            } else if (lane == 0) {
-                bytes[nb >> 3] = uint8_t(hi | uint32_t(nib));
-            }
-            nb += 4;
+            const uint32_t inv = __ballot_sync(kFull, uint32_t(lane) < nsy && nib < 0);
+            const uint32_t nval = inv ? uint32_t(__ffs(inv) - 1) : nsy;
+            const int lo = __shfl_down_sync(kFull, nib, 1);
+            if (lane < 6 && (lane & 1) == 0 && uint32_t(lane) < nval)
+                bytes[(nb >> 3) + (lane >> 1)] = uint8_t((uint32_t(nib) << 4) | (uint32_t(lane) + 1 < nval ? uint32_t(lo) : 0u));
+            nb += 4 * nval;
+            if (inv) stop = true;
         }
     }
-    if ((nb & 7u) == 4 && lane == 0) bytes[nb >> 3] = uint8_t(hi);  // trailing nibble, low bits zero
     __syncwarp();
     return nb;
 }
@@ -535,14 +626,20 @@ __device__ void emit(const Ctx& c, Emit& em, uint32_t status, const Detection& d
     em.ord++;
 }
 
-__global__ void __launch_bounds__(kWarpsPerCta * 32)
+__global__ void __launch_bounds__(kWarpsPerCta * 32, 4)
 walk_kernel(const float* __restrict__ samples, const TmkStreamDev* __restrict__ streams, uint32_t n_streams,
-            const TmkPattern* __restrict__ patterns, const float2* __restrict__ blk_info,
+            const TmkPattern* __restrict__ patterns, const float4* __restrict__ blk_info,
             const uint32_t* __restrict__ cand_bits, tmk_frame_rec* recs, uint32_t* rec_ord, uint64_t rec_cap,
             uint8_t* payload, uint64_t payload_cap, uint32_t* stream_cnt, TmkCounters* counters) {
     __shared__ WarpScratch scratch[kWarpsPerCta];
     const uint32_t warp = threadIdx.x >> 5;
-    const uint32_t sidx = blockIdx.x * kWarpsPerCta + warp;
+    const int lane_id = threadIdx.x & 31;
+    // persistent warps: streams differ a lot in cost (idle noise vs dense traffic), so every warp
+    // pulls the next stream from a counter instead of owning a fixed one
+    for (;;) {
+    uint32_t sidx = 0;
+    if (lane_id == 0) sidx = atomicAdd(&counters->next_stream, 1u);
+    sidx = __shfl_sync(kFull, sidx, 0);
     if (sidx >= n_streams) return;
     const TmkStreamDev sd = streams[sidx];
     Ctx c;
@@ -558,12 +655,17 @@ walk_kernel(const float* __restrict__ samples, const TmkStreamDev* __restrict__ 
     c.thr = sd.threshold;
     c.local_addr = sd.local_addr;
     c.max_frame_bytes = sd.max_frame_bytes;
-    c.lane = threadIdx.x & 31;
+    c.lane = lane_id;
     c.sc = &scratch[warp];
     c.rvalid = false;
     c.rseed = c.rpos = 0;
     c.rE = 0.f;
+    c.a_seed = c.a_w = 0;
+    c.a_err = 0.f;
     c.n_replays = c.n_cands = c.n_det = 0;
+    __syncwarp();
+    for (uint32_t k = lane_id; k < c.P; k += 32) c.sc->pre[k] = c.pat->levels[k / c.pat->spl];
+    __syncwarp();
     Emit em{recs, rec_ord, rec_cap, payload, payload_cap, counters, sidx, 0};
     uint32_t n_ok = 0, n_crc = 0, n_hdr = 0, n_nfu = 0;
 
@@ -650,6 +752,7 @@ walk_kernel(const float* __restrict__ samples, const TmkStreamDev* __restrict__ 
         atomicAdd(&counters->stats[TMK_STAT_EXACT_REPLAYS], (unsigned long long)c.n_replays);
         atomicAdd(&counters->stats[TMK_STAT_CANDIDATES], (unsigned long long)c.n_cands);
     }
+    }  // next stream
 }
 
 // ---------------------------------------------------------------- ordering of the records
@@ -720,11 +823,20 @@ int tmk_launch_excl_scan(const uint32_t* cnt, uint64_t* base, uint32_t n, cudaSt
 }
 
 int tmk_launch_walk(const float* samples, const TmkStreamDev* streams, uint32_t n_streams,
-                    const TmkPattern* patterns, const float2* blk_info, const uint32_t* cand_bits,
+                    const TmkPattern* patterns, const float4* blk_info, const uint32_t* cand_bits,
                     tmk_frame_rec* recs, uint32_t* rec_ord, uint64_t rec_cap, uint8_t* payload,
                     uint64_t payload_cap, uint32_t* stream_cnt, TmkCounters* counters, cudaStream_t st) {
     if (n_streams == 0) return 0;
-    const uint32_t grid = (n_streams + kWarpsPerCta - 1) / kWarpsPerCta;
+    static int max_ctas = 0;
+    if (max_ctas == 0) {
+        int dev = 0, sms = 0, per_sm = 0;
+        cudaGetDevice(&dev);
+        cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+        cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, walk_kernel, kWarpsPerCta * 32, 0);
+        max_ctas = sms * (per_sm > 0 ? per_sm : 1);
+    }
+    uint32_t grid = (n_streams + kWarpsPerCta - 1) / kWarpsPerCta;
+    if (grid > uint32_t(max_ctas)) grid = uint32_t(max_ctas);
     walk_kernel<<<grid, kWarpsPerCta * 32, 0, st>>>(samples, streams, n_streams, patterns, blk_info, cand_bits, recs,
                                                     rec_ord, rec_cap, payload, payload_cap, stream_cnt, counters);
     return 1;
