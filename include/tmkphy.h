@@ -162,6 +162,16 @@ int tmk_decode_batch(tmk_engine* e, const float* samples, uint64_t total_samples
 int tmk_correlate(tmk_engine* e, const float* samples, uint64_t total_samples, const tmk_stream* streams,
                   uint32_t n_streams, float* corr_out);
 
+/* Diagnostic: the raw output of the preamble scan kernel (the candidate filter in front of the walk).
+ * Blocks are TMK_SCAN_BLOCK windows; stream i owns blocks blk_base[i] .. blk_base[i] + ceil(nwin_i / block) - 1.
+ * blk_info: 4 floats per block (min window energy, max window energy, max corr^2, #candidates);
+ * cand_bits: TMK_SCAN_BLOCK / 32 words per block, bit w = window w of the block passed
+ * corr >= threshold * 0.85 / 0.9. Host pointers only. */
+#define TMK_SCAN_BLOCK 480
+int tmk_scan_probe(tmk_engine* e, const float* samples, uint64_t total_samples, const tmk_stream* streams,
+                   uint32_t n_streams, float* blk_info, uint32_t* cand_bits, uint64_t block_cap, uint64_t* n_blocks,
+                   uint64_t* blk_base);
+
 /* busy[i] = -1 (fewer than 20 samples), 0 or 1 : mac::is_channel_busy per stream */
 int tmk_channel_busy(tmk_engine* e, const float* samples, uint64_t total_samples, const tmk_stream* streams,
                      uint32_t n_streams, int8_t* busy);

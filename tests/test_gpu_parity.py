@@ -282,3 +282,47 @@ def test_stats_and_launch_count(engine, orc):
     assert stt["samples"] == len(c) and stt["detections"] == len(recs)
     assert stt["frames_ok"] == int((recs["status"] == 0).sum())
     assert stt["not_for_us"] == int((recs["status"] == 4).sum())
+
+
+@pytest.mark.parametrize("kind,spl,pb", [(FB, 3, 2), (MAN, 3, 2), (FB, 4, 2), (MAN, 2, 1)])
+def test_scan_filter_contract(engine, orc, kind, spl, pb):
+    """the scan kernels (fast for the shipped constants, general otherwise) against float64 numpy:
+    every window with corr >= 0.85/0.9*thr is marked, none clearly below is; block summaries agree"""
+    import tmkphy
+    rng = np.random.default_rng(61 + kind + spl)
+    cfg = tmkphy.make_config(kind, local_addr=1, spl=spl, preamble_bytes=pb)
+    caps = [helpers.make_capture(orc, cfg, rng, n_frames=12, snr_db=snr, amplitude=amp, max_len=60)
+            for snr, amp in ((6, 1.0), (10, 0.3), (None, 1.0), (3, 50.0), (20, 1e-3))]
+    caps.append(caps[0][:4000])
+    caps.append(caps[1][:481 + len(orc.preamble(kind, spl, pb))])
+    s, st = helpers.pack(caps, cfg, tmkphy)
+    info, bits, base = engine.scan_probe(s, st)
+    pre = orc.preamble(kind, spl, pb).astype(np.float64)
+    P = len(pre)
+    thr_c = np.float32(0.9) * np.float32(0.9444444)
+    for i, c in enumerate(caps):
+        x = c.astype(np.float64)
+        nwin = len(x) - P + 1
+        D = np.correlate(x, pre, mode="valid")
+        cs = np.concatenate([[0.0], np.cumsum(x * x)])
+        E = cs[P:] - cs[:-P]
+        corr = np.where(E > 0, D / np.sqrt(np.maximum(E, 1e-300) * P), 0.0)
+        nb = (nwin + 479) // 480
+        b0 = int(base[i])
+        got_bits = np.unpackbits(bits[b0:b0 + nb].view(np.uint8), bitorder="little").reshape(nb, 480 + 0)[:, :480].reshape(-1)[:nwin]
+        must = corr >= thr_c * 1.002
+        must_not = corr < thr_c * 0.998
+        assert got_bits[must].all(), f"capture {i}: {(must & (got_bits == 0)).sum()} windows above the filter level are unmarked"
+        assert not got_bits[must_not].any(), f"capture {i}: windows below the filter level are marked"
+        for b in range(nb):
+            e = E[b * 480:(b + 1) * 480]
+            cc = corr[b * 480:(b + 1) * 480]
+            emin, emax, rmax, ncand = info[b0 + b]
+            tol = 1e-3 * e.max() + 1e-30
+            assert abs(emin - e.min()) <= tol and abs(emax - e.max()) <= tol, (i, b, emin, e.min(), emax, e.max())
+            want_r = max(0.0, cc.max()) ** 2
+            # max corr^2 is an upper bound the walk relies on; tight when the block is well conditioned
+            assert rmax >= want_r * (1 - 2e-3) - 1e-6, (i, b, rmax, want_r)
+            if e.min() >= 1e-3 * e.max():
+                assert rmax <= want_r * (1 + 2e-3) + 1e-6, (i, b, rmax, want_r)
+            assert ncand == got_bits[b * 480:(b + 1) * 480].sum()

@@ -44,7 +44,7 @@ struct tmk_engine {
     cudaStream_t copy_stream = nullptr;
     std::string err;
     std::vector<TmkPattern> patterns;  // host mirror of the device pattern table
-    DevBuf d_patterns, d_streams, d_blk_info, d_cand, d_recs_tmp, d_rec_ord, d_recs, d_payload, d_cnt, d_base,
+    DevBuf d_tile_dir, d_patterns, d_streams, d_blk_info, d_cand, d_recs_tmp, d_rec_ord, d_recs, d_payload, d_cnt, d_base,
         d_counters, d_samples, d_misc, d_misc2;
     cudaEvent_t ev[6] = {};
     cudaEvent_t tev[2] = {};
@@ -149,6 +149,7 @@ int pattern_index(tmk_engine* e, const tmk_phy_config& c, uint32_t* out) {
 struct Batch {
     std::vector<TmkStreamDev> sd;
     uint64_t n_tiles = 0, n_blocks = 0;
+    uint32_t kinds = 0;  // which scan kernels the batch needs
 };
 
 int prepare_batch(tmk_engine* e, uint64_t total_samples, const tmk_stream* streams, uint32_t n_streams, Batch* b) {
@@ -178,6 +179,8 @@ int prepare_batch(tmk_engine* e, uint64_t total_samples, const tmk_stream* strea
         d.max_frame_bytes = st.cfg.max_frame_bytes;
         d.chunk = st.cfg.chunk;
         tiles += d.n_tiles;
+        const TmkPattern& pp = e->patterns[pi];
+        if (d.n_tiles) b->kinds |= (pp.spl == 3 && pp.preamble_bytes == 2) ? (pp.line_code == TMK_LINE_4B5B ? 1u : 2u) : 4u;
     }
     b->n_tiles = tiles;
     b->n_blocks = tiles * TMK_TILE_BLKS;
@@ -237,7 +240,7 @@ void tmk_engine_destroy(tmk_engine* e) {
     if (!e) return;
     cudaSetDevice(e->device);
     if (e->stream) cudaStreamSynchronize(e->stream);
-    DevBuf* bufs[] = {&e->d_patterns, &e->d_streams, &e->d_blk_info, &e->d_cand, &e->d_recs_tmp, &e->d_rec_ord,
+    DevBuf* bufs[] = {&e->d_tile_dir, &e->d_patterns, &e->d_streams, &e->d_blk_info, &e->d_cand, &e->d_recs_tmp, &e->d_rec_ord,
                       &e->d_recs, &e->d_payload, &e->d_cnt, &e->d_base, &e->d_counters, &e->d_samples,
                       &e->d_misc, &e->d_misc2};
     for (DevBuf* b : bufs) b->release();
@@ -361,8 +364,14 @@ int tmk_decode_batch(tmk_engine* e, const float* samples, uint64_t total_samples
     uint32_t* dcb = static_cast<uint32_t*>(e->d_cand.p);
     TmkCounters* dc = static_cast<TmkCounters*>(e->d_counters.p);
 
+    if (reinterpret_cast<uintptr_t>(dx) % 16 != 0) return fail(e, TMK_E_INVALID, "sample buffer must be 16-byte aligned");
+    CK(e->d_tile_dir.reserve(sizeof(uint32_t) * std::max<uint64_t>(1, b.n_tiles)));
+    uint32_t* dtd = static_cast<uint32_t*>(e->d_tile_dir.p);
     CK(cudaEventRecord(e->ev[1], e->stream));
-    e->launches += tmk_launch_scan(dx, ds, n_streams, uint32_t(b.n_tiles), dp, dbi, dcb, e->stream);
+    e->launches += tmk_launch_tile_dir(ds, n_streams, uint32_t(b.n_tiles), dtd, e->stream);
+    CK(cudaMemsetAsync(dcb, 0, sizeof(uint32_t) * TMK_BLK_WORDS * b.n_blocks, e->stream));
+    e->launches += tmk_launch_scan(dx, total_samples, ds, n_streams, dtd, uint32_t(b.n_tiles), dp, b.kinds, dbi, dcb,
+                                   e->stream);
     CK(cudaGetLastError());
     CK(cudaEventRecord(e->ev[2], e->stream));
 
@@ -446,6 +455,43 @@ int tmk_correlate(tmk_engine* e, const float* samples, uint64_t total_samples, c
                                         n_streams, static_cast<const TmkPattern*>(e->d_patterns.p), d_out, e->stream);
     CK(cudaGetLastError());
     if (!dev_out) CK(cudaMemcpyAsync(corr_out, d_out, total_samples * sizeof(float), cudaMemcpyDeviceToHost, e->stream));
+    CK(cudaStreamSynchronize(e->stream));
+    return TMK_OK;
+}
+
+int tmk_scan_probe(tmk_engine* e, const float* samples, uint64_t total_samples, const tmk_stream* streams,
+                   uint32_t n_streams, float* blk_info, uint32_t* cand_bits, uint64_t block_cap, uint64_t* n_blocks,
+                   uint64_t* blk_base) {
+    static_assert(TMK_SCAN_BLOCK == TMK_BLK, "header and kernels disagree on the scan block size");
+    if (!e || !samples || !streams || !blk_info || !cand_bits || !n_blocks || !blk_base)
+        return fail(e, TMK_E_INVALID, "tmk_scan_probe: null argument");
+    CK(cudaSetDevice(e->device));
+    Batch b;
+    int rc = prepare_batch(e, total_samples, streams, n_streams, &b);
+    if (rc != TMK_OK) return rc;
+    *n_blocks = b.n_blocks;
+    for (uint32_t s = 0; s < n_streams; ++s) blk_base[s] = b.sd[s].blk_base;
+    if (b.n_blocks > block_cap) return fail(e, TMK_E_CAPACITY, "tmk_scan_probe: block buffers too small");
+    if (b.n_blocks == 0) return TMK_OK;
+    CK(e->d_streams.reserve(sizeof(TmkStreamDev) * n_streams));
+    CK(cudaMemcpyAsync(e->d_streams.p, b.sd.data(), sizeof(TmkStreamDev) * n_streams, cudaMemcpyHostToDevice, e->stream));
+    const void* d_samples = nullptr;
+    rc = stage_in(e, e->d_samples, samples, total_samples * sizeof(float), &d_samples);
+    if (rc != TMK_OK) return rc;
+    CK(e->d_blk_info.reserve(sizeof(float4) * b.n_blocks));
+    CK(e->d_cand.reserve(sizeof(uint32_t) * TMK_BLK_WORDS * b.n_blocks));
+    CK(e->d_tile_dir.reserve(sizeof(uint32_t) * b.n_tiles));
+    const TmkStreamDev* ds = static_cast<const TmkStreamDev*>(e->d_streams.p);
+    uint32_t* dtd = static_cast<uint32_t*>(e->d_tile_dir.p);
+    CK(cudaMemsetAsync(e->d_blk_info.p, 0, sizeof(float4) * b.n_blocks, e->stream));
+    CK(cudaMemsetAsync(e->d_cand.p, 0, sizeof(uint32_t) * TMK_BLK_WORDS * b.n_blocks, e->stream));
+    e->launches += tmk_launch_tile_dir(ds, n_streams, uint32_t(b.n_tiles), dtd, e->stream);
+    e->launches += tmk_launch_scan(static_cast<const float*>(d_samples), total_samples, ds, n_streams, dtd,
+                                   uint32_t(b.n_tiles), static_cast<const TmkPattern*>(e->d_patterns.p), b.kinds,
+                                   static_cast<float4*>(e->d_blk_info.p), static_cast<uint32_t*>(e->d_cand.p), e->stream);
+    CK(cudaGetLastError());
+    CK(cudaMemcpyAsync(blk_info, e->d_blk_info.p, sizeof(float4) * b.n_blocks, cudaMemcpyDeviceToHost, e->stream));
+    CK(cudaMemcpyAsync(cand_bits, e->d_cand.p, sizeof(uint32_t) * TMK_BLK_WORDS * b.n_blocks, cudaMemcpyDeviceToHost, e->stream));
     CK(cudaStreamSynchronize(e->stream));
     return TMK_OK;
 }

@@ -16,33 +16,18 @@ namespace {
 constexpr int kThreads = 256;
 constexpr int kSmemX = TMK_TILE + TMK_MAX_P + 8;
 
-// stream that owns scan tile `tile` (streams are sorted by tile_base)
-__device__ __forceinline__ uint32_t find_stream(const TmkStreamDev* __restrict__ streams, uint32_t n_streams,
-                                                uint32_t tile) {
-    uint32_t lo = 0, hi = n_streams - 1;
-    while (lo < hi) {
-        uint32_t mid = (lo + hi + 1) >> 1;
-        if (streams[mid].tile_base <= tile) lo = mid; else hi = mid - 1;
-    }
-    // skip streams without tiles that share the same tile_base
-    while (streams[lo].n_tiles == 0 && lo + 1 < n_streams) ++lo;
-    return lo;
-}
-
 __global__ void __launch_bounds__(kThreads)
 scan_generic_kernel(const float* __restrict__ samples, const TmkStreamDev* __restrict__ streams,
-                    uint32_t n_streams, const TmkPattern* __restrict__ patterns, float4* __restrict__ blk_info,
-                    uint32_t* __restrict__ cand_bits) {
+                    const uint32_t* __restrict__ tile_stream, const TmkPattern* __restrict__ patterns,
+                    float4* __restrict__ blk_info, uint32_t* __restrict__ cand_bits) {
     __shared__ float xs[kSmemX];   // raw samples, then box sums of spl samples
     __shared__ float qs[kSmemX];   // box sums of spl squared samples
     __shared__ float lev[TMK_MAX_LEVELS];
-    __shared__ uint32_t s_stream;
 
     const uint32_t tile = blockIdx.x;
-    if (threadIdx.x == 0) s_stream = find_stream(streams, n_streams, tile);
-    __syncthreads();
-    const TmkStreamDev sd = streams[s_stream];
+    const TmkStreamDev sd = streams[tile_stream[tile]];
     const TmkPattern* pat = patterns + sd.pattern;
+    if (pat->spl == 3 && pat->preamble_bytes == 2) return;  // scan_fast.cu owns the shipped shapes
     const uint32_t P = pat->P, L = pat->L, spl = pat->spl;
     const uint64_t n = sd.n_samples;
     const uint64_t nwin = n - P + 1;  // n >= P, otherwise the stream has no tiles
@@ -96,7 +81,7 @@ scan_generic_kernel(const float* __restrict__ samples, const TmkStreamDev* __res
     const uint32_t warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const uint32_t bw0 = warp * TMK_BLK;  // this warp's block inside the tile
     float emin = __int_as_float(0x7f800000), emax = 0.f, dmax = 0.f;
-    uint32_t myword = 0;
+    uint32_t myword = 0, ncand = 0;
 #pragma unroll 1
     for (uint32_t i = 0; i < TMK_BLK_WORDS; ++i) {
         const uint32_t w = bw0 + i * 32 + lane;
@@ -113,6 +98,7 @@ scan_generic_kernel(const float* __restrict__ samples, const TmkStreamDev* __res
             if (D > 0.f) dmax = fmaxf(dmax, D * D / (float(P) * E));  // largest corr^2 of the block
         }
         const uint32_t word = __ballot_sync(0xffffffffu, cand);
+        ncand += __popc(word);
         if (lane == i) myword = word;
     }
 #pragma unroll
@@ -125,15 +111,16 @@ scan_generic_kernel(const float* __restrict__ samples, const TmkStreamDev* __res
     if (blk_in_stream * TMK_BLK < nwin) {
         const uint64_t gb = sd.blk_base + blk_in_stream;
         if (lane < TMK_BLK_WORDS) cand_bits[gb * TMK_BLK_WORDS + lane] = myword;
-        if (lane == 0) blk_info[gb] = make_float4(emin, emax, dmax, 0.f);
+        if (lane == 0) blk_info[gb] = make_float4(emin, emax, dmax, float(ncand));
     }
 }
 
 }  // namespace
 
-int tmk_launch_scan(const float* samples, const TmkStreamDev* streams, uint32_t n_streams, uint32_t n_tiles,
-                            const TmkPattern* patterns, float4* blk_info, uint32_t* cand_bits, cudaStream_t st) {
+int tmk_launch_scan_generic(const float* samples, const TmkStreamDev* streams, const uint32_t* tile_stream,
+                            uint32_t n_tiles, const TmkPattern* patterns, float4* blk_info, uint32_t* cand_bits,
+                            cudaStream_t st) {
     if (n_tiles == 0) return 0;
-    scan_generic_kernel<<<n_tiles, kThreads, 0, st>>>(samples, streams, n_streams, patterns, blk_info, cand_bits);
+    scan_generic_kernel<<<n_tiles, kThreads, 0, st>>>(samples, streams, tile_stream, patterns, blk_info, cand_bits);
     return 1;
 }

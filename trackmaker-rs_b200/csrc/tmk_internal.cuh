@@ -2,8 +2,9 @@
 //
 // Data layout in HBM:
 //   samples      float[total]             all captures of a batch, stream s at streams[s].offset
-//   blk_info     float4[n_blocks]         per block of TMK_BLK windows: (min E, max E, max corr^2, 0)
-//   cand_bits    uint32[n_blocks * 8]     1 bit per window: corr_approx >= thr * CAND_RATIO
+//   blk_info     float4[n_blocks]         per block of TMK_BLK windows: (min E, max E, max corr^2,
+//                                          number of candidate windows as float)
+//   cand_bits    uint32[n_blocks * 15]    1 bit per window: corr_approx >= thr * CAND_RATIO
 //   recs/payload tmk_frame_rec[] / u8[]   verdict records + decoded payload bytes
 //
 // "Exact" device helpers use __fadd_rn/__fmul_rn/__fdiv_rn/__fsqrt_rn so that nvcc never
@@ -15,10 +16,11 @@
 
 #include "../../include/tmkphy.h"
 
-#define TMK_BLK 256          // windows per block (candidate bitmap / energy summary granularity)
-#define TMK_BLK_WORDS 8      // TMK_BLK / 32
+#define TMK_BLK 480          // windows per block (candidate bitmap / energy summary granularity):
+                             // 4 lanes x 120 windows of the fast scan kernel, 15 whole bitmap words
+#define TMK_BLK_WORDS 15     // TMK_BLK / 32
 #define TMK_TILE_BLKS 8      // blocks per scan tile
-#define TMK_TILE (TMK_BLK * TMK_TILE_BLKS)  // 2048 windows per scan tile
+#define TMK_TILE (TMK_BLK * TMK_TILE_BLKS)  // 3840 windows per scan tile (one warp of the fast kernel)
 #define TMK_MAX_P 1024       // longest supported preamble in samples
 #define TMK_MAX_LEVELS 512   // longest supported preamble in levels
 #define TMK_CAND_RATIO 0.9444444f  // candidate filter keeps corr_approx >= thr * (0.85 / 0.9)
@@ -101,8 +103,15 @@ __device__ __forceinline__ uint32_t crc8_step(uint32_t crc, uint32_t byte) {
 #endif
 
 // kernel launchers (each returns the number of kernels it launched)
-int tmk_launch_scan(const float* samples, const TmkStreamDev* streams, uint32_t n_streams, uint32_t n_tiles,
-                    const TmkPattern* patterns, float4* blk_info, uint32_t* cand_bits, cudaStream_t st);
+int tmk_launch_tile_dir(const TmkStreamDev* streams, uint32_t n_streams, uint32_t n_tiles, uint32_t* tile_stream,
+                        cudaStream_t st);
+// kinds: bit 0 = 4B5B/spl 3/2 bytes streams present, bit 1 = Manchester/3/2, bit 2 = any other shape
+int tmk_launch_scan(const float* samples, uint64_t total_samples, const TmkStreamDev* streams, uint32_t n_streams,
+                    const uint32_t* tile_stream, uint32_t n_tiles, const TmkPattern* patterns, uint32_t kinds,
+                    float4* blk_info, uint32_t* cand_bits, cudaStream_t st);
+int tmk_launch_scan_generic(const float* samples, const TmkStreamDev* streams, const uint32_t* tile_stream,
+                            uint32_t n_tiles, const TmkPattern* patterns, float4* blk_info, uint32_t* cand_bits,
+                            cudaStream_t st);
 int tmk_launch_walk(const float* samples, const TmkStreamDev* streams, uint32_t n_streams,
                     const TmkPattern* patterns, const float4* blk_info, const uint32_t* cand_bits,
                     tmk_frame_rec* recs, uint32_t* rec_ord, uint64_t rec_cap, uint8_t* payload,

@@ -22,7 +22,7 @@ namespace {
 constexpr int kWarpsPerCta = 4;
 constexpr int kMaxFrameBytesCap = 1024;                 // cfg.max_frame_bytes upper limit
 constexpr int kByteBuf = TMK_PHY_HEADER_BYTES + kMaxFrameBytesCap + 9;
-constexpr int kQBuf = TMK_BLK + 256;                    // prefix sums for P <= 255
+constexpr int kQBuf = TMK_BLK + 256;                    // prefix sums of one block for P <= 255
 constexpr float kU = 5.9604645e-8f;                     // 2^-24, unit roundoff of f32
 constexpr unsigned kFull = 0xffffffffu;
 // A window outside the candidate bitmap has corr_approx < thr * TMK_CAND_RATIO; the reference can
@@ -358,9 +358,7 @@ __device__ bool search(Ctx& c, uint64_t q, uint64_t avail, Detection* det) {
         bool any = false;
         if (valid) {
             info = c.blk_info[bb];
-            const uint4* wp = reinterpret_cast<const uint4*>(c.cand_bits + bb * TMK_BLK_WORDS);
-            uint4 a = wp[0], b = wp[1];
-            any = (a.x | a.y | a.z | a.w | b.x | b.y | b.z | b.w) != 0u;
+            any = info.w != 0.f;
         }
         // neighbourhood maximum (blocks bb-1 .. bb+1) for the scan kernel's own approximation error
         float nb = max_nan(info.y, max_nan(__shfl_up_sync(kFull, info.y, 1), __shfl_down_sync(kFull, info.y, 1)));

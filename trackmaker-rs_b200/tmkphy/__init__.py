@@ -220,6 +220,19 @@ class Engine:
         self._check(self._lib.tmk_correlate(self._h, _ptr(s), s.size, _ptr(st), len(st), _ptr(out)))
         return out
 
+    def scan_probe(self, samples, streams):
+        """raw scan-kernel output: (blk_info[n_blocks,4], cand_bits[n_blocks,15], blk_base[n_streams])"""
+        s = np.ascontiguousarray(samples, dtype=np.float32)
+        st = np.ascontiguousarray(streams, dtype=STREAM_DTYPE)
+        cap = int(sum((int(n) + 479) // 480 for n in st["n_samples"])) + 8 * len(st) + 8
+        info = np.zeros((cap, 4), np.float32)
+        bits = np.zeros((cap, 15), np.uint32)
+        base = np.zeros(len(st), np.uint64)
+        nb = C.c_uint64(0)
+        self._check(self._lib.tmk_scan_probe(self._h, _ptr(s), s.size, _ptr(st), len(st), _ptr(info), _ptr(bits), cap,
+                                             C.byref(nb), _ptr(base)))
+        return info[:nb.value], bits[:nb.value], base
+
     def channel_busy(self, samples, streams):
         s = np.ascontiguousarray(samples, dtype=np.float32)
         st = np.ascontiguousarray(streams, dtype=STREAM_DTYPE)

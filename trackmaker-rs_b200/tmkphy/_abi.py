@@ -76,6 +76,7 @@ SYMBOLS = {
     "tmk_modulate": (C.c_int, [_vp, _pcfg, _vp, _u32, _vp, _u64, _u32, _vp, _u64, _pu64]),
     "tmk_decode_batch": (C.c_int, [_vp, _vp, _u64, _vp, _u32, _vp, _u64, _pu64, _vp, _u64, _pu64]),
     "tmk_correlate": (C.c_int, [_vp, _vp, _u64, _vp, _u32, _vp]),
+    "tmk_scan_probe": (C.c_int, [_vp, _vp, _u64, _vp, _u32, _vp, _vp, _u64, _pu64, _vp]),
     "tmk_channel_busy": (C.c_int, [_vp, _vp, _u64, _vp, _u32, _vp]),
     "tmk_stats": (C.c_int, [_vp, _pu64]),
     "tmk_stats_reset": (C.c_int, [_vp]),
