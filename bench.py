@@ -108,7 +108,7 @@ def run_reference(args):
     n_s = max(64, 8 * threads)
     n_per = 120000
     caps = []
-    base = [helpers.make_capture(orc, cfg, np.random.default_rng(100 + i), n_frames=40, snr_db=SNRS[i % 8],
+    base = [helpers.make_capture(orc, cfg, np.random.default_rng(100 + i), n_frames=40, snr_db=SNRS[i % len(SNRS)],
                                  gap_range=(48, 4800)) for i in range(16)]
     for i in range(n_s):
         b = base[i % 16]
@@ -144,8 +144,12 @@ def main():
     ap.add_argument("--chunk", type=int, default=0)
     ap.add_argument("--e2e-steps", type=int, default=3)
     ap.add_argument("--no-cpu", action="store_true")
+    ap.add_argument("--snrs", default="", help="comma-separated SNRs in dB replacing the C2 sweep (diagnostics)")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 0)
+    if args.snrs:
+        global SNRS
+        SNRS = [float(v) for v in args.snrs.split(",")]
     if args.impl == "reference":
         return run_reference(args)
 
@@ -260,7 +264,7 @@ def main():
             "metric": METRIC, "value": world * total * args.steps / (ms_all * 1e-3) / 1e6, "unit": "Msamples/s",
             "n_gpus": world, "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms_all / args.steps,
             "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-            "config": {"workload": WORKLOAD if (n_s, n_per, kind) == (N_STREAMS, N_PER_STREAM, tmkphy.LINE_4B5B)
+            "config": {"workload": WORKLOAD if (n_s, n_per, kind) == (N_STREAMS, N_PER_STREAM, tmkphy.LINE_4B5B) and not args.snrs
                        else f"{n_s} streams x {n_per} samples, line code {args.line_code}",
                        "streams_per_gpu": n_s, "samples_per_stream": n_per, "line_code": args.line_code,
                        "chunk": args.chunk, "l2": "inputs (7.9 GB/GPU) far larger than the 126 MB L2",
