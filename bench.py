@@ -276,7 +276,8 @@ def main():
                          "algorithmic_bytes_per_launch": 4 * total},
             "clocks": sampler.summary(),
             "decode": {"records": int(counters[0]), "payload_bytes": int(counters[1]), "frames_planted": int(counters[2]),
-                       **{k: int(v) for k, v in zip(tmkphy.STAT_NAMES, counters[3:])}},
+                       **{k: int(v) for k, v in zip(tmkphy.STAT_NAMES, counters[3:])},
+                       "walk_last_step": eng.debug_counters()},
         }
         if e2e_all is not None:
             out["e2e"] = {"value": world * total * args.e2e_steps / (e2e_all * 1e-3) / 1e6, "unit": "Msamples/s",
@@ -286,20 +287,38 @@ def main():
             from oracle import oracle as orc
             orc.build()
             threads = host_threads()
+
+            def gather(n_cpu):
+                """n_cpu of the captures, spread evenly over the SNR groups, copied back from HBM"""
+                idx = np.linspace(0, n_s - 1, n_cpu).astype(np.int64)
+                sub = np.empty(n_cpu * n_per, np.float32)
+                for k, i in enumerate(idx):
+                    eng.d2h(sub[k * n_per:(k + 1) * n_per], d_x + int(i) * n_per * 4)
+                return sub
+
+            # size the sample for about 10 s of host-core work (bounded by the whole workload)
             n_cpu = min(n_s, max(64, 2 * threads))
-            if h_x is None:
-                h_x = np.zeros(n_cpu * n_per, np.float32)
-                eng.d2h(h_x, d_x)
-            # spread the sample over the SNR groups
-            idx = np.linspace(0, n_s - 1, n_cpu).astype(np.int64)
-            sub = np.concatenate([h_x[i * n_per:(i + 1) * n_per] for i in idx])
+            sub = gather(n_cpu)
             v, crecs, cpl, sec = cpu_leg(orc, tmkphy, sub, n_cpu, n_per, cfg, threads)
+            want = int(min(n_s, max(n_cpu, 10.0 * v * 1e6 / n_per)))
+            if want > n_cpu:
+                n_cpu = want
+                sub = gather(n_cpu)
+                v, crecs, cpl, sec = cpu_leg(orc, tmkphy, sub, n_cpu, n_per, cfg, threads)
             st_sub, _ = make_streams(tmkphy, cfg, n_cpu, n_per)
-            grecs, gpl = eng.decode_batch(sub, st_sub)
-            same = (len(grecs) == len(crecs) and all(np.array_equal(grecs[f], crecs[f]) for f in
-                    ("stream", "status", "preamble_start", "frame_start", "consumed", "len", "crc", "seq", "dst")))
+            grecs, gpl = eng.decode_batch(sub, st_sub, rec_cap=len(crecs) + 16, payload_cap=len(cpl) + 16)
+            fields = ("stream", "status", "preamble_start", "frame_start", "consumed", "len", "crc", "type", "seq",
+                      "src", "dst", "hdr_valid")
+
+            def payload_in_record_order(recs, pl):
+                keep = np.isin(recs["status"], (0, 4, 5))
+                return b"".join(pl[int(o):int(o) + int(n)].tobytes() for o, n in
+                                zip(recs["payload_off"][keep], recs["len"][keep]))
+
+            same = (len(grecs) == len(crecs) and all(np.array_equal(grecs[f], crecs[f]) for f in fields)
+                    and payload_in_record_order(grecs, gpl) == payload_in_record_order(crecs, cpl))
             out["cpu_baseline"] = {"value": v, "unit": "Msamples/s", "cores": threads, "kind": "port",
-                                   "sample": f"{n_cpu} of the {n_s} captures x {n_per} samples, {sec:.1f} s",
+                                   "sample": f"{n_cpu} of the {n_s} captures x {n_per} samples, {sec:.2f} s",
                                    "parity_vs_gpu": "bit-exact" if same else "MISMATCH", "records": int(len(crecs))}
         print(json.dumps(out))
     if dist is not None:

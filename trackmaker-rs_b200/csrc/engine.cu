@@ -51,6 +51,7 @@ struct tmk_engine {
     float stage_ms[4] = {0, 0, 0, 0};
     uint64_t launches = 0;
     uint64_t stats[TMK_STAT_COUNT] = {};
+    uint64_t dbg[8] = {};
 };
 
 namespace {
@@ -403,6 +404,7 @@ int tmk_decode_batch(tmk_engine* e, const float* samples, uint64_t total_samples
     *n_recs = hc.n_recs;
     *payload_len = hc.n_payload;
     for (int i = 0; i < TMK_STAT_COUNT; ++i) e->stats[i] += hc.stats[i];
+    for (int i = 0; i < 8; ++i) e->dbg[i] = hc.dbg[i];
     const bool overflow = hc.n_recs > rec_cap || hc.n_payload > payload_cap;
     if (!overflow && hc.n_recs) {
         tmk_frame_rec* dout = recs;
@@ -530,6 +532,12 @@ int tmk_channel_busy(tmk_engine* e, const float* samples, uint64_t total_samples
 int tmk_stats(tmk_engine* e, uint64_t counters[TMK_STAT_COUNT]) {
     if (!e || !counters) return TMK_E_INVALID;
     for (int i = 0; i < TMK_STAT_COUNT; ++i) counters[i] = e->stats[i];
+    return TMK_OK;
+}
+
+int tmk_debug_counters(tmk_engine* e, uint64_t out[8]) {
+    if (!e || !out) return TMK_E_INVALID;
+    for (int i = 0; i < 8; ++i) out[i] = e->dbg[i];
     return TMK_OK;
 }
 

@@ -60,6 +60,7 @@ struct TmkCounters {
     unsigned int next_stream;  // persistent walk warps pull stream indices from here
     unsigned int pad_;
     unsigned long long stats[TMK_STAT_COUNT];
+    unsigned long long dbg[8];  // walk diagnostics (tmk_debug_counters)
 };
 
 __host__ __device__ inline uint64_t tmk_sfb(int line_code, uint32_t spl, uint64_t nbits) {

@@ -65,6 +65,8 @@ struct Ctx {
     float a_err;
     // stats
     uint32_t n_replays, n_cands, n_det;
+    // diagnostics: [0] process_block calls, [1] re-anchors, [2] replay steps, [3] blk_info groups
+    unsigned long long dbg[4];
 };
 
 // samples the reference has buffered when it examines window w, given the current `avail`
@@ -127,6 +129,57 @@ __device__ float exact_energy(Ctx& c, uint64_t seed, uint64_t w) {
     }
     const float* __restrict__ x = c.x;
     const uint32_t P = c.P;
+    c.dbg[2] += w - pos;
+    // Full groups of kG x 32 steps. The loads of the next group are in flight while the current one
+    // is consumed (the chain is a dependent add/add per step; without the prefetch every 32 steps
+    // paid one exposed HBM round trip).
+    // A batch of 32 steps first runs WITHOUT the clamp `if e < 0 { e = 0 }` (decoder.rs:231-233),
+    // tracking the minimum off the critical path: if no intermediate value was negative the clamp
+    // never fired and the values are the reference's; otherwise the batch is redone literally.
+    // NaN/inf need no special case: they propagate identically with and without the clamp.
+    constexpr int kG = 4;
+    if (pos + 32 * kG <= w) {
+        float lv[kG], en[kG];
+#pragma unroll
+        for (int g = 0; g < kG; ++g) {
+            lv[g] = x[pos + g * 32 + c.lane];
+            en[g] = x[pos + P + g * 32 + c.lane];
+        }
+        for (;;) {
+            const bool more = pos + 2 * 32 * kG <= w;
+            float nlv[kG], nen[kG];
+#pragma unroll
+            for (int g = 0; g < kG; ++g) {
+                nlv[g] = more ? x[pos + 32 * kG + g * 32 + c.lane] : 0.f;
+                nen[g] = more ? x[pos + 32 * kG + P + g * 32 + c.lane] : 0.f;
+            }
+#pragma unroll
+            for (int g = 0; g < kG; ++g) {
+                const float a = ex_mul(lv[g], lv[g]), b = ex_mul(en[g], en[g]);
+                const float e0 = e;
+                float mn = e;
+#pragma unroll
+                for (int j = 0; j < 32; ++j) {
+                    e = ex_add(ex_sub(e, __shfl_sync(kFull, a, j)), __shfl_sync(kFull, b, j));
+                    mn = fminf(mn, e);
+                }
+                if (!(mn >= 0.0f)) {  // a clamp fired (or e0 was NaN): literal form
+                    e = e0;
+                    for (int j = 0; j < 32; ++j) {
+                        e = ex_add(ex_sub(e, __shfl_sync(kFull, a, j)), __shfl_sync(kFull, b, j));
+                        e = e < 0.0f ? 0.0f : e;
+                    }
+                }
+            }
+            pos += 32 * kG;
+            if (!more) break;
+#pragma unroll
+            for (int g = 0; g < kG; ++g) {
+                lv[g] = nlv[g];
+                en[g] = nen[g];
+            }
+        }
+    }
     while (pos < w) {
         const uint64_t left = w - pos;
         const uint32_t n = left < 32 ? uint32_t(left) : 32u;
@@ -137,18 +190,9 @@ __device__ float exact_energy(Ctx& c, uint64_t seed, uint64_t w) {
         }
         lv = ex_mul(lv, lv);
         en = ex_mul(en, en);
-        // `if e < 0 { e = 0 }` equals max(e, 0) unless e is NaN (sign of zero never matters: the
-        // energy gate keeps zeros away from sqrt); NaN / inf batches take the literal form
-        const bool finite = __all_sync(kFull, fabsf(lv) <= 3.0e38f && fabsf(en) <= 3.0e38f) && fabsf(e) <= 3.0e38f;
-        if (n == 32 && finite) {
-#pragma unroll
-            for (int j = 0; j < 32; ++j)
-                e = fmaxf(ex_add(ex_sub(e, __shfl_sync(kFull, lv, j)), __shfl_sync(kFull, en, j)), 0.0f);
-        } else {
-            for (uint32_t j = 0; j < n; ++j) {
-                e = ex_add(ex_sub(e, __shfl_sync(kFull, lv, j)), __shfl_sync(kFull, en, j));
-                e = e < 0.0f ? 0.0f : e;
-            }
+        for (uint32_t j = 0; j < n; ++j) {
+            e = ex_add(ex_sub(e, __shfl_sync(kFull, lv, j)), __shfl_sync(kFull, en, j));
+            e = e < 0.0f ? 0.0f : e;
         }
         pos += n;
     }
@@ -241,6 +285,7 @@ __device__ bool process_block(Ctx& c, uint64_t bb, uint64_t q, uint64_t avail, f
     const int lane = c.lane;
     const uint32_t P = c.P;
     const uint64_t wb0 = bb * TMK_BLK;
+    c.dbg[0]++;
     const float* __restrict__ x = c.x;
     const float silent = 0.5f * c.thr * c.thr * 1e-6f;
     // neighbourhood maximum for the scan kernel's own approximation error
@@ -249,25 +294,63 @@ __device__ bool process_block(Ctx& c, uint64_t bb, uint64_t q, uint64_t avail, f
     if (bb + 1 < c.nblk) nb = max_nan(nb, c.blk_info[bb + 1].y);
     const float dscan = 128.f * kU * nb;
 
+    // the block's candidate words: lane r holds word r (one load round instead of 15)
+    const uint32_t myword = lane < TMK_BLK_WORDS ? c.cand_bits[bb * TMK_BLK_WORDS + lane] : 0u;
     const bool fast = P <= 255;
     if (fast) {
-        // prefix sums of the rounded squares in double: E_c(w) = Q[w+P] - Q[w]
+        // prefix sums of the rounded squares in double: E_c(w) = Q[w+P] - Q[w].
+        // Every lane owns K consecutive samples, fetched as float4s that are all in flight together
+        // (one HBM round trip for the block), summed serially per lane, then one warp scan of the
+        // 32 lane totals.
         uint64_t ns64 = c.N - wb0;
         const uint32_t ns = ns64 < uint64_t(TMK_BLK + P - 1) ? uint32_t(ns64) : TMK_BLK + P - 1;
-        double carry = 0.0;
-        if (lane == 0) c.sc->Q[0] = 0.0;
-        for (uint32_t base = 0; base < ns; base += 32) {
-            uint32_t i = base + lane;
-            float xv = i < ns ? x[wb0 + i] : 0.f;
-            double v = double(ex_mul(xv, xv));
-            v = warp_incl_scan_add(v, lane);
-            if (i < ns) c.sc->Q[i + 1] = carry + v;
-            carry += __shfl_sync(kFull, v, 31);
+        constexpr int kMaxK4 = (TMK_BLK + 255 + 127) / 128;  // float4s per lane, 6
+        const uint32_t K4 = (ns + 127) / 128;
+        const uint32_t i0 = uint32_t(lane) * K4 * 4;
+        const float* __restrict__ xb = x + wb0 + i0;
+        float4 v[kMaxK4];
+#pragma unroll
+        for (int k = 0; k < kMaxK4; ++k) {
+            v[k] = make_float4(0.f, 0.f, 0.f, 0.f);
+            if (uint32_t(k) < K4) {
+                const uint32_t i = i0 + 4 * k;
+                if (i + 4 <= ns) {
+                    v[k] = *reinterpret_cast<const float4*>(xb + 4 * k);
+                } else {
+                    if (i + 0 < ns) v[k].x = xb[4 * k + 0];
+                    if (i + 1 < ns) v[k].y = xb[4 * k + 1];
+                    if (i + 2 < ns) v[k].z = xb[4 * k + 2];
+                }
+            }
+        }
+        double tot = 0.0;
+#pragma unroll
+        for (int k = 0; k < kMaxK4; ++k) {
+            tot += double(ex_mul(v[k].x, v[k].x));
+            tot += double(ex_mul(v[k].y, v[k].y));
+            tot += double(ex_mul(v[k].z, v[k].z));
+            tot += double(ex_mul(v[k].w, v[k].w));
+        }
+        double run = warp_incl_scan_add(tot, lane) - tot;  // exclusive
+        double* Q = c.sc->Q;
+        if (lane == 0) Q[0] = 0.0;
+#pragma unroll
+        for (int k = 0; k < kMaxK4; ++k) {
+            if (uint32_t(k) < K4) {
+                const uint32_t i = i0 + 4 * k;
+                run += double(ex_mul(v[k].x, v[k].x));
+                if (i + 0 < ns) Q[i + 1] = run;
+                run += double(ex_mul(v[k].y, v[k].y));
+                if (i + 1 < ns) Q[i + 2] = run;
+                run += double(ex_mul(v[k].z, v[k].z));
+                if (i + 2 < ns) Q[i + 3] = run;
+                run += double(ex_mul(v[k].w, v[k].w));
+                if (i + 3 < ns) Q[i + 4] = run;
+            }
         }
         __syncwarp();
     }
     float pmcarry = prevmax * 1.001f;  // block maxima come from the approximate scan
-    const uint32_t* words = c.cand_bits + bb * TMK_BLK_WORDS;
     for (uint32_t r = 0; r < TMK_BLK_WORDS; ++r) {
         const uint32_t wl = r * 32 + lane;
         const uint64_t w = wb0 + wl;
@@ -295,7 +378,7 @@ __device__ bool process_block(Ctx& c, uint64_t bb, uint64_t q, uint64_t avail, f
             delta = drift_bound(P, same ? w - c.a_w : w - seed, same ? c.a_err : 0.f, pm) + 2.5f * kU * Ec;
             tight = (delta + dscan) <= kTight * Ec;
         }
-        const bool bit = (words[r] >> lane) & 1u;
+        const bool bit = (__shfl_sync(kFull, myword, int(r)) >> lane) & 1u;
         const bool possible = Ec >= silent || !(Ec == Ec);
         const bool eval = valid && possible && (bit || !tight);
         uint32_t em = __ballot_sync(kFull, eval);
@@ -347,11 +430,14 @@ __device__ bool search(Ctx& c, uint64_t q, uint64_t avail, Detection* det) {
     c.a_w = q;
     c.a_err = 0.f;
     float runmax = 0.f;  // bound on the window energies in (a_w, first window of the group)
-    // the block that contains q is partial: its summary also covers windows before q
+    // the block that contains q is partial: its summary also covers windows before q (the frame that was
+    // just consumed, whose energy must not loosen the drift bounds of the gap behind it), so it is
+    // always examined window by window
     uint64_t b0 = q / TMK_BLK;
     if (process_block(c, b0, q, avail, 0.f, det, &runmax)) return true;
     ++b0;
     while (b0 < c.nblk) {
+        c.dbg[3]++;
         const uint64_t bb = b0 + lane;
         const bool valid = bb < c.nblk;
         float4 info = make_float4(0.f, 0.f, 0.f, 0.f);
@@ -362,7 +448,7 @@ __device__ bool search(Ctx& c, uint64_t q, uint64_t avail, Detection* det) {
         }
         // neighbourhood maximum (blocks bb-1 .. bb+1) for the scan kernel's own approximation error
         float nb = max_nan(info.y, max_nan(__shfl_up_sync(kFull, info.y, 1), __shfl_down_sync(kFull, info.y, 1)));
-        if (valid && lane == 0) nb = max_nan(nb, c.blk_info[bb - 1].y);
+        if (valid && lane == 0 && bb > 0) nb = max_nan(nb, c.blk_info[bb - 1].y);
         if (valid && lane == 31 && bb + 1 < c.nblk) nb = max_nan(nb, c.blk_info[bb + 1].y);
         const float incl = warp_incl_scan_maxnan(info.y, lane);
         const float up = __shfl_up_sync(kFull, incl, 1);
@@ -403,6 +489,7 @@ __device__ bool search(Ctx& c, uint64_t q, uint64_t avail, Detection* det) {
         const bool one_seed = c.C == 0 || seed_for(c, wf + TMK_BLK - 1 < c.nwin ? wf + TMK_BLK - 1 : c.nwin - 1, q, avail) == sf;
         if (hl && one_seed && kj > 1024) {
             // re-anchor: roll the reference's chain up to this block once and measure its drift
+            c.dbg[1]++;
             const float eref = exact_energy(c, sf, wf);
             const float ec = window_energy(c, wf);
             float err = fabsf(eref - ec) + 1.2f * kU * ec;
@@ -417,8 +504,9 @@ __device__ bool search(Ctx& c, uint64_t q, uint64_t avail, Detection* det) {
         const float pmax = __shfl_sync(kFull, excl, j);
         float pm_blk;
         if (process_block(c, b0 + j, q, avail, pmax, det, &pm_blk)) return true;
-        // continue behind block j; the running maximum now covers it
-        runmax = max_nan(pmax, __shfl_sync(kFull, info.y, j));
+        // continue behind block j; the running maximum now covers it (pm_blk: exact energies of the
+        // block's windows >= q on top of pmax)
+        runmax = pm_blk;
         b0 += j + 1;
     }
     return false;
@@ -436,13 +524,24 @@ __device__ uint64_t refine(const Ctx& c, const Detection& d) {
     if (hi > d.avail - sl) hi = d.avail - sl;
     float best = -1.0f;
     uint64_t best_off = expect;
+    // stage the samples [lo, hi + sl) in shared memory with one coalesced round of loads (the prefix-sum
+    // buffer of process_block is dead here); every lane then walks its own offset out of shared memory
+    const uint64_t span = hi >= lo ? hi + sl - lo : 0;
+    float* xs = reinterpret_cast<float*>(c.sc->Q);
+    const bool staged = span <= 2 * kQBuf;
+    if (staged) {
+        __syncwarp();
+        for (uint32_t i = c.lane; i < uint32_t(span); i += 32) xs[i] = x[lo + i];
+        __syncwarp();
+    }
     for (uint64_t base = lo; base <= hi; base += 32) {
         const uint64_t j = base + c.lane;
         float corr = -2.0f;
         if (j <= hi) {
             float dot = 0.0f, we = 0.0f;
+            const float* wp = staged ? xs + (j - lo) : x + j;
             for (uint32_t t = 0; t < sl; ++t) {
-                const float w = x[j + t];
+                const float w = wp[t];
                 dot = ex_add(dot, ex_mul(w, c.sc->pre[P - sl + t]));
                 we = ex_add(we, ex_mul(w, w));
             }
@@ -661,6 +760,7 @@ walk_kernel(const float* __restrict__ samples, const TmkStreamDev* __restrict__ 
     c.a_seed = c.a_w = 0;
     c.a_err = 0.f;
     c.n_replays = c.n_cands = c.n_det = 0;
+    c.dbg[0] = c.dbg[1] = c.dbg[2] = c.dbg[3] = 0;
     __syncwarp();
     for (uint32_t k = lane_id; k < c.P; k += 32) c.sc->pre[k] = c.pat->levels[k / c.pat->spl];
     __syncwarp();
@@ -676,6 +776,11 @@ walk_kernel(const float* __restrict__ samples, const TmkStreamDev* __restrict__ 
     while (search(c, q, avail, &d)) {
         c.n_det++;
         avail = d.avail;
+        {   // pull the head of the frame towards L2 while the refinement and the header decode run
+            const uint64_t f0 = d.c + c.P;
+            for (uint64_t i = uint64_t(lane_id) * 32; i < 2560 && f0 + i < c.N; i += 1024)
+                asm volatile("prefetch.global.L2 [%0];" ::"l"(c.x + f0 + i));
+        }
         const uint64_t fs = refine(c, d);
         // ---- decode_frame (decoder.rs:242-356); `avail` grows by one chunk per call
         bool truncated = false;
@@ -749,6 +854,7 @@ walk_kernel(const float* __restrict__ samples, const TmkStreamDev* __restrict__ 
         atomicAdd(&counters->stats[TMK_STAT_NOT_FOR_US], (unsigned long long)n_nfu);
         atomicAdd(&counters->stats[TMK_STAT_EXACT_REPLAYS], (unsigned long long)c.n_replays);
         atomicAdd(&counters->stats[TMK_STAT_CANDIDATES], (unsigned long long)c.n_cands);
+        for (int i = 0; i < 4; ++i) atomicAdd(&counters->dbg[i], c.dbg[i]);
     }
     }  // next stream
 }

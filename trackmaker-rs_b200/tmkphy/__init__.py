@@ -169,6 +169,12 @@ class Engine:
     def stats_reset(self):
         self._check(self._lib.tmk_stats_reset(self._h))
 
+    def debug_counters(self):
+        """walk diagnostics of the last decode_batch call (tmk_debug_counters)"""
+        c = (C.c_uint64 * 8)()
+        self._check(self._lib.tmk_debug_counters(self._h, c))
+        return dict(zip(("blocks_examined", "reanchors", "replay_steps", "summary_groups"), [int(v) for v in c[:4]]))
+
     # ---- the path
     def modulate(self, cfg, frames, gap=INTER_FRAME_GAP_SAMPLES, out_device_ptr=None):
         """PhyEncoder::encode_frames. frames: list of Frame. Returns float32 samples (host)."""

@@ -80,6 +80,7 @@ SYMBOLS = {
     "tmk_channel_busy": (C.c_int, [_vp, _vp, _u64, _vp, _u32, _vp]),
     "tmk_stats": (C.c_int, [_vp, _pu64]),
     "tmk_stats_reset": (C.c_int, [_vp]),
+    "tmk_debug_counters": (C.c_int, [_vp, _pu64]),
     "tmk_device_alloc": (C.c_int, [_vp, _u64, C.POINTER(_vp)]),
     "tmk_device_free": (C.c_int, [_vp, _vp]),
     "tmk_host_alloc_pinned": (C.c_int, [_vp, _u64, C.POINTER(_vp)]),
