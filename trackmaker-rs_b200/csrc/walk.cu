@@ -34,10 +34,10 @@ constexpr float kTight = 0.09f;
 
 __device__ uint8_t g_crc_pow[kMaxFrameBytesCap + 8];    // x^(8k) mod 0x107, k = 0..
 
-struct WarpScratch {
+struct alignas(16) WarpScratch {
+    alignas(16) uint8_t bytes[kByteBuf];  // decoded frame bytes; staging of the replay during a search
     double Q[kQBuf + 1];
-    float pre[TMK_MAX_P];  // preamble samples (levels expanded by spl)
-    uint8_t bytes[kByteBuf];
+    int8_t pre[TMK_MAX_P];  // preamble samples (+1/-1 levels expanded by spl; x * +-1.0f is exact)
 };
 
 struct Ctx {
@@ -70,40 +70,48 @@ struct Ctx {
 };
 
 // samples the reference has buffered when it examines window w, given the current `avail`
+__device__ __noinline__ uint64_t avail_for_slow(const uint64_t P, const uint64_t C, const uint64_t N, uint64_t w) {
+    uint64_t t = ((w + P + C - 1) / C) * C;  // C > 0 here (one shot has avail == N)
+    return t < N ? t : N;
+}
+
 __device__ __forceinline__ uint64_t avail_for(const Ctx& c, uint64_t w, uint64_t avail) {
     if (w + c.P <= avail) return avail;
-    uint64_t t = ((w + c.P + c.C - 1) / c.C) * c.C;  // C > 0 here (one shot has avail == N)
-    return t < c.N ? t : c.N;
+    return avail_for_slow(c.P, c.C, c.N, w);
 }
 
 // position at which the search that examines window w was (re)entered = where its rolling
 // energy was seeded (decoder.rs:133-136)
+__device__ __noinline__ uint64_t seed_for_slow(const uint64_t P, const uint64_t C, const uint64_t N, uint64_t w, uint64_t q) {
+    uint64_t aw = avail_for_slow(P, C, N, w);
+    uint64_t prev = ((aw - 1) / C) * C;  // avail of the previous process_samples call
+    if (prev + 1 < P) return q;
+    uint64_t s = prev + 1 - P;
+    return s > q ? s : q;
+}
+
 __device__ __forceinline__ uint64_t seed_for(const Ctx& c, uint64_t w, uint64_t q, uint64_t avail) {
     if (w + c.P <= avail) return q;
-    uint64_t aw = avail_for(c, w, avail);
-    uint64_t prev = ((aw - 1) / c.C) * c.C;  // avail of the previous process_samples call
-    if (prev + 1 < uint64_t(c.P)) return q;
-    uint64_t s = prev + 1 - c.P;
-    return s > q ? s : q;
+    return seed_for_slow(c.P, c.C, c.N, w, q);
 }
 
 // compute_dot_product_avx (decoder.rs:381-417): 8 lanes of mul-then-add, lane l + lane l+4,
 // the 4 partials summed left to right from 0, then the len % 8 tail. Runs per thread.
-__device__ float dot_avx_order(const Ctx& c, const float* __restrict__ w) {
+__device__ __noinline__ float dot_avx_order(const Ctx& c, const float* __restrict__ w) {
     const uint32_t P = c.P;
-    const float* __restrict__ pre = c.sc->pre;
+    const int8_t* __restrict__ pre = c.sc->pre;
     float a[8];
 #pragma unroll
     for (int l = 0; l < 8; ++l) a[l] = 0.0f;
     uint32_t i = 0;
     for (; i + 8 <= P; i += 8) {
 #pragma unroll
-        for (int l = 0; l < 8; ++l) a[l] = ex_add(a[l], ex_mul(w[i + l], pre[i + l]));
+        for (int l = 0; l < 8; ++l) a[l] = ex_add(a[l], ex_mul(w[i + l], float(pre[i + l])));
     }
     float s = 0.0f;
 #pragma unroll
     for (int l = 0; l < 4; ++l) s = ex_add(s, ex_add(a[l], a[l + 4]));
-    for (; i < P; ++i) s = ex_add(s, ex_mul(w[i], pre[i]));
+    for (; i < P; ++i) s = ex_add(s, ex_mul(w[i], float(pre[i])));
     return s;
 }
 
@@ -117,7 +125,7 @@ __device__ float seq_energy(const float* __restrict__ w, uint32_t n) {
 // Exact rolling window energy of window `w` for a search seeded at `seed` (decoder.rs:133-136,
 // 224-233). Sequential by construction: the squares are formed lane-parallel, 32 steps per
 // coalesced load, the dependent (sub, add, clamp) chain runs redundantly on every lane.
-__device__ float exact_energy(Ctx& c, uint64_t seed, uint64_t w) {
+__device__ __noinline__ float exact_energy(Ctx& c, uint64_t seed, uint64_t w) {
     float e;
     uint64_t pos;
     if (c.rvalid && c.rseed == seed && c.rpos <= w) {
@@ -132,13 +140,17 @@ __device__ float exact_energy(Ctx& c, uint64_t seed, uint64_t w) {
     c.dbg[2] += w - pos;
     // Full groups of kG x 32 steps. The loads of the next group are in flight while the current one
     // is consumed (the chain is a dependent add/add per step; without the prefetch every 32 steps
-    // paid one exposed HBM round trip).
+    // paid one exposed HBM round trip). The squares of a group are staged in shared memory (the
+    // byte buffer of the frame decoder is idle during a search) and read back as broadcast float4s.
     // A batch of 32 steps first runs WITHOUT the clamp `if e < 0 { e = 0 }` (decoder.rs:231-233),
     // tracking the minimum off the critical path: if no intermediate value was negative the clamp
     // never fired and the values are the reference's; otherwise the batch is redone literally.
     // NaN/inf need no special case: they propagate identically with and without the clamp.
     constexpr int kG = 4;
+    static_assert(kByteBuf >= 2 * 32 * kG * 4, "staging buffer of the replay");
     if (pos + 32 * kG <= w) {
+        float* sa = reinterpret_cast<float*>(c.sc->bytes);  // a[128] | b[128]
+        float* sb = sa + 32 * kG;
         float lv[kG], en[kG];
 #pragma unroll
         for (int g = 0; g < kG; ++g) {
@@ -147,38 +159,47 @@ __device__ float exact_energy(Ctx& c, uint64_t seed, uint64_t w) {
         }
         for (;;) {
             const bool more = pos + 2 * 32 * kG <= w;
-            float nlv[kG], nen[kG];
+            __syncwarp();
 #pragma unroll
             for (int g = 0; g < kG; ++g) {
-                nlv[g] = more ? x[pos + 32 * kG + g * 32 + c.lane] : 0.f;
-                nen[g] = more ? x[pos + 32 * kG + P + g * 32 + c.lane] : 0.f;
+                sa[g * 32 + c.lane] = ex_mul(lv[g], lv[g]);
+                sb[g * 32 + c.lane] = ex_mul(en[g], en[g]);
             }
+            __syncwarp();
+            if (more) {
 #pragma unroll
+                for (int g = 0; g < kG; ++g) {
+                    lv[g] = x[pos + 32 * kG + g * 32 + c.lane];
+                    en[g] = x[pos + 32 * kG + P + g * 32 + c.lane];
+                }
+            }
+#pragma unroll 1
             for (int g = 0; g < kG; ++g) {
-                const float a = ex_mul(lv[g], lv[g]), b = ex_mul(en[g], en[g]);
+                const float4* a4 = reinterpret_cast<const float4*>(sa + g * 32);
+                const float4* b4 = reinterpret_cast<const float4*>(sb + g * 32);
                 const float e0 = e;
                 float mn = e;
 #pragma unroll
-                for (int j = 0; j < 32; ++j) {
-                    e = ex_add(ex_sub(e, __shfl_sync(kFull, a, j)), __shfl_sync(kFull, b, j));
-                    mn = fminf(mn, e);
+                for (int j = 0; j < 8; ++j) {
+                    const float4 a = a4[j], b = b4[j];
+                    e = ex_add(ex_sub(e, a.x), b.x); mn = fminf(mn, e);
+                    e = ex_add(ex_sub(e, a.y), b.y); mn = fminf(mn, e);
+                    e = ex_add(ex_sub(e, a.z), b.z); mn = fminf(mn, e);
+                    e = ex_add(ex_sub(e, a.w), b.w); mn = fminf(mn, e);
                 }
                 if (!(mn >= 0.0f)) {  // a clamp fired (or e0 was NaN): literal form
                     e = e0;
+#pragma unroll 1
                     for (int j = 0; j < 32; ++j) {
-                        e = ex_add(ex_sub(e, __shfl_sync(kFull, a, j)), __shfl_sync(kFull, b, j));
+                        e = ex_add(ex_sub(e, sa[g * 32 + j]), sb[g * 32 + j]);
                         e = e < 0.0f ? 0.0f : e;
                     }
                 }
             }
             pos += 32 * kG;
             if (!more) break;
-#pragma unroll
-            for (int g = 0; g < kG; ++g) {
-                lv[g] = nlv[g];
-                en[g] = nen[g];
-            }
         }
+        __syncwarp();
     }
     while (pos < w) {
         const uint64_t left = w - pos;
@@ -280,7 +301,7 @@ __device__ bool exact_window(Ctx& c, uint64_t w, uint64_t seed, float D, float* 
 // Examine the windows of block `bb` that are >= q, in order. `prevmax` bounds the window energies
 // of the chain between the anchor and this block; *pm_out receives the bound including this block.
 // Returns true with *det filled on a detection.
-__device__ bool process_block(Ctx& c, uint64_t bb, uint64_t q, uint64_t avail, float prevmax, Detection* det,
+__device__ __noinline__ bool process_block(Ctx& c, uint64_t bb, uint64_t q, uint64_t avail, float prevmax, Detection* det,
                               float* pm_out) {
     const int lane = c.lane;
     const uint32_t P = c.P;
@@ -351,6 +372,7 @@ __device__ bool process_block(Ctx& c, uint64_t bb, uint64_t q, uint64_t avail, f
         __syncwarp();
     }
     float pmcarry = prevmax * 1.001f;  // block maxima come from the approximate scan
+#pragma unroll 1
     for (uint32_t r = 0; r < TMK_BLK_WORDS; ++r) {
         const uint32_t wl = r * 32 + lane;
         const uint64_t w = wb0 + wl;
@@ -421,7 +443,7 @@ __device__ bool process_block(Ctx& c, uint64_t bb, uint64_t q, uint64_t avail, f
 }
 
 // search_for_preamble over all future calls: first window >= q with corr_ref >= thr.
-__device__ bool search(Ctx& c, uint64_t q, uint64_t avail, Detection* det) {
+__device__ __noinline__ bool search(Ctx& c, uint64_t q, uint64_t avail, Detection* det) {
     if (c.nwin == 0 || q >= c.nwin) return false;
     const int lane = c.lane;
     const uint32_t P = c.P;
@@ -513,7 +535,7 @@ __device__ bool search(Ctx& c, uint64_t q, uint64_t avail, Detection* det) {
 }
 
 // ---------------------------------------------------------------- refinement (decoder.rs:157-221)
-__device__ uint64_t refine(const Ctx& c, const Detection& d) {
+__device__ __noinline__ uint64_t refine(const Ctx& c, const Detection& d) {
     const TmkPattern* pat = c.pat;
     const uint32_t P = c.P, sl = pat->sync_len, margin = pat->margin;
     const float* __restrict__ x = c.x;
@@ -542,7 +564,7 @@ __device__ uint64_t refine(const Ctx& c, const Detection& d) {
             const float* wp = staged ? xs + (j - lo) : x + j;
             for (uint32_t t = 0; t < sl; ++t) {
                 const float w = wp[t];
-                dot = ex_add(dot, ex_mul(w, c.sc->pre[P - sl + t]));
+                dot = ex_add(dot, ex_mul(w, float(c.sc->pre[P - sl + t])));
                 we = ex_add(we, ex_mul(w, w));
             }
             corr = (we > 1e-6f && pat->sync_energy > 1e-6f) ? ex_div(dot, ex_mul(ex_sqrt(we), pat->sync_energy)) : 0.0f;
@@ -583,77 +605,92 @@ __device__ __forceinline__ float level_mean(const float* __restrict__ s, uint32_
 // LineCode::decode over the samples of `total_bits` bits starting at fs. Writes MSB-first packed
 // bytes (crc.rs:63-75) to c.sc->bytes and returns the number of bits decoded (4B5B stops at the
 // first invalid symbol, line_coding.rs:281-286).
-__device__ uint32_t line_decode(const Ctx& c, uint64_t fs, uint32_t total_bits) {
+__device__ __noinline__ uint32_t line_decode(const Ctx& c, uint64_t fs, uint32_t total_bits) {
     const float* __restrict__ s = c.x + fs;
     const uint32_t spl = c.pat->spl;
     const int lane = c.lane;
     uint8_t* bytes = c.sc->bytes;
-    constexpr int U = 8;  // iterations whose loads are issued together (the walk is latency bound)
-    if (c.pat->line_code == TMK_LINE_MANCHESTER) {
-        for (uint32_t b0 = 0; b0 < total_bits; b0 += 32 * U) {
-            float a[U], b[U];
-#pragma unroll
-            for (int u = 0; u < U; ++u) {
-                const uint32_t bi = b0 + u * 32 + lane;
-                a[u] = b[u] = 0.f;
-                if (bi < total_bits) {
-                    a[u] = level_mean(s + uint64_t(bi) * 2 * spl, spl);
-                    b[u] = level_mean(s + uint64_t(bi) * 2 * spl + spl, spl);
-                }
-            }
-#pragma unroll
-            for (int u = 0; u < U; ++u) {
-                const uint32_t bb = b0 + u * 32;
-                if (bb >= total_bits) break;
-                const bool bit = (bb + lane < total_bits) && !(a[u] > b[u]);  // first > second -> 0, else 1 (tie -> 1)
-                const uint32_t rev = __brev(__ballot_sync(kFull, bit));
-                if (lane < 4 && bb + lane * 8 < total_bits) bytes[bb / 8 + lane] = uint8_t(rev >> (24 - 8 * lane));
-            }
-        }
-        __syncwarp();
-        return total_bits;
-    }
-    const uint32_t nlev = (total_bits / 4) * 5;
+    // level means are staged in shared memory (the prefix-sum buffer is idle during a decode):
+    // pass 1 fills a chunk with independent loads in flight, pass 2 decides out of shared memory
+    float* lev = reinterpret_cast<float*>(c.sc->Q);
+    constexpr uint32_t kChunk = 1280;  // levels per chunk: 256 4B5B symbols = 128 bytes, 640 Manchester bits = 80 bytes
+    static_assert(kChunk <= 2 * kQBuf && kChunk % 160 == 0 && kChunk % 64 == 0, "level chunk");
+    const bool man = c.pat->line_code == TMK_LINE_MANCHESTER;
+    const uint32_t nlev = man ? total_bits * 2 : (total_bits / 4) * 5;
     float last = 1.0f;  // prev_level_avg restarts at 1.0 on every decode call (line_coding.rs:251)
     uint32_t nb = 0;
-    bool stop = false;
-    for (uint32_t g0 = 0; g0 < nlev && !stop; g0 += 30 * U) {
-        float curs[U];
-#pragma unroll
-        for (int u = 0; u < U; ++u) {
-            const uint32_t li = g0 + u * 30 + lane;
-            curs[u] = (lane < 30 && li < nlev) ? level_mean(s + uint64_t(li) * spl, spl) : 0.0f;
+    for (uint32_t c0 = 0; c0 < nlev; c0 += kChunk) {
+        const uint32_t nl = nlev - c0 < kChunk ? nlev - c0 : kChunk;
+        __syncwarp();
+        if (spl == 3) {
+#pragma unroll 4
+            for (uint32_t i = lane; i < nl; i += 32) {
+                const float* p = s + uint64_t(c0 + i) * 3;
+                lev[i] = ex_div(ex_add(ex_add(ex_add(0.0f, p[0]), p[1]), p[2]), 3.0f);
+            }
+        } else {
+#pragma unroll 2
+            for (uint32_t i = lane; i < nl; i += 32) lev[i] = level_mean(s + uint64_t(c0 + i) * spl, spl);
         }
+        __syncwarp();
+        if (man) {
+            // one lane per bit: first half > second half -> 0, else 1 (tie -> 1)  line_coding.rs:104-119
+            const uint32_t nbit = nl / 2;
+#pragma unroll 1
+            for (uint32_t b0 = 0; b0 < nbit; b0 += 32) {
+                const uint32_t bi = b0 + lane;
+                bool bit = false;
+                if (bi < nbit) {
+                    const float2 ab = *reinterpret_cast<const float2*>(lev + 2 * bi);
+                    bit = !(ab.x > ab.y);
+                }
+                const uint32_t rev = __brev(__ballot_sync(kFull, bit));
+                if (lane < 4 && b0 + lane * 8 < nbit) bytes[(nb >> 3) + lane] = uint8_t(rev >> (24 - 8 * lane));
+                nb += nbit - b0 < 32 ? nbit - b0 : 32;
+            }
+            continue;
+        }
+        // 4B5B + NRZI: one lane per 5-level symbol, 32 symbols (16 bytes) per step
+        const uint32_t nsym = nl / 5;
+        bool stop = false;
+#pragma unroll 1
+        for (uint32_t s0 = 0; s0 < nsym && !stop; s0 += 32) {
+            const uint32_t si = s0 + lane;
+            const bool active = si < nsym;
+            float v[5];
 #pragma unroll
-        for (int u = 0; u < U; ++u) {
-            const uint32_t l0 = g0 + u * 30;
-            if (l0 >= nlev || stop) break;
-            const uint32_t li = l0 + lane;
-            const bool active = lane < 30 && li < nlev;
-            const float cur = curs[u];
-            const bool valid = active && fabsf(cur) > 1e-6f;
-            const uint32_t vm = __ballot_sync(kFull, valid);
-            const uint32_t below = vm & ((1u << lane) - 1u);
-            const int src = below ? 31 - __clz(below) : 0;
-            const float pv = __shfl_sync(kFull, cur, src);
-            const float lastv = below ? pv : last;
-            const bool bit = active && ex_mul(lastv, cur) < 0.0f;
-            const uint32_t bm = __ballot_sync(kFull, bit);
-            if (vm) last = __shfl_sync(kFull, cur, 31 - __clz(vm));
-            uint32_t nsy = (nlev - l0) / 5;
-            if (nsy > 6) nsy = 6;
-            // lane k decodes symbol k (levels 5k..5k+4, first level = MSB); an iteration always
-            // starts on a byte boundary (6 symbols = 3 bytes)
-            const uint32_t sym = __brev((bm >> (5 * (lane < 6 ? lane : 0))) & 31u) >> 27;
+            for (int j = 0; j < 5; ++j) v[j] = active ? lev[5 * si + j] : 0.0f;
+            // the last level of this symbol with |avg| > 1e-6, if any (line_coding.rs:268-270)
+            float mylast = 0.0f;
+            bool have = false;
+#pragma unroll
+            for (int j = 0; j < 5; ++j)
+                if (fabsf(v[j]) > 1e-6f) {
+                    mylast = v[j];
+                    have = true;
+                }
+            const uint32_t hm = __ballot_sync(kFull, have);
+            const uint32_t below = hm & ((1u << lane) - 1u);
+            const float pv = __shfl_sync(kFull, mylast, below ? 31 - __clz(below) : 0);
+            float lastv = below ? pv : last;
+            uint32_t sym = 0;
+#pragma unroll
+            for (int j = 0; j < 5; ++j) {
+                sym = (sym << 1) | (ex_mul(lastv, v[j]) < 0.0f ? 1u : 0u);  // :262-266, first level = MSB
+                if (fabsf(v[j]) > 1e-6f) lastv = v[j];
+            }
+            if (hm) last = __shfl_sync(kFull, mylast, 31 - __clz(hm));
             const int nib = c_dec5[sym];
-            const uint32_t inv = __ballot_sync(kFull, uint32_t(lane) < nsy && nib < 0);
-            const uint32_t nval = inv ? uint32_t(__ffs(inv) - 1) : nsy;
+            const uint32_t nsy = nsym - s0 < 32 ? nsym - s0 : 32;
+            const uint32_t inv = __ballot_sync(kFull, active && nib < 0);
+            const uint32_t nval = inv ? uint32_t(__ffs(inv) - 1) : nsy;  // stop at the first invalid symbol :281-286
             const int lo = __shfl_down_sync(kFull, nib, 1);
-            if (lane < 6 && (lane & 1) == 0 && uint32_t(lane) < nval)
+            if ((lane & 1) == 0 && uint32_t(lane) < nval)
                 bytes[(nb >> 3) + (lane >> 1)] = uint8_t((uint32_t(nib) << 4) | (uint32_t(lane) + 1 < nval ? uint32_t(lo) : 0u));
             nb += 4 * nval;
             if (inv) stop = true;
         }
+        if (stop) break;
     }
     __syncwarp();
     return nb;
@@ -689,7 +726,7 @@ struct Emit {
     uint32_t ord;  // records emitted by this stream so far
 };
 
-__device__ void emit(const Ctx& c, Emit& em, uint32_t status, const Detection& d, uint64_t frame_start,
+__device__ __noinline__ void emit(const Ctx& c, Emit& em, uint32_t status, const Detection& d, uint64_t frame_start,
                      uint32_t consumed, bool have_hdr, const uint8_t* hdr, uint32_t data_len) {
     unsigned long long slot = 0, poff = 0;
     if (c.lane == 0) {
@@ -723,7 +760,7 @@ __device__ void emit(const Ctx& c, Emit& em, uint32_t status, const Detection& d
     em.ord++;
 }
 
-__global__ void __launch_bounds__(kWarpsPerCta * 32, 4)
+__global__ void __launch_bounds__(kWarpsPerCta * 32, 7)
 walk_kernel(const float* __restrict__ samples, const TmkStreamDev* __restrict__ streams, uint32_t n_streams,
             const TmkPattern* __restrict__ patterns, const float4* __restrict__ blk_info,
             const uint32_t* __restrict__ cand_bits, tmk_frame_rec* recs, uint32_t* rec_ord, uint64_t rec_cap,
@@ -762,7 +799,7 @@ walk_kernel(const float* __restrict__ samples, const TmkStreamDev* __restrict__ 
     c.n_replays = c.n_cands = c.n_det = 0;
     c.dbg[0] = c.dbg[1] = c.dbg[2] = c.dbg[3] = 0;
     __syncwarp();
-    for (uint32_t k = lane_id; k < c.P; k += 32) c.sc->pre[k] = c.pat->levels[k / c.pat->spl];
+    for (uint32_t k = lane_id; k < c.P; k += 32) c.sc->pre[k] = int8_t(c.pat->levels[k / c.pat->spl]);
     __syncwarp();
     Emit em{recs, rec_ord, rec_cap, payload, payload_cap, counters, sidx, 0};
     uint32_t n_ok = 0, n_crc = 0, n_hdr = 0, n_nfu = 0;
