@@ -24,19 +24,21 @@
 namespace {
 
 constexpr int kS = 120;      // windows per lane strip
-constexpr int kWarps = 4;    // warps per CTA (each works on its own tiles)
+constexpr int kMaxWarps = 4; // warps per CTA (each works on its own tiles): Shape<LC>::kWarps <= kMaxWarps
 constexpr unsigned kFull = 0xffffffffu;
 
 template <int LC> struct Shape;
 template <> struct Shape<TMK_LINE_4B5B> {
     static constexpr int L = 20, P = 60;
-    static constexpr int kCopy = 180;  // floats copied per lane row (>= kS + P - 1, multiple of 4)
-    static constexpr int kRow = 180;   // row pitch in floats: 720 B = 45 x 16 B
+    static constexpr int kCopy = 184;  // floats copied per lane row (3 x 60 steps read x[0 .. 183]), multiple of 4
+    static constexpr int kRow = 188;   // row pitch in floats: 752 B = 47 x 16 B (odd: conflict-free LDS.128)
+    static constexpr int kWarps = 4;   // 96 KB of rows per CTA, 2 CTAs per SM
 };
 template <> struct Shape<TMK_LINE_MANCHESTER> {
     static constexpr int L = 32, P = 96;
-    static constexpr int kCopy = 216;
-    static constexpr int kRow = 220;   // 880 B = 55 x 16 B
+    static constexpr int kCopy = 232;  // 3 x 76 steps read x[0 .. 231]
+    static constexpr int kRow = 236;   // 944 B = 59 x 16 B
+    static constexpr int kWarps = 3;   // 91 KB of rows per CTA, 2 CTAs per SM
 };
 
 __device__ __forceinline__ uint32_t smem_u32(const void* p) { return uint32_t(__cvta_generic_to_shared(p)); }
@@ -74,28 +76,59 @@ struct LaneOut {
     uint32_t ncand;
 };
 
-// finish window n of the strip: candidate test and block statistics
-template <bool FULL>
-__device__ __forceinline__ void finish_window(int n, float D, float E, float kap, int nvalid, uint32_t* __restrict__ bits,
-                                              uint32_t bit0, LaneOut& o) {
+// static ring index: (i mod R) for i that may be negative
+template <int R> __device__ __forceinline__ constexpr int rix(int i) { return ((i % R) + R) % R; }
+
+// finish window n of the strip (branch free): block statistics and the candidate predicate.
+// `valid` masks the windows that do not belong to the strip (warm-up, past the strip / the stream).
+__device__ __forceinline__ bool finish_window(float D, float E, float kap, bool valid, LaneOut& o) {
     const float dp = fmaxf(D, 0.0f);
-    const float r = dp * dp * rcp_approx(E);  // P * corr^2 (NaN for silence: never a candidate)
-    const bool ok = FULL || n < nvalid;
-    if (FULL) {
-        o.emin = fminf(o.emin, E);
-        o.emax = max_nan(o.emax, E);
-        o.rmax = fmaxf(o.rmax, r);
-    } else if (ok) {
-        o.emin = fminf(o.emin, E);
-        o.emax = max_nan(o.emax, E);
-        o.rmax = fmaxf(o.rmax, r);
-    }
-    if (r > kap && ok) {  // rare
-        const uint32_t b = bit0 + uint32_t(n);
-        atomicOr(bits + (b >> 5), 1u << (b & 31));
-        o.ncand++;
+    const float Ev = valid ? E : __int_as_float(0x7fc00000);  // NaN: ignored by fminf / fmaxf, never a candidate
+    const float r = dp * dp * rcp_approx(Ev);                  // P * corr^2 (NaN for silence: never a candidate)
+    o.emin = fminf(o.emin, Ev);
+    o.emax = max_nan(o.emax, valid ? E : 0.0f);                // a NaN SAMPLE must stay visible in max E
+    o.rmax = fmaxf(o.rmax, r);
+    return r > kap;
+}
+
+// candidate bits of one loop iteration (U steps): rare, so the bits are flushed with atomics
+template <int U, int LAT>
+__device__ __forceinline__ void flush_cands(uint64_t cm0, uint64_t cm1, int k, int nvalid, uint32_t* __restrict__ bits,
+                                            uint32_t bit0, LaneOut& o) {
+    // bit j of (cm1:cm0) is step j of iteration k, i.e. window n = U * k + j - LAT
+#pragma unroll 1
+    for (int h = 0; h < 2; ++h) {
+        uint64_t cm = h ? cm1 : cm0;
+        while (cm) {
+            const int j = __ffsll((long long)cm) - 1 + 64 * h;
+            cm &= cm - 1;
+            const int n = U * k + j - LAT;
+            if (n >= 0 && n < nvalid) {
+                const uint32_t b = bit0 + uint32_t(n);
+                atomicOr(bits + (b >> 5), 1u << (b & 31));
+                o.ncand++;
+            }
+        }
     }
 }
+
+// Which loop iterations k (of NIT) make step j finish a window of the strip: n = U * k + j - LAT in [0, hi).
+// j is a compile-time constant after unrolling, so this folds to an OR of at most NIT iteration flags.
+template <int U, int LAT, int NIT>
+__device__ __forceinline__ bool step_valid(int j, int hi, const bool (&is)[NIT]) {
+    bool v = false;
+#pragma unroll
+    for (int kk = 0; kk < NIT; ++kk) {
+        const int n = U * kk + j - LAT;
+        if (n >= 0 && n < hi) v = v || is[kk];
+    }
+    return v;
+}
+
+// The strips are ROLLED loops of NIT iterations x U steps: the unrolled body is the same ~3 K instructions
+// for every warp and stays resident in the instruction cache (the fully unrolled 177 / 213-step form was
+// 148 KB of straight-line code streamed by every warp). All ring indices are static because the ring sizes
+// divide U; warm-up steps run the same code on zeroed rings and are masked when a window is finished.
 
 // ---------------------------------------------------------------- 4B5B: levels --++-++--++--+-++-++
 // D(n) = -d[n] - y[n+12] + p2[n+15] - d[n+21] - p2[n+33] + y[n+39] - y[n+42] + p2[n+45] - y[n+51] + p2[n+54]
@@ -103,9 +136,15 @@ __device__ __forceinline__ void finish_window(int n, float D, float E, float kap
 template <bool FULL>
 __device__ __forceinline__ void strip_4b5b(const float* __restrict__ row, float kap, int nvalid,
                                            uint32_t* __restrict__ bits, uint32_t bit0, LaneOut& o) {
-    constexpr int P = 60;
-    constexpr int M = kS + P - 3;  // level sums needed: y[0 .. M-1]
-    float acc[64], yb[4], p2b[8], db[4], xr[8], xo[4];
+    constexpr int U = 60, LAT = 57, NIT = 3;  // steps per iteration, steps from a window's start to its finish
+    static_assert(U * NIT >= kS + LAT && U % 12 == 0 && U <= 64, "strip steps");
+    float acc[60], yb[4], p2b[12], db[4], xr[12], xo[4];
+#pragma unroll
+    for (int i = 0; i < 60; ++i) acc[i] = 0.f;
+#pragma unroll
+    for (int i = 0; i < 12; ++i) p2b[i] = xr[i] = 0.f;
+#pragma unroll
+    for (int i = 0; i < 4; ++i) yb[i] = db[i] = xo[i] = 0.f;
     float e = 0.0f;
     {
         const float4 v = *reinterpret_cast<const float4*>(row);
@@ -113,44 +152,47 @@ __device__ __forceinline__ void strip_4b5b(const float* __restrict__ row, float 
         e = fmaf(v.x, v.x, e);
         e = fmaf(v.y, v.y, e);
     }
+#pragma unroll 1
+    for (int k = 0; k < NIT; ++k) {
+        const float* __restrict__ rk = row + U * k;
+        const bool is[NIT] = {k == 0, k == 1, k == 2};
+        uint64_t cm = 0;
 #pragma unroll
-    for (int m = 0; m < M; ++m) {
-        if (((m + 2) & 3) == 0) {  // x[m+2 .. m+5] become needed
-            const float4 v = *reinterpret_cast<const float4*>(row + m + 2);
-            xr[(m + 2) & 7] = v.x; xr[(m + 3) & 7] = v.y; xr[(m + 4) & 7] = v.z; xr[(m + 5) & 7] = v.w;
-        }
-        const float x2 = xr[(m + 2) & 7];
-        const float y = (xr[m & 7] + xr[(m + 1) & 7]) + x2;
-        e = fmaf(x2, x2, e);  // window energy: x[m+2] enters
-        yb[m & 3] = y;
-        float p2 = 0.f, d = 0.f;
-        if (m >= 3) {
-            p2 = yb[(m - 3) & 3] + y;  // p2[m-3]
-            p2b[(m - 3) & 7] = p2;
-        }
-        if (m >= 9) {
-            d = p2b[(m - 9) & 7] - p2;  // d[m-9]
-            db[(m - 9) & 3] = d;
-        }
-        if (m - 12 >= 0 && m - 12 < kS) acc[(m - 12) & 63] = -db[(m - 12) & 3] - y;
-        if (m - 18 >= 0 && m - 18 < kS) acc[(m - 18) & 63] += p2;
-        if (m - 30 >= 0 && m - 30 < kS) acc[(m - 30) & 63] -= d;
-        if (m - 36 >= 0 && m - 36 < kS) acc[(m - 36) & 63] -= p2;
-        if (m - 39 >= 0 && m - 39 < kS) acc[(m - 39) & 63] += y;
-        if (m - 42 >= 0 && m - 42 < kS) acc[(m - 42) & 63] -= y;
-        if (m - 48 >= 0 && m - 48 < kS) acc[(m - 48) & 63] += p2;
-        if (m - 51 >= 0 && m - 51 < kS) acc[(m - 51) & 63] -= y;
-        if (m - 57 >= 0) {
-            const int n = m - 57;  // window n is complete: x[n .. n+59] have entered e
-            const float D = acc[n & 63] + p2;
-            finish_window<FULL>(n, D, e, kap, nvalid, bits, bit0, o);
-            if ((n & 3) == 0) {
-                const float4 v = *reinterpret_cast<const float4*>(row + n);
+        for (int j = 0; j < U; ++j) {  // m = U * k + j
+            if (((j + 2) & 3) == 0) {  // x[m+2 .. m+5] become needed
+                const float4 v = *reinterpret_cast<const float4*>(rk + j + 2);
+                xr[rix<12>(j + 2)] = v.x; xr[rix<12>(j + 3)] = v.y; xr[rix<12>(j + 4)] = v.z; xr[rix<12>(j + 5)] = v.w;
+            }
+            const float x2 = xr[rix<12>(j + 2)];
+            const float y = (xr[rix<12>(j)] + xr[rix<12>(j + 1)]) + x2;
+            e = fmaf(x2, x2, e);  // window energy: x[m+2] enters
+            const float p2 = yb[rix<4>(j - 3)] + y;    // p2[m-3]
+            yb[rix<4>(j)] = y;
+            const float d = p2b[rix<12>(j - 9)] - p2;  // d[m-9]
+            p2b[rix<12>(j - 3)] = p2;
+            acc[rix<60>(j - 12)] = -db[rix<4>(j - 12)] - y;
+            db[rix<4>(j - 9)] = d;
+            acc[rix<60>(j - 18)] += p2;
+            acc[rix<60>(j - 30)] -= d;
+            acc[rix<60>(j - 36)] -= p2;
+            acc[rix<60>(j - 39)] += y;
+            acc[rix<60>(j - 42)] -= y;
+            acc[rix<60>(j - 48)] += p2;
+            acc[rix<60>(j - 51)] -= y;
+            // window n = m - 57 is complete: x[n .. n+59] have entered e
+            const float D = acc[rix<60>(j - LAT)] + p2;
+            bool valid = step_valid<U, LAT, NIT>(j, kS, is);
+            if (!FULL) valid = valid && (U * k + j - LAT) < nvalid;
+            if (finish_window(D, e, kap, valid, o)) cm |= 1ull << j;
+            if (((j - LAT) & 3) == 0) {  // x[n .. n+3] (row start for the warm-up steps: unused)
+                const int nn = U * k + j - LAT;
+                const float4 v = *reinterpret_cast<const float4*>(row + (nn >= 0 ? nn : 0));
                 xo[0] = v.x; xo[1] = v.y; xo[2] = v.z; xo[3] = v.w;
             }
-            const float xl = xo[n & 3];
+            const float xl = step_valid<U, LAT, NIT>(j, 1 << 20, is) ? xo[(j - LAT) & 3] : 0.0f;
             e = fmaf(-xl, xl, e);  // x[n] leaves
         }
+        if (cm) flush_cands<U, LAT>(cm, 0, k, FULL ? kS : nvalid, bits, bit0, o);
     }
 }
 
@@ -160,9 +202,15 @@ __device__ __forceinline__ void strip_4b5b(const float* __restrict__ row, float 
 template <bool FULL>
 __device__ __forceinline__ void strip_manchester(const float* __restrict__ row, float kap, int nvalid,
                                                  uint32_t* __restrict__ bits, uint32_t bit0, LaneOut& o) {
-    constexpr int P = 96;
-    constexpr int M = kS + P - 3;
-    float acc[128], yb[4], zb[8], wb[16], ub[16], xr[8], xo[4];
+    constexpr int U = 76, LAT = 93, NIT = 3;
+    static_assert(U * NIT >= kS + LAT && U % 19 == 0 && U % 4 == 0 && U <= 128, "strip steps");
+    float acc[76], yb[4], zb[19], wb[19], ub[19], xr[19], xo[4];
+#pragma unroll
+    for (int i = 0; i < 76; ++i) acc[i] = 0.f;
+#pragma unroll
+    for (int i = 0; i < 19; ++i) zb[i] = wb[i] = ub[i] = xr[i] = 0.f;
+#pragma unroll
+    for (int i = 0; i < 4; ++i) yb[i] = xo[i] = 0.f;
     float e = 0.0f;
     {
         const float4 v = *reinterpret_cast<const float4*>(row);
@@ -170,56 +218,60 @@ __device__ __forceinline__ void strip_manchester(const float* __restrict__ row, 
         e = fmaf(v.x, v.x, e);
         e = fmaf(v.y, v.y, e);
     }
+#pragma unroll 1
+    for (int k = 0; k < NIT; ++k) {
+        const float* __restrict__ rk = row + U * k;
+        const bool is[NIT] = {k == 0, k == 1, k == 2};
+        uint64_t cm0 = 0, cm1 = 0;
 #pragma unroll
-    for (int m = 0; m < M; ++m) {
-        if (((m + 2) & 3) == 0) {
-            const float4 v = *reinterpret_cast<const float4*>(row + m + 2);
-            xr[(m + 2) & 7] = v.x; xr[(m + 3) & 7] = v.y; xr[(m + 4) & 7] = v.z; xr[(m + 5) & 7] = v.w;
-        }
-        const float x2 = xr[(m + 2) & 7];
-        const float y = (xr[m & 7] + xr[(m + 1) & 7]) + x2;
-        e = fmaf(x2, x2, e);
-        yb[m & 3] = y;
-        float z = 0.f, w = 0.f, u = 0.f, vv = 0.f, tt = 0.f;
-        if (m >= 3) {
-            z = yb[(m - 3) & 3] - y;  // z[m-3]
-            zb[(m - 3) & 7] = z;
-        }
-        if (m >= 9) {
-            w = zb[(m - 9) & 7] + z;  // w[m-9], u[m-9]
-            u = zb[(m - 9) & 7] - z;
-            wb[(m - 9) & 15] = w;
-            ub[(m - 9) & 15] = u;
-        }
-        if (m >= 21) {
-            vv = wb[(m - 21) & 15] - w;  // v[m-21], t[m-21]
-            tt = ub[(m - 21) & 15] + u;
-        }
-        if (m - 21 >= 0 && m - 21 < kS) acc[(m - 21) & 127] = vv;
-        if (m - 45 >= 0 && m - 45 < kS) acc[(m - 45) & 127] += vv;
-        if (m - 69 >= 0 && m - 69 < kS) acc[(m - 69) & 127] += tt;
-        if (m - 93 >= 0) {
-            const int n = m - 93;
-            const float D = acc[n & 127] - tt;
-            finish_window<FULL>(n, D, e, kap, nvalid, bits, bit0, o);
-            if ((n & 3) == 0) {
-                const float4 v = *reinterpret_cast<const float4*>(row + n);
+        for (int j = 0; j < U; ++j) {  // m = U * k + j
+            if (((j + 2) & 3) == 0) {
+                const float4 v = *reinterpret_cast<const float4*>(rk + j + 2);
+                xr[rix<19>(j + 2)] = v.x; xr[rix<19>(j + 3)] = v.y; xr[rix<19>(j + 4)] = v.z; xr[rix<19>(j + 5)] = v.w;
+            }
+            const float x2 = xr[rix<19>(j + 2)];
+            const float y = (xr[rix<19>(j)] + xr[rix<19>(j + 1)]) + x2;
+            e = fmaf(x2, x2, e);
+            const float z = yb[rix<4>(j - 3)] - y;  // z[m-3]
+            yb[rix<4>(j)] = y;
+            const float zo = zb[rix<19>(j - 9)];
+            const float w = zo + z, u = zo - z;      // w[m-9], u[m-9]
+            zb[rix<19>(j - 3)] = z;
+            const float vv = wb[rix<19>(j - 21)] - w;  // v[m-21], t[m-21]
+            const float tt = ub[rix<19>(j - 21)] + u;
+            wb[rix<19>(j - 9)] = w;
+            ub[rix<19>(j - 9)] = u;
+            acc[rix<76>(j - 21)] = vv;
+            acc[rix<76>(j - 45)] += vv;
+            acc[rix<76>(j - 69)] += tt;
+            const float D = acc[rix<76>(j - LAT)] - tt;  // window n = m - 93
+            bool valid = step_valid<U, LAT, NIT>(j, kS, is);
+            if (!FULL) valid = valid && (U * k + j - LAT) < nvalid;
+            if (finish_window(D, e, kap, valid, o)) {
+                if (j < 64) cm0 |= 1ull << (j & 63);
+                else cm1 |= 1ull << (j & 63);
+            }
+            if (((j - LAT) & 3) == 0) {
+                const int nn = U * k + j - LAT;
+                const float4 v = *reinterpret_cast<const float4*>(row + (nn >= 0 ? nn : 0));
                 xo[0] = v.x; xo[1] = v.y; xo[2] = v.z; xo[3] = v.w;
             }
-            const float xl = xo[n & 3];
+            const float xl = step_valid<U, LAT, NIT>(j, 1 << 20, is) ? xo[(j - LAT) & 3] : 0.0f;
             e = fmaf(-xl, xl, e);
         }
+        if (cm0 | cm1) flush_cands<U, LAT>(cm0, cm1, k, FULL ? kS : nvalid, bits, bit0, o);
     }
 }
 
 template <int LC>
-__global__ void __launch_bounds__(kWarps * 32, 2)
+__global__ void __launch_bounds__(Shape<LC>::kWarps * 32, 2)
 scan_fast_kernel(const float* __restrict__ samples, uint64_t total_samples, const TmkStreamDev* __restrict__ streams,
                  const uint32_t* __restrict__ tile_stream, uint32_t n_tiles, const TmkPattern* __restrict__ patterns,
                  float4* __restrict__ blk_info, uint32_t* __restrict__ cand_bits) {
     using Sh = Shape<LC>;
     extern __shared__ __align__(128) float smem[];
-    __shared__ __align__(8) uint64_t mbar[kWarps];
+    __shared__ __align__(8) uint64_t mbar[kMaxWarps];
+    constexpr int kWarps = Sh::kWarps;
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     float* row = smem + size_t(warp * 32 + lane) * Sh::kRow;
     uint64_t* bar = &mbar[warp];
@@ -306,6 +358,7 @@ template <int LC>
 void launch_fast(const float* samples, uint64_t total_samples, const TmkStreamDev* streams, const uint32_t* tile_stream,
                  uint32_t n_tiles, const TmkPattern* patterns, float4* blk_info, uint32_t* cand_bits, cudaStream_t st) {
     static int grid_cap = 0;
+    constexpr int kWarps = Shape<LC>::kWarps;
     const size_t smem = size_t(kWarps) * 32 * Shape<LC>::kRow * sizeof(float);
     if (grid_cap == 0) {
         int dev = 0, sms = 0, per_sm = 0;
