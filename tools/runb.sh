@@ -1,6 +1,6 @@
 timeout 600 python -m pytest tests -m gpu -x -q 2>&1 | tail -2
-python bench.py --steps 5 --warmup 3 --e2e-steps 0 > gpurun_out/b3.json 2> gpurun_out/b3.err; echo rc=$?; tail -3 gpurun_out/b3.err
+python bench.py --steps 5 --warmup 3 > gpurun_out/b3.json 2> gpurun_out/b3.err; echo rc=$?; tail -3 gpurun_out/b3.err
 python -c "
 import json
 d=json.load(open('gpurun_out/b3.json'))
-print('RES', round(d['value']), d['stage_ms_per_step'], d['cpu_baseline']['parity_vs_gpu'], d['decode']['walk_last_step'])"
+print('RES', round(d['value']), d.get('e2e'), d['stage_ms_per_step'], d['cpu_baseline']['parity_vs_gpu'], d['decode']['walk_last_step'])"

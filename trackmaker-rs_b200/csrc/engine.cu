@@ -4,6 +4,7 @@
 #include <algorithm>
 #include <cmath>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <string>
 #include <vector>
@@ -42,12 +43,14 @@ struct tmk_engine {
     int device = 0;
     cudaStream_t stream = nullptr;
     cudaStream_t copy_stream = nullptr;
+    cudaStream_t walk_stream = nullptr;
     std::string err;
     std::vector<TmkPattern> patterns;  // host mirror of the device pattern table
     DevBuf d_tile_dir, d_patterns, d_streams, d_blk_info, d_cand, d_recs_tmp, d_rec_ord, d_recs, d_payload, d_cnt, d_base,
-        d_counters, d_samples, d_misc, d_misc2;
+        d_counters, d_samples, d_misc, d_misc2, d_next;
     cudaEvent_t ev[6] = {};
     cudaEvent_t tev[2] = {};
+    cudaEvent_t cev[6] = {};  // copy/compute hand-over of the chunked staging
     float stage_ms[4] = {0, 0, 0, 0};
     uint64_t launches = 0;
     uint64_t stats[TMK_STAT_COUNT] = {};
@@ -224,9 +227,11 @@ int tmk_engine_create(int device, tmk_engine** out) {
     tmk_engine* e = new tmk_engine();
     e->device = device;
     bool ok = cudaStreamCreateWithFlags(&e->stream, cudaStreamNonBlocking) == cudaSuccess &&
-              cudaStreamCreateWithFlags(&e->copy_stream, cudaStreamNonBlocking) == cudaSuccess;
+              cudaStreamCreateWithFlags(&e->copy_stream, cudaStreamNonBlocking) == cudaSuccess &&
+              cudaStreamCreateWithFlags(&e->walk_stream, cudaStreamNonBlocking) == cudaSuccess;
     for (int i = 0; ok && i < 6; ++i) ok = cudaEventCreate(&e->ev[i]) == cudaSuccess;
     for (int i = 0; ok && i < 2; ++i) ok = cudaEventCreate(&e->tev[i]) == cudaSuccess;
+    for (int i = 0; ok && i < 6; ++i) ok = cudaEventCreateWithFlags(&e->cev[i], cudaEventDisableTiming) == cudaSuccess;
     ok = ok && tmk_walk_init() == 0;
     ok = ok && e->d_counters.reserve(sizeof(TmkCounters)) == cudaSuccess;
     if (!ok) {
@@ -243,14 +248,17 @@ void tmk_engine_destroy(tmk_engine* e) {
     if (e->stream) cudaStreamSynchronize(e->stream);
     DevBuf* bufs[] = {&e->d_tile_dir, &e->d_patterns, &e->d_streams, &e->d_blk_info, &e->d_cand, &e->d_recs_tmp, &e->d_rec_ord,
                       &e->d_recs, &e->d_payload, &e->d_cnt, &e->d_base, &e->d_counters, &e->d_samples,
-                      &e->d_misc, &e->d_misc2};
+                      &e->d_misc, &e->d_misc2, &e->d_next};
     for (DevBuf* b : bufs) b->release();
     for (int i = 0; i < 6; ++i)
         if (e->ev[i]) cudaEventDestroy(e->ev[i]);
     for (int i = 0; i < 2; ++i)
         if (e->tev[i]) cudaEventDestroy(e->tev[i]);
+    for (int i = 0; i < 6; ++i)
+        if (e->cev[i]) cudaEventDestroy(e->cev[i]);
     if (e->stream) cudaStreamDestroy(e->stream);
     if (e->copy_stream) cudaStreamDestroy(e->copy_stream);
+    if (e->walk_stream) cudaStreamDestroy(e->walk_stream);
     delete e;
 }
 
@@ -350,55 +358,133 @@ int tmk_decode_batch(tmk_engine* e, const float* samples, uint64_t total_samples
     CK(e->d_streams.reserve(sizeof(TmkStreamDev) * n_streams));
     CK(cudaMemcpyAsync(e->d_streams.p, b.sd.data(), sizeof(TmkStreamDev) * n_streams, cudaMemcpyHostToDevice, e->stream));
     CK(cudaEventRecord(e->ev[0], e->stream));
-    const void* d_samples = nullptr;
-    rc = stage_in(e, e->d_samples, samples, total_samples * sizeof(float), &d_samples);
-    if (rc != TMK_OK) return rc;
+    // Host-resident captures are staged in chunks of whole streams: the copy of chunk g+1 (copy stream)
+    // overlaps the scan + walk of chunk g (compute stream). Device-resident captures are one chunk.
+    const bool host_samples = total_samples && !is_device_ptr(samples);
+    struct Chunk { uint32_t s0, s1, t0, t1; uint64_t lo, hi; };
+    std::vector<Chunk> chunks;
+    {
+        bool ordered = true;  // streams in increasing, non-overlapping offset order
+        for (uint32_t s = 1; s < n_streams && ordered; ++s)
+            ordered = streams[s].offset >= streams[s - 1].offset + streams[s - 1].n_samples;
+        // samples per chunk: 1 GB. The walks of the chunks share one stream and each is a ~5-8 ms serial chain, so
+        // chunks must be large enough for a walk to hide behind the next copy (measured: 8 M -> 1.8, 48 M -> 9.6,
+        // 256 M -> 13.0, one chunk -> 12.2 Gsamples/s end to end at C2)
+        uint64_t target = 256ull << 20;
+        if (const char* ev = getenv("TMK_CHUNK_MSAMPLES")) target = std::max<uint64_t>(1, strtoull(ev, nullptr, 10)) << 20;
+        if (!host_samples || !ordered || total_samples <= target) {
+            chunks.push_back({0, n_streams, 0, uint32_t(b.n_tiles), 0, total_samples});
+        } else {
+            uint32_t s0 = 0;
+            while (s0 < n_streams) {
+                uint32_t s1 = s0;
+                const uint64_t lo = streams[s0].offset;
+                uint64_t hi = lo;
+                while (s1 < n_streams && (s1 == s0 || streams[s1].offset + streams[s1].n_samples - lo <= target)) {
+                    hi = streams[s1].offset + streams[s1].n_samples;
+                    ++s1;
+                }
+                const uint32_t t0 = b.sd[s0].tile_base;
+                const uint32_t t1 = s1 < n_streams ? b.sd[s1].tile_base : uint32_t(b.n_tiles);
+                chunks.push_back({s0, s1, t0, t1, lo, hi});
+                s0 = s1;
+            }
+        }
+    }
+    const float* dx = samples;
+    if (host_samples) {
+        CK(e->d_samples.reserve(total_samples * sizeof(float)));
+        dx = static_cast<const float*>(e->d_samples.p);
+    }
     CK(e->d_blk_info.reserve(sizeof(float4) * std::max<uint64_t>(1, b.n_blocks)));
     CK(e->d_cand.reserve(sizeof(uint32_t) * TMK_BLK_WORDS * std::max<uint64_t>(1, b.n_blocks)));
     CK(e->d_cnt.reserve(sizeof(uint32_t) * n_streams));
     CK(e->d_base.reserve(sizeof(uint64_t) * (n_streams + 1)));
+    CK(e->d_next.reserve(sizeof(unsigned int) * (chunks.size() + 1)));
 
     const TmkStreamDev* ds = static_cast<const TmkStreamDev*>(e->d_streams.p);
     const TmkPattern* dp = static_cast<const TmkPattern*>(e->d_patterns.p);
-    const float* dx = static_cast<const float*>(d_samples);
     float4* dbi = static_cast<float4*>(e->d_blk_info.p);
     uint32_t* dcb = static_cast<uint32_t*>(e->d_cand.p);
     TmkCounters* dc = static_cast<TmkCounters*>(e->d_counters.p);
+    unsigned int* dnext = static_cast<unsigned int*>(e->d_next.p);
 
     if (reinterpret_cast<uintptr_t>(dx) % 16 != 0) return fail(e, TMK_E_INVALID, "sample buffer must be 16-byte aligned");
     CK(e->d_tile_dir.reserve(sizeof(uint32_t) * std::max<uint64_t>(1, b.n_tiles)));
     uint32_t* dtd = static_cast<uint32_t*>(e->d_tile_dir.p);
-    CK(cudaEventRecord(e->ev[1], e->stream));
-    e->launches += tmk_launch_tile_dir(ds, n_streams, uint32_t(b.n_tiles), dtd, e->stream);
-    CK(cudaMemsetAsync(dcb, 0, sizeof(uint32_t) * TMK_BLK_WORDS * b.n_blocks, e->stream));
-    e->launches += tmk_launch_scan(dx, total_samples, ds, n_streams, dtd, uint32_t(b.n_tiles), dp, b.kinds, dbi, dcb,
-                                   e->stream);
-    CK(cudaGetLastError());
-    CK(cudaEventRecord(e->ev[2], e->stream));
 
     // record / payload scratch on the device: start from a guess, rerun the (cheap) walk if the
     // counts say it was too small and the caller's buffers are larger.
     const bool recs_dev = rec_cap && is_device_ptr(recs), pay_dev = payload_cap && is_device_ptr(payload);
     uint64_t dev_rec_cap = std::min<uint64_t>(rec_cap, std::max<uint64_t>(4096, total_samples / 192 + 2ull * n_streams));
     uint64_t dev_pay_cap = pay_dev ? payload_cap : std::min<uint64_t>(payload_cap, std::max<uint64_t>(65536, total_samples / 24));
+    CK(e->d_recs_tmp.reserve(sizeof(tmk_frame_rec) * std::max<uint64_t>(1, dev_rec_cap)));
+    CK(e->d_rec_ord.reserve(sizeof(uint32_t) * std::max<uint64_t>(1, dev_rec_cap)));
+    if (!pay_dev) CK(e->d_payload.reserve(std::max<uint64_t>(1, dev_pay_cap)));
+
+    CK(cudaEventRecord(e->ev[1], e->stream));
+    e->launches += tmk_launch_tile_dir(ds, n_streams, uint32_t(b.n_tiles), dtd, e->stream);
+    CK(cudaMemsetAsync(dcb, 0, sizeof(uint32_t) * TMK_BLK_WORDS * b.n_blocks, e->stream));
+    CK(cudaMemsetAsync(dc, 0, sizeof(TmkCounters), e->stream));
+    CK(cudaMemsetAsync(dnext, 0, sizeof(unsigned int) * (chunks.size() + 1), e->stream));
+    if (host_samples) {
+        // the copy stream may only overwrite the staging buffer once earlier work on it is done
+        CK(cudaEventRecord(e->cev[0], e->stream));
+        CK(cudaStreamWaitEvent(e->copy_stream, e->cev[0], 0));
+    }
+    for (size_t g = 0; g < chunks.size(); ++g) {
+        const Chunk& ch = chunks[g];
+        if (host_samples) {
+            CK(cudaMemcpyAsync(const_cast<float*>(dx) + ch.lo, samples + ch.lo, (ch.hi - ch.lo) * sizeof(float),
+                               cudaMemcpyHostToDevice, e->copy_stream));
+            cudaEvent_t ce = e->cev[1 + (g & 1)];
+            CK(cudaEventRecord(ce, e->copy_stream));
+            CK(cudaStreamWaitEvent(e->stream, ce, 0));
+        }
+        e->launches += tmk_launch_scan(dx, total_samples, ds, n_streams, dtd, ch.t0, ch.t1 - ch.t0, dp, b.kinds, dbi, dcb,
+                                       e->stream);
+        if (chunks.size() == 1) CK(cudaEventRecord(e->ev[2], e->stream));
+        uint8_t* dpay = pay_dev ? payload : static_cast<uint8_t*>(e->d_payload.p);
+        // A walk is a latency-bound serial chain per stream (milliseconds whatever the number of streams), so
+        // the walks of the chunks run on their own stream, concurrently with each other and with later scans.
+        cudaStream_t ws = chunks.size() == 1 ? e->stream : e->walk_stream;
+        if (ws != e->stream) {
+            cudaEvent_t se = e->cev[3 + (g & 1)];
+            CK(cudaEventRecord(se, e->stream));
+            CK(cudaStreamWaitEvent(ws, se, 0));
+        }
+        e->launches += tmk_launch_walk(dx, ds, ch.s0, ch.s1, dnext + g, dp, dbi, dcb,
+                                       static_cast<tmk_frame_rec*>(e->d_recs_tmp.p), static_cast<uint32_t*>(e->d_rec_ord.p),
+                                       dev_rec_cap, dpay, dev_pay_cap, static_cast<uint32_t*>(e->d_cnt.p), dc, ws);
+        CK(cudaGetLastError());
+    }
+    if (chunks.size() != 1) {
+        CK(cudaEventRecord(e->cev[5], e->walk_stream));
+        CK(cudaStreamWaitEvent(e->stream, e->cev[5], 0));
+        CK(cudaEventRecord(e->ev[2], e->stream));
+    }
     TmkCounters hc;
-    for (int attempt = 0;; ++attempt) {
+    CK(cudaMemcpyAsync(&hc, dc, sizeof hc, cudaMemcpyDeviceToHost, e->stream));
+    CK(cudaStreamSynchronize(e->stream));
+    for (int attempt = 0; attempt < 2; ++attempt) {
+        const bool rec_short = hc.n_recs > dev_rec_cap && dev_rec_cap < rec_cap;
+        const bool pay_short = hc.n_payload > dev_pay_cap && dev_pay_cap < payload_cap;
+        if (!rec_short && !pay_short) break;
+        // the guess was too small: grow the scratch and walk every stream again (everything is resident now)
+        if (rec_short) dev_rec_cap = std::min<uint64_t>(rec_cap, hc.n_recs);
+        if (pay_short) dev_pay_cap = std::min<uint64_t>(payload_cap, hc.n_payload);
         CK(e->d_recs_tmp.reserve(sizeof(tmk_frame_rec) * std::max<uint64_t>(1, dev_rec_cap)));
         CK(e->d_rec_ord.reserve(sizeof(uint32_t) * std::max<uint64_t>(1, dev_rec_cap)));
         if (!pay_dev) CK(e->d_payload.reserve(std::max<uint64_t>(1, dev_pay_cap)));
         uint8_t* dpay = pay_dev ? payload : static_cast<uint8_t*>(e->d_payload.p);
         CK(cudaMemsetAsync(dc, 0, sizeof(TmkCounters), e->stream));
-        e->launches += tmk_launch_walk(dx, ds, n_streams, dp, dbi, dcb, static_cast<tmk_frame_rec*>(e->d_recs_tmp.p),
-                                       static_cast<uint32_t*>(e->d_rec_ord.p), dev_rec_cap, dpay, dev_pay_cap,
-                                       static_cast<uint32_t*>(e->d_cnt.p), dc, e->stream);
+        CK(cudaMemsetAsync(dnext + chunks.size(), 0, sizeof(unsigned int), e->stream));
+        e->launches += tmk_launch_walk(dx, ds, 0, n_streams, dnext + chunks.size(), dp, dbi, dcb,
+                                       static_cast<tmk_frame_rec*>(e->d_recs_tmp.p), static_cast<uint32_t*>(e->d_rec_ord.p),
+                                       dev_rec_cap, dpay, dev_pay_cap, static_cast<uint32_t*>(e->d_cnt.p), dc, e->stream);
         CK(cudaGetLastError());
         CK(cudaMemcpyAsync(&hc, dc, sizeof hc, cudaMemcpyDeviceToHost, e->stream));
         CK(cudaStreamSynchronize(e->stream));
-        const bool rec_short = hc.n_recs > dev_rec_cap && dev_rec_cap < rec_cap;
-        const bool pay_short = hc.n_payload > dev_pay_cap && dev_pay_cap < payload_cap;
-        if ((!rec_short && !pay_short) || attempt >= 2) break;
-        if (rec_short) dev_rec_cap = std::min<uint64_t>(rec_cap, hc.n_recs);
-        if (pay_short) dev_pay_cap = std::min<uint64_t>(payload_cap, hc.n_payload);
     }
     CK(cudaEventRecord(e->ev[3], e->stream));
     *n_recs = hc.n_recs;
@@ -488,7 +574,7 @@ int tmk_scan_probe(tmk_engine* e, const float* samples, uint64_t total_samples, 
     CK(cudaMemsetAsync(e->d_blk_info.p, 0, sizeof(float4) * b.n_blocks, e->stream));
     CK(cudaMemsetAsync(e->d_cand.p, 0, sizeof(uint32_t) * TMK_BLK_WORDS * b.n_blocks, e->stream));
     e->launches += tmk_launch_tile_dir(ds, n_streams, uint32_t(b.n_tiles), dtd, e->stream);
-    e->launches += tmk_launch_scan(static_cast<const float*>(d_samples), total_samples, ds, n_streams, dtd,
+    e->launches += tmk_launch_scan(static_cast<const float*>(d_samples), total_samples, ds, n_streams, dtd, 0,
                                    uint32_t(b.n_tiles), static_cast<const TmkPattern*>(e->d_patterns.p), b.kinds,
                                    static_cast<float4*>(e->d_blk_info.p), static_cast<uint32_t*>(e->d_cand.p), e->stream);
     CK(cudaGetLastError());

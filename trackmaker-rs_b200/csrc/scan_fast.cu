@@ -266,8 +266,8 @@ __device__ __forceinline__ void strip_manchester(const float* __restrict__ row, 
 template <int LC>
 __global__ void __launch_bounds__(Shape<LC>::kWarps * 32, 2)
 scan_fast_kernel(const float* __restrict__ samples, uint64_t total_samples, const TmkStreamDev* __restrict__ streams,
-                 const uint32_t* __restrict__ tile_stream, uint32_t n_tiles, const TmkPattern* __restrict__ patterns,
-                 float4* __restrict__ blk_info, uint32_t* __restrict__ cand_bits) {
+                 const uint32_t* __restrict__ tile_stream, uint32_t tile0, uint32_t n_tiles,
+                 const TmkPattern* __restrict__ patterns, float4* __restrict__ blk_info, uint32_t* __restrict__ cand_bits) {
     using Sh = Shape<LC>;
     extern __shared__ __align__(128) float smem[];
     __shared__ __align__(8) uint64_t mbar[kMaxWarps];
@@ -281,7 +281,8 @@ scan_fast_kernel(const float* __restrict__ samples, uint64_t total_samples, cons
     }
     __syncwarp();
     uint32_t parity = 0;
-    for (uint32_t tile = blockIdx.x * kWarps + warp; tile < n_tiles; tile += gridDim.x * kWarps) {
+    for (uint32_t tl = blockIdx.x * kWarps + warp; tl < n_tiles; tl += gridDim.x * kWarps) {
+        const uint32_t tile = tile0 + tl;  // tiles [tile0, tile0 + n_tiles) of the batch
         const uint32_t sidx = tile_stream[tile];
         const TmkStreamDev sd = streams[sidx];
         const TmkPattern* pat = patterns + sd.pattern;
@@ -356,7 +357,7 @@ __global__ void tile_dir_kernel(const TmkStreamDev* __restrict__ streams, uint32
 
 template <int LC>
 void launch_fast(const float* samples, uint64_t total_samples, const TmkStreamDev* streams, const uint32_t* tile_stream,
-                 uint32_t n_tiles, const TmkPattern* patterns, float4* blk_info, uint32_t* cand_bits, cudaStream_t st) {
+                 uint32_t tile0, uint32_t n_tiles, const TmkPattern* patterns, float4* blk_info, uint32_t* cand_bits, cudaStream_t st) {
     static int grid_cap = 0;
     constexpr int kWarps = Shape<LC>::kWarps;
     const size_t smem = size_t(kWarps) * 32 * Shape<LC>::kRow * sizeof(float);
@@ -370,7 +371,7 @@ void launch_fast(const float* samples, uint64_t total_samples, const TmkStreamDe
     }
     uint32_t grid = (n_tiles + kWarps - 1) / kWarps;
     if (grid > uint32_t(grid_cap)) grid = uint32_t(grid_cap);
-    scan_fast_kernel<LC><<<grid, kWarps * 32, smem, st>>>(samples, total_samples, streams, tile_stream, n_tiles,
+    scan_fast_kernel<LC><<<grid, kWarps * 32, smem, st>>>(samples, total_samples, streams, tile_stream, tile0, n_tiles,
                                                         patterns, blk_info, cand_bits);
 }
 
@@ -385,19 +386,19 @@ int tmk_launch_tile_dir(const TmkStreamDev* streams, uint32_t n_streams, uint32_
 
 // kinds: bit 0 = some stream is 4B5B/3/2, bit 1 = Manchester/3/2, bit 2 = any other shape (generic kernel)
 int tmk_launch_scan(const float* samples, uint64_t total_samples, const TmkStreamDev* streams, uint32_t n_streams,
-                    const uint32_t* tile_stream, uint32_t n_tiles, const TmkPattern* patterns, uint32_t kinds,
-                    float4* blk_info, uint32_t* cand_bits, cudaStream_t st) {
+                    const uint32_t* tile_stream, uint32_t tile0, uint32_t n_tiles, const TmkPattern* patterns,
+                    uint32_t kinds, float4* blk_info, uint32_t* cand_bits, cudaStream_t st) {
     if (n_tiles == 0) return 0;
     int launches = 0;
     if (kinds & 1u) {
-        launch_fast<TMK_LINE_4B5B>(samples, total_samples, streams, tile_stream, n_tiles, patterns, blk_info, cand_bits, st);
+        launch_fast<TMK_LINE_4B5B>(samples, total_samples, streams, tile_stream, tile0, n_tiles, patterns, blk_info, cand_bits, st);
         ++launches;
     }
     if (kinds & 2u) {
-        launch_fast<TMK_LINE_MANCHESTER>(samples, total_samples, streams, tile_stream, n_tiles, patterns, blk_info,
+        launch_fast<TMK_LINE_MANCHESTER>(samples, total_samples, streams, tile_stream, tile0, n_tiles, patterns, blk_info,
                                          cand_bits, st);
         ++launches;
     }
-    if (kinds & 4u) launches += tmk_launch_scan_generic(samples, streams, tile_stream, n_tiles, patterns, blk_info, cand_bits, st);
+    if (kinds & 4u) launches += tmk_launch_scan_generic(samples, streams, tile_stream, tile0, n_tiles, patterns, blk_info, cand_bits, st);
     return launches;
 }

@@ -18,13 +18,13 @@ constexpr int kSmemX = TMK_TILE + TMK_MAX_P + 8;
 
 __global__ void __launch_bounds__(kThreads)
 scan_generic_kernel(const float* __restrict__ samples, const TmkStreamDev* __restrict__ streams,
-                    const uint32_t* __restrict__ tile_stream, const TmkPattern* __restrict__ patterns,
+                    const uint32_t* __restrict__ tile_stream, uint32_t tile0, const TmkPattern* __restrict__ patterns,
                     float4* __restrict__ blk_info, uint32_t* __restrict__ cand_bits) {
     __shared__ float xs[kSmemX];   // raw samples, then box sums of spl samples
     __shared__ float qs[kSmemX];   // box sums of spl squared samples
     __shared__ float lev[TMK_MAX_LEVELS];
 
-    const uint32_t tile = blockIdx.x;
+    const uint32_t tile = tile0 + blockIdx.x;
     const TmkStreamDev sd = streams[tile_stream[tile]];
     const TmkPattern* pat = patterns + sd.pattern;
     if (pat->spl == 3 && pat->preamble_bytes == 2) return;  // scan_fast.cu owns the shipped shapes
@@ -118,9 +118,9 @@ scan_generic_kernel(const float* __restrict__ samples, const TmkStreamDev* __res
 }  // namespace
 
 int tmk_launch_scan_generic(const float* samples, const TmkStreamDev* streams, const uint32_t* tile_stream,
-                            uint32_t n_tiles, const TmkPattern* patterns, float4* blk_info, uint32_t* cand_bits,
+                            uint32_t tile0, uint32_t n_tiles, const TmkPattern* patterns, float4* blk_info, uint32_t* cand_bits,
                             cudaStream_t st) {
     if (n_tiles == 0) return 0;
-    scan_generic_kernel<<<n_tiles, kThreads, 0, st>>>(samples, streams, tile_stream, patterns, blk_info, cand_bits);
+    scan_generic_kernel<<<n_tiles, kThreads, 0, st>>>(samples, streams, tile_stream, tile0, patterns, blk_info, cand_bits);
     return 1;
 }

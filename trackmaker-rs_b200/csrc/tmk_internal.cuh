@@ -108,12 +108,13 @@ int tmk_launch_tile_dir(const TmkStreamDev* streams, uint32_t n_streams, uint32_
                         cudaStream_t st);
 // kinds: bit 0 = 4B5B/spl 3/2 bytes streams present, bit 1 = Manchester/3/2, bit 2 = any other shape
 int tmk_launch_scan(const float* samples, uint64_t total_samples, const TmkStreamDev* streams, uint32_t n_streams,
-                    const uint32_t* tile_stream, uint32_t n_tiles, const TmkPattern* patterns, uint32_t kinds,
-                    float4* blk_info, uint32_t* cand_bits, cudaStream_t st);
+                    const uint32_t* tile_stream, uint32_t tile0, uint32_t n_tiles, const TmkPattern* patterns,
+                    uint32_t kinds, float4* blk_info, uint32_t* cand_bits, cudaStream_t st);
 int tmk_launch_scan_generic(const float* samples, const TmkStreamDev* streams, const uint32_t* tile_stream,
-                            uint32_t n_tiles, const TmkPattern* patterns, float4* blk_info, uint32_t* cand_bits,
-                            cudaStream_t st);
-int tmk_launch_walk(const float* samples, const TmkStreamDev* streams, uint32_t n_streams,
+                            uint32_t tile0, uint32_t n_tiles, const TmkPattern* patterns, float4* blk_info,
+                            uint32_t* cand_bits, cudaStream_t st);
+// walks streams [s0, s1); `next` is a zeroed work counter owned by this launch
+int tmk_launch_walk(const float* samples, const TmkStreamDev* streams, uint32_t s0, uint32_t s1, unsigned int* next,
                     const TmkPattern* patterns, const float4* blk_info, const uint32_t* cand_bits,
                     tmk_frame_rec* recs, uint32_t* rec_ord, uint64_t rec_cap, uint8_t* payload,
                     uint64_t payload_cap, uint32_t* stream_cnt, TmkCounters* counters, cudaStream_t st);

@@ -761,7 +761,8 @@ __device__ __noinline__ void emit(const Ctx& c, Emit& em, uint32_t status, const
 }
 
 __global__ void __launch_bounds__(kWarpsPerCta * 32, 7)
-walk_kernel(const float* __restrict__ samples, const TmkStreamDev* __restrict__ streams, uint32_t n_streams,
+walk_kernel(const float* __restrict__ samples, const TmkStreamDev* __restrict__ streams, uint32_t s0, uint32_t s1,
+            unsigned int* __restrict__ next,
             const TmkPattern* __restrict__ patterns, const float4* __restrict__ blk_info,
             const uint32_t* __restrict__ cand_bits, tmk_frame_rec* recs, uint32_t* rec_ord, uint64_t rec_cap,
             uint8_t* payload, uint64_t payload_cap, uint32_t* stream_cnt, TmkCounters* counters) {
@@ -772,9 +773,9 @@ walk_kernel(const float* __restrict__ samples, const TmkStreamDev* __restrict__ 
     // pulls the next stream from a counter instead of owning a fixed one
     for (;;) {
     uint32_t sidx = 0;
-    if (lane_id == 0) sidx = atomicAdd(&counters->next_stream, 1u);
+    if (lane_id == 0) sidx = s0 + atomicAdd(next, 1u);
     sidx = __shfl_sync(kFull, sidx, 0);
-    if (sidx >= n_streams) return;
+    if (sidx >= s1) return;
     const TmkStreamDev sd = streams[sidx];
     Ctx c;
     c.x = samples + sd.offset;
@@ -963,11 +964,12 @@ int tmk_launch_excl_scan(const uint32_t* cnt, uint64_t* base, uint32_t n, cudaSt
     return 1;
 }
 
-int tmk_launch_walk(const float* samples, const TmkStreamDev* streams, uint32_t n_streams,
+int tmk_launch_walk(const float* samples, const TmkStreamDev* streams, uint32_t s0, uint32_t s1, unsigned int* next,
                     const TmkPattern* patterns, const float4* blk_info, const uint32_t* cand_bits,
                     tmk_frame_rec* recs, uint32_t* rec_ord, uint64_t rec_cap, uint8_t* payload,
                     uint64_t payload_cap, uint32_t* stream_cnt, TmkCounters* counters, cudaStream_t st) {
-    if (n_streams == 0) return 0;
+    if (s1 <= s0) return 0;
+    const uint32_t n_streams = s1 - s0;
     static int max_ctas = 0;
     if (max_ctas == 0) {
         int dev = 0, sms = 0, per_sm = 0;
@@ -978,7 +980,7 @@ int tmk_launch_walk(const float* samples, const TmkStreamDev* streams, uint32_t 
     }
     uint32_t grid = (n_streams + kWarpsPerCta - 1) / kWarpsPerCta;
     if (grid > uint32_t(max_ctas)) grid = uint32_t(max_ctas);
-    walk_kernel<<<grid, kWarpsPerCta * 32, 0, st>>>(samples, streams, n_streams, patterns, blk_info, cand_bits, recs,
+    walk_kernel<<<grid, kWarpsPerCta * 32, 0, st>>>(samples, streams, s0, s1, next, patterns, blk_info, cand_bits, recs,
                                                     rec_ord, rec_cap, payload, payload_cap, stream_cnt, counters);
     return 1;
 }
