@@ -155,16 +155,16 @@ def main():
 
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
-    local = int(os.environ.get("LOCAL_RANK", "0"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
     dist = None
     if world > 1:
         import torch
         import torch.distributed as dist
-        torch.cuda.set_device(local)
-        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+        torch.cuda.set_device(local_rank)
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
 
     import tmkphy
-    eng = tmkphy.Engine(local)  # raises without a B200: no CPU fallback
+    eng = tmkphy.Engine(local_rank)  # raises without a B200: no CPU fallback
     kind = tmkphy.LINE_4B5B if args.line_code.lower() == "4b5b" else tmkphy.LINE_MANCHESTER
     cfg = tmkphy.make_config(kind, local_addr=1, chunk=args.chunk)
     n_s, n_per = args.streams, args.samples
@@ -205,7 +205,7 @@ def main():
 
     for _ in range(args.warmup):
         step_resident()
-    sampler = ClockSampler(local)
+    sampler = ClockSampler(local_rank)
     sampler.start()
     barrier()
     l0 = eng.launch_count()
@@ -244,17 +244,19 @@ def main():
         barrier()
         e2e_d2h = int(nr.value) * 48 + int(npl.value)
 
-    # ---- max over ranks
-    ms_all, e2e_all = ms_total, e2e_ms
-    counters = np.array([stats_recs, stats_pay, planted] + [eng.stats()[k] for k in tmkphy.STAT_NAMES], dtype=np.int64)
+    # ---- max over ranks of the device times, sum of the decode counters (the only collective)
+    from tmkphy import sharding
+    names = ["records", "payload_bytes", "frames_planted"] + list(tmkphy.STAT_NAMES)
+    local = dict(zip(names, [stats_recs, stats_pay, planted] + [eng.stats()[k] for k in tmkphy.STAT_NAMES]))
+    dev = None
     if dist is not None:
         import torch
-        t = torch.tensor([ms_total, e2e_ms or 0.0], device=f"cuda:{local}", dtype=torch.float64)
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        ms_all, e2e_all = float(t[0]), (float(t[1]) if e2e_ms is not None else None)
-        ct = torch.tensor(counters, device=f"cuda:{local}")
-        dist.all_reduce(ct, op=dist.ReduceOp.SUM)  # the only collective: decode statistics
-        counters = ct.cpu().numpy()
+        dev = torch.device("cuda", local_rank)
+    summed, ms_all = sharding.reduce_stats(local, ms_total, device=dev)
+    e2e_all = e2e_ms
+    if e2e_ms is not None:
+        _, e2e_all = sharding.reduce_stats({}, e2e_ms, device=dev)
+    counters = np.array([summed[k] for k in names], dtype=np.int64)
 
     if rank == 0:
         hbm, which = peaks()
