@@ -213,6 +213,44 @@ int tmk_synth_batch(tmk_engine* e, const tmk_phy_config* cfg, uint64_t seed, uin
                     uint64_t n_per_stream, float snr_db, float amplitude, float* samples,
                     tmk_frame_rec* truth, uint64_t truth_cap, uint64_t* n_truth);
 
+/* ------------------------------------------------------------------------------------------------
+ * Chirp + BPSK modem of examples/ask.rs (project 1): 440-sample chirp preamble 2 kHz -> 10 kHz -> 2 kHz,
+ * BPSK on a 10 kHz carrier at 44 samples per bit, frames of 100 bits + 8 zero bits.
+ *   tmk_ask_modulate      replaces the TX loop                  examples/ask.rs:608-637 (live :176-218)
+ *   tmk_ask_decode_batch  replaces the RX loop                  examples/ask.rs:668-796 (live :360-496):
+ *                         EMA power, 440-tap sliding chirp correlation / 200, peak pick with 200-sample
+ *                         hold-off, carrier mixing, 11-tap moving average, integrate-and-dump, id check
+ *   tmk_ask_tables        the preamble / carrier tables         examples/ask.rs:574-605
+ */
+#define TMK_ASK_PREAMBLE 440
+#define TMK_ASK_SAMPLES_PER_BIT 44
+#define TMK_ASK_FRAME_BITS 108
+#define TMK_ASK_DATA_BITS 100
+#define TMK_ASK_FRAME_SAMPLES (TMK_ASK_SAMPLES_PER_BIT * TMK_ASK_FRAME_BITS) /* 4752 */
+
+typedef struct tmk_ask_rec {
+    uint32_t stream;
+    uint32_t accepted;    /* 1 <= id <= 100 (ask.rs:771) */
+    uint64_t start_index; /* sample index of the sync peak that locked (ask.rs:716) */
+    float sync_power;     /* its value */
+    uint8_t id;           /* first 8 decided bits, MSB first */
+    uint8_t bits[14];     /* the 108 decided bits, MSB first: bit j is bits[j / 8] >> (7 - j % 8) */
+    uint8_t _pad[5];
+} tmk_ask_rec;
+
+/* the tables the engine uses (computed once on the host in the reference's f32 operation order) */
+int tmk_ask_tables(tmk_engine* e, float* preamble440, float* carrier, uint64_t n_carrier);
+/* bits: n_frames x 100 values 0/1; gap1/gap2: zeros before/after each frame. Returns the track. */
+uint64_t tmk_ask_modulated_len(uint32_t n_frames, const uint32_t* gap1, const uint32_t* gap2);
+int tmk_ask_modulate(tmk_engine* e, const uint8_t* bits, uint32_t n_frames, const uint32_t* gap1,
+                     const uint32_t* gap2, float* out_samples, uint64_t out_cap, uint64_t* out_len);
+/* one record per locked frame, sorted by (stream, start_index). Only offset / n_samples of the
+ * streams are used. samples: host or device; recs: host. */
+int tmk_ask_decode_batch(tmk_engine* e, const float* samples, uint64_t total_samples, const tmk_stream* streams,
+                         uint32_t n_streams, tmk_ask_rec* recs, uint64_t rec_cap, uint64_t* n_recs);
+/* device time of the stages of the last tmk_ask_decode_batch call, ms: [0] chirp scan, [1] walk */
+int tmk_ask_last_stage_ms(tmk_engine* e, float ms[2]);
+
 #ifdef __cplusplus
 }
 #endif

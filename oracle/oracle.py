@@ -52,6 +52,9 @@ def lib():
             "orc_correlate": (u64, [pcfg, vp, u64, vp]),
             "orc_channel_busy": (C.c_int, [vp, u64]),
             "orc_hardware_threads": (C.c_int, []),
+            "orc_ask_tables": (None, [vp, vp, u64]),
+            "orc_ask_modulate": (u64, [vp, u32, vp, vp, vp, u64]),
+            "orc_ask_demodulate": (u64, [vp, u64, u32, vp, u64]),
         }
         for n, (r, a) in sig.items():
             f = getattr(L, n)
@@ -185,3 +188,32 @@ def channel_busy(samples) -> int:
 
 def hardware_threads() -> int:
     return lib().orc_hardware_threads()
+
+
+# ---- chirp + BPSK modem (examples/ask.rs)
+def ask_tables(n_carrier=4752):
+    pre, car = np.zeros(440, np.float32), np.zeros(n_carrier, np.float32)
+    lib().orc_ask_tables(_ptr(pre), _ptr(car), n_carrier)
+    return pre, car
+
+
+def ask_modulate(bits, gap1, gap2) -> np.ndarray:
+    """bits: (n_frames, 100) array of 0/1; gap1/gap2: zeros before / after each frame"""
+    b = np.ascontiguousarray(bits, dtype=np.uint8).reshape(-1, 100)
+    g1 = np.ascontiguousarray(gap1, dtype=np.uint32)
+    g2 = np.ascontiguousarray(gap2, dtype=np.uint32)
+    n = int(len(b) * (440 + 4752) + g1.sum() + g2.sum())
+    out = np.zeros(max(n, 1), np.float32)
+    got = lib().orc_ask_modulate(_ptr(b), len(b), _ptr(g1), _ptr(g2), _ptr(out), n)
+    assert got == n
+    return out[:n]
+
+
+def ask_demodulate(samples, stream=0, cap=None) -> np.ndarray:
+    from tmkphy._abi import ASK_REC_DTYPE
+    s = np.ascontiguousarray(samples, dtype=np.float32)
+    cap = cap or max(16, len(s) // 4000 + 4)
+    recs = np.zeros(cap, ASK_REC_DTYPE)
+    n = lib().orc_ask_demodulate(_ptr(s), len(s), stream, _ptr(recs), cap)
+    assert n <= cap
+    return recs[:n].copy()

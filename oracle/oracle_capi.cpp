@@ -4,6 +4,7 @@
 #include <chrono>
 #include <thread>
 
+#include "ask_modem.hpp"
 #include "phy_decoder.hpp"
 
 using namespace orc;
@@ -167,6 +168,37 @@ int orc_channel_busy(const float* s, uint64_t n) {
     for (uint64_t i = 0; i < n; ++i)
         if (std::fabs(s[i]) > 0.5f) return 1;
     return 0;
+}
+
+// ---- chirp + BPSK modem (examples/ask.rs)
+void orc_ask_tables(float* preamble440, float* carrier, uint64_t n_carrier) {
+    auto p = orc_ask::preamble();
+    std::copy(p.begin(), p.end(), preamble440);
+    auto c = orc_ask::carrier(n_carrier);
+    std::copy(c.begin(), c.end(), carrier);
+}
+
+uint64_t orc_ask_modulate(const uint8_t* bits, uint32_t n_frames, const uint32_t* gap1, const uint32_t* gap2,
+                          float* out, uint64_t cap) {
+    auto v = orc_ask::modulate(bits, n_frames, gap1, gap2);
+    std::copy(v.begin(), v.begin() + std::min<uint64_t>(cap, v.size()), out);
+    return v.size();
+}
+
+// recs: tmk_ask_rec layout (include/tmkphy.h)
+uint64_t orc_ask_demodulate(const float* rx, uint64_t n, uint32_t stream, tmk_ask_rec* recs, uint64_t cap) {
+    auto v = orc_ask::demodulate(rx, n);
+    for (size_t i = 0; i < v.size() && i < cap; ++i) {
+        tmk_ask_rec r{};
+        r.stream = stream;
+        r.accepted = v[i].accepted;
+        r.start_index = v[i].start_index;
+        r.sync_power = v[i].sync_power;
+        r.id = v[i].id;
+        std::memcpy(r.bits, v[i].bits, 14);
+        recs[i] = r;
+    }
+    return v.size();
 }
 
 int orc_hardware_threads(void) { return int(std::thread::hardware_concurrency()); }

@@ -1,0 +1,108 @@
+"""Parity of the chirp + BPSK modem (examples/ask.rs:526-858) through the C ABI against the oracle:
+tables, modulated track and every record field bit-exact (sync peaks, sync power, decided bits, ids)."""
+import os
+
+import numpy as np
+import pytest
+
+pytestmark = pytest.mark.gpu
+GOLDEN = os.path.join(os.path.dirname(__file__), "golden")
+
+
+def ask_frames(text, n=100):
+    """examples/ask.rs:546-569: bits 0-7 = frame id 1.., bits 8-99 = the next 92 payload bits, wrapping"""
+    tb = np.unpackbits(np.frombuffer(text, np.uint8))
+    fr = np.zeros((n, 100), np.uint8)
+    bi = 0
+    for i in range(n):
+        fr[i, :8] = [((i + 1) >> (7 - j)) & 1 for j in range(8)]
+        for j in range(8, 100):
+            if bi >= len(tb):
+                bi = 0
+            fr[i, j] = tb[bi]
+            bi += 1
+    return fr
+
+
+def assert_ask_equal(got, want, ctx=""):
+    assert len(got) == len(want), f"{ctx}: {len(got)} records, oracle {len(want)}"
+    for f in ("stream", "accepted", "start_index", "id"):
+        assert np.array_equal(got[f], want[f]), f"{ctx}: field {f} differs"
+    assert np.array_equal(got["bits"], want["bits"]), f"{ctx}: decided bits differ"
+    assert np.array_equal(got["sync_power"].view(np.uint32), want["sync_power"].view(np.uint32)), f"{ctx}: sync_power"
+
+
+def oracle_batch(orc, s, st):
+    out = [orc.ask_demodulate(s[int(t["offset"]):int(t["offset"]) + int(t["n_samples"])], stream=i) for i, t in enumerate(st)]
+    return np.concatenate(out) if out else np.zeros(0)
+
+
+def test_ask_tables_and_modulate_bit_exact(engine, orc):
+    pre, car = engine.ask_tables(48000)
+    opre, ocar = orc.ask_tables(48000)
+    assert np.array_equal(pre.view(np.uint32), opre.view(np.uint32)) and np.array_equal(car.view(np.uint32), ocar.view(np.uint32))
+    assert pre[0] == 0.0 and abs(pre).max() <= 1.0
+    rng = np.random.default_rng(1)
+    fr = rng.integers(0, 2, (7, 100)).astype(np.uint8)
+    g1, g2 = rng.integers(0, 100, 7), rng.integers(0, 100, 7)
+    got, want = engine.ask_modulate(fr, g1, g2), orc.ask_modulate(fr, g1, g2)
+    assert np.array_equal(got.view(np.uint32), want.view(np.uint32))
+    assert len(engine.ask_modulate(np.zeros((0, 100), np.uint8), [], [])) == 0
+
+
+def test_ask_loopback_think_different(engine, orc):
+    """the reference's own offline test: 100 frames of assets/think-different.txt, decoded text matches"""
+    import tmkphy
+    text = open(os.path.join(GOLDEN, "think-different.txt"), "rb").read()
+    fr = ask_frames(text)
+    rng = np.random.default_rng(7)
+    g1, g2 = rng.integers(0, 100, 100), rng.integers(0, 100, 100)
+    x = engine.ask_modulate(fr, g1, g2)
+    st, total = tmkphy.make_streams([len(x)], tmkphy.make_config(1))
+    got = engine.ask_decode_batch(x, st)
+    assert_ask_equal(got, orc.ask_demodulate(x), "loopback")
+    assert len(got) == 100 and got["accepted"].all() and list(got["id"]) == list(range(1, 101))
+    bits = np.unpackbits(got["bits"], axis=1)[:, 8:100].reshape(-1)
+    decoded = np.packbits(bits[:len(bits) // 8 * 8]).tobytes()
+    n = min(len(decoded), len(text))
+    assert decoded[:n] == text[:n]
+    assert got["start_index"][0] == g1[0] + 439
+
+
+def impaired(rng, x, snr_db=None, amp=1.0, multipath=False):
+    y = x.astype(np.float64) * amp
+    if multipath:
+        h = np.zeros(41)
+        h[0], h[int(rng.integers(2, 13))], h[int(rng.integers(13, 41))] = 1.0, 0.35, -0.2
+        y = np.convolve(y, h / np.sqrt((h * h).sum()))[:len(y)]
+    if snr_db is not None:
+        y = y + rng.normal(0, amp * np.sqrt(0.5) * 10 ** (-snr_db / 20), len(y))
+    return y.astype(np.float32)
+
+
+def test_ask_batch_impairments(engine, orc):
+    """ragged batch: AWGN sweep, amplitude scaling, multipath, long gaps, truncation inside a frame and inside a
+    preamble, silence, streams shorter than the preamble, a loud burst before quiet frames"""
+    import tmkphy
+    rng = np.random.default_rng(11)
+    caps = []
+    for i, snr in enumerate((None, 30, 20, 12, 8, 5, 3, 0, -3)):
+        fr = rng.integers(0, 2, (6, 100)).astype(np.uint8)
+        fr[:, :8] = [[((k + 1) >> (7 - j)) & 1 for j in range(8)] for k in range(6)]
+        if i % 3 == 2:
+            fr[2, :8] = 1  # id 255: decoded but not accepted
+        x = orc.ask_modulate(fr, rng.integers(0, 3000, 6), rng.integers(0, 100, 6))
+        caps.append(impaired(rng, x, snr, amp=float(rng.uniform(0.2, 1.0)), multipath=(i % 2 == 1)))
+    base = orc.ask_modulate(rng.integers(0, 2, (3, 100)).astype(np.uint8), [50, 0, 10], [0, 30, 500])
+    caps += [base[:6000], base[:250], base[:5192 + 50 + 300], np.zeros(3000, np.float32), np.zeros(100, np.float32),
+             np.zeros(0, np.float32), impaired(rng, base, 10)[:20000]]
+    loud = rng.normal(0, 20.0, 4000).astype(np.float32)
+    caps.append(np.concatenate([loud, base * 0.05, loud[:700], base * 0.3]).astype(np.float32))
+    st, total = tmkphy.make_streams([len(c) for c in caps], tmkphy.make_config(1))
+    s = np.zeros(total, np.float32)
+    for i, c in enumerate(caps):
+        s[int(st[i]["offset"]):int(st[i]["offset"]) + len(c)] = c
+    got = engine.ask_decode_batch(s, st)
+    want = oracle_batch(orc, s, st)
+    assert_ask_equal(got, want, "impairments")
+    assert got["accepted"].sum() > 30 and (got["accepted"] == 0).any()

@@ -1,0 +1,579 @@
+// ask.cu — the chirp + BPSK modem of the reference's project 1, examples/ask.rs::test_sender_receiver
+// (:526-858; live TX :104-262, live RX :264-524), batched over many captures.
+//
+//   ask_scan_kernel   FILTER over every sample: 440-tap chirp correlation / 200 (fp32 FMA, register-blocked
+//                     out of shared memory) and the EMA power (affine block scan), marks every 32-sample
+//                     word in which `sync_power > 2 power && sync_power > 0.05` (ask.rs:711-714) could hold,
+//                     with margins that cover the re-association error.
+//   ask_walk_kernel   one warp per capture replays the reference's state machine over the marked words
+//                     only, in the reference's f32 operation order: sequential 440-term dot product
+//                     (ask.rs:704-709), the exact EMA chain (:696-697, carried over every sample), running
+//                     maximum with the 200-sample hold-off (:711-723), the dropped sample start_index+201,
+//                     the zeroed FIFO after a frame, carrier mixing + 11-tap moving average + integrate and
+//                     dump (:733-761), id check (:764-771).
+//   ask_modulate_kernel  TX (:608-637).
+// Tables (preamble, carrier) are computed once on the host with sinf in the reference's operation order
+// (ask.rs:574-605) and uploaded, so device sin never enters.
+//
+// Bound: the filter is a 440-tap direct-form FIR, 880 flop per 4-byte sample: FP32-pipe bound, far above
+// the HBM ridge (an overlap-save FFT in shared memory is the planned replacement).
+#include <algorithm>
+#include <cmath>
+#include <cstring>
+
+#include "engine.hpp"
+
+namespace {
+
+constexpr int kPre = TMK_ASK_PREAMBLE;
+constexpr int kFrame = TMK_ASK_FRAME_SAMPLES;
+constexpr int kBits = TMK_ASK_FRAME_BITS;
+constexpr unsigned kFull = 0xffffffffu;
+constexpr float kC = 0.984375f;     // 1.0 - 1.0 / 64.0   (exact)
+constexpr float kInv64 = 0.015625f;  // x * x / 64.0: scaling by a power of two, same rounding as the divide
+
+struct AskStream {
+    uint64_t offset, n;
+    uint64_t word_base;  // first flag bit of this stream (one bit per 32 samples)
+    uint32_t tile_base;  // first scan tile
+    uint32_t pad_;
+};
+
+// ---------------------------------------------------------------- TX
+__global__ void ask_modulate_kernel(const float* __restrict__ tab, const uint8_t* __restrict__ bits,
+                                    const uint64_t* __restrict__ frame_off, const uint32_t* __restrict__ gap1,
+                                    const uint32_t* __restrict__ gap2, float* __restrict__ out) {
+    const uint32_t f = blockIdx.x;
+    float* o = out + frame_off[f];
+    const uint32_t g1 = gap1[f], g2 = gap2[f];
+    const float* pre = tab;
+    const float* car = tab + kPre;
+    for (uint32_t i = threadIdx.x; i < g1; i += blockDim.x) o[i] = 0.0f;
+    o += g1;
+    for (uint32_t i = threadIdx.x; i < kPre; i += blockDim.x) o[i] = pre[i];
+    o += kPre;
+    for (uint32_t k = threadIdx.x; k < kFrame; k += blockDim.x) {
+        const uint32_t j = k / TMK_ASK_SAMPLES_PER_BIT;
+        const bool one = j < TMK_ASK_DATA_BITS && bits[f * TMK_ASK_DATA_BITS + j] == 1;
+        o[k] = one ? car[k] : -car[k];  // carrier[k] * (+-1.0) is exact
+    }
+    o += kFrame;
+    for (uint32_t i = threadIdx.x; i < g2; i += blockDim.x) o[i] = 0.0f;
+}
+
+// ---------------------------------------------------------------- filter
+constexpr int kT = 1024;      // positions per tile
+constexpr int kThreads = 128; // 8 positions per thread
+constexpr int kW = 2048;      // EMA warm-up: 0.984375^2048 ~ 1e-14
+constexpr int kXs = kW + kT;  // staged samples: x[t0 - kW .. t0 + kT)
+
+__global__ void __launch_bounds__(kThreads)
+ask_scan_kernel(const float* __restrict__ samples, const AskStream* __restrict__ streams, uint32_t n_streams,
+                const float* __restrict__ tab, uint32_t* __restrict__ wflag) {
+    __shared__ __align__(16) float xs[kXs];
+    __shared__ __align__(16) float ps[kT];
+    __shared__ __align__(16) float pre[kPre];
+    __shared__ float red[kThreads / 32];
+    __shared__ float carry[kThreads / 32];
+    const uint32_t tile = blockIdx.x;
+    uint32_t lo = 0, hi = n_streams - 1;
+    while (lo < hi) {
+        const uint32_t mid = (lo + hi + 1) >> 1;
+        if (streams[mid].tile_base <= tile) lo = mid; else hi = mid - 1;
+    }
+    const AskStream sd = streams[lo];
+    const float* __restrict__ x = samples + sd.offset;
+    const int64_t n = int64_t(sd.n);
+    const int64_t t0 = int64_t(tile - sd.tile_base) * kT;
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    for (int i = tid; i < kPre; i += kThreads) pre[i] = tab[i];
+    float xmax = 0.0f;
+    for (int i = tid; i < kXs; i += kThreads) {
+        const int64_t g = t0 - kW + i;
+        const float v = (g >= 0 && g < n) ? x[g] : 0.0f;
+        xs[i] = v;
+        xmax = fmaxf(xmax, fabsf(v));
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) xmax = fmaxf(xmax, __shfl_xor_sync(kFull, xmax, o));
+    if (lane == 0) red[warp] = xmax;
+    __syncthreads();
+    xmax = fmaxf(fmaxf(red[0], red[1]), fmaxf(red[2], red[3]));
+    if (!(xmax <= 3.0e38f)) xmax = 3.0e38f;  // NaN / inf samples: everything in the tile becomes a candidate
+
+    // ---- EMA power p_i = c p_{i-1} + x_i^2 / 64 over the staged range, zero state at its start
+    constexpr int kPer = kXs / kThreads;  // 24 consecutive samples per thread
+    float q = 0.0f;
+#pragma unroll
+    for (int j = 0; j < kPer; ++j) {
+        const float v = xs[tid * kPer + j];
+        q = fmaf(q, kC, v * v * kInv64);
+    }
+    // inclusive scan of the affine maps p -> c^24 p + q over the threads (c^24 constant per step)
+    float v = q, mul = powf(kC, float(kPer));
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+        const float t = __shfl_up_sync(kFull, v, o);
+        if (lane >= o) v = fmaf(t, mul, v);
+        mul *= mul;
+    }
+    if (lane == 31) carry[warp] = v;
+    __syncthreads();
+    const float c768 = powf(kC, float(kPer * 32));  // one warp's span
+    float pin = 0.0f;  // state entering this warp
+    for (int w = 0; w < warp; ++w) pin = fmaf(pin, c768, carry[w]);
+    // state entering this thread = (inclusive of previous lane) advanced
+    float prev = __shfl_up_sync(kFull, v, 1);
+    if (lane == 0) prev = 0.0f;
+    float p = fmaf(pin, powf(kC, float(kPer * lane)), prev);
+#pragma unroll
+    for (int j = 0; j < kPer; ++j) {
+        const int i = tid * kPer + j;
+        const float xv = xs[i];
+        p = fmaf(p, kC, xv * xv * kInv64);
+        if (i >= kW) ps[i - kW] = p;
+    }
+    __syncthreads();
+
+    // ---- 440-tap correlation, 8 consecutive positions per thread: position t0 + 8 tid + j uses
+    //      x[i - 439 + k] = xs[kW - 439 + 8 tid + j + k]
+    float acc[8];
+#pragma unroll
+    for (int j = 0; j < 8; ++j) acc[j] = 0.0f;
+    const float* xp = xs + (kW - 440) + 8 * tid;  // 16-byte aligned; element [1 + j + k] is the sample of tap k
+#pragma unroll 2
+    for (int k = 0; k < kPre; k += 4) {
+        const float4 pr = *reinterpret_cast<const float4*>(pre + k);
+        const float4 a = *reinterpret_cast<const float4*>(xp + k);
+        const float4 b = *reinterpret_cast<const float4*>(xp + k + 4);
+        const float4 c = *reinterpret_cast<const float4*>(xp + k + 8);
+        const float xv[12] = {a.x, a.y, a.z, a.w, b.x, b.y, b.z, b.w, c.x, c.y, c.z, c.w};
+        const float pk[4] = {pr.x, pr.y, pr.z, pr.w};
+#pragma unroll
+        for (int kk = 0; kk < 4; ++kk)
+#pragma unroll
+            for (int j = 0; j < 8; ++j) acc[j] = fmaf(xv[1 + j + kk], pk[kk], acc[j]);
+    }
+    // ---- candidate test with margins for the re-association error of both sides
+    const float tol = 1.3e-4f * xmax + 1e-7f;  // both sums are within 440 u sum|x pre| / 200 <= 5.8e-5 xmax of the exact value
+    uint32_t any = 0;
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+        const int64_t i = t0 + 8 * tid + j;
+        const float sp = acc[j] * (1.0f / 200.0f) + tol;
+        const float pw = ps[8 * tid + j];
+        const bool cand = i < n && (!(sp <= 0.05f) && !(sp <= 2.0f * pw * (1.0f - 1e-4f)));  // NaN -> candidate
+        any |= cand ? 1u : 0u;
+    }
+    // 4 threads cover one 32-sample word
+    any |= __shfl_xor_sync(kFull, any, 1);
+    any |= __shfl_xor_sync(kFull, any, 2);
+    if ((lane & 3) == 0 && any) {
+        const uint64_t wbit = sd.word_base + uint64_t(t0 + 8 * tid) / 32;
+        atomicOr(wflag + (wbit >> 5), 1u << (wbit & 31));
+    }
+}
+
+// ---------------------------------------------------------------- walk
+__device__ __forceinline__ float fadd(float a, float b) { return __fadd_rn(a, b); }
+__device__ __forceinline__ float fmul(float a, float b) { return __fmul_rn(a, b); }
+
+struct AskCtx {
+    const float* x;
+    int64_t n;
+    const float* pre;  // shared memory copy
+    const float* car;  // global
+    int lane;
+    // exact EMA chain: `p` is the power after sample cpos - 1 (0 before the first sample)
+    int64_t cpos;
+    float p;
+    float* stage;  // 64 floats of shared memory per warp
+};
+
+// advance the EMA chain to `target` (power after sample target - 1)            ask.rs:696-697
+__device__ __noinline__ void chain_to(AskCtx& c, int64_t target) {
+    const float* __restrict__ x = c.x;
+    float p = c.p;
+    int64_t pos = c.cpos;
+    while (pos < target) {
+        const int64_t left = target - pos;
+        const int nstep = left < 32 ? int(left) : 32;
+        float v = c.lane < nstep ? x[pos + c.lane] : 0.0f;
+        v = fmul(fmul(v, v), kInv64);
+        __syncwarp();
+        c.stage[c.lane] = v;
+        __syncwarp();
+        if (nstep == 32) {
+#pragma unroll
+            for (int j = 0; j < 8; ++j) {
+                const float4 q = *reinterpret_cast<const float4*>(c.stage + 4 * j);
+                p = fadd(fmul(p, kC), q.x);
+                p = fadd(fmul(p, kC), q.y);
+                p = fadd(fmul(p, kC), q.z);
+                p = fadd(fmul(p, kC), q.w);
+            }
+        } else {
+            for (int j = 0; j < nstep; ++j) p = fadd(fmul(p, kC), c.stage[j]);
+        }
+        pos += nstep;
+    }
+    c.p = p;
+    c.cpos = target;
+}
+
+// exact sync_power and power of the 32 positions of word w (position 32 w + lane); `r` is where the FIFO
+// was last zeroed (samples before r read as zeros)                                 ask.rs:701-709
+__device__ __noinline__ void eval_word(AskCtx& c, int64_t w, int64_t r, float* sp_out, float* pw_out) {
+    const int64_t i = w * 32 + c.lane;
+    chain_to(c, w * 32);
+    // power after each of the next 32 samples, captured by the lane that owns the position
+    {
+        float v = i < c.n ? c.x[i] : 0.0f;
+        v = fmul(fmul(v, v), kInv64);
+        float p = c.p, mine = 0.0f;
+#pragma unroll
+        for (int j = 0; j < 32; ++j) {
+            p = fadd(fmul(p, kC), __shfl_sync(kFull, v, j));
+            if (j == c.lane) mine = p;
+        }
+        *pw_out = mine;
+        // the chain itself only advances over real samples
+        const int64_t lim = c.n - w * 32;
+        if (lim >= 32) {
+            c.p = p;
+            c.cpos = w * 32 + 32;
+        } else {
+            c.p = __shfl_sync(kFull, mine, int(lim > 0 ? lim - 1 : 0));
+            c.cpos = c.n;
+        }
+    }
+    float sum = 0.0f;
+    const int64_t first = i - (kPre - 1);  // sample index of tap 0
+    const float* __restrict__ x = c.x;
+#pragma unroll 4
+    for (int k = 0; k < kPre; ++k) {
+        const int64_t g = first + k;
+        if (g >= r && g >= 0 && i < c.n) sum = fadd(sum, fmul(x[g], c.pre[k]));
+    }
+    *sp_out = __fdiv_rn(sum, 200.0f);
+}
+
+// carrier mixing, 11-tap moving average, integrate and dump of the 108 bits      ask.rs:733-761
+__device__ __noinline__ void decode_frame(const AskCtx& c, int64_t s, uint8_t* bits14, uint32_t* id_out) {
+    uint32_t words[4];
+    for (int rnd = 0; rnd < 4; ++rnd) {
+        const int j = rnd * 32 + c.lane;
+        bool bit = false;
+        if (j < kBits) {
+            float tot = 0.0f;
+            for (int t = 0; t < 20; ++t) {
+                const int idx = 10 + j * TMK_ASK_SAMPLES_PER_BIT + t;
+                float sm = 0.0f;
+#pragma unroll
+                for (int k = idx - 5; k < idx + 6; ++k) {
+                    // decode_fifo[k]: rx[s+1 .. s+201) then rx[s+202 ..)  (the sample at s+201 is dropped)
+                    const float f = c.x[s + 1 + k + (k >= 200 ? 1 : 0)];
+                    sm = fadd(sm, fmul(f, c.car[k]));
+                }
+                tot = fadd(tot, __fdiv_rn(sm, 11.0f));
+            }
+            bit = tot > 0.0f;
+        }
+        words[rnd] = __brev(__ballot_sync(kFull, bit));  // bit j at the MSB side
+    }
+    if (c.lane < 14) bits14[c.lane] = uint8_t(words[c.lane >> 2] >> (24 - 8 * (c.lane & 3)));
+    *id_out = words[0] >> 24;
+}
+
+__global__ void __launch_bounds__(128)
+ask_walk_kernel(const float* __restrict__ samples, const AskStream* __restrict__ streams, uint32_t n_streams,
+                const float* __restrict__ tab, const uint32_t* __restrict__ wflag, tmk_ask_rec* __restrict__ recs,
+                uint64_t rec_cap, unsigned long long* __restrict__ counters) {
+    __shared__ __align__(16) float pre_s[kPre];
+    __shared__ __align__(16) float stage_s[4][64];
+    for (int i = threadIdx.x; i < kPre; i += blockDim.x) pre_s[i] = tab[i];
+    __syncthreads();
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    for (;;) {
+        uint32_t sidx = 0;
+        if (lane == 0) sidx = uint32_t(atomicAdd(&counters[1], 1ull));
+        sidx = __shfl_sync(kFull, sidx, 0);
+        if (sidx >= n_streams) return;
+        const AskStream sd = streams[sidx];
+        AskCtx c;
+        c.x = samples + sd.offset;
+        c.n = int64_t(sd.n);
+        c.pre = pre_s;
+        c.car = tab + kPre;
+        c.lane = lane;
+        c.cpos = 0;
+        c.p = 0.0f;
+        c.stage = stage_s[warp];
+        const int64_t nwords = (c.n + 31) / 32;
+        int64_t r = 0, cur = 0, start = 0;
+        float local_max = 0.0f;
+        bool done = false;
+        while (!done) {
+            // ---- next word to evaluate: everything inside the first 439 positions after the FIFO was zeroed
+            //      (partial windows are not covered by the filter), afterwards the flagged words only
+            int64_t w = cur >> 5;
+            if (cur >= r + (kPre - 1)) {
+                int64_t found = -1;
+                while (w < nwords && found < 0) {
+                    // 32 flag words = 1024 sample words per round
+                    const uint64_t b0 = sd.word_base + uint64_t(w);
+                    const uint64_t fw0 = b0 >> 5;
+                    const uint64_t lastbit = sd.word_base + uint64_t(nwords) - 1;
+                    uint32_t fl = 0;
+                    if (fw0 + lane <= (lastbit >> 5)) fl = wflag[fw0 + lane];
+                    if (lane == 0) fl &= ~0u << (b0 & 31);  // bits before w
+                    if (fw0 + lane == (lastbit >> 5) && (lastbit & 31) != 31) fl &= (2u << (lastbit & 31)) - 1u;  // next stream's bits
+                    const uint32_t m = __ballot_sync(kFull, fl != 0);
+                    if (m) {
+                        const int l = __ffs(m) - 1;
+                        const uint32_t f = __shfl_sync(kFull, fl, l);
+                        found = int64_t(((fw0 + l) << 5) + (__ffs(f) - 1) - sd.word_base);
+                    } else {
+                        w = int64_t(((fw0 + 32) << 5) - sd.word_base);
+                    }
+                }
+                w = found < 0 ? nwords : found;
+            }
+            // ---- a pending lock that comes before the next evaluated word            ask.rs:717-723
+            int64_t lock = -1;
+            if (start != 0 && start + 201 < (w < nwords ? w * 32 : c.n)) lock = start + 201;
+            if (lock < 0) {
+                if (w >= nwords) break;
+                float sp, pw;
+                eval_word(c, w, r, &sp, &pw);
+                const int64_t i = w * 32 + lane;
+                const bool cond0 = i >= cur && i < c.n && sp > fmul(pw, 2.0f) && sp > 0.05f;
+                uint32_t m = __ballot_sync(kFull, cond0);
+                const int64_t wend = (w * 32 + 32 < c.n) ? w * 32 + 32 : c.n;
+                while (m) {
+                    const int l = __ffs(m) - 1;
+                    m &= m - 1;
+                    const int64_t il = w * 32 + l;
+                    if (start != 0 && start + 201 < il) { lock = start + 201; break; }
+                    const float spl = __shfl_sync(kFull, sp, l);
+                    if (spl > local_max) {
+                        local_max = spl;
+                        start = il;
+                    } else if (start != 0 && il > start + 200) {
+                        lock = il;
+                        break;
+                    }
+                }
+                if (lock < 0 && start != 0 && start + 201 < wend) lock = start + 201;
+                if (lock < 0) {
+                    cur = w * 32 + 32;
+                    if (cur >= c.n) break;
+                    continue;
+                }
+            }
+            // ---- locked at `lock` (= start + 201): gather 4752 samples, decode     ask.rs:725-793
+            const int64_t s = start;
+            if (s + 2 + kFrame > c.n) break;  // the capture ends while the frame is being gathered
+            uint32_t id = 0;
+            unsigned long long slot = 0;
+            if (lane == 0) slot = atomicAdd(&counters[0], 1ull);
+            slot = __shfl_sync(kFull, slot, 0);
+            __shared__ uint8_t bits_s[4][16];
+            decode_frame(c, s, bits_s[warp], &id);
+            __syncwarp();
+            if (lane == 0 && slot < rec_cap) {
+                tmk_ask_rec rec;
+                memset(&rec, 0, sizeof rec);
+                rec.stream = sidx;
+                rec.accepted = (id > 0 && id <= 100) ? 1u : 0u;
+                rec.start_index = uint64_t(s);
+                rec.sync_power = local_max;
+                rec.id = uint8_t(id);
+                for (int b = 0; b < 14; ++b) rec.bits[b] = bits_s[warp][b];
+                recs[slot] = rec;
+            }
+            __syncwarp();
+            r = s + 2 + kFrame;  // first sample examined in state 0 again
+            cur = r;
+            start = 0;
+            local_max = 0.0f;
+            if (cur >= c.n) done = true;
+        }
+    }
+}
+
+void host_tables(std::vector<float>& tab, size_t n_carrier) {
+    // examples/ask.rs:574-605, f32 operation order
+    const float pi = 3.14159265358979323846f;
+    tab.assign(kPre + n_carrier, 0.0f);
+    float fp[kPre];
+    for (int i = 0; i < 220; ++i) fp[i] = 2000.0f + (8000.0f * float(i) / 219.0f);
+    for (int i = 0; i < 220; ++i) fp[220 + i] = 10000.0f - (8000.0f * float(i) / 219.0f);
+    float omega = 0.0f;
+    tab[0] = sinf(2.0f * pi * fp[0] * (0.0f / 48000.0f));
+    for (int i = 1; i < kPre; ++i) {
+        const float dt = float(i) / 48000.0f - float(i - 1) / 48000.0f;
+        omega += pi * (fp[i] + fp[i - 1]) * dt;
+        tab[i] = sinf(omega);
+    }
+    for (size_t k = 0; k < n_carrier; ++k) tab[kPre + k] = sinf(2.0f * pi * 10000.0f * (float(k) / 48000.0f));
+}
+
+int ensure_tables(tmk_engine* e) {
+    if (e->ask_ready) return TMK_OK;
+    std::vector<float> tab;
+    host_tables(tab, kFrame);
+    CK(e->d_ask_tab.reserve(tab.size() * sizeof(float)));
+    CK(cudaMemcpyAsync(e->d_ask_tab.p, tab.data(), tab.size() * sizeof(float), cudaMemcpyHostToDevice, e->stream));
+    CK(cudaStreamSynchronize(e->stream));
+    e->ask_ready = true;
+    return TMK_OK;
+}
+
+}  // namespace
+
+extern "C" {
+
+int tmk_ask_tables(tmk_engine* e, float* preamble440, float* carrier, uint64_t n_carrier) {
+    if (!e || !preamble440 || (!carrier && n_carrier)) return tmk_fail(e, TMK_E_INVALID, "tmk_ask_tables: null argument");
+    std::vector<float> tab;
+    host_tables(tab, size_t(n_carrier));
+    std::memcpy(preamble440, tab.data(), kPre * sizeof(float));
+    if (n_carrier) std::memcpy(carrier, tab.data() + kPre, size_t(n_carrier) * sizeof(float));
+    return TMK_OK;
+}
+
+uint64_t tmk_ask_modulated_len(uint32_t n_frames, const uint32_t* gap1, const uint32_t* gap2) {
+    uint64_t total = 0;
+    for (uint32_t f = 0; f < n_frames; ++f) total += uint64_t(gap1 ? gap1[f] : 0) + kPre + kFrame + (gap2 ? gap2[f] : 0);
+    return total;
+}
+
+int tmk_ask_modulate(tmk_engine* e, const uint8_t* bits, uint32_t n_frames, const uint32_t* gap1, const uint32_t* gap2,
+                     float* out_samples, uint64_t out_cap, uint64_t* out_len) {
+    if (!e || (!bits && n_frames) || !out_len || ((!gap1 || !gap2) && n_frames))
+        return tmk_fail(e, TMK_E_INVALID, "tmk_ask_modulate: null argument");
+    CK(cudaSetDevice(e->device));
+    std::vector<uint64_t> off(n_frames + 1, 0);
+    for (uint32_t f = 0; f < n_frames; ++f) off[f + 1] = off[f] + gap1[f] + kPre + kFrame + gap2[f];
+    const uint64_t total = off[n_frames];
+    *out_len = total;
+    if (total > out_cap) return tmk_fail(e, TMK_E_CAPACITY, "tmk_ask_modulate: output buffer too small");
+    if (total == 0) return TMK_OK;
+    if (!out_samples) return tmk_fail(e, TMK_E_INVALID, "tmk_ask_modulate: null output");
+    int rc = ensure_tables(e);
+    if (rc != TMK_OK) return rc;
+    const size_t ob = sizeof(uint64_t) * (n_frames + 1), gb = sizeof(uint32_t) * n_frames, bb = size_t(n_frames) * TMK_ASK_DATA_BITS;
+    CK(e->d_misc.reserve(ob + 2 * gb + bb + 64));
+    char* dm = static_cast<char*>(e->d_misc.p);
+    CK(cudaMemcpyAsync(dm, off.data(), ob, cudaMemcpyHostToDevice, e->stream));
+    CK(cudaMemcpyAsync(dm + ob, gap1, gb, cudaMemcpyHostToDevice, e->stream));
+    CK(cudaMemcpyAsync(dm + ob + gb, gap2, gb, cudaMemcpyHostToDevice, e->stream));
+    CK(cudaMemcpyAsync(dm + ob + 2 * gb, bits, bb, cudaMemcpyHostToDevice, e->stream));
+    float* d_out = out_samples;
+    const bool dev_out = tmk_is_device_ptr(out_samples);
+    if (!dev_out) {
+        CK(e->d_samples.reserve(total * sizeof(float)));
+        d_out = static_cast<float*>(e->d_samples.p);
+    }
+    ask_modulate_kernel<<<n_frames, 256, 0, e->stream>>>(static_cast<const float*>(e->d_ask_tab.p),
+                                                         reinterpret_cast<const uint8_t*>(dm + ob + 2 * gb),
+                                                         reinterpret_cast<const uint64_t*>(dm),
+                                                         reinterpret_cast<const uint32_t*>(dm + ob),
+                                                         reinterpret_cast<const uint32_t*>(dm + ob + gb), d_out);
+    e->launches += 1;
+    CK(cudaGetLastError());
+    if (!dev_out) CK(cudaMemcpyAsync(out_samples, d_out, total * sizeof(float), cudaMemcpyDeviceToHost, e->stream));
+    CK(cudaStreamSynchronize(e->stream));
+    return TMK_OK;
+}
+
+int tmk_ask_decode_batch(tmk_engine* e, const float* samples, uint64_t total_samples, const tmk_stream* streams,
+                         uint32_t n_streams, tmk_ask_rec* recs, uint64_t rec_cap, uint64_t* n_recs) {
+    if (!e || (!samples && total_samples) || (!streams && n_streams) || !n_recs || (!recs && rec_cap))
+        return tmk_fail(e, TMK_E_INVALID, "tmk_ask_decode_batch: null argument");
+    *n_recs = 0;
+    if (n_streams == 0) return TMK_OK;
+    CK(cudaSetDevice(e->device));
+    int rc = ensure_tables(e);
+    if (rc != TMK_OK) return rc;
+    std::vector<AskStream> sd(n_streams);
+    uint64_t words = 0, tiles = 0;
+    for (uint32_t s = 0; s < n_streams; ++s) {
+        if (streams[s].offset % 4 != 0) return tmk_fail(e, TMK_E_INVALID, "stream offset must be a multiple of 4 samples");
+        if (streams[s].offset > total_samples || streams[s].n_samples > total_samples - streams[s].offset)
+            return tmk_fail(e, TMK_E_INVALID, "stream " + std::to_string(s) + " exceeds the sample buffer");
+        sd[s].offset = streams[s].offset;
+        sd[s].n = streams[s].n_samples;
+        sd[s].word_base = words;
+        sd[s].tile_base = uint32_t(tiles);
+        sd[s].pad_ = 0;
+        words += (streams[s].n_samples + 31) / 32;
+        tiles += (streams[s].n_samples + kT - 1) / kT;
+        if (tiles > 0x7fffffffull) return tmk_fail(e, TMK_E_INVALID, "batch too large (tile count)");
+    }
+    const float* dx = samples;
+    if (total_samples && !tmk_is_device_ptr(samples)) {
+        CK(e->d_samples.reserve(total_samples * sizeof(float)));
+        CK(cudaMemcpyAsync(e->d_samples.p, samples, total_samples * sizeof(float), cudaMemcpyHostToDevice, e->stream));
+        dx = static_cast<const float*>(e->d_samples.p);
+    }
+    const size_t flag_words = size_t(words / 32 + 2);
+    CK(e->d_streams.reserve(sizeof(AskStream) * n_streams));
+    CK(e->d_ask_bits.reserve(flag_words * sizeof(uint32_t)));
+    CK(e->d_ask_l2.reserve(4 * sizeof(unsigned long long)));
+    uint64_t dev_cap = std::max<uint64_t>(1024, total_samples / 4096 + 2ull * n_streams);
+    CK(e->d_ask_recs.reserve(dev_cap * sizeof(tmk_ask_rec)));
+    CK(cudaMemcpyAsync(e->d_streams.p, sd.data(), sizeof(AskStream) * n_streams, cudaMemcpyHostToDevice, e->stream));
+    CK(cudaMemsetAsync(e->d_ask_bits.p, 0, flag_words * sizeof(uint32_t), e->stream));
+    CK(cudaMemsetAsync(e->d_ask_l2.p, 0, 4 * sizeof(unsigned long long), e->stream));
+    const AskStream* ds = static_cast<const AskStream*>(e->d_streams.p);
+    const float* tab = static_cast<const float*>(e->d_ask_tab.p);
+    CK(cudaEventRecord(e->ev[0], e->stream));
+    if (tiles) {
+        ask_scan_kernel<<<uint32_t(tiles), kThreads, 0, e->stream>>>(dx, ds, n_streams, tab, static_cast<uint32_t*>(e->d_ask_bits.p));
+        e->launches += 1;
+    }
+    CK(cudaGetLastError());
+    CK(cudaEventRecord(e->ev[1], e->stream));
+    static int walk_ctas = 0;
+    if (walk_ctas == 0) {
+        int sms = 0, per_sm = 0;
+        cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, e->device);
+        cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, ask_walk_kernel, 128, 0);
+        walk_ctas = sms * (per_sm > 0 ? per_sm : 1);
+    }
+    const uint32_t grid = std::min<uint32_t>((n_streams + 3) / 4, uint32_t(walk_ctas));
+    ask_walk_kernel<<<grid, 128, 0, e->stream>>>(dx, ds, n_streams, tab, static_cast<const uint32_t*>(e->d_ask_bits.p),
+                                                 static_cast<tmk_ask_rec*>(e->d_ask_recs.p), dev_cap,
+                                                 static_cast<unsigned long long*>(e->d_ask_l2.p));
+    e->launches += 1;
+    CK(cudaGetLastError());
+    CK(cudaEventRecord(e->ev[2], e->stream));
+    unsigned long long hc[2] = {0, 0};
+    CK(cudaMemcpyAsync(hc, e->d_ask_l2.p, sizeof hc, cudaMemcpyDeviceToHost, e->stream));
+    CK(cudaStreamSynchronize(e->stream));
+    cudaEventElapsedTime(&e->ask_ms[0], e->ev[0], e->ev[1]);
+    cudaEventElapsedTime(&e->ask_ms[1], e->ev[1], e->ev[2]);
+    *n_recs = hc[0];
+    if (hc[0] > dev_cap) return tmk_fail(e, TMK_E_CAPACITY, "tmk_ask_decode_batch: internal record scratch too small");
+    if (hc[0] > rec_cap) return tmk_fail(e, TMK_E_CAPACITY, "tmk_ask_decode_batch: record buffer too small");
+    if (hc[0]) {
+        CK(cudaMemcpyAsync(recs, e->d_ask_recs.p, hc[0] * sizeof(tmk_ask_rec), cudaMemcpyDeviceToHost, e->stream));
+        CK(cudaStreamSynchronize(e->stream));
+        // reference order: per capture, in time (the warps emit through an atomic slot counter)
+        std::sort(recs, recs + hc[0], [](const tmk_ask_rec& a, const tmk_ask_rec& b) {
+            return a.stream != b.stream ? a.stream < b.stream : a.start_index < b.start_index;
+        });
+    }
+    return TMK_OK;
+}
+
+int tmk_ask_last_stage_ms(tmk_engine* e, float ms[2]) {
+    if (!e || !ms) return TMK_E_INVALID;
+    ms[0] = e->ask_ms[0];
+    ms[1] = e->ask_ms[1];
+    return TMK_OK;
+}
+
+}  // extern "C"

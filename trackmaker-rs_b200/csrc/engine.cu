@@ -9,77 +9,12 @@
 #include <string>
 #include <vector>
 
-#include "tmk_internal.cuh"
+#include "engine.hpp"
 
 namespace {
 
-struct DevBuf {  // grow-only device scratch
-    void* p = nullptr;
-    size_t cap = 0;
-    cudaError_t reserve(size_t bytes) {
-        if (bytes <= cap) return cudaSuccess;
-        if (p) cudaFree(p);
-        p = nullptr;
-        cap = 0;
-        size_t want = bytes + bytes / 8 + 256;
-        cudaError_t e = cudaMalloc(&p, want);
-        if (e != cudaSuccess) {
-            e = cudaMalloc(&p, bytes);
-            want = bytes;
-        }
-        if (e == cudaSuccess) cap = want;
-        return e;
-    }
-    void release() {
-        if (p) cudaFree(p);
-        p = nullptr;
-        cap = 0;
-    }
-};
-
-}  // namespace
-
-struct tmk_engine {
-    int device = 0;
-    cudaStream_t stream = nullptr;
-    cudaStream_t copy_stream = nullptr;
-    cudaStream_t walk_stream = nullptr;
-    std::string err;
-    std::vector<TmkPattern> patterns;  // host mirror of the device pattern table
-    DevBuf d_tile_dir, d_patterns, d_streams, d_blk_info, d_cand, d_recs_tmp, d_rec_ord, d_recs, d_payload, d_cnt, d_base,
-        d_counters, d_samples, d_misc, d_misc2, d_next;
-    cudaEvent_t ev[6] = {};
-    cudaEvent_t tev[2] = {};
-    cudaEvent_t cev[6] = {};  // copy/compute hand-over of the chunked staging
-    float stage_ms[4] = {0, 0, 0, 0};
-    uint64_t launches = 0;
-    uint64_t stats[TMK_STAT_COUNT] = {};
-    uint64_t dbg[8] = {};
-};
-
-namespace {
-
-int fail(tmk_engine* e, int code, const std::string& msg) {
-    if (e) e->err = msg;
-    return code;
-}
-
-#define CK(call)                                                                                   \
-    do {                                                                                           \
-        cudaError_t _err = (call);                                                                 \
-        if (_err != cudaSuccess)                                                                   \
-            return fail(e, _err == cudaErrorMemoryAllocation ? TMK_E_NOMEM : TMK_E_CUDA,           \
-                        std::string(#call) + ": " + cudaGetErrorString(_err));                     \
-    } while (0)
-
-bool is_device_ptr(const void* p) {
-    cudaPointerAttributes a;
-    if (cudaPointerGetAttributes(&a, p) != cudaSuccess) {
-        cudaGetLastError();
-        return false;
-    }
-    return a.type == cudaMemoryTypeDevice || a.type == cudaMemoryTypeManaged;
-}
+int fail(tmk_engine* e, int code, const std::string& msg) { return tmk_fail(e, code, msg); }
+bool is_device_ptr(const void* p) { return tmk_is_device_ptr(p); }
 
 bool valid_cfg(const tmk_phy_config& c) {
     if (c.line_code != TMK_LINE_MANCHESTER && c.line_code != TMK_LINE_4B5B) return false;
@@ -248,7 +183,8 @@ void tmk_engine_destroy(tmk_engine* e) {
     if (e->stream) cudaStreamSynchronize(e->stream);
     DevBuf* bufs[] = {&e->d_tile_dir, &e->d_patterns, &e->d_streams, &e->d_blk_info, &e->d_cand, &e->d_recs_tmp, &e->d_rec_ord,
                       &e->d_recs, &e->d_payload, &e->d_cnt, &e->d_base, &e->d_counters, &e->d_samples,
-                      &e->d_misc, &e->d_misc2, &e->d_next};
+                      &e->d_misc, &e->d_misc2, &e->d_next, &e->d_ask_tab, &e->d_ask_bits, &e->d_ask_l2,
+                      &e->d_ask_recs, &e->d_ask_recs2};
     for (DevBuf* b : bufs) b->release();
     for (int i = 0; i < 6; ++i)
         if (e->ev[i]) cudaEventDestroy(e->ev[i]);

@@ -1,0 +1,74 @@
+// engine.hpp — the engine object behind the C ABI and the small host helpers shared by the
+// translation units that implement entry points (engine.cu, ask.cu).
+#pragma once
+#include <string>
+#include <vector>
+
+#include "tmk_internal.cuh"
+
+struct DevBuf {  // grow-only device scratch
+    void* p = nullptr;
+    size_t cap = 0;
+    cudaError_t reserve(size_t bytes) {
+        if (bytes <= cap) return cudaSuccess;
+        if (p) cudaFree(p);
+        p = nullptr;
+        cap = 0;
+        size_t want = bytes + bytes / 8 + 256;
+        cudaError_t e = cudaMalloc(&p, want);
+        if (e != cudaSuccess) {
+            e = cudaMalloc(&p, bytes);
+            want = bytes;
+        }
+        if (e == cudaSuccess) cap = want;
+        return e;
+    }
+    void release() {
+        if (p) cudaFree(p);
+        p = nullptr;
+        cap = 0;
+    }
+};
+
+struct tmk_engine {
+    int device = 0;
+    cudaStream_t stream = nullptr;
+    cudaStream_t copy_stream = nullptr;
+    cudaStream_t walk_stream = nullptr;
+    std::string err;
+    std::vector<TmkPattern> patterns;  // host mirror of the device pattern table
+    DevBuf d_tile_dir, d_patterns, d_streams, d_blk_info, d_cand, d_recs_tmp, d_rec_ord, d_recs, d_payload, d_cnt, d_base,
+        d_counters, d_samples, d_misc, d_misc2, d_next;
+    DevBuf d_ask_tab, d_ask_bits, d_ask_l2, d_ask_recs, d_ask_recs2;  // chirp+BPSK path (ask.cu)
+    bool ask_ready = false;
+    cudaEvent_t ev[6] = {};
+    cudaEvent_t tev[2] = {};
+    cudaEvent_t cev[6] = {};  // copy/compute hand-over of the chunked staging
+    float stage_ms[4] = {0, 0, 0, 0};
+    float ask_ms[2] = {0, 0};  // last tmk_ask_decode_batch: scan, walk
+    uint64_t launches = 0;
+    uint64_t stats[TMK_STAT_COUNT] = {};
+    uint64_t dbg[8] = {};
+};
+
+inline int tmk_fail(tmk_engine* e, int code, const std::string& msg) {
+    if (e) e->err = msg;
+    return code;
+}
+
+#define CK(call)                                                                                   \
+    do {                                                                                           \
+        cudaError_t _err = (call);                                                                 \
+        if (_err != cudaSuccess)                                                                   \
+            return tmk_fail(e, _err == cudaErrorMemoryAllocation ? TMK_E_NOMEM : TMK_E_CUDA,       \
+                            std::string(#call) + ": " + cudaGetErrorString(_err));                 \
+    } while (0)
+
+inline bool tmk_is_device_ptr(const void* p) {
+    cudaPointerAttributes a;
+    if (cudaPointerGetAttributes(&a, p) != cudaSuccess) {
+        cudaGetLastError();
+        return false;
+    }
+    return a.type == cudaMemoryTypeDevice || a.type == cudaMemoryTypeManaged;
+}

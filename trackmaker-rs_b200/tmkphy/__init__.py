@@ -175,6 +175,43 @@ class Engine:
         self._check(self._lib.tmk_debug_counters(self._h, c))
         return dict(zip(("blocks_examined", "reanchors", "replay_steps", "summary_groups"), [int(v) for v in c[:4]]))
 
+    # ---- chirp + BPSK modem of examples/ask.rs
+    def ask_tables(self, n_carrier=4752):
+        pre, car = np.zeros(440, np.float32), np.zeros(n_carrier, np.float32)
+        self._check(self._lib.tmk_ask_tables(self._h, _ptr(pre), _ptr(car), n_carrier))
+        return pre, car
+
+    def ask_modulate(self, bits, gap1, gap2):
+        """TX of examples/ask.rs:608-637. bits: (n_frames, 100) of 0/1; gaps: zeros before / after each frame."""
+        b = np.ascontiguousarray(bits, dtype=np.uint8).reshape(-1, 100)
+        g1 = np.ascontiguousarray(gap1, dtype=np.uint32)
+        g2 = np.ascontiguousarray(gap2, dtype=np.uint32)
+        n = int(self._lib.tmk_ask_modulated_len(len(b), _ptr(g1), _ptr(g2)))
+        out = np.zeros(max(n, 1), np.float32)
+        ln = C.c_uint64(0)
+        self._check(self._lib.tmk_ask_modulate(self._h, _ptr(b), len(b), _ptr(g1), _ptr(g2), _ptr(out), n, C.byref(ln)))
+        return out[:int(ln.value)]
+
+    def ask_decode_batch(self, samples, streams, rec_cap=None, total_samples=None):
+        """RX of examples/ask.rs:668-796 over a batch of captures -> ndarray[ASK_REC_DTYPE]"""
+        st = np.ascontiguousarray(streams, dtype=STREAM_DTYPE)
+        if isinstance(samples, np.ndarray):
+            s = np.ascontiguousarray(samples, dtype=np.float32)
+            sp, total = _ptr(s), s.size
+        else:
+            sp, total = C.c_void_p(int(samples)), int(total_samples)
+        tot = int(st["n_samples"].sum()) if len(st) else 0
+        rec_cap = int(rec_cap) if rec_cap is not None else max(64, tot // 4096 + 2 * len(st))
+        recs = np.zeros(rec_cap, _abi.ASK_REC_DTYPE)
+        n = C.c_uint64(0)
+        self._check(self._lib.tmk_ask_decode_batch(self._h, sp, total, _ptr(st), len(st), _ptr(recs), rec_cap, C.byref(n)))
+        return recs[:int(n.value)].copy()
+
+    def ask_last_stage_ms(self):
+        ms = (C.c_float * 2)()
+        self._check(self._lib.tmk_ask_last_stage_ms(self._h, ms))
+        return {"scan": ms[0], "walk": ms[1]}
+
     # ---- the path
     def modulate(self, cfg, frames, gap=INTER_FRAME_GAP_SAMPLES, out_device_ptr=None):
         """PhyEncoder::encode_frames. frames: list of Frame. Returns float32 samples (host)."""

@@ -57,7 +57,10 @@ REC_DTYPE = np.dtype([("stream", "<u4"), ("status", "<u4"), ("preamble_start", "
                       ("hdr_valid", "u1")])
 DESC_DTYPE = np.dtype([("payload_off", "<u8"), ("len", "<u4"), ("type", "u1"), ("seq", "u1"), ("src", "u1"),
                        ("dst", "u1")])
+ASK_REC_DTYPE = np.dtype([("stream", "<u4"), ("accepted", "<u4"), ("start_index", "<u8"), ("sync_power", "<f4"),
+                          ("id", "u1"), ("bits", "u1", (14,)), ("_pad", "u1", (5,))])
 assert STREAM_DTYPE.itemsize == 48 and REC_DTYPE.itemsize == 48 and DESC_DTYPE.itemsize == 16
+assert ASK_REC_DTYPE.itemsize == 40
 
 _vp, _u64, _u32, _i32 = C.c_void_p, C.c_uint64, C.c_uint32, C.c_int32
 _pu64 = C.POINTER(C.c_uint64)
@@ -94,6 +97,11 @@ SYMBOLS = {
     "tmk_timer_start": (C.c_int, [_vp]),
     "tmk_timer_stop": (C.c_int, [_vp, C.POINTER(C.c_float)]),
     "tmk_launch_count": (_u64, [_vp]),
+    "tmk_ask_tables": (C.c_int, [_vp, _vp, _vp, _u64]),
+    "tmk_ask_modulated_len": (_u64, [_u32, _vp, _vp]),
+    "tmk_ask_modulate": (C.c_int, [_vp, _vp, _u32, _vp, _vp, _vp, _u64, _pu64]),
+    "tmk_ask_decode_batch": (C.c_int, [_vp, _vp, _u64, _vp, _u32, _vp, _u64, _pu64]),
+    "tmk_ask_last_stage_ms": (C.c_int, [_vp, C.POINTER(C.c_float)]),
     "tmk_synth_batch": (C.c_int, [_vp, _pcfg, _u64, _u32, _u64, C.c_float, C.c_float, _vp, _vp, _u64, _pu64]),
 }
 
