@@ -760,7 +760,10 @@ __device__ __noinline__ void emit(const Ctx& c, Emit& em, uint32_t status, const
     em.ord++;
 }
 
-__global__ void __launch_bounds__(kWarpsPerCta * 32, 7)
+#ifndef TMK_WALK_CTAS
+#define TMK_WALK_CTAS 4  // measured at C2: 4 -> 11.7 ms, 5 -> 12.8, 6 -> 12.2, 7 -> 15.4 (spills in process_block)
+#endif
+__global__ void __launch_bounds__(kWarpsPerCta * 32, TMK_WALK_CTAS)
 walk_kernel(const float* __restrict__ samples, const TmkStreamDev* __restrict__ streams, uint32_t s0, uint32_t s1,
             unsigned int* __restrict__ next,
             const TmkPattern* __restrict__ patterns, const float4* __restrict__ blk_info,

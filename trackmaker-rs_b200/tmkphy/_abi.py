@@ -106,7 +106,7 @@ SYMBOLS = {
 }
 
 PKG_DIR = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
-LIB_PATH = os.path.join(PKG_DIR, "libtmkphy.so")
+LIB_PATH = os.environ.get("TMKPHY_LIB") or os.path.join(PKG_DIR, "libtmkphy.so")
 
 _lib = None
 
