@@ -183,7 +183,8 @@ void tmk_engine_destroy(tmk_engine* e) {
     if (e->stream) cudaStreamSynchronize(e->stream);
     DevBuf* bufs[] = {&e->d_tile_dir, &e->d_patterns, &e->d_streams, &e->d_blk_info, &e->d_cand, &e->d_recs_tmp, &e->d_rec_ord,
                       &e->d_recs, &e->d_payload, &e->d_cnt, &e->d_base, &e->d_counters, &e->d_samples,
-                      &e->d_misc, &e->d_misc2, &e->d_next, &e->d_ask_tab, &e->d_ask_bits, &e->d_ask_l2,
+                      &e->d_misc, &e->d_misc2, &e->d_next, &e->d_cblk, &e->d_blk_ptr, &e->d_entries, &e->d_spec, &e->d_pool,
+                      &e->d_ask_tab, &e->d_ask_bits, &e->d_ask_l2,
                       &e->d_ask_recs, &e->d_ask_recs2};
     for (DevBuf* b : bufs) b->release();
     for (int i = 0; i < 6; ++i)
@@ -337,6 +338,15 @@ int tmk_decode_batch(tmk_engine* e, const float* samples, uint64_t total_samples
     CK(e->d_cnt.reserve(sizeof(uint32_t) * n_streams));
     CK(e->d_base.reserve(sizeof(uint64_t) * (n_streams + 1)));
     CK(e->d_next.reserve(sizeof(unsigned int) * (chunks.size() + 1)));
+    // cluster pass (walk.cu): candidate entries + speculative verdicts, per chunk its own list region / counter
+    const bool use_fast = b.n_blocks > 0 && b.n_blocks < (1ull << 31) && !getenv("TMK_NO_CLUSTER");
+    const uint64_t entry_cap = std::min<uint64_t>((1ull << 27) - 1, b.n_blocks / 2 + 4096);
+    if (use_fast) {
+        CK(e->d_cblk.reserve(sizeof(uint32_t) * b.n_blocks));
+        CK(e->d_blk_ptr.reserve(sizeof(uint32_t) * b.n_blocks));
+        CK(e->d_entries.reserve(sizeof(TmkCandEntry) * entry_cap));
+        CK(e->d_pool.reserve(sizeof(unsigned int) * (2 + chunks.size())));
+    }
 
     const TmkStreamDev* ds = static_cast<const TmkStreamDev*>(e->d_streams.p);
     const TmkPattern* dp = static_cast<const TmkPattern*>(e->d_patterns.p);
@@ -357,12 +367,30 @@ int tmk_decode_batch(tmk_engine* e, const float* samples, uint64_t total_samples
     CK(e->d_recs_tmp.reserve(sizeof(tmk_frame_rec) * std::max<uint64_t>(1, dev_rec_cap)));
     CK(e->d_rec_ord.reserve(sizeof(uint32_t) * std::max<uint64_t>(1, dev_rec_cap)));
     if (!pay_dev) CK(e->d_payload.reserve(std::max<uint64_t>(1, dev_pay_cap)));
+    uint64_t spec_cap = std::min<uint64_t>(0x7fffffffull, 2 * dev_rec_cap + 1024);
+    if (use_fast) CK(e->d_spec.reserve(sizeof(tmk_frame_rec) * spec_cap));
+    auto fast_of = [&](size_t g, const Chunk& ch) {
+        TmkFast f;
+        std::memset(&f, 0, sizeof f);
+        if (!use_fast) return f;
+        unsigned int* pool = static_cast<unsigned int*>(e->d_pool.p);
+        f.cblk_list = static_cast<uint32_t*>(e->d_cblk.p) + uint64_t(ch.t0) * TMK_TILE_BLKS;
+        f.cblk_count = pool + 2 + g;
+        f.blk_ptr = static_cast<uint32_t*>(e->d_blk_ptr.p);
+        f.entries = static_cast<TmkCandEntry*>(e->d_entries.p);
+        f.entry_cap = uint32_t(entry_cap);
+        f.spec = static_cast<tmk_frame_rec*>(e->d_spec.p);
+        f.spec_cap = uint32_t(spec_cap);
+        f.pool = pool;
+        return f;
+    };
 
     CK(cudaEventRecord(e->ev[1], e->stream));
     e->launches += tmk_launch_tile_dir(ds, n_streams, uint32_t(b.n_tiles), dtd, e->stream);
     CK(cudaMemsetAsync(dcb, 0, sizeof(uint32_t) * TMK_BLK_WORDS * b.n_blocks, e->stream));
     CK(cudaMemsetAsync(dc, 0, sizeof(TmkCounters), e->stream));
     CK(cudaMemsetAsync(dnext, 0, sizeof(unsigned int) * (chunks.size() + 1), e->stream));
+    if (use_fast) CK(cudaMemsetAsync(e->d_pool.p, 0, sizeof(unsigned int) * (2 + chunks.size()), e->stream));
     if (host_samples) {
         // the copy stream may only overwrite the staging buffer once earlier work on it is done
         CK(cudaEventRecord(e->cev[0], e->stream));
@@ -377,8 +405,9 @@ int tmk_decode_batch(tmk_engine* e, const float* samples, uint64_t total_samples
             CK(cudaEventRecord(ce, e->copy_stream));
             CK(cudaStreamWaitEvent(e->stream, ce, 0));
         }
+        const TmkFast fast = fast_of(g, ch);
         e->launches += tmk_launch_scan(dx, total_samples, ds, n_streams, dtd, ch.t0, ch.t1 - ch.t0, dp, b.kinds, dbi, dcb,
-                                       e->stream);
+                                       const_cast<uint32_t*>(fast.cblk_list), fast.cblk_count, e->stream);
         if (chunks.size() == 1) CK(cudaEventRecord(e->ev[2], e->stream));
         uint8_t* dpay = pay_dev ? payload : static_cast<uint8_t*>(e->d_payload.p);
         // A walk is a latency-bound serial chain per stream (milliseconds whatever the number of streams), so
@@ -389,7 +418,9 @@ int tmk_decode_batch(tmk_engine* e, const float* samples, uint64_t total_samples
             CK(cudaEventRecord(se, e->stream));
             CK(cudaStreamWaitEvent(ws, se, 0));
         }
-        e->launches += tmk_launch_walk(dx, ds, ch.s0, ch.s1, dnext + g, dp, dbi, dcb,
+        if (use_fast)
+            e->launches += tmk_launch_cluster(dx, ds, dtd, dp, dbi, dcb, fast, dpay, dev_pay_cap, dc, ws);
+        e->launches += tmk_launch_walk(dx, ds, ch.s0, ch.s1, dnext + g, fast, dp, dbi, dcb,
                                        static_cast<tmk_frame_rec*>(e->d_recs_tmp.p), static_cast<uint32_t*>(e->d_rec_ord.p),
                                        dev_rec_cap, dpay, dev_pay_cap, static_cast<uint32_t*>(e->d_cnt.p), dc, ws);
         CK(cudaGetLastError());
@@ -415,7 +446,11 @@ int tmk_decode_batch(tmk_engine* e, const float* samples, uint64_t total_samples
         uint8_t* dpay = pay_dev ? payload : static_cast<uint8_t*>(e->d_payload.p);
         CK(cudaMemsetAsync(dc, 0, sizeof(TmkCounters), e->stream));
         CK(cudaMemsetAsync(dnext + chunks.size(), 0, sizeof(unsigned int), e->stream));
-        e->launches += tmk_launch_walk(dx, ds, 0, n_streams, dnext + chunks.size(), dp, dbi, dcb,
+        // the speculative verdicts of the cluster pass point into the payload scratch that was just re-sized:
+        // this (rare) second pass lets the walk evaluate everything itself
+        TmkFast nofast;
+        std::memset(&nofast, 0, sizeof nofast);
+        e->launches += tmk_launch_walk(dx, ds, 0, n_streams, dnext + chunks.size(), nofast, dp, dbi, dcb,
                                        static_cast<tmk_frame_rec*>(e->d_recs_tmp.p), static_cast<uint32_t*>(e->d_rec_ord.p),
                                        dev_rec_cap, dpay, dev_pay_cap, static_cast<uint32_t*>(e->d_cnt.p), dc, e->stream);
         CK(cudaGetLastError());
@@ -512,7 +547,8 @@ int tmk_scan_probe(tmk_engine* e, const float* samples, uint64_t total_samples, 
     e->launches += tmk_launch_tile_dir(ds, n_streams, uint32_t(b.n_tiles), dtd, e->stream);
     e->launches += tmk_launch_scan(static_cast<const float*>(d_samples), total_samples, ds, n_streams, dtd, 0,
                                    uint32_t(b.n_tiles), static_cast<const TmkPattern*>(e->d_patterns.p), b.kinds,
-                                   static_cast<float4*>(e->d_blk_info.p), static_cast<uint32_t*>(e->d_cand.p), e->stream);
+                                   static_cast<float4*>(e->d_blk_info.p), static_cast<uint32_t*>(e->d_cand.p), nullptr, nullptr,
+                                   e->stream);
     CK(cudaGetLastError());
     CK(cudaMemcpyAsync(blk_info, e->d_blk_info.p, sizeof(float4) * b.n_blocks, cudaMemcpyDeviceToHost, e->stream));
     CK(cudaMemcpyAsync(cand_bits, e->d_cand.p, sizeof(uint32_t) * TMK_BLK_WORDS * b.n_blocks, cudaMemcpyDeviceToHost, e->stream));

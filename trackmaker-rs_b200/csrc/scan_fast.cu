@@ -267,7 +267,8 @@ template <int LC>
 __global__ void __launch_bounds__(Shape<LC>::kWarps * 32, 2)
 scan_fast_kernel(const float* __restrict__ samples, uint64_t total_samples, const TmkStreamDev* __restrict__ streams,
                  const uint32_t* __restrict__ tile_stream, uint32_t tile0, uint32_t n_tiles,
-                 const TmkPattern* __restrict__ patterns, float4* __restrict__ blk_info, uint32_t* __restrict__ cand_bits) {
+                 const TmkPattern* __restrict__ patterns, float4* __restrict__ blk_info, uint32_t* __restrict__ cand_bits,
+                 uint32_t* __restrict__ cblk_list, unsigned int* __restrict__ cblk_count) {
     using Sh = Shape<LC>;
     extern __shared__ __align__(128) float smem[];
     __shared__ __align__(8) uint64_t mbar[kMaxWarps];
@@ -334,8 +335,10 @@ scan_fast_kernel(const float* __restrict__ samples, uint64_t total_samples, cons
             o.rmax = fmaxf(o.rmax, __shfl_xor_sync(kFull, o.rmax, s));
             ncf += __shfl_xor_sync(kFull, ncf, s);
         }
-        if ((lane & 3) == 0 && w0 + uint64_t(lane >> 2) * TMK_BLK < nwin)
+        if ((lane & 3) == 0 && w0 + uint64_t(lane >> 2) * TMK_BLK < nwin) {
             blk_info[blk0 + (lane >> 2)] = make_float4(o.emin, o.emax, o.rmax * (1.0f / float(Sh::P)), ncf);
+            if (ncf > 0.f && cblk_list) cblk_list[atomicAdd(cblk_count, 1u)] = uint32_t(blk0 + (lane >> 2));
+        }
         __syncwarp();
     }
 }
@@ -357,7 +360,8 @@ __global__ void tile_dir_kernel(const TmkStreamDev* __restrict__ streams, uint32
 
 template <int LC>
 void launch_fast(const float* samples, uint64_t total_samples, const TmkStreamDev* streams, const uint32_t* tile_stream,
-                 uint32_t tile0, uint32_t n_tiles, const TmkPattern* patterns, float4* blk_info, uint32_t* cand_bits, cudaStream_t st) {
+                 uint32_t tile0, uint32_t n_tiles, const TmkPattern* patterns, float4* blk_info, uint32_t* cand_bits,
+                 uint32_t* cblk_list, unsigned int* cblk_count, cudaStream_t st) {
     static int grid_cap = 0;
     constexpr int kWarps = Shape<LC>::kWarps;
     const size_t smem = size_t(kWarps) * 32 * Shape<LC>::kRow * sizeof(float);
@@ -372,7 +376,7 @@ void launch_fast(const float* samples, uint64_t total_samples, const TmkStreamDe
     uint32_t grid = (n_tiles + kWarps - 1) / kWarps;
     if (grid > uint32_t(grid_cap)) grid = uint32_t(grid_cap);
     scan_fast_kernel<LC><<<grid, kWarps * 32, smem, st>>>(samples, total_samples, streams, tile_stream, tile0, n_tiles,
-                                                        patterns, blk_info, cand_bits);
+                                                        patterns, blk_info, cand_bits, cblk_list, cblk_count);
 }
 
 }  // namespace
@@ -387,18 +391,21 @@ int tmk_launch_tile_dir(const TmkStreamDev* streams, uint32_t n_streams, uint32_
 // kinds: bit 0 = some stream is 4B5B/3/2, bit 1 = Manchester/3/2, bit 2 = any other shape (generic kernel)
 int tmk_launch_scan(const float* samples, uint64_t total_samples, const TmkStreamDev* streams, uint32_t n_streams,
                     const uint32_t* tile_stream, uint32_t tile0, uint32_t n_tiles, const TmkPattern* patterns,
-                    uint32_t kinds, float4* blk_info, uint32_t* cand_bits, cudaStream_t st) {
+                    uint32_t kinds, float4* blk_info, uint32_t* cand_bits, uint32_t* cblk_list, unsigned int* cblk_count,
+                    cudaStream_t st) {
     if (n_tiles == 0) return 0;
     int launches = 0;
     if (kinds & 1u) {
-        launch_fast<TMK_LINE_4B5B>(samples, total_samples, streams, tile_stream, tile0, n_tiles, patterns, blk_info, cand_bits, st);
+        launch_fast<TMK_LINE_4B5B>(samples, total_samples, streams, tile_stream, tile0, n_tiles, patterns, blk_info, cand_bits,
+                                   cblk_list, cblk_count, st);
         ++launches;
     }
     if (kinds & 2u) {
         launch_fast<TMK_LINE_MANCHESTER>(samples, total_samples, streams, tile_stream, tile0, n_tiles, patterns, blk_info,
-                                         cand_bits, st);
+                                         cand_bits, cblk_list, cblk_count, st);
         ++launches;
     }
-    if (kinds & 4u) launches += tmk_launch_scan_generic(samples, streams, tile_stream, tile0, n_tiles, patterns, blk_info, cand_bits, st);
+    if (kinds & 4u) launches += tmk_launch_scan_generic(samples, streams, tile_stream, tile0, n_tiles, patterns, blk_info, cand_bits,
+                                                            cblk_list, cblk_count, st);
     return launches;
 }

@@ -19,7 +19,8 @@ constexpr int kSmemX = TMK_TILE + TMK_MAX_P + 8;
 __global__ void __launch_bounds__(kThreads)
 scan_generic_kernel(const float* __restrict__ samples, const TmkStreamDev* __restrict__ streams,
                     const uint32_t* __restrict__ tile_stream, uint32_t tile0, const TmkPattern* __restrict__ patterns,
-                    float4* __restrict__ blk_info, uint32_t* __restrict__ cand_bits) {
+                    float4* __restrict__ blk_info, uint32_t* __restrict__ cand_bits, uint32_t* __restrict__ cblk_list,
+                    unsigned int* __restrict__ cblk_count) {
     __shared__ float xs[kSmemX];   // raw samples, then box sums of spl samples
     __shared__ float qs[kSmemX];   // box sums of spl squared samples
     __shared__ float lev[TMK_MAX_LEVELS];
@@ -111,7 +112,10 @@ scan_generic_kernel(const float* __restrict__ samples, const TmkStreamDev* __res
     if (blk_in_stream * TMK_BLK < nwin) {
         const uint64_t gb = sd.blk_base + blk_in_stream;
         if (lane < TMK_BLK_WORDS) cand_bits[gb * TMK_BLK_WORDS + lane] = myword;
-        if (lane == 0) blk_info[gb] = make_float4(emin, emax, dmax, float(ncand));
+        if (lane == 0) {
+            blk_info[gb] = make_float4(emin, emax, dmax, float(ncand));
+            if (ncand && cblk_list) cblk_list[atomicAdd(cblk_count, 1u)] = uint32_t(gb);  // blocks with candidates
+        }
     }
 }
 
@@ -119,8 +123,10 @@ scan_generic_kernel(const float* __restrict__ samples, const TmkStreamDev* __res
 
 int tmk_launch_scan_generic(const float* samples, const TmkStreamDev* streams, const uint32_t* tile_stream,
                             uint32_t tile0, uint32_t n_tiles, const TmkPattern* patterns, float4* blk_info, uint32_t* cand_bits,
+                            uint32_t* cblk_list, unsigned int* cblk_count,
                             cudaStream_t st) {
     if (n_tiles == 0) return 0;
-    scan_generic_kernel<<<n_tiles, kThreads, 0, st>>>(samples, streams, tile_stream, tile0, patterns, blk_info, cand_bits);
+    scan_generic_kernel<<<n_tiles, kThreads, 0, st>>>(samples, streams, tile_stream, tile0, patterns, blk_info, cand_bits, cblk_list,
+                                                            cblk_count);
     return 1;
 }

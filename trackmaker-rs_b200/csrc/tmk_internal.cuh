@@ -63,6 +63,26 @@ struct TmkCounters {
     unsigned long long dbg[8];  // walk diagnostics (tmk_debug_counters)
 };
 
+// ---- cluster pass (walk.cu): per-candidate results computed in parallel before the per-stream walk
+struct TmkCandEntry {  // one candidate window of a block, in window order
+    uint16_t wl;       // window offset inside the block
+    uint16_t flags;
+    float D;           // exact AVX-order dot product   (decoder.rs:381-417)
+    float Ec;          // accurately summed window energy
+    uint32_t spec;     // speculative frame record of a detection at this window, or TMK_ENT_INVALID
+};
+#define TMK_ENT_INVALID 0xffffffffu
+struct TmkFast {
+    const uint32_t* cblk_list;       // global ids of the blocks with candidates (appended by the scan kernels)
+    unsigned int* cblk_count;
+    uint32_t* blk_ptr;               // per global block: (first entry << 5) | count, or TMK_ENT_INVALID
+    TmkCandEntry* entries;
+    uint32_t entry_cap;
+    tmk_frame_rec* spec;             // speculative verdict records (payload already in the payload buffer)
+    uint32_t spec_cap;
+    unsigned int* pool;              // [0] entries used, [1] spec records used
+};
+
 __host__ __device__ inline uint64_t tmk_sfb(int line_code, uint32_t spl, uint64_t nbits) {
     // LineCode::samples_for_bits  line_coding.rs:125-127 (Manchester), :295-300 (4B5B)
     return line_code == TMK_LINE_MANCHESTER ? nbits * spl * 2 : ((nbits + 3) / 4) * 5 * spl;
@@ -109,12 +129,18 @@ int tmk_launch_tile_dir(const TmkStreamDev* streams, uint32_t n_streams, uint32_
 // kinds: bit 0 = 4B5B/spl 3/2 bytes streams present, bit 1 = Manchester/3/2, bit 2 = any other shape
 int tmk_launch_scan(const float* samples, uint64_t total_samples, const TmkStreamDev* streams, uint32_t n_streams,
                     const uint32_t* tile_stream, uint32_t tile0, uint32_t n_tiles, const TmkPattern* patterns,
-                    uint32_t kinds, float4* blk_info, uint32_t* cand_bits, cudaStream_t st);
+                    uint32_t kinds, float4* blk_info, uint32_t* cand_bits, uint32_t* cblk_list, unsigned int* cblk_count,
+                    cudaStream_t st);  // cblk_list / cblk_count (nullable): global ids of the blocks with candidates
 int tmk_launch_scan_generic(const float* samples, const TmkStreamDev* streams, const uint32_t* tile_stream,
                             uint32_t tile0, uint32_t n_tiles, const TmkPattern* patterns, float4* blk_info,
-                            uint32_t* cand_bits, cudaStream_t st);
+                            uint32_t* cand_bits, uint32_t* cblk_list, unsigned int* cblk_count, cudaStream_t st);
 // walks streams [s0, s1); `next` is a zeroed work counter owned by this launch
+// cluster pass over the blocks listed in f.cblk_list (one-shot streams; others are marked invalid)
+int tmk_launch_cluster(const float* samples, const TmkStreamDev* streams, const uint32_t* tile_stream,
+                       const TmkPattern* patterns, const float4* blk_info, const uint32_t* cand_bits, TmkFast f,
+                       uint8_t* payload, uint64_t payload_cap, TmkCounters* counters, cudaStream_t st);
 int tmk_launch_walk(const float* samples, const TmkStreamDev* streams, uint32_t s0, uint32_t s1, unsigned int* next,
+                    TmkFast fast,
                     const TmkPattern* patterns, const float4* blk_info, const uint32_t* cand_bits,
                     tmk_frame_rec* recs, uint32_t* rec_ord, uint64_t rec_cap, uint8_t* payload,
                     uint64_t payload_cap, uint32_t* stream_cnt, TmkCounters* counters, cudaStream_t st);

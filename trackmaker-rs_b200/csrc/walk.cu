@@ -48,6 +48,9 @@ struct Ctx {
     const TmkPattern* pat;
     const float4* blk_info;
     const uint32_t* cand_bits;
+    const uint32_t* blk_ptr;         // cluster pass results of this stream's blocks (nullptr: none)
+    const TmkCandEntry* entries;
+    const tmk_frame_rec* spec;
     uint64_t nblk;
     float thr;
     int32_t local_addr;
@@ -63,6 +66,11 @@ struct Ctx {
     // right after a search entry; a measured value after an exact re-anchoring)
     uint64_t a_seed, a_w;
     float a_err;
+    // sum form of the drift bound, valid while the anchor is the seed of a one-shot search (see fast_block):
+    // bound on the sum of the chain's window energies before the block handed to process_block, and on
+    // the energy of the seed window
+    float racc_in, efirst;
+    bool sum_ok;
     // stats
     uint32_t n_replays, n_cands, n_det;
     // diagnostics: [0] process_block calls, [1] re-anchors, [2] replay steps, [3] blk_info groups
@@ -179,9 +187,15 @@ __device__ __noinline__ float exact_energy(Ctx& c, uint64_t seed, uint64_t w) {
                 const float4* b4 = reinterpret_cast<const float4*>(sb + g * 32);
                 const float e0 = e;
                 float mn = e;
+                float4 av[8], bv[8];  // all 16 broadcast loads of the batch in flight before the dependent chain
 #pragma unroll
                 for (int j = 0; j < 8; ++j) {
-                    const float4 a = a4[j], b = b4[j];
+                    av[j] = a4[j];
+                    bv[j] = b4[j];
+                }
+#pragma unroll
+                for (int j = 0; j < 8; ++j) {
+                    const float4 a = av[j], b = bv[j];
                     e = ex_add(ex_sub(e, a.x), b.x); mn = fminf(mn, e);
                     e = ex_add(ex_sub(e, a.y), b.y); mn = fminf(mn, e);
                     e = ex_add(ex_sub(e, a.z), b.z); mn = fminf(mn, e);
@@ -288,6 +302,7 @@ struct Detection {
     uint64_t seed;   // where the search that found it was entered (search area start)
     uint64_t avail;  // samples buffered at that time
     float corr;      // reference correlation value of the detecting window
+    uint32_t spec;   // speculative verdict record of the cluster pass for this window, or TMK_ENT_INVALID
 };
 
 // Exact evaluation of window w (literal reference arithmetic). All lanes, uniform arguments.
@@ -298,27 +313,16 @@ __device__ bool exact_window(Ctx& c, uint64_t w, uint64_t seed, float D, float* 
     return corr >= c.thr;
 }
 
-// Examine the windows of block `bb` that are >= q, in order. `prevmax` bounds the window energies
-// of the chain between the anchor and this block; *pm_out receives the bound including this block.
-// Returns true with *det filled on a detection.
-__device__ __noinline__ bool process_block(Ctx& c, uint64_t bb, uint64_t q, uint64_t avail, float prevmax, Detection* det,
-                              float* pm_out) {
+// Prefix sums of the rounded squares of block `bb` in double: E_c(w) = Q[w+P] - Q[w]  (P <= 255).
+// Every lane owns K consecutive samples, fetched as float4s that are all in flight together (one HBM
+// round trip for the block), summed serially per lane, then one warp scan of the 32 lane totals.
+__device__ __noinline__ void block_prefix(Ctx& c, uint64_t bb) {
     const int lane = c.lane;
     const uint32_t P = c.P;
     const uint64_t wb0 = bb * TMK_BLK;
-    c.dbg[0]++;
     const float* __restrict__ x = c.x;
-    const float silent = 0.5f * c.thr * c.thr * 1e-6f;
-    // neighbourhood maximum for the scan kernel's own approximation error
-    float nb = c.blk_info[bb].y;
-    if (bb > 0) nb = max_nan(nb, c.blk_info[bb - 1].y);
-    if (bb + 1 < c.nblk) nb = max_nan(nb, c.blk_info[bb + 1].y);
-    const float dscan = 128.f * kU * nb;
+    {
 
-    // the block's candidate words: lane r holds word r (one load round instead of 15)
-    const uint32_t myword = lane < TMK_BLK_WORDS ? c.cand_bits[bb * TMK_BLK_WORDS + lane] : 0u;
-    const bool fast = P <= 255;
-    if (fast) {
         // prefix sums of the rounded squares in double: E_c(w) = Q[w+P] - Q[w].
         // Every lane owns K consecutive samples, fetched as float4s that are all in flight together
         // (one HBM round trip for the block), summed serially per lane, then one warp scan of the
@@ -371,7 +375,31 @@ __device__ __noinline__ bool process_block(Ctx& c, uint64_t bb, uint64_t q, uint
         }
         __syncwarp();
     }
+}
+
+// Examine the windows of block `bb` that are >= q, in order. `prevmax` bounds the window energies
+// of the chain between the anchor and this block; *pm_out receives the bound including this block.
+// Returns true with *det filled on a detection.
+__device__ __noinline__ bool process_block(Ctx& c, uint64_t bb, uint64_t q, uint64_t avail, float prevmax, Detection* det,
+                              float* pm_out) {
+    const int lane = c.lane;
+    const uint32_t P = c.P;
+    const uint64_t wb0 = bb * TMK_BLK;
+    c.dbg[0]++;
+    const float* __restrict__ x = c.x;
+    const float silent = 0.5f * c.thr * c.thr * 1e-6f;
+    // neighbourhood maximum for the scan kernel's own approximation error
+    float nb = c.blk_info[bb].y;
+    if (bb > 0) nb = max_nan(nb, c.blk_info[bb - 1].y);
+    if (bb + 1 < c.nblk) nb = max_nan(nb, c.blk_info[bb + 1].y);
+    const float dscan = 128.f * kU * nb;
+
+    // the block's candidate words: lane r holds word r (one load round instead of 15)
+    const uint32_t myword = lane < TMK_BLK_WORDS ? c.cand_bits[bb * TMK_BLK_WORDS + lane] : 0u;
+    const bool fast = P <= 255;
+    if (fast) block_prefix(c, bb);
     float pmcarry = prevmax * 1.001f;  // block maxima come from the approximate scan
+    float sumcarry = c.racc_in;
 #pragma unroll 1
     for (uint32_t r = 0; r < TMK_BLK_WORDS; ++r) {
         const uint32_t wl = r * 32 + lane;
@@ -391,13 +419,28 @@ __device__ __noinline__ bool process_block(Ctx& c, uint64_t bb, uint64_t q, uint
         float pm = warp_incl_scan_maxnan(Ec, lane);
         pm = max_nan(pm, pmcarry);
         pmcarry = __shfl_sync(kFull, pm, 31);
+        // running SUM of the window energies (sum form of the drift bound)
+        float cs = valid ? Ec * 1.0001f : 0.f;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            const float t = __shfl_up_sync(kFull, cs, o);
+            if (lane >= o) cs += t;
+        }
+        cs += sumcarry;
+        sumcarry = __shfl_sync(kFull, cs, 31);
         uint64_t seed = q;
         float delta = 0.f;
         bool tight = false;
         if (valid) {
             seed = seed_for(c, w, q, avail);
             const bool same = seed == c.a_seed && w >= c.a_w;
-            delta = drift_bound(P, same ? w - c.a_w : w - seed, same ? c.a_err : 0.f, pm) + 2.5f * kU * Ec;
+            float db = drift_bound(P, same ? w - c.a_w : w - seed, same ? c.a_err : 0.f, pm);
+            if (c.sum_ok && same) {
+                const float kf = float(w - c.a_w);
+                const float growth = kf < 65536.f ? 1.01f : __expf(2.2f * kU * kf) * 1.01f;
+                db = fminf(db, kU * (1.5f * float(P) * c.efirst + 2.2f * cs) * growth);
+            }
+            delta = db + 2.5f * kU * Ec;
             tight = (delta + dscan) <= kTight * Ec;
         }
         const bool bit = (__shfl_sync(kFull, myword, int(r)) >> lane) & 1u;
@@ -434,12 +477,81 @@ __device__ __noinline__ bool process_block(Ctx& c, uint64_t bb, uint64_t q, uint
                 det->seed = sj;
                 det->avail = avail_for(c, wj, avail);
                 det->corr = corr;
+                det->spec = TMK_ENT_INVALID;
                 return true;
             }
         }
     }
     *pm_out = pmcarry;
     return false;
+}
+
+// Fast path of a block (one-shot captures, cluster pass available): when the drift bound at the END of
+// the block leaves every unmarked window provably below the threshold ("tight by summary"), only the
+// candidate entries the cluster pass prepared (exact dot, accurate energy) have to be decided.
+// Returns 0: no detection in the block, 1: detection (*det filled), 2: not applicable (caller falls back
+// to process_block).
+//   smax      bound on the window energies of the chain up to the end of this block (running maximum)
+//   racc_end  bound on the SUM of those window energies, efirst on the energy of the seed window:
+//             |E_ref - S| <= u (1.5 P S_seed + 2.2 sum_i S_i) is the same rounding argument as drift_bound()
+//             without replacing every term by the maximum, so a loud frame just before the seed does not
+//             loosen the bound of the quiet gap behind it
+//   emin_lo   lower bound of the window energies of the block's windows >= q
+__device__ __noinline__ int fast_block(Ctx& c, uint64_t bb, uint64_t q, float4 info, float nb, float smax, float racc_end,
+                                       float efirst, float emin_lo, Detection* det) {
+    if (c.blk_ptr == nullptr || c.C != 0 || c.P > 255 || c.a_w != c.a_seed || c.a_err != 0.f) return 2;
+    const float silent = 0.5f * c.thr * c.thr * 1e-6f;
+    if (info.y < silent) return 0;  // every window is gated or cannot reach the threshold (as in search())
+    const uint64_t wb0 = bb * TMK_BLK;
+    uint64_t wlast = wb0 + (TMK_BLK - 1);
+    if (wlast >= c.nwin) wlast = c.nwin - 1;
+    const uint64_t k_end = wlast - c.a_w;
+    const float dmax = drift_bound(c.P, k_end, 0.f, smax);
+    const float kf = float(k_end);
+    const float growth = kf < 65536.f ? 1.01f : __expf(2.2f * kU * kf) * 1.01f;
+    const float dsum = kU * (1.5f * float(c.P) * efirst + 2.2f * racc_end) * growth;
+    const float d_end = fminf(dmax, dsum);  // both are rigorous; NaN in either falls through below
+    const float dscan = 128.f * kU * nb;
+    if (!(d_end + dscan <= kTight * emin_lo) || !(d_end <= 3.0e38f) || !(dscan <= 3.0e38f)) return 2;
+    if (info.w == 0.f) return 0;
+    const uint32_t ptr = c.blk_ptr[bb];
+    if (ptr == TMK_ENT_INVALID) return 2;
+    const uint32_t n = ptr & 31u;
+    TmkCandEntry e;
+    e.wl = 0; e.flags = 0; e.D = 0.f; e.Ec = 0.f; e.spec = TMK_ENT_INVALID;
+    if (uint32_t(c.lane) < n) e = c.entries[(ptr >> 5) + c.lane];
+    const uint64_t w = wb0 + e.wl;
+    const bool valid = uint32_t(c.lane) < n && w >= q && w < c.nwin;
+    int dec = DEC_NO;
+    if (valid) dec = decide_interval(c, e.D, e.Ec, d_end + 2.5f * kU * e.Ec);
+    c.n_cands += __popc(__ballot_sync(kFull, valid));
+    uint32_t pend = __ballot_sync(kFull, dec != DEC_NO);
+    while (pend) {
+        const int j = __ffs(pend) - 1;
+        pend &= pend - 1;
+        const int dj = __shfl_sync(kFull, dec, j);
+        const uint64_t wj = __shfl_sync(kFull, w, j);
+        const float Dj = __shfl_sync(kFull, e.D, j);
+        const float Ecj = __shfl_sync(kFull, e.Ec, j);
+        const uint32_t sj = __shfl_sync(kFull, e.spec, j);
+        float corr;
+        bool hit;
+        if (dj == DEC_YES) {
+            corr = ex_corr(Dj, Ecj, c.pat->pe);
+            hit = true;
+        } else {
+            hit = exact_window(c, wj, q, Dj, &corr);
+        }
+        if (hit) {
+            det->c = wj;
+            det->seed = q;
+            det->avail = c.N;
+            det->corr = corr;
+            det->spec = sj;
+            return 1;
+        }
+    }
+    return 0;
 }
 
 // search_for_preamble over all future calls: first window >= q with corr_ref >= thr.
@@ -453,13 +565,66 @@ __device__ __noinline__ bool search(Ctx& c, uint64_t q, uint64_t avail, Detectio
     c.a_err = 0.f;
     float runmax = 0.f;  // bound on the window energies in (a_w, first window of the group)
     // the block that contains q is partial: its summary also covers windows before q (the frame that was
-    // just consumed, whose energy must not loosen the drift bounds of the gap behind it), so it is
-    // always examined window by window
+    // just consumed). The fast path bounds the drift by the SUM of the energies, which that frame does not
+    // enter; otherwise the block is examined window by window.
     uint64_t b0 = q / TMK_BLK;
-    if (process_block(c, b0, q, avail, 0.f, det, &runmax)) return true;
+    float racc = 0.f, efirst = 0.f;  // sum / seed-window bounds of the chain (see fast_block)
+    {
+        const float4 i0 = c.blk_info[b0];
+        float nb0 = i0.y;
+        if (b0 > 0) nb0 = max_nan(nb0, c.blk_info[b0 - 1].y);
+        if (b0 + 1 < c.nblk) nb0 = max_nan(nb0, c.blk_info[b0 + 1].y);
+        uint64_t wl0 = b0 * TMK_BLK + (TMK_BLK - 1);
+        if (wl0 >= c.nwin) wl0 = c.nwin - 1;
+        const float dscan0 = 128.f * kU * nb0;
+        // 1. summary only: every window >= q bounded by the block maximum (which the consumed frame may own)
+        efirst = i0.y * 1.001f;
+        racc = float(wl0 - q + 1) * i0.y * 1.001f;
+        // (a block with a strong contrast is the end of the consumed frame: its maximum would pollute the
+        // bounds of the whole gap behind it, so it goes straight to the exact energies)
+        int r = 2;
+        if (!(i0.y > 8.f * i0.x)) {
+            r = fast_block(c, b0, q, i0, nb0, i0.y * 1.001f, racc, efirst, i0.x - dscan0, det);
+            if (r == 1) return true;
+            if (r == 0) runmax = i0.y * 1.001f;
+        }
+        if (r == 2 && c.blk_ptr != nullptr && c.C == 0 && c.P <= 255) {
+            // 2. exact energies of the windows [q, end of block] (one block load): sum, maximum, minimum
+            block_prefix(c, b0);
+            const uint32_t lo = uint32_t(q - b0 * TMK_BLK), hi = uint32_t(wl0 - b0 * TMK_BLK);
+            float es = 0.f, emx = 0.f, emn = __int_as_float(0x7f800000), eq = 0.f;
+            for (uint32_t wl = lo + lane; wl <= hi; wl += 32) {
+                const float ec = __double2float_rn(c.sc->Q[wl + P] - c.sc->Q[wl]);
+                es += ec;
+                emx = max_nan(emx, ec);
+                emn = fminf(emn, ec);
+                if (wl == lo) eq = ec;
+            }
+#pragma unroll
+            for (int o = 16; o > 0; o >>= 1) {
+                es += __shfl_xor_sync(kFull, es, o);
+                emx = max_nan(emx, __shfl_xor_sync(kFull, emx, o));
+                emn = fminf(emn, __shfl_xor_sync(kFull, emn, o));
+            }
+            eq = __shfl_sync(kFull, eq, 0);
+            const float racc_x = es * 1.0001f;
+            r = fast_block(c, b0, q, i0, nb0, emx * 1.0001f, racc_x, eq * 1.0001f, emn * 0.9999f, det);
+            if (r == 1) return true;
+            if (r == 0) {
+                runmax = emx * 1.0001f;
+                racc = racc_x;
+                efirst = eq * 1.0001f;
+            }
+        }
+        c.sum_ok = c.C == 0;
+        c.efirst = efirst;
+        c.racc_in = 0.f;
+        if (r == 2 && process_block(c, b0, q, avail, 0.f, det, &runmax)) return true;
+    }
     ++b0;
     while (b0 < c.nblk) {
         c.dbg[3]++;
+        const bool sum_ok = c.C == 0 && c.a_w == c.a_seed && c.a_err == 0.f;
         const uint64_t bb = b0 + lane;
         const bool valid = bb < c.nblk;
         float4 info = make_float4(0.f, 0.f, 0.f, 0.f);
@@ -478,6 +643,19 @@ __device__ __noinline__ bool search(Ctx& c, uint64_t q, uint64_t avail, Detectio
         const float run = max_nan(runmax, incl);
         bool need = false, hist_loose = false;
         uint64_t wfirst = bb * TMK_BLK, s_first = q, kk = 0;
+        // sum of the window energies block by block (exclusive prefix over the lanes), for fast_block
+        float contrib = 0.f;
+        if (valid) {
+            uint64_t wl2 = wfirst + (TMK_BLK - 1);
+            if (wl2 >= c.nwin) wl2 = c.nwin - 1;
+            contrib = float(wl2 - wfirst + 1) * info.y * 1.001f;
+        }
+        float cincl = contrib;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            const float t = __shfl_up_sync(kFull, cincl, o);
+            if (lane >= o) cincl += t;
+        }
         if (valid) {
             uint64_t wlast = wfirst + (TMK_BLK - 1);
             if (wlast >= c.nwin) wlast = c.nwin - 1;
@@ -485,7 +663,14 @@ __device__ __noinline__ bool search(Ctx& c, uint64_t q, uint64_t avail, Detectio
             const bool same = s_first == c.a_seed;
             kk = wlast - (same ? c.a_w : s_first);
             const float e0 = same ? c.a_err : 0.f;
-            const float delta = drift_bound(P, kk, e0, run * 1.001f) + 128.f * kU * nb + 2.5f * kU * info.y;
+            float dbi = drift_bound(P, kk, e0, run * 1.001f), dbe = drift_bound(P, kk, e0, excl * 1.001f);
+            if (sum_ok && same) {
+                const float kf = float(kk);
+                const float growth = kf < 65536.f ? 1.01f : __expf(2.2f * kU * kf) * 1.01f;
+                dbi = fminf(dbi, kU * (1.5f * float(P) * efirst + 2.2f * (racc + cincl)) * growth);
+                dbe = fminf(dbe, kU * (1.5f * float(P) * efirst + 2.2f * (racc + cincl - contrib)) * growth);
+            }
+            const float delta = dbi + 128.f * kU * nb + 2.5f * kU * info.y;
             // (1) no window of the block can reach the threshold even with the lowest possible E_ref:
             //     corr_ref^2 = corr_true^2 * S / E_ref  with  E_ref >= max(S - delta, 1e-6)
             float gain;  // upper bound of S / E_ref over the block
@@ -496,15 +681,36 @@ __device__ __noinline__ bool search(Ctx& c, uint64_t q, uint64_t avail, Detectio
             const bool is_silent = info.y < silent;
             need = !is_silent && (any || !safe);
             // (2) is the drift accumulated BEFORE this block what makes its windows undecidable?
-            hist_loose = drift_bound(P, kk, e0, excl * 1.001f) > 0.25f * kTight * info.x;
+            hist_loose = dbe > 0.25f * kTight * info.x;
         }
         const uint32_t m = __ballot_sync(kFull, need);
         if (m == 0) {
             runmax = __shfl_sync(kFull, run, 31);
+            racc += __shfl_sync(kFull, cincl, 31);
             b0 += 32;
             continue;
         }
         const int j = __ffs(m) - 1;
+        {
+            const float pmax_j = __shfl_sync(kFull, excl, j);
+            float4 ij;
+            ij.x = __shfl_sync(kFull, info.x, j);
+            ij.y = __shfl_sync(kFull, info.y, j);
+            ij.z = __shfl_sync(kFull, info.z, j);
+            ij.w = __shfl_sync(kFull, info.w, j);
+            const float nbj = __shfl_sync(kFull, nb, j);
+            const float racc_end_j = racc + __shfl_sync(kFull, cincl, j);
+            const int r = fast_block(c, b0 + j, q, ij, nbj, max_nan(pmax_j, ij.y * 1.001f), racc_end_j, efirst,
+                                     ij.x - 128.f * kU * nbj, det);
+            if (r == 1) return true;
+            if (r == 0) {
+                runmax = max_nan(pmax_j, ij.y * 1.001f);
+                racc = racc + __shfl_sync(kFull, cincl, j);
+                b0 += j + 1;
+                continue;
+            }
+        }
+        racc += __shfl_sync(kFull, cincl, j);  // the slow paths below continue behind block j (or re-anchor at it)
         const uint64_t wf = __shfl_sync(kFull, wfirst, j), sf = __shfl_sync(kFull, s_first, j);
         const uint64_t kj = __shfl_sync(kFull, kk, j);
         const bool hl = __shfl_sync(kFull, int(hist_loose), j) != 0;
@@ -524,6 +730,9 @@ __device__ __noinline__ bool search(Ctx& c, uint64_t q, uint64_t avail, Detectio
             continue;  // re-evaluate from this block with the measured anchor
         }
         const float pmax = __shfl_sync(kFull, excl, j);
+        c.sum_ok = sum_ok;
+        c.efirst = efirst;
+        c.racc_in = racc - __shfl_sync(kFull, contrib, j);  // racc already includes block j here
         float pm_blk;
         if (process_block(c, b0 + j, q, avail, pmax, det, &pm_blk)) return true;
         // continue behind block j; the running maximum now covers it (pm_blk: exact energies of the
@@ -760,12 +969,221 @@ __device__ __noinline__ void emit(const Ctx& c, Emit& em, uint32_t status, const
     em.ord++;
 }
 
+__device__ __forceinline__ void init_ctx(Ctx& c, const float* samples, const TmkStreamDev& sd, const TmkPattern* patterns,
+                                         const float4* blk_info, const uint32_t* cand_bits, const TmkFast& f, int lane,
+                                         WarpScratch* sc) {
+    c.x = samples + sd.offset;
+    c.N = sd.n_samples;
+    c.pat = patterns + sd.pattern;
+    c.P = c.pat->P;
+    c.nwin = c.N >= c.P ? c.N - c.P + 1 : 0;
+    c.C = (sd.chunk == 0 || sd.chunk >= c.N) ? 0 : sd.chunk;
+    c.blk_info = blk_info + sd.blk_base;
+    c.cand_bits = cand_bits + sd.blk_base * TMK_BLK_WORDS;
+    c.blk_ptr = f.blk_ptr ? f.blk_ptr + sd.blk_base : nullptr;
+    c.entries = f.entries;
+    c.spec = f.spec;
+    c.nblk = (c.nwin + TMK_BLK - 1) / TMK_BLK;
+    c.thr = sd.threshold;
+    c.local_addr = sd.local_addr;
+    c.max_frame_bytes = sd.max_frame_bytes;
+    c.lane = lane;
+    c.sc = sc;
+    c.rvalid = false;
+    c.rseed = c.rpos = 0;
+    c.rE = 0.f;
+    c.a_seed = c.a_w = 0;
+    c.a_err = 0.f;
+    c.racc_in = c.efirst = 0.f;
+    c.sum_ok = false;
+    c.n_replays = c.n_cands = c.n_det = 0;
+    c.dbg[0] = c.dbg[1] = c.dbg[2] = c.dbg[3] = 0;
+    __syncwarp();
+    for (uint32_t k = lane; k < c.P; k += 32) sc->pre[k] = int8_t(c.pat->levels[k / c.pat->spl]);
+    __syncwarp();
+}
+
+// ---------------------------------------------------------------- cluster pass
+// decode_frame (decoder.rs:242-356) for a detection at window w of a ONE-SHOT capture (the whole capture is
+// buffered: avail == N), exactly the sequence of the walk kernel below. Fills a verdict record; the payload
+// goes straight into the payload buffer.
+__device__ __noinline__ void spec_decode(Ctx& c, uint64_t w, float corr, uint32_t stream, tmk_frame_rec* out,
+                                         uint8_t* payload, uint64_t payload_cap, TmkCounters* counters) {
+    Detection d;
+    d.c = w;
+    d.seed = 0;  // refinement range [expect - margin, expect + margin]: the walk checks that its seed agrees
+    d.avail = c.N;
+    d.corr = corr;
+    d.spec = TMK_ENT_INVALID;
+    const int lc = c.pat->line_code;
+    const uint32_t spl = c.pat->spl, hs = c.pat->hdr_samples;
+    const uint64_t fs = refine(c, d);
+    uint32_t status, consumed = 0, len = 0, data_len = 0;
+    bool have_hdr = false;
+    uint8_t hdr[TMK_PHY_HEADER_BYTES];
+    for (int i = 0; i < TMK_PHY_HEADER_BYTES; ++i) hdr[i] = 0;
+    if (c.N < fs + hs) {
+        status = TMK_FRAME_TRUNCATED;
+    } else {
+        const uint8_t* hb = c.sc->bytes;
+        const uint32_t hbits = line_decode(c, fs, 8 * TMK_PHY_HEADER_BYTES);
+        const bool have7 = (hbits + 7) / 8 >= TMK_PHY_HEADER_BYTES;
+        for (int i = 0; i < TMK_PHY_HEADER_BYTES; ++i) hdr[i] = have7 ? hb[i] : 0;
+        __syncwarp();
+        const uint32_t type = hdr[3];
+        len = (uint32_t(hdr[0]) << 8) | hdr[1];
+        if (!have7 || (type != TMK_FRAME_TYPE_DATA && type != TMK_FRAME_TYPE_ACK)) {
+            status = TMK_FRAME_HDR_PARSE;
+            consumed = hs;
+            have_hdr = have7;
+        } else if ((type == TMK_FRAME_TYPE_DATA && len == 0) || len > c.max_frame_bytes) {
+            status = TMK_FRAME_BAD_LEN;
+            consumed = 1;
+            have_hdr = true;
+        } else {
+            const uint32_t total_bits = (TMK_PHY_HEADER_BYTES + len) * 8;
+            const uint64_t total_samples = tmk_sfb(lc, spl, total_bits);
+            if (c.N < fs + total_samples) {
+                status = TMK_FRAME_TRUNCATED;
+            } else {
+                const uint32_t nbits = line_decode(c, fs, total_bits);
+                consumed = c.P + uint32_t(tmk_sfb(lc, spl, nbits));
+                have_hdr = true;
+                if (nbits < total_bits) {
+                    status = TMK_FRAME_SHORT_DECODE;
+                } else if (c.local_addr >= 0 && hdr[6] != uint32_t(c.local_addr)) {
+                    status = TMK_FRAME_NOT_FOR_US;
+                    data_len = len;
+                } else {
+                    const uint32_t crc = crc8_warp(c.sc->bytes + TMK_PHY_HEADER_BYTES, len, c.lane);
+                    status = crc != hdr[2] ? TMK_FRAME_CRC_FAIL : TMK_FRAME_OK;
+                    data_len = len;
+                }
+            }
+        }
+    }
+    unsigned long long poff = 0;
+    if (c.lane == 0 && data_len) poff = atomicAdd(&counters->n_payload, (unsigned long long)data_len);
+    poff = __shfl_sync(kFull, poff, 0);
+    if (data_len && poff + data_len <= payload_cap)
+        for (uint32_t i = c.lane; i < data_len; i += 32) payload[poff + i] = c.sc->bytes[TMK_PHY_HEADER_BYTES + i];
+    if (c.lane == 0) {
+        tmk_frame_rec r;
+        r.stream = stream;
+        r.status = status;
+        r.preamble_start = w;
+        r.frame_start = fs;
+        r.payload_off = poff;
+        r.corr = corr;
+        r.consumed = consumed;
+        r.len = have_hdr ? uint16_t(len) : 0;
+        r.crc = have_hdr ? hdr[2] : 0;
+        r.type = have_hdr ? hdr[3] : 0;
+        r.seq = have_hdr ? hdr[4] : 0;
+        r.src = have_hdr ? hdr[5] : 0;
+        r.dst = have_hdr ? hdr[6] : 0;
+        r.hdr_valid = have_hdr ? 1 : 0;
+        *out = r;
+    }
+    __syncwarp();
+}
+
+// One warp per block with candidates: exact dot product and accurate energy of every candidate window, and a
+// speculative refine + demodulation + CRC of the windows a walk that enters the block in Searching state would
+// detect. All of it is independent of the rest of the capture, so it runs at full occupancy; the per-stream
+// walk then only decides (the drift bound depends on where ITS search started) and links the results.
+__global__ void __launch_bounds__(kWarpsPerCta * 32, 4)
+cluster_kernel(const float* __restrict__ samples, const TmkStreamDev* __restrict__ streams,
+               const uint32_t* __restrict__ tile_stream, const TmkPattern* __restrict__ patterns,
+               const float4* __restrict__ blk_info, const uint32_t* __restrict__ cand_bits, TmkFast f, uint8_t* payload,
+               uint64_t payload_cap, TmkCounters* counters) {
+    __shared__ WarpScratch scratch[kWarpsPerCta];
+    __shared__ TmkCandEntry ents[kWarpsPerCta][32];
+    const uint32_t warp = threadIdx.x >> 5;
+    const int lane = threadIdx.x & 31;
+    const uint32_t n_items = *f.cblk_count;
+    for (uint32_t item = blockIdx.x * kWarpsPerCta + warp; item < n_items; item += gridDim.x * kWarpsPerCta) {
+        const uint32_t gb = f.cblk_list[item];
+        const uint32_t sidx = tile_stream[gb / TMK_TILE_BLKS];
+        const TmkStreamDev sd = streams[sidx];
+        Ctx c;
+        init_ctx(c, samples, sd, patterns, blk_info, cand_bits, f, lane, &scratch[warp]);
+        const uint64_t bb = uint64_t(gb) - sd.blk_base;
+        if (c.C != 0 || c.P > 255) {  // chunked feeding / long preambles keep the walk's own evaluation
+            if (lane == 0) f.blk_ptr[gb] = TMK_ENT_INVALID;
+            continue;
+        }
+        const uint64_t wb0 = bb * TMK_BLK;
+        block_prefix(c, bb);
+        const uint32_t myword = lane < TMK_BLK_WORDS ? c.cand_bits[bb * TMK_BLK_WORDS + lane] : 0u;
+        uint32_t n_ent = 0;
+#pragma unroll 1
+        for (uint32_t r = 0; r < TMK_BLK_WORDS; ++r) {
+            const uint32_t word = __shfl_sync(kFull, myword, int(r));
+            if (word == 0) continue;
+            const uint32_t wl = r * 32 + lane;
+            const uint64_t w = wb0 + wl;
+            const bool valid = ((word >> lane) & 1u) && w < c.nwin;
+            TmkCandEntry e;
+            e.wl = uint16_t(wl);
+            e.flags = 0;
+            e.D = 0.f;
+            e.Ec = 0.f;
+            e.spec = TMK_ENT_INVALID;
+            if (valid) {
+                e.D = dot_avx_order(c, c.x + w);
+                e.Ec = __double2float_rn(c.sc->Q[wl + c.P] - c.sc->Q[wl]);
+            }
+            const uint32_t m = __ballot_sync(kFull, valid);
+            const uint32_t idx = n_ent + __popc(m & ((1u << lane) - 1u));
+            if (valid && idx < 32) ents[warp][idx] = e;
+            n_ent += __popc(m);
+        }
+        __syncwarp();
+        if (n_ent > 31) {
+            if (lane == 0) f.blk_ptr[gb] = TMK_ENT_INVALID;
+            continue;
+        }
+        // speculative decodes, mimicking a walk that meets the entries in order
+        uint64_t skip_until = 0;
+        for (uint32_t i = 0; i < n_ent; ++i) {
+            const TmkCandEntry e = ents[warp][i];
+            const uint64_t w = wb0 + e.wl;
+            if (w < skip_until) continue;
+            const float corr = ex_corr(e.D, e.Ec, c.pat->pe);
+            if (!(corr >= c.thr)) continue;
+            unsigned int sp = 0;
+            if (lane == 0) sp = atomicAdd(&f.pool[1], 1u);
+            sp = __shfl_sync(kFull, sp, 0);
+            if (sp >= f.spec_cap) break;  // pool exhausted: the walk decodes the rest itself
+            spec_decode(c, w, corr, sidx, f.spec + sp, payload, payload_cap, counters);
+            if (lane == 0) ents[warp][i].spec = sp;
+            __syncwarp();
+            const tmk_frame_rec* r = f.spec + sp;
+            const uint32_t st = __shfl_sync(kFull, lane == 0 ? r->status : 0u, 0);
+            const uint32_t cons = __shfl_sync(kFull, lane == 0 ? r->consumed : 0u, 0);
+            if (st == TMK_FRAME_TRUNCATED) break;
+            skip_until = w + cons;
+        }
+        __syncwarp();
+        unsigned int base = 0;
+        if (lane == 0) base = n_ent ? atomicAdd(&f.pool[0], n_ent) : 0u;
+        base = __shfl_sync(kFull, base, 0);
+        if (base + n_ent > f.entry_cap || base + n_ent >= (1u << 27)) {
+            if (lane == 0) f.blk_ptr[gb] = TMK_ENT_INVALID;
+            continue;
+        }
+        if (uint32_t(lane) < n_ent) f.entries[base + lane] = ents[warp][lane];
+        if (lane == 0) f.blk_ptr[gb] = (base << 5) | n_ent;
+    }
+}
+
 #ifndef TMK_WALK_CTAS
 #define TMK_WALK_CTAS 4  // measured at C2: 4 -> 11.7 ms, 5 -> 12.8, 6 -> 12.2, 7 -> 15.4 (spills in process_block)
 #endif
 __global__ void __launch_bounds__(kWarpsPerCta * 32, TMK_WALK_CTAS)
 walk_kernel(const float* __restrict__ samples, const TmkStreamDev* __restrict__ streams, uint32_t s0, uint32_t s1,
-            unsigned int* __restrict__ next,
+            unsigned int* __restrict__ next, TmkFast fast,
             const TmkPattern* __restrict__ patterns, const float4* __restrict__ blk_info,
             const uint32_t* __restrict__ cand_bits, tmk_frame_rec* recs, uint32_t* rec_ord, uint64_t rec_cap,
             uint8_t* payload, uint64_t payload_cap, uint32_t* stream_cnt, TmkCounters* counters) {
@@ -781,30 +1199,7 @@ walk_kernel(const float* __restrict__ samples, const TmkStreamDev* __restrict__ 
     if (sidx >= s1) return;
     const TmkStreamDev sd = streams[sidx];
     Ctx c;
-    c.x = samples + sd.offset;
-    c.N = sd.n_samples;
-    c.pat = patterns + sd.pattern;
-    c.P = c.pat->P;
-    c.nwin = c.N >= c.P ? c.N - c.P + 1 : 0;
-    c.C = (sd.chunk == 0 || sd.chunk >= c.N) ? 0 : sd.chunk;
-    c.blk_info = blk_info + sd.blk_base;
-    c.cand_bits = cand_bits + sd.blk_base * TMK_BLK_WORDS;
-    c.nblk = (c.nwin + TMK_BLK - 1) / TMK_BLK;
-    c.thr = sd.threshold;
-    c.local_addr = sd.local_addr;
-    c.max_frame_bytes = sd.max_frame_bytes;
-    c.lane = lane_id;
-    c.sc = &scratch[warp];
-    c.rvalid = false;
-    c.rseed = c.rpos = 0;
-    c.rE = 0.f;
-    c.a_seed = c.a_w = 0;
-    c.a_err = 0.f;
-    c.n_replays = c.n_cands = c.n_det = 0;
-    c.dbg[0] = c.dbg[1] = c.dbg[2] = c.dbg[3] = 0;
-    __syncwarp();
-    for (uint32_t k = lane_id; k < c.P; k += 32) c.sc->pre[k] = int8_t(c.pat->levels[k / c.pat->spl]);
-    __syncwarp();
+    init_ctx(c, samples, sd, patterns, blk_info, cand_bits, fast, lane_id, &scratch[warp]);
     Emit em{recs, rec_ord, rec_cap, payload, payload_cap, counters, sidx, 0};
     uint32_t n_ok = 0, n_crc = 0, n_hdr = 0, n_nfu = 0;
 
@@ -817,6 +1212,29 @@ walk_kernel(const float* __restrict__ samples, const TmkStreamDev* __restrict__ 
     while (search(c, q, avail, &d)) {
         c.n_det++;
         avail = d.avail;
+        if (d.spec != TMK_ENT_INVALID && d.c + c.P - c.pat->sync_len - d.seed >= c.pat->margin) {
+            // the cluster pass already refined, demodulated and checked the frame of this detection (its
+            // refinement range [expect - margin, expect + margin] is the walk's because the search started at
+            // least `margin` samples before `expect`): link the verdict, payload bytes are in place
+            tmk_frame_rec r = c.spec[d.spec];
+            unsigned long long slot = 0;
+            if (c.lane == 0) slot = atomicAdd(&counters->n_recs, 1ull);
+            slot = __shfl_sync(kFull, slot, 0);
+            if (c.lane == 0 && slot < rec_cap) {
+                r.stream = sidx;
+                r.corr = d.corr;
+                recs[slot] = r;
+                rec_ord[slot] = em.ord;
+            }
+            em.ord++;
+            if (r.status == TMK_FRAME_OK) n_ok++;
+            else if (r.status == TMK_FRAME_CRC_FAIL) n_crc++;
+            else if (r.status == TMK_FRAME_NOT_FOR_US) n_nfu++;
+            else if (r.status != TMK_FRAME_TRUNCATED) n_hdr++;
+            if (r.status == TMK_FRAME_TRUNCATED) break;
+            q = d.c + r.consumed;
+            continue;
+        }
         {   // pull the head of the frame towards L2 while the refinement and the header decode run
             const uint64_t f0 = d.c + c.P;
             for (uint64_t i = uint64_t(lane_id) * 32; i < 2560 && f0 + i < c.N; i += 1024)
@@ -967,7 +1385,24 @@ int tmk_launch_excl_scan(const uint32_t* cnt, uint64_t* base, uint32_t n, cudaSt
     return 1;
 }
 
+int tmk_launch_cluster(const float* samples, const TmkStreamDev* streams, const uint32_t* tile_stream,
+                       const TmkPattern* patterns, const float4* blk_info, const uint32_t* cand_bits, TmkFast f,
+                       uint8_t* payload, uint64_t payload_cap, TmkCounters* counters, cudaStream_t st) {
+    static int max_ctas = 0;
+    if (max_ctas == 0) {
+        int dev = 0, sms = 0, per_sm = 0;
+        cudaGetDevice(&dev);
+        cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+        cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, cluster_kernel, kWarpsPerCta * 32, 0);
+        max_ctas = sms * (per_sm > 0 ? per_sm : 1);
+    }
+    cluster_kernel<<<max_ctas, kWarpsPerCta * 32, 0, st>>>(samples, streams, tile_stream, patterns, blk_info, cand_bits, f,
+                                                           payload, payload_cap, counters);
+    return 1;
+}
+
 int tmk_launch_walk(const float* samples, const TmkStreamDev* streams, uint32_t s0, uint32_t s1, unsigned int* next,
+                    TmkFast fast,
                     const TmkPattern* patterns, const float4* blk_info, const uint32_t* cand_bits,
                     tmk_frame_rec* recs, uint32_t* rec_ord, uint64_t rec_cap, uint8_t* payload,
                     uint64_t payload_cap, uint32_t* stream_cnt, TmkCounters* counters, cudaStream_t st) {
@@ -983,7 +1418,7 @@ int tmk_launch_walk(const float* samples, const TmkStreamDev* streams, uint32_t 
     }
     uint32_t grid = (n_streams + kWarpsPerCta - 1) / kWarpsPerCta;
     if (grid > uint32_t(max_ctas)) grid = uint32_t(max_ctas);
-    walk_kernel<<<grid, kWarpsPerCta * 32, 0, st>>>(samples, streams, s0, s1, next, patterns, blk_info, cand_bits, recs,
+    walk_kernel<<<grid, kWarpsPerCta * 32, 0, st>>>(samples, streams, s0, s1, next, fast, patterns, blk_info, cand_bits, recs,
                                                     rec_ord, rec_cap, payload, payload_cap, stream_cnt, counters);
     return 1;
 }
