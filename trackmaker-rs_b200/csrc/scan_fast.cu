@@ -30,15 +30,15 @@ constexpr unsigned kFull = 0xffffffffu;
 template <int LC> struct Shape;
 template <> struct Shape<TMK_LINE_4B5B> {
     static constexpr int L = 20, P = 60;
-    static constexpr int kCopy = 184;  // floats copied per lane row (3 x 60 steps read x[0 .. 183]), multiple of 4
-    static constexpr int kRow = 188;   // row pitch in floats: 752 B = 47 x 16 B (odd: conflict-free LDS.128)
-    static constexpr int kWarps = 4;   // 96 KB of rows per CTA, 2 CTAs per SM
+    static constexpr int kCopy = 180;  // floats copied per lane row (>= kS + P - 1, multiple of 4)
+    static constexpr int kRow = 180;   // row pitch in floats: 720 B = 45 x 16 B (odd: conflict-free LDS.128)
+    static constexpr int kWarps = 4;   // 92 KB of rows per CTA, 2 CTAs per SM
 };
 template <> struct Shape<TMK_LINE_MANCHESTER> {
     static constexpr int L = 32, P = 96;
-    static constexpr int kCopy = 232;  // 3 x 76 steps read x[0 .. 231]
-    static constexpr int kRow = 236;   // 944 B = 59 x 16 B
-    static constexpr int kWarps = 3;   // 91 KB of rows per CTA, 2 CTAs per SM
+    static constexpr int kCopy = 216;
+    static constexpr int kRow = 220;   // 880 B = 55 x 16 B
+    static constexpr int kWarps = 4;   // 113 KB of rows per CTA, 2 CTAs per SM
 };
 
 __device__ __forceinline__ uint32_t smem_u32(const void* p) { return uint32_t(__cvta_generic_to_shared(p)); }
@@ -79,14 +79,22 @@ struct LaneOut {
 // static ring index: (i mod R) for i that may be negative
 template <int R> __device__ __forceinline__ constexpr int rix(int i) { return ((i % R) + R) % R; }
 
-// finish window n of the strip (branch free): block statistics and the candidate predicate.
-// `valid` masks the windows that do not belong to the strip (warm-up, past the strip / the stream).
+// finish a window of the strip (branch free): block statistics and the candidate predicate.
+// Only tail tiles (FULL == false) have windows to mask: past the end of the stream.
+template <bool FULL>
 __device__ __forceinline__ bool finish_window(float D, float E, float kap, bool valid, LaneOut& o) {
     const float dp = fmaxf(D, 0.0f);
+    if (FULL) {
+        const float r = dp * dp * rcp_approx(E);  // P * corr^2 (NaN for silence: never a candidate)
+        o.emin = fminf(o.emin, E);
+        o.emax = max_nan(o.emax, E);              // a NaN sample stays visible in max E
+        o.rmax = fmaxf(o.rmax, r);
+        return r > kap;
+    }
     const float Ev = valid ? E : __int_as_float(0x7fc00000);  // NaN: ignored by fminf / fmaxf, never a candidate
-    const float r = dp * dp * rcp_approx(Ev);                  // P * corr^2 (NaN for silence: never a candidate)
+    const float r = dp * dp * rcp_approx(Ev);
     o.emin = fminf(o.emin, Ev);
-    o.emax = max_nan(o.emax, valid ? E : 0.0f);                // a NaN SAMPLE must stay visible in max E
+    o.emax = max_nan(o.emax, valid ? E : 0.0f);
     o.rmax = fmaxf(o.rmax, r);
     return r > kap;
 }
@@ -112,23 +120,12 @@ __device__ __forceinline__ void flush_cands(uint64_t cm0, uint64_t cm1, int k, i
     }
 }
 
-// Which loop iterations k (of NIT) make step j finish a window of the strip: n = U * k + j - LAT in [0, hi).
-// j is a compile-time constant after unrolling, so this folds to an OR of at most NIT iteration flags.
-template <int U, int LAT, int NIT>
-__device__ __forceinline__ bool step_valid(int j, int hi, const bool (&is)[NIT]) {
-    bool v = false;
-#pragma unroll
-    for (int kk = 0; kk < NIT; ++kk) {
-        const int n = U * kk + j - LAT;
-        if (n >= 0 && n < hi) v = v || is[kk];
-    }
-    return v;
-}
-
-// The strips are ROLLED loops of NIT iterations x U steps: the unrolled body is the same ~3 K instructions
-// for every warp and stays resident in the instruction cache (the fully unrolled 177 / 213-step form was
-// 148 KB of straight-line code streamed by every warp). All ring indices are static because the ring sizes
-// divide U; warm-up steps run the same code on zeroed rings and are masked when a window is finished.
+// The strips run in two phases. Phase A (the first P - 3 steps) only warms the rings up: no window is
+// complete yet, so it carries no finish code. Phase B finishes one window per step, all of them inside
+// the strip, so nothing has to be masked (tail tiles mask by `n < nvalid`). For 4B5B phase B is a ROLLED
+// loop of 2 x 60 steps (every ring size divides 60, so all register indices stay static); the code that
+// every warp executes is ~2.6 K instructions and stays resident in the instruction cache (the first
+// version, 177 fully unrolled steps with a branch per window, was 148 KB of straight-line code).
 
 // ---------------------------------------------------------------- 4B5B: levels --++-++--++--+-++-++
 // D(n) = -d[n] - y[n+12] + p2[n+15] - d[n+21] - p2[n+33] + y[n+39] - y[n+42] + p2[n+45] - y[n+51] + p2[n+54]
@@ -136,15 +133,13 @@ __device__ __forceinline__ bool step_valid(int j, int hi, const bool (&is)[NIT])
 template <bool FULL>
 __device__ __forceinline__ void strip_4b5b(const float* __restrict__ row, float kap, int nvalid,
                                            uint32_t* __restrict__ bits, uint32_t bit0, LaneOut& o) {
-    constexpr int U = 60, LAT = 57, NIT = 3;  // steps per iteration, steps from a window's start to its finish
-    static_assert(U * NIT >= kS + LAT && U % 12 == 0 && U <= 64, "strip steps");
+    constexpr int U = 60, LAT = 57;  // steps per phase-B iteration; steps from a window's first sample to its finish
+    static_assert(2 * U == kS && U % 12 == 0 && U <= 64, "strip steps");
     float acc[60], yb[4], p2b[12], db[4], xr[12], xo[4];
 #pragma unroll
-    for (int i = 0; i < 60; ++i) acc[i] = 0.f;
+    for (int i = 0; i < 12; ++i) p2b[i] = 0.f;
 #pragma unroll
-    for (int i = 0; i < 12; ++i) p2b[i] = xr[i] = 0.f;
-#pragma unroll
-    for (int i = 0; i < 4; ++i) yb[i] = db[i] = xo[i] = 0.f;
+    for (int i = 0; i < 4; ++i) yb[i] = db[i] = 0.f;
     float e = 0.0f;
     {
         const float4 v = *reinterpret_cast<const float4*>(row);
@@ -152,65 +147,75 @@ __device__ __forceinline__ void strip_4b5b(const float* __restrict__ row, float 
         e = fmaf(v.x, v.x, e);
         e = fmaf(v.y, v.y, e);
     }
+    // one step of the recurrences at sample m = base + mm (mm static); `rb` = row + base
+#define TMK_STEP_4B5B(rb, mm, PHASE_B)                                                                      \
+    if ((((mm) + 2) & 3) == 0) {                                                                            \
+        const float4 v = *reinterpret_cast<const float4*>((rb) + (mm) + 2);                                 \
+        xr[rix<12>((mm) + 2)] = v.x; xr[rix<12>((mm) + 3)] = v.y;                                           \
+        xr[rix<12>((mm) + 4)] = v.z; xr[rix<12>((mm) + 5)] = v.w;                                           \
+    }                                                                                                       \
+    const float x2 = xr[rix<12>((mm) + 2)];                                                                 \
+    const float y = (xr[rix<12>(mm)] + xr[rix<12>((mm) + 1)]) + x2;                                         \
+    e = fmaf(x2, x2, e);                                                                                    \
+    const float p2 = yb[rix<4>((mm) - 3)] + y;                                                              \
+    yb[rix<4>(mm)] = y;                                                                                     \
+    const float d = p2b[rix<12>((mm) - 9)] - p2;                                                            \
+    p2b[rix<12>((mm) - 3)] = p2;                                                                            \
+    if (PHASE_B || (mm) >= 12) acc[rix<60>((mm) - 12)] = -db[rix<4>((mm) - 12)] - y;                        \
+    db[rix<4>((mm) - 9)] = d;                                                                               \
+    if (PHASE_B || (mm) >= 18) acc[rix<60>((mm) - 18)] += p2;                                               \
+    if (PHASE_B || (mm) >= 30) acc[rix<60>((mm) - 30)] -= d;                                                \
+    if (PHASE_B || (mm) >= 36) acc[rix<60>((mm) - 36)] -= p2;                                               \
+    if (PHASE_B || (mm) >= 39) acc[rix<60>((mm) - 39)] += y;                                                \
+    if (PHASE_B || (mm) >= 42) acc[rix<60>((mm) - 42)] -= y;                                                \
+    if (PHASE_B || (mm) >= 48) acc[rix<60>((mm) - 48)] += p2;                                               \
+    if (PHASE_B || (mm) >= 51) acc[rix<60>((mm) - 51)] -= y;
+
+    // ---- phase A: samples 0 .. 56
+#pragma unroll
+    for (int m = 0; m < LAT; ++m) {
+        TMK_STEP_4B5B(row, m, false)
+        (void)p2;
+    }
+    // ---- phase B: samples 57 .. 176, window n = m - 57 finishes at every step
 #pragma unroll 1
-    for (int k = 0; k < NIT; ++k) {
+    for (int k = 0; k < 2; ++k) {
         const float* __restrict__ rk = row + U * k;
-        const bool is[NIT] = {k == 0, k == 1, k == 2};
         uint64_t cm = 0;
 #pragma unroll
-        for (int j = 0; j < U; ++j) {  // m = U * k + j
-            if (((j + 2) & 3) == 0) {  // x[m+2 .. m+5] become needed
-                const float4 v = *reinterpret_cast<const float4*>(rk + j + 2);
-                xr[rix<12>(j + 2)] = v.x; xr[rix<12>(j + 3)] = v.y; xr[rix<12>(j + 4)] = v.z; xr[rix<12>(j + 5)] = v.w;
-            }
-            const float x2 = xr[rix<12>(j + 2)];
-            const float y = (xr[rix<12>(j)] + xr[rix<12>(j + 1)]) + x2;
-            e = fmaf(x2, x2, e);  // window energy: x[m+2] enters
-            const float p2 = yb[rix<4>(j - 3)] + y;    // p2[m-3]
-            yb[rix<4>(j)] = y;
-            const float d = p2b[rix<12>(j - 9)] - p2;  // d[m-9]
-            p2b[rix<12>(j - 3)] = p2;
-            acc[rix<60>(j - 12)] = -db[rix<4>(j - 12)] - y;
-            db[rix<4>(j - 9)] = d;
-            acc[rix<60>(j - 18)] += p2;
-            acc[rix<60>(j - 30)] -= d;
-            acc[rix<60>(j - 36)] -= p2;
-            acc[rix<60>(j - 39)] += y;
-            acc[rix<60>(j - 42)] -= y;
-            acc[rix<60>(j - 48)] += p2;
-            acc[rix<60>(j - 51)] -= y;
-            // window n = m - 57 is complete: x[n .. n+59] have entered e
-            const float D = acc[rix<60>(j - LAT)] + p2;
-            bool valid = step_valid<U, LAT, NIT>(j, kS, is);
-            if (!FULL) valid = valid && (U * k + j - LAT) < nvalid;
-            if (finish_window(D, e, kap, valid, o)) cm |= 1ull << j;
-            if (((j - LAT) & 3) == 0) {  // x[n .. n+3] (row start for the warm-up steps: unused)
-                const int nn = U * k + j - LAT;
-                const float4 v = *reinterpret_cast<const float4*>(row + (nn >= 0 ? nn : 0));
+        for (int j = 0; j < U; ++j) {
+            TMK_STEP_4B5B(rk, LAT + j, true)
+            const float D = acc[rix<60>(j)] + p2;  // window n = U * k + j: x[n .. n+59] have entered e
+            const bool valid = FULL || (U * k + j) < nvalid;
+            if (finish_window<FULL>(D, e, kap, valid, o)) cm |= 1ull << j;
+            if ((j & 3) == 0) {
+                const float4 v = *reinterpret_cast<const float4*>(rk + j);
                 xo[0] = v.x; xo[1] = v.y; xo[2] = v.z; xo[3] = v.w;
             }
-            const float xl = step_valid<U, LAT, NIT>(j, 1 << 20, is) ? xo[(j - LAT) & 3] : 0.0f;
+            const float xl = xo[j & 3];
             e = fmaf(-xl, xl, e);  // x[n] leaves
         }
-        if (cm) flush_cands<U, LAT>(cm, 0, k, FULL ? kS : nvalid, bits, bit0, o);
+        if (cm) flush_cands<U, 0>(cm, 0, k, FULL ? kS : nvalid, bits, bit0, o);
     }
+#undef TMK_STEP_4B5B
 }
 
 // ---------------------------------------------------------------- Manchester, bits 0011 0011 0101 1010
 // D(n) = v[n] + v[n+24] + t[n+48] - t[n+72]
 //   z[m] = y[m]-y[m+3]  w[m] = z[m]+z[m+6]  u[m] = z[m]-z[m+6]  v[m] = w[m]-w[m+12]  t[m] = u[m]+u[m+12]
+// (phase B is 120 straight-line steps: the accumulator ring needs 73 slots, more than any divisor of 120
+//  below 120 offers)
 template <bool FULL>
 __device__ __forceinline__ void strip_manchester(const float* __restrict__ row, float kap, int nvalid,
                                                  uint32_t* __restrict__ bits, uint32_t bit0, LaneOut& o) {
-    constexpr int U = 76, LAT = 93, NIT = 3;
-    static_assert(U * NIT >= kS + LAT && U % 19 == 0 && U % 4 == 0 && U <= 128, "strip steps");
-    float acc[76], yb[4], zb[19], wb[19], ub[19], xr[19], xo[4];
+    constexpr int LAT = 93;
+    float acc[80], yb[4], zb[8], wb[16], ub[16], xr[8], xo[4];
 #pragma unroll
-    for (int i = 0; i < 76; ++i) acc[i] = 0.f;
+    for (int i = 0; i < 16; ++i) wb[i] = ub[i] = 0.f;
 #pragma unroll
-    for (int i = 0; i < 19; ++i) zb[i] = wb[i] = ub[i] = xr[i] = 0.f;
+    for (int i = 0; i < 8; ++i) zb[i] = 0.f;
 #pragma unroll
-    for (int i = 0; i < 4; ++i) yb[i] = xo[i] = 0.f;
+    for (int i = 0; i < 4; ++i) yb[i] = 0.f;
     float e = 0.0f;
     {
         const float4 v = *reinterpret_cast<const float4*>(row);
@@ -218,49 +223,45 @@ __device__ __forceinline__ void strip_manchester(const float* __restrict__ row, 
         e = fmaf(v.x, v.x, e);
         e = fmaf(v.y, v.y, e);
     }
-#pragma unroll 1
-    for (int k = 0; k < NIT; ++k) {
-        const float* __restrict__ rk = row + U * k;
-        const bool is[NIT] = {k == 0, k == 1, k == 2};
-        uint64_t cm0 = 0, cm1 = 0;
+    uint64_t cm0 = 0, cm1 = 0;
 #pragma unroll
-        for (int j = 0; j < U; ++j) {  // m = U * k + j
-            if (((j + 2) & 3) == 0) {
-                const float4 v = *reinterpret_cast<const float4*>(rk + j + 2);
-                xr[rix<19>(j + 2)] = v.x; xr[rix<19>(j + 3)] = v.y; xr[rix<19>(j + 4)] = v.z; xr[rix<19>(j + 5)] = v.w;
+    for (int m = 0; m < kS + LAT; ++m) {
+        if (((m + 2) & 3) == 0) {
+            const float4 v = *reinterpret_cast<const float4*>(row + m + 2);
+            xr[(m + 2) & 7] = v.x; xr[(m + 3) & 7] = v.y; xr[(m + 4) & 7] = v.z; xr[(m + 5) & 7] = v.w;
+        }
+        const float x2 = xr[(m + 2) & 7];
+        const float y = (xr[m & 7] + xr[(m + 1) & 7]) + x2;
+        e = fmaf(x2, x2, e);
+        const float z = yb[(m + 1) & 3] - y;  // z[m-3]
+        yb[m & 3] = y;
+        const float zo = zb[(m + 7) & 7];     // z[m-9]
+        const float w = zo + z, u = zo - z;   // w[m-9], u[m-9]
+        zb[(m + 5) & 7] = z;
+        const float vv = wb[(m + 11) & 15] - w;  // v[m-21], t[m-21]
+        const float tt = ub[(m + 11) & 15] + u;
+        wb[(m + 7) & 15] = w;
+        ub[(m + 7) & 15] = u;
+        if (m >= 21) acc[(m - 21) % 80] = vv;
+        if (m >= 45) acc[(m - 45) % 80] += vv;
+        if (m >= 69) acc[(m - 69) % 80] += tt;
+        if (m >= LAT) {
+            const int n = m - LAT;  // window n is complete
+            const float D = acc[n % 80] - tt;
+            const bool valid = FULL || n < nvalid;
+            if (finish_window<FULL>(D, e, kap, valid, o)) {
+                if (n < 64) cm0 |= 1ull << (n & 63);
+                else cm1 |= 1ull << (n & 63);
             }
-            const float x2 = xr[rix<19>(j + 2)];
-            const float y = (xr[rix<19>(j)] + xr[rix<19>(j + 1)]) + x2;
-            e = fmaf(x2, x2, e);
-            const float z = yb[rix<4>(j - 3)] - y;  // z[m-3]
-            yb[rix<4>(j)] = y;
-            const float zo = zb[rix<19>(j - 9)];
-            const float w = zo + z, u = zo - z;      // w[m-9], u[m-9]
-            zb[rix<19>(j - 3)] = z;
-            const float vv = wb[rix<19>(j - 21)] - w;  // v[m-21], t[m-21]
-            const float tt = ub[rix<19>(j - 21)] + u;
-            wb[rix<19>(j - 9)] = w;
-            ub[rix<19>(j - 9)] = u;
-            acc[rix<76>(j - 21)] = vv;
-            acc[rix<76>(j - 45)] += vv;
-            acc[rix<76>(j - 69)] += tt;
-            const float D = acc[rix<76>(j - LAT)] - tt;  // window n = m - 93
-            bool valid = step_valid<U, LAT, NIT>(j, kS, is);
-            if (!FULL) valid = valid && (U * k + j - LAT) < nvalid;
-            if (finish_window(D, e, kap, valid, o)) {
-                if (j < 64) cm0 |= 1ull << (j & 63);
-                else cm1 |= 1ull << (j & 63);
-            }
-            if (((j - LAT) & 3) == 0) {
-                const int nn = U * k + j - LAT;
-                const float4 v = *reinterpret_cast<const float4*>(row + (nn >= 0 ? nn : 0));
+            if ((n & 3) == 0) {
+                const float4 v = *reinterpret_cast<const float4*>(row + n);
                 xo[0] = v.x; xo[1] = v.y; xo[2] = v.z; xo[3] = v.w;
             }
-            const float xl = step_valid<U, LAT, NIT>(j, 1 << 20, is) ? xo[(j - LAT) & 3] : 0.0f;
+            const float xl = xo[n & 3];
             e = fmaf(-xl, xl, e);
         }
-        if (cm0 | cm1) flush_cands<U, LAT>(cm0, cm1, k, FULL ? kS : nvalid, bits, bit0, o);
     }
+    if (cm0 | cm1) flush_cands<128, 0>(cm0, cm1, 0, FULL ? kS : nvalid, bits, bit0, o);
 }
 
 template <int LC>
