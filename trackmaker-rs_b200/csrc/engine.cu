@@ -162,8 +162,14 @@ int tmk_engine_create(int device, tmk_engine** out) {
     tmk_engine* e = new tmk_engine();
     e->device = device;
     bool ok = cudaStreamCreateWithFlags(&e->stream, cudaStreamNonBlocking) == cudaSuccess &&
-              cudaStreamCreateWithFlags(&e->copy_stream, cudaStreamNonBlocking) == cudaSuccess &&
-              cudaStreamCreateWithFlags(&e->walk_stream, cudaStreamNonBlocking) == cudaSuccess;
+              cudaStreamCreateWithFlags(&e->copy_stream, cudaStreamNonBlocking) == cudaSuccess;
+    {
+        int lo_pri = 0, hi_pri = 0;  // numerically lowest = highest priority
+        cudaDeviceGetStreamPriorityRange(&lo_pri, &hi_pri);
+        for (int i = 0; ok && i < 4; ++i)
+            ok = cudaStreamCreateWithPriority(&e->walk_streams[i], cudaStreamNonBlocking, hi_pri) == cudaSuccess &&
+                 cudaEventCreateWithFlags(&e->wev[i], cudaEventDisableTiming) == cudaSuccess;
+    }
     for (int i = 0; ok && i < 6; ++i) ok = cudaEventCreate(&e->ev[i]) == cudaSuccess;
     for (int i = 0; ok && i < 2; ++i) ok = cudaEventCreate(&e->tev[i]) == cudaSuccess;
     for (int i = 0; ok && i < 6; ++i) ok = cudaEventCreateWithFlags(&e->cev[i], cudaEventDisableTiming) == cudaSuccess;
@@ -195,7 +201,10 @@ void tmk_engine_destroy(tmk_engine* e) {
         if (e->cev[i]) cudaEventDestroy(e->cev[i]);
     if (e->stream) cudaStreamDestroy(e->stream);
     if (e->copy_stream) cudaStreamDestroy(e->copy_stream);
-    if (e->walk_stream) cudaStreamDestroy(e->walk_stream);
+    for (int i = 0; i < 4; ++i) {
+        if (e->walk_streams[i]) cudaStreamDestroy(e->walk_streams[i]);
+        if (e->wev[i]) cudaEventDestroy(e->wev[i]);
+    }
     delete e;
 }
 
@@ -308,8 +317,12 @@ int tmk_decode_batch(tmk_engine* e, const float* samples, uint64_t total_samples
         // chunks must be large enough for a walk to hide behind the next copy (measured: 8 M -> 1.8, 48 M -> 9.6,
         // 256 M -> 13.0, one chunk -> 12.2 Gsamples/s end to end at C2)
         uint64_t target = 256ull << 20;
-        if (const char* ev = getenv("TMK_CHUNK_MSAMPLES")) target = std::max<uint64_t>(1, strtoull(ev, nullptr, 10)) << 20;
-        if (!host_samples || !ordered || total_samples <= target) {
+        // (device-resident captures: one chunk unless TMK_RESIDENT_CHUNK_MSAMPLES asks otherwise — measured at C2,
+        //  the walk CTAs fill the register file, so chunk walks and later scans take turns instead of overlapping:
+        //  one chunk 14.05 ms, 256 M 13.9, 128 M 17.5, 64 M 23.4 ms per step)
+        const char* ev = getenv(host_samples ? "TMK_CHUNK_MSAMPLES" : "TMK_RESIDENT_CHUNK_MSAMPLES");
+        if (ev) target = std::max<uint64_t>(1, strtoull(ev, nullptr, 10)) << 20;
+        if (!ordered || total_samples <= target || (!host_samples && !ev)) {
             chunks.push_back({0, n_streams, 0, uint32_t(b.n_tiles), 0, total_samples});
         } else {
             uint32_t s0 = 0;
@@ -340,10 +353,10 @@ int tmk_decode_batch(tmk_engine* e, const float* samples, uint64_t total_samples
     CK(e->d_next.reserve(sizeof(unsigned int) * (chunks.size() + 1)));
     // cluster pass (walk.cu): candidate entries + speculative verdicts, per chunk its own list region / counter
     const bool use_fast = b.n_blocks > 0 && b.n_blocks < (1ull << 31) && !getenv("TMK_NO_CLUSTER");
-    const uint64_t entry_cap = std::min<uint64_t>((1ull << 27) - 1, b.n_blocks / 2 + 4096);
+    const uint64_t entry_cap = std::min<uint64_t>((1ull << 26) - 1, b.n_blocks / 2 + 4096);
     if (use_fast) {
         CK(e->d_cblk.reserve(sizeof(uint32_t) * b.n_blocks));
-        CK(e->d_blk_ptr.reserve(sizeof(uint32_t) * b.n_blocks));
+        CK(e->d_blk_ptr.reserve(2 * sizeof(uint32_t) * b.n_blocks));  // pointers | gains
         CK(e->d_entries.reserve(sizeof(TmkCandEntry) * entry_cap));
         CK(e->d_pool.reserve(sizeof(unsigned int) * (2 + chunks.size())));
     }
@@ -377,6 +390,7 @@ int tmk_decode_batch(tmk_engine* e, const float* samples, uint64_t total_samples
         f.cblk_list = static_cast<uint32_t*>(e->d_cblk.p) + uint64_t(ch.t0) * TMK_TILE_BLKS;
         f.cblk_count = pool + 2 + g;
         f.blk_ptr = static_cast<uint32_t*>(e->d_blk_ptr.p);
+        f.blk_gain = reinterpret_cast<float*>(f.blk_ptr + b.n_blocks);
         f.entries = static_cast<TmkCandEntry*>(e->d_entries.p);
         f.entry_cap = uint32_t(entry_cap);
         f.spec = static_cast<tmk_frame_rec*>(e->d_spec.p);
@@ -412,7 +426,7 @@ int tmk_decode_batch(tmk_engine* e, const float* samples, uint64_t total_samples
         uint8_t* dpay = pay_dev ? payload : static_cast<uint8_t*>(e->d_payload.p);
         // A walk is a latency-bound serial chain per stream (milliseconds whatever the number of streams), so
         // the walks of the chunks run on their own stream, concurrently with each other and with later scans.
-        cudaStream_t ws = chunks.size() == 1 ? e->stream : e->walk_stream;
+        cudaStream_t ws = chunks.size() == 1 ? e->stream : e->walk_streams[g % 4];
         if (ws != e->stream) {
             cudaEvent_t se = e->cev[3 + (g & 1)];
             CK(cudaEventRecord(se, e->stream));
@@ -420,15 +434,18 @@ int tmk_decode_batch(tmk_engine* e, const float* samples, uint64_t total_samples
         }
         if (use_fast)
             e->launches += tmk_launch_cluster(dx, ds, dtd, dp, dbi, dcb, fast, dpay, dev_pay_cap, dc, ws);
+        if (chunks.size() == 1) CK(cudaEventRecord(e->ev[5], e->stream));
         e->launches += tmk_launch_walk(dx, ds, ch.s0, ch.s1, dnext + g, fast, dp, dbi, dcb,
                                        static_cast<tmk_frame_rec*>(e->d_recs_tmp.p), static_cast<uint32_t*>(e->d_rec_ord.p),
                                        dev_rec_cap, dpay, dev_pay_cap, static_cast<uint32_t*>(e->d_cnt.p), dc, ws);
         CK(cudaGetLastError());
     }
     if (chunks.size() != 1) {
-        CK(cudaEventRecord(e->cev[5], e->walk_stream));
-        CK(cudaStreamWaitEvent(e->stream, e->cev[5], 0));
-        CK(cudaEventRecord(e->ev[2], e->stream));
+        CK(cudaEventRecord(e->ev[2], e->stream));  // end of the last scan; the walks of the earlier chunks are under way
+        for (int i = 0; i < 4 && size_t(i) < chunks.size(); ++i) {
+            CK(cudaEventRecord(e->wev[i], e->walk_streams[i]));
+            CK(cudaStreamWaitEvent(e->stream, e->wev[i], 0));
+        }
     }
     TmkCounters hc;
     CK(cudaMemcpyAsync(&hc, dc, sizeof hc, cudaMemcpyDeviceToHost, e->stream));
@@ -462,6 +479,10 @@ int tmk_decode_batch(tmk_engine* e, const float* samples, uint64_t total_samples
     *payload_len = hc.n_payload;
     for (int i = 0; i < TMK_STAT_COUNT; ++i) e->stats[i] += hc.stats[i];
     for (int i = 0; i < 8; ++i) e->dbg[i] = hc.dbg[i];
+    if (chunks.size() == 1) {  // [4]: device time of the cluster pass in microseconds (part of stage [1])
+        float cms = 0.f;
+        if (cudaEventElapsedTime(&cms, e->ev[2], e->ev[5]) == cudaSuccess) e->dbg[4] = uint64_t(cms * 1000.f);
+    }
     const bool overflow = hc.n_recs > rec_cap || hc.n_payload > payload_cap;
     if (!overflow && hc.n_recs) {
         tmk_frame_rec* dout = recs;

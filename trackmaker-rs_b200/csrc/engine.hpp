@@ -34,7 +34,8 @@ struct tmk_engine {
     int device = 0;
     cudaStream_t stream = nullptr;
     cudaStream_t copy_stream = nullptr;
-    cudaStream_t walk_stream = nullptr;
+    cudaStream_t walk_streams[4] = {};  // cluster pass + walk of chunk g run on walk_streams[g % 4] (high priority)
+    cudaEvent_t wev[4] = {};
     std::string err;
     std::vector<TmkPattern> patterns;  // host mirror of the device pattern table
     DevBuf d_tile_dir, d_patterns, d_streams, d_blk_info, d_cand, d_recs_tmp, d_rec_ord, d_recs, d_payload, d_cnt, d_base,

@@ -75,7 +75,8 @@ struct TmkCandEntry {  // one candidate window of a block, in window order
 struct TmkFast {
     const uint32_t* cblk_list;       // global ids of the blocks with candidates (appended by the scan kernels)
     unsigned int* cblk_count;
-    uint32_t* blk_ptr;               // per global block: (first entry << 5) | count, or TMK_ENT_INVALID
+    uint32_t* blk_ptr;               // per global block: (first entry << 6) | count, or TMK_ENT_INVALID
+    float* blk_gain;                 // per listed block: max_w (window energies of the block up to w) / S_w
     TmkCandEntry* entries;
     uint32_t entry_cap;
     tmk_frame_rec* spec;             // speculative verdict records (payload already in the payload buffer)

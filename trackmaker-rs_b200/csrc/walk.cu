@@ -40,6 +40,14 @@ struct alignas(16) WarpScratch {
     int8_t pre[TMK_MAX_P];  // preamble samples (+1/-1 levels expanded by spl; x * +-1.0f is exact)
 };
 
+// One scratch per warp, at namespace scope so that every access compiles to LDS / STS (through a pointer
+// handed from function to function the accesses are generic loads: slower, and on the long scoreboard).
+__shared__ WarpScratch g_scratch[kWarpsPerCta];
+struct ScratchRef {
+    uint32_t w;
+    __device__ __forceinline__ WarpScratch* operator->() const { return &g_scratch[w]; }
+};
+
 struct Ctx {
     const float* x;       // stream samples
     uint64_t N;           // samples in the stream
@@ -50,6 +58,7 @@ struct Ctx {
     const uint32_t* cand_bits;
     const uint32_t* blk_ptr;         // cluster pass results of this stream's blocks (nullptr: none)
     const TmkCandEntry* entries;
+    const float* blk_gain;
     const tmk_frame_rec* spec;
     uint64_t nblk;
     float thr;
@@ -57,7 +66,7 @@ struct Ctx {
     uint32_t max_frame_bytes;
     uint32_t P;
     int lane;
-    WarpScratch* sc;
+    ScratchRef sc;
     // exact replay cache: rolling energy `rE` of window `rpos` for a chain seeded at `rseed`
     uint64_t rseed, rpos;
     float rE;
@@ -150,20 +159,32 @@ __device__ __noinline__ float exact_energy(Ctx& c, uint64_t seed, uint64_t w) {
     // is consumed (the chain is a dependent add/add per step; without the prefetch every 32 steps
     // paid one exposed HBM round trip). The squares of a group are staged in shared memory (the
     // byte buffer of the frame decoder is idle during a search) and read back as broadcast float4s.
-    // A batch of 32 steps first runs WITHOUT the clamp `if e < 0 { e = 0 }` (decoder.rs:231-233),
+    // A group of 128 steps first runs WITHOUT the clamp `if e < 0 { e = 0 }` (decoder.rs:231-233),
     // tracking the minimum off the critical path: if no intermediate value was negative the clamp
-    // never fired and the values are the reference's; otherwise the batch is redone literally.
+    // never fired and the values are the reference's; otherwise the group is redone literally.
     // NaN/inf need no special case: they propagate identically with and without the clamp.
     constexpr int kG = 4;
+    constexpr int kQuads = 8 * kG;  // float4s of a group per operand
     static_assert(kByteBuf >= 2 * 32 * kG * 4, "staging buffer of the replay");
     if (pos + 32 * kG <= w) {
         float* sa = reinterpret_cast<float*>(c.sc->bytes);  // a[128] | b[128]
         float* sb = sa + 32 * kG;
-        float lv[kG], en[kG];
+        // global loads run TWO groups ahead of the chain (one group is ~1.5 K cycles of chain, less than a
+        // loaded HBM round trip), shared-memory loads two float4 pairs ahead: the warp issues in order, so
+        // anything the chain has to wait for stalls all of it
+        float lv[kG], en[kG], lv2[kG], en2[kG];
 #pragma unroll
         for (int g = 0; g < kG; ++g) {
             lv[g] = x[pos + g * 32 + c.lane];
             en[g] = x[pos + P + g * 32 + c.lane];
+            lv2[g] = en2[g] = 0.f;
+        }
+        if (pos + 2 * 32 * kG <= w) {
+#pragma unroll
+            for (int g = 0; g < kG; ++g) {
+                lv2[g] = x[pos + 32 * kG + g * 32 + c.lane];
+                en2[g] = x[pos + 32 * kG + P + g * 32 + c.lane];
+            }
         }
         for (;;) {
             const bool more = pos + 2 * 32 * kG <= w;
@@ -174,40 +195,43 @@ __device__ __noinline__ float exact_energy(Ctx& c, uint64_t seed, uint64_t w) {
                 sb[g * 32 + c.lane] = ex_mul(en[g], en[g]);
             }
             __syncwarp();
-            if (more) {
+#pragma unroll
+            for (int g = 0; g < kG; ++g) {
+                lv[g] = lv2[g];
+                en[g] = en2[g];
+            }
+            if (pos + 3 * 32 * kG <= w) {
 #pragma unroll
                 for (int g = 0; g < kG; ++g) {
-                    lv[g] = x[pos + 32 * kG + g * 32 + c.lane];
-                    en[g] = x[pos + 32 * kG + P + g * 32 + c.lane];
+                    lv2[g] = x[pos + 2 * 32 * kG + g * 32 + c.lane];
+                    en2[g] = x[pos + 2 * 32 * kG + P + g * 32 + c.lane];
                 }
             }
-#pragma unroll 1
-            for (int g = 0; g < kG; ++g) {
-                const float4* a4 = reinterpret_cast<const float4*>(sa + g * 32);
-                const float4* b4 = reinterpret_cast<const float4*>(sb + g * 32);
-                const float e0 = e;
-                float mn = e;
-                float4 av[8], bv[8];  // all 16 broadcast loads of the batch in flight before the dependent chain
+            const float4* a4 = reinterpret_cast<const float4*>(sa);
+            const float4* b4 = reinterpret_cast<const float4*>(sb);
+            const float e0 = e;
+            float mn = e;
+            float4 A[3], B[3];
+            A[0] = a4[0]; B[0] = b4[0];
+            A[1] = a4[1]; B[1] = b4[1];
 #pragma unroll
-                for (int j = 0; j < 8; ++j) {
-                    av[j] = a4[j];
-                    bv[j] = b4[j];
+            for (int j = 0; j < kQuads; ++j) {
+                if (j + 2 < kQuads) {
+                    A[(j + 2) % 3] = a4[j + 2];
+                    B[(j + 2) % 3] = b4[j + 2];
                 }
-#pragma unroll
-                for (int j = 0; j < 8; ++j) {
-                    const float4 a = av[j], b = bv[j];
-                    e = ex_add(ex_sub(e, a.x), b.x); mn = fminf(mn, e);
-                    e = ex_add(ex_sub(e, a.y), b.y); mn = fminf(mn, e);
-                    e = ex_add(ex_sub(e, a.z), b.z); mn = fminf(mn, e);
-                    e = ex_add(ex_sub(e, a.w), b.w); mn = fminf(mn, e);
-                }
-                if (!(mn >= 0.0f)) {  // a clamp fired (or e0 was NaN): literal form
-                    e = e0;
+                const float4 a = A[j % 3], b = B[j % 3];
+                e = ex_add(ex_sub(e, a.x), b.x); mn = fminf(mn, e);
+                e = ex_add(ex_sub(e, a.y), b.y); mn = fminf(mn, e);
+                e = ex_add(ex_sub(e, a.z), b.z); mn = fminf(mn, e);
+                e = ex_add(ex_sub(e, a.w), b.w); mn = fminf(mn, e);
+            }
+            if (!(mn >= 0.0f)) {  // a clamp fired (or e0 was NaN): literal form
+                e = e0;
 #pragma unroll 1
-                    for (int j = 0; j < 32; ++j) {
-                        e = ex_add(ex_sub(e, sa[g * 32 + j]), sb[g * 32 + j]);
-                        e = e < 0.0f ? 0.0f : e;
-                    }
+                for (int j = 0; j < 32 * kG; ++j) {
+                    e = ex_add(ex_sub(e, sa[j]), sb[j]);
+                    e = e < 0.0f ? 0.0f : e;
                 }
             }
             pos += 32 * kG;
@@ -377,6 +401,26 @@ __device__ __noinline__ void block_prefix(Ctx& c, uint64_t bb) {
     }
 }
 
+// speculative verdict record the cluster pass prepared for window wl of block bb (or TMK_ENT_INVALID)
+__device__ __noinline__ uint32_t lookup_spec(const Ctx& c, uint64_t bb, uint32_t wl) {
+    if (c.blk_ptr == nullptr || c.C != 0 || c.P > 255) return TMK_ENT_INVALID;
+    const uint32_t ptr = c.blk_ptr[bb];
+    if (ptr == TMK_ENT_INVALID) return TMK_ENT_INVALID;
+    const uint32_t n = ptr & 63u;
+    for (uint32_t r0 = 0; r0 < n; r0 += 32) {
+        uint32_t spec = TMK_ENT_INVALID;
+        bool match = false;
+        if (r0 + uint32_t(c.lane) < n) {
+            const TmkCandEntry e = c.entries[(ptr >> 6) + r0 + c.lane];
+            match = e.wl == wl;
+            spec = e.spec;
+        }
+        const uint32_t m = __ballot_sync(kFull, match);
+        if (m) return __shfl_sync(kFull, spec, __ffs(m) - 1);
+    }
+    return TMK_ENT_INVALID;
+}
+
 // Examine the windows of block `bb` that are >= q, in order. `prevmax` bounds the window energies
 // of the chain between the anchor and this block; *pm_out receives the bound including this block.
 // Returns true with *det filled on a detection.
@@ -477,7 +521,7 @@ __device__ __noinline__ bool process_block(Ctx& c, uint64_t bb, uint64_t q, uint
                 det->seed = sj;
                 det->avail = avail_for(c, wj, avail);
                 det->corr = corr;
-                det->spec = TMK_ENT_INVALID;
+                det->spec = lookup_spec(c, bb, uint32_t(wj - wb0));
                 return true;
             }
         }
@@ -498,7 +542,7 @@ __device__ __noinline__ bool process_block(Ctx& c, uint64_t bb, uint64_t q, uint
 //             loosen the bound of the quiet gap behind it
 //   emin_lo   lower bound of the window energies of the block's windows >= q
 __device__ __noinline__ int fast_block(Ctx& c, uint64_t bb, uint64_t q, float4 info, float nb, float smax, float racc_end,
-                                       float efirst, float emin_lo, Detection* det) {
+                                       float racc_in, float efirst, float emin_lo, Detection* det) {
     if (c.blk_ptr == nullptr || c.C != 0 || c.P > 255 || c.a_w != c.a_seed || c.a_err != 0.f) return 2;
     const float silent = 0.5f * c.thr * c.thr * 1e-6f;
     if (info.y < silent) return 0;  // every window is gated or cannot reach the threshold (as in search())
@@ -512,43 +556,61 @@ __device__ __noinline__ int fast_block(Ctx& c, uint64_t bb, uint64_t q, float4 i
     const float dsum = kU * (1.5f * float(c.P) * efirst + 2.2f * racc_end) * growth;
     const float d_end = fminf(dmax, dsum);  // both are rigorous; NaN in either falls through below
     const float dscan = 128.f * kU * nb;
-    if (!(d_end + dscan <= kTight * emin_lo) || !(d_end <= 3.0e38f) || !(dscan <= 3.0e38f)) return 2;
+    // the bound of a window of energy S is  d_abs + d_rel * S
+    float d_abs = d_end, d_rel = 2.5f * kU;
+    if (!(d_end + dscan <= kTight * emin_lo) || !(d_end <= 3.0e38f) || !(dscan <= 3.0e38f)) {
+        // A block whose energy RISES (the quiet gap runs into a loud preamble) fails the test above only
+        // because the drift at the END of the block is held against the energy at its START. Window by
+        // window the sum form is  u (1.5 P S_seed + 2.2 (racc_in + B_w)),  B_w = the window energies of
+        // this block up to w; the cluster pass measured  gain >= B_w / S_w  for every window of the block.
+        if (info.w == 0.f || !(racc_in >= 0.f)) return 2;
+        const uint32_t ptr0 = c.blk_ptr[bb];
+        if (ptr0 == TMK_ENT_INVALID) return 2;
+        const float gain = c.blk_gain[bb];
+        const float hist = kU * (1.5f * float(c.P) * efirst + 2.2f * racc_in) * growth;
+        const float rel = 2.2f * kU * growth * gain + 2.5f * kU;
+        if (!(hist + dscan <= 0.5f * kTight * emin_lo) || !(rel <= 0.5f * kTight)) return 2;
+        d_abs = hist;
+        d_rel = rel;
+    }
     if (info.w == 0.f) return 0;
     const uint32_t ptr = c.blk_ptr[bb];
     if (ptr == TMK_ENT_INVALID) return 2;
-    const uint32_t n = ptr & 31u;
-    TmkCandEntry e;
-    e.wl = 0; e.flags = 0; e.D = 0.f; e.Ec = 0.f; e.spec = TMK_ENT_INVALID;
-    if (uint32_t(c.lane) < n) e = c.entries[(ptr >> 5) + c.lane];
-    const uint64_t w = wb0 + e.wl;
-    const bool valid = uint32_t(c.lane) < n && w >= q && w < c.nwin;
-    int dec = DEC_NO;
-    if (valid) dec = decide_interval(c, e.D, e.Ec, d_end + 2.5f * kU * e.Ec);
-    c.n_cands += __popc(__ballot_sync(kFull, valid));
-    uint32_t pend = __ballot_sync(kFull, dec != DEC_NO);
-    while (pend) {
-        const int j = __ffs(pend) - 1;
-        pend &= pend - 1;
-        const int dj = __shfl_sync(kFull, dec, j);
-        const uint64_t wj = __shfl_sync(kFull, w, j);
-        const float Dj = __shfl_sync(kFull, e.D, j);
-        const float Ecj = __shfl_sync(kFull, e.Ec, j);
-        const uint32_t sj = __shfl_sync(kFull, e.spec, j);
-        float corr;
-        bool hit;
-        if (dj == DEC_YES) {
-            corr = ex_corr(Dj, Ecj, c.pat->pe);
-            hit = true;
-        } else {
-            hit = exact_window(c, wj, q, Dj, &corr);
-        }
-        if (hit) {
-            det->c = wj;
-            det->seed = q;
-            det->avail = c.N;
-            det->corr = corr;
-            det->spec = sj;
-            return 1;
+    const uint32_t n = ptr & 63u;
+    for (uint32_t r0 = 0; r0 < n; r0 += 32) {
+        TmkCandEntry e;
+        e.wl = 0; e.flags = 0; e.D = 0.f; e.Ec = 0.f; e.spec = TMK_ENT_INVALID;
+        if (r0 + uint32_t(c.lane) < n) e = c.entries[(ptr >> 6) + r0 + c.lane];
+        const uint64_t w = wb0 + e.wl;
+        const bool valid = r0 + uint32_t(c.lane) < n && w >= q && w < c.nwin;
+        int dec = DEC_NO;
+        if (valid) dec = decide_interval(c, e.D, e.Ec, d_abs + d_rel * e.Ec);
+        c.n_cands += __popc(__ballot_sync(kFull, valid));
+        uint32_t pend = __ballot_sync(kFull, dec != DEC_NO);
+        while (pend) {
+            const int j = __ffs(pend) - 1;
+            pend &= pend - 1;
+            const int dj = __shfl_sync(kFull, dec, j);
+            const uint64_t wj = __shfl_sync(kFull, w, j);
+            const float Dj = __shfl_sync(kFull, e.D, j);
+            const float Ecj = __shfl_sync(kFull, e.Ec, j);
+            const uint32_t sj = __shfl_sync(kFull, e.spec, j);
+            float corr;
+            bool hit;
+            if (dj == DEC_YES) {
+                corr = ex_corr(Dj, Ecj, c.pat->pe);
+                hit = true;
+            } else {
+                hit = exact_window(c, wj, q, Dj, &corr);
+            }
+            if (hit) {
+                det->c = wj;
+                det->seed = q;
+                det->avail = c.N;
+                det->corr = corr;
+                det->spec = sj;
+                return 1;
+            }
         }
     }
     return 0;
@@ -584,7 +646,7 @@ __device__ __noinline__ bool search(Ctx& c, uint64_t q, uint64_t avail, Detectio
         // bounds of the whole gap behind it, so it goes straight to the exact energies)
         int r = 2;
         if (!(i0.y > 8.f * i0.x)) {
-            r = fast_block(c, b0, q, i0, nb0, i0.y * 1.001f, racc, efirst, i0.x - dscan0, det);
+            r = fast_block(c, b0, q, i0, nb0, i0.y * 1.001f, racc, 0.f, efirst, i0.x - dscan0, det);
             if (r == 1) return true;
             if (r == 0) runmax = i0.y * 1.001f;
         }
@@ -608,7 +670,7 @@ __device__ __noinline__ bool search(Ctx& c, uint64_t q, uint64_t avail, Detectio
             }
             eq = __shfl_sync(kFull, eq, 0);
             const float racc_x = es * 1.0001f;
-            r = fast_block(c, b0, q, i0, nb0, emx * 1.0001f, racc_x, eq * 1.0001f, emn * 0.9999f, det);
+            r = fast_block(c, b0, q, i0, nb0, emx * 1.0001f, racc_x, 0.f, eq * 1.0001f, emn * 0.9999f, det);
             if (r == 1) return true;
             if (r == 0) {
                 runmax = emx * 1.0001f;
@@ -700,7 +762,8 @@ __device__ __noinline__ bool search(Ctx& c, uint64_t q, uint64_t avail, Detectio
             ij.w = __shfl_sync(kFull, info.w, j);
             const float nbj = __shfl_sync(kFull, nb, j);
             const float racc_end_j = racc + __shfl_sync(kFull, cincl, j);
-            const int r = fast_block(c, b0 + j, q, ij, nbj, max_nan(pmax_j, ij.y * 1.001f), racc_end_j, efirst,
+            const float racc_in_j = racc_end_j - __shfl_sync(kFull, contrib, j);
+            const int r = fast_block(c, b0 + j, q, ij, nbj, max_nan(pmax_j, ij.y * 1.001f), racc_end_j, racc_in_j, efirst,
                                      ij.x - 128.f * kU * nbj, det);
             if (r == 1) return true;
             if (r == 0) {
@@ -832,10 +895,26 @@ __device__ __noinline__ uint32_t line_decode(const Ctx& c, uint64_t fs, uint32_t
         const uint32_t nl = nlev - c0 < kChunk ? nlev - c0 : kChunk;
         __syncwarp();
         if (spl == 3) {
-#pragma unroll 4
-            for (uint32_t i = lane; i < nl; i += 32) {
-                const float* p = s + uint64_t(c0 + i) * 3;
-                lev[i] = ex_div(ex_add(ex_add(ex_add(0.0f, p[0]), p[1]), p[2]), 3.0f);
+            // 8 rounds of loads (24 per lane) in flight before the first store: the stores to `lev` may alias
+            // the samples as far as the compiler knows, so a plain loop pays one HBM round trip per round
+            constexpr int kB = 8;
+            for (uint32_t i0 = 0; i0 < nl; i0 += 32 * kB) {
+                float a[kB][3];
+#pragma unroll
+                for (int u = 0; u < kB; ++u) {
+                    const uint32_t i = i0 + u * 32 + lane;
+                    if (i < nl) {
+                        const float* p = s + uint64_t(c0 + i) * 3;
+                        a[u][0] = p[0];
+                        a[u][1] = p[1];
+                        a[u][2] = p[2];
+                    }
+                }
+#pragma unroll
+                for (int u = 0; u < kB; ++u) {
+                    const uint32_t i = i0 + u * 32 + lane;
+                    if (i < nl) lev[i] = ex_div(ex_add(ex_add(ex_add(0.0f, a[u][0]), a[u][1]), a[u][2]), 3.0f);
+                }
             }
         } else {
 #pragma unroll 2
@@ -971,7 +1050,7 @@ __device__ __noinline__ void emit(const Ctx& c, Emit& em, uint32_t status, const
 
 __device__ __forceinline__ void init_ctx(Ctx& c, const float* samples, const TmkStreamDev& sd, const TmkPattern* patterns,
                                          const float4* blk_info, const uint32_t* cand_bits, const TmkFast& f, int lane,
-                                         WarpScratch* sc) {
+                                         uint32_t warp) {
     c.x = samples + sd.offset;
     c.N = sd.n_samples;
     c.pat = patterns + sd.pattern;
@@ -982,13 +1061,15 @@ __device__ __forceinline__ void init_ctx(Ctx& c, const float* samples, const Tmk
     c.cand_bits = cand_bits + sd.blk_base * TMK_BLK_WORDS;
     c.blk_ptr = f.blk_ptr ? f.blk_ptr + sd.blk_base : nullptr;
     c.entries = f.entries;
+    c.blk_gain = f.blk_gain ? f.blk_gain + sd.blk_base : nullptr;
     c.spec = f.spec;
     c.nblk = (c.nwin + TMK_BLK - 1) / TMK_BLK;
     c.thr = sd.threshold;
     c.local_addr = sd.local_addr;
     c.max_frame_bytes = sd.max_frame_bytes;
     c.lane = lane;
-    c.sc = sc;
+    c.sc.w = warp;
+    const ScratchRef sc = c.sc;
     c.rvalid = false;
     c.rseed = c.rpos = 0;
     c.rE = 0.f;
@@ -1097,8 +1178,7 @@ cluster_kernel(const float* __restrict__ samples, const TmkStreamDev* __restrict
                const uint32_t* __restrict__ tile_stream, const TmkPattern* __restrict__ patterns,
                const float4* __restrict__ blk_info, const uint32_t* __restrict__ cand_bits, TmkFast f, uint8_t* payload,
                uint64_t payload_cap, TmkCounters* counters) {
-    __shared__ WarpScratch scratch[kWarpsPerCta];
-    __shared__ TmkCandEntry ents[kWarpsPerCta][32];
+    __shared__ TmkCandEntry ents[kWarpsPerCta][64];
     const uint32_t warp = threadIdx.x >> 5;
     const int lane = threadIdx.x & 31;
     const uint32_t n_items = *f.cblk_count;
@@ -1107,7 +1187,7 @@ cluster_kernel(const float* __restrict__ samples, const TmkStreamDev* __restrict
         const uint32_t sidx = tile_stream[gb / TMK_TILE_BLKS];
         const TmkStreamDev sd = streams[sidx];
         Ctx c;
-        init_ctx(c, samples, sd, patterns, blk_info, cand_bits, f, lane, &scratch[warp]);
+        init_ctx(c, samples, sd, patterns, blk_info, cand_bits, f, lane, warp);
         const uint64_t bb = uint64_t(gb) - sd.blk_base;
         if (c.C != 0 || c.P > 255) {  // chunked feeding / long preambles keep the walk's own evaluation
             if (lane == 0) f.blk_ptr[gb] = TMK_ENT_INVALID;
@@ -1136,13 +1216,36 @@ cluster_kernel(const float* __restrict__ samples, const TmkStreamDev* __restrict
             }
             const uint32_t m = __ballot_sync(kFull, valid);
             const uint32_t idx = n_ent + __popc(m & ((1u << lane) - 1u));
-            if (valid && idx < 32) ents[warp][idx] = e;
+            if (valid && idx < 64) ents[warp][idx] = e;
             n_ent += __popc(m);
         }
         __syncwarp();
-        if (n_ent > 31) {
+        if (n_ent > 63) {
             if (lane == 0) f.blk_ptr[gb] = TMK_ENT_INVALID;
             continue;
+        }
+        // gain = max over the block's windows of (sum of the window energies of the block up to w) / S_w,
+        // for fast_block's window-by-window form of the drift bound (NaN propagates and disables it)
+        float gain = 0.f;
+        {
+            float carry = 0.f;
+#pragma unroll 1
+            for (uint32_t r = 0; r < TMK_BLK_WORDS; ++r) {
+                const uint32_t wl = r * 32 + lane;
+                const bool valid = wb0 + wl < c.nwin;
+                const float S = valid ? __double2float_rn(c.sc->Q[wl + c.P] - c.sc->Q[wl]) : 0.f;
+                float cs = S * 1.0001f;
+#pragma unroll
+                for (int o = 1; o < 32; o <<= 1) {
+                    const float t = __shfl_up_sync(kFull, cs, o);
+                    if (lane >= o) cs += t;
+                }
+                cs += carry;
+                carry = __shfl_sync(kFull, cs, 31);
+                if (valid) gain = max_nan(gain, S > 0.f ? __fdiv_ru(cs, S) : (S == 0.f ? __int_as_float(0x7f800000) : S));
+            }
+#pragma unroll
+            for (int o = 16; o > 0; o >>= 1) gain = max_nan(gain, __shfl_xor_sync(kFull, gain, o));
         }
         // speculative decodes, mimicking a walk that meets the entries in order
         uint64_t skip_until = 0;
@@ -1169,12 +1272,15 @@ cluster_kernel(const float* __restrict__ samples, const TmkStreamDev* __restrict
         unsigned int base = 0;
         if (lane == 0) base = n_ent ? atomicAdd(&f.pool[0], n_ent) : 0u;
         base = __shfl_sync(kFull, base, 0);
-        if (base + n_ent > f.entry_cap || base + n_ent >= (1u << 27)) {
+        if (base + n_ent > f.entry_cap || base + n_ent >= (1u << 26)) {
             if (lane == 0) f.blk_ptr[gb] = TMK_ENT_INVALID;
             continue;
         }
-        if (uint32_t(lane) < n_ent) f.entries[base + lane] = ents[warp][lane];
-        if (lane == 0) f.blk_ptr[gb] = (base << 5) | n_ent;
+        for (uint32_t i = lane; i < n_ent; i += 32) f.entries[base + i] = ents[warp][i];
+        if (lane == 0) {
+            f.blk_gain[gb] = gain;
+            f.blk_ptr[gb] = (base << 6) | n_ent;
+        }
     }
 }
 
@@ -1187,7 +1293,6 @@ walk_kernel(const float* __restrict__ samples, const TmkStreamDev* __restrict__ 
             const TmkPattern* __restrict__ patterns, const float4* __restrict__ blk_info,
             const uint32_t* __restrict__ cand_bits, tmk_frame_rec* recs, uint32_t* rec_ord, uint64_t rec_cap,
             uint8_t* payload, uint64_t payload_cap, uint32_t* stream_cnt, TmkCounters* counters) {
-    __shared__ WarpScratch scratch[kWarpsPerCta];
     const uint32_t warp = threadIdx.x >> 5;
     const int lane_id = threadIdx.x & 31;
     // persistent warps: streams differ a lot in cost (idle noise vs dense traffic), so every warp
@@ -1199,7 +1304,7 @@ walk_kernel(const float* __restrict__ samples, const TmkStreamDev* __restrict__ 
     if (sidx >= s1) return;
     const TmkStreamDev sd = streams[sidx];
     Ctx c;
-    init_ctx(c, samples, sd, patterns, blk_info, cand_bits, fast, lane_id, &scratch[warp]);
+    init_ctx(c, samples, sd, patterns, blk_info, cand_bits, fast, lane_id, warp);
     Emit em{recs, rec_ord, rec_cap, payload, payload_cap, counters, sidx, 0};
     uint32_t n_ok = 0, n_crc = 0, n_hdr = 0, n_nfu = 0;
 
