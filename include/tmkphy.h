@@ -215,6 +215,33 @@ int tmk_synth_batch(tmk_engine* e, const tmk_phy_config* cfg, uint64_t seed, uin
                     tmk_frame_rec* truth, uint64_t truth_cap, uint64_t* n_truth);
 
 /* ------------------------------------------------------------------------------------------------
+ * Links: n persistent PhyDecoder instances fed with process_samples calls (the live cadence,
+ * src/mac/csma.rs:446-465 polls 25 ms = 1200 samples; src/mac/acoustic_interface.rs:334-353). All links of
+ * a call are decoded in ONE batch on the GPU. Carried per link, exactly as decoder.rs:16-33 does:
+ * the sample buffer drained to P-1 samples before buffer_offset (:90-109), buffer_offset, and the state
+ * Searching | Decoding(frame_start).
+ *   tmk_links_create           replaces n x PhyDecoder::new        src/phy/decoder.rs:36-65 (cfg.chunk is ignored)
+ *   tmk_links_process_samples  replaces n x process_samples        src/phy/decoder.rs:68-112
+ *   tmk_links_reset            replaces reset                      src/phy/decoder.rs:114-119
+ */
+typedef struct tmk_links tmk_links;
+int tmk_links_create(tmk_engine* e, const tmk_phy_config* cfgs, uint32_t n_links, tmk_links** out);
+void tmk_links_destroy(tmk_links* l);
+/* link i receives samples[offsets[i] .. offsets[i] + lens[i]) (host or device memory; 0 = empty slice).
+ * Returns the records of the frames whose decode finished in this call (host memory), sorted by
+ * (link, order of detection): `stream` is the link index, preamble_start / frame_start count from the
+ * first sample ever fed to the link; status == TMK_FRAME_OK records are the Frames process_samples
+ * returns. A frame still being gathered is carried state, not a record. On an error (TMK_E_CAPACITY
+ * included) nothing was consumed and the call may be repeated. */
+int tmk_links_process_samples(tmk_links* l, const float* samples, uint64_t total_samples, const uint64_t* offsets,
+                              const uint64_t* lens, tmk_frame_rec* recs, uint64_t rec_cap, uint64_t* n_recs,
+                              uint8_t* payload, uint64_t payload_cap, uint64_t* payload_len);
+/* link == UINT32_MAX resets every link */
+int tmk_links_reset(tmk_links* l, uint32_t link);
+/* sample_buffer.len(), buffer_offset and (state == Decoding) of one link */
+int tmk_links_state(const tmk_links* l, uint32_t link, uint64_t* buffered, uint64_t* buffer_offset, int* decoding);
+
+/* ------------------------------------------------------------------------------------------------
  * Chirp + BPSK modem of examples/ask.rs (project 1): 440-sample chirp preamble 2 kHz -> 10 kHz -> 2 kHz,
  * BPSK on a 10 kHz carrier at 44 samples per bit, frames of 100 bits + 8 zero bits.
  *   tmk_ask_modulate      replaces the TX loop                  examples/ask.rs:608-637 (live :176-218)

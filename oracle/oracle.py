@@ -47,6 +47,7 @@ def lib():
             "orc_frame_to_bytes": (u64, [vp, vp, vp]),
             "orc_modulate": (u64, [pcfg, vp, u32, vp, u32, vp, u64]),
             "orc_decode_stream": (u64, [pcfg, vp, u64, u32, vp, u64, vp, u64, C.POINTER(u64)]),
+            "orc_decode_feeds": (u64, [pcfg, vp, u64, vp, u32, u32, vp, vp, u64, vp, u64, C.POINTER(u64)]),
             "orc_decode_batch_mt": (u64, [vp, vp, u32, C.c_int, vp, u64, vp, u64, C.POINTER(u64),
                                           C.POINTER(C.c_double)]),
             "orc_correlate": (u64, [pcfg, vp, u64, vp]),
@@ -153,6 +154,22 @@ def decode_stream(cfg, samples, stream_id=0):
                                 C.byref(plen))
     assert n <= cap and plen.value <= len(pl)
     return recs[:n].copy(), pl[:plen.value].copy()
+
+
+def decode_feeds(cfg, samples, feed_sizes, stream_id=0):
+    """One PhyDecoder fed with process_samples calls of the given sizes.
+    -> (records, payload, feed_of_rec): feed_of_rec[i] is the call that returned record i."""
+    s = np.ascontiguousarray(samples, dtype=np.float32)
+    fs = np.ascontiguousarray(feed_sizes, dtype=np.uint64)
+    cap = max(16, len(s) // 8 + 16)
+    recs = np.zeros(cap, REC_DTYPE)
+    fo = np.zeros(cap, np.uint32)
+    pl = np.zeros(max(1024, len(s) // 4), np.uint8)
+    plen = C.c_uint64(0)
+    n = lib().orc_decode_feeds(C.byref(cfg), _ptr(s), len(s), _ptr(fs), len(fs), stream_id, _ptr(recs), _ptr(fo), cap,
+                               _ptr(pl), len(pl), C.byref(plen))
+    assert n <= cap and plen.value <= len(pl)
+    return recs[:n].copy(), pl[:plen.value].copy(), fo[:n].copy()
 
 
 def decode_batch(samples, streams, n_threads=0, rec_cap=None, payload_cap=None):

@@ -106,6 +106,32 @@ uint64_t orc_decode_stream(const tmk_phy_config* cfg, const float* s, uint64_t n
     return r.size();
 }
 
+// One capture through ONE PhyDecoder fed with process_samples calls of the given sizes (the live cadence,
+// src/mac/csma.rs:446-465). feed_of_rec[i] receives the index of the call that returned record i. The
+// capture is not finished: a frame still being gathered when the feeds end yields no record.
+uint64_t orc_decode_feeds(const tmk_phy_config* cfg, const float* s, uint64_t n, const uint64_t* feed_sizes,
+                          uint32_t n_feeds, uint32_t stream_id, tmk_frame_rec* recs, uint32_t* feed_of_rec,
+                          uint64_t rec_cap, uint8_t* payload, uint64_t payload_cap, uint64_t* payload_len) {
+    std::vector<tmk_frame_rec> r;
+    std::vector<uint8_t> p;
+    Decoder d(*cfg);
+    d.stream_id = stream_id;
+    d.recs = &r;
+    d.payload = &p;
+    uint64_t pos = 0, done = 0;
+    for (uint32_t f = 0; f < n_feeds; ++f) {
+        const uint64_t len = std::min<uint64_t>(feed_sizes[f], n - pos);
+        d.process_samples(s + pos, len);
+        pos += len;
+        for (; done < r.size(); ++done)
+            if (feed_of_rec && done < rec_cap) feed_of_rec[done] = f;
+    }
+    for (size_t i = 0; i < r.size() && i < rec_cap; ++i) recs[i] = r[i];
+    std::copy(p.begin(), p.begin() + std::min<uint64_t>(payload_cap, p.size()), payload);
+    if (payload_len) *payload_len = p.size();
+    return r.size();
+}
+
 // Ragged batch over a thread pool (one PhyDecoder per stream, like one decoder per MAC node,
 // src/mac/csma.rs:37-47). Records come back sorted by stream; payload offsets are global.
 // Returns records; *seconds receives the wall time of the decode region.

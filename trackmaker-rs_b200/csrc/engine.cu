@@ -117,6 +117,10 @@ int prepare_batch(tmk_engine* e, uint64_t total_samples, const tmk_stream* strea
         d.threshold = st.cfg.threshold;
         d.max_frame_bytes = st.cfg.max_frame_bytes;
         d.chunk = st.cfg.chunk;
+        d.init_q = 0;
+        d.init_fs = TMK_NO_FRAME;
+        d.init_corr = 0.f;
+        d.pad_ = 0;
         tiles += d.n_tiles;
         const TmkPattern& pp = e->patterns[pi];
         if (d.n_tiles) b->kinds |= (pp.spl == 3 && pp.preamble_bytes == 2) ? (pp.line_code == TMK_LINE_4B5B ? 1u : 2u) : 4u;
@@ -189,7 +193,7 @@ void tmk_engine_destroy(tmk_engine* e) {
     if (e->stream) cudaStreamSynchronize(e->stream);
     DevBuf* bufs[] = {&e->d_tile_dir, &e->d_patterns, &e->d_streams, &e->d_blk_info, &e->d_cand, &e->d_recs_tmp, &e->d_rec_ord,
                       &e->d_recs, &e->d_payload, &e->d_cnt, &e->d_base, &e->d_counters, &e->d_samples,
-                      &e->d_misc, &e->d_misc2, &e->d_next, &e->d_cblk, &e->d_blk_ptr, &e->d_entries, &e->d_spec, &e->d_pool,
+                      &e->d_misc, &e->d_misc2, &e->d_next, &e->d_cblk, &e->d_blk_ptr, &e->d_entries, &e->d_spec, &e->d_pool, &e->d_link,
                       &e->d_ask_tab, &e->d_ask_bits, &e->d_ask_l2,
                       &e->d_ask_recs, &e->d_ask_recs2};
     for (DevBuf* b : bufs) b->release();
@@ -300,6 +304,22 @@ int tmk_decode_batch(tmk_engine* e, const float* samples, uint64_t total_samples
     Batch b;
     int rc = prepare_batch(e, total_samples, streams, n_streams, &b);
     if (rc != TMK_OK) return rc;
+    // carried PhyDecoder state of the links module (links.cu): entry state in, exit state out
+    const TmkLinkState* link_init = e->link_init;
+    TmkLinkState* link_final = e->link_final;
+    e->link_init = nullptr;
+    e->link_final = nullptr;
+    TmkLinkState* d_link = nullptr;
+    if (link_init)
+        for (uint32_t s = 0; s < n_streams; ++s) {
+            b.sd[s].init_q = link_init[s].off;
+            b.sd[s].init_fs = link_init[s].fs;
+            b.sd[s].init_corr = link_init[s].corr;
+        }
+    if (link_final) {
+        CK(e->d_link.reserve(sizeof(TmkLinkState) * n_streams));
+        d_link = static_cast<TmkLinkState*>(e->d_link.p);
+    }
 
     CK(e->d_streams.reserve(sizeof(TmkStreamDev) * n_streams));
     CK(cudaMemcpyAsync(e->d_streams.p, b.sd.data(), sizeof(TmkStreamDev) * n_streams, cudaMemcpyHostToDevice, e->stream));
@@ -437,7 +457,7 @@ int tmk_decode_batch(tmk_engine* e, const float* samples, uint64_t total_samples
         if (chunks.size() == 1) CK(cudaEventRecord(e->ev[5], e->stream));
         e->launches += tmk_launch_walk(dx, ds, ch.s0, ch.s1, dnext + g, fast, dp, dbi, dcb,
                                        static_cast<tmk_frame_rec*>(e->d_recs_tmp.p), static_cast<uint32_t*>(e->d_rec_ord.p),
-                                       dev_rec_cap, dpay, dev_pay_cap, static_cast<uint32_t*>(e->d_cnt.p), dc, ws);
+                                       dev_rec_cap, dpay, dev_pay_cap, static_cast<uint32_t*>(e->d_cnt.p), dc, d_link, ws);
         CK(cudaGetLastError());
     }
     if (chunks.size() != 1) {
@@ -469,11 +489,13 @@ int tmk_decode_batch(tmk_engine* e, const float* samples, uint64_t total_samples
         std::memset(&nofast, 0, sizeof nofast);
         e->launches += tmk_launch_walk(dx, ds, 0, n_streams, dnext + chunks.size(), nofast, dp, dbi, dcb,
                                        static_cast<tmk_frame_rec*>(e->d_recs_tmp.p), static_cast<uint32_t*>(e->d_rec_ord.p),
-                                       dev_rec_cap, dpay, dev_pay_cap, static_cast<uint32_t*>(e->d_cnt.p), dc, e->stream);
+                                       dev_rec_cap, dpay, dev_pay_cap, static_cast<uint32_t*>(e->d_cnt.p), dc, d_link, e->stream);
         CK(cudaGetLastError());
         CK(cudaMemcpyAsync(&hc, dc, sizeof hc, cudaMemcpyDeviceToHost, e->stream));
         CK(cudaStreamSynchronize(e->stream));
     }
+    if (link_final)
+        CK(cudaMemcpyAsync(link_final, d_link, sizeof(TmkLinkState) * n_streams, cudaMemcpyDeviceToHost, e->stream));
     CK(cudaEventRecord(e->ev[3], e->stream));
     *n_recs = hc.n_recs;
     *payload_len = hc.n_payload;

@@ -52,6 +52,20 @@ struct TmkStreamDev {
     float threshold;
     uint32_t max_frame_bytes;
     uint64_t chunk;       // 0 = one shot
+    // carried PhyDecoder state (links.cu): buffer_offset at entry, and DecoderState::Decoding(frame_start)
+    // with the correlation of its detection, or init_fs == TMK_NO_FRAME for DecoderState::Searching
+    uint64_t init_q;
+    uint64_t init_fs;
+    float init_corr;
+    uint32_t pad_;
+};
+#define TMK_NO_FRAME 0xffffffffffffffffull
+// PhyDecoder state after the call (decoder.rs:16-33): buffer_offset, Decoding(frame_start) or TMK_NO_FRAME
+struct TmkLinkState {
+    uint64_t off;
+    uint64_t fs;
+    float corr;
+    uint32_t pad_;
 };
 
 struct TmkCounters {
@@ -144,7 +158,8 @@ int tmk_launch_walk(const float* samples, const TmkStreamDev* streams, uint32_t 
                     TmkFast fast,
                     const TmkPattern* patterns, const float4* blk_info, const uint32_t* cand_bits,
                     tmk_frame_rec* recs, uint32_t* rec_ord, uint64_t rec_cap, uint8_t* payload,
-                    uint64_t payload_cap, uint32_t* stream_cnt, TmkCounters* counters, cudaStream_t st);
+                    uint64_t payload_cap, uint32_t* stream_cnt, TmkCounters* counters, TmkLinkState* link_out,
+                    cudaStream_t st);
 int tmk_launch_order(const tmk_frame_rec* recs_in, const uint32_t* rec_ord, uint64_t n_recs,
                      const uint32_t* stream_cnt, uint64_t* stream_base, uint32_t n_streams,
                      tmk_frame_rec* recs_out, cudaStream_t st);

@@ -1292,7 +1292,8 @@ walk_kernel(const float* __restrict__ samples, const TmkStreamDev* __restrict__ 
             unsigned int* __restrict__ next, TmkFast fast,
             const TmkPattern* __restrict__ patterns, const float4* __restrict__ blk_info,
             const uint32_t* __restrict__ cand_bits, tmk_frame_rec* recs, uint32_t* rec_ord, uint64_t rec_cap,
-            uint8_t* payload, uint64_t payload_cap, uint32_t* stream_cnt, TmkCounters* counters) {
+            uint8_t* payload, uint64_t payload_cap, uint32_t* stream_cnt, TmkCounters* counters,
+            TmkLinkState* link_out) {
     const uint32_t warp = threadIdx.x >> 5;
     const int lane_id = threadIdx.x & 31;
     // persistent warps: streams differ a lot in cost (idle noise vs dense traffic), so every warp
@@ -1311,10 +1312,31 @@ walk_kernel(const float* __restrict__ samples, const TmkStreamDev* __restrict__ 
     const int lc = c.pat->line_code;
     const uint32_t spl = c.pat->spl;
     const uint32_t hs = c.pat->hdr_samples;
-    uint64_t q = 0;                           // buffer_offset (absolute)
+    uint64_t q = sd.init_q;                   // buffer_offset (absolute)
     uint64_t avail = c.C ? c.C : c.N;         // samples fed so far
+    bool resume = sd.init_fs != TMK_NO_FRAME;  // the previous process_samples call ended in Decoding(frame_start)
+    TmkLinkState fin;
+    fin.off = q;
+    fin.fs = TMK_NO_FRAME;
+    fin.corr = 0.f;
+    fin.pad_ = 0;
     Detection d;
-    while (search(c, q, avail, &d)) {
+    for (;;) {
+        uint64_t fs;
+        if (resume) {
+            resume = false;
+            d.c = sd.init_q;
+            d.seed = sd.init_q;
+            d.avail = avail;
+            d.corr = sd.init_corr;
+            d.spec = TMK_ENT_INVALID;
+            fs = sd.init_fs;
+        } else {
+        if (!search(c, q, avail, &d)) {
+            // search_for_preamble scanned every window of the buffer: buffer_offset += windows (decoder.rs:236)
+            fin.off = (c.N >= q && c.N - q >= c.P) ? c.N - c.P + 1 : q;
+            break;
+        }
         c.n_det++;
         avail = d.avail;
         if (d.spec != TMK_ENT_INVALID && d.c + c.P - c.pat->sync_len - d.seed >= c.pat->margin) {
@@ -1336,7 +1358,12 @@ walk_kernel(const float* __restrict__ samples, const TmkStreamDev* __restrict__ 
             else if (r.status == TMK_FRAME_CRC_FAIL) n_crc++;
             else if (r.status == TMK_FRAME_NOT_FOR_US) n_nfu++;
             else if (r.status != TMK_FRAME_TRUNCATED) n_hdr++;
-            if (r.status == TMK_FRAME_TRUNCATED) break;
+            if (r.status == TMK_FRAME_TRUNCATED) {
+                fin.off = d.c;
+                fin.fs = r.frame_start;
+                fin.corr = d.corr;
+                break;
+            }
             q = d.c + r.consumed;
             continue;
         }
@@ -1345,7 +1372,8 @@ walk_kernel(const float* __restrict__ samples, const TmkStreamDev* __restrict__ 
             for (uint64_t i = uint64_t(lane_id) * 32; i < 2560 && f0 + i < c.N; i += 1024)
                 asm volatile("prefetch.global.L2 [%0];" ::"l"(c.x + f0 + i));
         }
-        const uint64_t fs = refine(c, d);
+        fs = refine(c, d);
+        }
         // ---- decode_frame (decoder.rs:242-356); `avail` grows by one chunk per call
         bool truncated = false;
         while (avail < fs + hs) {
@@ -1354,6 +1382,9 @@ walk_kernel(const float* __restrict__ samples, const TmkStreamDev* __restrict__ 
         }
         if (truncated) {
             emit(c, em, TMK_FRAME_TRUNCATED, d, fs, 0, false, nullptr, 0);
+            fin.off = d.c;
+            fin.fs = fs;
+            fin.corr = d.corr;
             break;
         }
         const uint8_t* hb = c.sc->bytes;
@@ -1384,6 +1415,9 @@ walk_kernel(const float* __restrict__ samples, const TmkStreamDev* __restrict__ 
         }
         if (truncated) {
             emit(c, em, TMK_FRAME_TRUNCATED, d, fs, 0, false, nullptr, 0);
+            fin.off = d.c;
+            fin.fs = fs;
+            fin.corr = d.corr;
             break;
         }
         const uint32_t nbits = line_decode(c, fs, total_bits);
@@ -1409,6 +1443,7 @@ walk_kernel(const float* __restrict__ samples, const TmkStreamDev* __restrict__ 
         n_ok++;
     }
     if (c.lane == 0) {
+        if (link_out) link_out[sidx] = fin;
         stream_cnt[sidx] = em.ord;
         atomicAdd(&counters->stats[TMK_STAT_SAMPLES], (unsigned long long)c.N);
         atomicAdd(&counters->stats[TMK_STAT_DETECTIONS], (unsigned long long)c.n_det);
@@ -1510,7 +1545,8 @@ int tmk_launch_walk(const float* samples, const TmkStreamDev* streams, uint32_t 
                     TmkFast fast,
                     const TmkPattern* patterns, const float4* blk_info, const uint32_t* cand_bits,
                     tmk_frame_rec* recs, uint32_t* rec_ord, uint64_t rec_cap, uint8_t* payload,
-                    uint64_t payload_cap, uint32_t* stream_cnt, TmkCounters* counters, cudaStream_t st) {
+                    uint64_t payload_cap, uint32_t* stream_cnt, TmkCounters* counters, TmkLinkState* link_out,
+                    cudaStream_t st) {
     if (s1 <= s0) return 0;
     const uint32_t n_streams = s1 - s0;
     static int max_ctas = 0;
@@ -1524,7 +1560,7 @@ int tmk_launch_walk(const float* samples, const TmkStreamDev* streams, uint32_t 
     uint32_t grid = (n_streams + kWarpsPerCta - 1) / kWarpsPerCta;
     if (grid > uint32_t(max_ctas)) grid = uint32_t(max_ctas);
     walk_kernel<<<grid, kWarpsPerCta * 32, 0, st>>>(samples, streams, s0, s1, next, fast, patterns, blk_info, cand_bits, recs,
-                                                    rec_ord, rec_cap, payload, payload_cap, stream_cnt, counters);
+                                                    rec_ord, rec_cap, payload, payload_cap, stream_cnt, counters, link_out);
     return 1;
 }
 

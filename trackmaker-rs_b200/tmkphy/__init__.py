@@ -370,3 +370,65 @@ class PhyDecoder:
     def reset(self):  # decoder.rs:114-119 — nothing is carried between calls
         self.last_records = np.zeros(0, REC_DTYPE)
         self.last_payload = np.zeros(0, np.uint8)
+
+
+class PhyDecoderBank:
+    """n persistent PhyDecoders (decoder.rs:16-33) fed with process_samples calls, all decoded in one
+    batch per call (tmk_links_*): the live cadence of src/mac/csma.rs:446-465 for many links at once."""
+
+    def __init__(self, engine, cfgs):
+        self.engine = engine
+        self._lib = engine._lib
+        self.cfgs = (PhyConfig * len(cfgs))(*cfgs)
+        self.n = len(cfgs)
+        h = C.c_void_p()
+        engine._check(self._lib.tmk_links_create(engine._h, C.byref(self.cfgs) if self.n else None, self.n, C.byref(h)))
+        self._h = h
+
+    def close(self):
+        if getattr(self, "_h", None):
+            self._lib.tmk_links_destroy(self._h)
+            self._h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def process_samples(self, chunks, rec_cap=None, payload_cap=None):
+        """chunks: one float32 array per link (may be empty). -> (records ndarray[REC_DTYPE], payload ndarray[u8]);
+        records[i]["stream"] is the link index, positions are absolute per link."""
+        assert len(chunks) == self.n
+        lens = np.array([len(c) for c in chunks], np.uint64)
+        offs = np.zeros(self.n, np.uint64)
+        if self.n:
+            offs[1:] = np.cumsum(lens)[:-1]
+        total = int(lens.sum())
+        s = np.zeros(max(total, 1), np.float32)
+        for c, o in zip(chunks, offs):
+            s[int(o):int(o) + len(c)] = c
+        rec_cap = int(rec_cap) if rec_cap is not None else max(1024, total // 96 + 4 * self.n)
+        payload_cap = int(payload_cap) if payload_cap is not None else max(65536, total // 12 + 1100 * self.n)
+        recs = np.zeros(rec_cap, REC_DTYPE)
+        pl = np.zeros(payload_cap, np.uint8)
+        nr, npl = C.c_uint64(0), C.c_uint64(0)
+        rc = self._lib.tmk_links_process_samples(self._h, _ptr(s), total, _ptr(offs), _ptr(lens), _ptr(recs), rec_cap,
+                                                 C.byref(nr), _ptr(pl), payload_cap, C.byref(npl))
+        if rc == _abi.E_CAPACITY and (nr.value > rec_cap or npl.value > payload_cap):
+            return self.process_samples(chunks, max(rec_cap, nr.value), max(payload_cap, npl.value))
+        self.engine._check(rc)
+        return recs[:nr.value].copy(), pl[:npl.value].copy()
+
+    def process_frames(self, chunks):
+        """-> list (per link) of the Frames this call returned, like PhyDecoder::process_samples"""
+        recs, pl = self.process_samples(chunks)
+        return [records_to_frames(recs[recs["stream"] == i], pl) for i in range(self.n)]
+
+    def reset(self, link=None):  # decoder.rs:114-119
+        self.engine._check(self._lib.tmk_links_reset(self._h, 0xffffffff if link is None else int(link)))
+
+    def state(self, link):
+        b, o, d = C.c_uint64(0), C.c_uint64(0), C.c_int(0)
+        self.engine._check(self._lib.tmk_links_state(self._h, int(link), C.byref(b), C.byref(o), C.byref(d)))
+        return {"buffered": b.value, "buffer_offset": o.value, "decoding": bool(d.value)}

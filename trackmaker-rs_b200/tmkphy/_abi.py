@@ -97,6 +97,11 @@ SYMBOLS = {
     "tmk_timer_start": (C.c_int, [_vp]),
     "tmk_timer_stop": (C.c_int, [_vp, C.POINTER(C.c_float)]),
     "tmk_launch_count": (_u64, [_vp]),
+    "tmk_links_create": (C.c_int, [_vp, _vp, _u32, C.POINTER(_vp)]),
+    "tmk_links_destroy": (None, [_vp]),
+    "tmk_links_process_samples": (C.c_int, [_vp, _vp, _u64, _vp, _vp, _vp, _u64, _pu64, _vp, _u64, _pu64]),
+    "tmk_links_reset": (C.c_int, [_vp, _u32]),
+    "tmk_links_state": (C.c_int, [_vp, _u32, _pu64, _pu64, C.POINTER(C.c_int)]),
     "tmk_ask_tables": (C.c_int, [_vp, _vp, _vp, _u64]),
     "tmk_ask_modulated_len": (_u64, [_u32, _vp, _vp]),
     "tmk_ask_modulate": (C.c_int, [_vp, _vp, _u32, _vp, _vp, _vp, _u64, _pu64]),
