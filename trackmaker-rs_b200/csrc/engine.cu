@@ -373,12 +373,15 @@ int tmk_decode_batch(tmk_engine* e, const float* samples, uint64_t total_samples
     CK(e->d_next.reserve(sizeof(unsigned int) * (chunks.size() + 1)));
     // cluster pass (walk.cu): candidate entries + speculative verdicts, per chunk its own list region / counter
     const bool use_fast = b.n_blocks > 0 && b.n_blocks < (1ull << 31) && !getenv("TMK_NO_CLUSTER");
+    // measured at C2: the cluster pass beside the walk (each on half of the CTA slots) takes 10.3 ms instead of 3.8,
+    // and most walks wait for it anyway (step 16.2 ms against 12.0): off unless TMK_CONCURRENT_CLUSTER is set
+    const bool serial_cluster = getenv("TMK_CONCURRENT_CLUSTER") == nullptr;
     const uint64_t entry_cap = std::min<uint64_t>((1ull << 26) - 1, b.n_blocks / 2 + 4096);
     if (use_fast) {
         CK(e->d_cblk.reserve(sizeof(uint32_t) * b.n_blocks));
         CK(e->d_blk_ptr.reserve(2 * sizeof(uint32_t) * b.n_blocks));  // pointers | gains
         CK(e->d_entries.reserve(sizeof(TmkCandEntry) * entry_cap));
-        CK(e->d_pool.reserve(sizeof(unsigned int) * (2 + chunks.size())));
+        CK(e->d_pool.reserve(sizeof(unsigned int) * (2 + 2 * chunks.size())));
     }
 
     const TmkStreamDev* ds = static_cast<const TmkStreamDev*>(e->d_streams.p);
@@ -409,6 +412,7 @@ int tmk_decode_batch(tmk_engine* e, const float* samples, uint64_t total_samples
         unsigned int* pool = static_cast<unsigned int*>(e->d_pool.p);
         f.cblk_list = static_cast<uint32_t*>(e->d_cblk.p) + uint64_t(ch.t0) * TMK_TILE_BLKS;
         f.cblk_count = pool + 2 + g;
+        f.item_next = pool + 2 + chunks.size() + g;
         f.blk_ptr = static_cast<uint32_t*>(e->d_blk_ptr.p);
         f.blk_gain = reinterpret_cast<float*>(f.blk_ptr + b.n_blocks);
         f.entries = static_cast<TmkCandEntry*>(e->d_entries.p);
@@ -424,7 +428,12 @@ int tmk_decode_batch(tmk_engine* e, const float* samples, uint64_t total_samples
     CK(cudaMemsetAsync(dcb, 0, sizeof(uint32_t) * TMK_BLK_WORDS * b.n_blocks, e->stream));
     CK(cudaMemsetAsync(dc, 0, sizeof(TmkCounters), e->stream));
     CK(cudaMemsetAsync(dnext, 0, sizeof(unsigned int) * (chunks.size() + 1), e->stream));
-    if (use_fast) CK(cudaMemsetAsync(e->d_pool.p, 0, sizeof(unsigned int) * (2 + chunks.size()), e->stream));
+    if (use_fast) {
+        CK(cudaMemsetAsync(e->d_pool.p, 0, sizeof(unsigned int) * (2 + 2 * chunks.size()), e->stream));
+        // every block starts PENDING (0xfffffffe in each byte pair is not expressible by memset: 0xfe bytes give
+        // 0xfefefefe, so the sentinel is that value) — see TMK_ENT_PENDING
+        CK(cudaMemsetAsync(e->d_blk_ptr.p, 0xfe, sizeof(uint32_t) * b.n_blocks, e->stream));
+    }
     if (host_samples) {
         // the copy stream may only overwrite the staging buffer once earlier work on it is done
         CK(cudaEventRecord(e->cev[0], e->stream));
@@ -444,28 +453,32 @@ int tmk_decode_batch(tmk_engine* e, const float* samples, uint64_t total_samples
                                        const_cast<uint32_t*>(fast.cblk_list), fast.cblk_count, e->stream);
         if (chunks.size() == 1) CK(cudaEventRecord(e->ev[2], e->stream));
         uint8_t* dpay = pay_dev ? payload : static_cast<uint8_t*>(e->d_payload.p);
-        // A walk is a latency-bound serial chain per stream (milliseconds whatever the number of streams), so
-        // the walks of the chunks run on their own stream, concurrently with each other and with later scans.
-        cudaStream_t ws = chunks.size() == 1 ? e->stream : e->walk_streams[g % 4];
-        if (ws != e->stream) {
-            cudaEvent_t se = e->cev[3 + (g & 1)];
-            CK(cudaEventRecord(se, e->stream));
-            CK(cudaStreamWaitEvent(ws, se, 0));
+        // The walks / cluster passes of different chunks overlap each other and the later scans (high-priority
+        // streams). Within a chunk the walk follows the cluster pass; they CAN run side by side (the cluster
+        // pass publishes every block with a release store, a walk that reaches a block first waits for it,
+        // bounded, or evaluates the block itself), but that measured slower (see serial_cluster above).
+        cudaStream_t cs = e->walk_streams[(2 * g) % 4], ws = e->walk_streams[(2 * g + 1) % 4];
+        cudaEvent_t se = e->cev[3 + (g & 1)];
+        CK(cudaEventRecord(se, e->stream));
+        CK(cudaStreamWaitEvent(cs, se, 0));
+        CK(cudaStreamWaitEvent(ws, se, 0));
+        if (use_fast) {
+            e->launches += tmk_launch_cluster(dx, ds, dtd, dp, dbi, dcb, fast, dpay, dev_pay_cap, dc, !serial_cluster, cs);
+            if (chunks.size() == 1) CK(cudaEventRecord(e->ev[5], cs));
+            if (serial_cluster) {
+                CK(cudaEventRecord(e->wev[0], cs));
+                CK(cudaStreamWaitEvent(ws, e->wev[0], 0));
+            }
         }
-        if (use_fast)
-            e->launches += tmk_launch_cluster(dx, ds, dtd, dp, dbi, dcb, fast, dpay, dev_pay_cap, dc, ws);
-        if (chunks.size() == 1) CK(cudaEventRecord(e->ev[5], e->stream));
         e->launches += tmk_launch_walk(dx, ds, ch.s0, ch.s1, dnext + g, fast, dp, dbi, dcb,
                                        static_cast<tmk_frame_rec*>(e->d_recs_tmp.p), static_cast<uint32_t*>(e->d_rec_ord.p),
                                        dev_rec_cap, dpay, dev_pay_cap, static_cast<uint32_t*>(e->d_cnt.p), dc, d_link, ws);
         CK(cudaGetLastError());
     }
-    if (chunks.size() != 1) {
-        CK(cudaEventRecord(e->ev[2], e->stream));  // end of the last scan; the walks of the earlier chunks are under way
-        for (int i = 0; i < 4 && size_t(i) < chunks.size(); ++i) {
-            CK(cudaEventRecord(e->wev[i], e->walk_streams[i]));
-            CK(cudaStreamWaitEvent(e->stream, e->wev[i], 0));
-        }
+    if (chunks.size() != 1) CK(cudaEventRecord(e->ev[2], e->stream));  // end of the last scan
+    for (int i = 0; i < 4; ++i) {
+        CK(cudaEventRecord(e->wev[i], e->walk_streams[i]));
+        CK(cudaStreamWaitEvent(e->stream, e->wev[i], 0));
     }
     TmkCounters hc;
     CK(cudaMemcpyAsync(&hc, dc, sizeof hc, cudaMemcpyDeviceToHost, e->stream));

@@ -86,6 +86,7 @@ struct TmkCandEntry {  // one candidate window of a block, in window order
     uint32_t spec;     // speculative frame record of a detection at this window, or TMK_ENT_INVALID
 };
 #define TMK_ENT_INVALID 0xffffffffu
+#define TMK_ENT_PENDING 0xfefefefeu  // blk_ptr of a block the cluster pass has not reached yet (it runs beside the walk)
 struct TmkFast {
     const uint32_t* cblk_list;       // global ids of the blocks with candidates (appended by the scan kernels)
     unsigned int* cblk_count;
@@ -96,6 +97,7 @@ struct TmkFast {
     tmk_frame_rec* spec;             // speculative verdict records (payload already in the payload buffer)
     uint32_t spec_cap;
     unsigned int* pool;              // [0] entries used, [1] spec records used
+    unsigned int* item_next;         // work counter of the cluster pass (one per chunk)
 };
 
 __host__ __device__ inline uint64_t tmk_sfb(int line_code, uint32_t spl, uint64_t nbits) {
@@ -153,7 +155,7 @@ int tmk_launch_scan_generic(const float* samples, const TmkStreamDev* streams, c
 // cluster pass over the blocks listed in f.cblk_list (one-shot streams; others are marked invalid)
 int tmk_launch_cluster(const float* samples, const TmkStreamDev* streams, const uint32_t* tile_stream,
                        const TmkPattern* patterns, const float4* blk_info, const uint32_t* cand_bits, TmkFast f,
-                       uint8_t* payload, uint64_t payload_cap, TmkCounters* counters, cudaStream_t st);
+                       uint8_t* payload, uint64_t payload_cap, TmkCounters* counters, bool beside_walk, cudaStream_t st);
 int tmk_launch_walk(const float* samples, const TmkStreamDev* streams, uint32_t s0, uint32_t s1, unsigned int* next,
                     TmkFast fast,
                     const TmkPattern* patterns, const float4* blk_info, const uint32_t* cand_bits,

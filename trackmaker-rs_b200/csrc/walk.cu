@@ -401,17 +401,63 @@ __device__ __noinline__ void block_prefix(Ctx& c, uint64_t bb) {
     }
 }
 
+// ---- results of the cluster pass, which runs BESIDE the walk (other CTAs, other stream)
+// blk_ptr of a block with candidates: published by the cluster pass with a release store after its entries,
+// gain, speculative records and payload bytes. A walk that gets there first waits — bounded, so that a cluster
+// pass that cannot get an SM never stalls the walk for good: after the bound the block counts as "no cluster
+// result" and is evaluated by the walk itself (same results, more work). Everything the cluster pass wrote is
+// read through L2 (ld.cg): an L1 line of this SM may predate the write.
+__device__ __forceinline__ uint32_t ld_acquire_u32(const uint32_t* p) {
+    uint32_t v;
+    asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+    return v;
+}
+__device__ __noinline__ uint32_t wait_blk_ptr(const Ctx& c, uint64_t bb) {
+    const uint32_t* p = c.blk_ptr + bb;
+    uint32_t v = 0;
+    if (c.lane == 0) {
+        v = ld_acquire_u32(p);
+        for (int it = 0; v == TMK_ENT_PENDING && it < 40000; ++it) {  // ~10 ms
+            __nanosleep(250);
+            v = ld_acquire_u32(p);
+        }
+        if (v == TMK_ENT_PENDING) v = TMK_ENT_INVALID;
+    }
+    return __shfl_sync(kFull, v, 0);
+}
+__device__ __forceinline__ TmkCandEntry ld_entry(const TmkCandEntry* p) {
+    static_assert(sizeof(TmkCandEntry) == 16, "entry size");
+    const uint4 v = __ldcg(reinterpret_cast<const uint4*>(p));
+    TmkCandEntry e;
+    e.wl = uint16_t(v.x & 0xffffu);
+    e.flags = uint16_t(v.x >> 16);
+    e.D = __uint_as_float(v.y);
+    e.Ec = __uint_as_float(v.z);
+    e.spec = v.w;
+    return e;
+}
+__device__ __forceinline__ tmk_frame_rec ld_spec(const tmk_frame_rec* p) {
+    static_assert(sizeof(tmk_frame_rec) == 48, "record size");
+    union { tmk_frame_rec r; uint4 v[3]; } u;
+    const uint4* q = reinterpret_cast<const uint4*>(p);
+    u.v[0] = __ldcg(q);
+    u.v[1] = __ldcg(q + 1);
+    u.v[2] = __ldcg(q + 2);
+    return u.r;
+}
+
 // speculative verdict record the cluster pass prepared for window wl of block bb (or TMK_ENT_INVALID)
 __device__ __noinline__ uint32_t lookup_spec(const Ctx& c, uint64_t bb, uint32_t wl) {
     if (c.blk_ptr == nullptr || c.C != 0 || c.P > 255) return TMK_ENT_INVALID;
-    const uint32_t ptr = c.blk_ptr[bb];
+    if (c.blk_info[bb].w == 0.f) return TMK_ENT_INVALID;  // not on the cluster pass's list: never published
+    const uint32_t ptr = wait_blk_ptr(c, bb);
     if (ptr == TMK_ENT_INVALID) return TMK_ENT_INVALID;
     const uint32_t n = ptr & 63u;
     for (uint32_t r0 = 0; r0 < n; r0 += 32) {
         uint32_t spec = TMK_ENT_INVALID;
         bool match = false;
         if (r0 + uint32_t(c.lane) < n) {
-            const TmkCandEntry e = c.entries[(ptr >> 6) + r0 + c.lane];
+            const TmkCandEntry e = ld_entry(c.entries + (ptr >> 6) + r0 + c.lane);
             match = e.wl == wl;
             spec = e.spec;
         }
@@ -558,15 +604,16 @@ __device__ __noinline__ int fast_block(Ctx& c, uint64_t bb, uint64_t q, float4 i
     const float dscan = 128.f * kU * nb;
     // the bound of a window of energy S is  d_abs + d_rel * S
     float d_abs = d_end, d_rel = 2.5f * kU;
+    uint32_t ptr = TMK_ENT_PENDING;
     if (!(d_end + dscan <= kTight * emin_lo) || !(d_end <= 3.0e38f) || !(dscan <= 3.0e38f)) {
         // A block whose energy RISES (the quiet gap runs into a loud preamble) fails the test above only
         // because the drift at the END of the block is held against the energy at its START. Window by
         // window the sum form is  u (1.5 P S_seed + 2.2 (racc_in + B_w)),  B_w = the window energies of
         // this block up to w; the cluster pass measured  gain >= B_w / S_w  for every window of the block.
         if (info.w == 0.f || !(racc_in >= 0.f)) return 2;
-        const uint32_t ptr0 = c.blk_ptr[bb];
-        if (ptr0 == TMK_ENT_INVALID) return 2;
-        const float gain = c.blk_gain[bb];
+        ptr = wait_blk_ptr(c, bb);
+        if (ptr == TMK_ENT_INVALID) return 2;
+        const float gain = __ldcg(c.blk_gain + bb);
         const float hist = kU * (1.5f * float(c.P) * efirst + 2.2f * racc_in) * growth;
         const float rel = 2.2f * kU * growth * gain + 2.5f * kU;
         if (!(hist + dscan <= 0.5f * kTight * emin_lo) || !(rel <= 0.5f * kTight)) return 2;
@@ -574,13 +621,13 @@ __device__ __noinline__ int fast_block(Ctx& c, uint64_t bb, uint64_t q, float4 i
         d_rel = rel;
     }
     if (info.w == 0.f) return 0;
-    const uint32_t ptr = c.blk_ptr[bb];
+    if (ptr == TMK_ENT_PENDING) ptr = wait_blk_ptr(c, bb);
     if (ptr == TMK_ENT_INVALID) return 2;
     const uint32_t n = ptr & 63u;
     for (uint32_t r0 = 0; r0 < n; r0 += 32) {
         TmkCandEntry e;
         e.wl = 0; e.flags = 0; e.D = 0.f; e.Ec = 0.f; e.spec = TMK_ENT_INVALID;
-        if (r0 + uint32_t(c.lane) < n) e = c.entries[(ptr >> 6) + r0 + c.lane];
+        if (r0 + uint32_t(c.lane) < n) e = ld_entry(c.entries + (ptr >> 6) + r0 + c.lane);
         const uint64_t w = wb0 + e.wl;
         const bool valid = r0 + uint32_t(c.lane) < n && w >= q && w < c.nwin;
         int dec = DEC_NO;
@@ -1169,6 +1216,13 @@ __device__ __noinline__ void spec_decode(Ctx& c, uint64_t w, float corr, uint32_
     __syncwarp();
 }
 
+// release store of a block's result word: everything the warp wrote for the block (entries, gain, speculative
+// records, payload bytes) is visible to a walk that acquires the word
+__device__ __forceinline__ void publish_blk(uint32_t* p, uint32_t v) {
+    __threadfence();
+    asm volatile("st.release.gpu.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+
 // One warp per block with candidates: exact dot product and accurate energy of every candidate window, and a
 // speculative refine + demodulation + CRC of the windows a walk that enters the block in Searching state would
 // detect. All of it is independent of the rest of the capture, so it runs at full occupancy; the per-stream
@@ -1182,7 +1236,13 @@ cluster_kernel(const float* __restrict__ samples, const TmkStreamDev* __restrict
     const uint32_t warp = threadIdx.x >> 5;
     const int lane = threadIdx.x & 31;
     const uint32_t n_items = *f.cblk_count;
-    for (uint32_t item = blockIdx.x * kWarpsPerCta + warp; item < n_items; item += gridDim.x * kWarpsPerCta) {
+    for (;;) {
+        // items are pulled, not strided: whatever share of the cluster CTAs is resident beside the walk makes
+        // progress on every listed block
+        uint32_t item = 0;
+        if (lane == 0) item = atomicAdd(f.item_next, 1u);
+        item = __shfl_sync(kFull, item, 0);
+        if (item >= n_items) break;
         const uint32_t gb = f.cblk_list[item];
         const uint32_t sidx = tile_stream[gb / TMK_TILE_BLKS];
         const TmkStreamDev sd = streams[sidx];
@@ -1190,7 +1250,7 @@ cluster_kernel(const float* __restrict__ samples, const TmkStreamDev* __restrict
         init_ctx(c, samples, sd, patterns, blk_info, cand_bits, f, lane, warp);
         const uint64_t bb = uint64_t(gb) - sd.blk_base;
         if (c.C != 0 || c.P > 255) {  // chunked feeding / long preambles keep the walk's own evaluation
-            if (lane == 0) f.blk_ptr[gb] = TMK_ENT_INVALID;
+            if (lane == 0) publish_blk(f.blk_ptr + gb, TMK_ENT_INVALID);
             continue;
         }
         const uint64_t wb0 = bb * TMK_BLK;
@@ -1221,7 +1281,7 @@ cluster_kernel(const float* __restrict__ samples, const TmkStreamDev* __restrict
         }
         __syncwarp();
         if (n_ent > 63) {
-            if (lane == 0) f.blk_ptr[gb] = TMK_ENT_INVALID;
+            if (lane == 0) publish_blk(f.blk_ptr + gb, TMK_ENT_INVALID);
             continue;
         }
         // gain = max over the block's windows of (sum of the window energies of the block up to w) / S_w,
@@ -1273,13 +1333,15 @@ cluster_kernel(const float* __restrict__ samples, const TmkStreamDev* __restrict
         if (lane == 0) base = n_ent ? atomicAdd(&f.pool[0], n_ent) : 0u;
         base = __shfl_sync(kFull, base, 0);
         if (base + n_ent > f.entry_cap || base + n_ent >= (1u << 26)) {
-            if (lane == 0) f.blk_ptr[gb] = TMK_ENT_INVALID;
+            if (lane == 0) publish_blk(f.blk_ptr + gb, TMK_ENT_INVALID);
             continue;
         }
         for (uint32_t i = lane; i < n_ent; i += 32) f.entries[base + i] = ents[warp][i];
+        __syncwarp();
         if (lane == 0) {
             f.blk_gain[gb] = gain;
-            f.blk_ptr[gb] = (base << 6) | n_ent;
+            const uint32_t v = (base << 6) | n_ent;
+            publish_blk(f.blk_ptr + gb, v == TMK_ENT_PENDING ? TMK_ENT_INVALID : v);
         }
     }
 }
@@ -1343,7 +1405,7 @@ walk_kernel(const float* __restrict__ samples, const TmkStreamDev* __restrict__ 
             // the cluster pass already refined, demodulated and checked the frame of this detection (its
             // refinement range [expect - margin, expect + margin] is the walk's because the search started at
             // least `margin` samples before `expect`): link the verdict, payload bytes are in place
-            tmk_frame_rec r = c.spec[d.spec];
+            tmk_frame_rec r = ld_spec(c.spec + d.spec);
             unsigned long long slot = 0;
             if (c.lane == 0) slot = atomicAdd(&counters->n_recs, 1ull);
             slot = __shfl_sync(kFull, slot, 0);
@@ -1527,7 +1589,9 @@ int tmk_launch_excl_scan(const uint32_t* cnt, uint64_t* base, uint32_t n, cudaSt
 
 int tmk_launch_cluster(const float* samples, const TmkStreamDev* streams, const uint32_t* tile_stream,
                        const TmkPattern* patterns, const float4* blk_info, const uint32_t* cand_bits, TmkFast f,
-                       uint8_t* payload, uint64_t payload_cap, TmkCounters* counters, cudaStream_t st) {
+                       uint8_t* payload, uint64_t payload_cap, TmkCounters* counters, bool beside_walk, cudaStream_t st) {
+    // beside the walk: half of the SMs' CTA slots: the walk (launched right after, on another stream) takes the other half at
+    // once and the rest as these CTAs retire
     static int max_ctas = 0;
     if (max_ctas == 0) {
         int dev = 0, sms = 0, per_sm = 0;
@@ -1536,7 +1600,13 @@ int tmk_launch_cluster(const float* samples, const TmkStreamDev* streams, const 
         cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, cluster_kernel, kWarpsPerCta * 32, 0);
         max_ctas = sms * (per_sm > 0 ? per_sm : 1);
     }
-    cluster_kernel<<<max_ctas, kWarpsPerCta * 32, 0, st>>>(samples, streams, tile_stream, patterns, blk_info, cand_bits, f,
+    int grid = max_ctas;
+    if (beside_walk) {
+        int share = 2;
+        if (const char* ev = getenv("TMK_CLUSTER_CTAS")) share = std::max(1, atoi(ev));
+        grid = std::max(1, max_ctas / 4 * share);
+    }
+    cluster_kernel<<<grid, kWarpsPerCta * 32, 0, st>>>(samples, streams, tile_stream, patterns, blk_info, cand_bits, f,
                                                            payload, payload_cap, counters);
     return 1;
 }
