@@ -31,6 +31,7 @@ sys.path.insert(0, ROOT)
 sys.path.insert(0, os.path.join(ROOT, "trackmaker-rs_b200"))
 
 N_STREAMS = 4096
+NCU_SCAN_TRAFFIC = 7.894586e9 + 79.60192e6  # bytes per scan launch at C2, ncu --set full (profiles/)
 N_PER_STREAM = 480000
 SNRS = [-3.0, 0.0, 3.0, 6.0, 10.0, 15.0, 20.0, 30.0]
 METRIC = "Msamples/s sync+demod (48 kHz streams)"
@@ -210,12 +211,14 @@ def main():
     barrier()
     l0 = eng.launch_count()
     stage = {"scan": 0.0, "walk": 0.0, "order": 0.0}
+    cluster_ms = 0.0
     eng.timer_start()
     for _ in range(args.steps):
         step_resident()
         s = eng.last_stage_ms()
         for k in stage:
             stage[k] += s[k]
+        cluster_ms += eng.debug_counters()["cluster_us"] * 1e-3  # part of "walk": the per-block cluster pass
     ms_total = eng.timer_stop()
     launches = eng.launch_count() - l0
     barrier()
@@ -272,9 +275,15 @@ def main():
                        "chunk": args.chunk, "l2": "inputs (7.9 GB/GPU) far larger than the 126 MB L2",
                        "sharding": f"streams x{world}, no data-path collective"},
             "gpu_launches": launches,
-            "stage_ms_per_step": {k: v / args.steps for k, v in stage.items()},
+            "stage_ms_per_step": {"scan": stage["scan"] / args.steps, "cluster": cluster_ms / args.steps,
+                                  "walk": (stage["walk"] - cluster_ms) / args.steps, "order": stage["order"] / args.steps},
             "roofline": {"bound": "hbm", "kernel": "preamble scan", "achieved": achieved, "peak": hbm, "unit": "GB/s",
-                         "frac": achieved / hbm, "traffic": None, "peak_source": which,
+                         "frac": achieved / hbm,
+                         # dram__bytes_read.sum + dram__bytes_write.sum of one launch at this workload
+                         # (profiles/r01_ncu_full_summary_final.txt); null for any other workload
+                         "traffic": NCU_SCAN_TRAFFIC if (n_s, n_per, kind) == (N_STREAMS, N_PER_STREAM, tmkphy.LINE_4B5B)
+                         and not args.snrs else None,
+                         "peak_source": which,
                          "algorithmic_bytes_per_launch": 4 * total},
             "clocks": sampler.summary(),
             "decode": {"records": int(counters[0]), "payload_bytes": int(counters[1]), "frames_planted": int(counters[2]),
