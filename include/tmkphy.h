@@ -181,7 +181,8 @@ int tmk_stats_reset(tmk_engine* e);
 /* Diagnostic counters of the walk kernel of the last tmk_decode_batch call: [0] blocks examined window by
  * window, [1] exact re-anchorings of the rolling-energy bound, [2] sequential replay steps,
  * [3] groups of 32 block summaries read, [4] device time of the cluster pass in microseconds (single-chunk
- * calls); [5..7] reserved. */
+ * calls), [5] rolling steps covered by the lane-parallel exact replay, [6] its segments that had to be rolled
+ * literally; [7] reserved. ([2] counts literally rolled steps only.) */
 int tmk_debug_counters(tmk_engine* e, uint64_t out[8]);
 
 /* plumbing for callers without a CUDA runtime of their own (tests, bench, the Rust shim) */

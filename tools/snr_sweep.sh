@@ -3,7 +3,7 @@ for s in -3 0 3 6 10 15 20 30; do
   python bench.py --snrs=$s --streams 512 --no-cpu --e2e-steps 0 --steps 3 --warmup 2 2>/dev/null | python -c "
 import json,sys
 d=json.loads(sys.stdin.readline())
-print('SNR', '$s', d['stage_ms_per_step'], d['decode']['walk_last_step'], d['decode'].get('frames_ok'))"
+print('SNR', '$s', {k: round(v,3) for k,v in d['stage_ms_per_step'].items()}, d['decode']['walk_last_step'])"
 done
 python bench.py --snrs=30,20,15,10,6,3,0,-3 --no-cpu --e2e-steps 0 --steps 3 --warmup 2 2>/dev/null | python -c "
 import json,sys

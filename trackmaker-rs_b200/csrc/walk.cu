@@ -74,6 +74,8 @@ struct Ctx {
     // anchor: |E_ref(a_w) - S(a_w)| <= a_err for the chain seeded at a_seed (a_w == a_seed, a_err == 0
     // right after a search entry; a measured value after an exact re-anchoring)
     uint64_t a_seed, a_w;
+    uint64_t n_par_steps;  // steps rolled by the lane-parallel replay, and segments it had to roll literally
+    uint32_t n_par_doubt;
     float a_err;
     // sum form of the drift bound, valid while the anchor is the seed of a one-shot search (see fast_block):
     // bound on the sum of the chain's window energies before the block handed to process_block, and on
@@ -139,19 +141,10 @@ __device__ float seq_energy(const float* __restrict__ w, uint32_t n) {
     return e;
 }
 
-// Exact rolling window energy of window `w` for a search seeded at `seed` (decoder.rs:133-136,
-// 224-233). Sequential by construction: the squares are formed lane-parallel, 32 steps per
-// coalesced load, the dependent (sub, add, clamp) chain runs redundantly on every lane.
-__device__ __noinline__ float exact_energy(Ctx& c, uint64_t seed, uint64_t w) {
-    float e;
-    uint64_t pos;
-    if (c.rvalid && c.rseed == seed && c.rpos <= w) {
-        e = c.rE;
-        pos = c.rpos;
-    } else {
-        e = seq_energy(c.x + seed, c.P);
-        pos = seed;
-    }
+// The literal rolling chain from position `pos` (value e) to window `w` (decoder.rs:224-233). Sequential by
+// construction: the squares are formed lane-parallel, the dependent (sub, add, clamp) chain runs redundantly
+// on every lane.
+__device__ __noinline__ float roll_literal(Ctx& c, float e, uint64_t pos, uint64_t w) {
     const float* __restrict__ x = c.x;
     const uint32_t P = c.P;
     c.dbg[2] += w - pos;
@@ -255,6 +248,158 @@ __device__ __noinline__ float exact_energy(Ctx& c, uint64_t seed, uint64_t w) {
         }
         pos += n;
     }
+    return e;
+}
+
+// ---------------------------------------------------------------- lane-parallel exact replay
+// The chain  e' = clamp(fl(fl(e - a) + b))  is serial, but it is TRANSLATION INVARIANT inside a binade: if every
+// intermediate t of a chain started at g' and its translate t + s lie in the same binade [2^m, 2^(m+1)), and s is
+// an even multiple of the coarsest rounding grid that occurs, then every rounding (ties included: an even
+// multiple of the grid keeps the parity of both neighbours) and therefore the whole chain commutes with the
+// translation:  chain(g' + s) = chain(g') + s,  exactly. So the 32 lanes roll 32 consecutive segments at once,
+// each from a GUESS g (the accurately summed window energy at the segment start) — in fact from the four bases
+// g, g+u, g+2u, g+3u (u = ulp(g)), so that whatever the true start e is, one base differs from it by a multiple
+// of 4u, which is an even multiple of the coarsest grid as long as the segment stays at most one binade above g.
+// The step map is monotone, so the four chains stay ordered; the smallest distance of chain 0 to the binade
+// boundary below and of chain 3 to the boundary above bounds the margin of all four. The segments are then
+// stitched in order: true start - base = s, accepted if |s| is inside the segment's margin (in units of its
+// smallest ulp, one ulp held back for the rounded vs real intermediate), negative / zero / subnormal / NaN /
+// inf values, a clamp, or chains 0 and 3 in different binades make the segment "in doubt": it is rolled
+// literally (roll_literal) from the exact start value that is known by then.
+constexpr uint32_t kParMinSeg = 128;  // steps per lane below which a parallel round is not worth it
+#ifndef TMK_PAR_SEG
+#define TMK_PAR_SEG 512
+#endif
+constexpr uint32_t kParMaxSeg = TMK_PAR_SEG;  // steps per lane and round: the chance that a segment is in doubt and the cost of
+                                              // rolling it literally both grow with it (2048: 42 % of the segments at C2)
+
+__device__ __noinline__ float roll_parallel(Ctx& c, float e, uint64_t* pos_io, uint64_t w) {
+    const float* __restrict__ x = c.x;
+    const uint32_t P = c.P;
+    const int lane = c.lane;
+    constexpr uint32_t kM = 0x7fffffu;
+    uint64_t pos = *pos_io;
+    while (w - pos >= 32ull * kParMinSeg) {
+        const uint64_t l64 = (w - pos) / 32;
+        const uint32_t L = uint32_t(l64 < kParMaxSeg ? l64 : kParMaxSeg) & ~7u;
+        const float* __restrict__ xp = x + pos + uint64_t(lane) * L;  // this lane's segment
+        // guess: accurately summed energy of the window at the segment start
+        double S = 0.0;
+        for (uint32_t i = 0; i < P; i += 4) {
+            const float4 v = *reinterpret_cast<const float4*>(xp + i);
+            S += double(ex_mul(v.x, v.x));
+            S += double(ex_mul(v.y, v.y));
+            S += double(ex_mul(v.z, v.z));
+            S += double(ex_mul(v.w, v.w));
+        }
+        const float g = __double2float_rn(S);
+        const uint32_t gbits = __float_as_uint(g);
+        const uint32_t gexp = gbits >> 23;  // (sign bit set -> huge -> rejected)
+        bool ok = gexp >= 32u && gexp <= 250u && (gbits & kM) <= 0x7ffff0u;
+        const float u = __uint_as_float(((ok ? gexp : 64u) - 23u) << 23);  // ulp(g)
+        float c0 = g, c1 = ex_add(g, u), c2 = ex_add(g, ex_add(u, u)), c3 = ex_add(g, ex_mul(3.0f, u));
+        uint32_t below = kM, top = 0u, xr = 0u, hi = 0u;
+        int32_t lo = 0x7fffffff;
+        // samples as float4s (pos and P are multiples of 4 here, the stream base is 16-byte aligned): every load
+        // instruction touches 32 different lines, so the instruction count is what the L1 pays for
+        const float4* __restrict__ xa = reinterpret_cast<const float4*>(xp);
+        const float4* __restrict__ xb = reinterpret_cast<const float4*>(xp + P);
+        float4 a0 = xa[0], a1 = xa[1], b0 = xb[0], b1 = xb[1];
+        for (uint32_t k = 0; k < L; k += 8) {
+            float4 an0 = a0, an1 = a1, bn0 = b0, bn1 = b1;
+            if (k + 8 < L) {
+                an0 = xa[k / 4 + 2];
+                an1 = xa[k / 4 + 3];
+                bn0 = xb[k / 4 + 2];
+                bn1 = xb[k / 4 + 3];
+            }
+            const float a[8] = {a0.x, a0.y, a0.z, a0.w, a1.x, a1.y, a1.z, a1.w};
+            const float b[8] = {b0.x, b0.y, b0.z, b0.w, b1.x, b1.y, b1.z, b1.w};
+#pragma unroll
+            for (int t = 0; t < 8; ++t) {
+                const float aa = ex_mul(a[t], a[t]), bb = ex_mul(b[t], b[t]);
+                const float t0 = ex_sub(c0, aa), t1 = ex_sub(c1, aa), t2 = ex_sub(c2, aa), t3 = ex_sub(c3, aa);
+                c0 = ex_add(t0, bb);
+                c1 = ex_add(t1, bb);
+                c2 = ex_add(t2, bb);
+                c3 = ex_add(t3, bb);
+                const uint32_t bt0 = __float_as_uint(t0), bt3 = __float_as_uint(t3);
+                const uint32_t bc0 = __float_as_uint(c0), bc3 = __float_as_uint(c3);
+                below = min(below, min(bt0 & kM, bc0 & kM));
+                top = max(top, max(bt3 & kM, bc3 & kM));
+                xr |= (bt0 ^ bt3) | (bc0 ^ bc3);
+                lo = min(lo, min(int32_t(bt0), int32_t(bc0)));
+                hi = max(hi, max(bt3, bc3));
+            }
+            a0 = an0;
+            a1 = an1;
+            b0 = bn0;
+            b1 = bn1;
+        }
+        // chains 0 and 3 in the same binade (and of the same sign) at every operation; everything normal and
+        // positive (no clamp, no gate); at most one binade above the guess
+        ok = ok && (xr >> 23) == 0u && lo >= int32_t(32u << 23) && (hi >> 23) <= gexp + 1u && (hi >> 23) <= 250u;
+        float margin = 0.f;
+        if (ok) {
+            const uint32_t mi = min(below, 0x800000u - top);  // in ulps of the value it was measured on (>= smallest ulp)
+            const uint32_t emin = uint32_t(lo) >> 23;
+            if (mi >= 2u) margin = ex_mul(float(mi - 1u), __uint_as_float((emin - 23u) << 23));
+        }
+        const float inv_u = __uint_as_float((277u - (ok ? gexp : 64u)) << 23);  // 1 / ulp(g), exact
+        // ---- stitch the segments in order (warp-uniform)
+        float ecur = e;
+        for (int j = 0; j < 32; ++j) {
+            const bool okj = __shfl_sync(kFull, int(ok), j) != 0;
+            const float gj = __shfl_sync(kFull, g, j), uj = __shfl_sync(kFull, u, j), iuj = __shfl_sync(kFull, inv_u, j);
+            const float mj = __shfl_sync(kFull, margin, j);
+            const float r0 = __shfl_sync(kFull, c0, j), r1 = __shfl_sync(kFull, c1, j);
+            const float r2 = __shfl_sync(kFull, c2, j), r3 = __shfl_sync(kFull, c3, j);
+            bool use = okj && (__float_as_uint(ecur) >> 23) == (__float_as_uint(gj) >> 23);  // same binade, positive
+            float enext = 0.f;
+            if (use) {
+                const float d = ex_sub(ecur, gj);   // exact: same binade
+                const float qf = ex_mul(d, iuj);    // exact: a power of two
+                use = fabsf(qf) < 4.0e6f;
+                if (use) {
+                    const int iq = __float2int_rn(qf);  // qf is an integer
+                    const int i = iq & 3;
+                    const float sft = ex_mul(float(iq - i), uj);  // multiple of 4 ulp(g), exact
+                    use = fabsf(sft) <= mj;
+                    if (use) enext = ex_add(i == 0 ? r0 : i == 1 ? r1 : i == 2 ? r2 : r3, sft);  // exact by the lemma
+                }
+            }
+            if (!use) {
+                enext = roll_literal(c, ecur, pos + uint64_t(j) * L, pos + uint64_t(j + 1) * L);
+                c.n_par_doubt++;
+            }
+            ecur = enext;
+        }
+        c.n_par_steps += 32ull * L;
+        e = ecur;
+        pos += 32ull * L;
+    }
+    *pos_io = pos;
+    return e;
+}
+
+// Exact rolling window energy of window `w` for a search seeded at `seed` (decoder.rs:133-136, 224-233).
+__device__ __noinline__ float exact_energy(Ctx& c, uint64_t seed, uint64_t w) {
+    float e;
+    uint64_t pos;
+    if (c.rvalid && c.rseed == seed && c.rpos <= w) {
+        e = c.rE;
+        pos = c.rpos;
+    } else {
+        e = seq_energy(c.x + seed, c.P);
+        pos = seed;
+    }
+    if (w - pos >= 32ull * kParMinSeg + 4 && c.P % 4 == 0) {
+        const uint64_t al = (pos + 3) & ~3ull;  // the parallel replay loads float4s
+        if (al != pos) e = roll_literal(c, e, pos, al);
+        pos = al;
+        e = roll_parallel(c, e, &pos, w);
+    }
+    e = roll_literal(c, e, pos, w);
     c.rvalid = true;
     c.rseed = seed;
     c.rpos = w;
@@ -1126,6 +1271,8 @@ __device__ __forceinline__ void init_ctx(Ctx& c, const float* samples, const Tmk
     c.sum_ok = false;
     c.n_replays = c.n_cands = c.n_det = 0;
     c.dbg[0] = c.dbg[1] = c.dbg[2] = c.dbg[3] = 0;
+    c.n_par_steps = 0;
+    c.n_par_doubt = 0;
     __syncwarp();
     for (uint32_t k = lane; k < c.P; k += 32) sc->pre[k] = int8_t(c.pat->levels[k / c.pat->spl]);
     __syncwarp();
@@ -1519,6 +1666,8 @@ walk_kernel(const float* __restrict__ samples, const TmkStreamDev* __restrict__ 
         atomicAdd(&counters->stats[TMK_STAT_EXACT_REPLAYS], (unsigned long long)c.n_replays);
         atomicAdd(&counters->stats[TMK_STAT_CANDIDATES], (unsigned long long)c.n_cands);
         for (int i = 0; i < 4; ++i) atomicAdd(&counters->dbg[i], c.dbg[i]);
+        atomicAdd(&counters->dbg[5], (unsigned long long)c.n_par_steps);
+        atomicAdd(&counters->dbg[6], (unsigned long long)c.n_par_doubt);
     }
     }  // next stream
 }

@@ -173,8 +173,8 @@ class Engine:
         """walk diagnostics of the last decode_batch call (tmk_debug_counters)"""
         c = (C.c_uint64 * 8)()
         self._check(self._lib.tmk_debug_counters(self._h, c))
-        return dict(zip(("blocks_examined", "reanchors", "replay_steps", "summary_groups", "cluster_us"),
-                        [int(v) for v in c[:5]]))
+        return dict(zip(("blocks_examined", "reanchors", "replay_steps", "summary_groups", "cluster_us",
+                         "parallel_replay_steps", "parallel_replay_doubts"), [int(v) for v in c[:7]]))
 
     # ---- chirp + BPSK modem of examples/ask.rs
     def ask_tables(self, n_carrier=4752):
