@@ -1,6 +1,11 @@
-for v in "" _c5 _c6; do
-  TMKPHY_LIB=$PWD/trackmaker-rs_b200/libtmkphy$v.so timeout 300 python bench.py --no-cpu --e2e-steps 0 --steps 5 --warmup 3 2>/dev/null | python -c "
+for v in "" _p128 _p256 _p1024; do
+  export TMKPHY_LIB=$PWD/trackmaker-rs_b200/libtmkphy$v.so
+  timeout 300 python bench.py --no-cpu --e2e-steps 0 --steps 5 --warmup 3 2>/dev/null | python -c "
 import json,sys
 d=json.loads(sys.stdin.readline())
-print('LIB', '$v', round(d['value']), round(d['ms_per_step'],2), d['stage_ms_per_step'], d['decode']['walk_last_step']['cluster_us'])"
+print('LIB', '$v', round(d['value']), round(d['ms_per_step'],2), {k: round(x,2) for k,x in d['stage_ms_per_step'].items()}, d['decode']['walk_last_step']['replay_steps'], d['decode']['walk_last_step']['parallel_replay_doubts'])"
+  timeout 300 python bench.py --snrs=3 --streams 512 --no-cpu --e2e-steps 0 --steps 3 --warmup 2 2>/dev/null | python -c "
+import json,sys
+d=json.loads(sys.stdin.readline())
+print('  3dB', '$v', {k: round(x,2) for k,x in d['stage_ms_per_step'].items()})"
 done

@@ -1436,26 +1436,51 @@ cluster_kernel(const float* __restrict__ samples, const TmkStreamDev* __restrict
         }
         // gain = max over the block's windows of (sum of the window energies of the block up to w) / S_w,
         // for fast_block's window-by-window form of the drift bound (NaN propagates and disables it)
+        // Cheap form first: (sum of all window energies of the block) / (smallest one) bounds every ratio; only a
+        // block with a strong contrast (a quiet gap running into a loud frame) needs the window-by-window maximum.
         float gain = 0.f;
         {
-            float carry = 0.f;
+            float ssum = 0.f, smin = __int_as_float(0x7f800000);
+            bool bad = false;
 #pragma unroll 1
             for (uint32_t r = 0; r < TMK_BLK_WORDS; ++r) {
                 const uint32_t wl = r * 32 + lane;
-                const bool valid = wb0 + wl < c.nwin;
-                const float S = valid ? __double2float_rn(c.sc->Q[wl + c.P] - c.sc->Q[wl]) : 0.f;
-                float cs = S * 1.0001f;
-#pragma unroll
-                for (int o = 1; o < 32; o <<= 1) {
-                    const float t = __shfl_up_sync(kFull, cs, o);
-                    if (lane >= o) cs += t;
+                if (wb0 + wl < c.nwin) {
+                    const float S = __double2float_rn(c.sc->Q[wl + c.P] - c.sc->Q[wl]);
+                    ssum += S;
+                    smin = fminf(smin, S);
+                    bad = bad || !(S == S);
                 }
-                cs += carry;
-                carry = __shfl_sync(kFull, cs, 31);
-                if (valid) gain = max_nan(gain, S > 0.f ? __fdiv_ru(cs, S) : (S == 0.f ? __int_as_float(0x7f800000) : S));
             }
 #pragma unroll
-            for (int o = 16; o > 0; o >>= 1) gain = max_nan(gain, __shfl_xor_sync(kFull, gain, o));
+            for (int o = 16; o > 0; o >>= 1) {
+                ssum += __shfl_xor_sync(kFull, ssum, o);
+                smin = fminf(smin, __shfl_xor_sync(kFull, smin, o));
+            }
+            bad = __any_sync(kFull, bad);
+            const float cheap = smin > 0.f ? __fdiv_ru(ssum * 1.001f, smin) : __int_as_float(0x7f800000);
+            if (!bad && cheap <= 1.0e5f) {
+                gain = cheap;
+            } else {
+                float carry = 0.f;
+#pragma unroll 1
+                for (uint32_t r = 0; r < TMK_BLK_WORDS; ++r) {
+                    const uint32_t wl = r * 32 + lane;
+                    const bool valid = wb0 + wl < c.nwin;
+                    const float S = valid ? __double2float_rn(c.sc->Q[wl + c.P] - c.sc->Q[wl]) : 0.f;
+                    float cs = S * 1.0001f;
+#pragma unroll
+                    for (int o = 1; o < 32; o <<= 1) {
+                        const float t = __shfl_up_sync(kFull, cs, o);
+                        if (lane >= o) cs += t;
+                    }
+                    cs += carry;
+                    carry = __shfl_sync(kFull, cs, 31);
+                    if (valid) gain = max_nan(gain, S > 0.f ? __fdiv_ru(cs, S) : (S == 0.f ? __int_as_float(0x7f800000) : S));
+                }
+#pragma unroll
+                for (int o = 16; o > 0; o >>= 1) gain = max_nan(gain, __shfl_xor_sync(kFull, gain, o));
+            }
         }
         // speculative decodes, mimicking a walk that meets the entries in order
         uint64_t skip_until = 0;
