@@ -172,6 +172,14 @@ int tmk_scan_probe(tmk_engine* e, const float* samples, uint64_t total_samples, 
                    uint32_t n_streams, float* blk_info, uint32_t* cand_bits, uint64_t block_cap, uint64_t* n_blocks,
                    uint64_t* blk_base);
 
+/* Diagnostic: the exact rolling window energy E_ref (decoder.rs:133-136, 224-233) of the windows[i] (ascending,
+ * >= seed) for a search_for_preamble call entered at `seed`, through the very replay the walk uses when a
+ * decision is too close for its drift bound (lane-parallel rounds + literal rounds). Host pointers for windows /
+ * energy. counts: [0] steps rolled literally, [1] steps covered by lane-parallel rounds, [2] segments of those
+ * rounds that had to be rolled literally. */
+int tmk_replay_probe(tmk_engine* e, const float* samples, uint64_t n_samples, const tmk_phy_config* cfg, uint64_t seed,
+                     const uint64_t* windows, uint32_t n_windows, float* energy, uint64_t counts[3]);
+
 /* busy[i] = -1 (fewer than 20 samples), 0 or 1 : mac::is_channel_busy per stream */
 int tmk_channel_busy(tmk_engine* e, const float* samples, uint64_t total_samples, const tmk_stream* streams,
                      uint32_t n_streams, int8_t* busy);

@@ -51,6 +51,7 @@ def lib():
             "orc_decode_batch_mt": (u64, [vp, vp, u32, C.c_int, vp, u64, vp, u64, C.POINTER(u64),
                                           C.POINTER(C.c_double)]),
             "orc_correlate": (u64, [pcfg, vp, u64, vp]),
+            "orc_rolling_energy": (None, [vp, u64, u32, u64, vp, u32, vp]),
             "orc_channel_busy": (C.c_int, [vp, u64]),
             "orc_hardware_threads": (C.c_int, []),
             "orc_ask_tables": (None, [vp, vp, u64]),
@@ -189,6 +190,15 @@ def decode_batch(samples, streams, n_threads=0, rec_cap=None, payload_cap=None):
                                   payload_cap, C.byref(plen), C.byref(sec))
     assert n <= rec_cap and plen.value <= payload_cap, "oracle output capacity too small"
     return recs[:n].copy(), pl[:plen.value].copy(), sec.value
+
+
+def rolling_energy(samples, P, seed, windows) -> np.ndarray:
+    """the reference's rolling window energy for a search entered at `seed`, at the ascending `windows`"""
+    s = np.ascontiguousarray(samples, dtype=np.float32)
+    w = np.ascontiguousarray(windows, dtype=np.uint64)
+    out = np.zeros(len(w), np.float32)
+    lib().orc_rolling_energy(_ptr(s), len(s), int(P), int(seed), _ptr(w), len(w), _ptr(out))
+    return out
 
 
 def correlate(cfg, samples) -> np.ndarray:

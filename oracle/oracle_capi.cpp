@@ -170,6 +170,23 @@ uint64_t orc_decode_batch_mt(const float* samples, const tmk_stream* streams, ui
     return nr;
 }
 
+// The rolling window energy of search_for_preamble (decoder.rs:133-136, 224-233) entered at `seed`, at the given
+// ascending windows: fresh sequential seed sum, then  e = e - x[i]^2 + x[i+P]^2  with the clamp at 0.
+void orc_rolling_energy(const float* s, uint64_t n, uint32_t P, uint64_t seed, const uint64_t* windows, uint32_t n_windows,
+                        float* out) {
+    float e = seq_energy(s + seed, P);
+    uint64_t pos = seed;
+    for (uint32_t k = 0; k < n_windows; ++k) {
+        for (; pos < windows[k]; ++pos) {
+            float leaving = s[pos], entering = s[pos + P];
+            e = e - leaving * leaving + entering * entering;
+            if (e < 0.0f) e = 0.0f;
+        }
+        out[k] = e;
+    }
+    (void)n;
+}
+
 // Correlation of every window in reference arithmetic (one search_for_preamble pass that
 // never stops: seed at window 0, rolling energy, AVX-order dot, energy gate).
 uint64_t orc_correlate(const tmk_phy_config* cfg, const float* s, uint64_t n, float* out) {

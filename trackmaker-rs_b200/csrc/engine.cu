@@ -612,6 +612,52 @@ int tmk_scan_probe(tmk_engine* e, const float* samples, uint64_t total_samples, 
     return TMK_OK;
 }
 
+int tmk_replay_probe(tmk_engine* e, const float* samples, uint64_t n_samples, const tmk_phy_config* cfg, uint64_t seed,
+                     const uint64_t* windows, uint32_t n_windows, float* energy, uint64_t counts[3]) {
+    if (!e || !samples || !cfg || (!windows && n_windows) || (!energy && n_windows))
+        return fail(e, TMK_E_INVALID, "tmk_replay_probe: null argument");
+    CK(cudaSetDevice(e->device));
+    tmk_stream st;
+    st.offset = 0;
+    st.n_samples = n_samples;
+    st.cfg = *cfg;
+    st.cfg.chunk = 0;
+    Batch b;
+    int rc = prepare_batch(e, n_samples, &st, 1, &b);
+    if (rc != TMK_OK) return rc;
+    const uint64_t P = e->patterns[b.sd[0].pattern].P;
+    uint64_t prev = seed;
+    for (uint32_t i = 0; i < n_windows; ++i) {
+        if (windows[i] < prev || windows[i] + P > n_samples)
+            return fail(e, TMK_E_INVALID, "tmk_replay_probe: windows must ascend from the seed and lie inside the capture");
+        prev = windows[i];
+    }
+    if (n_windows == 0) return TMK_OK;
+    CK(e->d_streams.reserve(sizeof(TmkStreamDev)));
+    CK(cudaMemcpyAsync(e->d_streams.p, b.sd.data(), sizeof(TmkStreamDev), cudaMemcpyHostToDevice, e->stream));
+    const void* d_samples = nullptr;
+    rc = stage_in(e, e->d_samples, samples, n_samples * sizeof(float), &d_samples);
+    if (rc != TMK_OK) return rc;
+    const size_t wbytes = sizeof(uint64_t) * n_windows, obytes = sizeof(float) * n_windows;
+    CK(e->d_misc.reserve(wbytes + obytes + 64));
+    char* dm = static_cast<char*>(e->d_misc.p);
+    CK(cudaMemcpyAsync(dm, windows, wbytes, cudaMemcpyHostToDevice, e->stream));
+    CK(e->d_misc2.reserve(64));
+    e->launches += tmk_launch_replay_probe(static_cast<const float*>(d_samples), static_cast<const TmkStreamDev*>(e->d_streams.p),
+                                           static_cast<const TmkPattern*>(e->d_patterns.p), seed,
+                                           reinterpret_cast<const uint64_t*>(dm), n_windows,
+                                           reinterpret_cast<float*>(dm + wbytes), static_cast<unsigned long long*>(e->d_misc2.p),
+                                           e->stream);
+    CK(cudaGetLastError());
+    CK(cudaMemcpyAsync(energy, dm + wbytes, obytes, cudaMemcpyDeviceToHost, e->stream));
+    unsigned long long hc[3] = {0, 0, 0};
+    CK(cudaMemcpyAsync(hc, e->d_misc2.p, sizeof hc, cudaMemcpyDeviceToHost, e->stream));
+    CK(cudaStreamSynchronize(e->stream));
+    if (counts)
+        for (int i = 0; i < 3; ++i) counts[i] = hc[i];
+    return TMK_OK;
+}
+
 int tmk_channel_busy(tmk_engine* e, const float* samples, uint64_t total_samples, const tmk_stream* streams,
                      uint32_t n_streams, int8_t* busy) {
     if (!e || (!samples && total_samples) || !streams || !busy) return fail(e, TMK_E_INVALID, "tmk_channel_busy: null argument");

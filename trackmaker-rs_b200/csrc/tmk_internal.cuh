@@ -162,6 +162,8 @@ int tmk_launch_walk(const float* samples, const TmkStreamDev* streams, uint32_t 
                     tmk_frame_rec* recs, uint32_t* rec_ord, uint64_t rec_cap, uint8_t* payload,
                     uint64_t payload_cap, uint32_t* stream_cnt, TmkCounters* counters, TmkLinkState* link_out,
                     cudaStream_t st);
+int tmk_launch_replay_probe(const float* samples, const TmkStreamDev* streams, const TmkPattern* patterns, uint64_t seed,
+                            const uint64_t* ws, uint32_t n, float* out, unsigned long long* counts, cudaStream_t st);
 int tmk_launch_order(const tmk_frame_rec* recs_in, const uint32_t* rec_ord, uint64_t n_recs,
                      const uint32_t* stream_cnt, uint64_t* stream_base, uint32_t n_streams,
                      tmk_frame_rec* recs_out, cudaStream_t st);

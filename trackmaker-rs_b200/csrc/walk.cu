@@ -1746,6 +1746,27 @@ __global__ void order_kernel(const tmk_frame_rec* __restrict__ in, const uint32_
 
 }  // namespace
 
+// parity probe of the exact replay (tmk_replay_probe): E_ref(w[i]) of a search seeded at `seed`, through the very
+// function the walk uses (cached chain position, lane-parallel rounds, literal rounds)
+__global__ void __launch_bounds__(32)
+replay_probe_kernel(const float* __restrict__ samples, const TmkStreamDev* __restrict__ streams,
+                    const TmkPattern* __restrict__ patterns, uint64_t seed, const uint64_t* __restrict__ ws, uint32_t n,
+                    float* __restrict__ out, unsigned long long* __restrict__ counts) {
+    Ctx c;
+    TmkFast nofast;
+    memset(&nofast, 0, sizeof nofast);
+    init_ctx(c, samples, streams[0], patterns, nullptr, nullptr, nofast, int(threadIdx.x), 0);
+    for (uint32_t i = 0; i < n; ++i) {
+        const float e = exact_energy(c, seed, ws[i]);
+        if (threadIdx.x == 0) out[i] = e;
+    }
+    if (threadIdx.x == 0) {
+        counts[0] = c.dbg[2];        // literal steps
+        counts[1] = c.n_par_steps;   // steps covered by lane-parallel rounds
+        counts[2] = c.n_par_doubt;   // segments rolled literally inside them
+    }
+}
+
 int tmk_walk_init() {
     uint8_t tab[kMaxFrameBytesCap + 8];
     uint32_t v = 1;  // x^0
@@ -1808,6 +1829,12 @@ int tmk_launch_walk(const float* samples, const TmkStreamDev* streams, uint32_t 
     if (grid > uint32_t(max_ctas)) grid = uint32_t(max_ctas);
     walk_kernel<<<grid, kWarpsPerCta * 32, 0, st>>>(samples, streams, s0, s1, next, fast, patterns, blk_info, cand_bits, recs,
                                                     rec_ord, rec_cap, payload, payload_cap, stream_cnt, counters, link_out);
+    return 1;
+}
+
+int tmk_launch_replay_probe(const float* samples, const TmkStreamDev* streams, const TmkPattern* patterns, uint64_t seed,
+                            const uint64_t* ws, uint32_t n, float* out, unsigned long long* counts, cudaStream_t st) {
+    replay_probe_kernel<<<1, 32, 0, st>>>(samples, streams, patterns, seed, ws, n, out, counts);
     return 1;
 }
 

@@ -277,6 +277,16 @@ class Engine:
                                              C.byref(nb), _ptr(base)))
         return info[:nb.value], bits[:nb.value], base
 
+    def replay_probe(self, cfg, samples, seed, windows):
+        """tmk_replay_probe -> (E_ref of the windows for a search entered at `seed`, counters dict)"""
+        s = np.ascontiguousarray(samples, dtype=np.float32)
+        w = np.ascontiguousarray(windows, dtype=np.uint64)
+        out = np.zeros(len(w), np.float32)
+        cnt = (C.c_uint64 * 3)()
+        self._check(self._lib.tmk_replay_probe(self._h, _ptr(s), s.size, C.byref(cfg), int(seed), _ptr(w), len(w),
+                                               _ptr(out), cnt))
+        return out, {"literal_steps": int(cnt[0]), "parallel_steps": int(cnt[1]), "parallel_doubts": int(cnt[2])}
+
     def channel_busy(self, samples, streams):
         s = np.ascontiguousarray(samples, dtype=np.float32)
         st = np.ascontiguousarray(streams, dtype=STREAM_DTYPE)
