@@ -1,4 +1,4 @@
-for v in "" _p128 _p256 _p1024; do
+for v in "" _w3 _w2; do
   export TMKPHY_LIB=$PWD/trackmaker-rs_b200/libtmkphy$v.so
   timeout 300 python bench.py --no-cpu --e2e-steps 0 --steps 5 --warmup 3 2>/dev/null | python -c "
 import json,sys

@@ -1522,7 +1522,10 @@ cluster_kernel(const float* __restrict__ samples, const TmkStreamDev* __restrict
 }
 
 #ifndef TMK_WALK_CTAS
-#define TMK_WALK_CTAS 4  // measured at C2: 4 -> 11.7 ms, 5 -> 12.8, 6 -> 12.2, 7 -> 15.4 (spills in process_block)
+// measured at C2 (walk kernel, ms): 2 CTAs/SM 3.72, 3 -> 3.71, 4 -> 3.99, 5 -> 4.21, 6 -> 4.44. The kernel is the sum of
+// the streams' serial latencies; beyond 12 warps per SM every warp slows the others down (instruction-cache misses
+// of warps that sit in different stages of 136 KB of code, spills below 168 registers).
+#define TMK_WALK_CTAS 3
 #endif
 __global__ void __launch_bounds__(kWarpsPerCta * 32, TMK_WALK_CTAS)
 walk_kernel(const float* __restrict__ samples, const TmkStreamDev* __restrict__ streams, uint32_t s0, uint32_t s1,
