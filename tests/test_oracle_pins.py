@@ -136,3 +136,40 @@ def test_ask_oracle_loopback(orc):
     decoded = np.packbits(bits[:, 8:100].reshape(-1)[:9200 // 8 * 8]).tobytes()
     n = min(len(decoded), len(text))
     assert decoded[:n] == text[:n]
+
+
+@pytest.mark.parametrize("kind", [FB, MAN])
+def test_feed_by_feed_decode_is_the_chunked_decode(orc, kind):
+    """decode_feeds (one PhyDecoder fed with process_samples calls, the checker of tmk_links_*) with equal call
+    sizes is decode_stream with cfg.chunk, and with ONE call the one-shot decode (src/main.rs:540)"""
+    import helpers
+    rng = np.random.default_rng(5)
+    cfg = orc.make_config(kind, local_addr=1)
+    x = helpers.make_capture(orc, cfg, rng, n_frames=5, snr_db=15.0)
+    for chunk in (1200, 257, len(x)):
+        c2 = orc.make_config(kind, local_addr=1, chunk=0 if chunk == len(x) else chunk)
+        want, wpl = orc.decode_stream(c2, x)
+        want = want[want["status"] != 6]  # a frame cut off by the end of the capture is not a record of any call
+        got, gpl, feed = orc.decode_feeds(cfg, x, [chunk] * (len(x) // chunk + 1))
+        helpers.assert_records_equal(got, gpl, want, wpl, f"chunk {chunk}")
+        assert (np.diff(feed.astype(np.int64)) >= 0).all()
+        assert len(got) >= 4
+
+
+def test_rolling_energy_is_the_energy_of_correlate(orc):
+    """orc.rolling_energy (the checker of tmk_replay_probe) against the search loop itself: corr = dot / (sqrt(E) pe),
+    so E follows from correlate() wherever corr != 0; here only consistency of the chain with a direct recompute at
+    the seed and of resumed queries"""
+    rng = np.random.default_rng(6)
+    x = rng.normal(0, 0.4, 5000).astype(np.float32)
+    e = orc.rolling_energy(x, 60, 100, [100, 101, 160, 4000])
+    seed_sum = np.float32(0)
+    for v in x[100:160]:
+        seed_sum = np.float32(seed_sum + np.float32(v * v))
+    assert e[0] == seed_sum
+    step = np.float32(np.float32(seed_sum - np.float32(x[100] * x[100])) + np.float32(x[160] * x[160]))
+    assert e[1] == max(step, np.float32(0))
+    again = orc.rolling_energy(x, 60, 100, [4000])
+    assert again[0] == e[3]
+    exact = float((x[4000:4060].astype(np.float64) ** 2).sum())
+    assert abs(float(e[3]) - exact) < 1e-3 * exact
