@@ -292,7 +292,14 @@ __device__ __noinline__ float roll_parallel(Ctx& c, float e, uint64_t* pos_io, u
             S += double(ex_mul(v.z, v.z));
             S += double(ex_mul(v.w, v.w));
         }
-        const float g = __double2float_rn(S);
+        // The chain's drift against the accurately summed energy is a slow random walk (hundreds of ulps after 100 k
+        // steps, a few tens more over one round), so every guess is shifted by the drift measured at the start of
+        // the round: the translations that remain are a few tens of ulps and far fewer segments end up in doubt.
+        float g = __double2float_rn(S);
+        {
+            const float d0 = ex_sub(e, __shfl_sync(kFull, g, 0));
+            if (fabsf(d0) <= 0.01f * g) g = ex_add(g, d0);  // (NaN / wild values: keep the plain guess)
+        }
         const uint32_t gbits = __float_as_uint(g);
         const uint32_t gexp = gbits >> 23;  // (sign bit set -> huge -> rejected)
         bool ok = gexp >= 32u && gexp <= 250u && (gbits & kM) <= 0x7ffff0u;
