@@ -288,6 +288,77 @@ int tmk_ask_decode_batch(tmk_engine* e, const float* samples, uint64_t total_sam
 /* device time of the stages of the last tmk_ask_decode_batch call, ms: [0] chirp scan, [1] walk */
 int tmk_ask_last_stage_ms(tmk_engine* e, float ms[2]);
 
+/* ------------------------------------------------------------------------------------------------
+ * 16-bit PCM captures. Recordings reach the reference as int16 WAV:
+ *   tmk_pcm16_encode        replaces the sample loop of dump_to_wav   src/utils/dump.rs:37-40
+ *                           amplitude = (sample * i16::MAX as f32) as i16  (Rust `as`: truncates toward zero,
+ *                           saturates at -32768 / 32767, NaN -> 0)
+ *   tmk_pcm16_to_f32        replaces the S16 arm of convert_audio_buffer_to_f32   src/audio/codec.rs:121-125
+ *                           sample as f32 / 32768.0 (exact in f32)
+ *   tmk_decode_batch_pcm16  = tmk_pcm16_to_f32 on the device followed by tmk_decode_batch: host captures cross
+ *                           PCIe as 2 bytes per sample; records / payload exactly as tmk_decode_batch returns them
+ *                           for the converted samples. stream offsets are multiples of 4 samples, the pcm base
+ *                           pointer is 8-byte aligned.
+ * All pointers host or device. */
+int tmk_pcm16_encode(tmk_engine* e, const float* samples, uint64_t n, int16_t* pcm_out);
+int tmk_pcm16_to_f32(tmk_engine* e, const int16_t* pcm, uint64_t n, float* samples_out);
+int tmk_decode_batch_pcm16(tmk_engine* e, const int16_t* pcm, uint64_t total_samples, const tmk_stream* streams,
+                           uint32_t n_streams, tmk_frame_rec* recs, uint64_t rec_cap, uint64_t* n_recs,
+                           uint8_t* payload, uint64_t payload_cap, uint64_t* payload_len);
+
+/* ------------------------------------------------------------------------------------------------
+ * IP fragments: the payload layer directly above the PHY. Decoded frames carry IPv4 packets or
+ * fragments of them in Frame::data.
+ *   tmk_reassemble_batch  replaces, per link, the loop of AcousticInterface::receive_packet
+ *                         (src/mac/acoustic_interface.rs:343-366: frames with type Data, or Ack with data, go to the
+ *                         reassembler) around IpReassembler::process_fragment (src/net/fragmentation.rs:232-401):
+ *                         key (identification, source ip); a packet with MF = 0 and offset 0 passes through
+ *                         unchanged; fragments are kept in arrival order, and once the MF = 0 fragment of a key was
+ *                         seen every arrival re-checks the stable-sorted offsets for a gap-free chain starting at 0
+ *                         (next = offset + ceil(len / 8)); a complete datagram = header of the FIRST fragment that
+ *                         arrived + payloads in offset order, total_length rewritten (as u16), bytes 6..8 zeroed,
+ *                         the key forgotten. Every link starts with an empty reassembler and, unlike
+ *                         receive_packet (which returns at the first packet), every packet of the capture is
+ *                         returned; an Err of process_fragment (fragmentation.rs:236-249) is a record with
+ *                         status != TMK_PKT_OK instead of an early return.
+ *   tmk_fragment_batch    replaces IpFragmenter::fragment_packet (src/net/fragmentation.rs:85-203) for a list of
+ *                         packets sent through ONE fragmenter: packets <= mtu pass unchanged, others are cut into
+ *                         ((mtu - ihl) / 8) * 8-byte pieces under copies of the first 20 header bytes (+ options)
+ *                         with identification = first_identification + (number of fragmented packets before it),
+ *                         wrapping; flags/offset, total length rewritten, checksum copied as is.
+ */
+#define TMK_PKT_OK 0
+#define TMK_PKT_E_SHORT 1      /* fragmentation.rs:236-240 / :111-113: fewer than 20 bytes */
+#define TMK_PKT_E_IHL 2        /* fragmentation.rs:246-248 / :122-124: ihl < 20 or ihl > len */
+#define TMK_PKT_E_TOO_MANY 3   /* more than TMK_MAX_FRAGMENTS fragments under one key (engine limit) */
+#define TMK_PKT_E_MTU 4        /* fragmentation.rs:131-136: (mtu - ihl) / 8 == 0 */
+#define TMK_MAX_FRAGMENTS 512
+
+typedef struct tmk_packet_rec {
+    uint32_t link;      /* reassembly: stream index of the frames; fragmentation: index of the input packet */
+    uint32_t status;    /* TMK_PKT_* */
+    uint32_t frame;     /* reassembly: index of the frame record that completed (or failed) the packet;
+                           fragmentation: index of the fragment within its packet */
+    uint32_t len;       /* bytes at data_off (0 when status != TMK_PKT_OK) */
+    uint64_t data_off;  /* into the output byte buffer */
+    uint16_t identification;
+    uint16_t n_fragments; /* reassembly: fragments joined (1 for a pass-through packet) */
+    uint32_t _pad;
+} tmk_packet_rec;
+
+/* recs / payload: what tmk_decode_batch returned (host or device), sorted by stream. pkts (host) sorted by
+ * (link, frame); bytes (host). */
+int tmk_reassemble_batch(tmk_engine* e, const tmk_frame_rec* recs, uint64_t n_recs, const uint8_t* payload,
+                         uint64_t payload_len, uint32_t n_links, tmk_packet_rec* pkts, uint64_t pkt_cap,
+                         uint64_t* n_pkts, uint8_t* bytes, uint64_t byte_cap, uint64_t* n_bytes);
+/* packets: n_packets IPv4 packets, packet i = data[pkt_off[i] .. pkt_off[i + 1]) (host or device; pkt_off host).
+ * frags (host): one record per output fragment sorted by (link = packet, frame = fragment index), or one record
+ * with status != TMK_PKT_OK for a packet fragment_packet would reject. *next_identification (optional) receives
+ * the fragmenter's counter after the batch. */
+int tmk_fragment_batch(tmk_engine* e, const uint8_t* data, const uint64_t* pkt_off, uint32_t n_packets, uint32_t mtu,
+                       uint16_t first_identification, tmk_packet_rec* frags, uint64_t frag_cap, uint64_t* n_frags,
+                       uint8_t* bytes, uint64_t byte_cap, uint64_t* n_bytes, uint16_t* next_identification);
+
 #ifdef __cplusplus
 }
 #endif

@@ -20,7 +20,7 @@ LIB = os.path.join(_HERE, "liboracle.so")
 
 
 def build(force=False):
-    srcs = [os.path.join(_HERE, f) for f in ("oracle_capi.cpp", "phy_core.hpp", "phy_decoder.hpp")]
+    srcs = [os.path.join(_HERE, f) for f in ("oracle_capi.cpp", "phy_core.hpp", "phy_decoder.hpp", "ask_modem.hpp", "ip_fragments.hpp")]
     if force or not os.path.exists(LIB) or any(os.path.getmtime(s) > os.path.getmtime(LIB) for s in srcs):
         subprocess.check_call(["make", "-C", _HERE, "-B", "liboracle.so"], stdout=subprocess.DEVNULL)
 
@@ -54,6 +54,13 @@ def lib():
             "orc_rolling_energy": (None, [vp, u64, u32, u64, vp, u32, vp]),
             "orc_channel_busy": (C.c_int, [vp, u64]),
             "orc_hardware_threads": (C.c_int, []),
+            "orc_pcm16_encode": (None, [vp, u64, vp]),
+            "orc_pcm16_to_f32": (None, [vp, u64, vp]),
+            "orc_fraginfo_to_u16": (C.c_uint16, [C.c_uint16, C.c_int, C.c_uint16]),
+            "orc_fraginfo_from_u16": (None, [C.c_uint16, C.POINTER(C.c_int), C.POINTER(C.c_uint16)]),
+            "orc_fragment_batch": (u64, [vp, vp, u32, u32, C.c_uint16, vp, u64, vp, u64, C.POINTER(u64),
+                                         C.POINTER(C.c_uint16)]),
+            "orc_reassemble_batch": (u64, [vp, u64, vp, u32, vp, u64, vp, u64, C.POINTER(u64)]),
             "orc_ask_tables": (None, [vp, vp, u64]),
             "orc_ask_modulate": (u64, [vp, u32, vp, vp, vp, u64]),
             "orc_ask_demodulate": (u64, [vp, u64, u32, vp, u64]),
@@ -244,3 +251,60 @@ def ask_demodulate(samples, stream=0, cap=None) -> np.ndarray:
     n = lib().orc_ask_demodulate(_ptr(s), len(s), stream, _ptr(recs), cap)
     assert n <= cap
     return recs[:n].copy()
+
+
+# ---- 16-bit PCM (dump.rs:37-40, codec.rs:121-125)
+def pcm16_encode(samples) -> np.ndarray:
+    s = np.ascontiguousarray(samples, dtype=np.float32)
+    out = np.zeros(s.size, np.int16)
+    lib().orc_pcm16_encode(_ptr(s), s.size, _ptr(out))
+    return out
+
+
+def pcm16_to_f32(pcm) -> np.ndarray:
+    p = np.ascontiguousarray(pcm, dtype=np.int16)
+    out = np.zeros(p.size, np.float32)
+    lib().orc_pcm16_to_f32(_ptr(p), p.size, _ptr(out))
+    return out
+
+
+# ---- IP fragments (fragmentation.rs)
+def fraginfo_to_u16(identification, more, offset) -> int:
+    return lib().orc_fraginfo_to_u16(identification, int(more), offset)
+
+
+def fraginfo_from_u16(v):
+    more, off = C.c_int(0), C.c_uint16(0)
+    lib().orc_fraginfo_from_u16(v, C.byref(more), C.byref(off))
+    return bool(more.value), int(off.value)
+
+
+def fragment_batch(packets, mtu, first_identification=0):
+    """One IpFragmenter over a list of packets: (records[PKT_DTYPE], bytes, next_identification)."""
+    from tmkphy._abi import PKT_DTYPE
+    off = np.zeros(len(packets) + 1, np.uint64)
+    if packets:
+        off[1:] = np.cumsum([len(p) for p in packets], dtype=np.uint64)
+    data = np.frombuffer(b"".join(bytes(p) for p in packets) + b"\0", dtype=np.uint8).copy()
+    cap = len(packets) + int(off[-1]) // 8 + 8
+    bcap = int(off[-1]) + 60 * cap + 64
+    fr, by = np.zeros(cap, PKT_DTYPE), np.zeros(bcap, np.uint8)
+    nb, nid = C.c_uint64(0), C.c_uint16(0)
+    n = lib().orc_fragment_batch(_ptr(data), _ptr(off), len(packets), int(mtu), int(first_identification) & 0xffff,
+                                 _ptr(fr), cap, _ptr(by), bcap, C.byref(nb), C.byref(nid))
+    assert n <= cap and nb.value <= bcap
+    return fr[:n].copy(), by[:nb.value].copy(), int(nid.value)
+
+
+def reassemble_batch(recs, payload, n_links):
+    from tmkphy._abi import PKT_DTYPE
+    r = np.ascontiguousarray(recs, dtype=REC_DTYPE)
+    pl = np.ascontiguousarray(payload, dtype=np.uint8)
+    if pl.size == 0:
+        pl = np.zeros(1, np.uint8)
+    cap, bcap = max(16, len(r)), max(4096, pl.size + 64 * len(r))
+    pk, by = np.zeros(cap, PKT_DTYPE), np.zeros(bcap, np.uint8)
+    nb = C.c_uint64(0)
+    n = lib().orc_reassemble_batch(_ptr(r), len(r), _ptr(pl), int(n_links), _ptr(pk), cap, _ptr(by), bcap, C.byref(nb))
+    assert n <= cap and nb.value <= bcap
+    return pk[:n].copy(), by[:nb.value].copy()

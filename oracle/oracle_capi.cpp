@@ -5,6 +5,7 @@
 #include <thread>
 
 #include "ask_modem.hpp"
+#include "ip_fragments.hpp"
 #include "phy_decoder.hpp"
 
 using namespace orc;
@@ -242,6 +243,90 @@ uint64_t orc_ask_demodulate(const float* rx, uint64_t n, uint32_t stream, tmk_as
         recs[i] = r;
     }
     return v.size();
+}
+
+// ---- 16-bit PCM (dump.rs:37-40, codec.rs:121-125)
+void orc_pcm16_encode(const float* s, uint64_t n, int16_t* out) {
+    for (uint64_t i = 0; i < n; ++i) out[i] = pcm16_of(s[i]);
+}
+void orc_pcm16_to_f32(const int16_t* p, uint64_t n, float* out) {
+    for (uint64_t i = 0; i < n; ++i) out[i] = f32_of_pcm16(p[i]);
+}
+
+// ---- IP fragments (fragmentation.rs)
+uint16_t orc_fraginfo_to_u16(uint16_t id, int more, uint16_t off) { return FragmentationInfo{id, more != 0, off}.to_u16(); }
+void orc_fraginfo_from_u16(uint16_t v, int* more, uint16_t* off) {
+    const auto fi = FragmentationInfo::from_u16(v);
+    *more = fi.more_fragments;
+    *off = fi.fragment_offset;
+}
+
+// one IpFragmenter over a list of packets (packet i = data[off[i] .. off[i+1])). Records as tmk_fragment_batch.
+uint64_t orc_fragment_batch(const uint8_t* data, const uint64_t* off, uint32_t n, uint32_t mtu, uint16_t first_id,
+                            tmk_packet_rec* frags, uint64_t frag_cap, uint8_t* bytes, uint64_t byte_cap, uint64_t* n_bytes,
+                            uint16_t* next_id) {
+    IpFragmenter fr(mtu);
+    fr.next_id = first_id;
+    uint64_t nf = 0, nb = 0;
+    for (uint32_t i = 0; i < n; ++i) {
+        Bytes pkt(data + off[i], data + off[i + 1]);
+        std::vector<Bytes> out;
+        const uint16_t id = fr.next_id;
+        const std::string err = fr.fragment_packet(pkt, out);
+        if (!err.empty()) {
+            const uint32_t st = err.find("too small for header") != std::string::npos ? TMK_PKT_E_SHORT
+                                : err.find("header length") != std::string::npos    ? TMK_PKT_E_IHL
+                                                                                     : TMK_PKT_E_MTU;
+            if (nf < frag_cap) frags[nf] = tmk_packet_rec{i, st, 0, 0, nb, 0, 0, 0};
+            ++nf;
+            continue;
+        }
+        const bool cut = fr.next_id != id;
+        for (size_t f = 0; f < out.size(); ++f) {
+            if (nf < frag_cap) frags[nf] = tmk_packet_rec{i, TMK_PKT_OK, uint32_t(f), uint32_t(out[f].size()), nb,
+                                                          uint16_t(cut ? id : 0), uint16_t(out.size()), 0};
+            ++nf;
+            if (nb + out[f].size() <= byte_cap) std::copy(out[f].begin(), out[f].end(), bytes + nb);
+            nb += out[f].size();
+        }
+    }
+    *n_bytes = nb;
+    *next_id = fr.next_id;
+    return nf;
+}
+
+// per link one IpReassembler fed with the frames receive_packet would hand it (acoustic_interface.rs:343-366);
+// records sorted by stream as tmk_decode_batch returns them.
+uint64_t orc_reassemble_batch(const tmk_frame_rec* recs, uint64_t n_recs, const uint8_t* payload, uint32_t n_links,
+                              tmk_packet_rec* pkts, uint64_t pkt_cap, uint8_t* bytes, uint64_t byte_cap, uint64_t* n_bytes) {
+    uint64_t np = 0, nb = 0, i = 0;
+    while (i < n_recs) {
+        const uint32_t link = recs[i].stream;
+        IpReassembler ra;
+        for (; i < n_recs && recs[i].stream == link; ++i) {
+            const tmk_frame_rec& r = recs[i];
+            if (link >= n_links || r.status != TMK_FRAME_OK) continue;
+            if (!(r.type == TMK_FRAME_TYPE_DATA || (r.type == TMK_FRAME_TYPE_ACK && r.len != 0))) continue;
+            Bytes out;
+            const uint8_t* p = payload + r.payload_off;
+            const int rc = ra.process_fragment(p, r.len, out);
+            if (rc == 0) continue;
+            tmk_packet_rec pr{link, TMK_PKT_OK, uint32_t(i), 0, nb, 0, 0, 0};
+            if (rc < 0) {
+                pr.status = rc == -1 ? TMK_PKT_E_SHORT : TMK_PKT_E_IHL;
+            } else {
+                pr.len = uint32_t(out.size());
+                pr.identification = uint16_t(p[4] << 8 | p[5]);
+                pr.n_fragments = uint16_t(ra.joined);
+                if (nb + out.size() <= byte_cap) std::copy(out.begin(), out.end(), bytes + nb);
+                nb += out.size();
+            }
+            if (np < pkt_cap) pkts[np] = pr;
+            ++np;
+        }
+    }
+    *n_bytes = nb;
+    return np;
 }
 
 int orc_hardware_threads(void) { return int(std::thread::hardware_concurrency()); }

@@ -173,3 +173,53 @@ def test_rolling_energy_is_the_energy_of_correlate(orc):
     assert again[0] == e[3]
     exact = float((x[4000:4060].astype(np.float64) ** 2).sum())
     assert abs(float(e[3]) - exact) < 1e-3 * exact
+
+
+# ---------------------------------------------------------------- §8 f3: src/net/fragmentation.rs:404-515
+def test_fragmentation_info_encode_decode(orc):  # fragmentation.rs:408-423
+    enc = orc.fraginfo_to_u16(12345, True, 100)
+    assert enc & 0x2000 == 0x2000 and enc & 0x1FFF == 100
+    assert orc.fraginfo_from_u16(enc) == (True, 100)
+
+
+def _frags(orc, pkt, mtu, first=0):
+    fr, by, nid = orc.fragment_batch([pkt], mtu, first)
+    assert (fr["status"] == 0).all()
+    return [bytes(by[int(r["data_off"]):int(r["data_off"]) + int(r["len"])]) for r in fr], nid
+
+
+def test_no_fragmentation_needed(orc):  # fragmentation.rs:425-437
+    frs, nid = _frags(orc, bytes(100), 500)
+    assert frs == [bytes(100)] and nid == 0
+
+
+def test_fragmentation_basic(orc):  # fragmentation.rs:439-457
+    frs, nid = _frags(orc, b"\x45" * 20 + bytes(300), 100)
+    assert len(frs) > 1 and all(len(f) <= 100 for f in frs) and nid == 1
+    assert len(frs) == 4 and [len(f) for f in frs] == [100, 100, 100, 80]
+
+
+def test_fragment_assemble(orc):  # fragmentation.rs:459-514
+    from tmkphy._abi import REC_DTYPE
+    hdr = bytes([0x45, 0, 0, 0, 0, 0, 0, 0, 0x40, 0x11, 0, 0, 192, 168, 1, 1, 192, 168, 1, 2])
+    payload = bytes(range(100))
+    pkt = bytearray(hdr + payload)
+    pkt[2:4] = len(pkt).to_bytes(2, "big")
+    frs, _ = _frags(orc, bytes(pkt), 60)
+    assert len(frs) > 1
+    recs = np.zeros(len(frs), REC_DTYPE)
+    blob = b""
+    for i, f in enumerate(frs):
+        recs[i]["type"], recs[i]["len"], recs[i]["payload_off"] = 1, len(f), len(blob)
+        blob += f
+    pk, by = orc.reassemble_batch(recs, np.frombuffer(blob, np.uint8), 1)
+    assert len(pk) == 1 and pk[0]["frame"] == len(frs) - 1 and pk[0]["status"] == 0
+    out = bytes(by)
+    assert out[20:] == payload and out[:2] == bytes(pkt[:2]) and out[2:4] == len(pkt).to_bytes(2, "big") and out[6:8] == b"\0\0"
+
+
+def test_pcm16_rules(orc):  # dump.rs:37-40 (Rust `as i16`), codec.rs:121-125
+    x = np.array([0.0, 1.0, -1.0, 0.5, -0.5, 2.0, -2.0, np.nan, np.inf, -np.inf, 0.99999, 3.1e-5], np.float32)
+    assert orc.pcm16_encode(x).tolist() == [0, 32767, -32767, 16383, -16383, 32767, -32768, 0, 32767, -32768, 32766, 1]
+    p = np.array([-32768, -1, 0, 1, 16384, 32767], np.int16)
+    assert orc.pcm16_to_f32(p).tolist() == [-1.0, -1 / 32768, 0.0, 1 / 32768, 0.5, 32767 / 32768]

@@ -193,7 +193,7 @@ void tmk_engine_destroy(tmk_engine* e) {
     if (e->stream) cudaStreamSynchronize(e->stream);
     DevBuf* bufs[] = {&e->d_tile_dir, &e->d_patterns, &e->d_streams, &e->d_blk_info, &e->d_cand, &e->d_recs_tmp, &e->d_rec_ord,
                       &e->d_recs, &e->d_payload, &e->d_cnt, &e->d_base, &e->d_counters, &e->d_samples,
-                      &e->d_misc, &e->d_misc2, &e->d_next, &e->d_cblk, &e->d_blk_ptr, &e->d_entries, &e->d_spec, &e->d_pool, &e->d_link,
+                      &e->d_misc, &e->d_misc2, &e->d_next, &e->d_cblk, &e->d_blk_ptr, &e->d_entries, &e->d_spec, &e->d_pool, &e->d_link, &e->d_pcm, &e->d_frag,
                       &e->d_ask_tab, &e->d_ask_bits, &e->d_ask_l2,
                       &e->d_ask_recs, &e->d_ask_recs2};
     for (DevBuf* b : bufs) b->release();
@@ -291,10 +291,14 @@ int tmk_modulate(tmk_engine* e, const tmk_phy_config* cfg, const tmk_frame_desc*
     return TMK_OK;
 }
 
-int tmk_decode_batch(tmk_engine* e, const float* samples, uint64_t total_samples, const tmk_stream* streams,
-                     uint32_t n_streams, tmk_frame_rec* recs, uint64_t rec_cap, uint64_t* n_recs, uint8_t* payload,
-                     uint64_t payload_cap, uint64_t* payload_len) {
-    if (!e || (!samples && total_samples) || (!streams && n_streams) || !n_recs || !payload_len ||
+// tmk_decode_batch / tmk_decode_batch_pcm16: `samples_v` is f32, or int16 PCM that is widened on the device
+// (codec.rs:121-125) chunk by chunk in front of the scan.
+static int decode_batch_impl(tmk_engine* e, const void* samples_v, bool pcm16, uint64_t total_samples, const tmk_stream* streams,
+                             uint32_t n_streams, tmk_frame_rec* recs, uint64_t rec_cap, uint64_t* n_recs, uint8_t* payload,
+                             uint64_t payload_cap, uint64_t* payload_len) {
+    const float* samples = pcm16 ? nullptr : static_cast<const float*>(samples_v);
+    const int16_t* pcm = pcm16 ? static_cast<const int16_t*>(samples_v) : nullptr;
+    if (!e || (!samples_v && total_samples) || (!streams && n_streams) || !n_recs || !payload_len ||
         (!recs && rec_cap) || (!payload && payload_cap))
         return fail(e, TMK_E_INVALID, "tmk_decode_batch: null argument");
     *n_recs = 0;
@@ -326,7 +330,7 @@ int tmk_decode_batch(tmk_engine* e, const float* samples, uint64_t total_samples
     CK(cudaEventRecord(e->ev[0], e->stream));
     // Host-resident captures are staged in chunks of whole streams: the copy of chunk g+1 (copy stream)
     // overlaps the scan + walk of chunk g (compute stream). Device-resident captures are one chunk.
-    const bool host_samples = total_samples && !is_device_ptr(samples);
+    const bool host_samples = total_samples && !is_device_ptr(samples_v);
     struct Chunk { uint32_t s0, s1, t0, t1; uint64_t lo, hi; };
     std::vector<Chunk> chunks;
     {
@@ -362,9 +366,17 @@ int tmk_decode_batch(tmk_engine* e, const float* samples, uint64_t total_samples
         }
     }
     const float* dx = samples;
-    if (host_samples) {
+    const int16_t* dpcm = pcm;
+    if (host_samples || pcm16) {
         CK(e->d_samples.reserve(total_samples * sizeof(float)));
         dx = static_cast<const float*>(e->d_samples.p);
+    }
+    if (pcm16) {
+        if (reinterpret_cast<uintptr_t>(pcm) % 8 != 0) return fail(e, TMK_E_INVALID, "pcm buffer must be 8-byte aligned");
+        if (host_samples) {
+            CK(e->d_pcm.reserve(total_samples * sizeof(int16_t)));
+            dpcm = static_cast<const int16_t*>(e->d_pcm.p);
+        }
     }
     CK(e->d_blk_info.reserve(sizeof(float4) * std::max<uint64_t>(1, b.n_blocks)));
     CK(e->d_cand.reserve(sizeof(uint32_t) * TMK_BLK_WORDS * std::max<uint64_t>(1, b.n_blocks)));
@@ -442,12 +454,17 @@ int tmk_decode_batch(tmk_engine* e, const float* samples, uint64_t total_samples
     for (size_t g = 0; g < chunks.size(); ++g) {
         const Chunk& ch = chunks[g];
         if (host_samples) {
-            CK(cudaMemcpyAsync(const_cast<float*>(dx) + ch.lo, samples + ch.lo, (ch.hi - ch.lo) * sizeof(float),
-                               cudaMemcpyHostToDevice, e->copy_stream));
+            if (pcm16)
+                CK(cudaMemcpyAsync(const_cast<int16_t*>(dpcm) + ch.lo, pcm + ch.lo, (ch.hi - ch.lo) * sizeof(int16_t),
+                                   cudaMemcpyHostToDevice, e->copy_stream));
+            else
+                CK(cudaMemcpyAsync(const_cast<float*>(dx) + ch.lo, samples + ch.lo, (ch.hi - ch.lo) * sizeof(float),
+                                   cudaMemcpyHostToDevice, e->copy_stream));
             cudaEvent_t ce = e->cev[1 + (g & 1)];
             CK(cudaEventRecord(ce, e->copy_stream));
             CK(cudaStreamWaitEvent(e->stream, ce, 0));
         }
+        if (pcm16) e->launches += tmk_launch_pcm16_to_f32(dpcm + ch.lo, const_cast<float*>(dx) + ch.lo, ch.hi - ch.lo, e->stream);
         const TmkFast fast = fast_of(g, ch);
         e->launches += tmk_launch_scan(dx, total_samples, ds, n_streams, dtd, ch.t0, ch.t1 - ch.t0, dp, b.kinds, dbi, dcb,
                                        const_cast<uint32_t*>(fast.cblk_list), fast.cblk_count, e->stream);
@@ -544,6 +561,60 @@ int tmk_decode_batch(tmk_engine* e, const float* samples, uint64_t total_samples
     cudaEventElapsedTime(&e->stage_ms[1], e->ev[2], e->ev[3]);
     cudaEventElapsedTime(&e->stage_ms[2], e->ev[3], e->ev[4]);
     if (overflow) return fail(e, TMK_E_CAPACITY, "tmk_decode_batch: record or payload buffer too small");
+    return TMK_OK;
+}
+
+int tmk_decode_batch(tmk_engine* e, const float* samples, uint64_t total_samples, const tmk_stream* streams,
+                     uint32_t n_streams, tmk_frame_rec* recs, uint64_t rec_cap, uint64_t* n_recs, uint8_t* payload,
+                     uint64_t payload_cap, uint64_t* payload_len) {
+    return decode_batch_impl(e, samples, false, total_samples, streams, n_streams, recs, rec_cap, n_recs, payload, payload_cap,
+                             payload_len);
+}
+
+int tmk_decode_batch_pcm16(tmk_engine* e, const int16_t* pcm, uint64_t total_samples, const tmk_stream* streams,
+                           uint32_t n_streams, tmk_frame_rec* recs, uint64_t rec_cap, uint64_t* n_recs, uint8_t* payload,
+                           uint64_t payload_cap, uint64_t* payload_len) {
+    return decode_batch_impl(e, pcm, true, total_samples, streams, n_streams, recs, rec_cap, n_recs, payload, payload_cap,
+                             payload_len);
+}
+
+int tmk_pcm16_encode(tmk_engine* e, const float* samples, uint64_t n, int16_t* pcm_out) {
+    if (!e || ((!samples || !pcm_out) && n)) return fail(e, TMK_E_INVALID, "tmk_pcm16_encode: null argument");
+    if (n == 0) return TMK_OK;
+    CK(cudaSetDevice(e->device));
+    const void* d_in = nullptr;
+    int rc = stage_in(e, e->d_samples, samples, n * sizeof(float), &d_in);
+    if (rc != TMK_OK) return rc;
+    int16_t* d_out = pcm_out;
+    const bool dev_out = is_device_ptr(pcm_out);
+    if (!dev_out) {
+        CK(e->d_pcm.reserve(n * sizeof(int16_t)));
+        d_out = static_cast<int16_t*>(e->d_pcm.p);
+    }
+    e->launches += tmk_launch_pcm16_encode(static_cast<const float*>(d_in), d_out, n, e->stream);
+    CK(cudaGetLastError());
+    if (!dev_out) CK(cudaMemcpyAsync(pcm_out, d_out, n * sizeof(int16_t), cudaMemcpyDeviceToHost, e->stream));
+    CK(cudaStreamSynchronize(e->stream));
+    return TMK_OK;
+}
+
+int tmk_pcm16_to_f32(tmk_engine* e, const int16_t* pcm, uint64_t n, float* samples_out) {
+    if (!e || ((!pcm || !samples_out) && n)) return fail(e, TMK_E_INVALID, "tmk_pcm16_to_f32: null argument");
+    if (n == 0) return TMK_OK;
+    CK(cudaSetDevice(e->device));
+    const void* d_in = nullptr;
+    int rc = stage_in(e, e->d_pcm, pcm, n * sizeof(int16_t), &d_in);
+    if (rc != TMK_OK) return rc;
+    float* d_out = samples_out;
+    const bool dev_out = is_device_ptr(samples_out);
+    if (!dev_out) {
+        CK(e->d_samples.reserve(n * sizeof(float)));
+        d_out = static_cast<float*>(e->d_samples.p);
+    }
+    e->launches += tmk_launch_pcm16_to_f32(static_cast<const int16_t*>(d_in), d_out, n, e->stream);
+    CK(cudaGetLastError());
+    if (!dev_out) CK(cudaMemcpyAsync(samples_out, d_out, n * sizeof(float), cudaMemcpyDeviceToHost, e->stream));
+    CK(cudaStreamSynchronize(e->stream));
     return TMK_OK;
 }
 

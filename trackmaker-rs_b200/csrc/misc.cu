@@ -1,5 +1,7 @@
 // misc.cu — small kernels around the hot path: modulator (PhyEncoder), correlation probe,
 // channel-busy detector.
+#include <algorithm>
+
 #include "tmk_internal.cuh"
 
 namespace {
@@ -172,7 +174,54 @@ __global__ void busy_kernel(const float* __restrict__ samples, const TmkStreamDe
     if (threadIdx.x == 0) busy[blockIdx.x] = any ? 1 : 0;
 }
 
+// ---------------------------------------------------------------- 16-bit PCM
+// convert_audio_buffer_to_f32, S16 arm (src/audio/codec.rs:121-125): sample as f32 / 32768.0 — a power-of-two scale,
+// exact. Four samples per thread per step: one 8-byte load, one 16-byte store, grid-stride over 148 x 8 CTAs.
+__global__ void __launch_bounds__(256) pcm16_to_f32_kernel(const int16_t* __restrict__ pcm, float* __restrict__ out, uint64_t n) {
+    const uint64_t n4 = n / 4, stride = uint64_t(gridDim.x) * blockDim.x;
+    const short4* __restrict__ in4 = reinterpret_cast<const short4*>(pcm);
+    float4* __restrict__ out4 = reinterpret_cast<float4*>(out);
+    for (uint64_t i = uint64_t(blockIdx.x) * blockDim.x + threadIdx.x; i < n4; i += stride) {
+        const short4 v = __ldg(in4 + i);
+        out4[i] = make_float4(float(v.x) * (1.0f / 32768.0f), float(v.y) * (1.0f / 32768.0f), float(v.z) * (1.0f / 32768.0f),
+                              float(v.w) * (1.0f / 32768.0f));
+    }
+    if (blockIdx.x == 0 && threadIdx.x < (n & 3)) out[n4 * 4 + threadIdx.x] = float(pcm[n4 * 4 + threadIdx.x]) * (1.0f / 32768.0f);
+}
+
+// dump_to_wav (src/utils/dump.rs:37-40): (sample * i16::MAX as f32) as i16. Rust's float -> int `as` truncates toward
+// zero, saturates, and maps NaN to 0: cvt.rzi.s32.f32 does the same at 32 bits, then the clamp to 16.
+__device__ __forceinline__ int16_t pcm16_of(float s) {
+    const int v = __float2int_rz(__fmul_rn(s, 32767.0f));
+    return int16_t(max(-32768, min(32767, v)));
+}
+
+__global__ void __launch_bounds__(256) pcm16_encode_kernel(const float* __restrict__ x, int16_t* __restrict__ out, uint64_t n) {
+    const uint64_t n4 = n / 4, stride = uint64_t(gridDim.x) * blockDim.x;
+    const float4* __restrict__ in4 = reinterpret_cast<const float4*>(x);
+    short4* __restrict__ out4 = reinterpret_cast<short4*>(out);
+    for (uint64_t i = uint64_t(blockIdx.x) * blockDim.x + threadIdx.x; i < n4; i += stride) {
+        const float4 v = __ldg(in4 + i);
+        out4[i] = make_short4(pcm16_of(v.x), pcm16_of(v.y), pcm16_of(v.z), pcm16_of(v.w));
+    }
+    if (blockIdx.x == 0 && threadIdx.x < (n & 3)) out[n4 * 4 + threadIdx.x] = pcm16_of(x[n4 * 4 + threadIdx.x]);
+}
+
 }  // namespace
+
+int tmk_launch_pcm16_to_f32(const int16_t* pcm, float* out, uint64_t n, cudaStream_t st) {
+    if (n == 0) return 0;
+    const uint64_t want = (n / 4 + 255) / 256;
+    pcm16_to_f32_kernel<<<unsigned(std::min<uint64_t>(std::max<uint64_t>(want, 1), 148 * 8)), 256, 0, st>>>(pcm, out, n);
+    return 1;
+}
+
+int tmk_launch_pcm16_encode(const float* samples, int16_t* out, uint64_t n, cudaStream_t st) {
+    if (n == 0) return 0;
+    const uint64_t want = (n / 4 + 255) / 256;
+    pcm16_encode_kernel<<<unsigned(std::min<uint64_t>(std::max<uint64_t>(want, 1), 148 * 8)), 256, 0, st>>>(samples, out, n);
+    return 1;
+}
 
 int tmk_launch_modulate(const TmkPattern* pattern, const tmk_frame_desc* frames, const uint64_t* frame_off,
                         uint32_t n_frames, const uint8_t* payload, float* out, cudaStream_t st) {

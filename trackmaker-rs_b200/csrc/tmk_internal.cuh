@@ -174,6 +174,9 @@ int tmk_launch_correlate(const float* samples, const TmkStreamDev* streams, uint
                          const TmkPattern* patterns, float* corr_out, cudaStream_t st);
 int tmk_launch_busy(const float* samples, const TmkStreamDev* streams, uint32_t n_streams, int8_t* busy,
                     cudaStream_t st);
+// 16-bit PCM ingest / dump (misc.cu): codec.rs:121-125 and dump.rs:37-40
+int tmk_launch_pcm16_to_f32(const int16_t* pcm, float* out, uint64_t n, cudaStream_t st);
+int tmk_launch_pcm16_encode(const float* samples, int16_t* out, uint64_t n, cudaStream_t st);
 int tmk_launch_modulate(const TmkPattern* pattern, const tmk_frame_desc* frames, const uint64_t* frame_off,
                         uint32_t n_frames, const uint8_t* payload, float* out, cudaStream_t st);
 // synthetic captures (synth.cu)

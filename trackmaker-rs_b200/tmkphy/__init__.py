@@ -257,6 +257,69 @@ class Engine:
         self._check(rc)
         return recs[:nr.value].copy(), pl[:npl.value].copy()
 
+    # ---- 16-bit PCM captures (src/utils/dump.rs:37-40, src/audio/codec.rs:121-125)
+    def pcm16_encode(self, samples):
+        s = np.ascontiguousarray(samples, dtype=np.float32)
+        out = np.zeros(s.size, np.int16)
+        self._check(self._lib.tmk_pcm16_encode(self._h, _ptr(s), s.size, _ptr(out)))
+        return out
+
+    def pcm16_to_f32(self, pcm):
+        p = np.ascontiguousarray(pcm, dtype=np.int16)
+        out = np.zeros(p.size, np.float32)
+        self._check(self._lib.tmk_pcm16_to_f32(self._h, _ptr(p), p.size, _ptr(out)))
+        return out
+
+    def decode_batch_pcm16(self, pcm, streams, rec_cap=None, payload_cap=None, total_samples=None):
+        """tmk_decode_batch_pcm16. pcm: int16 ndarray (host) or an int device pointer."""
+        st = np.ascontiguousarray(streams, dtype=STREAM_DTYPE)
+        if isinstance(pcm, np.ndarray):
+            s = np.ascontiguousarray(pcm, dtype=np.int16)
+            sp, total = _ptr(s), s.size
+        else:
+            sp, total = C.c_void_p(int(pcm)), int(total_samples)
+        tot = int(st["n_samples"].sum()) if len(st) else 0
+        rec_cap = int(rec_cap) if rec_cap is not None else max(1024, tot // 96 + 2 * len(st))
+        payload_cap = int(payload_cap) if payload_cap is not None else max(65536, tot // 12)
+        recs = np.zeros(rec_cap, REC_DTYPE)
+        pl = np.zeros(payload_cap, np.uint8)
+        nr, npl = C.c_uint64(0), C.c_uint64(0)
+        self._check(self._lib.tmk_decode_batch_pcm16(self._h, sp, total, _ptr(st), len(st), _ptr(recs), rec_cap,
+                                                     C.byref(nr), _ptr(pl), payload_cap, C.byref(npl)))
+        return recs[:nr.value].copy(), pl[:npl.value].copy()
+
+    # ---- IP fragments above the PHY (src/net/fragmentation.rs)
+    def reassemble_batch(self, recs, payload, n_links, pkt_cap=None, byte_cap=None):
+        """tmk_reassemble_batch: (packet records ndarray[PKT_DTYPE], bytes ndarray[u8])."""
+        r = np.ascontiguousarray(recs, dtype=REC_DTYPE)
+        pl = np.ascontiguousarray(payload, dtype=np.uint8)
+        pkt_cap = int(pkt_cap) if pkt_cap is not None else max(16, len(r))
+        byte_cap = int(byte_cap) if byte_cap is not None else max(4096, pl.size + 64 * len(r))
+        pk = np.zeros(pkt_cap, _abi.PKT_DTYPE)
+        by = np.zeros(byte_cap, np.uint8)
+        n, nb = C.c_uint64(0), C.c_uint64(0)
+        self._check(self._lib.tmk_reassemble_batch(self._h, _ptr(r), len(r), _ptr(pl), pl.size, int(n_links), _ptr(pk),
+                                                   pkt_cap, C.byref(n), _ptr(by), byte_cap, C.byref(nb)))
+        return pk[:n.value].copy(), by[:nb.value].copy()
+
+    def fragment_batch(self, packets, mtu, first_identification=0, frag_cap=None, byte_cap=None):
+        """tmk_fragment_batch over a list of bytes objects sent through one IpFragmenter.
+        Returns (fragment records, bytes, next_identification)."""
+        off = np.zeros(len(packets) + 1, np.uint64)
+        off[1:] = np.cumsum([len(p) for p in packets], dtype=np.uint64) if packets else 0
+        data = np.frombuffer(b"".join(bytes(p) for p in packets) + b"\0", dtype=np.uint8).copy()
+        if frag_cap is None:
+            frag_cap = len(packets) + sum(len(p) // max(8, (int(mtu) - 60) // 8 * 8) + 1 for p in packets)
+        if byte_cap is None:
+            byte_cap = int(off[-1]) + 60 * int(frag_cap) + 64
+        fr = np.zeros(int(frag_cap), _abi.PKT_DTYPE)
+        by = np.zeros(int(byte_cap), np.uint8)
+        n, nb, nid = C.c_uint64(0), C.c_uint64(0), C.c_uint16(0)
+        self._check(self._lib.tmk_fragment_batch(self._h, _ptr(data), _ptr(off), len(packets), int(mtu),
+                                                 int(first_identification) & 0xffff, _ptr(fr), int(frag_cap), C.byref(n),
+                                                 _ptr(by), int(byte_cap), C.byref(nb), C.byref(nid)))
+        return fr[:n.value].copy(), by[:nb.value].copy(), int(nid.value)
+
     def correlate(self, samples, streams):
         s = np.ascontiguousarray(samples, dtype=np.float32)
         st = np.ascontiguousarray(streams, dtype=STREAM_DTYPE)
@@ -442,3 +505,28 @@ class PhyDecoderBank:
         b, o, d = C.c_uint64(0), C.c_uint64(0), C.c_int(0)
         self.engine._check(self._lib.tmk_links_state(self._h, int(link), C.byref(b), C.byref(o), C.byref(d)))
         return {"buffered": b.value, "buffer_offset": o.value, "decoding": bool(d.value)}
+
+
+class IpFragmenter:
+    """Mirror of IpFragmenter (src/net/fragmentation.rs:60-204); every call runs tmk_fragment_batch."""
+
+    def __init__(self, engine, mtu):
+        self._e, self.mtu, self._next = engine, int(mtu), 0
+
+    def fragment_packets(self, packets):
+        recs, by, self._next = self._e.fragment_batch(list(packets), self.mtu, self._next)
+        out = [[] for _ in packets]
+        for r in recs:
+            if r["status"] != _abi.PKT_OK:
+                raise ValueError(f"packet {int(r['link'])}: fragment_packet error {int(r['status'])}")
+            out[int(r["link"])].append(bytes(by[int(r["data_off"]):int(r["data_off"]) + int(r["len"])]))
+        return out
+
+    def fragment_packet(self, packet):  # fragmentation.rs:85-203
+        return self.fragment_packets([packet])[0]
+
+
+def packets_of(pkts, data):
+    """[(link, bytes)] of the TMK_PKT_OK records of Engine.reassemble_batch."""
+    return [(int(p["link"]), bytes(data[int(p["data_off"]):int(p["data_off"]) + int(p["len"])])) for p in pkts
+            if p["status"] == _abi.PKT_OK]

@@ -59,6 +59,11 @@ DESC_DTYPE = np.dtype([("payload_off", "<u8"), ("len", "<u4"), ("type", "u1"), (
                        ("dst", "u1")])
 ASK_REC_DTYPE = np.dtype([("stream", "<u4"), ("accepted", "<u4"), ("start_index", "<u8"), ("sync_power", "<f4"),
                           ("id", "u1"), ("bits", "u1", (14,)), ("_pad", "u1", (5,))])
+PKT_DTYPE = np.dtype([("link", "<u4"), ("status", "<u4"), ("frame", "<u4"), ("len", "<u4"), ("data_off", "<u8"),
+                      ("identification", "<u2"), ("n_fragments", "<u2"), ("_pad", "<u4")])
+assert PKT_DTYPE.itemsize == 32
+PKT_OK, PKT_E_SHORT, PKT_E_IHL, PKT_E_TOO_MANY, PKT_E_MTU = range(5)
+MAX_FRAGMENTS = 512
 assert STREAM_DTYPE.itemsize == 48 and REC_DTYPE.itemsize == 48 and DESC_DTYPE.itemsize == 16
 assert ASK_REC_DTYPE.itemsize == 40
 
@@ -108,6 +113,12 @@ SYMBOLS = {
     "tmk_ask_modulate": (C.c_int, [_vp, _vp, _u32, _vp, _vp, _vp, _u64, _pu64]),
     "tmk_ask_decode_batch": (C.c_int, [_vp, _vp, _u64, _vp, _u32, _vp, _u64, _pu64]),
     "tmk_ask_last_stage_ms": (C.c_int, [_vp, C.POINTER(C.c_float)]),
+    "tmk_pcm16_encode": (C.c_int, [_vp, _vp, _u64, _vp]),
+    "tmk_pcm16_to_f32": (C.c_int, [_vp, _vp, _u64, _vp]),
+    "tmk_decode_batch_pcm16": (C.c_int, [_vp, _vp, _u64, _vp, _u32, _vp, _u64, _pu64, _vp, _u64, _pu64]),
+    "tmk_reassemble_batch": (C.c_int, [_vp, _vp, _u64, _vp, _u64, _u32, _vp, _u64, _pu64, _vp, _u64, _pu64]),
+    "tmk_fragment_batch": (C.c_int, [_vp, _vp, _vp, _u32, _u32, C.c_uint16, _vp, _u64, _pu64, _vp, _u64, _pu64,
+                                     C.POINTER(C.c_uint16)]),
     "tmk_synth_batch": (C.c_int, [_vp, _pcfg, _u64, _u32, _u64, C.c_float, C.c_float, _vp, _vp, _u64, _pu64]),
 }
 
