@@ -144,6 +144,7 @@ def main():
     ap.add_argument("--line-code", default="4b5b")
     ap.add_argument("--chunk", type=int, default=0)
     ap.add_argument("--e2e-steps", type=int, default=3)
+    ap.add_argument("--no-pcm16", action="store_true", help="skip the 16-bit PCM end-to-end leg")
     ap.add_argument("--no-cpu", action="store_true")
     ap.add_argument("--snrs", default="", help="comma-separated SNRs in dB replacing the C2 sweep (diagnostics)")
     args = ap.parse_args()
@@ -246,6 +247,32 @@ def main():
         e2e_ms = eng.timer_stop()
         barrier()
         e2e_d2h = int(nr.value) * 48 + int(npl.value)
+        e2e_recs = int(nr.value)
+        eng.pinned_free(h_x.ctypes.data)
+        h_x = None
+
+    # ---- the same captures as 16-bit PCM (what dump_to_wav stores): host int16 -> tmk_decode_batch_pcm16
+    pcm_ms, pcm_recs = None, 0
+    if args.e2e_steps > 0 and not args.no_pcm16:
+        d_p = eng.device_alloc(total * 2)
+        eng._check(lib.tmk_pcm16_encode(h, C.c_void_p(d_x), total, C.c_void_p(d_p)))
+        h_p = eng.pinned_array((total,), np.int16)
+        eng.d2h(h_p, d_p)
+        eng.device_free(d_p)
+        pcp = h_p.ctypes.data_as(C.c_void_p)
+
+        def step_pcm():
+            eng._check(lib.tmk_decode_batch_pcm16(h, pcp, total, stp, n_s, rp, rec_cap, C.byref(nr), pp, pay_cap, C.byref(npl)))
+
+        step_pcm()
+        barrier()
+        eng.timer_start()
+        for _ in range(args.e2e_steps):
+            step_pcm()
+        pcm_ms = eng.timer_stop()
+        barrier()
+        pcm_recs = int(nr.value)
+        eng.pinned_free(h_p.ctypes.data)
 
     # ---- max over ranks of the device times, sum of the decode counters (the only collective)
     from tmkphy import sharding
@@ -294,6 +321,11 @@ def main():
             out["e2e"] = {"value": world * total * args.e2e_steps / (e2e_all * 1e-3) / 1e6, "unit": "Msamples/s",
                           "h2d_bytes_per_step": 4 * total + st.nbytes, "d2h_bytes_per_step": e2e_d2h,
                           "steps": args.e2e_steps}
+        if pcm_ms is not None:
+            # rank 0's own time (every rank runs the same step on its own PCIe link)
+            out["e2e_pcm16"] = {"value": world * total * args.e2e_steps / (pcm_ms * 1e-3) / 1e6, "unit": "Msamples/s",
+                                "h2d_bytes_per_step": 2 * total + st.nbytes, "records": pcm_recs,
+                                "note": "same captures stored as 16-bit PCM (dump.rs:37-40), widened on the GPU"}
         if not args.no_cpu:
             from oracle import oracle as orc
             orc.build()
