@@ -106,10 +106,10 @@ def run_reference(args):
     sys.path.insert(0, os.path.join(ROOT, "tests"))
     import helpers
     rng = np.random.default_rng(7)
-    n_s = max(64, 8 * threads)
-    n_per = 120000
+    n_s = max(256, 32 * threads)
+    n_per = N_PER_STREAM  # whole 10 s streams, 1/8 of the captures of the workload per step on a 16-core host
     caps = []
-    base = [helpers.make_capture(orc, cfg, np.random.default_rng(100 + i), n_frames=40, snr_db=SNRS[i % len(SNRS)],
+    base = [helpers.make_capture(orc, cfg, np.random.default_rng(100 + i), n_frames=150, snr_db=SNRS[i % len(SNRS)],
                                  gap_range=(48, 4800)) for i in range(16)]
     for i in range(n_s):
         b = base[i % 16]
@@ -144,6 +144,7 @@ def main():
     ap.add_argument("--line-code", default="4b5b")
     ap.add_argument("--chunk", type=int, default=0)
     ap.add_argument("--e2e-steps", type=int, default=3)
+    ap.add_argument("--cpu-max-captures", type=int, default=0, help="bound the cpu_baseline sample (0: by time)")
     ap.add_argument("--no-pcm16", action="store_true", help="skip the 16-bit PCM end-to-end leg")
     ap.add_argument("--no-cpu", action="store_true")
     ap.add_argument("--snrs", default="", help="comma-separated SNRs in dB replacing the C2 sweep (diagnostics)")
@@ -343,7 +344,7 @@ def main():
             n_cpu = min(n_s, max(64, 2 * threads))
             sub = gather(n_cpu)
             v, crecs, cpl, sec = cpu_leg(orc, tmkphy, sub, n_cpu, n_per, cfg, threads)
-            want = int(min(n_s, max(n_cpu, 10.0 * v * 1e6 / n_per)))
+            want = int(min(n_s, args.cpu_max_captures or n_s, max(n_cpu, 10.0 * v * 1e6 / n_per)))
             if want > n_cpu:
                 n_cpu = want
                 sub = gather(n_cpu)
