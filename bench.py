@@ -145,6 +145,7 @@ def main():
     ap.add_argument("--chunk", type=int, default=0)
     ap.add_argument("--e2e-steps", type=int, default=3)
     ap.add_argument("--cpu-max-captures", type=int, default=0, help="bound the cpu_baseline sample (0: by time)")
+    ap.add_argument("--no-numa-bind", action="store_true", help="do not bind the rank to the GPU's NUMA node")
     ap.add_argument("--no-pcm16", action="store_true", help="skip the 16-bit PCM end-to-end leg")
     ap.add_argument("--no-cpu", action="store_true")
     ap.add_argument("--snrs", default="", help="comma-separated SNRs in dB replacing the C2 sweep (diagnostics)")
@@ -156,6 +157,10 @@ def main():
     if args.impl == "reference":
         return run_reference(args)
 
+    # stdout carries exactly ONE JSON line: anything a library prints there (NCCL's version banner) goes to stderr
+    sys.stdout.flush()
+    real_stdout = os.dup(1)
+    os.dup2(2, 1)
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))
@@ -230,6 +235,8 @@ def main():
 
     # ---- e2e: pinned host buffers through the same C-ABI call (H2D + kernels + D2H of records/payload)
     e2e_ms, h_x = None, None
+    # pinned host buffers live on the GPU's own NUMA node (matters from 4 ranks up: two sockets feed eight PCIe links)
+    prev_affinity = eng.bind_host_thread() if not args.no_numa_bind else None
     if args.e2e_steps > 0:
         h_x = eng.pinned_array((total,), np.float32)
         eng.d2h(h_x, d_x)
@@ -274,6 +281,9 @@ def main():
         barrier()
         pcm_recs = int(nr.value)
         eng.pinned_free(h_p.ctypes.data)
+
+    if prev_affinity is not None:
+        os.sched_setaffinity(0, prev_affinity)  # the cpu_baseline leg uses every host core again
 
     # ---- max over ranks of the device times, sum of the decode counters (the only collective)
     from tmkphy import sharding
@@ -364,7 +374,8 @@ def main():
             out["cpu_baseline"] = {"value": v, "unit": "Msamples/s", "cores": threads, "kind": "port",
                                    "sample": f"{n_cpu} of the {n_s} captures x {n_per} samples, {sec:.2f} s",
                                    "parity_vs_gpu": "bit-exact" if same else "MISMATCH", "records": int(len(crecs))}
-        print(json.dumps(out))
+        sys.stdout.flush()
+        os.write(real_stdout, (json.dumps(out) + "\n").encode())
     if dist is not None:
         dist.barrier()
         dist.destroy_process_group()

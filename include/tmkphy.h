@@ -211,6 +211,9 @@ int tmk_last_stage_ms(tmk_engine* e, float ms[4]);
 /* CUDA-event stopwatch on the engine's stream (for callers without a CUDA runtime of their own) */
 int tmk_timer_start(tmk_engine* e);
 int tmk_timer_stop(tmk_engine* e, float* ms);
+/* PCI bus id of the engine's GPU ("0000:1b:00.0"), so that a host thread can bind itself to the GPU's NUMA node before it
+ * allocates pinned capture buffers (/sys/bus/pci/devices/<id>/local_cpulist) */
+int tmk_device_pci_bus_id(tmk_engine* e, char* out, int cap);
 /* how many kernels this engine has launched so far */
 uint64_t tmk_launch_count(const tmk_engine* e);
 

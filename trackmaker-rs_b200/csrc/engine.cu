@@ -858,6 +858,14 @@ int tmk_timer_stop(tmk_engine* e, float* ms) {
     return TMK_OK;
 }
 
+int tmk_device_pci_bus_id(tmk_engine* e, char* out, int cap) {
+    if (!e || !out || cap < 16) return TMK_E_INVALID;
+    CK(cudaDeviceGetPCIBusId(out, cap, e->device));
+    for (char* c = out; *c; ++c)
+        if (*c >= 'A' && *c <= 'Z') *c = char(*c - 'A' + 'a');
+    return TMK_OK;
+}
+
 uint64_t tmk_launch_count(const tmk_engine* e) { return e ? e->launches : 0; }
 
 int tmk_synth_batch(tmk_engine* e, const tmk_phy_config* cfg, uint64_t seed, uint32_t n_streams, uint64_t n_per_stream,

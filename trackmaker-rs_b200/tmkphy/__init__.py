@@ -148,6 +148,32 @@ class Engine:
         self._check(self._lib.tmk_timer_stop(self._h, C.byref(ms)))
         return ms.value
 
+    def pci_bus_id(self):
+        buf = C.create_string_buffer(32)
+        self._check(self._lib.tmk_device_pci_bus_id(self._h, buf, 32))
+        return buf.value.decode()
+
+    def bind_host_thread(self):
+        """Pin the calling thread to the CPUs of the GPU's NUMA node (sysfs local_cpulist), so that pinned capture
+        buffers allocated next are node-local and H2D copies do not cross sockets. Returns the previous affinity
+        (restore with os.sched_setaffinity(0, prev)), or None when the topology is not exposed."""
+        import os
+        try:
+            path = f"/sys/bus/pci/devices/{self.pci_bus_id()}/local_cpulist"
+            cpus = set()
+            for part in open(path).read().strip().split(","):
+                if part:
+                    a, _, b = part.partition("-")
+                    cpus.update(range(int(a), int(b or a) + 1))
+            prev = os.sched_getaffinity(0)
+            cpus &= prev
+            if not cpus or cpus == prev:
+                return None
+            os.sched_setaffinity(0, cpus)
+            return prev
+        except (OSError, ValueError, TmkError):
+            return None
+
     def launch_count(self):
         return int(self._lib.tmk_launch_count(self._h))
 

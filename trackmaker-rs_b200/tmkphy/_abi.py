@@ -102,6 +102,7 @@ SYMBOLS = {
     "tmk_last_stage_ms": (C.c_int, [_vp, C.POINTER(C.c_float)]),
     "tmk_timer_start": (C.c_int, [_vp]),
     "tmk_timer_stop": (C.c_int, [_vp, C.POINTER(C.c_float)]),
+    "tmk_device_pci_bus_id": (C.c_int, [_vp, C.c_char_p, C.c_int]),
     "tmk_launch_count": (_u64, [_vp]),
     "tmk_links_create": (C.c_int, [_vp, _vp, _u32, C.POINTER(_vp)]),
     "tmk_links_destroy": (None, [_vp]),
