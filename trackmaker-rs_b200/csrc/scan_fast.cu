@@ -65,6 +65,10 @@ __device__ __forceinline__ void bulk_g2s(void* dst, const void* src, uint32_t by
     asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(
                      smem_u32(dst)), "l"(src), "r"(bytes), "r"(smem_u32(bar)) : "memory");
 }
+// asynchronous HBM -> L2 prefetch of a byte range (no completion to wait for)
+__device__ __forceinline__ void l2_prefetch(const void* p, uint32_t bytes) {
+    asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(p), "r"(bytes) : "memory");
+}
 __device__ __forceinline__ float rcp_approx(float x) {
     float r;
     asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x));
@@ -310,6 +314,17 @@ scan_fast_kernel(const float* __restrict__ samples, uint64_t total_samples, cons
             parity ^= 1u;
         }
         __syncwarp();
+#ifndef TMK_SCAN_NO_PREFETCH
+        {   // the rows of this warp's NEXT tile start their trip from HBM to L2 now, under the strip below
+            const uint32_t tn = tl + gridDim.x * kWarps;
+            if (tn < n_tiles) {
+                const uint32_t tile_n = tile0 + tn, sn = tile_stream[tile_n];
+                const uint64_t an = streams[sn].offset + uint64_t(tile_n - streams[sn].tile_base) * TMK_TILE;
+                constexpr uint32_t kSpan = TMK_TILE + Sh::kCopy - kS;  // the 32 rows are one contiguous range
+                if (lane == 0 && an + kSpan <= total_samples) l2_prefetch(samples + an, kSpan * 4u);
+            }
+        }
+#endif
         // ---- stream the strip
         const float thr_c = sd.threshold * TMK_CAND_RATIO;
         const float kap = thr_c * thr_c * float(Sh::P);
