@@ -31,7 +31,7 @@ sys.path.insert(0, ROOT)
 sys.path.insert(0, os.path.join(ROOT, "trackmaker-rs_b200"))
 
 N_STREAMS = 4096
-NCU_SCAN_TRAFFIC = 7.894586e9 + 79.60192e6  # bytes per scan launch at C2, ncu --set full (profiles/)
+NCU_SCAN_TRAFFIC = 7.890631e9 + 79.098112e6  # bytes per scan launch at C2, ncu --set full (profiles/r01_ncu_full_summary_final2.txt)
 N_PER_STREAM = 480000
 SNRS = [-3.0, 0.0, 3.0, 6.0, 10.0, 15.0, 20.0, 30.0]
 METRIC = "Msamples/s sync+demod (48 kHz streams)"
