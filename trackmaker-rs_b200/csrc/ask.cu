@@ -19,6 +19,7 @@
 // the HBM ridge (an overlap-save FFT in shared memory is the planned replacement).
 #include <algorithm>
 #include <cmath>
+#include <cstdlib>
 #include <cstring>
 
 #include "engine.hpp"
@@ -171,6 +172,223 @@ ask_scan_kernel(const float* __restrict__ samples, const AskStream* __restrict__
     if ((lane & 3) == 0 && any) {
         const uint64_t wbit = sd.word_base + uint64_t(t0 + 8 * tid) / 32;
         atomicOr(wflag + (wbit >> 5), 1u << (wbit & 31));
+    }
+}
+
+// ---------------------------------------------------------------- filter, FFT form (overlap-save in shared memory)
+// The 440-tap chirp correlation of the filter as a fast correlation: TWO tiles of kT positions are packed as the
+// real and imaginary part of one 2048-point complex sequence z (the chirp is real, so corr(z, h) = corr(re z, h) +
+// i corr(im z, h)), z is transformed by a Stockham autosort FFT in shared memory (five radix-4 passes and one radix-2
+// pass, twiddles from a table computed in double on the host), multiplied by conj(H) / (N 200) (the chirp's spectrum,
+// also from the host), and transformed back. A tile needs z[0 .. kT + 439), the rest of the 2048 points is zero
+// padding, so nothing wraps around. ~120 flop per position instead of 880.
+// The result differs from the exactly rounded sum by at most (Higham, Accuracy and Stability of Numerical Algorithms,
+// §24.1: an n-stage FFT with correctly rounded twiddles has a 2-norm relative error <= n eta, eta ~ 7 u for radix 2,
+// ~ 12 u for radix 4) 2 x (5 x 12 + 7) u for the two transforms + 4 u for the product, ~ 138 u ~ 8.3e-6, of
+// |H|max / 200 x ||z||_2; the tolerance takes twice that, with ||z||_2 measured per CTA, next to the budget of the
+// walk's own sequential sum (6.5e-5 xmax, see ask_scan_kernel).
+constexpr int kN = 2048;
+constexpr int kFT = 256;           // threads: half 0 (tid < 128) owns the tile in re z, half 1 the tile in im z
+constexpr int kZ = kT + kPre - 1;  // staged samples of a tile that enter the correlation
+constexpr float kFftRel = 1.7e-5f;
+// EMA warm-up of the FFT filter: the truncated EMA only DROPS non-negative terms (0.984375^1024 ~ 1e-7 of the state
+// 1024 samples back), so the power it tests against is never above the exact one: truncation can add candidates,
+// never lose one.
+constexpr int kW2 = 1024;
+constexpr int kXs2 = kW2 + kT;
+
+struct FftSmem {
+    float2 buf[2][kN];
+    // twiddles, contiguous per pass (a strided walk through one table is a 16-way bank conflict): radix-4 pass with
+    // p = 4^s has w^k, w^2k, w^3k (w = exp(-2 pi i / 4p)) at [4^s - 1 + {0, p, 2p} + k]; the radix-2 pass
+    // exp(-2 pi i k / N) at [1023 + k]; one pad entry
+    float2 tw[kN];
+    float2 hc[kN];  // conj(H) / (N 200)
+    float xs[2][kXs2];
+    float ps[2][kT];
+    float red[kFT / 32], red2[kFT / 32];
+    float carry[2][4];
+};
+
+__device__ __forceinline__ float2 cmul(float2 a, float2 b) {
+    return make_float2(fmaf(a.x, b.x, -a.y * b.y), fmaf(a.x, b.y, a.y * b.x));
+}
+__device__ __forceinline__ float2 cadd(float2 a, float2 b) { return make_float2(a.x + b.x, a.y + b.y); }
+__device__ __forceinline__ float2 csub(float2 a, float2 b) { return make_float2(a.x - b.x, a.y - b.y); }
+
+// 2048-point Stockham FFT: input in a, scratch b, result in a (six passes). INV: conjugated twiddles, no scaling.
+template <bool INV>
+__device__ __forceinline__ void fft2048(float2* a, float2* b, const float2* __restrict__ tw, int tid) {
+    float2 *in = a, *out = b;
+#pragma unroll 1
+    for (int p = 1; p <= 256; p <<= 2) {
+        const float2* __restrict__ tp = tw + (p - 1);
+#pragma unroll
+        for (int i = tid; i < kN / 4; i += kFT) {
+            const int k = i & (p - 1), j = ((i - k) << 2) + k;
+            float2 w1 = tp[k], w2 = tp[p + k], w3 = tp[2 * p + k];
+            if (INV) {
+                w1.y = -w1.y;
+                w2.y = -w2.y;
+                w3.y = -w3.y;
+            }
+            const float2 u0 = in[i], u1 = cmul(in[i + kN / 4], w1), u2 = cmul(in[i + kN / 2], w2), u3 = cmul(in[i + 3 * kN / 4], w3);
+            const float2 v0 = cadd(u0, u2), v1 = csub(u0, u2), v2 = cadd(u1, u3), d = csub(u1, u3);
+            const float2 v3 = INV ? make_float2(-d.y, d.x) : make_float2(d.y, -d.x);  // * (+i) backward, * (-i) forward
+            out[j] = cadd(v0, v2);
+            out[j + p] = cadd(v1, v3);
+            out[j + 2 * p] = csub(v0, v2);
+            out[j + 3 * p] = csub(v1, v3);
+        }
+        __syncthreads();
+        float2* t = in;
+        in = out;
+        out = t;
+    }
+    // radix 2, p = 1024 (in == b here, out == a)
+#pragma unroll
+    for (int i = tid; i < kN / 2; i += kFT) {
+        float2 w = tw[1023 + i];
+        if (INV) w.y = -w.y;
+        const float2 u0 = in[i], u1 = cmul(in[i + kN / 2], w);
+        out[i] = cadd(u0, u1);
+        out[i + kN / 2] = csub(u0, u1);
+    }
+    __syncthreads();
+}
+
+__global__ void __launch_bounds__(kFT)
+ask_scan_fft_kernel(const float* __restrict__ samples, const AskStream* __restrict__ streams, uint32_t n_streams, uint32_t n_tiles,
+                    const float2* __restrict__ twg, const float2* __restrict__ hc, float h_scale, uint32_t* __restrict__ wflag) {
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    FftSmem& sm = *reinterpret_cast<FftSmem*>(smem_raw);
+    const int tid = threadIdx.x, half = tid >> 7, htid = tid & 127, lane = tid & 31, warp = tid >> 5, hwarp = htid >> 5;
+    // persistent CTAs: the tables are staged once, the constants of the EMA scan computed once
+    for (int i = tid; i < kN; i += kFT) {
+        sm.tw[i] = twg[i];
+        sm.hc[i] = hc[i];
+    }
+    constexpr int kPer = kXs2 / 128;
+    const float mul0 = powf(kC, float(kPer)), c768 = powf(kC, float(kPer * 32)), clane = powf(kC, float(kPer * lane));
+    const uint32_t n_pairs = (n_tiles + 1) / 2;
+#pragma unroll 1
+    for (uint32_t pair = blockIdx.x; pair < n_pairs; pair += gridDim.x) {
+    const uint32_t tile = 2 * pair + half;
+    const bool valid = tile < n_tiles;
+    AskStream sd = streams[0];
+    int64_t n = 0, t0 = 0;
+    if (valid) {
+        uint32_t lo = 0, hi = n_streams - 1;
+        while (lo < hi) {
+            const uint32_t mid = (lo + hi + 1) >> 1;
+            if (streams[mid].tile_base <= tile) lo = mid; else hi = mid - 1;
+        }
+        sd = streams[lo];
+        n = int64_t(sd.n);
+        t0 = int64_t(tile - sd.tile_base) * kT;
+    }
+    const float* __restrict__ x = samples + sd.offset;
+    float xmax = 0.0f, ss = 0.0f;
+    float* xs = sm.xs[half];
+    // 16-byte loads: stream offsets are multiples of 4 samples, t0 - kW2 too
+#pragma unroll
+    for (int r = 0; r < kXs2 / 4 / 128; ++r) {
+        const int i = 4 * (htid + 128 * r);
+        const int64_t g = t0 - kW2 + i;
+        float4 q4 = make_float4(0.f, 0.f, 0.f, 0.f);
+        if (valid && g >= 0 && g + 3 < n) {
+            q4 = __ldg(reinterpret_cast<const float4*>(x + g));
+        } else if (valid) {
+            if (g >= 0 && g < n) q4.x = x[g];
+            if (g + 1 >= 0 && g + 1 < n) q4.y = x[g + 1];
+            if (g + 2 >= 0 && g + 2 < n) q4.z = x[g + 2];
+            if (g + 3 >= 0 && g + 3 < n) q4.w = x[g + 3];
+        }
+        *reinterpret_cast<float4*>(xs + i) = q4;
+        xmax = fmaxf(fmaxf(xmax, fmaxf(fabsf(q4.x), fabsf(q4.y))), fmaxf(fabsf(q4.z), fabsf(q4.w)));
+        const float e4[4] = {q4.x, q4.y, q4.z, q4.w};
+#pragma unroll
+        for (int c = 0; c < 4; ++c)
+            if (i + c >= kW2 - (kPre - 1)) ss = fmaf(e4[c], e4[c], ss);
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+        xmax = fmaxf(xmax, __shfl_xor_sync(kFull, xmax, o));
+        ss += __shfl_xor_sync(kFull, ss, o);
+    }
+    if (lane == 0) {
+        sm.red[warp] = xmax;
+        sm.red2[warp] = ss;
+    }
+    __syncthreads();
+    xmax = 0.0f;
+    ss = 0.0f;
+#pragma unroll
+    for (int w = 0; w < kFT / 32; ++w) {
+        xmax = fmaxf(xmax, sm.red[w]);
+        ss += sm.red2[w];
+    }
+    if (!(xmax <= 3.0e38f)) xmax = 3.0e38f;  // NaN / inf samples: everything in the tile pair becomes a candidate
+    // pack the two tiles: z[i] = x_a[t0a - 439 + i] + i x_b[t0b - 439 + i]
+    for (int i = tid; i < kN; i += kFT)
+        sm.buf[0][i] = i < kZ ? make_float2(sm.xs[0][kW2 - (kPre - 1) + i], sm.xs[1][kW2 - (kPre - 1) + i]) : make_float2(0.f, 0.f);
+
+    // ---- EMA power (as in ask_scan_kernel), each half over its own tile
+    float q = 0.0f;
+#pragma unroll
+    for (int j = 0; j < kPer; ++j) {
+        const float v = xs[htid * kPer + j];
+        q = fmaf(q, kC, v * v * kInv64);
+    }
+    float v = q, mul = mul0;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+        const float t = __shfl_up_sync(kFull, v, o);
+        if (lane >= o) v = fmaf(t, mul, v);
+        mul *= mul;
+    }
+    if (lane == 31) sm.carry[half][hwarp] = v;
+    __syncthreads();
+    float pin = 0.0f;
+    for (int w = 0; w < hwarp; ++w) pin = fmaf(pin, c768, sm.carry[half][w]);
+    float prev = __shfl_up_sync(kFull, v, 1);
+    if (lane == 0) prev = 0.0f;
+    float p = fmaf(pin, clane, prev);
+#pragma unroll
+    for (int j = 0; j < kPer; ++j) {
+        const int i = htid * kPer + j;
+        const float xv = xs[i];
+        p = fmaf(p, kC, xv * xv * kInv64);
+        if (i >= kW2) sm.ps[half][i - kW2] = p;
+    }
+    __syncthreads();
+
+    // ---- fast correlation
+    fft2048<false>(sm.buf[0], sm.buf[1], sm.tw, tid);
+    for (int i = tid; i < kN; i += kFT) sm.buf[0][i] = cmul(sm.buf[0][i], sm.hc[i]);
+    __syncthreads();
+    fft2048<true>(sm.buf[0], sm.buf[1], sm.tw, tid);
+
+    // ---- candidate test; position t0 + m is z index m
+    const float tol = kFftRel * h_scale * sqrtf(ss) * 1.001f + 6.5e-5f * xmax + 1e-7f;
+    uint32_t any = 0;
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+        const int m = 8 * htid + j;
+        const int64_t i = t0 + m;
+        const float2 y = sm.buf[0][m];
+        const float sp = (half ? y.y : y.x) + tol;
+        const float pw = sm.ps[half][m];
+        const bool cand = valid && i < n && (!(sp <= 0.05f) && !(sp <= 2.0f * pw * (1.0f - 1e-4f)));  // NaN -> candidate
+        any |= cand ? 1u : 0u;
+    }
+    any |= __shfl_xor_sync(kFull, any, 1);
+    any |= __shfl_xor_sync(kFull, any, 2);
+    if ((lane & 3) == 0 && any) {
+        const uint64_t wbit = sd.word_base + uint64_t(t0 + 8 * htid) / 32;
+        atomicOr(wflag + (wbit >> 5), 1u << (wbit & 31));
+    }
+    __syncthreads();  // the next pair reuses xs / ps / buf
     }
 }
 
@@ -419,10 +637,37 @@ void host_tables(std::vector<float>& tab, size_t n_carrier) {
     for (size_t k = 0; k < n_carrier; ++k) tab[kPre + k] = sinf(2.0f * pi * 10000.0f * (float(k) / 48000.0f));
 }
 
+// layout of d_ask_tab: [kPre preamble | kFrame carrier | pad to 8 bytes | kN twiddles (float2) | kN conj(H) / (N 200) (float2)]
+constexpr size_t kTabFft = (size_t(kPre) + kFrame + 1) / 2 * 2;  // in floats; twiddles in the per-pass layout of FftSmem::tw
+
 int ensure_tables(tmk_engine* e) {
     if (e->ask_ready) return TMK_OK;
     std::vector<float> tab;
     host_tables(tab, kFrame);
+    tab.resize(kTabFft + 4 * kN, 0.0f);
+    const double two_pi = 6.283185307179586476925286766559;
+    double hmax = 0.0;
+    auto put_tw = [&](int slot, double turns) {  // exp(-2 pi i turns)
+        tab[kTabFft + 2 * slot] = float(std::cos(two_pi * turns));
+        tab[kTabFft + 2 * slot + 1] = float(-std::sin(two_pi * turns));
+    };
+    for (int p = 1; p <= 256; p *= 4)
+        for (int k = 0; k < p; ++k)
+            for (int q = 1; q <= 3; ++q) put_tw(p - 1 + (q - 1) * p + k, double(q * k) / double(4 * p));
+    for (int k = 0; k < kN / 2; ++k) put_tw(1023 + k, double(k) / double(kN));
+    put_tw(kN - 1, 0.0);
+    for (int m = 0; m < kN; ++m) {
+        double re = 0.0, im = 0.0;  // H[m] = sum_k h[k] exp(-2 pi i m k / N)
+        for (int k = 0; k < kPre; ++k) {
+            const double a = two_pi * double((int64_t(m) * k) % kN) / kN;
+            re += double(tab[k]) * std::cos(a);
+            im -= double(tab[k]) * std::sin(a);
+        }
+        hmax = std::max(hmax, std::sqrt(re * re + im * im));
+        tab[kTabFft + 2 * kN + 2 * m] = float(re / (double(kN) * 200.0));
+        tab[kTabFft + 2 * kN + 2 * m + 1] = float(-im / (double(kN) * 200.0));  // conj
+    }
+    e->ask_hscale = float(hmax / 200.0 * 1.0001);
     CK(e->d_ask_tab.reserve(tab.size() * sizeof(float)));
     CK(cudaMemcpyAsync(e->d_ask_tab.p, tab.data(), tab.size() * sizeof(float), cudaMemcpyHostToDevice, e->stream));
     CK(cudaStreamSynchronize(e->stream));
@@ -531,7 +776,27 @@ int tmk_ask_decode_batch(tmk_engine* e, const float* samples, uint64_t total_sam
     const float* tab = static_cast<const float*>(e->d_ask_tab.p);
     CK(cudaEventRecord(e->ev[0], e->stream));
     if (tiles) {
-        ask_scan_kernel<<<uint32_t(tiles), kThreads, 0, e->stream>>>(dx, ds, n_streams, tab, static_cast<uint32_t*>(e->d_ask_bits.p));
+        // TMK_ASK_DIRECT=1 keeps the direct-form filter (A/B and cross-check of the FFT form)
+        static const bool direct = getenv("TMK_ASK_DIRECT") != nullptr;
+        if (direct) {
+            ask_scan_kernel<<<uint32_t(tiles), kThreads, 0, e->stream>>>(dx, ds, n_streams, tab, static_cast<uint32_t*>(e->d_ask_bits.p));
+        } else {
+            static bool attr = false;
+            if (!attr) {
+                CK(cudaFuncSetAttribute(ask_scan_fft_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, int(sizeof(FftSmem))));
+                attr = true;
+            }
+            const float2* twg = reinterpret_cast<const float2*>(tab + kTabFft);
+            static int fft_ctas = 0;
+            if (fft_ctas == 0) {
+                int sms = 0, per_sm = 0;
+                cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, e->device);
+                cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, ask_scan_fft_kernel, kFT, sizeof(FftSmem));
+                fft_ctas = sms * (per_sm > 0 ? per_sm : 1);
+            }
+            ask_scan_fft_kernel<<<uint32_t(std::min<uint64_t>((tiles + 1) / 2, uint64_t(fft_ctas))), kFT, sizeof(FftSmem), e->stream>>>(
+                dx, ds, n_streams, uint32_t(tiles), twg, twg + kN, e->ask_hscale, static_cast<uint32_t*>(e->d_ask_bits.p));
+        }
         e->launches += 1;
     }
     CK(cudaGetLastError());

@@ -42,6 +42,7 @@ struct tmk_engine {
         d_counters, d_samples, d_misc, d_misc2, d_next, d_cblk, d_blk_ptr, d_entries, d_spec, d_pool, d_link, d_pcm, d_frag;
     DevBuf d_ask_tab, d_ask_bits, d_ask_l2, d_ask_recs, d_ask_recs2;  // chirp+BPSK path (ask.cu)
     bool ask_ready = false;
+    float ask_hscale = 0.0f;  // max |H| / 200 of the chirp spectrum (error bound of the FFT filter)
     cudaEvent_t ev[6] = {};
     cudaEvent_t tev[2] = {};
     cudaEvent_t cev[6] = {};  // copy/compute hand-over of the chunked staging
