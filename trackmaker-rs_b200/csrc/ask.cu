@@ -1,10 +1,13 @@
 // ask.cu — the chirp + BPSK modem of the reference's project 1, examples/ask.rs::test_sender_receiver
 // (:526-858; live TX :104-262, live RX :264-524), batched over many captures.
 //
-//   ask_scan_kernel   FILTER over every sample: 440-tap chirp correlation / 200 (fp32 FMA, register-blocked
-//                     out of shared memory) and the EMA power (affine block scan), marks every 32-sample
-//                     word in which `sync_power > 2 power && sync_power > 0.05` (ask.rs:711-714) could hold,
-//                     with margins that cover the re-association error.
+//   ask_scan_fft_kernel  FILTER over every sample: the 440-tap chirp correlation / 200 as a fast correlation
+//                     (2048-point Stockham FFT in shared memory, two tiles packed as re / im) and the EMA power
+//                     (affine block scan), marks every 32-sample word in which
+//                     `sync_power > 2 power && sync_power > 0.05` (ask.rs:711-714) could hold, with margins that
+//                     cover the FFT's error bound and the re-association error.
+//   ask_scan_kernel   the direct-form version of the same filter (fp32 FMA, register-blocked out of shared
+//                     memory), kept behind TMK_ASK_DIRECT=1 for A/B.
 //   ask_walk_kernel   one warp per capture replays the reference's state machine over the marked words
 //                     only, in the reference's f32 operation order: sequential 440-term dot product
 //                     (ask.rs:704-709), the exact EMA chain (:696-697, carried over every sample), running
@@ -15,8 +18,8 @@
 // Tables (preamble, carrier) are computed once on the host with sinf in the reference's operation order
 // (ask.rs:574-605) and uploaded, so device sin never enters.
 //
-// Bound: the filter is a 440-tap direct-form FIR, 880 flop per 4-byte sample: FP32-pipe bound, far above
-// the HBM ridge (an overlap-save FFT in shared memory is the planned replacement).
+// Bound: the FFT filter is shared-memory bound (~120 flop per sample, 12 passes over 16 KB per 2048 positions);
+// the direct form was FP32-pipe bound at 880 flop per 4-byte sample.
 #include <algorithm>
 #include <cmath>
 #include <cstdlib>
