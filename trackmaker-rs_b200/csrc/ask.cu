@@ -408,7 +408,7 @@ struct AskCtx {
     // exact EMA chain: `p` is the power after sample cpos - 1 (0 before the first sample)
     int64_t cpos;
     float p;
-    float* stage;  // 64 floats of shared memory per warp
+    float* stage;  // 128 floats of shared memory per warp
 };
 
 // advance the EMA chain to `target` (power after sample target - 1)            ask.rs:696-697
@@ -418,6 +418,29 @@ __device__ __noinline__ void chain_to(AskCtx& c, int64_t target) {
     int64_t pos = c.cpos;
     while (pos < target) {
         const int64_t left = target - pos;
+        if (left >= 128) {  // four loads in flight per lane: the chain is one exposed memory round trip per 128 samples
+            float v0 = x[pos + c.lane], v1 = x[pos + 32 + c.lane], v2 = x[pos + 64 + c.lane], v3 = x[pos + 96 + c.lane];
+            v0 = fmul(fmul(v0, v0), kInv64);
+            v1 = fmul(fmul(v1, v1), kInv64);
+            v2 = fmul(fmul(v2, v2), kInv64);
+            v3 = fmul(fmul(v3, v3), kInv64);
+            __syncwarp();
+            c.stage[c.lane] = v0;
+            c.stage[32 + c.lane] = v1;
+            c.stage[64 + c.lane] = v2;
+            c.stage[96 + c.lane] = v3;
+            __syncwarp();
+#pragma unroll
+            for (int j = 0; j < 32; ++j) {
+                const float4 q = *reinterpret_cast<const float4*>(c.stage + 4 * j);
+                p = fadd(fmul(p, kC), q.x);
+                p = fadd(fmul(p, kC), q.y);
+                p = fadd(fmul(p, kC), q.z);
+                p = fadd(fmul(p, kC), q.w);
+            }
+            pos += 128;
+            continue;
+        }
         const int nstep = left < 32 ? int(left) : 32;
         float v = c.lane < nstep ? x[pos + c.lane] : 0.0f;
         v = fmul(fmul(v, v), kInv64);
@@ -471,10 +494,22 @@ __device__ __noinline__ void eval_word(AskCtx& c, int64_t w, int64_t r, float* s
     float sum = 0.0f;
     const int64_t first = i - (kPre - 1);  // sample index of tap 0
     const float* __restrict__ x = c.x;
-#pragma unroll 4
-    for (int k = 0; k < kPre; ++k) {
-        const int64_t g = first + k;
-        if (g >= r && g >= 0 && i < c.n) sum = fadd(sum, fmul(x[g], c.pre[k]));
+    // taps below k_lo read the zeroed FIFO (samples before r >= 0): they add +-0.0 to a sum that starts at +0.0, which
+    // leaves it unchanged, so they are skipped — whole groups of 8 when no lane of the warp needs them (right after a
+    // frame most of the window is still empty)
+    int k_lo = first < r ? int(r - first < int64_t(kPre) ? r - first : int64_t(kPre)) : 0;
+    if (i >= c.n) k_lo = kPre;
+    const int k0 = __reduce_min_sync(kFull, k_lo) & ~7;
+#pragma unroll 1
+    for (int k = k0; k < kPre; k += 8) {
+        const float4 pa = *reinterpret_cast<const float4*>(c.pre + k), pb = *reinterpret_cast<const float4*>(c.pre + k + 4);
+        const float pk[8] = {pa.x, pa.y, pa.z, pa.w, pb.x, pb.y, pb.z, pb.w};
+        float xv[8];
+#pragma unroll
+        for (int j = 0; j < 8; ++j) xv[j] = k + j >= k_lo ? x[first + k + j] : 0.0f;
+#pragma unroll
+        for (int j = 0; j < 8; ++j)
+            if (k + j >= k_lo) sum = fadd(sum, fmul(xv[j], pk[j]));
     }
     *sp_out = __fdiv_rn(sum, 200.0f);
 }
@@ -511,7 +546,7 @@ ask_walk_kernel(const float* __restrict__ samples, const AskStream* __restrict__
                 const float* __restrict__ tab, const uint32_t* __restrict__ wflag, tmk_ask_rec* __restrict__ recs,
                 uint64_t rec_cap, unsigned long long* __restrict__ counters) {
     __shared__ __align__(16) float pre_s[kPre];
-    __shared__ __align__(16) float stage_s[4][64];
+    __shared__ __align__(16) float stage_s[4][128];
     for (int i = threadIdx.x; i < kPre; i += blockDim.x) pre_s[i] = tab[i];
     __syncthreads();
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
