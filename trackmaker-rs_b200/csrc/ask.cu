@@ -179,11 +179,11 @@ ask_scan_kernel(const float* __restrict__ samples, const AskStream* __restrict__
 }
 
 // ---------------------------------------------------------------- filter, FFT form (overlap-save in shared memory)
-// The 440-tap chirp correlation of the filter as a fast correlation: TWO tiles of kT positions are packed as the
+// The 440-tap chirp correlation of the filter as a fast correlation: TWO tiles of kT2 = 1536 positions are packed as the
 // real and imaginary part of one 2048-point complex sequence z (the chirp is real, so corr(z, h) = corr(re z, h) +
 // i corr(im z, h)), z is transformed by a Stockham autosort FFT in shared memory (five radix-4 passes and one radix-2
 // pass, twiddles from a table computed in double on the host), multiplied by conj(H) / (N 200) (the chirp's spectrum,
-// also from the host), and transformed back. A tile needs z[0 .. kT + 439), the rest of the 2048 points is zero
+// also from the host), and transformed back. A tile needs z[0 .. kT2 + 439), the rest of the 2048 points is zero
 // padding, so nothing wraps around. ~120 flop per position instead of 880.
 // The result differs from the exactly rounded sum by at most (Higham, Accuracy and Stability of Numerical Algorithms,
 // §24.1: an n-stage FFT with correctly rounded twiddles has a 2-norm relative error <= n eta, eta ~ 7 u for radix 2,
@@ -192,13 +192,14 @@ ask_scan_kernel(const float* __restrict__ samples, const AskStream* __restrict__
 // walk's own sequential sum (6.5e-5 xmax, see ask_scan_kernel).
 constexpr int kN = 2048;
 constexpr int kFT = 256;           // threads: half 0 (tid < 128) owns the tile in re z, half 1 the tile in im z
-constexpr int kZ = kT + kPre - 1;  // staged samples of a tile that enter the correlation
 constexpr float kFftRel = 1.7e-5f;
 // EMA warm-up of the FFT filter: the truncated EMA only DROPS non-negative terms (0.984375^1024 ~ 1e-7 of the state
 // 1024 samples back), so the power it tests against is never above the exact one: truncation can add candidates,
 // never lose one.
-constexpr int kW2 = 1024;
-constexpr int kXs2 = kW2 + kT;
+constexpr int kW2 = 512;            // (0.984375^512 ~ 3e-4; the 0.05 floor of the test keeps silence out)
+constexpr int kT2 = 1536;           // positions per tile of the FFT filter: 1536 + 439 of the 2048 points are data
+constexpr int kXs2 = kW2 + kT2;     // 2048 staged samples per tile
+constexpr int kZ2 = kT2 + kPre - 1;
 
 struct FftSmem {
     float2 buf[2][kN];
@@ -207,8 +208,7 @@ struct FftSmem {
     // exp(-2 pi i k / N) at [1023 + k]; one pad entry
     float2 tw[kN];
     float2 hc[kN];  // conj(H) / (N 200)
-    float xs[2][kXs2];
-    float ps[2][kT];
+    float ps[2][kT2];  // (the staged samples xs[2][kXs2] live in buf[1] until the first FFT pass overwrites them)
     float red[kFT / 32], red2[kFT / 32];
     float carry[2][4];
 };
@@ -238,10 +238,16 @@ __device__ __forceinline__ void fft2048(float2* a, float2* b, const float2* __re
             const float2 u0 = in[i], u1 = cmul(in[i + kN / 4], w1), u2 = cmul(in[i + kN / 2], w2), u3 = cmul(in[i + 3 * kN / 4], w3);
             const float2 v0 = cadd(u0, u2), v1 = csub(u0, u2), v2 = cadd(u1, u3), d = csub(u1, u3);
             const float2 v3 = INV ? make_float2(-d.y, d.x) : make_float2(d.y, -d.x);  // * (+i) backward, * (-i) forward
-            out[j] = cadd(v0, v2);
-            out[j + p] = cadd(v1, v3);
-            out[j + 2 * p] = csub(v0, v2);
-            out[j + 3 * p] = csub(v1, v3);
+            const float2 y0 = cadd(v0, v2), y1 = cadd(v1, v3), y2 = csub(v0, v2), y3 = csub(v1, v3);
+            if (p == 1) {  // the four results are neighbours: two 16-byte stores instead of four strided 8-byte ones
+                *reinterpret_cast<float4*>(out + j) = make_float4(y0.x, y0.y, y1.x, y1.y);
+                *reinterpret_cast<float4*>(out + j + 2) = make_float4(y2.x, y2.y, y3.x, y3.y);
+            } else {
+                out[j] = y0;
+                out[j + p] = y1;
+                out[j + 2 * p] = y2;
+                out[j + 3 * p] = y3;
+            }
         }
         __syncthreads();
         float2* t = in;
@@ -288,11 +294,13 @@ ask_scan_fft_kernel(const float* __restrict__ samples, const AskStream* __restri
         }
         sd = streams[lo];
         n = int64_t(sd.n);
-        t0 = int64_t(tile - sd.tile_base) * kT;
+        t0 = int64_t(tile - sd.tile_base) * kT2;
     }
     const float* __restrict__ x = samples + sd.offset;
     float xmax = 0.0f, ss = 0.0f;
-    float* xs = sm.xs[half];
+    static_assert(sizeof(float) * 2 * kXs2 <= sizeof(float2) * kN, "the staged samples alias buf[1]");
+    float* xs0 = reinterpret_cast<float*>(sm.buf[1]);
+    float* xs = xs0 + half * kXs2;
     // 16-byte loads: stream offsets are multiples of 4 samples, t0 - kW2 too
 #pragma unroll
     for (int r = 0; r < kXs2 / 4 / 128; ++r) {
@@ -334,7 +342,7 @@ ask_scan_fft_kernel(const float* __restrict__ samples, const AskStream* __restri
     if (!(xmax <= 3.0e38f)) xmax = 3.0e38f;  // NaN / inf samples: everything in the tile pair becomes a candidate
     // pack the two tiles: z[i] = x_a[t0a - 439 + i] + i x_b[t0b - 439 + i]
     for (int i = tid; i < kN; i += kFT)
-        sm.buf[0][i] = i < kZ ? make_float2(sm.xs[0][kW2 - (kPre - 1) + i], sm.xs[1][kW2 - (kPre - 1) + i]) : make_float2(0.f, 0.f);
+        sm.buf[0][i] = i < kZ2 ? make_float2(xs0[kW2 - (kPre - 1) + i], xs0[kXs2 + kW2 - (kPre - 1) + i]) : make_float2(0.f, 0.f);
 
     // ---- EMA power (as in ask_scan_kernel), each half over its own tile
     float q = 0.0f;
@@ -374,22 +382,25 @@ ask_scan_fft_kernel(const float* __restrict__ samples, const AskStream* __restri
 
     // ---- candidate test; position t0 + m is z index m
     const float tol = kFftRel * h_scale * sqrtf(ss) * 1.001f + 6.5e-5f * xmax + 1e-7f;
-    uint32_t any = 0;
+#pragma unroll 1
+    for (int chunk = htid; chunk < kT2 / 8; chunk += 128) {  // 8 positions per thread; four lanes cover a 32-sample word
+        uint32_t any = 0;
 #pragma unroll
-    for (int j = 0; j < 8; ++j) {
-        const int m = 8 * htid + j;
-        const int64_t i = t0 + m;
-        const float2 y = sm.buf[0][m];
-        const float sp = (half ? y.y : y.x) + tol;
-        const float pw = sm.ps[half][m];
-        const bool cand = valid && i < n && (!(sp <= 0.05f) && !(sp <= 2.0f * pw * (1.0f - 1e-4f)));  // NaN -> candidate
-        any |= cand ? 1u : 0u;
-    }
-    any |= __shfl_xor_sync(kFull, any, 1);
-    any |= __shfl_xor_sync(kFull, any, 2);
-    if ((lane & 3) == 0 && any) {
-        const uint64_t wbit = sd.word_base + uint64_t(t0 + 8 * htid) / 32;
-        atomicOr(wflag + (wbit >> 5), 1u << (wbit & 31));
+        for (int j = 0; j < 8; ++j) {
+            const int m = 8 * chunk + j;
+            const int64_t i = t0 + m;
+            const float2 y = sm.buf[0][m];
+            const float sp = (half ? y.y : y.x) + tol;
+            const float pw = sm.ps[half][m];
+            const bool cand = valid && i < n && (!(sp <= 0.05f) && !(sp <= 2.0f * pw * (1.0f - 1e-4f)));  // NaN -> candidate
+            any |= cand ? 1u : 0u;
+        }
+        any |= __shfl_xor_sync(kFull, any, 1);
+        any |= __shfl_xor_sync(kFull, any, 2);
+        if ((lane & 3) == 0 && any) {
+            const uint64_t wbit = sd.word_base + uint64_t(t0 + 8 * chunk) / 32;
+            atomicOr(wflag + (wbit >> 5), 1u << (wbit & 31));
+        }
     }
     __syncthreads();  // the next pair reuses xs / ps / buf
     }
@@ -780,6 +791,9 @@ int tmk_ask_decode_batch(tmk_engine* e, const float* samples, uint64_t total_sam
     CK(cudaSetDevice(e->device));
     int rc = ensure_tables(e);
     if (rc != TMK_OK) return rc;
+    // TMK_ASK_DIRECT=1 keeps the direct-form filter (A/B and cross-check of the FFT form)
+    static const bool direct = getenv("TMK_ASK_DIRECT") != nullptr;
+    const uint64_t tile_len = direct ? kT : kT2;
     std::vector<AskStream> sd(n_streams);
     uint64_t words = 0, tiles = 0;
     for (uint32_t s = 0; s < n_streams; ++s) {
@@ -792,7 +806,7 @@ int tmk_ask_decode_batch(tmk_engine* e, const float* samples, uint64_t total_sam
         sd[s].tile_base = uint32_t(tiles);
         sd[s].pad_ = 0;
         words += (streams[s].n_samples + 31) / 32;
-        tiles += (streams[s].n_samples + kT - 1) / kT;
+        tiles += (streams[s].n_samples + tile_len - 1) / tile_len;
         if (tiles > 0x7fffffffull) return tmk_fail(e, TMK_E_INVALID, "batch too large (tile count)");
     }
     const float* dx = samples;
@@ -814,8 +828,6 @@ int tmk_ask_decode_batch(tmk_engine* e, const float* samples, uint64_t total_sam
     const float* tab = static_cast<const float*>(e->d_ask_tab.p);
     CK(cudaEventRecord(e->ev[0], e->stream));
     if (tiles) {
-        // TMK_ASK_DIRECT=1 keeps the direct-form filter (A/B and cross-check of the FFT form)
-        static const bool direct = getenv("TMK_ASK_DIRECT") != nullptr;
         if (direct) {
             ask_scan_kernel<<<uint32_t(tiles), kThreads, 0, e->stream>>>(dx, ds, n_streams, tab, static_cast<uint32_t*>(e->d_ask_bits.p));
         } else {
