@@ -511,16 +511,29 @@ __device__ __noinline__ void eval_word(AskCtx& c, int64_t w, int64_t r, float* s
     int k_lo = first < r ? int(r - first < int64_t(kPre) ? r - first : int64_t(kPre)) : 0;
     if (i >= c.n) k_lo = kPre;
     const int k0 = __reduce_min_sync(kFull, k_lo) & ~7;
+    const int k_hi = __reduce_max_sync(kFull, k_lo);  // from here on every lane of the warp reads real samples
+    const float* __restrict__ xp = x + first;          // dereferenced only at taps >= k_lo, i.e. at samples >= r >= 0
+    int k = k0;
 #pragma unroll 1
-    for (int k = k0; k < kPre; k += 8) {
+    for (; k < kPre && k < k_hi; k += 8) {
         const float4 pa = *reinterpret_cast<const float4*>(c.pre + k), pb = *reinterpret_cast<const float4*>(c.pre + k + 4);
         const float pk[8] = {pa.x, pa.y, pa.z, pa.w, pb.x, pb.y, pb.z, pb.w};
         float xv[8];
 #pragma unroll
-        for (int j = 0; j < 8; ++j) xv[j] = k + j >= k_lo ? x[first + k + j] : 0.0f;
+        for (int j = 0; j < 8; ++j) xv[j] = k + j >= k_lo ? xp[k + j] : 0.0f;
 #pragma unroll
         for (int j = 0; j < 8; ++j)
             if (k + j >= k_lo) sum = fadd(sum, fmul(xv[j], pk[j]));
+    }
+#pragma unroll 4
+    for (; k < kPre; k += 8) {  // no lane needs a mask: load, multiply, add (unrolled: 32 loads in flight above the add chain)
+        const float4 pa = *reinterpret_cast<const float4*>(c.pre + k), pb = *reinterpret_cast<const float4*>(c.pre + k + 4);
+        const float pk[8] = {pa.x, pa.y, pa.z, pa.w, pb.x, pb.y, pb.z, pb.w};
+        float xv[8];
+#pragma unroll
+        for (int j = 0; j < 8; ++j) xv[j] = xp[k + j];
+#pragma unroll
+        for (int j = 0; j < 8; ++j) sum = fadd(sum, fmul(xv[j], pk[j]));
     }
     *sp_out = __fdiv_rn(sum, 200.0f);
 }
