@@ -208,7 +208,7 @@ struct FftSmem {
     // exp(-2 pi i k / N) at [1023 + k]; one pad entry
     float2 tw[kN];
     float2 hc[kN];  // conj(H) / (N 200)
-    float ps[2][kT2];  // (the staged samples xs[2][kXs2] live in buf[1] until the first FFT pass overwrites them)
+    __align__(16) float ps[2][kT2];  // (the staged samples xs[2][kXs2] live in buf[1] until the first FFT pass overwrites them)
     float red[kFT / 32], red2[kFT / 32];
     float carry[2][4];
 };
@@ -345,12 +345,21 @@ ask_scan_fft_kernel(const float* __restrict__ samples, const AskStream* __restri
         sm.buf[0][i] = i < kZ2 ? make_float2(xs0[kW2 - (kPre - 1) + i], xs0[kXs2 + kW2 - (kPre - 1) + i]) : make_float2(0.f, 0.f);
 
     // ---- EMA power (as in ask_scan_kernel), each half over its own tile
+    // a thread's kPer consecutive samples are read ONCE, as 16-byte loads (scalar loads at a 64-byte thread stride are
+    // 16-way bank conflicts), squared and scaled, and kept in registers for both passes of the scan
+    static_assert(kPer % 4 == 0 && kW2 % kPer == 0, "EMA blocking");
+    float e[kPer];
+#pragma unroll
+    for (int j = 0; j < kPer; j += 4) {
+        const float4 v4 = *reinterpret_cast<const float4*>(xs + htid * kPer + j);
+        e[j] = v4.x * v4.x * kInv64;
+        e[j + 1] = v4.y * v4.y * kInv64;
+        e[j + 2] = v4.z * v4.z * kInv64;
+        e[j + 3] = v4.w * v4.w * kInv64;
+    }
     float q = 0.0f;
 #pragma unroll
-    for (int j = 0; j < kPer; ++j) {
-        const float v = xs[htid * kPer + j];
-        q = fmaf(q, kC, v * v * kInv64);
-    }
+    for (int j = 0; j < kPer; ++j) q = fmaf(q, kC, e[j]);
     float v = q, mul = mul0;
 #pragma unroll
     for (int o = 1; o < 32; o <<= 1) {
@@ -367,10 +376,13 @@ ask_scan_fft_kernel(const float* __restrict__ samples, const AskStream* __restri
     float p = fmaf(pin, clane, prev);
 #pragma unroll
     for (int j = 0; j < kPer; ++j) {
-        const int i = htid * kPer + j;
-        const float xv = xs[i];
-        p = fmaf(p, kC, xv * xv * kInv64);
-        if (i >= kW2) sm.ps[half][i - kW2] = p;
+        p = fmaf(p, kC, e[j]);
+        e[j] = p;
+    }
+    if (htid * kPer >= kW2) {  // all of the thread's samples are positions of the tile (kW2 is a multiple of kPer)
+#pragma unroll
+        for (int j = 0; j < kPer; j += 4)
+            *reinterpret_cast<float4*>(&sm.ps[half][htid * kPer - kW2 + j]) = make_float4(e[j], e[j + 1], e[j + 2], e[j + 3]);
     }
     __syncthreads();
 
