@@ -280,41 +280,67 @@ ask_scan_fft_kernel(const float* __restrict__ samples, const AskStream* __restri
     constexpr int kPer = kXs2 / 128;
     const float mul0 = powf(kC, float(kPer)), c768 = powf(kC, float(kPer * 32)), clane = powf(kC, float(kPer * lane));
     const uint32_t n_pairs = (n_tiles + 1) / 2;
+    // software pipeline over the CTA's pairs: the samples of the NEXT pair are located and loaded into registers while
+    // the transforms of the current one run
+    constexpr int kLd = kXs2 / 4 / 128;  // 16-byte loads per thread and tile (stream offsets and t0 - kW2 are multiples of 4)
+    struct TileAt {
+        AskStream sd;
+        int64_t n, t0;
+        bool valid;
+    };
+    auto locate = [&](uint32_t pr) {
+        TileAt a;
+        const uint32_t tl = 2 * pr + half;
+        a.valid = pr < n_pairs && tl < n_tiles;
+        a.sd = streams[0];
+        a.n = 0;
+        a.t0 = 0;
+        if (a.valid) {
+            uint32_t lo = 0, hi = n_streams - 1;
+            while (lo < hi) {
+                const uint32_t mid = (lo + hi + 1) >> 1;
+                if (streams[mid].tile_base <= tl) lo = mid; else hi = mid - 1;
+            }
+            a.sd = streams[lo];
+            a.n = int64_t(a.sd.n);
+            a.t0 = int64_t(tl - a.sd.tile_base) * kT2;
+        }
+        return a;
+    };
+    auto fetch = [&](const TileAt& a, float4 (&q)[kLd]) {
+        const float* __restrict__ x = samples + a.sd.offset;
+#pragma unroll
+        for (int r = 0; r < kLd; ++r) {
+            const int64_t g = a.t0 - kW2 + 4 * (htid + 128 * r);
+            float4 q4 = make_float4(0.f, 0.f, 0.f, 0.f);
+            if (a.valid && g >= 0 && g + 3 < a.n) {
+                q4 = __ldg(reinterpret_cast<const float4*>(x + g));
+            } else if (a.valid) {
+                if (g >= 0 && g < a.n) q4.x = x[g];
+                if (g + 1 >= 0 && g + 1 < a.n) q4.y = x[g + 1];
+                if (g + 2 >= 0 && g + 2 < a.n) q4.z = x[g + 2];
+                if (g + 3 >= 0 && g + 3 < a.n) q4.w = x[g + 3];
+            }
+            q[r] = q4;
+        }
+    };
+    TileAt nxt = locate(blockIdx.x);
+    float4 qn[kLd];
+    fetch(nxt, qn);
 #pragma unroll 1
     for (uint32_t pair = blockIdx.x; pair < n_pairs; pair += gridDim.x) {
-    const uint32_t tile = 2 * pair + half;
-    const bool valid = tile < n_tiles;
-    AskStream sd = streams[0];
-    int64_t n = 0, t0 = 0;
-    if (valid) {
-        uint32_t lo = 0, hi = n_streams - 1;
-        while (lo < hi) {
-            const uint32_t mid = (lo + hi + 1) >> 1;
-            if (streams[mid].tile_base <= tile) lo = mid; else hi = mid - 1;
-        }
-        sd = streams[lo];
-        n = int64_t(sd.n);
-        t0 = int64_t(tile - sd.tile_base) * kT2;
-    }
-    const float* __restrict__ x = samples + sd.offset;
+    const TileAt cur = nxt;
+    const bool valid = cur.valid;
+    const AskStream sd = cur.sd;
+    const int64_t n = cur.n, t0 = cur.t0;
     float xmax = 0.0f, ss = 0.0f;
     static_assert(sizeof(float) * 2 * kXs2 <= sizeof(float2) * kN, "the staged samples alias buf[1]");
     float* xs0 = reinterpret_cast<float*>(sm.buf[1]);
     float* xs = xs0 + half * kXs2;
-    // 16-byte loads: stream offsets are multiples of 4 samples, t0 - kW2 too
 #pragma unroll
-    for (int r = 0; r < kXs2 / 4 / 128; ++r) {
+    for (int r = 0; r < kLd; ++r) {
         const int i = 4 * (htid + 128 * r);
-        const int64_t g = t0 - kW2 + i;
-        float4 q4 = make_float4(0.f, 0.f, 0.f, 0.f);
-        if (valid && g >= 0 && g + 3 < n) {
-            q4 = __ldg(reinterpret_cast<const float4*>(x + g));
-        } else if (valid) {
-            if (g >= 0 && g < n) q4.x = x[g];
-            if (g + 1 >= 0 && g + 1 < n) q4.y = x[g + 1];
-            if (g + 2 >= 0 && g + 2 < n) q4.z = x[g + 2];
-            if (g + 3 >= 0 && g + 3 < n) q4.w = x[g + 3];
-        }
+        const float4 q4 = qn[r];
         *reinterpret_cast<float4*>(xs + i) = q4;
         xmax = fmaxf(fmaxf(xmax, fmaxf(fabsf(q4.x), fabsf(q4.y))), fmaxf(fabsf(q4.z), fabsf(q4.w)));
         const float e4[4] = {q4.x, q4.y, q4.z, q4.w};
@@ -322,6 +348,8 @@ ask_scan_fft_kernel(const float* __restrict__ samples, const AskStream* __restri
         for (int c = 0; c < 4; ++c)
             if (i + c >= kW2 - (kPre - 1)) ss = fmaf(e4[c], e4[c], ss);
     }
+    nxt = locate(pair + gridDim.x);
+    fetch(nxt, qn);
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) {
         xmax = fmaxf(xmax, __shfl_xor_sync(kFull, xmax, o));
