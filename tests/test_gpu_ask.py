@@ -106,3 +106,44 @@ def test_ask_batch_impairments(engine, orc):
     want = oracle_batch(orc, s, st)
     assert_ask_equal(got, want, "impairments")
     assert got["accepted"].sum() > 30 and (got["accepted"] == 0).any()
+
+
+@pytest.mark.parametrize("seed", [0, 1])
+def test_ask_marginal_detection_many_streams(engine, orc, seed):
+    """256 captures whose sync peaks sit ON the `sync_power > 2 power` rule (ask.rs:711-714: amplitude and noise drawn
+    so that 1.1 a ~ 2 (a^2 / 2 + sigma^2)), plus DC offsets, bursts and silence: the FFT filter in front of the walk may
+    only ever add candidates, so every record must still be the oracle's"""
+    import tmkphy
+    rng = np.random.default_rng(900 + seed)
+    caps = []
+    for s in range(256):
+        nf = int(rng.integers(3, 9))
+        fr = rng.integers(0, 2, (nf, 100)).astype(np.uint8)
+        for i in range(nf):
+            fr[i, :8] = [((i + 1) >> (7 - j)) & 1 for j in range(8)]
+        x = orc.ask_modulate(fr, rng.integers(0, 700, nf), rng.integers(0, 700, nf))
+        a = float(rng.uniform(0.25, 1.4))
+        # marginal: 1.1 a = 2 (a^2 / 2 + sigma^2) (1 + d), d in +-8 %
+        d = float(rng.uniform(-0.08, 0.08))
+        s2 = max(1.1 * a / (2 * (1 + d)) - a * a / 2, 1e-6)
+        x = x * np.float32(a) + rng.normal(0, np.sqrt(s2), len(x)).astype(np.float32)
+        kind = s % 8
+        if kind == 1:
+            x += np.float32(rng.uniform(-0.2, 0.2))                 # DC offset
+        elif kind == 2:
+            p = int(rng.integers(0, len(x) - 400))
+            x[p:p + 300] += rng.normal(0, 3.0, 300).astype(np.float32)  # a loud burst, then quiet again
+        elif kind == 3:
+            p = int(rng.integers(0, len(x) - 3000))
+            x[p:p + 2500] = 0.0                                     # a stretch of exact silence
+        elif kind == 4:
+            x = np.concatenate([np.zeros(int(rng.integers(0, 3000)), np.float32), x])
+        caps.append(x.astype(np.float32))
+    st, total = tmkphy.make_streams([len(c) for c in caps], tmkphy.make_config(1))
+    buf = np.zeros(total, np.float32)
+    for c, t in zip(caps, st):
+        buf[int(t["offset"]):int(t["offset"]) + len(c)] = c
+    want = oracle_batch(orc, buf, st)
+    got = engine.ask_decode_batch(buf, st)
+    assert_ask_equal(got, want, f"marginal seed={seed}")
+    assert 300 < len(want) < 256 * 8 and (want["accepted"] == 1).sum() > 200
