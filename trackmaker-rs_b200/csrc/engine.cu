@@ -591,6 +591,8 @@ int tmk_pcm16_encode(tmk_engine* e, const float* samples, uint64_t n, int16_t* p
         CK(e->d_pcm.reserve(n * sizeof(int16_t)));
         d_out = static_cast<int16_t*>(e->d_pcm.p);
     }
+    if (reinterpret_cast<uintptr_t>(d_in) % 16 != 0 || reinterpret_cast<uintptr_t>(d_out) % 8 != 0)
+        return fail(e, TMK_E_INVALID, "tmk_pcm16_encode: device pointers must be aligned (samples 16 bytes, pcm 8 bytes)");
     e->launches += tmk_launch_pcm16_encode(static_cast<const float*>(d_in), d_out, n, e->stream);
     CK(cudaGetLastError());
     if (!dev_out) CK(cudaMemcpyAsync(pcm_out, d_out, n * sizeof(int16_t), cudaMemcpyDeviceToHost, e->stream));
@@ -611,6 +613,8 @@ int tmk_pcm16_to_f32(tmk_engine* e, const int16_t* pcm, uint64_t n, float* sampl
         CK(e->d_samples.reserve(n * sizeof(float)));
         d_out = static_cast<float*>(e->d_samples.p);
     }
+    if (reinterpret_cast<uintptr_t>(d_in) % 8 != 0 || reinterpret_cast<uintptr_t>(d_out) % 16 != 0)
+        return fail(e, TMK_E_INVALID, "tmk_pcm16_to_f32: device pointers must be aligned (pcm 8 bytes, samples 16 bytes)");
     e->launches += tmk_launch_pcm16_to_f32(static_cast<const int16_t*>(d_in), d_out, n, e->stream);
     CK(cudaGetLastError());
     if (!dev_out) CK(cudaMemcpyAsync(samples_out, d_out, n * sizeof(float), cudaMemcpyDeviceToHost, e->stream));
