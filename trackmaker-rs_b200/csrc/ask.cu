@@ -221,8 +221,9 @@ __device__ __forceinline__ float2 cadd(float2 a, float2 b) { return make_float2(
 __device__ __forceinline__ float2 csub(float2 a, float2 b) { return make_float2(a.x - b.x, a.y - b.y); }
 
 // 2048-point Stockham FFT: input in a, scratch b, result in a (six passes). INV: conjugated twiddles, no scaling.
+// The forward transform multiplies by the spectrum table `hm` on the way out of its last pass.
 template <bool INV>
-__device__ __forceinline__ void fft2048(float2* a, float2* b, const float2* __restrict__ tw, int tid) {
+__device__ __forceinline__ void fft2048(float2* a, float2* b, const float2* __restrict__ tw, const float2* __restrict__ hm, int tid) {
     float2 *in = a, *out = b;
 #pragma unroll 1
     for (int p = 1; p <= 256; p <<= 2) {
@@ -261,8 +262,13 @@ __device__ __forceinline__ void fft2048(float2* a, float2* b, const float2* __re
         float2 w = tw[1023 + i];
         if (INV) w.y = -w.y;
         const float2 u0 = in[i], u1 = cmul(in[i + kN / 2], w);
-        out[i] = cadd(u0, u1);
-        out[i + kN / 2] = csub(u0, u1);
+        if (!INV) {
+            out[i] = cmul(cadd(u0, u1), hm[i]);
+            out[i + kN / 2] = cmul(csub(u0, u1), hm[i + kN / 2]);
+        } else {
+            out[i] = cadd(u0, u1);
+            out[i + kN / 2] = csub(u0, u1);
+        }
     }
     __syncthreads();
 }
@@ -416,10 +422,8 @@ ask_scan_fft_kernel(const float* __restrict__ samples, const AskStream* __restri
     __syncthreads();
 
     // ---- fast correlation
-    fft2048<false>(sm.buf[0], sm.buf[1], sm.tw, tid);
-    for (int i = tid; i < kN; i += kFT) sm.buf[0][i] = cmul(sm.buf[0][i], sm.hc[i]);
-    __syncthreads();
-    fft2048<true>(sm.buf[0], sm.buf[1], sm.tw, tid);
+    fft2048<false>(sm.buf[0], sm.buf[1], sm.tw, sm.hc, tid);
+    fft2048<true>(sm.buf[0], sm.buf[1], sm.tw, nullptr, tid);
 
     // ---- candidate test; position t0 + m is z index m
     const float tol = kFftRel * h_scale * sqrtf(ss) * 1.001f + 6.5e-5f * xmax + 1e-7f;
