@@ -225,6 +225,26 @@ uint64_t tmk_launch_count(const tmk_engine* e);
 int tmk_synth_batch(tmk_engine* e, const tmk_phy_config* cfg, uint64_t seed, uint32_t n_streams,
                     uint64_t n_per_stream, float snr_db, float amplitude, float* samples,
                     tmk_frame_rec* truth, uint64_t truth_cap, uint64_t* n_truth);
+/* The same generator with the impairments of SURVEY §8d (BASELINE configs 3 and 4):
+ *   multipath   3-tap FIR h = [1, 0.35 @ t1, -0.2 @ t2] renormalised to unit energy, t1 in U{2..12}, t2 in U{13..40}
+ *               samples per stream
+ *   drift_ppm   clock drift: linear-interpolation resample by (1 + delta), delta in U[-drift_ppm, +drift_ppm] per
+ *               stream (truth positions are then rounded capture positions)
+ *   amp_min     > 0: the whole capture (frames and noise) of a stream is scaled by U[amp_min, 1]
+ *   gap_min/max inter-frame gaps U[gap_min, gap_max) samples (both 0: U[48, 4800)); sparse plans for hour captures
+ * All zero = tmk_synth_batch. */
+typedef struct tmk_synth_params {
+    float snr_db;      /* >= 100: no noise */
+    float amplitude;
+    uint32_t multipath;
+    float drift_ppm;
+    uint32_t gap_min, gap_max;
+    float amp_min;
+    uint32_t _pad;
+} tmk_synth_params;
+int tmk_synth_batch_ex(tmk_engine* e, const tmk_phy_config* cfg, uint64_t seed, uint32_t n_streams,
+                       uint64_t n_per_stream, const tmk_synth_params* prm, float* samples,
+                       tmk_frame_rec* truth, uint64_t truth_cap, uint64_t* n_truth);
 
 /* ------------------------------------------------------------------------------------------------
  * Links: n persistent PhyDecoder instances fed with process_samples calls (the live cadence,
@@ -288,6 +308,11 @@ int tmk_ask_modulate(tmk_engine* e, const uint8_t* bits, uint32_t n_frames, cons
  * streams are used. samples: host or device; recs: host. */
 int tmk_ask_decode_batch(tmk_engine* e, const float* samples, uint64_t total_samples, const tmk_stream* streams,
                          uint32_t n_streams, tmk_ask_rec* recs, uint64_t rec_cap, uint64_t* n_recs);
+/* Synthetic chirp + BPSK captures (measurement harness): n_streams x n_per_stream samples of AWGN (SNR against the
+ * BPSK carrier power 0.5) plus frames laid out like the TX loop of examples/ask.rs:608-637 (gaps U[0,100) before and
+ * after every frame, ids 1..100 cycling, hashed payload bits), generated on the GPU. samples: device or host. */
+int tmk_ask_synth_batch(tmk_engine* e, uint64_t seed, uint32_t n_streams, uint64_t n_per_stream, float snr_db,
+                        float* samples, uint64_t* n_frames);
 /* device time of the stages of the last tmk_ask_decode_batch call, ms: [0] chirp scan, [1] walk */
 int tmk_ask_last_stage_ms(tmk_engine* e, float ms[2]);
 
@@ -308,6 +333,56 @@ int tmk_pcm16_to_f32(tmk_engine* e, const int16_t* pcm, uint64_t n, float* sampl
 int tmk_decode_batch_pcm16(tmk_engine* e, const int16_t* pcm, uint64_t total_samples, const tmk_stream* streams,
                            uint32_t n_streams, tmk_frame_rec* recs, uint64_t rec_cap, uint64_t* n_recs,
                            uint8_t* payload, uint64_t payload_cap, uint64_t* payload_len);
+
+/* WAV container ingest: RIFF/WAVE files as dump_to_wav stores recordings (src/utils/dump.rs:23-46,
+ * hound: a `fmt ` chunk of 16 bytes, or the 40-byte WAVE_FORMAT_EXTENSIBLE form, and a `data` chunk) turned into the
+ * f32 samples the reference's reader produces (convert_audio_buffer_to_f32, src/audio/codec.rs:114-148): CHANNEL 0
+ * only; U8 (s - 128) / 128, S16 s / 32768, S24 s / 8388608, S32 s / 2147483648, F32 as is.
+ *   tmk_wav_parse         the RIFF chunk walk (host only; TMK_E_INVALID for anything that is not such a file)
+ *   tmk_wav_to_f32        n files back to back in one blob (host or device; file i = blob[file_off[i] .. file_off[i+1]))
+ *                         -> channel 0 of file i at samples_out[offsets_out[i] .. + lens_out[i]) (offsets multiples of 4;
+ *                         samples_out device or host; *total_out = floats needed, TMK_E_CAPACITY if sample_cap is smaller)
+ *   tmk_decode_batch_wav  the same unpack on the device in front of tmk_decode_batch: the files cross PCIe as raw
+ *                         bytes; record.stream = file index; streams_out (optional) receives the stream table.
+ * FLAC (src/audio/codec.rs:10-112, symphonia) and the JSON AudioData dump (dump.rs:12-21) are decoded on the host
+ * (the Python mirror reads the JSON form); their samples enter through tmk_decode_batch. */
+typedef struct tmk_wav_info {
+    uint32_t format;          /* 1 = integer PCM, 3 = IEEE float */
+    uint32_t channels;
+    uint32_t sample_rate;
+    uint32_t bits_per_sample;
+    uint32_t block_align;     /* bytes per frame (all channels) */
+    uint32_t _pad;
+    uint64_t data_off;        /* first byte of the first frame, from the start of the file */
+    uint64_t n_frames;        /* samples per channel */
+} tmk_wav_info;
+int tmk_wav_parse(const uint8_t* file, uint64_t len, tmk_wav_info* out);
+int tmk_wav_to_f32(tmk_engine* e, const uint8_t* blob, uint64_t blob_len, const uint64_t* file_off, uint32_t n_files,
+                   float* samples_out, uint64_t sample_cap, uint64_t* offsets_out, uint64_t* lens_out,
+                   uint64_t* total_out);
+int tmk_decode_batch_wav(tmk_engine* e, const uint8_t* blob, uint64_t blob_len, const uint64_t* file_off,
+                         uint32_t n_files, const tmk_phy_config* cfgs, tmk_stream* streams_out, tmk_frame_rec* recs,
+                         uint64_t rec_cap, uint64_t* n_recs, uint8_t* payload, uint64_t payload_cap,
+                         uint64_t* payload_len);
+
+/* ------------------------------------------------------------------------------------------------
+ * Counter reduction over the GPUs of a box: streams shard over ranks with no data-path traffic; the
+ * only collective is an NCCL all-reduce of the decode counters (and of a step time) after a batch. One process
+ * per GPU, one communicator per engine; libnccl is opened at run time (libnccl.so.2 or $TMK_NCCL_LIB).
+ *   tmk_comm_unique_id   ncclGetUniqueId: rank 0 creates the 128-byte id and hands it to the other ranks (the
+ *                        launcher's business: a file, a socket, an environment variable)
+ *   tmk_comm_init        ncclCommInitRank on the engine's device
+ *   tmk_stats_allreduce  the engine's tmk_stats counters summed over all ranks (ncclAllReduce, ncclUint64, ncclSum)
+ *   tmk_comm_allreduce_* the same for caller-provided counters / the maximum of doubles (device time of a step)
+ * Without a communicator the reductions are the identity, so single-GPU callers need no special case. */
+int tmk_comm_unique_id(void* out128);
+int tmk_comm_init(tmk_engine* e, const void* unique_id128, int rank, int world);
+int tmk_comm_size(const tmk_engine* e);
+int tmk_stats_allreduce(tmk_engine* e, uint64_t counters[TMK_STAT_COUNT]);
+int tmk_comm_allreduce_sum_u64(tmk_engine* e, uint64_t* counters, uint32_t n);
+int tmk_comm_allreduce_max_f64(tmk_engine* e, double* values, uint32_t n);
+int tmk_comm_barrier(tmk_engine* e);
+int tmk_comm_destroy(tmk_engine* e);
 
 /* ------------------------------------------------------------------------------------------------
  * IP fragments: the payload layer directly above the PHY. Decoded frames carry IPv4 packets or

@@ -308,3 +308,40 @@ def reassemble_batch(recs, payload, n_links):
     n = lib().orc_reassemble_batch(_ptr(r), len(r), _ptr(pl), int(n_links), _ptr(pk), cap, _ptr(by), bcap, C.byref(nb))
     assert n <= cap and nb.value <= bcap
     return pk[:n].copy(), by[:nb.value].copy()
+
+
+# ---- WAV container (dump.rs:23-46 writes, codec.rs:114-148 reads): numpy restatement, test infrastructure
+def wav_to_f32(data: bytes) -> np.ndarray:
+    """channel 0 of a RIFF/WAVE file as the reference's reader converts it (convert_audio_buffer_to_f32,
+    src/audio/codec.rs:114-148): U8 (s - 128) / 128, S16 s / 32768, S24 s / 8388608, S32 s / 2147483648, F32 as is."""
+    import struct
+    assert data[:4] == b"RIFF" and data[8:12] == b"WAVE"
+    pos, fmt = 12, None
+    while pos + 8 <= len(data):
+        cid, sz = data[pos:pos + 4], struct.unpack("<I", data[pos + 4:pos + 8])[0]
+        body = pos + 8
+        if cid == b"fmt ":
+            tag, ch, rate, _, align, bits = struct.unpack("<HHIIHH", data[body:body + 16])
+            if tag == 0xFFFE:
+                tag = struct.unpack("<H", data[body + 24:body + 26])[0]
+            fmt = (tag, ch, align, bits)
+        elif cid == b"data":
+            tag, ch, align, bits = fmt
+            raw = np.frombuffer(data[body:body + sz], dtype=np.uint8)
+            n = len(raw) // align
+            fr = raw[:n * align].reshape(n, align)[:, :bits // 8].astype(np.uint32)  # channel 0
+            if tag == 3:
+                v = fr[:, 0] | (fr[:, 1] << 8) | (fr[:, 2] << 16) | (fr[:, 3] << 24)
+                return v.astype(np.uint32).view(np.float32).copy()
+            if bits == 8:
+                return ((fr[:, 0].astype(np.float32) - np.float32(128.0)) / np.float32(128.0)).astype(np.float32)
+            if bits == 16:
+                v = (fr[:, 0] | (fr[:, 1] << 8)).astype(np.uint16).view(np.int16)
+                return (v.astype(np.float32) / np.float32(32768.0)).astype(np.float32)
+            if bits == 24:
+                v = ((fr[:, 0] << 8) | (fr[:, 1] << 16) | (fr[:, 2] << 24)).astype(np.uint32).view(np.int32) >> 8
+                return (v.astype(np.float32) / np.float32(8388608.0)).astype(np.float32)
+            v = (fr[:, 0] | (fr[:, 1] << 8) | (fr[:, 2] << 16) | (fr[:, 3] << 24)).astype(np.uint32).view(np.int32)
+            return (v.astype(np.float32) / np.float32(2147483648.0)).astype(np.float32)
+        pos = body + sz + (sz & 1)
+    raise ValueError("no data chunk")

@@ -129,3 +129,30 @@ def test_links_argument_errors(engine):
     recs, pl = bank.process_samples([np.zeros(0, np.float32), np.zeros(0, np.float32)])
     assert len(recs) == 0 and len(pl) == 0
     bank.close()
+
+
+@pytest.mark.parametrize("kind", [FB, MAN])
+def test_phy_decoder_is_streaming(engine, orc, kind):
+    """tmkphy.PhyDecoder carries its state like the reference's (decoder.rs:68-112): fed with the 1200-sample polls of
+    src/mac/csma.rs:446-465 it returns, call by call, the frames one oracle decoder returns for the same calls; reset()
+    starts over (decoder.rs:114-119)."""
+    import tmkphy
+    rng = np.random.default_rng(77 + kind)
+    cfg = tmkphy.make_config(kind, local_addr=1)
+    cap = helpers.make_capture(orc, cfg, rng, n_frames=10, snr_db=15.0)
+    sizes = [1200] * (len(cap) // 1200 + 1)
+    want, wpl, feed = orc.decode_feeds(cfg, cap, sizes)
+    dec = tmkphy.PhyDecoder(engine, 3, 2, kind, local_addr=1)
+    for rnd in range(2):
+        pos, n_frames = 0, 0
+        for k, ln in enumerate(sizes):
+            frames = dec.process_samples(cap[pos:pos + ln])
+            pos += ln
+            w = want[feed == k]
+            helpers.assert_records_equal(dec.last_records, dec.last_payload, w, wpl, f"PhyDecoder call {k}")
+            ok = w[w["status"] == 0]
+            assert [f.data for f in frames] == [bytes(wpl[int(r["payload_off"]):int(r["payload_off"]) + int(r["len"])]) for r in ok]
+            n_frames += len(frames)
+        assert n_frames == int((want["status"] == 0).sum()) and n_frames >= 5
+        dec.reset()
+    dec.close()

@@ -58,15 +58,19 @@ def test_loopback_think_different(engine, orc, kind, chunk):
     enc = tmkphy.PhyEncoder(engine, 3, 2, kind)
     wave = enc.encode_frames(frames, 48)
     assert len(wave) == (32136 if kind == FB else 51216)
-    dec = tmkphy.PhyDecoder(engine, 3, 2, kind, local_addr=1, chunk=chunk)
-    out = dec.process_samples(wave)
+    out, recs, pl = tmkphy.decode_capture(engine, tmkphy.make_config(kind, local_addr=1, chunk=chunk), wave)
     assert b"".join(f.data for f in out) == text and [f.sequence for f in out] == list(range(8))
     stride, P = (4158, 60) if kind == FB else (6624, 96)
-    assert list(dec.last_records["preamble_start"]) == [i * stride for i in range(8)]
-    assert list(dec.last_records["frame_start"]) == [i * stride + P for i in range(8)]
+    assert list(recs["preamble_start"]) == [i * stride for i in range(8)]
+    assert list(recs["frame_start"]) == [i * stride + P for i in range(8)]
     cfg = orc.make_config(kind, local_addr=1, chunk=chunk)
     want, wpl = orc.decode_stream(cfg, wave)
-    helpers.assert_records_equal(dec.last_records, dec.last_payload, want, wpl, "loopback")
+    helpers.assert_records_equal(recs, pl, want, wpl, "loopback")
+    # the reference's own call: ONE PhyDecoder::process_samples over the whole capture (src/main.rs:540)
+    dec = tmkphy.PhyDecoder(engine, 3, 2, kind, local_addr=1)
+    out2 = dec.process_samples(wave)
+    assert [f.data for f in out2] == [f.data for f in out]
+    dec.close()
 
 
 @pytest.mark.parametrize("kind", [FB, MAN])

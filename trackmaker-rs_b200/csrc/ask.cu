@@ -942,6 +942,42 @@ int tmk_ask_decode_batch(tmk_engine* e, const float* samples, uint64_t total_sam
     return TMK_OK;
 }
 
+// Synthetic chirp + BPSK captures (measurement harness): AWGN of the given SNR against the BPSK carrier power 0.5
+//  plus frames laid out like the reference's TX loop, generated on the GPU. samples: device or host.
+int tmk_ask_synth_batch(tmk_engine* e, uint64_t seed, uint32_t n_streams, uint64_t n_per_stream, float snr_db, float* samples,
+                        uint64_t* n_frames) {
+    if (!e || !samples || !n_frames) return tmk_fail(e, TMK_E_INVALID, "tmk_ask_synth_batch: null argument");
+    if (n_per_stream % 4 != 0 || n_per_stream >= (1ull << 32))
+        return tmk_fail(e, TMK_E_INVALID, "tmk_ask_synth_batch: n_per_stream must be a multiple of 4 below 2^32");
+    *n_frames = 0;
+    if (n_streams == 0) return TMK_OK;
+    CK(cudaSetDevice(e->device));
+    int rc = ensure_tables(e);
+    if (rc != TMK_OK) return rc;
+    const uint64_t total = uint64_t(n_streams) * n_per_stream;
+    float* d_x = samples;
+    const bool dev_out = tmk_is_device_ptr(samples);
+    if (!dev_out) {
+        CK(e->d_samples.reserve(total * sizeof(float)));
+        d_x = static_cast<float*>(e->d_samples.p);
+    }
+    TmkSynthImp imp;
+    std::memset(&imp, 0, sizeof imp);
+    const float sigma = snr_db >= 100.0f ? 0.0f : std::sqrt(0.5f) * std::pow(10.0f, -snr_db / 20.0f);
+    e->launches += tmk_launch_synth_noise(seed ^ 0xA5Cull, total, sigma, n_per_stream, imp, d_x, e->stream);
+    CK(e->d_ask_l2.reserve(4 * sizeof(unsigned long long)));
+    CK(cudaMemsetAsync(e->d_ask_l2.p, 0, 4 * sizeof(unsigned long long), e->stream));
+    e->launches += tmk_launch_ask_synth(static_cast<const float*>(e->d_ask_tab.p), seed, n_streams, n_per_stream, d_x,
+                                        static_cast<unsigned long long*>(e->d_ask_l2.p), e->stream);
+    CK(cudaGetLastError());
+    unsigned long long nf = 0;
+    CK(cudaMemcpyAsync(&nf, e->d_ask_l2.p, sizeof nf, cudaMemcpyDeviceToHost, e->stream));
+    if (!dev_out) CK(cudaMemcpyAsync(samples, d_x, total * sizeof(float), cudaMemcpyDeviceToHost, e->stream));
+    CK(cudaStreamSynchronize(e->stream));
+    *n_frames = nf;
+    return TMK_OK;
+}
+
 int tmk_ask_last_stage_ms(tmk_engine* e, float ms[2]) {
     if (!e || !ms) return TMK_E_INVALID;
     ms[0] = e->ask_ms[0];

@@ -191,7 +191,8 @@ void tmk_engine_destroy(tmk_engine* e) {
     if (!e) return;
     cudaSetDevice(e->device);
     if (e->stream) cudaStreamSynchronize(e->stream);
-    DevBuf* bufs[] = {&e->d_tile_dir, &e->d_patterns, &e->d_streams, &e->d_blk_info, &e->d_cand, &e->d_recs_tmp, &e->d_rec_ord,
+    tmk_comm_destroy(e);
+    DevBuf* bufs[] = {&e->d_comm, &e->d_wav, &e->d_wavdesc, &e->d_tile_dir, &e->d_patterns, &e->d_streams, &e->d_blk_info, &e->d_cand, &e->d_recs_tmp, &e->d_rec_ord,
                       &e->d_recs, &e->d_payload, &e->d_cnt, &e->d_base, &e->d_counters, &e->d_samples,
                       &e->d_misc, &e->d_misc2, &e->d_next, &e->d_cblk, &e->d_blk_ptr, &e->d_entries, &e->d_spec, &e->d_pool, &e->d_link, &e->d_pcm, &e->d_frag,
                       &e->d_ask_tab, &e->d_ask_bits, &e->d_ask_l2,
@@ -872,13 +873,22 @@ int tmk_device_pci_bus_id(tmk_engine* e, char* out, int cap) {
 
 uint64_t tmk_launch_count(const tmk_engine* e) { return e ? e->launches : 0; }
 
-int tmk_synth_batch(tmk_engine* e, const tmk_phy_config* cfg, uint64_t seed, uint32_t n_streams, uint64_t n_per_stream,
-                    float snr_db, float amplitude, float* samples, tmk_frame_rec* truth, uint64_t truth_cap,
-                    uint64_t* n_truth) {
-    if (!e || !cfg || !samples || !n_truth || (!truth && truth_cap))
+int tmk_synth_batch_ex(tmk_engine* e, const tmk_phy_config* cfg, uint64_t seed, uint32_t n_streams, uint64_t n_per_stream,
+                       const tmk_synth_params* prm, float* samples, tmk_frame_rec* truth, uint64_t truth_cap,
+                       uint64_t* n_truth) {
+    if (!e || !cfg || !prm || !samples || !n_truth || (!truth && truth_cap))
         return fail(e, TMK_E_INVALID, "tmk_synth_batch: null argument");
     if (!valid_cfg(*cfg) || n_per_stream % 4 != 0 || n_per_stream >= (1ull << 32))
         return fail(e, TMK_E_INVALID, "tmk_synth_batch: invalid config or n_per_stream (multiple of 4, < 2^32)");
+    TmkSynthImp imp;
+    imp.multipath = prm->multipath ? 1u : 0u;
+    imp.drift_ppm = prm->drift_ppm;
+    imp.gap_min = prm->gap_max > prm->gap_min ? prm->gap_min : 48u;
+    imp.gap_span = prm->gap_max > prm->gap_min ? prm->gap_max - prm->gap_min : 4800u - 48u;
+    imp.amp_min = prm->amp_min;
+    if (!(std::fabs(imp.drift_ppm) <= 10000.0f) || imp.amp_min < 0.0f || imp.amp_min > 1.0f || (imp.multipath && imp.gap_min < 48u))
+        return fail(e, TMK_E_INVALID, "tmk_synth_batch_ex: drift beyond +-10000 ppm, amp_min outside [0, 1] or gaps below 48 with multipath");
+    const float snr_db = prm->snr_db, amplitude = prm->amplitude;
     CK(cudaSetDevice(e->device));
     uint32_t pi = 0;
     int rc = pattern_index(e, *cfg, &pi);
@@ -892,12 +902,12 @@ int tmk_synth_batch(tmk_engine* e, const tmk_phy_config* cfg, uint64_t seed, uin
         d_x = static_cast<float*>(e->d_samples.p);
     }
     const float sigma = snr_db >= 100.0f ? 0.0f : amplitude * std::pow(10.0f, -snr_db / 20.0f);
-    e->launches += tmk_launch_synth_noise(seed, total, sigma, d_x, e->stream);
+    e->launches += tmk_launch_synth_noise(seed, total, sigma, n_per_stream, imp, d_x, e->stream);
     CK(e->d_cnt.reserve(sizeof(uint32_t) * std::max<uint32_t>(1, n_streams)));
     CK(e->d_base.reserve(sizeof(uint64_t) * (n_streams + 1)));
     uint32_t* d_cnt = static_cast<uint32_t*>(e->d_cnt.p);
     uint64_t* d_base = static_cast<uint64_t*>(e->d_base.p);
-    e->launches += tmk_launch_synth_plan(dp, cfg->local_addr, seed, n_streams, n_per_stream, d_cnt, nullptr, nullptr, 0, e->stream);
+    e->launches += tmk_launch_synth_plan(dp, cfg->local_addr, seed, n_streams, n_per_stream, imp, d_cnt, nullptr, nullptr, 0, e->stream);
     e->launches += tmk_launch_excl_scan(d_cnt, d_base, n_streams, e->stream);
     uint64_t n_frames = 0;
     CK(cudaMemcpyAsync(&n_frames, d_base + n_streams, sizeof n_frames, cudaMemcpyDeviceToHost, e->stream));
@@ -905,8 +915,8 @@ int tmk_synth_batch(tmk_engine* e, const tmk_phy_config* cfg, uint64_t seed, uin
     *n_truth = n_frames;
     CK(e->d_recs_tmp.reserve(sizeof(tmk_frame_rec) * std::max<uint64_t>(1, n_frames)));
     tmk_frame_rec* d_fr = static_cast<tmk_frame_rec*>(e->d_recs_tmp.p);
-    e->launches += tmk_launch_synth_plan(dp, cfg->local_addr, seed, n_streams, n_per_stream, d_cnt, d_base, d_fr, n_frames, e->stream);
-    e->launches += tmk_launch_synth_frames(dp, seed, n_per_stream, amplitude, d_fr, n_frames, d_x, e->stream);
+    e->launches += tmk_launch_synth_plan(dp, cfg->local_addr, seed, n_streams, n_per_stream, imp, d_cnt, d_base, d_fr, n_frames, e->stream);
+    e->launches += tmk_launch_synth_frames(dp, seed, n_per_stream, amplitude, imp, d_fr, n_frames, d_x, e->stream);
     CK(cudaGetLastError());
     if (!dev_out) CK(cudaMemcpyAsync(samples, d_x, total * sizeof(float), cudaMemcpyDeviceToHost, e->stream));
     if (truth && n_frames) {
@@ -917,6 +927,16 @@ int tmk_synth_batch(tmk_engine* e, const tmk_phy_config* cfg, uint64_t seed, uin
     CK(cudaStreamSynchronize(e->stream));
     if (truth && n_frames > truth_cap) return fail(e, TMK_E_CAPACITY, "tmk_synth_batch: truth buffer too small");
     return TMK_OK;
+}
+
+int tmk_synth_batch(tmk_engine* e, const tmk_phy_config* cfg, uint64_t seed, uint32_t n_streams, uint64_t n_per_stream,
+                    float snr_db, float amplitude, float* samples, tmk_frame_rec* truth, uint64_t truth_cap,
+                    uint64_t* n_truth) {
+    tmk_synth_params prm;
+    std::memset(&prm, 0, sizeof prm);
+    prm.snr_db = snr_db;
+    prm.amplitude = amplitude;
+    return tmk_synth_batch_ex(e, cfg, seed, n_streams, n_per_stream, &prm, samples, truth, truth_cap, n_truth);
 }
 
 }  // extern "C"

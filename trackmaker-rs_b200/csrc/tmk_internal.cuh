@@ -180,9 +180,18 @@ int tmk_launch_pcm16_encode(const float* samples, int16_t* out, uint64_t n, cuda
 int tmk_launch_modulate(const TmkPattern* pattern, const tmk_frame_desc* frames, const uint64_t* frame_off,
                         uint32_t n_frames, const uint8_t* payload, float* out, cudaStream_t st);
 // synthetic captures (synth.cu)
-int tmk_launch_synth_noise(uint64_t seed, uint64_t total, float sigma, float* samples, cudaStream_t st);
+struct TmkSynthImp {      // impairments of tmk_synth_batch_ex (defaults: no multipath, no drift, gaps U[48, 4800))
+    uint32_t multipath;
+    float drift_ppm;
+    uint32_t gap_min, gap_span;  // inter-frame gap = gap_min + U[0, gap_span)
+    float amp_min;               // > 0: per-stream amplitude scale U[amp_min, 1]
+};
+int tmk_launch_synth_noise(uint64_t seed, uint64_t total, float sigma, uint64_t n_per_stream, TmkSynthImp imp,
+                           float* samples, cudaStream_t st);
 int tmk_launch_synth_plan(const TmkPattern* pattern, int32_t local_addr, uint64_t seed, uint32_t n_streams,
-                          uint64_t n_per_stream, uint32_t* counts, const uint64_t* base, tmk_frame_rec* frames,
-                          uint64_t frame_cap, cudaStream_t st);
+                          uint64_t n_per_stream, TmkSynthImp imp, uint32_t* counts, const uint64_t* base,
+                          tmk_frame_rec* frames, uint64_t frame_cap, cudaStream_t st);
 int tmk_launch_synth_frames(const TmkPattern* pattern, uint64_t seed, uint64_t n_per_stream, float amplitude,
-                            tmk_frame_rec* frames, uint64_t n_frames, float* samples, cudaStream_t st);
+                            TmkSynthImp imp, tmk_frame_rec* frames, uint64_t n_frames, float* samples, cudaStream_t st);
+int tmk_launch_ask_synth(const float* tab, uint64_t seed, uint32_t n_streams, uint64_t n_per_stream, float* samples,
+                         unsigned long long* n_frames, cudaStream_t st);

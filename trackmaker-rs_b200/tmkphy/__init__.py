@@ -400,6 +400,142 @@ class Engine:
         return out, (truth[:nt.value].copy() if want_truth else int(nt.value))
 
 
+    def synth_batch_ex(self, cfg, seed, n_streams, n_per_stream, snr_db, amplitude=1.0, multipath=False, drift_ppm=0.0,
+                       gap=(0, 0), amp_min=0.0, device_ptr=None, want_truth=True):
+        """tmk_synth_batch_ex: the generator with the impairments of SURVEY §8d (multipath FIR, clock drift,
+        per-stream amplitude, sparse frame plans)."""
+        total = n_streams * n_per_stream
+        cap = (total // 300 + n_streams + 16) if want_truth else 0
+        truth = np.zeros(cap, REC_DTYPE) if want_truth else None
+        nt = C.c_uint64(0)
+        prm = _abi.SynthParams(snr_db, amplitude, 1 if multipath else 0, drift_ppm, int(gap[0]), int(gap[1]), amp_min, 0)
+        if device_ptr is None:
+            out = np.zeros(total, np.float32)
+            sp = _ptr(out)
+        else:
+            out, sp = None, C.c_void_p(int(device_ptr))
+        self._check(self._lib.tmk_synth_batch_ex(self._h, C.byref(cfg), seed, n_streams, n_per_stream, C.byref(prm), sp,
+                                                 _ptr(truth) if want_truth else None, cap, C.byref(nt)))
+        return out, (truth[:nt.value].copy() if want_truth else int(nt.value))
+
+    def ask_synth_batch(self, seed, n_streams, n_per_stream, snr_db, device_ptr=None):
+        """tmk_ask_synth_batch: chirp + BPSK captures. -> (samples or None, frames planted)"""
+        total = n_streams * n_per_stream
+        nf = C.c_uint64(0)
+        if device_ptr is None:
+            out = np.zeros(total, np.float32)
+            sp = _ptr(out)
+        else:
+            out, sp = None, C.c_void_p(int(device_ptr))
+        self._check(self._lib.tmk_ask_synth_batch(self._h, seed, n_streams, n_per_stream, snr_db, sp, C.byref(nf)))
+        return out, int(nf.value)
+
+    # ---- WAV container ingest (src/utils/dump.rs:23-46 writes them, src/audio/codec.rs:114-148 reads them)
+    def wav_to_f32(self, files):
+        """channel 0 of every WAVE file (list of bytes) as f32 -> list of float32 arrays"""
+        blob, off = _blob(files)
+        offs, lens = np.zeros(len(files), np.uint64), np.zeros(len(files), np.uint64)
+        total = C.c_uint64(0)
+        rc = self._lib.tmk_wav_to_f32(self._h, _ptr(blob), blob.size - 1, _ptr(off), len(files), None, 0, _ptr(offs),
+                                      _ptr(lens), C.byref(total))
+        if rc not in (0, _abi.E_CAPACITY):
+            self._check(rc)
+        out = np.zeros(max(1, total.value), np.float32)
+        self._check(self._lib.tmk_wav_to_f32(self._h, _ptr(blob), blob.size - 1, _ptr(off), len(files), _ptr(out),
+                                             out.size, _ptr(offs), _ptr(lens), C.byref(total)))
+        return [out[int(o):int(o) + int(n)].copy() for o, n in zip(offs, lens)]
+
+    def decode_batch_wav(self, files, cfgs, rec_cap=None, payload_cap=None):
+        """tmk_decode_batch_wav: WAVE files (list of bytes) in, (records, payload, streams) out; record.stream = file"""
+        blob, off = _blob(files)
+        cf = (PhyConfig * len(files))(*(cfgs if isinstance(cfgs, (list, tuple)) else [cfgs] * len(files)))
+        st = np.zeros(len(files), STREAM_DTYPE)
+        tot = blob.size // 2
+        rec_cap = int(rec_cap) if rec_cap is not None else max(1024, tot // 96 + 2 * len(files))
+        payload_cap = int(payload_cap) if payload_cap is not None else max(65536, tot // 12)
+        recs = np.zeros(rec_cap, REC_DTYPE)
+        pl = np.zeros(payload_cap, np.uint8)
+        nr, npl = C.c_uint64(0), C.c_uint64(0)
+        self._check(self._lib.tmk_decode_batch_wav(self._h, _ptr(blob), blob.size - 1, _ptr(off), len(files), cf,
+                                                   _ptr(st), _ptr(recs), rec_cap, C.byref(nr), _ptr(pl), payload_cap,
+                                                   C.byref(npl)))
+        return recs[:nr.value].copy(), pl[:npl.value].copy(), st
+
+    # ---- counter reduction over the GPUs of a box (NCCL, one process per GPU)
+    def comm_init(self, unique_id, rank, world):
+        buf = C.create_string_buffer(bytes(unique_id), 128)
+        self._check(self._lib.tmk_comm_init(self._h, buf, int(rank), int(world)))
+
+    def comm_size(self):
+        return int(self._lib.tmk_comm_size(self._h))
+
+    def stats_allreduce(self):
+        c = (C.c_uint64 * _abi.STAT_COUNT)()
+        self._check(self._lib.tmk_stats_allreduce(self._h, c))
+        return dict(zip(STAT_NAMES, [int(v) for v in c]))
+
+    def allreduce_sum(self, values):
+        c = (C.c_uint64 * len(values))(*[int(v) for v in values])
+        self._check(self._lib.tmk_comm_allreduce_sum_u64(self._h, c, len(values)))
+        return [int(v) for v in c]
+
+    def allreduce_max(self, values):
+        c = (C.c_double * len(values))(*[float(v) for v in values])
+        self._check(self._lib.tmk_comm_allreduce_max_f64(self._h, c, len(values)))
+        return [float(v) for v in c]
+
+    def comm_barrier(self):
+        self._check(self._lib.tmk_comm_barrier(self._h))
+
+    def comm_destroy(self):
+        self._check(self._lib.tmk_comm_destroy(self._h))
+
+
+def comm_unique_id():
+    """ncclGetUniqueId through the library (rank 0 calls it and hands the 128 bytes to the other ranks)"""
+    buf = C.create_string_buffer(128)
+    rc = _abi.load_library().tmk_comm_unique_id(buf)
+    if rc != 0:
+        raise TmkError(rc, "tmk_comm_unique_id failed (libnccl not loadable?)")
+    return buf.raw
+
+
+def _blob(files):
+    """list of bytes -> (uint8 array with one pad byte, uint64 offsets[n + 1])"""
+    off = np.zeros(len(files) + 1, np.uint64)
+    if files:
+        off[1:] = np.cumsum([len(f) for f in files], dtype=np.uint64)
+    return np.frombuffer(b"".join(bytes(f) for f in files) + b"\0", dtype=np.uint8).copy(), off
+
+
+def wav_parse(data):
+    """tmk_wav_parse -> dict (format, channels, sample_rate, bits_per_sample, block_align, data_off, n_frames)"""
+    b = np.frombuffer(bytes(data) + b"\0", dtype=np.uint8)
+    info = _abi.WavInfo()
+    rc = _abi.load_library().tmk_wav_parse(_ptr(b), len(data), C.byref(info))
+    if rc != 0:
+        raise ValueError("not a supported WAVE file")
+    return {k: int(getattr(info, k)) for k, _ in _abi.WavInfo._fields_ if k != "_pad"}
+
+
+def wav_bytes(pcm16, sample_rate=SAMPLE_RATE, channels=1):
+    """the file hound writes for dump_to_wav (src/utils/dump.rs:23-46): 44-byte PCM header + int16 little endian"""
+    import struct
+    d = np.ascontiguousarray(pcm16, dtype="<i2").tobytes()
+    return (b"RIFF" + struct.pack("<I", 36 + len(d)) + b"WAVEfmt " +
+            struct.pack("<IHHIIHH", 16, 1, channels, sample_rate, sample_rate * channels * 2, channels * 2, 16) +
+            b"data" + struct.pack("<I", len(d)) + d)
+
+
+def audio_data_from_json(text):
+    """AudioData as dump_to_json writes it (src/utils/dump.rs:4-21): {sample_rate, audio_data, duration, channels}.
+    serde_json reads the numbers as f64 and narrows to f32; so does this. Container parsing is host work."""
+    import json
+    d = json.loads(text)
+    return {"sample_rate": int(d["sample_rate"]), "channels": int(d["channels"]), "duration": float(d["duration"]),
+            "audio_data": np.asarray(d["audio_data"], dtype=np.float64).astype(np.float32)}
+
+
 def make_config(kind, local_addr=1, spl=SAMPLES_PER_LEVEL, preamble_bytes=PREAMBLE_PATTERN_BYTES, threshold=0.9,
                 max_frame_bytes=2 * MAX_FRAME_DATA_SIZE, chunk=0):
     return PhyConfig(int(kind), spl, preamble_bytes, local_addr, threshold, max_frame_bytes, chunk)
@@ -449,26 +585,44 @@ class PhyEncoder:
 class PhyDecoder:
     """PhyDecoder::new(samples_per_level, preamble_bytes, line_coding_kind, local_addr)  decoder.rs:36-65
 
-    Offline use: every process_samples call decodes one whole capture with a fresh decoder state
-    (what src/main.rs:540 does); `chunk` reproduces the verdicts of feeding it in chunk-sized calls.
-    """
+    STREAMING, like the reference (decoder.rs:68-112): every process_samples call appends the slice to the
+    decoder's buffer, runs search / decode_frame until more data is needed, and returns the frames that completed
+    in this call; a frame still being gathered is carried to the next call. It is a bank of one link
+    (tmk_links_*); feed many decoders at once through PhyDecoderBank. reset() is decoder.rs:114-119."""
 
-    def __init__(self, engine, samples_per_level, preamble_bytes, line_coding_kind, local_addr, chunk=0):
+    def __init__(self, engine, samples_per_level, preamble_bytes, line_coding_kind, local_addr):
         self.engine = engine
         self.cfg = make_config(line_coding_kind, local_addr=local_addr, spl=samples_per_level,
-                               preamble_bytes=preamble_bytes, chunk=chunk)
-        self.last_records = np.zeros(0, REC_DTYPE)
+                               preamble_bytes=preamble_bytes)
+        self._bank = PhyDecoderBank(engine, [self.cfg])
+        self.last_records = np.zeros(0, REC_DTYPE)  # verdict records of the last call (positions from the first sample fed)
         self.last_payload = np.zeros(0, np.uint8)
 
     def process_samples(self, samples):
         s = np.ascontiguousarray(samples, dtype=np.float32)
-        st, _ = make_streams([s.size], self.cfg)
-        self.last_records, self.last_payload = self.engine.decode_batch(s, st)
+        self.last_records, self.last_payload = self._bank.process_samples([s])
         return records_to_frames(self.last_records, self.last_payload)
 
-    def reset(self):  # decoder.rs:114-119 — nothing is carried between calls
+    def reset(self):
+        self._bank.reset()
         self.last_records = np.zeros(0, REC_DTYPE)
         self.last_payload = np.zeros(0, np.uint8)
+
+    def state(self):
+        return self._bank.state(0)
+
+    def close(self):
+        self._bank.close()
+
+
+def decode_capture(engine, cfg, samples):
+    """One-shot decode of a whole capture with a fresh decoder (what src/main.rs:540 does with one process_samples
+    call); cfg.chunk reproduces the verdicts of feeding it in chunk-sized calls. -> (frames, records, payload);
+    a frame the capture cuts off is a TMK_FRAME_TRUNCATED record."""
+    s = np.ascontiguousarray(samples, dtype=np.float32)
+    st, _ = make_streams([s.size], cfg)
+    recs, pl = engine.decode_batch(s, st)
+    return records_to_frames(recs, pl), recs, pl
 
 
 class PhyDecoderBank:

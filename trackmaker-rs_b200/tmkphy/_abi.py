@@ -44,8 +44,19 @@ class FrameDesc(C.Structure):
                 ("src", C.c_uint8), ("dst", C.c_uint8)]
 
 
+class SynthParams(C.Structure):
+    _fields_ = [("snr_db", C.c_float), ("amplitude", C.c_float), ("multipath", C.c_uint32), ("drift_ppm", C.c_float),
+                ("gap_min", C.c_uint32), ("gap_max", C.c_uint32), ("amp_min", C.c_float), ("_pad", C.c_uint32)]
+
+
+class WavInfo(C.Structure):
+    _fields_ = [("format", C.c_uint32), ("channels", C.c_uint32), ("sample_rate", C.c_uint32),
+                ("bits_per_sample", C.c_uint32), ("block_align", C.c_uint32), ("_pad", C.c_uint32),
+                ("data_off", C.c_uint64), ("n_frames", C.c_uint64)]
+
+
 assert C.sizeof(PhyConfig) == 32 and C.sizeof(Stream) == 48 and C.sizeof(FrameRec) == 48
-assert C.sizeof(FrameDesc) == 16
+assert C.sizeof(FrameDesc) == 16 and C.sizeof(SynthParams) == 32 and C.sizeof(WavInfo) == 40
 
 # numpy mirrors (zero-copy views of record arrays)
 CFG_DTYPE = np.dtype([("line_code", "<i4"), ("spl", "<u4"), ("preamble_bytes", "<u4"), ("local_addr", "<i4"),
@@ -121,6 +132,19 @@ SYMBOLS = {
     "tmk_fragment_batch": (C.c_int, [_vp, _vp, _vp, _u32, _u32, C.c_uint16, _vp, _u64, _pu64, _vp, _u64, _pu64,
                                      C.POINTER(C.c_uint16)]),
     "tmk_synth_batch": (C.c_int, [_vp, _pcfg, _u64, _u32, _u64, C.c_float, C.c_float, _vp, _vp, _u64, _pu64]),
+    "tmk_synth_batch_ex": (C.c_int, [_vp, _pcfg, _u64, _u32, _u64, C.POINTER(SynthParams), _vp, _vp, _u64, _pu64]),
+    "tmk_ask_synth_batch": (C.c_int, [_vp, _u64, _u32, _u64, C.c_float, _vp, _pu64]),
+    "tmk_wav_parse": (C.c_int, [_vp, _u64, C.POINTER(WavInfo)]),
+    "tmk_wav_to_f32": (C.c_int, [_vp, _vp, _u64, _vp, _u32, _vp, _u64, _vp, _vp, _pu64]),
+    "tmk_decode_batch_wav": (C.c_int, [_vp, _vp, _u64, _vp, _u32, _vp, _vp, _vp, _u64, _pu64, _vp, _u64, _pu64]),
+    "tmk_comm_unique_id": (C.c_int, [_vp]),
+    "tmk_comm_init": (C.c_int, [_vp, _vp, C.c_int, C.c_int]),
+    "tmk_comm_size": (C.c_int, [_vp]),
+    "tmk_stats_allreduce": (C.c_int, [_vp, _pu64]),
+    "tmk_comm_allreduce_sum_u64": (C.c_int, [_vp, _pu64, _u32]),
+    "tmk_comm_allreduce_max_f64": (C.c_int, [_vp, C.POINTER(C.c_double), _u32]),
+    "tmk_comm_barrier": (C.c_int, [_vp]),
+    "tmk_comm_destroy": (C.c_int, [_vp]),
 }
 
 PKG_DIR = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
