@@ -219,7 +219,8 @@ def phy_leg(eng, orc, tmkphy, name, d_x, st, total, steps, warmup, hbm, n_parity
     ms, stage, _ = dec.timed(steps, warmup)
     res = {"workload": name, "msamples_per_s": total * steps / (ms * 1e-3) / 1e6, "ms_per_step": ms / steps,
            "stage_ms": {k: round(v, 4) for k, v in stage.items()},
-           "frac_hbm": 4.0 * total / (ms / steps * 1e-3) / 1e9 / hbm, "records": int(dec.nr.value)}
+           "frac_hbm": 4.0 * total / (ms / steps * 1e-3) / 1e9 / hbm, "records": int(dec.nr.value),
+           "walk_counters": eng.debug_counters()}
     dec.free()
     if orc is not None and n_parity:
         idx = np.unique(np.linspace(0, len(st) - 1, n_parity).astype(np.int64))

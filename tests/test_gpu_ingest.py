@@ -28,7 +28,9 @@ def test_synth_impairments_decode_bit_exact(engine, orc, kind):
         got, gpl = engine.decode_batch(x, st)
         helpers.assert_records_equal(got, gpl, want, wpl, f"synth {imp}", corr_tol=None)
         ok = int(np.isin(want["status"], (0, 4)).sum())
-        assert ok > 0.6 * len(truth), (imp, ok, len(truth))
+        # (the echoes put the preamble correlation near h0 = 0.93 +- its autocorrelation at the echo lags: with
+        #  multipath a good part of the frames stays below the 0.9 threshold, for the oracle and the engine alike)
+        assert ok > (0.25 if imp.get("multipath") else 0.6) * len(truth), (imp, ok, len(truth))
         if "drift_ppm" in imp:  # truth positions are rounded capture positions: detections sit within a sample of them
             t0 = truth[truth["stream"] == 0]["preamble_start"].astype(np.int64)
             d0 = want[(want["stream"] == 0) & np.isin(want["status"], (0, 4))]["preamble_start"].astype(np.int64)

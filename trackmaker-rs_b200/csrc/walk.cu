@@ -600,7 +600,7 @@ __device__ __forceinline__ tmk_frame_rec ld_spec(const tmk_frame_rec* p) {
 
 // speculative verdict record the cluster pass prepared for window wl of block bb (or TMK_ENT_INVALID)
 __device__ __noinline__ uint32_t lookup_spec(const Ctx& c, uint64_t bb, uint32_t wl) {
-    if (c.blk_ptr == nullptr || c.C != 0 || c.P > 255) return TMK_ENT_INVALID;
+    if (c.blk_ptr == nullptr || c.P > 255) return TMK_ENT_INVALID;
     if (c.blk_info[bb].w == 0.f) return TMK_ENT_INVALID;  // not on the cluster pass's list: never published
     const uint32_t ptr = wait_blk_ptr(c, bb);
     if (ptr == TMK_ENT_INVALID) return TMK_ENT_INVALID;
@@ -739,24 +739,50 @@ __device__ __noinline__ bool process_block(Ctx& c, uint64_t bb, uint64_t q, uint
 //             without replacing every term by the maximum, so a loud frame just before the seed does not
 //             loosen the bound of the quiet gap behind it
 //   emin_lo   lower bound of the window energies of the block's windows >= q
+//   pmax_in   bound on the window energies of the chain BEFORE this block (windows >= q)
+//   avail     samples fed so far (chunked feeding: the seed of a window depends on it)
 __device__ __noinline__ int fast_block(Ctx& c, uint64_t bb, uint64_t q, float4 info, float nb, float smax, float racc_end,
-                                       float racc_in, float efirst, float emin_lo, Detection* det) {
-    if (c.blk_ptr == nullptr || c.C != 0 || c.P > 255 || c.a_w != c.a_seed || c.a_err != 0.f) return 2;
+                                       float racc_in, float efirst, float emin_lo, float pmax_in, uint64_t avail,
+                                       Detection* det) {
+    if (c.blk_ptr == nullptr || c.P > 255 || c.a_w != c.a_seed || c.a_err != 0.f) return 2;
     const float silent = 0.5f * c.thr * c.thr * 1e-6f;
     if (info.y < silent) return 0;  // every window is gated or cannot reach the threshold (as in search())
     const uint64_t wb0 = bb * TMK_BLK;
     uint64_t wlast = wb0 + (TMK_BLK - 1);
     if (wlast >= c.nwin) wlast = c.nwin - 1;
     const uint64_t k_end = wlast - c.a_w;
+    const float dscan = 128.f * kU * nb;
+    // the bound of a window of energy S is  d_abs + d_rel * S
+    float d_abs, d_rel = 2.5f * kU;
+    uint32_t ptr = TMK_ENT_PENDING;
+    if (c.C != 0) {
+        // Chunked feeding: every process_samples call re-seeds the rolling energy (decoder.rs:133-136), so the chain
+        // of a window has at most C + P steps, all of them over windows in [q, w] (a search never starts before q).
+        // |E_ref - S| <= u (1.5 P + 2.2 k) max(window energies of the chain) growth: the maximum is bounded by
+        // `smax` for the whole block, or window by window by  pmax_in + mgain * S_w  where the cluster pass
+        // measured  mgain >= (largest window energy of the block up to w) / S_w.
+        uint64_t k = c.C + c.P + TMK_BLK;
+        if (k > k_end) k = k_end;
+        const float per = drift_bound(c.P, k, 0.f, 1.0f);  // bound per unit of the chain's largest window energy
+        d_abs = per * smax;
+        if (!(d_abs + dscan <= kTight * emin_lo) || !(d_abs <= 3.0e38f) || !(dscan <= 3.0e38f)) {
+            if (info.w == 0.f || !(pmax_in >= 0.f)) return 2;
+            ptr = wait_blk_ptr(c, bb);
+            if (ptr == TMK_ENT_INVALID) return 2;
+            const float mgain = __ldcg(c.blk_gain + bb);
+            const float hist = per * pmax_in;
+            const float rel = per * mgain + 2.5f * kU;
+            if (!(hist + dscan <= 0.5f * kTight * emin_lo) || !(rel <= 0.5f * kTight)) return 2;
+            d_abs = hist;
+            d_rel = rel;
+        }
+    } else {
     const float dmax = drift_bound(c.P, k_end, 0.f, smax);
     const float kf = float(k_end);
     const float growth = kf < 65536.f ? 1.01f : __expf(2.2f * kU * kf) * 1.01f;
     const float dsum = kU * (1.5f * float(c.P) * efirst + 2.2f * racc_end) * growth;
     const float d_end = fminf(dmax, dsum);  // both are rigorous; NaN in either falls through below
-    const float dscan = 128.f * kU * nb;
-    // the bound of a window of energy S is  d_abs + d_rel * S
-    float d_abs = d_end, d_rel = 2.5f * kU;
-    uint32_t ptr = TMK_ENT_PENDING;
+    d_abs = d_end;
     if (!(d_end + dscan <= kTight * emin_lo) || !(d_end <= 3.0e38f) || !(dscan <= 3.0e38f)) {
         // A block whose energy RISES (the quiet gap runs into a loud preamble) fails the test above only
         // because the drift at the END of the block is held against the energy at its START. Window by
@@ -771,6 +797,7 @@ __device__ __noinline__ int fast_block(Ctx& c, uint64_t bb, uint64_t q, float4 i
         if (!(hist + dscan <= 0.5f * kTight * emin_lo) || !(rel <= 0.5f * kTight)) return 2;
         d_abs = hist;
         d_rel = rel;
+    }
     }
     if (info.w == 0.f) return 0;
     if (ptr == TMK_ENT_PENDING) ptr = wait_blk_ptr(c, bb);
@@ -794,18 +821,19 @@ __device__ __noinline__ int fast_block(Ctx& c, uint64_t bb, uint64_t q, float4 i
             const float Dj = __shfl_sync(kFull, e.D, j);
             const float Ecj = __shfl_sync(kFull, e.Ec, j);
             const uint32_t sj = __shfl_sync(kFull, e.spec, j);
+            const uint64_t seedj = seed_for(c, wj, q, avail);  // == q for one-shot captures
             float corr;
             bool hit;
             if (dj == DEC_YES) {
                 corr = ex_corr(Dj, Ecj, c.pat->pe);
                 hit = true;
             } else {
-                hit = exact_window(c, wj, q, Dj, &corr);
+                hit = exact_window(c, wj, seedj, Dj, &corr);
             }
             if (hit) {
                 det->c = wj;
-                det->seed = q;
-                det->avail = c.N;
+                det->seed = seedj;
+                det->avail = avail_for(c, wj, avail);
                 det->corr = corr;
                 det->spec = sj;
                 return 1;
@@ -845,11 +873,11 @@ __device__ __noinline__ bool search(Ctx& c, uint64_t q, uint64_t avail, Detectio
         // bounds of the whole gap behind it, so it goes straight to the exact energies)
         int r = 2;
         if (!(i0.y > 8.f * i0.x)) {
-            r = fast_block(c, b0, q, i0, nb0, i0.y * 1.001f, racc, 0.f, efirst, i0.x - dscan0, det);
+            r = fast_block(c, b0, q, i0, nb0, i0.y * 1.001f, racc, 0.f, efirst, i0.x - dscan0, 0.f, avail, det);
             if (r == 1) return true;
             if (r == 0) runmax = i0.y * 1.001f;
         }
-        if (r == 2 && c.blk_ptr != nullptr && c.C == 0 && c.P <= 255) {
+        if (r == 2 && c.blk_ptr != nullptr && c.P <= 255) {
             // 2. exact energies of the windows [q, end of block] (one block load): sum, maximum, minimum
             block_prefix(c, b0);
             const uint32_t lo = uint32_t(q - b0 * TMK_BLK), hi = uint32_t(wl0 - b0 * TMK_BLK);
@@ -869,7 +897,7 @@ __device__ __noinline__ bool search(Ctx& c, uint64_t q, uint64_t avail, Detectio
             }
             eq = __shfl_sync(kFull, eq, 0);
             const float racc_x = es * 1.0001f;
-            r = fast_block(c, b0, q, i0, nb0, emx * 1.0001f, racc_x, 0.f, eq * 1.0001f, emn * 0.9999f, det);
+            r = fast_block(c, b0, q, i0, nb0, emx * 1.0001f, racc_x, 0.f, eq * 1.0001f, emn * 0.9999f, 0.f, avail, det);
             if (r == 1) return true;
             if (r == 0) {
                 runmax = emx * 1.0001f;
@@ -963,7 +991,7 @@ __device__ __noinline__ bool search(Ctx& c, uint64_t q, uint64_t avail, Detectio
             const float racc_end_j = racc + __shfl_sync(kFull, cincl, j);
             const float racc_in_j = racc_end_j - __shfl_sync(kFull, contrib, j);
             const int r = fast_block(c, b0 + j, q, ij, nbj, max_nan(pmax_j, ij.y * 1.001f), racc_end_j, racc_in_j, efirst,
-                                     ij.x - 128.f * kU * nbj, det);
+                                     ij.x - 128.f * kU * nbj, pmax_j, avail, det);
             if (r == 1) return true;
             if (r == 0) {
                 runmax = max_nan(pmax_j, ij.y * 1.001f);
@@ -1406,7 +1434,7 @@ cluster_kernel(const float* __restrict__ samples, const TmkStreamDev* __restrict
         Ctx c;
         init_ctx(c, samples, sd, patterns, blk_info, cand_bits, f, lane, warp);
         const uint64_t bb = uint64_t(gb) - sd.blk_base;
-        if (c.C != 0 || c.P > 255) {  // chunked feeding / long preambles keep the walk's own evaluation
+        if (c.P > 255) {  // long preambles keep the walk's own evaluation
             if (lane == 0) publish_blk(f.blk_ptr + gb, TMK_ENT_INVALID);
             continue;
         }
@@ -1446,7 +1474,22 @@ cluster_kernel(const float* __restrict__ samples, const TmkStreamDev* __restrict
         // Cheap form first: (sum of all window energies of the block) / (smallest one) bounds every ratio; only a
         // block with a strong contrast (a quiet gap running into a loud frame) needs the window-by-window maximum.
         float gain = 0.f;
-        {
+        if (c.C != 0) {
+            // chunked feeding (chains of at most C + P steps): fast_block bounds the largest window energy of a chain
+            // window by window with  mgain = max_w (largest window energy of the block up to w) / S_w
+            float carry = 0.f;
+#pragma unroll 1
+            for (uint32_t r = 0; r < TMK_BLK_WORDS; ++r) {
+                const uint32_t wl = r * 32 + lane;
+                const bool valid = wb0 + wl < c.nwin;
+                const float S = valid ? __double2float_rn(c.sc->Q[wl + c.P] - c.sc->Q[wl]) : 0.f;
+                const float pm = max_nan(warp_incl_scan_maxnan(S, lane), carry);
+                carry = __shfl_sync(kFull, pm, 31);
+                if (valid) gain = max_nan(gain, S > 0.f ? __fdiv_ru(pm * 1.0001f, S) : (S == 0.f ? __int_as_float(0x7f800000) : S));
+            }
+#pragma unroll
+            for (int o = 16; o > 0; o >>= 1) gain = max_nan(gain, __shfl_xor_sync(kFull, gain, o));
+        } else {
             float ssum = 0.f, smin = __int_as_float(0x7f800000);
             bool bad = false;
 #pragma unroll 1
@@ -1586,11 +1629,20 @@ walk_kernel(const float* __restrict__ samples, const TmkStreamDev* __restrict__ 
         }
         c.n_det++;
         avail = d.avail;
-        if (d.spec != TMK_ENT_INVALID && d.c + c.P - c.pat->sync_len - d.seed >= c.pat->margin) {
+        if (d.spec != TMK_ENT_INVALID && d.c + c.P - c.pat->sync_len - d.seed >= c.pat->margin &&
+            (d.avail >= c.N || d.avail >= d.c + c.P + c.pat->margin)) {
             // the cluster pass already refined, demodulated and checked the frame of this detection (its
             // refinement range [expect - margin, expect + margin] is the walk's because the search started at
-            // least `margin` samples before `expect`): link the verdict, payload bytes are in place
+            // least `margin` samples before `expect` and, with chunked feeding, the samples fed when the window
+            // was examined reach `expect + margin + sync_len`, decoder.rs:179-181): link the verdict, payload
+            // bytes are in place
             tmk_frame_rec r = ld_spec(c.spec + d.spec);
+            if (c.C != 0 && r.status != TMK_FRAME_TRUNCATED) {
+                // decode_frame waited for the header, then for the whole frame (decoder.rs:248-254, 289-297)
+                const bool hdr_only = r.status == TMK_FRAME_HDR_PARSE || r.status == TMK_FRAME_BAD_LEN;
+                const uint64_t need = r.frame_start + (hdr_only ? uint64_t(hs) : tmk_sfb(lc, spl, (TMK_PHY_HEADER_BYTES + uint64_t(r.len)) * 8));
+                while (avail < need && avail < c.N) avail = avail + c.C < c.N ? avail + c.C : c.N;
+            }
             unsigned long long slot = 0;
             if (c.lane == 0) slot = atomicAdd(&counters->n_recs, 1ull);
             slot = __shfl_sync(kFull, slot, 0);
