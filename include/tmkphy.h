@@ -165,12 +165,18 @@ int tmk_correlate(tmk_engine* e, const float* samples, uint64_t total_samples, c
 /* Diagnostic: the raw output of the preamble scan kernel (the candidate filter in front of the walk).
  * Blocks are TMK_SCAN_BLOCK windows; stream i owns blocks blk_base[i] .. blk_base[i] + ceil(nwin_i / block) - 1.
  * blk_info: 4 floats per block (min window energy, max window energy, max corr^2, #candidates);
- * cand_bits: TMK_SCAN_BLOCK / 32 words per block, bit w = window w of the block passed
+ * cand_bits: tmk_scan_block() / 32 words per block, bit w = window w of the block passed
  * corr >= threshold * 0.85 / 0.9. Host pointers only. */
-#define TMK_SCAN_BLOCK 480
+#define TMK_SCAN_BLOCK 512
+uint32_t tmk_scan_block(void); /* the block size this library was built with (TMK_SCAN_BLOCK; 480 in the A/B build of the round-1 scan) */
 int tmk_scan_probe(tmk_engine* e, const float* samples, uint64_t total_samples, const tmk_stream* streams,
                    uint32_t n_streams, float* blk_info, uint32_t* cand_bits, uint64_t block_cap, uint64_t* n_blocks,
                    uint64_t* blk_base);
+
+/* Diagnostic: the correlation numerators D(w) = sum_t x[w + t] p[t] of the scan filter for the shipped shapes
+ * (TF32 tensor-core products; within 2^-10 sum |x| of the exact value), dot_out[stream offset + w]. Host output. */
+int tmk_scan_dot_probe(tmk_engine* e, const float* samples, uint64_t total_samples, const tmk_stream* streams,
+                       uint32_t n_streams, float* dot_out);
 
 /* Diagnostic: the exact rolling window energy E_ref (decoder.rs:133-136, 224-233) of the windows[i] (ascending,
  * >= seed) for a search_for_preamble call entered at `seed`, through the very replay the walk uses when a

@@ -301,6 +301,7 @@ def test_scan_filter_contract(engine, orc, kind, spl, pb):
     caps.append(caps[1][:481 + len(orc.preamble(kind, spl, pb))])
     s, st = helpers.pack(caps, cfg, tmkphy)
     info, bits, base = engine.scan_probe(s, st)
+    B = engine.scan_block()
     pre = orc.preamble(kind, spl, pb).astype(np.float64)
     P = len(pre)
     thr_c = np.float32(0.9) * np.float32(0.9444444)
@@ -311,16 +312,16 @@ def test_scan_filter_contract(engine, orc, kind, spl, pb):
         cs = np.concatenate([[0.0], np.cumsum(x * x)])
         E = cs[P:] - cs[:-P]
         corr = np.where(E > 0, D / np.sqrt(np.maximum(E, 1e-300) * P), 0.0)
-        nb = (nwin + 479) // 480
+        nb = (nwin + B - 1) // B
         b0 = int(base[i])
-        got_bits = np.unpackbits(bits[b0:b0 + nb].view(np.uint8), bitorder="little").reshape(nb, 480 + 0)[:, :480].reshape(-1)[:nwin]
+        got_bits = np.unpackbits(bits[b0:b0 + nb].view(np.uint8), bitorder="little").reshape(nb, B)[:, :B].reshape(-1)[:nwin]
         must = corr >= thr_c * 1.002
         must_not = corr < thr_c * 0.998
         assert got_bits[must].all(), f"capture {i}: {(must & (got_bits == 0)).sum()} windows above the filter level are unmarked"
         assert not got_bits[must_not].any(), f"capture {i}: windows below the filter level are marked"
         for b in range(nb):
-            e = E[b * 480:(b + 1) * 480]
-            cc = corr[b * 480:(b + 1) * 480]
+            e = E[b * B:(b + 1) * B]
+            cc = corr[b * B:(b + 1) * B]
             emin, emax, rmax, ncand = info[b0 + b]
             tol = 1e-3 * e.max() + 1e-30
             assert abs(emin - e.min()) <= tol and abs(emax - e.max()) <= tol, (i, b, emin, e.min(), emax, e.max())
@@ -329,4 +330,4 @@ def test_scan_filter_contract(engine, orc, kind, spl, pb):
             assert rmax >= want_r * (1 - 2e-3) - 1e-6, (i, b, rmax, want_r)
             if e.min() >= 1e-3 * e.max():
                 assert rmax <= want_r * (1 + 2e-3) + 1e-6, (i, b, rmax, want_r)
-            assert ncand == got_bits[b * 480:(b + 1) * 480].sum()
+            assert ncand == got_bits[b * B:(b + 1) * B].sum()

@@ -63,6 +63,13 @@ void build_pattern(const tmk_phy_config& c, TmkPattern* p) {
     // sqrt of a sequential f32 sum of +-1 squares: exact integers, so sqrtf(P) (decoder.rs:46-50,167-171)
     p->pe = std::sqrt(float(p->P));
     p->sync_energy = std::sqrt(float(p->sync_len));
+    {   // the f32 quotient sum / spl is monotone in the sum: find where it crosses the 1e-6 gate of the NRZI decoder
+        const float dv = float(c.spl);
+        volatile float t = 1e-6f * dv;
+        while (float(t / dv) > 1e-6f) t = std::nextafterf(t, 0.0f);
+        while (!(float(t / dv) > 1e-6f)) t = std::nextafterf(t, 1.0f);
+        p->lev_thr = t;
+    }
 }
 
 // index of the pattern of `c` in the engine's table (uploads the table when it grows)
@@ -438,7 +445,9 @@ static int decode_batch_impl(tmk_engine* e, const void* samples_v, bool pcm16, u
 
     CK(cudaEventRecord(e->ev[1], e->stream));
     e->launches += tmk_launch_tile_dir(ds, n_streams, uint32_t(b.n_tiles), dtd, e->stream);
-    CK(cudaMemsetAsync(dcb, 0, sizeof(uint32_t) * TMK_BLK_WORDS * b.n_blocks, e->stream));
+#ifdef TMK_SCAN_ARM_A
+    CK(cudaMemsetAsync(dcb, 0, sizeof(uint32_t) * TMK_BLK_WORDS * b.n_blocks, e->stream));  // (the CUDA-core scan ORs its bits in)
+#endif
     CK(cudaMemsetAsync(dc, 0, sizeof(TmkCounters), e->stream));
     CK(cudaMemsetAsync(dnext, 0, sizeof(unsigned int) * (chunks.size() + 1), e->stream));
     if (use_fast) {
@@ -653,7 +662,9 @@ int tmk_correlate(tmk_engine* e, const float* samples, uint64_t total_samples, c
 int tmk_scan_probe(tmk_engine* e, const float* samples, uint64_t total_samples, const tmk_stream* streams,
                    uint32_t n_streams, float* blk_info, uint32_t* cand_bits, uint64_t block_cap, uint64_t* n_blocks,
                    uint64_t* blk_base) {
+#ifndef TMK_SCAN_ARM_A
     static_assert(TMK_SCAN_BLOCK == TMK_BLK, "header and kernels disagree on the scan block size");
+#endif
     if (!e || !samples || !streams || !blk_info || !cand_bits || !n_blocks || !blk_base)
         return fail(e, TMK_E_INVALID, "tmk_scan_probe: null argument");
     CK(cudaSetDevice(e->device));
@@ -680,10 +691,37 @@ int tmk_scan_probe(tmk_engine* e, const float* samples, uint64_t total_samples, 
     e->launches += tmk_launch_scan(static_cast<const float*>(d_samples), total_samples, ds, n_streams, dtd, 0,
                                    uint32_t(b.n_tiles), static_cast<const TmkPattern*>(e->d_patterns.p), b.kinds,
                                    static_cast<float4*>(e->d_blk_info.p), static_cast<uint32_t*>(e->d_cand.p), nullptr, nullptr,
-                                   e->stream);
+                                   e->stream, e->scan_dbg_dot);
     CK(cudaGetLastError());
     CK(cudaMemcpyAsync(blk_info, e->d_blk_info.p, sizeof(float4) * b.n_blocks, cudaMemcpyDeviceToHost, e->stream));
     CK(cudaMemcpyAsync(cand_bits, e->d_cand.p, sizeof(uint32_t) * TMK_BLK_WORDS * b.n_blocks, cudaMemcpyDeviceToHost, e->stream));
+    CK(cudaStreamSynchronize(e->stream));
+    return TMK_OK;
+}
+
+uint32_t tmk_scan_block(void) { return TMK_BLK; }
+
+// Diagnostic: the correlation numerators D(w) = sum_t x[w + t] p[t] the scan filter computed (TF32 tensor-core
+// products in the default build), dot_out[stream offset + w]; windows the filter does not cover stay 0.
+int tmk_scan_dot_probe(tmk_engine* e, const float* samples, uint64_t total_samples, const tmk_stream* streams,
+                       uint32_t n_streams, float* dot_out) {
+    if (!e || !samples || !streams || !dot_out) return fail(e, TMK_E_INVALID, "tmk_scan_dot_probe: null argument");
+    if (is_device_ptr(dot_out)) return fail(e, TMK_E_INVALID, "tmk_scan_dot_probe: host output only");
+    CK(cudaSetDevice(e->device));
+    Batch b;
+    int rc = prepare_batch(e, total_samples, streams, n_streams, &b);
+    if (rc != TMK_OK) return rc;
+    std::vector<float> info(4 * std::max<uint64_t>(1, b.n_blocks));
+    std::vector<uint32_t> bits(TMK_BLK_WORDS * std::max<uint64_t>(1, b.n_blocks));
+    std::vector<uint64_t> base(n_streams);
+    uint64_t nb = 0;
+    CK(e->d_misc2.reserve(total_samples * sizeof(float)));
+    CK(cudaMemsetAsync(e->d_misc2.p, 0, total_samples * sizeof(float), e->stream));
+    e->scan_dbg_dot = static_cast<float*>(e->d_misc2.p);
+    rc = tmk_scan_probe(e, samples, total_samples, streams, n_streams, info.data(), bits.data(), b.n_blocks, &nb, base.data());
+    e->scan_dbg_dot = nullptr;
+    if (rc != TMK_OK) return rc;
+    CK(cudaMemcpyAsync(dot_out, e->d_misc2.p, total_samples * sizeof(float), cudaMemcpyDeviceToHost, e->stream));
     CK(cudaStreamSynchronize(e->stream));
     return TMK_OK;
 }

@@ -42,6 +42,7 @@ struct tmk_engine {
         d_counters, d_samples, d_misc, d_misc2, d_next, d_cblk, d_blk_ptr, d_entries, d_spec, d_pool, d_link, d_pcm, d_frag;
     DevBuf d_ask_tab, d_ask_bits, d_ask_l2, d_ask_recs, d_ask_recs2;  // chirp+BPSK path (ask.cu)
     DevBuf d_comm, d_wav, d_wavdesc;  // staging of the counter all-reduce (comm.cu); raw WAV bytes + descriptors (wav.cu)
+    float* scan_dbg_dot = nullptr;    // set around tmk_scan_probe by tmk_scan_dot_probe (diagnostic)
     void* comm = nullptr;             // ncclComm_t (comm.cu), one per engine
     int comm_rank = 0, comm_world = 1;
     bool ask_ready = false;

@@ -19,6 +19,7 @@
 //    the window energy rolls (one FFMA in, one FFMA out).
 //  * nothing here is a dense contraction: no tensor cores, fp32 pipe + issue slots are the bound
 //    next to HBM (DESIGN.md has the instruction budget).
+#ifdef TMK_SCAN_ARM_A  // the default build runs the tensor-core scan (scan_tc.cu); this kernel is the A arm of the A/B
 #include "tmk_internal.cuh"
 
 namespace {
@@ -359,21 +360,6 @@ scan_fast_kernel(const float* __restrict__ samples, uint64_t total_samples, cons
     }
 }
 
-// stream that owns each scan tile (streams are sorted by tile_base)
-__global__ void tile_dir_kernel(const TmkStreamDev* __restrict__ streams, uint32_t n_streams, uint32_t n_tiles,
-                                uint32_t* __restrict__ tile_stream) {
-    const uint32_t tile = blockIdx.x * blockDim.x + threadIdx.x;
-    if (tile >= n_tiles) return;
-    uint32_t lo = 0, hi = n_streams - 1;
-    while (lo < hi) {
-        const uint32_t mid = (lo + hi + 1) >> 1;
-        if (streams[mid].tile_base <= tile) lo = mid; else hi = mid - 1;
-    }
-    // streams without tiles share their tile_base with the next one: lo is the last of them, and the
-    // only one that has tiles, because the search keeps the largest index with tile_base <= tile
-    tile_stream[tile] = lo;
-}
-
 template <int LC>
 void launch_fast(const float* samples, uint64_t total_samples, const TmkStreamDev* streams, const uint32_t* tile_stream,
                  uint32_t tile0, uint32_t n_tiles, const TmkPattern* patterns, float4* blk_info, uint32_t* cand_bits,
@@ -397,18 +383,13 @@ void launch_fast(const float* samples, uint64_t total_samples, const TmkStreamDe
 
 }  // namespace
 
-int tmk_launch_tile_dir(const TmkStreamDev* streams, uint32_t n_streams, uint32_t n_tiles, uint32_t* tile_stream,
-                        cudaStream_t st) {
-    if (n_tiles == 0) return 0;
-    tile_dir_kernel<<<(n_tiles + 255) / 256, 256, 0, st>>>(streams, n_streams, n_tiles, tile_stream);
-    return 1;
-}
-
 // kinds: bit 0 = some stream is 4B5B/3/2, bit 1 = Manchester/3/2, bit 2 = any other shape (generic kernel)
 int tmk_launch_scan(const float* samples, uint64_t total_samples, const TmkStreamDev* streams, uint32_t n_streams,
                     const uint32_t* tile_stream, uint32_t tile0, uint32_t n_tiles, const TmkPattern* patterns,
                     uint32_t kinds, float4* blk_info, uint32_t* cand_bits, uint32_t* cblk_list, unsigned int* cblk_count,
-                    cudaStream_t st) {
+                    cudaStream_t st, float* dbg_dot) {
+    (void)dbg_dot;
+    (void)n_streams;
     if (n_tiles == 0) return 0;
     int launches = 0;
     if (kinds & 1u) {
@@ -425,3 +406,4 @@ int tmk_launch_scan(const float* samples, uint64_t total_samples, const TmkStrea
                                                             cblk_list, cblk_count, st);
     return launches;
 }
+#endif  // TMK_SCAN_ARM_A

@@ -14,7 +14,27 @@
 namespace {
 
 constexpr int kThreads = 256;
-constexpr int kSmemX = TMK_TILE + TMK_MAX_P + 8;
+constexpr int kSubBlks = 8;                      // blocks per CTA: one warp per block
+constexpr int kSub = kSubBlks * TMK_BLK;         // windows per CTA (a scan tile is TMK_TILE_BLKS / kSubBlks of them)
+constexpr int kSubPerTile = TMK_TILE_BLKS / kSubBlks;
+static_assert(TMK_TILE_BLKS % kSubBlks == 0 && kSubBlks * 32 == kThreads, "sub-tiles of the generic scan");
+constexpr int kSmemX = kSub + TMK_MAX_P + 8;
+
+// stream that owns each scan tile (streams are sorted by tile_base)
+__global__ void tile_dir_kernel(const TmkStreamDev* __restrict__ streams, uint32_t n_streams, uint32_t n_tiles,
+                                uint32_t* __restrict__ tile_stream) {
+    const uint32_t tile = blockIdx.x * blockDim.x + threadIdx.x;
+    if (tile >= n_tiles) return;
+    uint32_t lo = 0, hi = n_streams - 1;
+    while (lo < hi) {
+        const uint32_t mid = (lo + hi + 1) >> 1;
+        if (streams[mid].tile_base <= tile) lo = mid; else hi = mid - 1;
+    }
+    // streams without tiles share their tile_base with the next one: lo is the last of them, and the
+    // only one that has tiles, because the search keeps the largest index with tile_base <= tile
+    tile_stream[tile] = lo;
+}
+
 
 __global__ void __launch_bounds__(kThreads)
 scan_generic_kernel(const float* __restrict__ samples, const TmkStreamDev* __restrict__ streams,
@@ -25,20 +45,21 @@ scan_generic_kernel(const float* __restrict__ samples, const TmkStreamDev* __res
     __shared__ float qs[kSmemX];   // box sums of spl squared samples
     __shared__ float lev[TMK_MAX_LEVELS];
 
-    const uint32_t tile = tile0 + blockIdx.x;
+    const uint32_t tile = tile0 + blockIdx.x / kSubPerTile;
     const TmkStreamDev sd = streams[tile_stream[tile]];
     const TmkPattern* pat = patterns + sd.pattern;
     if (pat->spl == 3 && pat->preamble_bytes == 2) return;  // scan_fast.cu owns the shipped shapes
     const uint32_t P = pat->P, L = pat->L, spl = pat->spl;
     const uint64_t n = sd.n_samples;
     const uint64_t nwin = n - P + 1;  // n >= P, otherwise the stream has no tiles
-    const uint64_t w0 = uint64_t(tile - sd.tile_base) * TMK_TILE;
+    const uint64_t w0 = uint64_t(tile - sd.tile_base) * TMK_TILE + uint64_t(blockIdx.x % kSubPerTile) * kSub;
+    if (w0 >= nwin) return;  // a sub-tile past the end of the stream
     const float* __restrict__ x = samples + sd.offset;
 
     for (uint32_t l = threadIdx.x; l < L; l += kThreads) lev[l] = pat->levels[l];
 
     // stage the tile (+ P - 1 halo) in shared memory: coalesced float4 loads, zero fill past the end
-    const uint32_t need = TMK_TILE + P - 1;
+    const uint32_t need = kSub + P - 1;
     for (uint32_t i = threadIdx.x * 4; i < need; i += kThreads * 4) {
         uint64_t g = w0 + i;
         float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
@@ -121,12 +142,19 @@ scan_generic_kernel(const float* __restrict__ samples, const TmkStreamDev* __res
 
 }  // namespace
 
+int tmk_launch_tile_dir(const TmkStreamDev* streams, uint32_t n_streams, uint32_t n_tiles, uint32_t* tile_stream,
+                        cudaStream_t st) {
+    if (n_tiles == 0) return 0;
+    tile_dir_kernel<<<(n_tiles + 255) / 256, 256, 0, st>>>(streams, n_streams, n_tiles, tile_stream);
+    return 1;
+}
+
 int tmk_launch_scan_generic(const float* samples, const TmkStreamDev* streams, const uint32_t* tile_stream,
                             uint32_t tile0, uint32_t n_tiles, const TmkPattern* patterns, float4* blk_info, uint32_t* cand_bits,
                             uint32_t* cblk_list, unsigned int* cblk_count,
                             cudaStream_t st) {
     if (n_tiles == 0) return 0;
-    scan_generic_kernel<<<n_tiles, kThreads, 0, st>>>(samples, streams, tile_stream, tile0, patterns, blk_info, cand_bits, cblk_list,
+    scan_generic_kernel<<<n_tiles * kSubPerTile, kThreads, 0, st>>>(samples, streams, tile_stream, tile0, patterns, blk_info, cand_bits, cblk_list,
                                                             cblk_count);
     return 1;
 }

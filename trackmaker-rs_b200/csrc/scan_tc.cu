@@ -1,0 +1,492 @@
+// scan_tc.cu — preamble scan for the reference's shipped constants (SAMPLES_PER_LEVEL = 3,
+// PREAMBLE_PATTERN_BYTES = 2; src/utils/consts.rs:30-34) on the 5th-generation tensor cores: the hot kernel of
+// the engine, one pass over HBM, 4 B per sample.
+//
+// It replaces the per-sample loop of PhyDecoder::search_for_preamble (src/phy/decoder.rs:138-147: P multiply-adds
+// + sqrt + divide per sample) as a FILTER (contract in scan_generic.cu): a candidate bit per window and
+// (min E, max E, max corr^2, #candidates) per block of 512 windows. The exact decision is taken later, only for
+// marked windows (walk.cu), so reduced precision here cannot change a result — which is what lets the sliding
+// +-1 correlation run as a banded-Toeplitz GEMM in TF32:
+//
+//   the capture is read as rows of 64 samples; a tile is 128 rows (8192 windows, 16 blocks).
+//   D[row r][offset n] = sum_t x[64 r + n + t] p[t]  =  sum_h  X_h (128 x 64)  .  T_h^T (64 x 64)
+//   X_h[r][k] = x[64 (r + h) + k]  (the tile's rows shifted by h rows),  T_h[n][k] = p[64 h + k - n]  (constant)
+//
+//   TMA      one 4-D tensor-map box per tile lands the rows in shared memory ALREADY in the canonical K-major
+//            core-matrix layout of tcgen05 (8 rows x 16 B), with the MMA row i = 8 a + b holding capture row
+//            16 b + a: "the next capture row" is then "+1 in a", a constant +SBO on the operand address, so X_1
+//            (X_2) is the same buffer with a shifted descriptor and every sample is staged once (the first one or
+//            two row groups of the next rows are the only duplicates, 6 %).
+//   UMMA     tcgen05.mma kind::tf32, M = 128, N = 64, K = 8 per instruction: 16 (4B5B, K = 128) or 20
+//            (Manchester, K = 160) instructions per tile, issued by one thread, accumulating in TMEM
+//            (2 accumulator stages of 64 columns).
+//   epilogue four warps read their TMEM lane quarter (tcgen05.ld 32x32b: one row = 64 consecutive windows per
+//            thread), roll the window energy out of the staged samples in fp32 (one FFMA in, one out), test
+//            D+^2 / E > P (0.85 thr / 0.9)^2 with rcp.approx, and reduce the block statistics. Candidate words are
+//            plain stores (a row owns two whole bitmap words): no atomics, no memset of the bitmap.
+//   The producer / MMA / epilogue roles are decoupled by mbarriers (4 shared-memory stages, 2 TMEM stages);
+//   CTAs are persistent, one per SM.
+//
+// TF32 keeps 10 mantissa bits of every sample (the +-1 pattern is exact): |D_tf32 - D| <= 2^-10 sum |x| <=
+// 2^-10 sqrt(P E), i.e. at most 0.1 % of the normalised correlation, inside the 0.9 % the walk leaves for the
+// filter's own error (kTight, walk.cu); max corr^2 is reported with that margin added.
+#ifndef TMK_SCAN_ARM_A
+#include <cuda.h>
+
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <vector>
+
+#include "tmk_internal.cuh"
+
+namespace {
+
+constexpr unsigned kFull = 0xffffffffu;
+constexpr int kRowLen = 64;                    // samples per row = window offsets per row (N)
+constexpr int kRows = 128;                     // rows per tile (M)
+static_assert(kRows * kRowLen == TMK_TILE && TMK_BLK == 8 * kRowLen && TMK_BLK_WORDS == 16, "tile geometry");
+constexpr int kStages = 4;                     // shared-memory stages (sample tiles in flight)
+constexpr int kAccStages = 2;                  // TMEM accumulator stages
+constexpr int kEpiWarps = 4;
+constexpr int kThreads = 32 * (2 + kEpiWarps);
+constexpr uint32_t kGroupBytes = 2048;         // one row group `a`: 16 chunks x 8 rows x 16 B
+constexpr uint32_t kIdesc = (1u << 4) | (2u << 7) | (2u << 10) | (uint32_t(kRowLen >> 3) << 17) | (uint32_t(kRows >> 4) << 24);
+
+template <int LC> struct Tc;
+// preamble levels of LineCode::generate_preamble(2) (line_coding.rs:13-21: 0x33 0x5A line coded), one char per level
+template <> struct Tc<TMK_LINE_4B5B> {
+    static constexpr int P = 60, kHalves = 2, kGroups = 17;  // K = 128: rows r, r + 1
+    static constexpr const char* kLevels = "--++-++--++--+-++-++";
+};
+template <> struct Tc<TMK_LINE_MANCHESTER> {
+    static constexpr int P = 96, kHalves = 3, kGroups = 18;  // K = 160: rows r, r + 1, first half of r + 2
+    static constexpr const char* kLevels = "+-+--+-++-+--+-++--++--+-++--++-";
+};
+constexpr int kMaxMaps = 8;           // one tensor map per window of 2^33 samples of the batch buffer
+struct TcMaps {
+    CUtensorMap m[kMaxMaps];
+};
+
+struct Smem {
+    // (dynamic shared memory, 1024-byte aligned) [stages x kGroups x 2048 | kHalves x 16 KB of T_h | ...]
+    uint64_t full[kStages], empty[kStages], tfull[kAccStages], tempty[kAccStages];
+    uint32_t tmem_base;
+    uint32_t pad_;
+    float4 stat[kAccStages][4][8];  // [acc stage][lane quarter][b]: half-block statistics
+};
+
+__device__ __forceinline__ uint32_t smem_u32(const void* p) { return uint32_t(__cvta_generic_to_shared(p)); }
+__device__ __forceinline__ void mbar_init(uint64_t* bar, uint32_t count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count) : "memory");
+}
+__device__ __forceinline__ void mbar_expect_tx(uint64_t* bar, uint32_t bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_arrive(uint64_t* bar) {
+    asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(bar)) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
+    asm volatile(
+        "{\n"
+        ".reg .pred p;\n"
+        "WAIT_%=:\n"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n"
+        "@p bra DONE_%=;\n"
+        "bra WAIT_%=;\n"
+        "DONE_%=:\n"
+        "}\n" ::"r"(smem_u32(bar)), "r"(parity) : "memory");
+}
+__device__ __forceinline__ float rcp_approx(float x) {
+    float r;
+    asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x));
+    return r;
+}
+// K-major, no swizzle: core matrices of 8 rows x 16 B; LBO = bytes between the two K halves of an instruction,
+// SBO = bytes between 8-row groups (cute::UMMA::SmemDescriptor: start >> 4 at [0,14), LBO >> 4 at [16,30),
+// SBO >> 4 at [32,46), version 1 at [46,48), layout type 0 at [61,64))
+__device__ __forceinline__ uint64_t umma_desc(uint32_t saddr, uint32_t lbo, uint32_t sbo) {
+    return uint64_t((saddr >> 4) & 0x3fffu) | (uint64_t((lbo >> 4) & 0x3fffu) << 16) | (uint64_t((sbo >> 4) & 0x3fffu) << 32) |
+           (1ull << 46);
+}
+__device__ __forceinline__ void umma_tf32(uint32_t tmem_d, uint64_t adesc, uint64_t bdesc, uint32_t idesc, uint32_t accumulate) {
+    asm volatile(
+        "{\n"
+        ".reg .pred p;\n"
+        "setp.ne.b32 p, %4, 0;\n"
+        "tcgen05.mma.cta_group::1.kind::tf32 [%0], %1, %2, %3, p;\n"
+        "}\n" ::"r"(tmem_d), "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate) : "memory");
+}
+__device__ __forceinline__ void umma_commit(uint64_t* bar) {
+    asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_u32(bar)) : "memory");
+}
+__device__ __forceinline__ void tmem_ld32(uint32_t taddr, float (&r)[32]) {
+    uint32_t u[32];
+    asm volatile(
+        "tcgen05.ld.sync.aligned.32x32b.x32.b32 "
+        "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, "
+        "%16, %17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31}, [%32];\n"
+        : "=r"(u[0]), "=r"(u[1]), "=r"(u[2]), "=r"(u[3]), "=r"(u[4]), "=r"(u[5]), "=r"(u[6]), "=r"(u[7]), "=r"(u[8]),
+          "=r"(u[9]), "=r"(u[10]), "=r"(u[11]), "=r"(u[12]), "=r"(u[13]), "=r"(u[14]), "=r"(u[15]), "=r"(u[16]),
+          "=r"(u[17]), "=r"(u[18]), "=r"(u[19]), "=r"(u[20]), "=r"(u[21]), "=r"(u[22]), "=r"(u[23]), "=r"(u[24]),
+          "=r"(u[25]), "=r"(u[26]), "=r"(u[27]), "=r"(u[28]), "=r"(u[29]), "=r"(u[30]), "=r"(u[31])
+        : "r"(taddr));
+    asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+#pragma unroll
+    for (int i = 0; i < 32; ++i) r[i] = __uint_as_float(u[i]);
+}
+
+struct RowStat {
+    float emin, emax, rmax;
+    uint32_t ncand;
+};
+
+template <int LC>
+__global__ void __launch_bounds__(kThreads, 1)
+scan_tc_kernel(const __grid_constant__ TcMaps maps, int n_maps, const float* __restrict__ samples,
+               uint64_t total_samples, const TmkStreamDev* __restrict__ streams, const uint32_t* __restrict__ tile_stream,
+               uint32_t tile0, uint32_t n_tiles, const TmkPattern* __restrict__ patterns, float4* __restrict__ blk_info,
+               uint32_t* __restrict__ cand_bits, uint32_t* __restrict__ cblk_list, unsigned int* __restrict__ cblk_count,
+               float* __restrict__ dbg_dot) {
+    using S = Tc<LC>;
+    constexpr int P = S::P;
+    constexpr uint32_t kStageBytes = S::kGroups * kGroupBytes;
+    constexpr uint32_t kTBytes = 16384;  // one T_h: 8 row groups x 2048 B
+    extern __shared__ uint8_t smem_dyn[];
+    uint8_t* smem_raw = smem_dyn + ((1024u - (smem_u32(smem_dyn) & 1023u)) & 1023u);
+    uint8_t* stage0 = smem_raw;
+    uint8_t* tmat = smem_raw + kStages * kStageBytes;
+    Smem& sm = *reinterpret_cast<Smem*>(tmat + S::kHalves * kTBytes);
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+
+    // ---- one-time setup: barriers, TMEM, the Toeplitz operands T_h[n][k] = p[64 h + k - n]
+    if (threadIdx.x == 0) {
+        for (int i = 0; i < kStages; ++i) {
+            mbar_init(&sm.full[i], 1);
+            mbar_init(&sm.empty[i], kEpiWarps);
+        }
+        for (int i = 0; i < kAccStages; ++i) {
+            mbar_init(&sm.tfull[i], 1);
+            mbar_init(&sm.tempty[i], kEpiWarps);
+        }
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    if (warp == 1) {
+        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(&sm.tmem_base)),
+                     "n"(kAccStages * kRowLen) : "memory");
+        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+    }
+    {
+        for (uint32_t i = threadIdx.x; i < uint32_t(S::kHalves) * 64 * 64; i += kThreads) {
+            const uint32_t h = i >> 12, n = (i >> 6) & 63, k = i & 63;
+            const int t = int(64 * h + k) - int(n);
+            const float v = (t >= 0 && t < P) ? (S::kLevels[t / 3] == '+' ? 1.0f : -1.0f) : 0.0f;
+            *reinterpret_cast<float*>(tmat + h * kTBytes + (n >> 3) * kGroupBytes + (k >> 2) * 128 + (n & 7) * 16 + (k & 3) * 4) = v;
+        }
+    }
+    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");  // T_h (generic stores) -> tensor-core reads (async proxy)
+    asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+    __syncthreads();
+    asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+    const uint32_t tmem_base = sm.tmem_base;
+
+    // every role walks the same sequence of tiles; `it` counts the tiles this CTA actually processes
+    auto tile_of = [&](uint32_t tl, TmkStreamDev& sd, uint64_t& w0) -> bool {
+        const uint32_t tile = tile0 + tl;
+        sd = streams[tile_stream[tile]];
+        const TmkPattern* pat = patterns + sd.pattern;
+        if (pat->line_code != LC || pat->spl != 3 || pat->preamble_bytes != 2) return false;  // another kernel's stream
+        w0 = uint64_t(tile - sd.tile_base) * TMK_TILE;
+        return true;
+    };
+
+    if (warp == 0) {
+        // ================================================================ producer: sample tiles -> shared memory
+        uint32_t it = 0;
+        for (uint32_t tl = blockIdx.x; tl < n_tiles; tl += gridDim.x) {
+            TmkStreamDev sd;
+            uint64_t w0;
+            if (!tile_of(tl, sd, w0)) continue;
+            const uint32_t s = it % kStages, ph = (it / kStages) & 1u;
+            ++it;
+            mbar_wait(&sm.empty[s], ph ^ 1u);
+            uint8_t* dst = stage0 + s * kStageBytes;
+            const uint64_t start = sd.offset + w0;  // first sample of the tile in the batch buffer
+            const uint64_t span = uint64_t(16 * 7 + S::kGroups) * kRowLen;  // samples the box reaches
+            const uint32_t mi = uint32_t(start >> 33);
+            const bool tma = mi < uint32_t(n_maps) && start + span <= total_samples;
+            if (tma) {
+                if (lane == 0) {
+                    mbar_expect_tx(&sm.full[s], kStageBytes);
+                    const int32_t c2 = int32_t((start - (uint64_t(mi) << 33)) >> 2);
+                    asm volatile(
+                        "cp.async.bulk.tensor.4d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4, %5, %6}], [%2];"
+                        ::"r"(smem_u32(dst)), "l"(reinterpret_cast<uint64_t>(&maps.m[mi])), "r"(smem_u32(&sm.full[s])), "r"(0), "r"(0),
+                        "r"(c2), "r"(0) : "memory");
+                }
+            } else {
+                // the last tiles of the buffer (the box would run past its end) and unsupported maps: the warp fills
+                // the same layout itself, zeros past the end
+                for (uint32_t g = lane; g < uint32_t(S::kGroups) * 128; g += 32) {
+                    const uint32_t a = g >> 7, kc = (g >> 3) & 15, b = g & 7;
+                    const uint64_t i0 = start + uint64_t(16 * b + a) * kRowLen + 4 * kc;
+                    float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
+                    if (i0 + 3 < total_samples) {
+                        v = __ldg(reinterpret_cast<const float4*>(samples + i0));
+                    } else {
+                        if (i0 < total_samples) v.x = samples[i0];
+                        if (i0 + 1 < total_samples) v.y = samples[i0 + 1];
+                        if (i0 + 2 < total_samples) v.z = samples[i0 + 2];
+                    }
+                    *reinterpret_cast<float4*>(dst + a * kGroupBytes + kc * 128 + b * 16) = v;
+                }
+                asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+                __syncwarp();
+                if (lane == 0) mbar_arrive(&sm.full[s]);
+            }
+            __syncwarp();
+        }
+    } else if (warp == 1) {
+        // ================================================================ MMA issuer
+        uint32_t it = 0;
+        for (uint32_t tl = blockIdx.x; tl < n_tiles; tl += gridDim.x) {
+            TmkStreamDev sd;
+            uint64_t w0;
+            if (!tile_of(tl, sd, w0)) continue;
+            const uint32_t s = it % kStages, ph = (it / kStages) & 1u;
+            const uint32_t t = it % kAccStages, tph = (it / kAccStages) & 1u;
+            ++it;
+            mbar_wait(&sm.full[s], ph);
+            mbar_wait(&sm.tempty[t], tph ^ 1u);
+            asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+            if (lane == 0) {
+                const uint32_t a0 = smem_u32(stage0 + s * kStageBytes), b0 = smem_u32(tmat);
+                const uint32_t d = tmem_base + t * kRowLen;
+                uint32_t acc = 0;
+#pragma unroll
+                for (int h = 0; h < S::kHalves; ++h) {
+                    const int ksteps = (P + 63 - 64 * h) >= 64 ? 8 : (P + 63 - 64 * h + 7) / 8;  // taps reach k < P + 63
+#pragma unroll
+                    for (int kk = 0; kk < ksteps; ++kk) {
+                        umma_tf32(d, umma_desc(a0 + h * kGroupBytes + kk * 256, 128, kGroupBytes),
+                                  umma_desc(b0 + h * kTBytes + kk * 256, 128, kGroupBytes), kIdesc, acc);
+                        acc = 1;
+                    }
+                }
+                umma_commit(&sm.tfull[t]);
+            }
+            __syncwarp();
+        }
+    } else {
+        // ================================================================ epilogue: energy, candidate test, block statistics
+        const int q = warp & 3;            // TMEM lane quarter of this warp
+        const int m = 32 * q + lane;       // MMA row = TMEM lane
+        const int a = m >> 3, b = m & 7;
+        const int rho = 16 * b + a;        // capture row of the tile
+        uint32_t it = 0;
+        for (uint32_t tl = blockIdx.x; tl < n_tiles; tl += gridDim.x) {
+            TmkStreamDev sd;
+            uint64_t w0;
+            if (!tile_of(tl, sd, w0)) continue;
+            const uint32_t s = it % kStages, ph = (it / kStages) & 1u;
+            const uint32_t t = it % kAccStages, tph = (it / kAccStages) & 1u;
+            ++it;
+            const uint64_t nwin = sd.n_samples - P + 1;
+            const float thr_c = sd.threshold * TMK_CAND_RATIO;
+            const float kap = thr_c * thr_c * float(P);
+            const uint64_t wrow = w0 + uint64_t(rho) * kRowLen;  // first window of this thread's row
+            const int nvalid = wrow >= nwin ? 0 : (nwin - wrow < uint64_t(kRowLen) ? int(nwin - wrow) : kRowLen);
+            mbar_wait(&sm.full[s], ph);   // the samples are visible to this thread
+            mbar_wait(&sm.tfull[t], tph);  // the dot products are in TMEM
+            asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+            const uint8_t* row = stage0 + s * kStageBytes + a * kGroupBytes + b * 16;  // chunk c of the row (and the rows behind it)
+            auto chunk = [&](int c) -> float4 {  // samples 4 c .. 4 c + 3 counted from the row start
+                return *reinterpret_cast<const float4*>(row + (c >> 4) * kGroupBytes + (c & 15) * 128);
+            };
+            // energy of the row's first window
+            float e = 0.0f;
+#pragma unroll
+            for (int c = 0; c < P / 4; ++c) {
+                const float4 v = chunk(c);
+                e = fmaf(v.x, v.x, e);
+                e = fmaf(v.y, v.y, e);
+                e = fmaf(v.z, v.z, e);
+                e = fmaf(v.w, v.w, e);
+            }
+            RowStat o{__int_as_float(0x7f800000), 0.0f, 0.0f, 0u};
+            uint32_t mask[2] = {0u, 0u};
+            const float nanv = __int_as_float(0x7fc00000);
+#pragma unroll
+            for (int half = 0; half < 2; ++half) {
+                float D[32];
+                tmem_ld32(tmem_base + (uint32_t(32 * q) << 16) + t * kRowLen + 32 * half, D);
+                if (half == 1) {  // both halves are in registers / consumed: the accumulator stage is free again
+                    asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+                    __syncwarp();
+                    if (lane == 0) mbar_arrive(&sm.tempty[t]);
+                }
+                if (dbg_dot != nullptr)
+                    for (int j = 0; j < 32; ++j)
+                        if (32 * half + j < nvalid) dbg_dot[sd.offset + wrow + 32 * half + j] = D[j];
+                uint32_t mk = 0;
+#pragma unroll
+                for (int c4 = 0; c4 < 8; ++c4) {
+                    const float4 xo = chunk(8 * half + c4), xi = chunk(8 * half + c4 + P / 4);
+                    const float xov[4] = {xo.x, xo.y, xo.z, xo.w}, xiv[4] = {xi.x, xi.y, xi.z, xi.w};
+#pragma unroll
+                    for (int u = 0; u < 4; ++u) {
+                        const int j = 4 * c4 + u, n = 32 * half + j;
+                        const float Dv = D[j];
+                        const bool valid = n < nvalid;
+                        // a NaN / inf dot product (a NaN or inf sample anywhere in the row pair) must stay visible in max E
+                        const float Es = fmaf(Dv, 0.0f, e);
+                        const float Ev = valid ? Es : nanv;  // NaN: ignored by fminf / fmaxf, never a candidate
+                        const float dp = fmaxf(Dv, 0.0f);
+                        const float r = dp * dp * rcp_approx(Ev);  // P * corr^2 (NaN for silence: never a candidate)
+                        o.emin = fminf(o.emin, Ev);
+                        o.emax = max_nan(o.emax, valid ? Es : 0.0f);
+                        o.rmax = fmaxf(o.rmax, r);
+                        if (r > kap) mk |= 1u << j;
+                        e = fmaf(xiv[u], xiv[u], e);    // x[n + P] enters
+                        e = fmaf(-xov[u], xov[u], e);   // x[n] leaves
+                    }
+                }
+                mask[half] = mk;
+                o.ncand += __popc(mk);
+            }
+            // ---- the staged samples are no longer needed
+            __syncwarp();
+            if (lane == 0) mbar_arrive(&sm.empty[s]);
+            // ---- candidate words: the row owns words 2 (rho % 8), 2 (rho % 8) + 1 of its block
+            const uint64_t blk0 = sd.blk_base + w0 / TMK_BLK;
+            const uint32_t blk = uint32_t(rho) >> 3;
+            const bool blk_exists = w0 + uint64_t(blk) * TMK_BLK < nwin;
+            if (blk_exists) {
+                uint2* wp = reinterpret_cast<uint2*>(cand_bits + (blk0 + blk) * TMK_BLK_WORDS + 2 * (rho & 7));
+                *wp = make_uint2(mask[0], mask[1]);
+            }
+            // ---- block statistics: the four rows a = 4 q .. 4 q + 3 of one b are half a block (lanes b, b + 8, b + 16, b + 24)
+            float ncf = float(o.ncand);
+#pragma unroll
+            for (int sft = 8; sft <= 16; sft <<= 1) {
+                o.emin = fminf(o.emin, __shfl_xor_sync(kFull, o.emin, sft));
+                o.emax = max_nan(o.emax, __shfl_xor_sync(kFull, o.emax, sft));
+                o.rmax = fmaxf(o.rmax, __shfl_xor_sync(kFull, o.rmax, sft));
+                ncf += __shfl_xor_sync(kFull, ncf, sft);
+            }
+            if (lane < 8) sm.stat[t][q][lane] = make_float4(o.emin, o.emax, o.rmax, ncf);
+            asm volatile("bar.sync 1, %0;" ::"n"(kEpiWarps * 32) : "memory");
+            if ((q & 1) == 0 && lane < 8) {  // quarters (0, 1) hold block 2 b, quarters (2, 3) block 2 b + 1
+                const float4 u = sm.stat[t][q][lane], v = sm.stat[t][q + 1][lane];
+                const uint32_t bk = 2 * uint32_t(lane) + (q >> 1);
+                if (w0 + uint64_t(bk) * TMK_BLK < nwin) {
+                    const float nc = u.w + v.w;
+                    // max corr^2 with the TF32 margin (see the header): 2 x 2^-10 of it, rounded up
+                    const float rm = fmaxf(u.z, v.z) * (1.0f / float(P)) * 1.0015f;
+                    blk_info[blk0 + bk] = make_float4(fminf(u.x, v.x), max_nan(u.y, v.y), rm, nc);
+                    if (nc > 0.f && cblk_list) cblk_list[atomicAdd(cblk_count, 1u)] = uint32_t(blk0 + bk);
+                }
+            }
+            // (stat[t] is rewritten two tiles later, behind the next tile's barrier: no second barrier needed)
+        }
+    }
+    __syncthreads();
+    if (warp == 1) {
+        asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "n"(kAccStages * kRowLen) : "memory");
+    }
+}
+
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*,
+                                  const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
+                                  CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+EncodeTiledFn encode_fn() {
+    static EncodeTiledFn fn = nullptr;
+    static bool tried = false;
+    if (!tried) {
+        tried = true;
+        void* p = nullptr;
+        cudaDriverEntryPointQueryResult qr;
+        if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &qr) == cudaSuccess &&
+            qr == cudaDriverEntryPointSuccess)
+            fn = reinterpret_cast<EncodeTiledFn>(p);
+        cudaGetLastError();
+    }
+    return fn;
+}
+
+// the box of one tile: (4 floats) x (8 rows b, 16 capture rows apart) x (16 chunks of a row) x (row groups a)
+bool make_map(CUtensorMap* map, const float* base, uint64_t n_samples, int groups) {
+    EncodeTiledFn fn = encode_fn();
+    if (fn == nullptr || getenv("TMK_SCAN_NO_TMA")) return false;
+    uint64_t chunks = n_samples / 4;
+    if (chunks == 0) return false;
+    if (chunks > 0xffffffffull) chunks = 0xffffffffull;
+    const cuuint64_t gdim[4] = {4, 8, chunks, cuuint64_t(groups)};
+    const cuuint64_t gstr[3] = {16 * kRowLen * 4, 16, kRowLen * 4};
+    const cuuint32_t box[4] = {4, 8, 16, cuuint32_t(groups)};
+    const cuuint32_t estr[4] = {1, 1, 1, 1};
+    const CUresult rc = fn(map, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 4, const_cast<float*>(base), gdim, gstr, box, estr,
+                           CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                           CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (rc != CUDA_SUCCESS) {
+        static bool said = false;
+        if (!said) fprintf(stderr, "libtmkphy: cuTensorMapEncodeTiled failed (%d): the scan stages its tiles without TMA\n", int(rc));
+        said = true;
+        return false;
+    }
+    return true;
+}
+
+template <int LC>
+int launch_tc(const float* samples, uint64_t total_samples, const TmkStreamDev* streams, const uint32_t* tile_stream,
+              uint32_t tile0, uint32_t n_tiles, const TmkPattern* patterns, float4* blk_info, uint32_t* cand_bits,
+              uint32_t* cblk_list, unsigned int* cblk_count, float* dbg_dot, cudaStream_t st) {
+    using S = Tc<LC>;
+    static int sms = 0;
+    const size_t smem = size_t(kStages) * S::kGroups * kGroupBytes + size_t(S::kHalves) * 16384 + sizeof(Smem) + 1024;
+    if (sms == 0) {
+        int dev = 0;
+        cudaGetDevice(&dev);
+        cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+        cudaFuncSetAttribute(scan_tc_kernel<LC>, cudaFuncAttributeMaxDynamicSharedMemorySize, int(smem));
+    }
+    // one tensor map per window of 2^33 samples (the box coordinate is a 32-bit index of 16-byte chunks); a tile is
+    // loaded through the map of the window its first sample lies in, which therefore reaches one tile past the window
+    TcMaps maps;
+    std::memset(&maps, 0, sizeof maps);
+    int n_maps = 0;
+    const uint64_t kWin = 1ull << 33;
+    for (uint64_t base = 0; base < total_samples && n_maps < kMaxMaps; base += kWin) {
+        uint64_t len = total_samples - base;
+        if (len > kWin + 16384) len = kWin + 16384;
+        if (!make_map(&maps.m[n_maps], samples + base, len, S::kGroups)) break;
+        ++n_maps;
+    }
+    const uint32_t grid = n_tiles < uint32_t(sms) ? n_tiles : uint32_t(sms);
+    scan_tc_kernel<LC><<<grid, kThreads, smem, st>>>(maps, n_maps, samples, total_samples, streams, tile_stream, tile0, n_tiles,
+                                                      patterns, blk_info, cand_bits, cblk_list, cblk_count, dbg_dot);
+    return 1;
+}
+
+}  // namespace
+
+// kinds: bit 0 = some stream is 4B5B/3/2, bit 1 = Manchester/3/2, bit 2 = any other shape (generic kernel)
+int tmk_launch_scan(const float* samples, uint64_t total_samples, const TmkStreamDev* streams, uint32_t n_streams,
+                    const uint32_t* tile_stream, uint32_t tile0, uint32_t n_tiles, const TmkPattern* patterns,
+                    uint32_t kinds, float4* blk_info, uint32_t* cand_bits, uint32_t* cblk_list, unsigned int* cblk_count,
+                    cudaStream_t st, float* dbg_dot) {
+    (void)n_streams;
+    if (n_tiles == 0) return 0;
+    int launches = 0;
+    if (kinds & 1u)
+        launches += launch_tc<TMK_LINE_4B5B>(samples, total_samples, streams, tile_stream, tile0, n_tiles, patterns, blk_info,
+                                             cand_bits, cblk_list, cblk_count, dbg_dot, st);
+    if (kinds & 2u)
+        launches += launch_tc<TMK_LINE_MANCHESTER>(samples, total_samples, streams, tile_stream, tile0, n_tiles, patterns,
+                                                   blk_info, cand_bits, cblk_list, cblk_count, dbg_dot, st);
+    if (kinds & 4u) launches += tmk_launch_scan_generic(samples, streams, tile_stream, tile0, n_tiles, patterns, blk_info, cand_bits,
+                                                            cblk_list, cblk_count, st);
+    return launches;
+}
+#endif  // !TMK_SCAN_ARM_A

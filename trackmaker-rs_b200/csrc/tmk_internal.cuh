@@ -16,11 +16,17 @@
 
 #include "../../include/tmkphy.h"
 
+#ifdef TMK_SCAN_ARM_A        // build of the round-1 CUDA-core scan (scan_fast.cu), kept for the A/B of DESIGN.md §3.1
 #define TMK_BLK 480          // windows per block (candidate bitmap / energy summary granularity):
                              // 4 lanes x 120 windows of the fast scan kernel, 15 whole bitmap words
 #define TMK_BLK_WORDS 15     // TMK_BLK / 32
 #define TMK_TILE_BLKS 8      // blocks per scan tile
-#define TMK_TILE (TMK_BLK * TMK_TILE_BLKS)  // 3840 windows per scan tile (one warp of the fast kernel)
+#else                        // tensor-core scan (scan_tc.cu): rows of 64 windows, 8 rows per block, 128 rows per tile
+#define TMK_BLK 512
+#define TMK_BLK_WORDS 16
+#define TMK_TILE_BLKS 16
+#endif
+#define TMK_TILE (TMK_BLK * TMK_TILE_BLKS)  // windows per scan tile
 #define TMK_MAX_P 1024       // longest supported preamble in samples
 #define TMK_MAX_LEVELS 512   // longest supported preamble in levels
 #define TMK_CAND_RATIO 0.9444444f  // candidate filter keeps corr_approx >= thr * (0.85 / 0.9)
@@ -37,6 +43,7 @@ struct TmkPattern {
     uint32_t hdr_samples;  // samples_for_bits(56)
     float pe;            // sqrt(sum p^2)           decoder.rs:46-50
     float sync_energy;   // sqrt(sum sync^2)        decoder.rs:167-171
+    float lev_thr;       // smallest level SUM s with fl(s / spl) > 1e-6f (line_coding.rs:268: |avg| > 1e-6 <=> |sum| >= lev_thr)
     float levels[TMK_MAX_LEVELS];  // +1/-1 per level
 };
 
@@ -147,7 +154,8 @@ int tmk_launch_tile_dir(const TmkStreamDev* streams, uint32_t n_streams, uint32_
 int tmk_launch_scan(const float* samples, uint64_t total_samples, const TmkStreamDev* streams, uint32_t n_streams,
                     const uint32_t* tile_stream, uint32_t tile0, uint32_t n_tiles, const TmkPattern* patterns,
                     uint32_t kinds, float4* blk_info, uint32_t* cand_bits, uint32_t* cblk_list, unsigned int* cblk_count,
-                    cudaStream_t st);  // cblk_list / cblk_count (nullable): global ids of the blocks with candidates
+                    cudaStream_t st, float* dbg_dot = nullptr);  // cblk_list / cblk_count (nullable): global ids of the blocks with candidates;
+                                                                 // dbg_dot (nullable): the filter's correlation numerators per window
 int tmk_launch_scan_generic(const float* samples, const TmkStreamDev* streams, const uint32_t* tile_stream,
                             uint32_t tile0, uint32_t n_tiles, const TmkPattern* patterns, float4* blk_info,
                             uint32_t* cand_bits, uint32_t* cblk_list, unsigned int* cblk_count, cudaStream_t st);

@@ -23,8 +23,13 @@ constexpr int kWarpsPerCta = 4;
 constexpr int kMaxFrameBytesCap = 1024;                 // cfg.max_frame_bytes upper limit
 constexpr int kByteBuf = TMK_PHY_HEADER_BYTES + kMaxFrameBytesCap + 9;
 constexpr int kQBuf = TMK_BLK + 256;                    // prefix sums of one block for P <= 255
+constexpr int kXsMaxP = 96;                             // longest preamble whose block samples are staged (shipped shapes: 60, 96)
+constexpr int kXs = TMK_BLK + kXsMaxP;
 constexpr float kU = 5.9604645e-8f;                     // 2^-24, unit roundoff of f32
 constexpr unsigned kFull = 0xffffffffu;
+// the scan kernels' window energies (fp32 FMA chains of at most P + 2 x 64 roundings from a strip / row start) are
+// within kScanErr x (largest window energy of the neighbourhood) of the exact sums
+constexpr float kScanErr = 256.f * kU;
 // A window outside the candidate bitmap has corr_approx < thr * TMK_CAND_RATIO; the reference can
 // only detect it if its rolling energy sits below (TMK_CAND_RATIO)^2 = 0.892 of the true window
 // energy. kTight is the share of the window energy the drift bound may use up before such a
@@ -38,7 +43,9 @@ struct alignas(16) WarpScratch {
     alignas(16) uint8_t bytes[kByteBuf];  // decoded frame bytes; staging of the replay during a search
     double Q[kQBuf + 1];
     int8_t pre[TMK_MAX_P];  // preamble samples (+1/-1 levels expanded by spl; x * +-1.0f is exact)
+    alignas(16) float xs[kXs];  // the samples of the block whose prefix sums are in Q (block_prefix), for P <= kXsMaxP
 };
+static_assert(sizeof(WarpScratch) * kWarpsPerCta + 64 * 16 * kWarpsPerCta + 256 <= 48 * 1024, "static shared memory of the walk / cluster kernels");
 
 // One scratch per warp, at namespace scope so that every access compiles to LDS / STS (through a pointer
 // handed from function to function the accesses are generic loads: slower, and on the long scoreboard).
@@ -114,6 +121,12 @@ __device__ __forceinline__ uint64_t seed_for(const Ctx& c, uint64_t w, uint64_t 
     return seed_for_slow(c.P, c.C, c.N, w, q);
 }
 
+// w * p for a preamble sample p = +-1.0f: exactly w with the sign flipped for p = -1 (what the f32 multiply returns,
+// signed zeros and NaN payloads included), without the int -> float conversion and the multiply
+__device__ __forceinline__ float mul_pm1(float w, int8_t p) {
+    return __uint_as_float(__float_as_uint(w) ^ (uint32_t(int32_t(p)) & 0x80000000u));
+}
+
 // compute_dot_product_avx (decoder.rs:381-417): 8 lanes of mul-then-add, lane l + lane l+4,
 // the 4 partials summed left to right from 0, then the len % 8 tail. Runs per thread.
 __device__ __noinline__ float dot_avx_order(const Ctx& c, const float* __restrict__ w) {
@@ -125,12 +138,38 @@ __device__ __noinline__ float dot_avx_order(const Ctx& c, const float* __restric
     uint32_t i = 0;
     for (; i + 8 <= P; i += 8) {
 #pragma unroll
-        for (int l = 0; l < 8; ++l) a[l] = ex_add(a[l], ex_mul(w[i + l], float(pre[i + l])));
+        for (int l = 0; l < 8; ++l) a[l] = ex_add(a[l], mul_pm1(w[i + l], pre[i + l]));
     }
     float s = 0.0f;
 #pragma unroll
     for (int l = 0; l < 4; ++l) s = ex_add(s, ex_add(a[l], a[l + 4]));
-    for (; i < P; ++i) s = ex_add(s, ex_mul(w[i], float(pre[i])));
+    for (; i < P; ++i) s = ex_add(s, mul_pm1(w[i], pre[i]));
+    return s;
+}
+
+// The same dot product for up to 4 windows at once, out of the block's staged samples (c.sc->xs, block_prefix):
+// the 8 lanes of group g = lane / 8 ARE the 8 AVX lanes of window wl[g], so the dependent chain is P / 8 adds
+// instead of P. wl: window offset inside the block (warp-uniform per group; groups beyond `n` idle).
+// Returns the dot product of the group's window on every lane of the group.
+__device__ __forceinline__ float dot_avx_coop(const Ctx& c, uint32_t wl_g, bool active) {
+    const uint32_t P = c.P;
+    const int l = c.lane & 7;
+    const int8_t* __restrict__ pre = c.sc->pre;
+    const float* __restrict__ w = c.sc->xs + wl_g;
+    float a = 0.0f;
+    uint32_t i = 0;
+    if (active)
+        for (; i + 8 <= P; i += 8) a = ex_add(a, mul_pm1(w[i + l], pre[i + l]));
+    i = P & ~7u;
+    // lane l + lane l + 4 (l < 4), then the four partials left to right from 0
+    const float hi = __shfl_down_sync(kFull, a, 4);
+    const float pr = ex_add(a, hi);
+    const int base = c.lane & ~7;
+    float s = 0.0f;
+#pragma unroll
+    for (int k = 0; k < 4; ++k) s = ex_add(s, __shfl_sync(kFull, pr, base + k));
+    if (active)
+        for (; i < P; ++i) s = ex_add(s, mul_pm1(w[i], pre[i]));
     return s;
 }
 
@@ -535,6 +574,12 @@ __device__ __noinline__ void block_prefix(Ctx& c, uint64_t bb) {
         double run = warp_incl_scan_add(tot, lane) - tot;  // exclusive
         double* Q = c.sc->Q;
         if (lane == 0) Q[0] = 0.0;
+        {   // the samples themselves (candidate dot products read them from here)
+            float* xs = c.sc->xs;
+#pragma unroll
+            for (int k = 0; k < kMaxK4; ++k)
+                if (uint32_t(k) < K4 && i0 + 4 * k + 4 <= uint32_t(kXs)) *reinterpret_cast<float4*>(xs + i0 + 4 * k) = v[k];
+        }
 #pragma unroll
         for (int k = 0; k < kMaxK4; ++k) {
             if (uint32_t(k) < K4) {
@@ -634,7 +679,7 @@ __device__ __noinline__ bool process_block(Ctx& c, uint64_t bb, uint64_t q, uint
     float nb = c.blk_info[bb].y;
     if (bb > 0) nb = max_nan(nb, c.blk_info[bb - 1].y);
     if (bb + 1 < c.nblk) nb = max_nan(nb, c.blk_info[bb + 1].y);
-    const float dscan = 128.f * kU * nb;
+    const float dscan = kScanErr * nb;
 
     // the block's candidate words: lane r holds word r (one load round instead of 15)
     const uint32_t myword = lane < TMK_BLK_WORDS ? c.cand_bits[bb * TMK_BLK_WORDS + lane] : 0u;
@@ -751,7 +796,7 @@ __device__ __noinline__ int fast_block(Ctx& c, uint64_t bb, uint64_t q, float4 i
     uint64_t wlast = wb0 + (TMK_BLK - 1);
     if (wlast >= c.nwin) wlast = c.nwin - 1;
     const uint64_t k_end = wlast - c.a_w;
-    const float dscan = 128.f * kU * nb;
+    const float dscan = kScanErr * nb;
     // the bound of a window of energy S is  d_abs + d_rel * S
     float d_abs, d_rel = 2.5f * kU;
     uint32_t ptr = TMK_ENT_PENDING;
@@ -865,7 +910,7 @@ __device__ __noinline__ bool search(Ctx& c, uint64_t q, uint64_t avail, Detectio
         if (b0 + 1 < c.nblk) nb0 = max_nan(nb0, c.blk_info[b0 + 1].y);
         uint64_t wl0 = b0 * TMK_BLK + (TMK_BLK - 1);
         if (wl0 >= c.nwin) wl0 = c.nwin - 1;
-        const float dscan0 = 128.f * kU * nb0;
+        const float dscan0 = kScanErr * nb0;
         // 1. summary only: every window >= q bounded by the block maximum (which the consumed frame may own)
         efirst = i0.y * 1.001f;
         racc = float(wl0 - q + 1) * i0.y * 1.001f;
@@ -959,7 +1004,7 @@ __device__ __noinline__ bool search(Ctx& c, uint64_t q, uint64_t avail, Detectio
                 dbi = fminf(dbi, kU * (1.5f * float(P) * efirst + 2.2f * (racc + cincl)) * growth);
                 dbe = fminf(dbe, kU * (1.5f * float(P) * efirst + 2.2f * (racc + cincl - contrib)) * growth);
             }
-            const float delta = dbi + 128.f * kU * nb + 2.5f * kU * info.y;
+            const float delta = dbi + kScanErr * nb + 2.5f * kU * info.y;
             // (1) no window of the block can reach the threshold even with the lowest possible E_ref:
             //     corr_ref^2 = corr_true^2 * S / E_ref  with  E_ref >= max(S - delta, 1e-6)
             float gain;  // upper bound of S / E_ref over the block
@@ -991,7 +1036,7 @@ __device__ __noinline__ bool search(Ctx& c, uint64_t q, uint64_t avail, Detectio
             const float racc_end_j = racc + __shfl_sync(kFull, cincl, j);
             const float racc_in_j = racc_end_j - __shfl_sync(kFull, contrib, j);
             const int r = fast_block(c, b0 + j, q, ij, nbj, max_nan(pmax_j, ij.y * 1.001f), racc_end_j, racc_in_j, efirst,
-                                     ij.x - 128.f * kU * nbj, pmax_j, avail, det);
+                                     ij.x - kScanErr * nbj, pmax_j, avail, det);
             if (r == 1) return true;
             if (r == 0) {
                 runmax = max_nan(pmax_j, ij.y * 1.001f);
@@ -1063,7 +1108,7 @@ __device__ __noinline__ uint64_t refine(const Ctx& c, const Detection& d) {
             const float* wp = staged ? xs + (j - lo) : x + j;
             for (uint32_t t = 0; t < sl; ++t) {
                 const float w = wp[t];
-                dot = ex_add(dot, ex_mul(w, float(c.sc->pre[P - sl + t])));
+                dot = ex_add(dot, mul_pm1(w, c.sc->pre[P - sl + t]));
                 we = ex_add(we, ex_mul(w, w));
             }
             corr = (we > 1e-6f && pat->sync_energy > 1e-6f) ? ex_div(dot, ex_mul(ex_sqrt(we), pat->sync_energy)) : 0.0f;
@@ -1090,33 +1135,64 @@ __device__ __noinline__ uint64_t refine(const Ctx& c, const Detection& d) {
 }
 
 // ---------------------------------------------------------------- line decode
-__constant__ int8_t c_dec5[32] = {  // decode_4b5b_symbol, line_coding.rs:157-180 (-1 = invalid)
-    -1, -1, -1, -1, -1, -1, -1, -1, -1, 1, 4, 5, -1, -1, 6, 7,
-    -1, -1, 8, 9, 2, 3, 10, 11, -1, -1, 12, 13, 14, 15, 0, -1};
+// decode_4b5b_symbol, line_coding.rs:157-180, as two packed tables: nibble of symbol s at bits 4 (s % 8) of
+// kDec5Nib[s / 8], validity at bit s of kDec5Valid
+constexpr int8_t kDec5[32] = {-1, -1, -1, -1, -1, -1, -1, -1, -1, 1, 4, 5, -1, -1, 6, 7,
+                              -1, -1, 8, 9, 2, 3, 10, 11, -1, -1, 12, 13, 14, 15, 0, -1};
+constexpr uint32_t dec5_nib_word(int w) {
+    uint32_t v = 0;
+    for (int k = 0; k < 8; ++k) v |= uint32_t(kDec5[8 * w + k] < 0 ? 0 : kDec5[8 * w + k]) << (4 * k);
+    return v;
+}
+constexpr uint32_t dec5_valid() {
+    uint32_t v = 0;
+    for (int k = 0; k < 32; ++k) v |= uint32_t(kDec5[k] >= 0) << k;
+    return v;
+}
+constexpr uint32_t kDec5Nib1 = dec5_nib_word(1), kDec5Nib2 = dec5_nib_word(2), kDec5Nib3 = dec5_nib_word(3);
+constexpr uint32_t kDec5Valid = dec5_valid();
+static_assert(dec5_nib_word(0) == 0 && kDec5Valid == 0x7CFCCE00u, "4B5B decode table");
+__device__ __forceinline__ int dec5(uint32_t sym) {  // nibble or -1
+    const uint32_t w = (sym >> 3) == 1 ? kDec5Nib1 : (sym >> 3) == 2 ? kDec5Nib2 : kDec5Nib3;
+    return ((kDec5Valid >> sym) & 1u) ? int((w >> (4 * (sym & 7))) & 15u) : -1;
+}
 
-// f32 mean of one level: sequential sum from 0, one divide (line_coding.rs:104-113, 258-261)
-__device__ __forceinline__ float level_mean(const float* __restrict__ s, uint32_t spl) {
+// f32 SUM of one level: sequential from 0 like the reference's mean (line_coding.rs:104-113, 258-261); the
+// division by spl is not performed here (see line_decode)
+__device__ __forceinline__ float level_sum(const float* __restrict__ s, uint32_t spl) {
     float acc = 0.0f;
     for (uint32_t i = 0; i < spl; ++i) acc = ex_add(acc, s[i]);
-    return ex_div(acc, float(spl));
+    return acc;
 }
 
 // LineCode::decode over the samples of `total_bits` bits starting at fs. Writes MSB-first packed
 // bytes (crc.rs:63-75) to c.sc->bytes and returns the number of bits decoded (4B5B stops at the
 // first invalid symbol, line_coding.rs:281-286).
+//
+// The reference decides on level MEANS avg = fl(sum / spl). The decisions only need
+//   Manchester (:115-119)   avg_a > avg_b
+//   4B5B + NRZI (:262-270)  last_avg * avg < 0   and   |avg| > 1e-6
+// and x -> fl(x / spl) is monotone, so they are taken on the level SUMS whenever that is provably the same:
+//   |avg| > 1e-6  <=>  |sum| >= lev_thr (the smallest sum whose quotient exceeds 1e-6, found on the host);
+//   the sign of last_avg * avg is the product of the signs unless the product can underflow to +-0, i.e. unless
+//   |sum| < 1e-30 (|last_avg| > 1e-6 always) — NaN sums fail the same test;
+//   sum_a > sum_b with a relative gap above 1e-6 (8 ulps) keeps avg_a > avg_b after both roundings.
+// Everything else (digital silence, NaN, near ties) takes the literal path with the IEEE divisions. The sums drop
+// the reference's leading `0.0 +`, which can only turn a -0.0 sum into +0.0: a zero mean decides the same either way.
 __device__ __noinline__ uint32_t line_decode(const Ctx& c, uint64_t fs, uint32_t total_bits) {
     const float* __restrict__ s = c.x + fs;
     const uint32_t spl = c.pat->spl;
+    const float dv = float(spl), lev_thr = c.pat->lev_thr;
     const int lane = c.lane;
     uint8_t* bytes = c.sc->bytes;
-    // level means are staged in shared memory (the prefix-sum buffer is idle during a decode):
+    // level sums are staged in shared memory (the prefix-sum buffer is idle during a decode):
     // pass 1 fills a chunk with independent loads in flight, pass 2 decides out of shared memory
     float* lev = reinterpret_cast<float*>(c.sc->Q);
     constexpr uint32_t kChunk = 1280;  // levels per chunk: 256 4B5B symbols = 128 bytes, 640 Manchester bits = 80 bytes
     static_assert(kChunk <= 2 * kQBuf && kChunk % 160 == 0 && kChunk % 64 == 0, "level chunk");
     const bool man = c.pat->line_code == TMK_LINE_MANCHESTER;
     const uint32_t nlev = man ? total_bits * 2 : (total_bits / 4) * 5;
-    float last = 1.0f;  // prev_level_avg restarts at 1.0 on every decode call (line_coding.rs:251)
+    float last = dv;  // prev_level_avg restarts at 1.0 on every decode call (line_coding.rs:251): the SUM whose mean is 1.0
     uint32_t nb = 0;
     for (uint32_t c0 = 0; c0 < nlev; c0 += kChunk) {
         const uint32_t nl = nlev - c0 < kChunk ? nlev - c0 : kChunk;
@@ -1140,12 +1216,12 @@ __device__ __noinline__ uint32_t line_decode(const Ctx& c, uint64_t fs, uint32_t
 #pragma unroll
                 for (int u = 0; u < kB; ++u) {
                     const uint32_t i = i0 + u * 32 + lane;
-                    if (i < nl) lev[i] = ex_div(ex_add(ex_add(ex_add(0.0f, a[u][0]), a[u][1]), a[u][2]), 3.0f);
+                    if (i < nl) lev[i] = ex_add(ex_add(a[u][0], a[u][1]), a[u][2]);
                 }
             }
         } else {
 #pragma unroll 2
-            for (uint32_t i = lane; i < nl; i += 32) lev[i] = level_mean(s + uint64_t(c0 + i) * spl, spl);
+            for (uint32_t i = lane; i < nl; i += 32) lev[i] = level_sum(s + uint64_t(c0 + i) * spl, spl);
         }
         __syncwarp();
         if (man) {
@@ -1157,7 +1233,9 @@ __device__ __noinline__ uint32_t line_decode(const Ctx& c, uint64_t fs, uint32_t
                 bool bit = false;
                 if (bi < nbit) {
                     const float2 ab = *reinterpret_cast<const float2*>(lev + 2 * bi);
-                    bit = !(ab.x > ab.y);
+                    const float m = fmaxf(fabsf(ab.x), fabsf(ab.y));
+                    if (fabsf(ab.x - ab.y) > 1e-6f * m && m >= 1e-30f && m <= 1e37f) bit = !(ab.x > ab.y);
+                    else bit = !(ex_div(ab.x, dv) > ex_div(ab.y, dv));
                 }
                 const uint32_t rev = __brev(__ballot_sync(kFull, bit));
                 if (lane < 4 && b0 + lane * 8 < nbit) bytes[(nb >> 3) + lane] = uint8_t(rev >> (24 - 8 * lane));
@@ -1174,28 +1252,55 @@ __device__ __noinline__ uint32_t line_decode(const Ctx& c, uint64_t fs, uint32_t
             const bool active = si < nsym;
             float v[5];
 #pragma unroll
-            for (int j = 0; j < 5; ++j) v[j] = active ? lev[5 * si + j] : 0.0f;
-            // the last level of this symbol with |avg| > 1e-6, if any (line_coding.rs:268-270)
+            for (int j = 0; j < 5; ++j) v[j] = active ? lev[5 * si + j] : 1.0f;
+            bool plain = true;  // every sum of the symbol is far from the underflow of last_avg * avg (and not NaN)
+#pragma unroll
+            for (int j = 0; j < 5; ++j) plain = plain && fabsf(v[j]) >= 1e-30f;
+            uint32_t sym = 0, hm;
             float mylast = 0.0f;
-            bool have = false;
+            if (__all_sync(kFull, plain)) {
+                // the last level of this symbol with |avg| > 1e-6, if any (line_coding.rs:268-270)
+                bool have = false;
 #pragma unroll
-            for (int j = 0; j < 5; ++j)
-                if (fabsf(v[j]) > 1e-6f) {
-                    mylast = v[j];
-                    have = true;
+                for (int j = 0; j < 5; ++j)
+                    if (fabsf(v[j]) >= lev_thr) {
+                        mylast = v[j];
+                        have = true;
+                    }
+                hm = __ballot_sync(kFull, have && active);
+                const uint32_t below = hm & ((1u << lane) - 1u);
+                const float pv = __shfl_sync(kFull, mylast, below ? 31 - __clz(below) : 0);
+                uint32_t lastbits = __float_as_uint(below ? pv : last);
+#pragma unroll
+                for (int j = 0; j < 5; ++j) {
+                    const uint32_t vb = __float_as_uint(v[j]);
+                    sym = (sym << 1) | ((lastbits ^ vb) >> 31);  // :262-266, first level = MSB
+                    if (fabsf(v[j]) >= lev_thr) lastbits = vb;
                 }
-            const uint32_t hm = __ballot_sync(kFull, have);
-            const uint32_t below = hm & ((1u << lane) - 1u);
-            const float pv = __shfl_sync(kFull, mylast, below ? 31 - __clz(below) : 0);
-            float lastv = below ? pv : last;
-            uint32_t sym = 0;
+            } else {
+                // literal: the means, their products, the 1e-6 gate
+                float av[5];
+                bool have = false;
 #pragma unroll
-            for (int j = 0; j < 5; ++j) {
-                sym = (sym << 1) | (ex_mul(lastv, v[j]) < 0.0f ? 1u : 0u);  // :262-266, first level = MSB
-                if (fabsf(v[j]) > 1e-6f) lastv = v[j];
+                for (int j = 0; j < 5; ++j) {
+                    av[j] = ex_div(v[j], dv);
+                    if (fabsf(av[j]) > 1e-6f) {
+                        mylast = v[j];
+                        have = true;
+                    }
+                }
+                hm = __ballot_sync(kFull, have && active);
+                const uint32_t below = hm & ((1u << lane) - 1u);
+                const float pv = __shfl_sync(kFull, mylast, below ? 31 - __clz(below) : 0);
+                float lastv = ex_div(below ? pv : last, dv);
+#pragma unroll
+                for (int j = 0; j < 5; ++j) {
+                    sym = (sym << 1) | (ex_mul(lastv, av[j]) < 0.0f ? 1u : 0u);
+                    if (fabsf(av[j]) > 1e-6f) lastv = av[j];
+                }
             }
             if (hm) last = __shfl_sync(kFull, mylast, 31 - __clz(hm));
-            const int nib = c_dec5[sym];
+            const int nib = dec5(sym);
             const uint32_t nsy = nsym - s0 < 32 ? nsym - s0 : 32;
             const uint32_t inv = __ballot_sync(kFull, active && nib < 0);
             const uint32_t nval = inv ? uint32_t(__ffs(inv) - 1) : nsy;  // stop at the first invalid symbol :281-286
@@ -1455,11 +1560,24 @@ cluster_kernel(const float* __restrict__ samples, const TmkStreamDev* __restrict
             e.D = 0.f;
             e.Ec = 0.f;
             e.spec = TMK_ENT_INVALID;
-            if (valid) {
-                e.D = dot_avx_order(c, c.x + w);
-                e.Ec = __double2float_rn(c.sc->Q[wl + c.P] - c.sc->Q[wl]);
-            }
+            if (valid) e.Ec = __double2float_rn(c.sc->Q[wl + c.P] - c.sc->Q[wl]);
             const uint32_t m = __ballot_sync(kFull, valid);
+            if (c.P > uint32_t(kXsMaxP)) {
+                if (valid) e.D = dot_avx_order(c, c.x + w);
+            } else
+            // exact AVX-order dot products, four candidate windows per round (8 lanes = the 8 AVX lanes of a window)
+            for (uint32_t rem = m; rem;) {
+                uint32_t t = rem;
+                for (int k = 0; k < (lane >> 3); ++k) t &= t - 1;  // this group's candidate: the (lane / 8)-th set bit
+                const float Dg = dot_avx_coop(c, r * 32 + (t ? uint32_t(__ffs(t) - 1) : 0u), t != 0);
+#pragma unroll
+                for (int k = 0; k < 4 && rem; ++k) {
+                    const int j = __ffs(rem) - 1;
+                    rem &= rem - 1;
+                    const float Dk = __shfl_sync(kFull, Dg, 8 * k);
+                    if (lane == j) e.D = Dk;
+                }
+            }
             const uint32_t idx = n_ent + __popc(m & ((1u << lane) - 1u));
             if (valid && idx < 64) ents[warp][idx] = e;
             n_ent += __popc(m);
@@ -1490,6 +1608,17 @@ cluster_kernel(const float* __restrict__ samples, const TmkStreamDev* __restrict
 #pragma unroll
             for (int o = 16; o > 0; o >>= 1) gain = max_nan(gain, __shfl_xor_sync(kFull, gain, o));
         } else {
+            // from the scan's summary alone: (windows of the block) x (largest energy) / (smallest energy) bounds every
+            // ratio; the scan's energies are within 128 u (neighbourhood maximum) of the exact ones
+            const float4 bi = c.blk_info[bb];
+            float nbm = bi.y;
+            if (bb > 0) nbm = max_nan(nbm, c.blk_info[bb - 1].y);
+            if (bb + 1 < c.nblk) nbm = max_nan(nbm, c.blk_info[bb + 1].y);
+            const float lo_e = bi.x - kScanErr * nbm;
+            const float quick = lo_e > 0.5f * bi.x ? __fdiv_ru(float(TMK_BLK) * (bi.y + kScanErr * nbm) * 1.001f, lo_e) : __int_as_float(0x7f800000);
+            if (quick <= 1.0e5f) gain = quick;
+        }
+        if (c.C == 0 && !(gain > 0.f)) {
             float ssum = 0.f, smin = __int_as_float(0x7f800000);
             bool bad = false;
 #pragma unroll 1

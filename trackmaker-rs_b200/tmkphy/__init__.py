@@ -354,17 +354,30 @@ class Engine:
         return out
 
     def scan_probe(self, samples, streams):
-        """raw scan-kernel output: (blk_info[n_blocks,4], cand_bits[n_blocks,15], blk_base[n_streams])"""
+        """raw scan-kernel output: (blk_info[n_blocks,4], cand_bits[n_blocks, block / 32], blk_base[n_streams]);
+        block = scan_block() windows"""
         s = np.ascontiguousarray(samples, dtype=np.float32)
         st = np.ascontiguousarray(streams, dtype=STREAM_DTYPE)
-        cap = int(sum((int(n) + 479) // 480 for n in st["n_samples"])) + 8 * len(st) + 8
+        blk = self.scan_block()
+        cap = int(sum((int(n) + blk - 1) // blk for n in st["n_samples"])) + 16 * len(st) + 16
         info = np.zeros((cap, 4), np.float32)
-        bits = np.zeros((cap, 15), np.uint32)
+        bits = np.zeros((cap, blk // 32), np.uint32)
         base = np.zeros(len(st), np.uint64)
         nb = C.c_uint64(0)
         self._check(self._lib.tmk_scan_probe(self._h, _ptr(s), s.size, _ptr(st), len(st), _ptr(info), _ptr(bits), cap,
                                              C.byref(nb), _ptr(base)))
         return info[:nb.value], bits[:nb.value], base
+
+    def scan_block(self):
+        return int(self._lib.tmk_scan_block())
+
+    def scan_dot_probe(self, samples, streams):
+        """the filter's correlation numerators per window (tmk_scan_dot_probe)"""
+        s = np.ascontiguousarray(samples, dtype=np.float32)
+        st = np.ascontiguousarray(streams, dtype=STREAM_DTYPE)
+        out = np.zeros(s.size, np.float32)
+        self._check(self._lib.tmk_scan_dot_probe(self._h, _ptr(s), s.size, _ptr(st), len(st), _ptr(out)))
+        return out
 
     def replay_probe(self, cfg, samples, seed, windows):
         """tmk_replay_probe -> (E_ref of the windows for a search entered at `seed`, counters dict)"""

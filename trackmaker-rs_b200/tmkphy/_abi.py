@@ -96,6 +96,8 @@ SYMBOLS = {
     "tmk_decode_batch": (C.c_int, [_vp, _vp, _u64, _vp, _u32, _vp, _u64, _pu64, _vp, _u64, _pu64]),
     "tmk_correlate": (C.c_int, [_vp, _vp, _u64, _vp, _u32, _vp]),
     "tmk_scan_probe": (C.c_int, [_vp, _vp, _u64, _vp, _u32, _vp, _vp, _u64, _pu64, _vp]),
+    "tmk_scan_block": (_u32, []),
+    "tmk_scan_dot_probe": (C.c_int, [_vp, _vp, _u64, _vp, _u32, _vp]),
     "tmk_replay_probe": (C.c_int, [_vp, _vp, _u64, _pcfg, _u64, _vp, _u32, _vp, _pu64]),
     "tmk_channel_busy": (C.c_int, [_vp, _vp, _u64, _vp, _u32, _vp]),
     "tmk_stats": (C.c_int, [_vp, _pu64]),
