@@ -167,7 +167,7 @@ int tmk_correlate(tmk_engine* e, const float* samples, uint64_t total_samples, c
  * blk_info: 4 floats per block (min window energy, max window energy, max corr^2, #candidates);
  * cand_bits: tmk_scan_block() / 32 words per block, bit w = window w of the block passed
  * corr >= threshold * 0.85 / 0.9. Host pointers only. */
-#define TMK_SCAN_BLOCK 512
+#define TMK_SCAN_BLOCK 256
 uint32_t tmk_scan_block(void); /* the block size this library was built with (TMK_SCAN_BLOCK; 480 in the A/B build of the round-1 scan) */
 int tmk_scan_probe(tmk_engine* e, const float* samples, uint64_t total_samples, const tmk_stream* streams,
                    uint32_t n_streams, float* blk_info, uint32_t* cand_bits, uint64_t block_cap, uint64_t* n_blocks,

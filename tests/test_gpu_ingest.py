@@ -51,9 +51,11 @@ def test_ask_synth_decodes_bit_exact(engine, orc):
     want = oracle_batch(orc, x, st)
     got = engine.ask_decode_batch(x, st)
     assert_ask_equal(got, want, "ask synth")
-    assert int(want["accepted"].sum()) > 0.9 * planted
-    ids = want[want["stream"] == 3]["id"]
-    assert list(ids[:5]) == [1, 2, 3, 4, 5]
+    # (frames follow each other after 0..200 samples like the reference's TX loop: the correlator restarts empty behind
+    #  a frame, ask.rs:717-723, so the receiver — the reference's included — loses about every other one)
+    assert int(want["accepted"].sum()) > 0.4 * planted
+    ids = want[(want["stream"] == 3) & (want["accepted"] == 1)]["id"].astype(int)
+    assert len(ids) > 3 and (np.diff(ids) > 0).all() and ids[0] <= 2  # ids count up along the capture
 
 
 def test_wav_ingest_formats(engine, orc):

@@ -199,7 +199,7 @@ void tmk_engine_destroy(tmk_engine* e) {
     cudaSetDevice(e->device);
     if (e->stream) cudaStreamSynchronize(e->stream);
     tmk_comm_destroy(e);
-    DevBuf* bufs[] = {&e->d_comm, &e->d_wav, &e->d_wavdesc, &e->d_tile_dir, &e->d_patterns, &e->d_streams, &e->d_blk_info, &e->d_cand, &e->d_recs_tmp, &e->d_rec_ord,
+    DevBuf* bufs[] = {&e->d_comm, &e->d_wav, &e->d_wavdesc, &e->d_tile_desc, &e->d_tile_dir, &e->d_patterns, &e->d_streams, &e->d_blk_info, &e->d_cand, &e->d_recs_tmp, &e->d_rec_ord,
                       &e->d_recs, &e->d_payload, &e->d_cnt, &e->d_base, &e->d_counters, &e->d_samples,
                       &e->d_misc, &e->d_misc2, &e->d_next, &e->d_cblk, &e->d_blk_ptr, &e->d_entries, &e->d_spec, &e->d_pool, &e->d_link, &e->d_pcm, &e->d_frag,
                       &e->d_ask_tab, &e->d_ask_bits, &e->d_ask_l2,
@@ -413,6 +413,7 @@ static int decode_batch_impl(tmk_engine* e, const void* samples_v, bool pcm16, u
 
     if (reinterpret_cast<uintptr_t>(dx) % 16 != 0) return fail(e, TMK_E_INVALID, "sample buffer must be 16-byte aligned");
     CK(e->d_tile_dir.reserve(sizeof(uint32_t) * std::max<uint64_t>(1, b.n_tiles)));
+    CK(e->d_tile_desc.reserve(tmk_scan_tile_desc_bytes(uint32_t(b.n_tiles)) + 64));
     uint32_t* dtd = static_cast<uint32_t*>(e->d_tile_dir.p);
 
     // record / payload scratch on the device: start from a guess, rerun the (cheap) walk if the
@@ -477,7 +478,8 @@ static int decode_batch_impl(tmk_engine* e, const void* samples_v, bool pcm16, u
         if (pcm16) e->launches += tmk_launch_pcm16_to_f32(dpcm + ch.lo, const_cast<float*>(dx) + ch.lo, ch.hi - ch.lo, e->stream);
         const TmkFast fast = fast_of(g, ch);
         e->launches += tmk_launch_scan(dx, total_samples, ds, n_streams, dtd, ch.t0, ch.t1 - ch.t0, dp, b.kinds, dbi, dcb,
-                                       const_cast<uint32_t*>(fast.cblk_list), fast.cblk_count, e->stream);
+                                       const_cast<uint32_t*>(fast.cblk_list), fast.cblk_count, e->stream,
+                                       static_cast<char*>(e->d_tile_desc.p) + tmk_scan_tile_desc_bytes(ch.t0) * (ch.t0 ? 1 : 0));
         if (chunks.size() == 1) CK(cudaEventRecord(e->ev[2], e->stream));
         uint8_t* dpay = pay_dev ? payload : static_cast<uint8_t*>(e->d_payload.p);
         // The walks / cluster passes of different chunks overlap each other and the later scans (high-priority
@@ -683,6 +685,7 @@ int tmk_scan_probe(tmk_engine* e, const float* samples, uint64_t total_samples, 
     CK(e->d_blk_info.reserve(sizeof(float4) * b.n_blocks));
     CK(e->d_cand.reserve(sizeof(uint32_t) * TMK_BLK_WORDS * b.n_blocks));
     CK(e->d_tile_dir.reserve(sizeof(uint32_t) * b.n_tiles));
+    CK(e->d_tile_desc.reserve(tmk_scan_tile_desc_bytes(uint32_t(b.n_tiles)) + 64));
     const TmkStreamDev* ds = static_cast<const TmkStreamDev*>(e->d_streams.p);
     uint32_t* dtd = static_cast<uint32_t*>(e->d_tile_dir.p);
     CK(cudaMemsetAsync(e->d_blk_info.p, 0, sizeof(float4) * b.n_blocks, e->stream));
@@ -691,7 +694,7 @@ int tmk_scan_probe(tmk_engine* e, const float* samples, uint64_t total_samples, 
     e->launches += tmk_launch_scan(static_cast<const float*>(d_samples), total_samples, ds, n_streams, dtd, 0,
                                    uint32_t(b.n_tiles), static_cast<const TmkPattern*>(e->d_patterns.p), b.kinds,
                                    static_cast<float4*>(e->d_blk_info.p), static_cast<uint32_t*>(e->d_cand.p), nullptr, nullptr,
-                                   e->stream, e->scan_dbg_dot);
+                                   e->stream, e->d_tile_desc.p, e->scan_dbg_dot);
     CK(cudaGetLastError());
     CK(cudaMemcpyAsync(blk_info, e->d_blk_info.p, sizeof(float4) * b.n_blocks, cudaMemcpyDeviceToHost, e->stream));
     CK(cudaMemcpyAsync(cand_bits, e->d_cand.p, sizeof(uint32_t) * TMK_BLK_WORDS * b.n_blocks, cudaMemcpyDeviceToHost, e->stream));

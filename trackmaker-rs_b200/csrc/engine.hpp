@@ -41,6 +41,7 @@ struct tmk_engine {
     DevBuf d_tile_dir, d_patterns, d_streams, d_blk_info, d_cand, d_recs_tmp, d_rec_ord, d_recs, d_payload, d_cnt, d_base,
         d_counters, d_samples, d_misc, d_misc2, d_next, d_cblk, d_blk_ptr, d_entries, d_spec, d_pool, d_link, d_pcm, d_frag;
     DevBuf d_ask_tab, d_ask_bits, d_ask_l2, d_ask_recs, d_ask_recs2;  // chirp+BPSK path (ask.cu)
+    DevBuf d_tile_desc;  // per-tile descriptors of the tensor-core scan (scan_tc.cu)
     DevBuf d_comm, d_wav, d_wavdesc;  // staging of the counter all-reduce (comm.cu); raw WAV bytes + descriptors (wav.cu)
     float* scan_dbg_dot = nullptr;    // set around tmk_scan_probe by tmk_scan_dot_probe (diagnostic)
     void* comm = nullptr;             // ncclComm_t (comm.cu), one per engine

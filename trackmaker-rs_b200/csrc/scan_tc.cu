@@ -4,19 +4,21 @@
 //
 // It replaces the per-sample loop of PhyDecoder::search_for_preamble (src/phy/decoder.rs:138-147: P multiply-adds
 // + sqrt + divide per sample) as a FILTER (contract in scan_generic.cu): a candidate bit per window and
-// (min E, max E, max corr^2, #candidates) per block of 512 windows. The exact decision is taken later, only for
+// (min E, max E, max corr^2, #candidates) per block of 256 windows. The exact decision is taken later, only for
 // marked windows (walk.cu), so reduced precision here cannot change a result — which is what lets the sliding
 // +-1 correlation run as a banded-Toeplitz GEMM in TF32:
 //
-//   the capture is read as rows of 64 samples; a tile is 128 rows (8192 windows, 16 blocks).
+//   the capture is read as rows of 64 samples; a tile is 128 rows (8192 windows, 32 blocks).
 //   D[row r][offset n] = sum_t x[64 r + n + t] p[t]  =  sum_h  X_h (128 x 64)  .  T_h^T (64 x 64)
 //   X_h[r][k] = x[64 (r + h) + k]  (the tile's rows shifted by h rows),  T_h[n][k] = p[64 h + k - n]  (constant)
 //
-//   TMA      one 4-D tensor-map box per tile lands the rows in shared memory ALREADY in the canonical K-major
-//            core-matrix layout of tcgen05 (8 rows x 16 B), with the MMA row i = 8 a + b holding capture row
-//            16 b + a: "the next capture row" is then "+1 in a", a constant +SBO on the operand address, so X_1
-//            (X_2) is the same buffer with a shifted descriptor and every sample is staged once (the first one or
-//            two row groups of the next rows are the only duplicates, 6 %).
+//   TMA      one 4-D tensor-map box per tile (128-byte rows, 128-byte swizzle) lands the rows in shared memory
+//            ALREADY in the canonical K-major SWIZZLE_128B layout of tcgen05, with the MMA row i = 8 a + b holding
+//            capture row 16 b + a: "the next capture row" is then "+1 in a", a constant +SBO on the operand
+//            address, so X_1 (X_2) is the same buffer with a shifted descriptor and every sample is staged once
+//            (the one or two row groups of the next rows are the only duplicates, 6 %). (A first version used the
+//            unswizzled core-matrix layout: its 16-byte box rows made 2176 TMA requests per tile and the kernel
+//            request-bound at 2.8 ms; 128-byte rows are 272.)
 //   UMMA     tcgen05.mma kind::tf32, M = 128, N = 64, K = 8 per instruction: 16 (4B5B, K = 128) or 20
 //            (Manchester, K = 160) instructions per tile, issued by one thread, accumulating in TMEM
 //            (2 accumulator stages of 64 columns).
@@ -45,12 +47,14 @@ namespace {
 constexpr unsigned kFull = 0xffffffffu;
 constexpr int kRowLen = 64;                    // samples per row = window offsets per row (N)
 constexpr int kRows = 128;                     // rows per tile (M)
-static_assert(kRows * kRowLen == TMK_TILE && TMK_BLK == 8 * kRowLen && TMK_BLK_WORDS == 16, "tile geometry");
-constexpr int kStages = 4;                     // shared-memory stages (sample tiles in flight)
-constexpr int kAccStages = 2;                  // TMEM accumulator stages
-constexpr int kEpiWarps = 4;
+static_assert(kRows * kRowLen == TMK_TILE && TMK_BLK == 4 * kRowLen && TMK_BLK_WORDS == 8, "tile geometry");
+constexpr int kTeams = 4;                      // epilogue teams of four warps (one per TMEM lane quarter); team = iteration % kTeams
+constexpr int kStages = kTeams;                // shared-memory stages (sample tiles in flight): one per team
+constexpr int kAccStages = kTeams;             // TMEM accumulator stages: one per team
+constexpr int kEpiWarps = 4 * kTeams;
 constexpr int kThreads = 32 * (2 + kEpiWarps);
-constexpr uint32_t kGroupBytes = 2048;         // one row group `a`: 16 chunks x 8 rows x 16 B
+constexpr uint32_t kGroupBytes = 2048;         // one row group `a`: two 128B-swizzle atoms (sample columns 0..31 | 32..63) of 8 rows x 128 B
+constexpr uint32_t kAtomBytes = 1024;
 constexpr uint32_t kIdesc = (1u << 4) | (2u << 7) | (2u << 10) | (uint32_t(kRowLen >> 3) << 17) | (uint32_t(kRows >> 4) << 24);
 
 template <int LC> struct Tc;
@@ -63,17 +67,46 @@ template <> struct Tc<TMK_LINE_MANCHESTER> {
     static constexpr int P = 96, kHalves = 3, kGroups = 18;  // K = 160: rows r, r + 1, first half of r + 2
     static constexpr const char* kLevels = "+-+--+-++-+--+-++--++--+-++--++-";
 };
-constexpr int kMaxMaps = 8;           // one tensor map per window of 2^33 samples of the batch buffer
+constexpr int kMaxMaps = 20;          // one tensor map per window of kMapWin samples of the batch buffer (int32 box coordinate)
+constexpr uint64_t kMapWin = (1ull << 31) - (1ull << 16);
 struct TcMaps {
     CUtensorMap m[kMaxMaps];
 };
+
+// what a role needs to know about a scan tile: one 32-byte load per tile instead of the chain
+// tile_stream -> stream -> pattern
+struct alignas(16) TileDesc {
+    uint64_t start;   // first sample of the tile in the batch buffer
+    uint64_t nwin;    // windows of the stream from the tile's first one on (0: a tile of another kernel)
+    uint64_t blk0;    // global index of the tile's first block
+    float thr;        // threshold of the stream
+    uint32_t kind;    // 1 = 4B5B / 3 / 2, 2 = Manchester / 3 / 2, 0 = any other shape
+};
+static_assert(sizeof(TileDesc) == 32, "tile descriptor");
+
+__global__ void tile_desc_kernel(const TmkStreamDev* __restrict__ streams, const uint32_t* __restrict__ tile_stream,
+                                 const TmkPattern* __restrict__ patterns, uint32_t tile0, uint32_t n_tiles,
+                                 TileDesc* __restrict__ out) {
+    const uint32_t tl = blockIdx.x * blockDim.x + threadIdx.x;
+    if (tl >= n_tiles) return;
+    const uint32_t tile = tile0 + tl;
+    const TmkStreamDev sd = streams[tile_stream[tile]];
+    const TmkPattern* pat = patterns + sd.pattern;
+    const uint64_t w0 = uint64_t(tile - sd.tile_base) * TMK_TILE;
+    TileDesc d;
+    d.start = sd.offset + w0;
+    d.nwin = sd.n_samples - pat->P + 1 - w0;
+    d.blk0 = sd.blk_base + w0 / TMK_BLK;
+    d.thr = sd.threshold;
+    d.kind = (pat->spl == 3 && pat->preamble_bytes == 2) ? (pat->line_code == TMK_LINE_4B5B ? 1u : 2u) : 0u;
+    out[tl] = d;
+}
 
 struct Smem {
     // (dynamic shared memory, 1024-byte aligned) [stages x kGroups x 2048 | kHalves x 16 KB of T_h | ...]
     uint64_t full[kStages], empty[kStages], tfull[kAccStages], tempty[kAccStages];
     uint32_t tmem_base;
     uint32_t pad_;
-    float4 stat[kAccStages][4][8];  // [acc stage][lane quarter][b]: half-block statistics
 };
 
 __device__ __forceinline__ uint32_t smem_u32(const void* p) { return uint32_t(__cvta_generic_to_shared(p)); }
@@ -102,12 +135,12 @@ __device__ __forceinline__ float rcp_approx(float x) {
     asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x));
     return r;
 }
-// K-major, no swizzle: core matrices of 8 rows x 16 B; LBO = bytes between the two K halves of an instruction,
-// SBO = bytes between 8-row groups (cute::UMMA::SmemDescriptor: start >> 4 at [0,14), LBO >> 4 at [16,30),
-// SBO >> 4 at [32,46), version 1 at [46,48), layout type 0 at [61,64))
-__device__ __forceinline__ uint64_t umma_desc(uint32_t saddr, uint32_t lbo, uint32_t sbo) {
-    return uint64_t((saddr >> 4) & 0x3fffu) | (uint64_t((lbo >> 4) & 0x3fffu) << 16) | (uint64_t((sbo >> 4) & 0x3fffu) << 32) |
-           (1ull << 46);
+// K-major, 128-byte swizzle: rows of 128 B (32 TF32 values of K), atoms of 8 rows (1024 B, 1024-byte aligned), the
+// 16-byte chunk j of row r stored at chunk j ^ (r % 8); SBO = bytes between 8-row groups; an instruction (K = 8)
+// starts 32 B further along the row (cute::UMMA::SmemDescriptor: start >> 4 at [0,14), LBO >> 4 at [16,30) — unused
+// for swizzled K-major, 1 —, SBO >> 4 at [32,46), version 1 at [46,48), layout type 2 = SWIZZLE_128B at [61,64))
+__device__ __forceinline__ uint64_t umma_desc(uint32_t saddr, uint32_t sbo) {
+    return uint64_t((saddr >> 4) & 0x3fffu) | (1ull << 16) | (uint64_t((sbo >> 4) & 0x3fffu) << 32) | (1ull << 46) | (2ull << 61);
 }
 __device__ __forceinline__ void umma_tf32(uint32_t tmem_d, uint64_t adesc, uint64_t bdesc, uint32_t idesc, uint32_t accumulate) {
     asm volatile(
@@ -141,17 +174,86 @@ struct RowStat {
     uint32_t ncand;
 };
 
+// one window of the epilogue. FULL: every window of the tile exists (no masking).
+template <bool FULL>
+__device__ __forceinline__ bool tc_window(float Dv, float e, float kap, bool valid, RowStat& o) {
+    const float dp = fmaxf(Dv, 0.0f);
+    if (FULL) {
+        const float r = dp * dp * rcp_approx(e);     // P * corr^2 (NaN for silence: never a candidate)
+        o.emin = fminf(o.emin, e);
+        o.emax = max_nan(o.emax, e);                 // a NaN energy stays visible in max E
+        o.rmax = fmaxf(o.rmax, r);
+        return r > kap;
+    }
+    const float Ev = valid ? e : __int_as_float(0x7fc00000);  // NaN: ignored by fminf / fmaxf, never a candidate
+    const float r = dp * dp * rcp_approx(Ev);
+    o.emin = fminf(o.emin, Ev);
+    o.emax = max_nan(o.emax, valid ? e : 0.0f);
+    o.rmax = fmaxf(o.rmax, r);
+    return r > kap;
+}
+
+// The 64 windows of one row: dot products from TMEM (two loads of 32 columns), the window energy rolled out of the
+// staged samples, candidate mask and row statistics. `row`: the thread's row in the stage (un-swizzle with b).
+template <int P, bool FULL>
+__device__ __forceinline__ void epi_row(const uint8_t* __restrict__ row, int b, uint32_t taddr, float kap, int nvalid,
+                                        uint64_t* tempty, int lane, float* __restrict__ dbg, RowStat& o, uint32_t (&mask)[2]) {
+    auto chunk = [&](int c) -> float4 {  // samples 4 c .. 4 c + 3 counted from the row start
+        return *reinterpret_cast<const float4*>(row + (c >> 4) * kGroupBytes + ((c >> 3) & 1) * kAtomBytes + (((c & 7) ^ b) << 4));
+    };
+    float e = 0.0f;  // energy of the row's first window
+#pragma unroll
+    for (int c = 0; c < P / 4; ++c) {
+        const float4 v = chunk(c);
+        e = fmaf(v.x, v.x, e);
+        e = fmaf(v.y, v.y, e);
+        e = fmaf(v.z, v.z, e);
+        e = fmaf(v.w, v.w, e);
+    }
+#pragma unroll
+    for (int half = 0; half < 2; ++half) {
+        float D[32];
+        tmem_ld32(taddr + 32 * half, D);
+        if (half == 1) {  // both halves are in registers: the accumulator stage is free again
+            asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+            __syncwarp();
+            if (lane == 0) mbar_arrive(tempty);
+        }
+        // a NaN / inf sample anywhere in the rows of this MMA row turns ALL its dot products into NaN (0 x NaN in
+        // the banded operand): one test per row keeps it visible in max E, like a NaN energy
+        if (half == 0 && nvalid > 0 && !(fabsf(D[0]) <= 3.0e38f)) o.emax = __int_as_float(0x7fc00000);
+        if (dbg != nullptr)
+            for (int j = 0; j < 32; ++j)
+                if (32 * half + j < nvalid) dbg[32 * half + j] = D[j];
+        uint32_t mk = 0;
+#pragma unroll
+        for (int c4 = 0; c4 < 8; ++c4) {
+            const float4 xo = chunk(8 * half + c4), xi = chunk(8 * half + c4 + P / 4);
+            const float xov[4] = {xo.x, xo.y, xo.z, xo.w}, xiv[4] = {xi.x, xi.y, xi.z, xi.w};
+#pragma unroll
+            for (int u = 0; u < 4; ++u) {
+                const int j = 4 * c4 + u;
+                if (tc_window<FULL>(D[j], e, kap, 32 * half + j < nvalid, o)) mk |= 1u << j;
+                e = fmaf(xiv[u], xiv[u], e);    // x[n + P] enters
+                e = fmaf(-xov[u], xov[u], e);   // x[n] leaves
+            }
+        }
+        mask[half] = mk;
+        o.ncand += __popc(mk);
+    }
+}
+
 template <int LC>
 __global__ void __launch_bounds__(kThreads, 1)
-scan_tc_kernel(const __grid_constant__ TcMaps maps, int n_maps, const float* __restrict__ samples,
-               uint64_t total_samples, const TmkStreamDev* __restrict__ streams, const uint32_t* __restrict__ tile_stream,
-               uint32_t tile0, uint32_t n_tiles, const TmkPattern* __restrict__ patterns, float4* __restrict__ blk_info,
+scan_tc_kernel(const __grid_constant__ TcMaps maps, int n_maps, const float* __restrict__ samples, uint64_t total_samples,
+               const TileDesc* __restrict__ tdesc, uint32_t n_tiles, float4* __restrict__ blk_info,
                uint32_t* __restrict__ cand_bits, uint32_t* __restrict__ cblk_list, unsigned int* __restrict__ cblk_count,
                float* __restrict__ dbg_dot) {
     using S = Tc<LC>;
     constexpr int P = S::P;
+    constexpr uint32_t kKind = LC == TMK_LINE_4B5B ? 1u : 2u;
     constexpr uint32_t kStageBytes = S::kGroups * kGroupBytes;
-    constexpr uint32_t kTBytes = 16384;  // one T_h: 8 row groups x 2048 B
+    constexpr uint32_t kTBytes = 16384;  // one T_h: column blocks c = 0, 1, each 8 atoms (64 rows n) of 1024 B
     extern __shared__ uint8_t smem_dyn[];
     uint8_t* smem_raw = smem_dyn + ((1024u - (smem_u32(smem_dyn) & 1023u)) & 1023u);
     uint8_t* stage0 = smem_raw;
@@ -163,11 +265,11 @@ scan_tc_kernel(const __grid_constant__ TcMaps maps, int n_maps, const float* __r
     if (threadIdx.x == 0) {
         for (int i = 0; i < kStages; ++i) {
             mbar_init(&sm.full[i], 1);
-            mbar_init(&sm.empty[i], kEpiWarps);
+            mbar_init(&sm.empty[i], 4);   // the four warps of the team that consumed the stage
         }
         for (int i = 0; i < kAccStages; ++i) {
             mbar_init(&sm.tfull[i], 1);
-            mbar_init(&sm.tempty[i], kEpiWarps);
+            mbar_init(&sm.tempty[i], 4);
         }
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
@@ -176,13 +278,12 @@ scan_tc_kernel(const __grid_constant__ TcMaps maps, int n_maps, const float* __r
                      "n"(kAccStages * kRowLen) : "memory");
         asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
     }
-    {
-        for (uint32_t i = threadIdx.x; i < uint32_t(S::kHalves) * 64 * 64; i += kThreads) {
-            const uint32_t h = i >> 12, n = (i >> 6) & 63, k = i & 63;
-            const int t = int(64 * h + k) - int(n);
-            const float v = (t >= 0 && t < P) ? (S::kLevels[t / 3] == '+' ? 1.0f : -1.0f) : 0.0f;
-            *reinterpret_cast<float*>(tmat + h * kTBytes + (n >> 3) * kGroupBytes + (k >> 2) * 128 + (n & 7) * 16 + (k & 3) * 4) = v;
-        }
+    for (uint32_t i = threadIdx.x; i < uint32_t(S::kHalves) * 64 * 64; i += kThreads) {
+        const uint32_t h = i >> 12, n = (i >> 6) & 63, k = i & 63;
+        const int t = int(64 * h + k) - int(n);
+        const float v = (t >= 0 && t < P) ? (S::kLevels[t / 3] == '+' ? 1.0f : -1.0f) : 0.0f;
+        const uint32_t c = k >> 5, kc = (k >> 2) & 7;
+        *reinterpret_cast<float*>(tmat + h * kTBytes + c * 8192 + (n >> 3) * kAtomBytes + (n & 7) * 128 + ((kc ^ (n & 7)) << 4) + (k & 3) * 4) = v;
     }
     asm volatile("fence.proxy.async.shared::cta;" ::: "memory");  // T_h (generic stores) -> tensor-core reads (async proxy)
     asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
@@ -190,39 +291,57 @@ scan_tc_kernel(const __grid_constant__ TcMaps maps, int n_maps, const float* __r
     asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
     const uint32_t tmem_base = sm.tmem_base;
 
-    // every role walks the same sequence of tiles; `it` counts the tiles this CTA actually processes
-    auto tile_of = [&](uint32_t tl, TmkStreamDev& sd, uint64_t& w0) -> bool {
-        const uint32_t tile = tile0 + tl;
-        sd = streams[tile_stream[tile]];
-        const TmkPattern* pat = patterns + sd.pattern;
-        if (pat->line_code != LC || pat->spl != 3 || pat->preamble_bytes != 2) return false;  // another kernel's stream
-        w0 = uint64_t(tile - sd.tile_base) * TMK_TILE;
-        return true;
+    // Every role walks the same sequence of tiles (tl = blockIdx.x, + gridDim.x, ...); `it` counts the tiles of THIS
+    // kernel's line code among them. The descriptor of the next tile is loaded while the current one is worked on.
+    auto load_desc = [&](uint32_t tl) -> TileDesc {
+        TileDesc d;
+        if (tl < n_tiles) {
+            const uint4* p = reinterpret_cast<const uint4*>(tdesc + tl);
+            const uint4 lo = __ldg(p), hi = __ldg(p + 1);
+            d.start = uint64_t(lo.x) | (uint64_t(lo.y) << 32);
+            d.nwin = uint64_t(lo.z) | (uint64_t(lo.w) << 32);
+            d.blk0 = uint64_t(hi.x) | (uint64_t(hi.y) << 32);
+            d.thr = __uint_as_float(hi.z);
+            d.kind = hi.w;
+        } else {
+            d.start = d.nwin = d.blk0 = 0;
+            d.thr = 0.f;
+            d.kind = 0;
+        }
+        return d;
     };
 
+    // Iteration j of a CTA is tile tl = blockIdx.x + j gridDim.x; team j % kTeams owns it, together with shared-memory
+    // stage and TMEM stage j % kTeams. Tiles of another kernel's line code are skipped by everybody; cnt[team] counts
+    // the tiles a team has processed (the phase of its barriers).
     if (warp == 0) {
         // ================================================================ producer: sample tiles -> shared memory
-        uint32_t it = 0;
-        for (uint32_t tl = blockIdx.x; tl < n_tiles; tl += gridDim.x) {
-            TmkStreamDev sd;
-            uint64_t w0;
-            if (!tile_of(tl, sd, w0)) continue;
-            const uint32_t s = it % kStages, ph = (it / kStages) & 1u;
-            ++it;
+        uint32_t cnt[kTeams] = {};
+        uint32_t j = 0;
+        TileDesc nxt = load_desc(blockIdx.x);
+        for (uint32_t tl = blockIdx.x; tl < n_tiles; tl += gridDim.x, ++j) {
+            const TileDesc td = nxt;
+            nxt = load_desc(tl + gridDim.x);
+            if (td.kind != kKind) continue;
+            const uint32_t s = j % kTeams;
+            uint32_t ph = 0;
+#pragma unroll
+            for (int k = 0; k < kTeams; ++k)
+                if (uint32_t(k) == s) ph = cnt[k]++ & 1u;
             mbar_wait(&sm.empty[s], ph ^ 1u);
             uint8_t* dst = stage0 + s * kStageBytes;
-            const uint64_t start = sd.offset + w0;  // first sample of the tile in the batch buffer
+            const uint64_t start = td.start;
             const uint64_t span = uint64_t(16 * 7 + S::kGroups) * kRowLen;  // samples the box reaches
-            const uint32_t mi = uint32_t(start >> 33);
+            const uint32_t mi = uint32_t(start / kMapWin);
             const bool tma = mi < uint32_t(n_maps) && start + span <= total_samples;
             if (tma) {
                 if (lane == 0) {
                     mbar_expect_tx(&sm.full[s], kStageBytes);
-                    const int32_t c2 = int32_t((start - (uint64_t(mi) << 33)) >> 2);
+                    const int32_t c0 = int32_t(start - uint64_t(mi) * kMapWin);  // in samples
                     asm volatile(
                         "cp.async.bulk.tensor.4d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4, %5, %6}], [%2];"
-                        ::"r"(smem_u32(dst)), "l"(reinterpret_cast<uint64_t>(&maps.m[mi])), "r"(smem_u32(&sm.full[s])), "r"(0), "r"(0),
-                        "r"(c2), "r"(0) : "memory");
+                        ::"r"(smem_u32(dst)), "l"(reinterpret_cast<uint64_t>(&maps.m[mi])), "r"(smem_u32(&sm.full[s])), "r"(c0), "r"(0),
+                        "r"(0), "r"(0) : "memory");
                 }
             } else {
                 // the last tiles of the buffer (the box would run past its end) and unsupported maps: the warp fills
@@ -238,7 +357,7 @@ scan_tc_kernel(const __grid_constant__ TcMaps maps, int n_maps, const float* __r
                         if (i0 + 1 < total_samples) v.y = samples[i0 + 1];
                         if (i0 + 2 < total_samples) v.z = samples[i0 + 2];
                     }
-                    *reinterpret_cast<float4*>(dst + a * kGroupBytes + kc * 128 + b * 16) = v;
+                    *reinterpret_cast<float4*>(dst + a * kGroupBytes + (kc >> 3) * kAtomBytes + b * 128 + (((kc & 7) ^ b) << 4)) = v;
                 }
                 asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
                 __syncwarp();
@@ -248,124 +367,80 @@ scan_tc_kernel(const __grid_constant__ TcMaps maps, int n_maps, const float* __r
         }
     } else if (warp == 1) {
         // ================================================================ MMA issuer
-        uint32_t it = 0;
-        for (uint32_t tl = blockIdx.x; tl < n_tiles; tl += gridDim.x) {
-            TmkStreamDev sd;
-            uint64_t w0;
-            if (!tile_of(tl, sd, w0)) continue;
-            const uint32_t s = it % kStages, ph = (it / kStages) & 1u;
-            const uint32_t t = it % kAccStages, tph = (it / kAccStages) & 1u;
-            ++it;
+        uint32_t cnt[kTeams] = {};
+        uint32_t j = 0;
+        TileDesc nxt = load_desc(blockIdx.x);
+        for (uint32_t tl = blockIdx.x; tl < n_tiles; tl += gridDim.x, ++j) {
+            const TileDesc td = nxt;
+            nxt = load_desc(tl + gridDim.x);
+            if (td.kind != kKind) continue;
+            const uint32_t s = j % kTeams;
+            uint32_t ph = 0;
+#pragma unroll
+            for (int k = 0; k < kTeams; ++k)
+                if (uint32_t(k) == s) ph = cnt[k]++ & 1u;
             mbar_wait(&sm.full[s], ph);
-            mbar_wait(&sm.tempty[t], tph ^ 1u);
+            mbar_wait(&sm.tempty[s], ph ^ 1u);
             asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
             if (lane == 0) {
                 const uint32_t a0 = smem_u32(stage0 + s * kStageBytes), b0 = smem_u32(tmat);
-                const uint32_t d = tmem_base + t * kRowLen;
+                const uint32_t d = tmem_base + s * kRowLen;
                 uint32_t acc = 0;
 #pragma unroll
                 for (int h = 0; h < S::kHalves; ++h) {
                     const int ksteps = (P + 63 - 64 * h) >= 64 ? 8 : (P + 63 - 64 * h + 7) / 8;  // taps reach k < P + 63
 #pragma unroll
-                    for (int kk = 0; kk < ksteps; ++kk) {
-                        umma_tf32(d, umma_desc(a0 + h * kGroupBytes + kk * 256, 128, kGroupBytes),
-                                  umma_desc(b0 + h * kTBytes + kk * 256, 128, kGroupBytes), kIdesc, acc);
+                    for (int kk = 0; kk < ksteps; ++kk) {  // K = 8 samples per instruction: column block kk / 4, 32 B further per step
+                        umma_tf32(d, umma_desc(a0 + h * kGroupBytes + (kk >> 2) * kAtomBytes + (kk & 3) * 32, kGroupBytes),
+                                  umma_desc(b0 + h * kTBytes + (kk >> 2) * 8192 + (kk & 3) * 32, kAtomBytes), kIdesc, acc);
                         acc = 1;
                     }
                 }
-                umma_commit(&sm.tfull[t]);
+                umma_commit(&sm.tfull[s]);
             }
             __syncwarp();
         }
     } else {
         // ================================================================ epilogue: energy, candidate test, block statistics
+        const uint32_t team = uint32_t(warp - 2) >> 2;
         const int q = warp & 3;            // TMEM lane quarter of this warp
         const int m = 32 * q + lane;       // MMA row = TMEM lane
         const int a = m >> 3, b = m & 7;
         const int rho = 16 * b + a;        // capture row of the tile
-        uint32_t it = 0;
-        for (uint32_t tl = blockIdx.x; tl < n_tiles; tl += gridDim.x) {
-            TmkStreamDev sd;
-            uint64_t w0;
-            if (!tile_of(tl, sd, w0)) continue;
-            const uint32_t s = it % kStages, ph = (it / kStages) & 1u;
-            const uint32_t t = it % kAccStages, tph = (it / kAccStages) & 1u;
-            ++it;
-            const uint64_t nwin = sd.n_samples - P + 1;
-            const float thr_c = sd.threshold * TMK_CAND_RATIO;
+        const uint32_t s = team;
+        uint32_t cnt = 0;
+        TileDesc nxt = load_desc(blockIdx.x + team * gridDim.x);
+        for (uint32_t tl = blockIdx.x + team * gridDim.x; tl < n_tiles; tl += kTeams * gridDim.x) {
+            const TileDesc td = nxt;
+            nxt = load_desc(tl + kTeams * gridDim.x);
+            if (td.kind != kKind) continue;
+            const uint32_t ph = cnt++ & 1u;
+            const uint64_t nwin = td.nwin;  // windows from the tile's first one on
+            const float thr_c = td.thr * TMK_CAND_RATIO;
             const float kap = thr_c * thr_c * float(P);
-            const uint64_t wrow = w0 + uint64_t(rho) * kRowLen;  // first window of this thread's row
+            const uint64_t wrow = uint64_t(rho) * kRowLen;  // first window of this thread's row, from the tile start
             const int nvalid = wrow >= nwin ? 0 : (nwin - wrow < uint64_t(kRowLen) ? int(nwin - wrow) : kRowLen);
-            mbar_wait(&sm.full[s], ph);   // the samples are visible to this thread
-            mbar_wait(&sm.tfull[t], tph);  // the dot products are in TMEM
+            const bool full = nwin >= uint64_t(TMK_TILE);
+            mbar_wait(&sm.full[s], ph);    // the samples are visible to this thread
+            mbar_wait(&sm.tfull[s], ph);   // the dot products are in TMEM
             asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
-            const uint8_t* row = stage0 + s * kStageBytes + a * kGroupBytes + b * 16;  // chunk c of the row (and the rows behind it)
-            auto chunk = [&](int c) -> float4 {  // samples 4 c .. 4 c + 3 counted from the row start
-                return *reinterpret_cast<const float4*>(row + (c >> 4) * kGroupBytes + (c & 15) * 128);
-            };
-            // energy of the row's first window
-            float e = 0.0f;
-#pragma unroll
-            for (int c = 0; c < P / 4; ++c) {
-                const float4 v = chunk(c);
-                e = fmaf(v.x, v.x, e);
-                e = fmaf(v.y, v.y, e);
-                e = fmaf(v.z, v.z, e);
-                e = fmaf(v.w, v.w, e);
-            }
+            const uint8_t* row = stage0 + s * kStageBytes + a * kGroupBytes + b * 128;  // the row (and, + kGroupBytes, the rows behind it)
+            const uint32_t taddr = tmem_base + (uint32_t(32 * q) << 16) + s * kRowLen;
             RowStat o{__int_as_float(0x7f800000), 0.0f, 0.0f, 0u};
-            uint32_t mask[2] = {0u, 0u};
-            const float nanv = __int_as_float(0x7fc00000);
-#pragma unroll
-            for (int half = 0; half < 2; ++half) {
-                float D[32];
-                tmem_ld32(tmem_base + (uint32_t(32 * q) << 16) + t * kRowLen + 32 * half, D);
-                if (half == 1) {  // both halves are in registers / consumed: the accumulator stage is free again
-                    asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
-                    __syncwarp();
-                    if (lane == 0) mbar_arrive(&sm.tempty[t]);
-                }
-                if (dbg_dot != nullptr)
-                    for (int j = 0; j < 32; ++j)
-                        if (32 * half + j < nvalid) dbg_dot[sd.offset + wrow + 32 * half + j] = D[j];
-                uint32_t mk = 0;
-#pragma unroll
-                for (int c4 = 0; c4 < 8; ++c4) {
-                    const float4 xo = chunk(8 * half + c4), xi = chunk(8 * half + c4 + P / 4);
-                    const float xov[4] = {xo.x, xo.y, xo.z, xo.w}, xiv[4] = {xi.x, xi.y, xi.z, xi.w};
-#pragma unroll
-                    for (int u = 0; u < 4; ++u) {
-                        const int j = 4 * c4 + u, n = 32 * half + j;
-                        const float Dv = D[j];
-                        const bool valid = n < nvalid;
-                        // a NaN / inf dot product (a NaN or inf sample anywhere in the row pair) must stay visible in max E
-                        const float Es = fmaf(Dv, 0.0f, e);
-                        const float Ev = valid ? Es : nanv;  // NaN: ignored by fminf / fmaxf, never a candidate
-                        const float dp = fmaxf(Dv, 0.0f);
-                        const float r = dp * dp * rcp_approx(Ev);  // P * corr^2 (NaN for silence: never a candidate)
-                        o.emin = fminf(o.emin, Ev);
-                        o.emax = max_nan(o.emax, valid ? Es : 0.0f);
-                        o.rmax = fmaxf(o.rmax, r);
-                        if (r > kap) mk |= 1u << j;
-                        e = fmaf(xiv[u], xiv[u], e);    // x[n + P] enters
-                        e = fmaf(-xov[u], xov[u], e);   // x[n] leaves
-                    }
-                }
-                mask[half] = mk;
-                o.ncand += __popc(mk);
-            }
+            uint32_t mask[2];
+            float* dbg = dbg_dot != nullptr ? dbg_dot + td.start + wrow : nullptr;
+            if (full) epi_row<P, true>(row, b, taddr, kap, kRowLen, &sm.tempty[s], lane, dbg, o, mask);
+            else epi_row<P, false>(row, b, taddr, kap, nvalid, &sm.tempty[s], lane, dbg, o, mask);
             // ---- the staged samples are no longer needed
             __syncwarp();
             if (lane == 0) mbar_arrive(&sm.empty[s]);
-            // ---- candidate words: the row owns words 2 (rho % 8), 2 (rho % 8) + 1 of its block
-            const uint64_t blk0 = sd.blk_base + w0 / TMK_BLK;
-            const uint32_t blk = uint32_t(rho) >> 3;
-            const bool blk_exists = w0 + uint64_t(blk) * TMK_BLK < nwin;
-            if (blk_exists) {
-                uint2* wp = reinterpret_cast<uint2*>(cand_bits + (blk0 + blk) * TMK_BLK_WORDS + 2 * (rho & 7));
+            // ---- candidate words: the row owns words 2 (rho % 4), 2 (rho % 4) + 1 of its block of 4 rows
+            const uint32_t blk = uint32_t(rho) >> 2;
+            if (uint64_t(blk) * TMK_BLK < nwin) {
+                uint2* wp = reinterpret_cast<uint2*>(cand_bits + (td.blk0 + blk) * TMK_BLK_WORDS + 2 * (rho & 3));
                 *wp = make_uint2(mask[0], mask[1]);
             }
-            // ---- block statistics: the four rows a = 4 q .. 4 q + 3 of one b are half a block (lanes b, b + 8, b + 16, b + 24)
+            // ---- block statistics: the four rows a = 4 q .. 4 q + 3 of one b ARE a block (lanes b, b + 8, b + 16, b + 24)
             float ncf = float(o.ncand);
 #pragma unroll
             for (int sft = 8; sft <= 16; sft <<= 1) {
@@ -374,20 +449,11 @@ scan_tc_kernel(const __grid_constant__ TcMaps maps, int n_maps, const float* __r
                 o.rmax = fmaxf(o.rmax, __shfl_xor_sync(kFull, o.rmax, sft));
                 ncf += __shfl_xor_sync(kFull, ncf, sft);
             }
-            if (lane < 8) sm.stat[t][q][lane] = make_float4(o.emin, o.emax, o.rmax, ncf);
-            asm volatile("bar.sync 1, %0;" ::"n"(kEpiWarps * 32) : "memory");
-            if ((q & 1) == 0 && lane < 8) {  // quarters (0, 1) hold block 2 b, quarters (2, 3) block 2 b + 1
-                const float4 u = sm.stat[t][q][lane], v = sm.stat[t][q + 1][lane];
-                const uint32_t bk = 2 * uint32_t(lane) + (q >> 1);
-                if (w0 + uint64_t(bk) * TMK_BLK < nwin) {
-                    const float nc = u.w + v.w;
-                    // max corr^2 with the TF32 margin (see the header): 2 x 2^-10 of it, rounded up
-                    const float rm = fmaxf(u.z, v.z) * (1.0f / float(P)) * 1.0015f;
-                    blk_info[blk0 + bk] = make_float4(fminf(u.x, v.x), max_nan(u.y, v.y), rm, nc);
-                    if (nc > 0.f && cblk_list) cblk_list[atomicAdd(cblk_count, 1u)] = uint32_t(blk0 + bk);
-                }
+            if (lane < 8 && uint64_t(blk) * TMK_BLK < nwin) {  // lane b holds block 4 b + q
+                // max corr^2 with the TF32 margin (see the header): 2 x 2^-10 of it, rounded up
+                blk_info[td.blk0 + blk] = make_float4(o.emin, o.emax, o.rmax * (1.0f / float(P)) * 1.0015f, ncf);
+                if (ncf > 0.f && cblk_list) cblk_list[atomicAdd(cblk_count, 1u)] = uint32_t(td.blk0 + blk);
             }
-            // (stat[t] is rewritten two tiles later, behind the next tile's barrier: no second barrier needed)
         }
     }
     __syncthreads();
@@ -415,19 +481,18 @@ EncodeTiledFn encode_fn() {
     return fn;
 }
 
-// the box of one tile: (4 floats) x (8 rows b, 16 capture rows apart) x (16 chunks of a row) x (row groups a)
+// the box of one tile: (32 samples = 128 B) x (8 rows b, 16 capture rows apart) x (2 column blocks of a row) x (row
+// groups a), written with the 128-byte swizzle: group a lands as two swizzle atoms [columns 0..31 | 32..63] of 8 rows
 bool make_map(CUtensorMap* map, const float* base, uint64_t n_samples, int groups) {
     EncodeTiledFn fn = encode_fn();
     if (fn == nullptr || getenv("TMK_SCAN_NO_TMA")) return false;
-    uint64_t chunks = n_samples / 4;
-    if (chunks == 0) return false;
-    if (chunks > 0xffffffffull) chunks = 0xffffffffull;
-    const cuuint64_t gdim[4] = {4, 8, chunks, cuuint64_t(groups)};
-    const cuuint64_t gstr[3] = {16 * kRowLen * 4, 16, kRowLen * 4};
-    const cuuint32_t box[4] = {4, 8, 16, cuuint32_t(groups)};
+    if (n_samples < 32) return false;
+    const cuuint64_t gdim[4] = {n_samples, 8, 2, cuuint64_t(groups)};
+    const cuuint64_t gstr[3] = {16 * kRowLen * 4, 32 * 4, kRowLen * 4};
+    const cuuint32_t box[4] = {32, 8, 2, cuuint32_t(groups)};
     const cuuint32_t estr[4] = {1, 1, 1, 1};
     const CUresult rc = fn(map, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 4, const_cast<float*>(base), gdim, gstr, box, estr,
-                           CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                           CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
                            CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
     if (rc != CUDA_SUCCESS) {
         static bool said = false;
@@ -439,9 +504,8 @@ bool make_map(CUtensorMap* map, const float* base, uint64_t n_samples, int group
 }
 
 template <int LC>
-int launch_tc(const float* samples, uint64_t total_samples, const TmkStreamDev* streams, const uint32_t* tile_stream,
-              uint32_t tile0, uint32_t n_tiles, const TmkPattern* patterns, float4* blk_info, uint32_t* cand_bits,
-              uint32_t* cblk_list, unsigned int* cblk_count, float* dbg_dot, cudaStream_t st) {
+int launch_tc(const float* samples, uint64_t total_samples, const TileDesc* tdesc, uint32_t n_tiles, float4* blk_info,
+              uint32_t* cand_bits, uint32_t* cblk_list, unsigned int* cblk_count, float* dbg_dot, cudaStream_t st) {
     using S = Tc<LC>;
     static int sms = 0;
     const size_t smem = size_t(kStages) * S::kGroups * kGroupBytes + size_t(S::kHalves) * 16384 + sizeof(Smem) + 1024;
@@ -451,40 +515,46 @@ int launch_tc(const float* samples, uint64_t total_samples, const TmkStreamDev* 
         cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
         cudaFuncSetAttribute(scan_tc_kernel<LC>, cudaFuncAttributeMaxDynamicSharedMemorySize, int(smem));
     }
-    // one tensor map per window of 2^33 samples (the box coordinate is a 32-bit index of 16-byte chunks); a tile is
+    // one tensor map per window of kMapWin samples (the box coordinate is a signed 32-bit sample index); a tile is
     // loaded through the map of the window its first sample lies in, which therefore reaches one tile past the window
     TcMaps maps;
     std::memset(&maps, 0, sizeof maps);
     int n_maps = 0;
-    const uint64_t kWin = 1ull << 33;
-    for (uint64_t base = 0; base < total_samples && n_maps < kMaxMaps; base += kWin) {
+    for (uint64_t base = 0; base < total_samples && n_maps < kMaxMaps; base += kMapWin) {
         uint64_t len = total_samples - base;
-        if (len > kWin + 16384) len = kWin + 16384;
+        if (len > kMapWin + 16384) len = kMapWin + 16384;
         if (!make_map(&maps.m[n_maps], samples + base, len, S::kGroups)) break;
         ++n_maps;
     }
     const uint32_t grid = n_tiles < uint32_t(sms) ? n_tiles : uint32_t(sms);
-    scan_tc_kernel<LC><<<grid, kThreads, smem, st>>>(maps, n_maps, samples, total_samples, streams, tile_stream, tile0, n_tiles,
-                                                      patterns, blk_info, cand_bits, cblk_list, cblk_count, dbg_dot);
+    scan_tc_kernel<LC><<<grid, kThreads, smem, st>>>(maps, n_maps, samples, total_samples, tdesc, n_tiles, blk_info, cand_bits,
+                                                      cblk_list, cblk_count, dbg_dot);
     return 1;
 }
 
 }  // namespace
 
+size_t tmk_scan_tile_desc_bytes(uint32_t n_tiles) { return sizeof(TileDesc) * size_t(n_tiles ? n_tiles : 1); }
+
 // kinds: bit 0 = some stream is 4B5B/3/2, bit 1 = Manchester/3/2, bit 2 = any other shape (generic kernel)
+// tile_desc: scratch of tmk_scan_tile_desc_bytes(n_tiles) bytes (descriptors of the tiles [tile0, tile0 + n_tiles))
 int tmk_launch_scan(const float* samples, uint64_t total_samples, const TmkStreamDev* streams, uint32_t n_streams,
                     const uint32_t* tile_stream, uint32_t tile0, uint32_t n_tiles, const TmkPattern* patterns,
                     uint32_t kinds, float4* blk_info, uint32_t* cand_bits, uint32_t* cblk_list, unsigned int* cblk_count,
-                    cudaStream_t st, float* dbg_dot) {
+                    cudaStream_t st, void* tile_desc, float* dbg_dot) {
     (void)n_streams;
     if (n_tiles == 0) return 0;
     int launches = 0;
+    TileDesc* td = static_cast<TileDesc*>(tile_desc);
+    if (kinds & 3u) {
+        tile_desc_kernel<<<(n_tiles + 255) / 256, 256, 0, st>>>(streams, tile_stream, patterns, tile0, n_tiles, td);
+        ++launches;
+    }
     if (kinds & 1u)
-        launches += launch_tc<TMK_LINE_4B5B>(samples, total_samples, streams, tile_stream, tile0, n_tiles, patterns, blk_info,
-                                             cand_bits, cblk_list, cblk_count, dbg_dot, st);
+        launches += launch_tc<TMK_LINE_4B5B>(samples, total_samples, td, n_tiles, blk_info, cand_bits, cblk_list, cblk_count, dbg_dot, st);
     if (kinds & 2u)
-        launches += launch_tc<TMK_LINE_MANCHESTER>(samples, total_samples, streams, tile_stream, tile0, n_tiles, patterns,
-                                                   blk_info, cand_bits, cblk_list, cblk_count, dbg_dot, st);
+        launches += launch_tc<TMK_LINE_MANCHESTER>(samples, total_samples, td, n_tiles, blk_info, cand_bits, cblk_list, cblk_count,
+                                                   dbg_dot, st);
     if (kinds & 4u) launches += tmk_launch_scan_generic(samples, streams, tile_stream, tile0, n_tiles, patterns, blk_info, cand_bits,
                                                             cblk_list, cblk_count, st);
     return launches;

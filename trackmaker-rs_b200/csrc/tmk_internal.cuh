@@ -21,10 +21,10 @@
                              // 4 lanes x 120 windows of the fast scan kernel, 15 whole bitmap words
 #define TMK_BLK_WORDS 15     // TMK_BLK / 32
 #define TMK_TILE_BLKS 8      // blocks per scan tile
-#else                        // tensor-core scan (scan_tc.cu): rows of 64 windows, 8 rows per block, 128 rows per tile
-#define TMK_BLK 512
-#define TMK_BLK_WORDS 16
-#define TMK_TILE_BLKS 16
+#else                        // tensor-core scan (scan_tc.cu): rows of 64 windows, 4 rows per block (the four rows one
+#define TMK_BLK 256          // epilogue warp holds for one `b`: block statistics need no exchange between warps),
+#define TMK_BLK_WORDS 8      // 128 rows per tile
+#define TMK_TILE_BLKS 32
 #endif
 #define TMK_TILE (TMK_BLK * TMK_TILE_BLKS)  // windows per scan tile
 #define TMK_MAX_P 1024       // longest supported preamble in samples
@@ -154,8 +154,10 @@ int tmk_launch_tile_dir(const TmkStreamDev* streams, uint32_t n_streams, uint32_
 int tmk_launch_scan(const float* samples, uint64_t total_samples, const TmkStreamDev* streams, uint32_t n_streams,
                     const uint32_t* tile_stream, uint32_t tile0, uint32_t n_tiles, const TmkPattern* patterns,
                     uint32_t kinds, float4* blk_info, uint32_t* cand_bits, uint32_t* cblk_list, unsigned int* cblk_count,
-                    cudaStream_t st, float* dbg_dot = nullptr);  // cblk_list / cblk_count (nullable): global ids of the blocks with candidates;
-                                                                 // dbg_dot (nullable): the filter's correlation numerators per window
+                    cudaStream_t st, void* tile_desc, float* dbg_dot = nullptr);
+// cblk_list / cblk_count (nullable): global ids of the blocks with candidates; tile_desc: device scratch of
+// tmk_scan_tile_desc_bytes(n_tiles) bytes; dbg_dot (nullable): the filter's correlation numerators per window
+size_t tmk_scan_tile_desc_bytes(uint32_t n_tiles);
 int tmk_launch_scan_generic(const float* samples, const TmkStreamDev* streams, const uint32_t* tile_stream,
                             uint32_t tile0, uint32_t n_tiles, const TmkPattern* patterns, float4* blk_info,
                             uint32_t* cand_bits, uint32_t* cblk_list, unsigned int* cblk_count, cudaStream_t st);

@@ -22,7 +22,8 @@ namespace {
 constexpr int kWarpsPerCta = 4;
 constexpr int kMaxFrameBytesCap = 1024;                 // cfg.max_frame_bytes upper limit
 constexpr int kByteBuf = TMK_PHY_HEADER_BYTES + kMaxFrameBytesCap + 9;
-constexpr int kQBuf = TMK_BLK + 256;                    // prefix sums of one block for P <= 255
+constexpr int kFastMaxP = 127;                          // longest preamble of the staged-block paths (shipped shapes: 60, 96)
+constexpr int kQBuf = TMK_BLK + kFastMaxP + 1;          // prefix sums of one block for P <= kFastMaxP
 constexpr int kXsMaxP = 96;                             // longest preamble whose block samples are staged (shipped shapes: 60, 96)
 constexpr int kXs = TMK_BLK + kXsMaxP;
 constexpr float kU = 5.9604645e-8f;                     // 2^-24, unit roundoff of f32
@@ -353,6 +354,12 @@ __device__ __noinline__ float roll_parallel(Ctx& c, float e, uint64_t* pos_io, u
         float4 a0 = xa[0], a1 = xa[1], b0 = xb[0], b1 = xb[1];
         for (uint32_t k = 0; k < L; k += 8) {
             float4 an0 = a0, an1 = a1, bn0 = b0, bn1 = b1;
+            // every lane streams its own segment (32 different lines per load): the lines two ahead start their trip
+            // to L1 now, so the loads below find them there instead of waiting for L2 / HBM
+            if ((k & 31u) == 0u && k + 96 < L + P) {
+                asm volatile("prefetch.global.L1 [%0];" ::"l"(xp + k + 64));
+                asm volatile("prefetch.global.L1 [%0];" ::"l"(xp + k + 64 + P));
+            }
             if (k + 8 < L) {
                 an0 = xa[k / 4 + 2];
                 an1 = xa[k / 4 + 3];
@@ -528,7 +535,7 @@ __device__ bool exact_window(Ctx& c, uint64_t w, uint64_t seed, float D, float* 
     return corr >= c.thr;
 }
 
-// Prefix sums of the rounded squares of block `bb` in double: E_c(w) = Q[w+P] - Q[w]  (P <= 255).
+// Prefix sums of the rounded squares of block `bb` in double: E_c(w) = Q[w+P] - Q[w]  (P <= uint32_t(kFastMaxP)).
 // Every lane owns K consecutive samples, fetched as float4s that are all in flight together (one HBM
 // round trip for the block), summed serially per lane, then one warp scan of the 32 lane totals.
 __device__ __noinline__ void block_prefix(Ctx& c, uint64_t bb) {
@@ -544,7 +551,7 @@ __device__ __noinline__ void block_prefix(Ctx& c, uint64_t bb) {
         // 32 lane totals.
         uint64_t ns64 = c.N - wb0;
         const uint32_t ns = ns64 < uint64_t(TMK_BLK + P - 1) ? uint32_t(ns64) : TMK_BLK + P - 1;
-        constexpr int kMaxK4 = (TMK_BLK + 255 + 127) / 128;  // float4s per lane, 6
+        constexpr int kMaxK4 = (TMK_BLK + kFastMaxP + 127) / 128;  // float4s per lane
         const uint32_t K4 = (ns + 127) / 128;
         const uint32_t i0 = uint32_t(lane) * K4 * 4;
         const float* __restrict__ xb = x + wb0 + i0;
@@ -645,7 +652,7 @@ __device__ __forceinline__ tmk_frame_rec ld_spec(const tmk_frame_rec* p) {
 
 // speculative verdict record the cluster pass prepared for window wl of block bb (or TMK_ENT_INVALID)
 __device__ __noinline__ uint32_t lookup_spec(const Ctx& c, uint64_t bb, uint32_t wl) {
-    if (c.blk_ptr == nullptr || c.P > 255) return TMK_ENT_INVALID;
+    if (c.blk_ptr == nullptr || c.P > uint32_t(kFastMaxP)) return TMK_ENT_INVALID;
     if (c.blk_info[bb].w == 0.f) return TMK_ENT_INVALID;  // not on the cluster pass's list: never published
     const uint32_t ptr = wait_blk_ptr(c, bb);
     if (ptr == TMK_ENT_INVALID) return TMK_ENT_INVALID;
@@ -683,7 +690,7 @@ __device__ __noinline__ bool process_block(Ctx& c, uint64_t bb, uint64_t q, uint
 
     // the block's candidate words: lane r holds word r (one load round instead of 15)
     const uint32_t myword = lane < TMK_BLK_WORDS ? c.cand_bits[bb * TMK_BLK_WORDS + lane] : 0u;
-    const bool fast = P <= 255;
+    const bool fast = P <= uint32_t(kFastMaxP);
     if (fast) block_prefix(c, bb);
     float pmcarry = prevmax * 1.001f;  // block maxima come from the approximate scan
     float sumcarry = c.racc_in;
@@ -789,7 +796,7 @@ __device__ __noinline__ bool process_block(Ctx& c, uint64_t bb, uint64_t q, uint
 __device__ __noinline__ int fast_block(Ctx& c, uint64_t bb, uint64_t q, float4 info, float nb, float smax, float racc_end,
                                        float racc_in, float efirst, float emin_lo, float pmax_in, uint64_t avail,
                                        Detection* det) {
-    if (c.blk_ptr == nullptr || c.P > 255 || c.a_w != c.a_seed || c.a_err != 0.f) return 2;
+    if (c.blk_ptr == nullptr || c.P > uint32_t(kFastMaxP) || c.a_w != c.a_seed || c.a_err != 0.f) return 2;
     const float silent = 0.5f * c.thr * c.thr * 1e-6f;
     if (info.y < silent) return 0;  // every window is gated or cannot reach the threshold (as in search())
     const uint64_t wb0 = bb * TMK_BLK;
@@ -922,7 +929,7 @@ __device__ __noinline__ bool search(Ctx& c, uint64_t q, uint64_t avail, Detectio
             if (r == 1) return true;
             if (r == 0) runmax = i0.y * 1.001f;
         }
-        if (r == 2 && c.blk_ptr != nullptr && c.P <= 255) {
+        if (r == 2 && c.blk_ptr != nullptr && c.P <= uint32_t(kFastMaxP)) {
             // 2. exact energies of the windows [q, end of block] (one block load): sum, maximum, minimum
             block_prefix(c, b0);
             const uint32_t lo = uint32_t(q - b0 * TMK_BLK), hi = uint32_t(wl0 - b0 * TMK_BLK);
@@ -1188,7 +1195,7 @@ __device__ __noinline__ uint32_t line_decode(const Ctx& c, uint64_t fs, uint32_t
     // level sums are staged in shared memory (the prefix-sum buffer is idle during a decode):
     // pass 1 fills a chunk with independent loads in flight, pass 2 decides out of shared memory
     float* lev = reinterpret_cast<float*>(c.sc->Q);
-    constexpr uint32_t kChunk = 1280;  // levels per chunk: 256 4B5B symbols = 128 bytes, 640 Manchester bits = 80 bytes
+    constexpr uint32_t kChunk = 640;  // levels per chunk: 128 4B5B symbols = 64 bytes, 320 Manchester bits = 40 bytes
     static_assert(kChunk <= 2 * kQBuf && kChunk % 160 == 0 && kChunk % 64 == 0, "level chunk");
     const bool man = c.pat->line_code == TMK_LINE_MANCHESTER;
     const uint32_t nlev = man ? total_bits * 2 : (total_bits / 4) * 5;
@@ -1539,7 +1546,7 @@ cluster_kernel(const float* __restrict__ samples, const TmkStreamDev* __restrict
         Ctx c;
         init_ctx(c, samples, sd, patterns, blk_info, cand_bits, f, lane, warp);
         const uint64_t bb = uint64_t(gb) - sd.blk_base;
-        if (c.P > 255) {  // long preambles keep the walk's own evaluation
+        if (c.P > uint32_t(kFastMaxP)) {  // long preambles keep the walk's own evaluation
             if (lane == 0) publish_blk(f.blk_ptr + gb, TMK_ENT_INVALID);
             continue;
         }
@@ -1669,6 +1676,9 @@ cluster_kernel(const float* __restrict__ samples, const TmkStreamDev* __restrict
             if (w < skip_until) continue;
             const float corr = ex_corr(e.D, e.Ec, c.pat->pe);
             if (!(corr >= c.thr)) continue;
+            // the frame behind the preamble starts its trip from HBM now (the refinement and the header decode run first)
+            for (uint32_t i = uint32_t(lane) * 32; i < 2304 && w + c.P + i < c.N; i += 1024)
+                asm volatile("prefetch.global.L2 [%0];" ::"l"(c.x + w + c.P + i));
             unsigned int sp = 0;
             if (lane == 0) sp = atomicAdd(&f.pool[1], 1u);
             sp = __shfl_sync(kFull, sp, 0);
