@@ -19,6 +19,9 @@
 
 namespace {
 
+#ifndef TMK_CONTRAST
+#define TMK_CONTRAST 512  // max / min window energy of the block that holds q beyond which its exact energies are computed
+#endif
 constexpr int kWarpsPerCta = 4;
 constexpr int kMaxFrameBytesCap = 1024;                 // cfg.max_frame_bytes upper limit
 constexpr int kByteBuf = TMK_PHY_HEADER_BYTES + kMaxFrameBytesCap + 9;
@@ -924,7 +927,7 @@ __device__ __noinline__ bool search(Ctx& c, uint64_t q, uint64_t avail, Detectio
         // (a block with a strong contrast is the end of the consumed frame: its maximum would pollute the
         // bounds of the whole gap behind it, so it goes straight to the exact energies)
         int r = 2;
-        if (!(i0.y > 8.f * i0.x)) {
+        if (!(i0.y > float(TMK_CONTRAST) * i0.x)) {
             r = fast_block(c, b0, q, i0, nb0, i0.y * 1.001f, racc, 0.f, efirst, i0.x - dscan0, 0.f, avail, det);
             if (r == 1) return true;
             if (r == 0) runmax = i0.y * 1.001f;
