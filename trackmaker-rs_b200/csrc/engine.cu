@@ -393,13 +393,13 @@ static int decode_batch_impl(tmk_engine* e, const void* samples_v, bool pcm16, u
     CK(e->d_next.reserve(sizeof(unsigned int) * (chunks.size() + 1)));
     // cluster pass (walk.cu): candidate entries + speculative verdicts, per chunk its own list region / counter
     const bool use_fast = b.n_blocks > 0 && b.n_blocks < (1ull << 31) && !getenv("TMK_NO_CLUSTER");
-    // measured at C2: the cluster pass beside the walk (each on half of the CTA slots) takes 10.3 ms instead of 3.8,
-    // and most walks wait for it anyway (step 16.2 ms against 12.0): off unless TMK_CONCURRENT_CLUSTER is set
-    const bool serial_cluster = getenv("TMK_CONCURRENT_CLUSTER") == nullptr;
+    // (the walk of a chunk follows its cluster pass: running them side by side — the walk waiting for blocks the
+    //  cluster pass had not reached — measured slower in round 1, 16.2 ms against 12.0 per step, and was removed)
+    const bool serial_cluster = true;
     const uint64_t entry_cap = std::min<uint64_t>((1ull << 26) - 1, b.n_blocks / 2 + 4096);
     if (use_fast) {
         CK(e->d_cblk.reserve(sizeof(uint32_t) * b.n_blocks));
-        CK(e->d_blk_ptr.reserve(2 * sizeof(uint32_t) * b.n_blocks));  // pointers | gains
+        CK(e->d_blk_ptr.reserve(sizeof(uint2) * b.n_blocks));  // (entry pointer, gain) per block with candidates
         CK(e->d_entries.reserve(sizeof(TmkCandEntry) * entry_cap));
         CK(e->d_pool.reserve(sizeof(unsigned int) * (2 + 2 * chunks.size())));
     }
@@ -419,10 +419,14 @@ static int decode_batch_impl(tmk_engine* e, const void* samples_v, bool pcm16, u
     // record / payload scratch on the device: start from a guess, rerun the (cheap) walk if the
     // counts say it was too small and the caller's buffers are larger.
     const bool recs_dev = rec_cap && is_device_ptr(recs), pay_dev = payload_cap && is_device_ptr(payload);
-    uint64_t dev_rec_cap = std::min<uint64_t>(rec_cap, std::max<uint64_t>(4096, total_samples / 192 + 2ull * n_streams));
+    // (the walk's warps reserve record slots 32 at a time: the scratch holds kSlotSlack slots more than the records
+    //  it is meant for, and the counter the walk returns counts reserved slots; the exact number is the sum of the
+    //  per-stream counts)
+    const uint64_t kSlotSlack = 32ull * 148 * 16 + 64;
+    uint64_t dev_rec_cap = std::min<uint64_t>(rec_cap, std::max<uint64_t>(4096, total_samples / 192 + 2ull * n_streams)) + kSlotSlack;
     uint64_t dev_pay_cap = pay_dev ? payload_cap : std::min<uint64_t>(payload_cap, std::max<uint64_t>(65536, total_samples / 24));
     CK(e->d_recs_tmp.reserve(sizeof(tmk_frame_rec) * std::max<uint64_t>(1, dev_rec_cap)));
-    CK(e->d_rec_ord.reserve(sizeof(uint32_t) * std::max<uint64_t>(1, dev_rec_cap)));
+    CK(e->d_rec_ord.reserve(sizeof(uint4) * std::max<uint64_t>(1, dev_rec_cap)));
     if (!pay_dev) CK(e->d_payload.reserve(std::max<uint64_t>(1, dev_pay_cap)));
     uint64_t spec_cap = std::min<uint64_t>(0x7fffffffull, 2 * dev_rec_cap + 1024);
     if (use_fast) CK(e->d_spec.reserve(sizeof(tmk_frame_rec) * spec_cap));
@@ -434,8 +438,7 @@ static int decode_batch_impl(tmk_engine* e, const void* samples_v, bool pcm16, u
         f.cblk_list = static_cast<uint32_t*>(e->d_cblk.p) + uint64_t(ch.t0) * TMK_TILE_BLKS;
         f.cblk_count = pool + 2 + g;
         f.item_next = pool + 2 + chunks.size() + g;
-        f.blk_ptr = static_cast<uint32_t*>(e->d_blk_ptr.p);
-        f.blk_gain = reinterpret_cast<float*>(f.blk_ptr + b.n_blocks);
+        f.blk_res = static_cast<uint2*>(e->d_blk_ptr.p);
         f.entries = static_cast<TmkCandEntry*>(e->d_entries.p);
         f.entry_cap = uint32_t(entry_cap);
         f.spec = static_cast<tmk_frame_rec*>(e->d_spec.p);
@@ -453,9 +456,6 @@ static int decode_batch_impl(tmk_engine* e, const void* samples_v, bool pcm16, u
     CK(cudaMemsetAsync(dnext, 0, sizeof(unsigned int) * (chunks.size() + 1), e->stream));
     if (use_fast) {
         CK(cudaMemsetAsync(e->d_pool.p, 0, sizeof(unsigned int) * (2 + 2 * chunks.size()), e->stream));
-        // every block starts PENDING (0xfffffffe in each byte pair is not expressible by memset: 0xfe bytes give
-        // 0xfefefefe, so the sentinel is that value) — see TMK_ENT_PENDING
-        CK(cudaMemsetAsync(e->d_blk_ptr.p, 0xfe, sizeof(uint32_t) * b.n_blocks, e->stream));
     }
     if (host_samples) {
         // the copy stream may only overwrite the staging buffer once earlier work on it is done
@@ -500,7 +500,7 @@ static int decode_batch_impl(tmk_engine* e, const void* samples_v, bool pcm16, u
             }
         }
         e->launches += tmk_launch_walk(dx, ds, ch.s0, ch.s1, dnext + g, fast, dp, dbi, dcb,
-                                       static_cast<tmk_frame_rec*>(e->d_recs_tmp.p), static_cast<uint32_t*>(e->d_rec_ord.p),
+                                       static_cast<tmk_frame_rec*>(e->d_recs_tmp.p), static_cast<uint4*>(e->d_rec_ord.p),
                                        dev_rec_cap, dpay, dev_pay_cap, static_cast<uint32_t*>(e->d_cnt.p), dc, d_link, ws);
         CK(cudaGetLastError());
     }
@@ -510,17 +510,20 @@ static int decode_batch_impl(tmk_engine* e, const void* samples_v, bool pcm16, u
         CK(cudaStreamWaitEvent(e->stream, e->wev[i], 0));
     }
     TmkCounters hc;
+    uint64_t n_exact = 0;  // records = sum of the per-stream counts
+    e->launches += tmk_launch_excl_scan(static_cast<const uint32_t*>(e->d_cnt.p), static_cast<uint64_t*>(e->d_base.p), n_streams, e->stream);
+    CK(cudaMemcpyAsync(&n_exact, static_cast<uint64_t*>(e->d_base.p) + n_streams, sizeof n_exact, cudaMemcpyDeviceToHost, e->stream));
     CK(cudaMemcpyAsync(&hc, dc, sizeof hc, cudaMemcpyDeviceToHost, e->stream));
     CK(cudaStreamSynchronize(e->stream));
     for (int attempt = 0; attempt < 2; ++attempt) {
-        const bool rec_short = hc.n_recs > dev_rec_cap && dev_rec_cap < rec_cap;
+        const bool rec_short = hc.n_recs > dev_rec_cap && dev_rec_cap < rec_cap + kSlotSlack;
         const bool pay_short = hc.n_payload > dev_pay_cap && dev_pay_cap < payload_cap;
         if (!rec_short && !pay_short) break;
         // the guess was too small: grow the scratch and walk every stream again (everything is resident now)
-        if (rec_short) dev_rec_cap = std::min<uint64_t>(rec_cap, hc.n_recs);
+        if (rec_short) dev_rec_cap = std::min<uint64_t>(rec_cap, hc.n_recs) + kSlotSlack;
         if (pay_short) dev_pay_cap = std::min<uint64_t>(payload_cap, hc.n_payload);
         CK(e->d_recs_tmp.reserve(sizeof(tmk_frame_rec) * std::max<uint64_t>(1, dev_rec_cap)));
-        CK(e->d_rec_ord.reserve(sizeof(uint32_t) * std::max<uint64_t>(1, dev_rec_cap)));
+        CK(e->d_rec_ord.reserve(sizeof(uint4) * std::max<uint64_t>(1, dev_rec_cap)));
         if (!pay_dev) CK(e->d_payload.reserve(std::max<uint64_t>(1, dev_pay_cap)));
         uint8_t* dpay = pay_dev ? payload : static_cast<uint8_t*>(e->d_payload.p);
         CK(cudaMemsetAsync(dc, 0, sizeof(TmkCounters), e->stream));
@@ -530,16 +533,18 @@ static int decode_batch_impl(tmk_engine* e, const void* samples_v, bool pcm16, u
         TmkFast nofast;
         std::memset(&nofast, 0, sizeof nofast);
         e->launches += tmk_launch_walk(dx, ds, 0, n_streams, dnext + chunks.size(), nofast, dp, dbi, dcb,
-                                       static_cast<tmk_frame_rec*>(e->d_recs_tmp.p), static_cast<uint32_t*>(e->d_rec_ord.p),
+                                       static_cast<tmk_frame_rec*>(e->d_recs_tmp.p), static_cast<uint4*>(e->d_rec_ord.p),
                                        dev_rec_cap, dpay, dev_pay_cap, static_cast<uint32_t*>(e->d_cnt.p), dc, d_link, e->stream);
         CK(cudaGetLastError());
+        e->launches += tmk_launch_excl_scan(static_cast<const uint32_t*>(e->d_cnt.p), static_cast<uint64_t*>(e->d_base.p), n_streams, e->stream);
+        CK(cudaMemcpyAsync(&n_exact, static_cast<uint64_t*>(e->d_base.p) + n_streams, sizeof n_exact, cudaMemcpyDeviceToHost, e->stream));
         CK(cudaMemcpyAsync(&hc, dc, sizeof hc, cudaMemcpyDeviceToHost, e->stream));
         CK(cudaStreamSynchronize(e->stream));
     }
     if (link_final)
         CK(cudaMemcpyAsync(link_final, d_link, sizeof(TmkLinkState) * n_streams, cudaMemcpyDeviceToHost, e->stream));
     CK(cudaEventRecord(e->ev[3], e->stream));
-    *n_recs = hc.n_recs;
+    *n_recs = n_exact;
     *payload_len = hc.n_payload;
     for (int i = 0; i < TMK_STAT_COUNT; ++i) e->stats[i] += hc.stats[i];
     for (int i = 0; i < 8; ++i) e->dbg[i] = hc.dbg[i];
@@ -547,21 +552,21 @@ static int decode_batch_impl(tmk_engine* e, const void* samples_v, bool pcm16, u
         float cms = 0.f;
         if (cudaEventElapsedTime(&cms, e->ev[2], e->ev[5]) == cudaSuccess) e->dbg[4] = uint64_t(cms * 1000.f);
     }
-    const bool overflow = hc.n_recs > rec_cap || hc.n_payload > payload_cap;
-    if (!overflow && hc.n_recs) {
+    const bool overflow = n_exact > rec_cap || hc.n_recs > dev_rec_cap || hc.n_payload > payload_cap;
+    if (!overflow && n_exact) {
         tmk_frame_rec* dout = recs;
         if (!recs_dev) {
-            CK(e->d_recs.reserve(sizeof(tmk_frame_rec) * hc.n_recs));
+            CK(e->d_recs.reserve(sizeof(tmk_frame_rec) * n_exact));
             dout = static_cast<tmk_frame_rec*>(e->d_recs.p);
         }
         e->launches += tmk_launch_order(static_cast<const tmk_frame_rec*>(e->d_recs_tmp.p),
-                                        static_cast<const uint32_t*>(e->d_rec_ord.p), hc.n_recs,
+                                        static_cast<const uint4*>(e->d_rec_ord.p), hc.n_recs,
                                         static_cast<const uint32_t*>(e->d_cnt.p), static_cast<uint64_t*>(e->d_base.p),
-                                        n_streams, dout, e->stream);
+                                        n_streams, use_fast ? static_cast<const tmk_frame_rec*>(e->d_spec.p) : nullptr, dout, e->stream);
         CK(cudaGetLastError());
         CK(cudaEventRecord(e->ev[4], e->stream));
         if (!recs_dev)
-            CK(cudaMemcpyAsync(recs, dout, sizeof(tmk_frame_rec) * hc.n_recs, cudaMemcpyDeviceToHost, e->stream));
+            CK(cudaMemcpyAsync(recs, dout, sizeof(tmk_frame_rec) * n_exact, cudaMemcpyDeviceToHost, e->stream));
         if (!pay_dev && hc.n_payload)
             CK(cudaMemcpyAsync(payload, e->d_payload.p, hc.n_payload, cudaMemcpyDeviceToHost, e->stream));
     } else {

@@ -85,20 +85,24 @@ struct TmkCounters {
 };
 
 // ---- cluster pass (walk.cu): per-candidate results computed in parallel before the per-stream walk
-struct TmkCandEntry {  // one candidate window of a block, in window order
+struct TmkCandEntry {  // one candidate window of a block, in window order (32 bytes: two 16-byte loads)
     uint16_t wl;       // window offset inside the block
-    uint16_t flags;
+    uint16_t status;   // verdict of the speculative record (TMK_FRAME_*), or TMK_ENT_NOSPEC
     float D;           // exact AVX-order dot product   (decoder.rs:381-417)
     float Ec;          // accurately summed window energy
     uint32_t spec;     // speculative frame record of a detection at this window, or TMK_ENT_INVALID
+    uint32_t consumed; // samples the frame consumes from the window (what the walk needs to go on without the record)
+    int32_t fs_off;    // frame_start - window
+    uint32_t len;      // payload length of the header (chunked feeding: how many samples decode_frame waited for)
+    uint32_t pad_;
 };
 #define TMK_ENT_INVALID 0xffffffffu
-#define TMK_ENT_PENDING 0xfefefefeu  // blk_ptr of a block the cluster pass has not reached yet (it runs beside the walk)
+#define TMK_ENT_NOSPEC 0xffffu
 struct TmkFast {
     const uint32_t* cblk_list;       // global ids of the blocks with candidates (appended by the scan kernels)
     unsigned int* cblk_count;
-    uint32_t* blk_ptr;               // per global block: (first entry << 6) | count, or TMK_ENT_INVALID
-    float* blk_gain;                 // per listed block: max_w (window energies of the block up to w) / S_w
+    uint2* blk_res;                  // per global block with candidates: x = (first entry << 6) | count, or TMK_ENT_INVALID;
+                                     // y = gain (float bits): max_w (window energies of the block up to w) / S_w
     TmkCandEntry* entries;
     uint32_t entry_cap;
     tmk_frame_rec* spec;             // speculative verdict records (payload already in the payload buffer)
@@ -169,14 +173,14 @@ int tmk_launch_cluster(const float* samples, const TmkStreamDev* streams, const 
 int tmk_launch_walk(const float* samples, const TmkStreamDev* streams, uint32_t s0, uint32_t s1, unsigned int* next,
                     TmkFast fast,
                     const TmkPattern* patterns, const float4* blk_info, const uint32_t* cand_bits,
-                    tmk_frame_rec* recs, uint32_t* rec_ord, uint64_t rec_cap, uint8_t* payload,
+                    tmk_frame_rec* recs, uint4* rec_ord, uint64_t rec_cap, uint8_t* payload,
                     uint64_t payload_cap, uint32_t* stream_cnt, TmkCounters* counters, TmkLinkState* link_out,
                     cudaStream_t st);
 int tmk_launch_replay_probe(const float* samples, const TmkStreamDev* streams, const TmkPattern* patterns, uint64_t seed,
                             const uint64_t* ws, uint32_t n, float* out, unsigned long long* counts, cudaStream_t st);
-int tmk_launch_order(const tmk_frame_rec* recs_in, const uint32_t* rec_ord, uint64_t n_recs,
+int tmk_launch_order(const tmk_frame_rec* recs_in, const uint4* rec_ord, uint64_t n_recs,
                      const uint32_t* stream_cnt, uint64_t* stream_base, uint32_t n_streams,
-                     tmk_frame_rec* recs_out, cudaStream_t st);
+                     const tmk_frame_rec* spec, tmk_frame_rec* recs_out, cudaStream_t st);
 int tmk_launch_excl_scan(const uint32_t* cnt, uint64_t* base, uint32_t n, cudaStream_t st);
 int tmk_walk_init();
 int tmk_walk_max_frame_bytes();

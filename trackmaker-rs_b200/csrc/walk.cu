@@ -54,6 +54,7 @@ static_assert(sizeof(WarpScratch) * kWarpsPerCta + 64 * 16 * kWarpsPerCta + 256 
 // One scratch per warp, at namespace scope so that every access compiles to LDS / STS (through a pointer
 // handed from function to function the accesses are generic loads: slower, and on the long scoreboard).
 __shared__ WarpScratch g_scratch[kWarpsPerCta];
+
 struct ScratchRef {
     uint32_t w;
     __device__ __forceinline__ WarpScratch* operator->() const { return &g_scratch[w]; }
@@ -67,9 +68,8 @@ struct Ctx {
     const TmkPattern* pat;
     const float4* blk_info;
     const uint32_t* cand_bits;
-    const uint32_t* blk_ptr;         // cluster pass results of this stream's blocks (nullptr: none)
+    const uint2* blk_res;            // cluster pass results of this stream's blocks (nullptr: none)
     const TmkCandEntry* entries;
-    const float* blk_gain;
     const tmk_frame_rec* spec;
     uint64_t nblk;
     float thr;
@@ -351,18 +351,15 @@ __device__ __noinline__ float roll_parallel(Ctx& c, float e, uint64_t* pos_io, u
         uint32_t below = kM, top = 0u, xr = 0u, hi = 0u;
         int32_t lo = 0x7fffffff;
         // samples as float4s (pos and P are multiples of 4 here, the stream base is 16-byte aligned): every load
-        // instruction touches 32 different lines, so the instruction count is what the L1 pays for
+        // instruction touches 32 different lines, so the instruction count is what the L1 pays for.
+        // (Tried in round 2: the samples through a per-lane cp.async ring in shared memory, four iterations ahead of
+        //  the chain — the 43 KB of dynamic shared memory per CTA come out of the L1 the rest of the walk lives on:
+        //  walk 2.9 -> 4.5 ms at C2. An L1 prefetch of the lines two ahead changed nothing.)
         const float4* __restrict__ xa = reinterpret_cast<const float4*>(xp);
         const float4* __restrict__ xb = reinterpret_cast<const float4*>(xp + P);
         float4 a0 = xa[0], a1 = xa[1], b0 = xb[0], b1 = xb[1];
         for (uint32_t k = 0; k < L; k += 8) {
             float4 an0 = a0, an1 = a1, bn0 = b0, bn1 = b1;
-            // every lane streams its own segment (32 different lines per load): the lines two ahead start their trip
-            // to L1 now, so the loads below find them there instead of waiting for L2 / HBM
-            if ((k & 31u) == 0u && k + 96 < L + P) {
-                asm volatile("prefetch.global.L1 [%0];" ::"l"(xp + k + 64));
-                asm volatile("prefetch.global.L1 [%0];" ::"l"(xp + k + 64 + P));
-            }
             if (k + 8 < L) {
                 an0 = xa[k / 4 + 2];
                 an1 = xa[k / 4 + 3];
@@ -528,6 +525,9 @@ struct Detection {
     uint64_t avail;  // samples buffered at that time
     float corr;      // reference correlation value of the detecting window
     uint32_t spec;   // speculative verdict record of the cluster pass for this window, or TMK_ENT_INVALID
+    // what the walk needs of that record to go on (from the candidate entry; status == TMK_ENT_NOSPEC: read the record)
+    uint32_t status, consumed, len;
+    uint64_t fs;
 };
 
 // Exact evaluation of window w (literal reference arithmetic). All lanes, uniform arguments.
@@ -608,39 +608,22 @@ __device__ __noinline__ void block_prefix(Ctx& c, uint64_t bb) {
     }
 }
 
-// ---- results of the cluster pass, which runs BESIDE the walk (other CTAs, other stream)
-// blk_ptr of a block with candidates: published by the cluster pass with a release store after its entries,
-// gain, speculative records and payload bytes. A walk that gets there first waits — bounded, so that a cluster
-// pass that cannot get an SM never stalls the walk for good: after the bound the block counts as "no cluster
-// result" and is evaluated by the walk itself (same results, more work). Everything the cluster pass wrote is
-// read through L2 (ld.cg): an L1 line of this SM may predate the write.
-__device__ __forceinline__ uint32_t ld_acquire_u32(const uint32_t* p) {
-    uint32_t v;
-    asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
-    return v;
-}
-__device__ __noinline__ uint32_t wait_blk_ptr(const Ctx& c, uint64_t bb) {
-    const uint32_t* p = c.blk_ptr + bb;
-    uint32_t v = 0;
-    if (c.lane == 0) {
-        v = ld_acquire_u32(p);
-        for (int it = 0; v == TMK_ENT_PENDING && it < 40000; ++it) {  // ~10 ms
-            __nanosleep(250);
-            v = ld_acquire_u32(p);
-        }
-        if (v == TMK_ENT_PENDING) v = TMK_ENT_INVALID;
-    }
-    return __shfl_sync(kFull, v, 0);
-}
+// ---- results of the cluster pass (it has finished when the walk of its chunk starts)
+// blk_res of a block with candidates: x = (first entry << 6) | count or TMK_ENT_INVALID, y = gain. Blocks without
+// candidates (blk_info.w == 0) have no result and are never looked up.
 __device__ __forceinline__ TmkCandEntry ld_entry(const TmkCandEntry* p) {
-    static_assert(sizeof(TmkCandEntry) == 16, "entry size");
-    const uint4 v = __ldcg(reinterpret_cast<const uint4*>(p));
+    static_assert(sizeof(TmkCandEntry) == 32, "entry size");
+    const uint4 v = __ldcg(reinterpret_cast<const uint4*>(p)), u = __ldcg(reinterpret_cast<const uint4*>(p) + 1);
     TmkCandEntry e;
     e.wl = uint16_t(v.x & 0xffffu);
-    e.flags = uint16_t(v.x >> 16);
+    e.status = uint16_t(v.x >> 16);
     e.D = __uint_as_float(v.y);
     e.Ec = __uint_as_float(v.z);
     e.spec = v.w;
+    e.consumed = u.x;
+    e.fs_off = int32_t(u.y);
+    e.len = u.z;
+    e.pad_ = 0;
     return e;
 }
 __device__ __forceinline__ tmk_frame_rec ld_spec(const tmk_frame_rec* p) {
@@ -655,9 +638,9 @@ __device__ __forceinline__ tmk_frame_rec ld_spec(const tmk_frame_rec* p) {
 
 // speculative verdict record the cluster pass prepared for window wl of block bb (or TMK_ENT_INVALID)
 __device__ __noinline__ uint32_t lookup_spec(const Ctx& c, uint64_t bb, uint32_t wl) {
-    if (c.blk_ptr == nullptr || c.P > uint32_t(kFastMaxP)) return TMK_ENT_INVALID;
-    if (c.blk_info[bb].w == 0.f) return TMK_ENT_INVALID;  // not on the cluster pass's list: never published
-    const uint32_t ptr = wait_blk_ptr(c, bb);
+    if (c.blk_res == nullptr || c.P > uint32_t(kFastMaxP)) return TMK_ENT_INVALID;
+    if (c.blk_info[bb].w == 0.f) return TMK_ENT_INVALID;  // not on the cluster pass's list: no result
+    const uint32_t ptr = __ldcg(c.blk_res + bb).x;
     if (ptr == TMK_ENT_INVALID) return TMK_ENT_INVALID;
     const uint32_t n = ptr & 63u;
     for (uint32_t r0 = 0; r0 < n; r0 += 32) {
@@ -775,6 +758,10 @@ __device__ __noinline__ bool process_block(Ctx& c, uint64_t bb, uint64_t q, uint
                 det->avail = avail_for(c, wj, avail);
                 det->corr = corr;
                 det->spec = lookup_spec(c, bb, uint32_t(wj - wb0));
+                det->status = TMK_ENT_NOSPEC;  // the walk reads the record itself
+                det->consumed = 0;
+                det->fs = 0;
+                det->len = 0;
                 return true;
             }
         }
@@ -798,8 +785,9 @@ __device__ __noinline__ bool process_block(Ctx& c, uint64_t bb, uint64_t q, uint
 //   avail     samples fed so far (chunked feeding: the seed of a window depends on it)
 __device__ __noinline__ int fast_block(Ctx& c, uint64_t bb, uint64_t q, float4 info, float nb, float smax, float racc_end,
                                        float racc_in, float efirst, float emin_lo, float pmax_in, uint64_t avail,
-                                       Detection* det) {
-    if (c.blk_ptr == nullptr || c.P > uint32_t(kFastMaxP) || c.a_w != c.a_seed || c.a_err != 0.f) return 2;
+                                       uint2 res, Detection* det) {
+    // res: blk_res of the block (loaded by the caller together with the summaries; meaningful when info.w != 0)
+    if (c.blk_res == nullptr || c.P > uint32_t(kFastMaxP) || c.a_w != c.a_seed || c.a_err != 0.f) return 2;
     const float silent = 0.5f * c.thr * c.thr * 1e-6f;
     if (info.y < silent) return 0;  // every window is gated or cannot reach the threshold (as in search())
     const uint64_t wb0 = bb * TMK_BLK;
@@ -809,7 +797,7 @@ __device__ __noinline__ int fast_block(Ctx& c, uint64_t bb, uint64_t q, float4 i
     const float dscan = kScanErr * nb;
     // the bound of a window of energy S is  d_abs + d_rel * S
     float d_abs, d_rel = 2.5f * kU;
-    uint32_t ptr = TMK_ENT_PENDING;
+    const uint32_t ptr = info.w != 0.f ? res.x : TMK_ENT_INVALID;
     if (c.C != 0) {
         // Chunked feeding: every process_samples call re-seeds the rolling energy (decoder.rs:133-136), so the chain
         // of a window has at most C + P steps, all of them over windows in [q, w] (a search never starts before q).
@@ -822,9 +810,8 @@ __device__ __noinline__ int fast_block(Ctx& c, uint64_t bb, uint64_t q, float4 i
         d_abs = per * smax;
         if (!(d_abs + dscan <= kTight * emin_lo) || !(d_abs <= 3.0e38f) || !(dscan <= 3.0e38f)) {
             if (info.w == 0.f || !(pmax_in >= 0.f)) return 2;
-            ptr = wait_blk_ptr(c, bb);
             if (ptr == TMK_ENT_INVALID) return 2;
-            const float mgain = __ldcg(c.blk_gain + bb);
+            const float mgain = __uint_as_float(res.y);
             const float hist = per * pmax_in;
             const float rel = per * mgain + 2.5f * kU;
             if (!(hist + dscan <= 0.5f * kTight * emin_lo) || !(rel <= 0.5f * kTight)) return 2;
@@ -844,9 +831,8 @@ __device__ __noinline__ int fast_block(Ctx& c, uint64_t bb, uint64_t q, float4 i
         // window the sum form is  u (1.5 P S_seed + 2.2 (racc_in + B_w)),  B_w = the window energies of
         // this block up to w; the cluster pass measured  gain >= B_w / S_w  for every window of the block.
         if (info.w == 0.f || !(racc_in >= 0.f)) return 2;
-        ptr = wait_blk_ptr(c, bb);
         if (ptr == TMK_ENT_INVALID) return 2;
-        const float gain = __ldcg(c.blk_gain + bb);
+        const float gain = __uint_as_float(res.y);
         const float hist = kU * (1.5f * float(c.P) * efirst + 2.2f * racc_in) * growth;
         const float rel = 2.2f * kU * growth * gain + 2.5f * kU;
         if (!(hist + dscan <= 0.5f * kTight * emin_lo) || !(rel <= 0.5f * kTight)) return 2;
@@ -855,12 +841,11 @@ __device__ __noinline__ int fast_block(Ctx& c, uint64_t bb, uint64_t q, float4 i
     }
     }
     if (info.w == 0.f) return 0;
-    if (ptr == TMK_ENT_PENDING) ptr = wait_blk_ptr(c, bb);
     if (ptr == TMK_ENT_INVALID) return 2;
     const uint32_t n = ptr & 63u;
     for (uint32_t r0 = 0; r0 < n; r0 += 32) {
         TmkCandEntry e;
-        e.wl = 0; e.flags = 0; e.D = 0.f; e.Ec = 0.f; e.spec = TMK_ENT_INVALID;
+        e.wl = 0; e.status = TMK_ENT_NOSPEC; e.D = 0.f; e.Ec = 0.f; e.spec = TMK_ENT_INVALID; e.consumed = 0; e.fs_off = 0; e.len = 0;
         if (r0 + uint32_t(c.lane) < n) e = ld_entry(c.entries + (ptr >> 6) + r0 + c.lane);
         const uint64_t w = wb0 + e.wl;
         const bool valid = r0 + uint32_t(c.lane) < n && w >= q && w < c.nwin;
@@ -891,6 +876,10 @@ __device__ __noinline__ int fast_block(Ctx& c, uint64_t bb, uint64_t q, float4 i
                 det->avail = avail_for(c, wj, avail);
                 det->corr = corr;
                 det->spec = sj;
+                det->status = __shfl_sync(kFull, uint32_t(e.status), j);
+                det->consumed = __shfl_sync(kFull, e.consumed, j);
+                det->fs = wj + int64_t(__shfl_sync(kFull, e.fs_off, j));
+                det->len = __shfl_sync(kFull, e.len, j);
                 return 1;
             }
         }
@@ -913,8 +902,18 @@ __device__ __noinline__ bool search(Ctx& c, uint64_t q, uint64_t avail, Detectio
     // enter; otherwise the block is examined window by window.
     uint64_t b0 = q / TMK_BLK;
     float racc = 0.f, efirst = 0.f;  // sum / seed-window bounds of the chain (see fast_block)
+    // the summaries and cluster results of the first group of blocks behind the one that holds q start their trip
+    // now, together with those of that block: one memory round trip instead of two
+    const uint64_t pre_b = b0 + 1;
+    float4 pre_info = make_float4(0.f, 0.f, 0.f, 0.f);
+    uint2 pre_res = make_uint2(TMK_ENT_INVALID, 0u);
+    if (pre_b + lane < c.nblk) {
+        pre_info = c.blk_info[pre_b + lane];
+        if (c.blk_res != nullptr) pre_res = __ldcg(c.blk_res + pre_b + lane);
+    }
     {
         const float4 i0 = c.blk_info[b0];
+        const uint2 res0 = c.blk_res != nullptr ? __ldcg(c.blk_res + b0) : make_uint2(TMK_ENT_INVALID, 0u);
         float nb0 = i0.y;
         if (b0 > 0) nb0 = max_nan(nb0, c.blk_info[b0 - 1].y);
         if (b0 + 1 < c.nblk) nb0 = max_nan(nb0, c.blk_info[b0 + 1].y);
@@ -928,11 +927,11 @@ __device__ __noinline__ bool search(Ctx& c, uint64_t q, uint64_t avail, Detectio
         // bounds of the whole gap behind it, so it goes straight to the exact energies)
         int r = 2;
         if (!(i0.y > float(TMK_CONTRAST) * i0.x)) {
-            r = fast_block(c, b0, q, i0, nb0, i0.y * 1.001f, racc, 0.f, efirst, i0.x - dscan0, 0.f, avail, det);
+            r = fast_block(c, b0, q, i0, nb0, i0.y * 1.001f, racc, 0.f, efirst, i0.x - dscan0, 0.f, avail, res0, det);
             if (r == 1) return true;
             if (r == 0) runmax = i0.y * 1.001f;
         }
-        if (r == 2 && c.blk_ptr != nullptr && c.P <= uint32_t(kFastMaxP)) {
+        if (r == 2 && c.blk_res != nullptr && c.P <= uint32_t(kFastMaxP)) {
             // 2. exact energies of the windows [q, end of block] (one block load): sum, maximum, minimum
             block_prefix(c, b0);
             const uint32_t lo = uint32_t(q - b0 * TMK_BLK), hi = uint32_t(wl0 - b0 * TMK_BLK);
@@ -952,7 +951,7 @@ __device__ __noinline__ bool search(Ctx& c, uint64_t q, uint64_t avail, Detectio
             }
             eq = __shfl_sync(kFull, eq, 0);
             const float racc_x = es * 1.0001f;
-            r = fast_block(c, b0, q, i0, nb0, emx * 1.0001f, racc_x, 0.f, eq * 1.0001f, emn * 0.9999f, 0.f, avail, det);
+            r = fast_block(c, b0, q, i0, nb0, emx * 1.0001f, racc_x, 0.f, eq * 1.0001f, emn * 0.9999f, 0.f, avail, res0, det);
             if (r == 1) return true;
             if (r == 0) {
                 runmax = emx * 1.0001f;
@@ -972,9 +971,15 @@ __device__ __noinline__ bool search(Ctx& c, uint64_t q, uint64_t avail, Detectio
         const uint64_t bb = b0 + lane;
         const bool valid = bb < c.nblk;
         float4 info = make_float4(0.f, 0.f, 0.f, 0.f);
+        uint2 res = make_uint2(TMK_ENT_INVALID, 0u);
         bool any = false;
-        if (valid) {
+        if (b0 == pre_b) {  // the group that was requested at the entry of the search
+            info = pre_info;
+            res = pre_res;
+            any = valid && info.w != 0.f;
+        } else if (valid) {
             info = c.blk_info[bb];
+            if (c.blk_res != nullptr) res = __ldcg(c.blk_res + bb);
             any = info.w != 0.f;
         }
         // neighbourhood maximum (blocks bb-1 .. bb+1) for the scan kernel's own approximation error
@@ -1045,8 +1050,11 @@ __device__ __noinline__ bool search(Ctx& c, uint64_t q, uint64_t avail, Detectio
             const float nbj = __shfl_sync(kFull, nb, j);
             const float racc_end_j = racc + __shfl_sync(kFull, cincl, j);
             const float racc_in_j = racc_end_j - __shfl_sync(kFull, contrib, j);
+            uint2 rj;
+            rj.x = __shfl_sync(kFull, res.x, j);
+            rj.y = __shfl_sync(kFull, res.y, j);
             const int r = fast_block(c, b0 + j, q, ij, nbj, max_nan(pmax_j, ij.y * 1.001f), racc_end_j, racc_in_j, efirst,
-                                     ij.x - kScanErr * nbj, pmax_j, avail, det);
+                                     ij.x - kScanErr * nbj, pmax_j, avail, rj, det);
             if (r == 1) return true;
             if (r == 0) {
                 runmax = max_nan(pmax_j, ij.y * 1.001f);
@@ -1347,23 +1355,35 @@ __device__ uint32_t crc8_warp(const uint8_t* bytes, uint32_t n, int lane) {
 // ---------------------------------------------------------------- verdict records
 struct Emit {
     tmk_frame_rec* recs;
-    uint32_t* rec_ord;
+    uint4* rec_ord;  // per record slot: (speculative record to gather or TMK_ENT_INVALID, order in the stream, stream, corr)
     uint64_t rec_cap;
     uint8_t* payload;
     uint64_t payload_cap;
     TmkCounters* counters;
     uint32_t stream;
     uint32_t ord;  // records emitted by this stream so far
+    // record slots are reserved 32 at a time per warp (one atomic per 32 records instead of one per record); the
+    // slots a warp leaves unused are marked in rec_ord (kNoRecord) and skipped by the ordering kernel
+    unsigned long long slot_cur, slot_end;
 };
+constexpr uint32_t kNoRecord = 0xffffffffu;
+
+__device__ __forceinline__ unsigned long long take_slot(int lane, Emit& em) {
+    if (em.slot_cur == em.slot_end) {
+        unsigned long long base = 0;
+        if (lane == 0) base = atomicAdd(&em.counters->n_recs, 32ull);
+        base = __shfl_sync(kFull, base, 0);
+        em.slot_cur = base;
+        em.slot_end = base + 32;
+    }
+    return em.slot_cur++;
+}
 
 __device__ __noinline__ void emit(const Ctx& c, Emit& em, uint32_t status, const Detection& d, uint64_t frame_start,
                      uint32_t consumed, bool have_hdr, const uint8_t* hdr, uint32_t data_len) {
-    unsigned long long slot = 0, poff = 0;
-    if (c.lane == 0) {
-        slot = atomicAdd(&em.counters->n_recs, 1ull);
-        if (data_len) poff = atomicAdd(&em.counters->n_payload, (unsigned long long)data_len);
-    }
-    slot = __shfl_sync(kFull, slot, 0);
+    const unsigned long long slot = take_slot(c.lane, em);
+    unsigned long long poff = 0;
+    if (c.lane == 0 && data_len) poff = atomicAdd(&em.counters->n_payload, (unsigned long long)data_len);
     poff = __shfl_sync(kFull, poff, 0);
     if (data_len && poff + data_len <= em.payload_cap) {
         for (uint32_t i = c.lane; i < data_len; i += 32) em.payload[poff + i] = c.sc->bytes[TMK_PHY_HEADER_BYTES + i];
@@ -1385,7 +1405,7 @@ __device__ __noinline__ void emit(const Ctx& c, Emit& em, uint32_t status, const
         r.dst = have_hdr ? hdr[6] : 0;
         r.hdr_valid = have_hdr ? 1 : 0;
         em.recs[slot] = r;
-        em.rec_ord[slot] = em.ord;
+        em.rec_ord[slot] = make_uint4(TMK_ENT_INVALID, em.ord, em.stream, __float_as_uint(d.corr));
     }
     em.ord++;
 }
@@ -1401,9 +1421,8 @@ __device__ __forceinline__ void init_ctx(Ctx& c, const float* samples, const Tmk
     c.C = (sd.chunk == 0 || sd.chunk >= c.N) ? 0 : sd.chunk;
     c.blk_info = blk_info + sd.blk_base;
     c.cand_bits = cand_bits + sd.blk_base * TMK_BLK_WORDS;
-    c.blk_ptr = f.blk_ptr ? f.blk_ptr + sd.blk_base : nullptr;
+    c.blk_res = f.blk_res ? f.blk_res + sd.blk_base : nullptr;
     c.entries = f.entries;
-    c.blk_gain = f.blk_gain ? f.blk_gain + sd.blk_base : nullptr;
     c.spec = f.spec;
     c.nblk = (c.nwin + TMK_BLK - 1) / TMK_BLK;
     c.thr = sd.threshold;
@@ -1513,11 +1532,9 @@ __device__ __noinline__ void spec_decode(Ctx& c, uint64_t w, float corr, uint32_
     __syncwarp();
 }
 
-// release store of a block's result word: everything the warp wrote for the block (entries, gain, speculative
-// records, payload bytes) is visible to a walk that acquires the word
-__device__ __forceinline__ void publish_blk(uint32_t* p, uint32_t v) {
-    __threadfence();
-    asm volatile("st.release.gpu.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+// result word of a block: the walk of the chunk starts when this kernel has finished, so plain stores suffice
+__device__ __forceinline__ void publish_blk(uint2* p, uint32_t v, float gain) {
+    *p = make_uint2(v, __float_as_uint(gain));
 }
 
 // One warp per block with candidates: exact dot product and accurate energy of every candidate window, and a
@@ -1550,7 +1567,7 @@ cluster_kernel(const float* __restrict__ samples, const TmkStreamDev* __restrict
         init_ctx(c, samples, sd, patterns, blk_info, cand_bits, f, lane, warp);
         const uint64_t bb = uint64_t(gb) - sd.blk_base;
         if (c.P > uint32_t(kFastMaxP)) {  // long preambles keep the walk's own evaluation
-            if (lane == 0) publish_blk(f.blk_ptr + gb, TMK_ENT_INVALID);
+            if (lane == 0) publish_blk(f.blk_res + gb, TMK_ENT_INVALID, 0.f);
             continue;
         }
         const uint64_t wb0 = bb * TMK_BLK;
@@ -1566,7 +1583,11 @@ cluster_kernel(const float* __restrict__ samples, const TmkStreamDev* __restrict
             const bool valid = ((word >> lane) & 1u) && w < c.nwin;
             TmkCandEntry e;
             e.wl = uint16_t(wl);
-            e.flags = 0;
+            e.status = TMK_ENT_NOSPEC;
+            e.consumed = 0;
+            e.fs_off = 0;
+            e.len = 0;
+            e.pad_ = 0;
             e.D = 0.f;
             e.Ec = 0.f;
             e.spec = TMK_ENT_INVALID;
@@ -1594,7 +1615,7 @@ cluster_kernel(const float* __restrict__ samples, const TmkStreamDev* __restrict
         }
         __syncwarp();
         if (n_ent > 63) {
-            if (lane == 0) publish_blk(f.blk_ptr + gb, TMK_ENT_INVALID);
+            if (lane == 0) publish_blk(f.blk_res + gb, TMK_ENT_INVALID, 0.f);
             continue;
         }
         // gain = max over the block's windows of (sum of the window energies of the block up to w) / S_w,
@@ -1687,11 +1708,18 @@ cluster_kernel(const float* __restrict__ samples, const TmkStreamDev* __restrict
             sp = __shfl_sync(kFull, sp, 0);
             if (sp >= f.spec_cap) break;  // pool exhausted: the walk decodes the rest itself
             spec_decode(c, w, corr, sidx, f.spec + sp, payload, payload_cap, counters);
-            if (lane == 0) ents[warp][i].spec = sp;
             __syncwarp();
             const tmk_frame_rec* r = f.spec + sp;
             const uint32_t st = __shfl_sync(kFull, lane == 0 ? r->status : 0u, 0);
             const uint32_t cons = __shfl_sync(kFull, lane == 0 ? r->consumed : 0u, 0);
+            if (lane == 0) {  // what a walk needs to go on without reading the record
+                ents[warp][i].spec = sp;
+                ents[warp][i].status = uint16_t(st);
+                ents[warp][i].consumed = cons;
+                ents[warp][i].fs_off = int32_t(int64_t(r->frame_start) - int64_t(w));
+                ents[warp][i].len = r->len;
+            }
+            __syncwarp();
             if (st == TMK_FRAME_TRUNCATED) break;
             skip_until = w + cons;
         }
@@ -1700,16 +1728,12 @@ cluster_kernel(const float* __restrict__ samples, const TmkStreamDev* __restrict
         if (lane == 0) base = n_ent ? atomicAdd(&f.pool[0], n_ent) : 0u;
         base = __shfl_sync(kFull, base, 0);
         if (base + n_ent > f.entry_cap || base + n_ent >= (1u << 26)) {
-            if (lane == 0) publish_blk(f.blk_ptr + gb, TMK_ENT_INVALID);
+            if (lane == 0) publish_blk(f.blk_res + gb, TMK_ENT_INVALID, 0.f);
             continue;
         }
         for (uint32_t i = lane; i < n_ent; i += 32) f.entries[base + i] = ents[warp][i];
         __syncwarp();
-        if (lane == 0) {
-            f.blk_gain[gb] = gain;
-            const uint32_t v = (base << 6) | n_ent;
-            publish_blk(f.blk_ptr + gb, v == TMK_ENT_PENDING ? TMK_ENT_INVALID : v);
-        }
+        if (lane == 0) publish_blk(f.blk_res + gb, (base << 6) | n_ent, gain);
     }
 }
 
@@ -1723,22 +1747,28 @@ __global__ void __launch_bounds__(kWarpsPerCta * 32, TMK_WALK_CTAS)
 walk_kernel(const float* __restrict__ samples, const TmkStreamDev* __restrict__ streams, uint32_t s0, uint32_t s1,
             unsigned int* __restrict__ next, TmkFast fast,
             const TmkPattern* __restrict__ patterns, const float4* __restrict__ blk_info,
-            const uint32_t* __restrict__ cand_bits, tmk_frame_rec* recs, uint32_t* rec_ord, uint64_t rec_cap,
+            const uint32_t* __restrict__ cand_bits, tmk_frame_rec* recs, uint4* rec_ord, uint64_t rec_cap,
             uint8_t* payload, uint64_t payload_cap, uint32_t* stream_cnt, TmkCounters* counters,
             TmkLinkState* link_out) {
     const uint32_t warp = threadIdx.x >> 5;
     const int lane_id = threadIdx.x & 31;
+    Emit em{recs, rec_ord, rec_cap, payload, payload_cap, counters, 0, 0, 0ull, 0ull};
     // persistent warps: streams differ a lot in cost (idle noise vs dense traffic), so every warp
     // pulls the next stream from a counter instead of owning a fixed one
     for (;;) {
     uint32_t sidx = 0;
     if (lane_id == 0) sidx = s0 + atomicAdd(next, 1u);
     sidx = __shfl_sync(kFull, sidx, 0);
-    if (sidx >= s1) return;
+    if (sidx >= s1) {
+        for (unsigned long long sl = em.slot_cur + lane_id; sl < em.slot_end; sl += 32)  // reserved, never used
+            if (sl < rec_cap) rec_ord[sl].y = kNoRecord;
+        return;
+    }
     const TmkStreamDev sd = streams[sidx];
     Ctx c;
     init_ctx(c, samples, sd, patterns, blk_info, cand_bits, fast, lane_id, warp);
-    Emit em{recs, rec_ord, rec_cap, payload, payload_cap, counters, sidx, 0};
+    em.stream = sidx;
+    em.ord = 0;
     uint32_t n_ok = 0, n_crc = 0, n_hdr = 0, n_nfu = 0;
 
     const int lc = c.pat->line_code;
@@ -1778,34 +1808,35 @@ walk_kernel(const float* __restrict__ samples, const TmkStreamDev* __restrict__ 
             // least `margin` samples before `expect` and, with chunked feeding, the samples fed when the window
             // was examined reach `expect + margin + sync_len`, decoder.rs:179-181): link the verdict, payload
             // bytes are in place
-            tmk_frame_rec r = ld_spec(c.spec + d.spec);
-            if (c.C != 0 && r.status != TMK_FRAME_TRUNCATED) {
+            if (d.status == TMK_ENT_NOSPEC) {  // found through the window-by-window path: the summary is in the record
+                const tmk_frame_rec r = ld_spec(c.spec + d.spec);
+                d.status = r.status;
+                d.fs = r.frame_start;
+                d.consumed = r.consumed;
+                d.len = r.len;
+            }
+            if (c.C != 0 && d.status != TMK_FRAME_TRUNCATED) {
                 // decode_frame waited for the header, then for the whole frame (decoder.rs:248-254, 289-297)
-                const bool hdr_only = r.status == TMK_FRAME_HDR_PARSE || r.status == TMK_FRAME_BAD_LEN;
-                const uint64_t need = r.frame_start + (hdr_only ? uint64_t(hs) : tmk_sfb(lc, spl, (TMK_PHY_HEADER_BYTES + uint64_t(r.len)) * 8));
+                const bool hdr_only = d.status == TMK_FRAME_HDR_PARSE || d.status == TMK_FRAME_BAD_LEN;
+                const uint64_t need = d.fs + (hdr_only ? uint64_t(hs) : tmk_sfb(lc, spl, (TMK_PHY_HEADER_BYTES + uint64_t(d.len)) * 8));
                 while (avail < need && avail < c.N) avail = avail + c.C < c.N ? avail + c.C : c.N;
             }
-            unsigned long long slot = 0;
-            if (c.lane == 0) slot = atomicAdd(&counters->n_recs, 1ull);
-            slot = __shfl_sync(kFull, slot, 0);
-            if (c.lane == 0 && slot < rec_cap) {
-                r.stream = sidx;
-                r.corr = d.corr;
-                recs[slot] = r;
-                rec_ord[slot] = em.ord;
+            {   // the verdict is LINKED, not copied: the ordering kernel gathers the record from the speculative pool
+                const unsigned long long slot = take_slot(c.lane, em);
+                if (c.lane == 0 && slot < rec_cap) rec_ord[slot] = make_uint4(d.spec, em.ord, sidx, __float_as_uint(d.corr));
             }
             em.ord++;
-            if (r.status == TMK_FRAME_OK) n_ok++;
-            else if (r.status == TMK_FRAME_CRC_FAIL) n_crc++;
-            else if (r.status == TMK_FRAME_NOT_FOR_US) n_nfu++;
-            else if (r.status != TMK_FRAME_TRUNCATED) n_hdr++;
-            if (r.status == TMK_FRAME_TRUNCATED) {
+            if (d.status == TMK_FRAME_OK) n_ok++;
+            else if (d.status == TMK_FRAME_CRC_FAIL) n_crc++;
+            else if (d.status == TMK_FRAME_NOT_FOR_US) n_nfu++;
+            else if (d.status != TMK_FRAME_TRUNCATED) n_hdr++;
+            if (d.status == TMK_FRAME_TRUNCATED) {
                 fin.off = d.c;
-                fin.fs = r.frame_start;
+                fin.fs = d.fs;
                 fin.corr = d.corr;
                 break;
             }
-            q = d.c + r.consumed;
+            q = d.c + d.consumed;
             continue;
         }
         {   // pull the head of the frame towards L2 while the refinement and the header decode run
@@ -1940,12 +1971,17 @@ scan_counts_kernel(const uint32_t* __restrict__ cnt, uint64_t* __restrict__ base
     if (threadIdx.x == 0) base[n] = carry_s;
 }
 
-__global__ void order_kernel(const tmk_frame_rec* __restrict__ in, const uint32_t* __restrict__ ord, uint64_t n,
-                             const uint64_t* __restrict__ base, tmk_frame_rec* __restrict__ out) {
+__global__ void order_kernel(const tmk_frame_rec* __restrict__ in, const uint4* __restrict__ ord, uint64_t n,
+                             const uint64_t* __restrict__ base, const tmk_frame_rec* __restrict__ spec,
+                             tmk_frame_rec* __restrict__ out) {
     const uint64_t i = uint64_t(blockIdx.x) * blockDim.x + threadIdx.x;
     if (i >= n) return;
-    const tmk_frame_rec r = in[i];
-    out[base[r.stream] + ord[i]] = r;
+    const uint4 ln = ord[i];
+    if (ln.y == kNoRecord) return;  // a slot some warp reserved and never used
+    tmk_frame_rec r = ln.x != TMK_ENT_INVALID ? spec[ln.x] : in[i];  // linked verdict of the cluster pass | the walk's own
+    r.stream = ln.z;
+    r.corr = __uint_as_float(ln.w);
+    out[base[ln.z] + ln.y] = r;
 }
 
 }  // namespace
@@ -2016,7 +2052,7 @@ int tmk_launch_cluster(const float* samples, const TmkStreamDev* streams, const 
 int tmk_launch_walk(const float* samples, const TmkStreamDev* streams, uint32_t s0, uint32_t s1, unsigned int* next,
                     TmkFast fast,
                     const TmkPattern* patterns, const float4* blk_info, const uint32_t* cand_bits,
-                    tmk_frame_rec* recs, uint32_t* rec_ord, uint64_t rec_cap, uint8_t* payload,
+                    tmk_frame_rec* recs, uint4* rec_ord, uint64_t rec_cap, uint8_t* payload,
                     uint64_t payload_cap, uint32_t* stream_cnt, TmkCounters* counters, TmkLinkState* link_out,
                     cudaStream_t st) {
     if (s1 <= s0) return 0;
@@ -2042,12 +2078,12 @@ int tmk_launch_replay_probe(const float* samples, const TmkStreamDev* streams, c
     return 1;
 }
 
-int tmk_launch_order(const tmk_frame_rec* recs_in, const uint32_t* rec_ord, uint64_t n_recs,
+int tmk_launch_order(const tmk_frame_rec* recs_in, const uint4* rec_ord, uint64_t n_recs,
                      const uint32_t* stream_cnt, uint64_t* stream_base, uint32_t n_streams,
-                     tmk_frame_rec* recs_out, cudaStream_t st) {
+                     const tmk_frame_rec* spec, tmk_frame_rec* recs_out, cudaStream_t st) {
     tmk_launch_excl_scan(stream_cnt, stream_base, n_streams, st);
     if (n_recs == 0) return 1;
     const uint32_t grid = uint32_t((n_recs + 255) / 256);
-    order_kernel<<<grid, 256, 0, st>>>(recs_in, rec_ord, n_recs, stream_base, recs_out);
+    order_kernel<<<grid, 256, 0, st>>>(recs_in, rec_ord, n_recs, stream_base, spec, recs_out);
     return 2;
 }
