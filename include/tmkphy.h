@@ -190,6 +190,19 @@ int tmk_replay_probe(tmk_engine* e, const float* samples, uint64_t n_samples, co
 int tmk_channel_busy(tmk_engine* e, const float* samples, uint64_t total_samples, const tmk_stream* streams,
                      uint32_t n_streams, int8_t* busy);
 
+/* The same result for callers that may not allocate device memory (code under CUDA graph capture, tight serving
+ * loops, harnesses that forbid cudaMalloc). No counterpart in the reference.
+ * All device scratch (stream descriptors, one flag per stream, a staging row for host results) lives in
+ * one static __device__ array of the library, sized for TMK_NOALLOC_MAX_STREAMS streams (84 KB per GPU, held until
+ * the process exits); the call issues no cudaMalloc / cudaFree / cudaMallocHost. `samples` must be DEVICE memory
+ * (staging a host buffer would allocate); `streams` is a host array; `busy` may be host or device. More than
+ * TMK_NOALLOC_MAX_STREAMS streams -> TMK_E_CAPACITY (nothing is computed). Every call on a GPU shares the array,
+ * which keeps the last call's contents (the call clears what it needs at zero): calls that overlapped on the GPU
+ * would race on it, so the entry point serialises its callers and returns only when its stream has drained. */
+#define TMK_NOALLOC_MAX_STREAMS 4096
+int tmk_channel_busy_noalloc(tmk_engine* e, const float* samples, uint64_t total_samples, const tmk_stream* streams,
+                             uint32_t n_streams, int8_t* busy);
+
 int tmk_stats(tmk_engine* e, uint64_t counters[TMK_STAT_COUNT]);
 int tmk_stats_reset(tmk_engine* e);
 /* Diagnostic counters of the walk kernel of the last tmk_decode_batch call: [0] blocks examined window by

@@ -396,6 +396,14 @@ class Engine:
         self._check(self._lib.tmk_channel_busy(self._h, _ptr(s), s.size, _ptr(st), len(st), _ptr(out)))
         return out
 
+    def channel_busy_noalloc(self, device_ptr, total_samples, streams):
+        """tmk_channel_busy_noalloc: samples resident at `device_ptr`; all device scratch is the library's static array"""
+        st = np.ascontiguousarray(streams, dtype=STREAM_DTYPE)
+        out = np.zeros(len(st), np.int8)
+        self._check(self._lib.tmk_channel_busy_noalloc(self._h, C.c_void_p(device_ptr), int(total_samples), _ptr(st), len(st),
+                                                       _ptr(out)))
+        return out
+
     def synth_batch(self, cfg, seed, n_streams, n_per_stream, snr_db, amplitude=1.0, device_ptr=None,
                     want_truth=True):
         """Synthetic captures. Returns (samples or None when device_ptr is given, truth records)."""

@@ -14,6 +14,7 @@ FRAME_TYPE_DATA = 1
 FRAME_TYPE_ACK = 2
 
 OK, E_INVALID, E_CUDA, E_CAPACITY, E_NOMEM = 0, -1, -2, -3, -4
+NOALLOC_MAX_STREAMS = 4096  # TMK_NOALLOC_MAX_STREAMS
 (FRAME_OK, FRAME_HDR_PARSE, FRAME_BAD_LEN, FRAME_SHORT_DECODE, FRAME_NOT_FOR_US, FRAME_CRC_FAIL,
  FRAME_TRUNCATED) = range(7)
 STATUS_NAMES = ["OK", "HDR_PARSE", "BAD_LEN", "SHORT_DECODE", "NOT_FOR_US", "CRC_FAIL", "TRUNCATED"]
@@ -100,6 +101,7 @@ SYMBOLS = {
     "tmk_scan_dot_probe": (C.c_int, [_vp, _vp, _u64, _vp, _u32, _vp]),
     "tmk_replay_probe": (C.c_int, [_vp, _vp, _u64, _pcfg, _u64, _vp, _u32, _vp, _pu64]),
     "tmk_channel_busy": (C.c_int, [_vp, _vp, _u64, _vp, _u32, _vp]),
+    "tmk_channel_busy_noalloc": (C.c_int, [_vp, _vp, _u64, _vp, _u32, _vp]),
     "tmk_stats": (C.c_int, [_vp, _pu64]),
     "tmk_stats_reset": (C.c_int, [_vp]),
     "tmk_debug_counters": (C.c_int, [_vp, _pu64]),
