@@ -14,7 +14,8 @@ samples each, 7.86 GB of fp32), src/phy 4B5B frames at random offsets, AWGN SNR 
                records compared bit for bit with the GPU's
   configs      every other BASELINE config at its stated size, each with Msamples/s, stage times, the fraction of
                the HBM roofline of the whole step, and bit-exact parity against the oracle on a bounded sample:
-               C2 Manchester, C2 fed in 1200-sample process_samples calls, C3 (16 384 x 2^20, multipath),
+               C2 Manchester, C2 fed in 1200-sample process_samples calls, C3 (16 384 x 2^20, multipath) for the
+               src/phy line codes AND for the FSK / OFDM demodulation on the batched FFT (build-defined spec),
                C4 (8 hour-long captures with clock drift), C5 (131 072 mixed-modulation streams x 2^18, sharded
                over the ranks: the strong-scaling leg)
 
@@ -275,6 +276,75 @@ def ask_leg(eng, tmkphy, orc, d_x, n_s, n_per, hbm, check_streams=8):
     return res
 
 
+def mcm_leg(eng, orc, tmkphy, hbm, n_s, n_per, check_streams=4):
+    """BASELINE config 3 as worded: FSK / OFDM demodulation with the batched FFT over n_s captures x n_per samples
+    (half FSK, half OFDM), 3-tap multipath + AWGN sweep. Build-defined specification (the reference has no FSK / OFDM /
+    FFT code): parity is against the build's own oracle and is UNPINNED by the reference."""
+    try:
+        d_x = eng.device_alloc(n_s * n_per * 4)
+    except tmkphy.TmkError:
+        return {"skipped": f"cannot allocate {n_s * n_per * 4 / 1e9:.1f} GB"}
+    half = n_s // 2
+    per_g = max(1, half // len(SNRS))
+    planted = [0, 0]
+    for m in (0, 1):
+        g0 = 0
+        for g, snr in enumerate(SNRS):
+            cnt = per_g if g + 1 < len(SNRS) else half - g0
+            cnt = min(cnt, half - g0)
+            if cnt <= 0:
+                break
+            _, nf = eng.mcm_synth_batch(m, 0xC3F0 + 16 * m + g, cnt, n_per, snr, multipath=True,
+                                        device_ptr=d_x + (m * half + g0) * n_per * 4)
+            planted[m] += nf
+            g0 += cnt
+    st, tot = tmkphy.make_streams([n_per] * half, tmkphy.make_config(1))
+    cap = tot // 5000 + 2 * half
+    res = {"workload": f"C3 (FSK/OFDM wording): {n_s} captures x {n_per} samples, {half} FSK + {half} OFDM frames streams, "
+                       "multipath h = [1, 0.35 @ t1, -0.2 @ t2] + AWGN sweep -3..30 dB; chirp sync (examples/ask.rs) + "
+                       "batched shared-memory FFT demodulation, symbol decision, CRC-8",
+           "parity_pinned_by_reference": False, "modes": {}}
+    total_ms, ok_all = 0.0, True
+    for m, name in ((0, "fsk"), (1, "ofdm")):
+        base = d_x + m * half * n_per * 4
+        recs, pl = eng.mcm_decode_batch(m, base, st, rec_cap=cap, total_samples=tot)  # warm-up
+        ms = []
+        for _ in range(2):
+            recs, pl = eng.mcm_decode_batch(m, base, st, rec_cap=cap, total_samples=tot)
+            ms.append(eng.mcm_last_stage_ms())
+        stage = {k: float(np.median([x[k] for x in ms])) for k in ("filter", "walk", "demod")}
+        t = sum(stage.values())
+        total_ms += t
+        r = {"msamples_per_s": tot / t / 1e3, "stage_ms": {k: round(v, 3) for k, v in stage.items()},
+             "frames_planted": planted[m], "records": int(len(recs)), "frames_ok": int((recs["status"] == 0).sum()),
+             "payload_bytes": int(len(pl)),
+             "demod_ffts": int(len(recs)) * (56 if m == 0 else 14), "fft_points": 64 if m == 0 else 256}
+        if orc is not None:
+            same = True
+            for i in np.unique(np.linspace(0, half - 1, check_streams).astype(np.int64)):
+                x = np.zeros(n_per, np.float32)
+                eng.d2h(x, base + int(i) * n_per * 4)
+                want, wpl = orc.mcm_demodulate(m, x, stream=int(i))
+                got = recs[recs["stream"] == i]
+                same = same and len(got) == len(want) and all(
+                    np.array_equal(got[f], want[f]) for f in ("stream", "status", "start_index", "seq", "len", "crc"))
+                if same:
+                    gp = b"".join(bytes(pl[int(a["payload_off"]):int(a["payload_off"]) + int(a["len"])]) for a in got if a["status"] != 2)
+                    same = gp == bytes(wpl)
+            r["parity"] = "bit-exact vs the build's own oracle" if same else "MISMATCH"
+            r["parity_sample"] = f"{check_streams} captures"
+            ok_all = ok_all and same
+        res["modes"][name] = r
+    res["msamples_per_s"] = n_s * n_per / total_ms / 1e3
+    res["ms_per_step"] = total_ms
+    res["frac_hbm"] = 4.0 * n_s * n_per / (total_ms * 1e-3) / 1e9 / hbm
+    if orc is not None:
+        res["parity"] = "bit-exact" if ok_all else "MISMATCH"
+        res["parity_note"] = "against oracle/mcm_modem.hpp (build-defined spec); unpinned by the reference"
+    eng.device_free(d_x)
+    return res
+
+
 def c5_leg(eng, orc, tmkphy, rank, world, hbm, steps, warmup, n_total, n_per, threads, barrier):
     """BASELINE config 5: n_total mixed-modulation streams x n_per samples, stream_id % 3 -> 4B5B / Manchester /
     chirp+BPSK, sharded over the ranks in contiguous id ranges (every range holds the same class and SNR mix, so the
@@ -425,7 +495,8 @@ def main():
     ap.add_argument("--no-pcm16", action="store_true", help="skip the 16-bit PCM end-to-end leg")
     ap.add_argument("--no-cpu", action="store_true")
     ap.add_argument("--no-configs", action="store_true", help="skip the C2-Manchester / chunk / C3 / C4 / C5 legs")
-    ap.add_argument("--configs", default="", help="comma-separated subset of man,chunk,c3,c4,c5")
+    ap.add_argument("--configs", default="", help="comma-separated subset of man,chunk,c3,mcm,c4,c5")
+    ap.add_argument("--mcm-streams", type=int, default=16384)
     ap.add_argument("--c5-streams", type=int, default=131072)
     ap.add_argument("--snrs", default="", help="comma-separated SNRs in dB replacing the C2 sweep (diagnostics)")
     args = ap.parse_args()
@@ -617,7 +688,7 @@ def main():
             del sub
 
     # ---- the other BASELINE configs (1 GPU: all of them; several GPUs: only the sharded C5 leg)
-    want_cfg = set(c for c in args.configs.split(",") if c) or {"man", "chunk", "c3", "c4", "c5"}
+    want_cfg = set(c for c in args.configs.split(",") if c) or {"man", "chunk", "c3", "mcm", "c4", "c5"}
     run_cfgs = headline and not args.no_configs
     configs = {}
     if run_cfgs and world == 1:
@@ -657,6 +728,8 @@ def main():
                     "8192 4B5B + 8192 Manchester (the FSK/OFDM demod of this config is the mcm leg)", d3, st3, tot3, 3, 2,
                     hbm, 96, threads, {"frames_planted": pl3})
                 eng.device_free(d3)
+        if "mcm" in want_cfg:
+            configs["C3_fsk_ofdm"] = mcm_leg(eng, orc, tmkphy, hbm, args.mcm_streams, 1 << 20)
         if "c4" in want_cfg:
             # C4: 8 hour-long captures (172.8 M samples each), one frame per ~0.5 s, +-100 ppm drift, amplitude U[0.3, 1], 10 dB
             n4, per4 = 8, 172_800_000

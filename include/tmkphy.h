@@ -336,6 +336,52 @@ int tmk_ask_synth_batch(tmk_engine* e, uint64_t seed, uint32_t n_streams, uint64
 int tmk_ask_last_stage_ms(tmk_engine* e, float ms[2]);
 
 /* ------------------------------------------------------------------------------------------------
+ * Multi-carrier modem: FSK and OFDM demodulation on a batched shared-memory FFT with symbol decision, bit packing
+ * and CRC-8 (north_star stages 3-4, BASELINE config 3). THE REFERENCE HAS NO CODE FOR THIS PATH (no FFT, FSK or
+ * OFDM in any .rs file; docs/proj/report.md:177-319 describes an amodem-style multi-carrier design in prose): the
+ * specification is this build's own (oracle/mcm_modem.hpp) and every result of these entry points
+ * is "parity unpinned by the reference". What IS the reference's: the 440-sample chirp preamble and its synchroniser
+ * (examples/ask.rs:586-605, :693-723), the MSB-first bit packing and CRC-8 (src/phy/crc.rs:7-22,41-60).
+ * A frame is the chirp followed by a 4752-sample body (the envelope of an ask.rs frame):
+ *   TMK_MCM_OFDM  16 zeros | training symbol | 13 data symbols | 256 zeros; symbol = 64 (cyclic prefix) + 256 samples,
+ *                 32 carriers on FFT bins 16..47, QPSK, one-tap equaliser from the training symbol; 104 bytes
+ *   TMK_MCM_FSK   16 zeros | 56 symbols | 256 zeros; symbol = 16 + 64 samples of one of 16 tones (FFT bins 4..19),
+ *                 decision = strongest bin; 28 bytes
+ *   bytes = [seq][len][payload][crc8(payload)][zero padding]; status: TMK_FRAME_OK / TMK_FRAME_BAD_LEN / TMK_FRAME_CRC_FAIL */
+#define TMK_MCM_FSK 0
+#define TMK_MCM_OFDM 1
+#define TMK_MCM_BODY_SAMPLES 4752
+#define TMK_MCM_MAX_PAYLOAD_FSK 25
+#define TMK_MCM_MAX_PAYLOAD_OFDM 100
+
+typedef struct tmk_mcm_rec {
+    uint32_t stream;
+    uint32_t status;      /* TMK_FRAME_OK, TMK_FRAME_BAD_LEN, TMK_FRAME_CRC_FAIL */
+    uint64_t start_index; /* sample index of the sync peak that locked (the body starts one sample later) */
+    uint64_t payload_off; /* `len` bytes at payload + payload_off (status OK or CRC_FAIL) */
+    float sync_power;
+    uint8_t seq, len, crc, mode;
+} tmk_mcm_rec;
+
+uint64_t tmk_mcm_modulated_len(uint32_t n_frames, const uint32_t* gap1, const uint32_t* gap2);
+/* payload_off: n_frames + 1 offsets into `payload`; seq: one byte per frame; gap1 / gap2: zeros before / after a frame */
+int tmk_mcm_modulate(tmk_engine* e, int32_t mode, const uint8_t* payload, const uint32_t* payload_off, const uint8_t* seq,
+                     uint32_t n_frames, const uint32_t* gap1, const uint32_t* gap2, float* out_samples, uint64_t out_cap,
+                     uint64_t* out_len);
+/* one record per locked frame, sorted by (stream, start_index). samples: host or device; recs / payload: host. */
+int tmk_mcm_decode_batch(tmk_engine* e, int32_t mode, const float* samples, uint64_t total_samples, const tmk_stream* streams,
+                         uint32_t n_streams, tmk_mcm_rec* recs, uint64_t rec_cap, uint64_t* n_recs, uint8_t* payload,
+                         uint64_t payload_cap, uint64_t* payload_len);
+/* Synthetic captures (measurement harness): n_streams x n_per_stream samples of AWGN (SNR against the body power 0.25)
+ * plus frames with hashed payloads, optionally through the 3-tap multipath channel of SURVEY §8d. */
+int tmk_mcm_synth_batch(tmk_engine* e, int32_t mode, uint64_t seed, uint32_t n_streams, uint64_t n_per_stream, float snr_db,
+                        int32_t multipath, float* samples, uint64_t* n_frames);
+/* parity probe of the FFT itself: n_ffts rows of n (64 or 256) real samples -> n_ffts x n x (re, im) */
+int tmk_mcm_fft_probe(tmk_engine* e, uint32_t n, const float* rows, uint32_t n_ffts, float* spectra);
+/* device time of the last tmk_mcm_decode_batch: chirp filter, sync walk, FFT demodulation (ms) */
+int tmk_mcm_last_stage_ms(tmk_engine* e, float ms[3]);
+
+/* ------------------------------------------------------------------------------------------------
  * 16-bit PCM captures. Recordings reach the reference as int16 WAV:
  *   tmk_pcm16_encode        replaces the sample loop of dump_to_wav   src/utils/dump.rs:37-40
  *                           amplitude = (sample * i16::MAX as f32) as i16  (Rust `as`: truncates toward zero,

@@ -20,7 +20,7 @@ LIB = os.path.join(_HERE, "liboracle.so")
 
 
 def build(force=False):
-    srcs = [os.path.join(_HERE, f) for f in ("oracle_capi.cpp", "phy_core.hpp", "phy_decoder.hpp", "ask_modem.hpp", "ip_fragments.hpp")]
+    srcs = [os.path.join(_HERE, f) for f in ("oracle_capi.cpp", "phy_core.hpp", "phy_decoder.hpp", "ask_modem.hpp", "mcm_modem.hpp", "ip_fragments.hpp")]
     if force or not os.path.exists(LIB) or any(os.path.getmtime(s) > os.path.getmtime(LIB) for s in srcs):
         subprocess.check_call(["make", "-C", _HERE, "-B", "liboracle.so"], stdout=subprocess.DEVNULL)
 
@@ -64,6 +64,9 @@ def lib():
             "orc_ask_tables": (None, [vp, vp, u64]),
             "orc_ask_modulate": (u64, [vp, u32, vp, vp, vp, u64]),
             "orc_ask_demodulate": (u64, [vp, u64, u32, vp, u64]),
+            "orc_mcm_modulate": (u64, [C.c_int, vp, vp, vp, u32, vp, vp, vp, u64]),
+            "orc_mcm_demodulate": (u64, [C.c_int, vp, u64, u32, vp, u64, vp, u64, C.POINTER(u64)]),
+            "orc_mcm_fft": (None, [C.c_int, vp, u32, vp]),
         }
         for n, (r, a) in sig.items():
             f = getattr(L, n)
@@ -251,6 +254,43 @@ def ask_demodulate(samples, stream=0, cap=None) -> np.ndarray:
     n = lib().orc_ask_demodulate(_ptr(s), len(s), stream, _ptr(recs), cap)
     assert n <= cap
     return recs[:n].copy()
+
+
+# ---- multi-carrier modem (build-defined FSK / OFDM spec; parity unpinned by the reference)
+def mcm_modulate(mode, payloads, seqs, gap1, gap2) -> np.ndarray:
+    """payloads: list of bytes (<= 25 FSK / <= 100 OFDM each); seqs: one byte per frame"""
+    off = np.zeros(len(payloads) + 1, np.uint32)
+    off[1:] = np.cumsum([len(p) for p in payloads])
+    blob = np.frombuffer(b"".join(payloads) + b"\0", np.uint8).copy()
+    sq = np.ascontiguousarray(seqs, dtype=np.uint8)
+    g1 = np.ascontiguousarray(gap1, dtype=np.uint32)
+    g2 = np.ascontiguousarray(gap2, dtype=np.uint32)
+    n = int(len(payloads) * (440 + 4752) + g1.sum() + g2.sum())
+    out = np.zeros(max(n, 1), np.float32)
+    got = lib().orc_mcm_modulate(mode, _ptr(blob), _ptr(off), _ptr(sq), len(payloads), _ptr(g1), _ptr(g2), _ptr(out), n)
+    assert got == n
+    return out[:n]
+
+
+def mcm_demodulate(mode, samples, stream=0, cap=None):
+    """-> (records in tmk_mcm_rec layout, payload bytes)"""
+    from tmkphy._abi import MCM_REC_DTYPE
+    s = np.ascontiguousarray(samples, dtype=np.float32)
+    cap = cap or max(16, len(s) // 4000 + 4)
+    recs = np.zeros(cap, MCM_REC_DTYPE)
+    pay = np.zeros(cap * 100 + 16, np.uint8)
+    pl = C.c_uint64(0)
+    n = lib().orc_mcm_demodulate(mode, _ptr(s), len(s), stream, _ptr(recs), cap, _ptr(pay), len(pay), C.byref(pl))
+    assert n <= cap and pl.value <= len(pay)
+    return recs[:n].copy(), pay[:pl.value].copy()
+
+
+def mcm_fft(rows) -> np.ndarray:
+    """rows: (n_ffts, 64 | 256) real f32 -> complex64 spectra in the specification's operation order"""
+    r = np.ascontiguousarray(rows, dtype=np.float32)
+    out = np.zeros(r.shape + (2,), np.float32)
+    lib().orc_mcm_fft(r.shape[1], _ptr(r), r.shape[0], _ptr(out))
+    return out.view(np.complex64)[..., 0]
 
 
 # ---- 16-bit PCM (dump.rs:37-40, codec.rs:121-125)

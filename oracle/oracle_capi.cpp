@@ -5,6 +5,7 @@
 #include <thread>
 
 #include "ask_modem.hpp"
+#include "mcm_modem.hpp"
 #include "ip_fragments.hpp"
 #include "phy_decoder.hpp"
 
@@ -243,6 +244,52 @@ uint64_t orc_ask_demodulate(const float* rx, uint64_t n, uint32_t stream, tmk_as
         recs[i] = r;
     }
     return v.size();
+}
+
+// ---- multi-carrier modem (build-defined FSK / OFDM spec, mcm_modem.hpp; parity unpinned by the reference)
+uint64_t orc_mcm_modulate(int mode, const uint8_t* payload, const uint32_t* off, const uint8_t* seq, uint32_t n_frames,
+                          const uint32_t* gap1, const uint32_t* gap2, float* out, uint64_t cap) {
+    auto v = orc_mcm::modulate(mode, payload, off, seq, n_frames, gap1, gap2);
+    std::copy(v.begin(), v.begin() + std::min<uint64_t>(cap, v.size()), out);
+    return v.size();
+}
+// recs: tmk_mcm_rec layout; payload bytes appended at *payload_len
+uint64_t orc_mcm_demodulate(int mode, const float* rx, uint64_t n, uint32_t stream, tmk_mcm_rec* recs, uint64_t cap,
+                            uint8_t* payload, uint64_t payload_cap, uint64_t* payload_len) {
+    auto v = orc_mcm::demodulate(mode, rx, n);
+    uint64_t pl = *payload_len;
+    for (size_t i = 0; i < v.size(); ++i) {
+        if (i < cap) {
+            tmk_mcm_rec r{};
+            r.stream = stream;
+            r.status = v[i].status;
+            r.start_index = v[i].start_index;
+            r.payload_off = pl;
+            r.sync_power = v[i].sync_power;
+            r.seq = v[i].seq;
+            r.len = v[i].len;
+            r.crc = v[i].crc;
+            r.mode = uint8_t(mode);
+            recs[i] = r;
+        }
+        for (uint8_t b : v[i].payload) {
+            if (pl < payload_cap) payload[pl] = b;
+            ++pl;
+        }
+    }
+    *payload_len = pl;
+    return v.size();
+}
+// complex FFT of n_ffts real rows of n (64 | 256) samples: out = n_ffts x n x (re, im)
+void orc_mcm_fft(int n, const float* in, uint32_t n_ffts, float* out) {
+    const auto W = orc_mcm::twiddles(n);
+    for (uint32_t f = 0; f < n_ffts; ++f) {
+        const auto X = orc_mcm::fft_real(in + size_t(f) * n, n, W);
+        for (int k = 0; k < n; ++k) {
+            out[(size_t(f) * n + k) * 2] = X[k].re;
+            out[(size_t(f) * n + k) * 2 + 1] = X[k].im;
+        }
+    }
 }
 
 // ---- 16-bit PCM (dump.rs:37-40, codec.rs:121-125)

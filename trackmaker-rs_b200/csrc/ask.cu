@@ -840,12 +840,17 @@ int tmk_ask_modulate(tmk_engine* e, const uint8_t* bits, uint32_t n_frames, cons
     return TMK_OK;
 }
 
-int tmk_ask_decode_batch(tmk_engine* e, const float* samples, uint64_t total_samples, const tmk_stream* streams,
-                         uint32_t n_streams, tmk_ask_rec* recs, uint64_t rec_cap, uint64_t* n_recs) {
-    if (!e || (!samples && total_samples) || (!streams && n_streams) || !n_recs || (!recs && rec_cap))
-        return tmk_fail(e, TMK_E_INVALID, "tmk_ask_decode_batch: null argument");
+}  // extern "C"
+
+// tables of the chirp + BPSK modem on the device (e->d_ask_tab: [440 chirp | 4752 carrier | FFT tables])
+int tmk_ask_ensure_tables(tmk_engine* e) { return ensure_tables(e); }
+
+// The synchroniser + BPSK demodulator on the device: records are left in e->d_ask_recs (unsorted: the warps emit through
+// an atomic slot counter), *dx_out is where the samples live on the device. Shared with mcm.cu, whose frames use the
+// same chirp preamble and frame envelope.
+int tmk_ask_sync_device(tmk_engine* e, const float* samples, uint64_t total_samples, const tmk_stream* streams, uint32_t n_streams,
+                        const float** dx_out, uint64_t* n_recs, uint64_t* dev_cap_out) {
     *n_recs = 0;
-    if (n_streams == 0) return TMK_OK;
     CK(cudaSetDevice(e->device));
     int rc = ensure_tables(e);
     if (rc != TMK_OK) return rc;
@@ -929,7 +934,30 @@ int tmk_ask_decode_batch(tmk_engine* e, const float* samples, uint64_t total_sam
     cudaEventElapsedTime(&e->ask_ms[0], e->ev[0], e->ev[1]);
     cudaEventElapsedTime(&e->ask_ms[1], e->ev[1], e->ev[2]);
     *n_recs = hc[0];
-    if (hc[0] > dev_cap) return tmk_fail(e, TMK_E_CAPACITY, "tmk_ask_decode_batch: internal record scratch too small");
+    *dx_out = dx;
+    *dev_cap_out = dev_cap;
+    if (hc[0] > dev_cap) return tmk_fail(e, TMK_E_CAPACITY, "chirp synchroniser: internal record scratch too small");
+    return TMK_OK;
+}
+
+extern "C" {
+
+int tmk_ask_decode_batch(tmk_engine* e, const float* samples, uint64_t total_samples, const tmk_stream* streams,
+                         uint32_t n_streams, tmk_ask_rec* recs, uint64_t rec_cap, uint64_t* n_recs) {
+    if (!e || (!samples && total_samples) || (!streams && n_streams) || !n_recs || (!recs && rec_cap))
+        return tmk_fail(e, TMK_E_INVALID, "tmk_ask_decode_batch: null argument");
+    *n_recs = 0;
+    if (n_streams == 0) return TMK_OK;
+    const float* dx = nullptr;
+    uint64_t dev_cap = 0;
+    unsigned long long hc[1] = {0};
+    {
+        uint64_t n = 0;
+        const int rc = tmk_ask_sync_device(e, samples, total_samples, streams, n_streams, &dx, &n, &dev_cap);
+        hc[0] = n;
+        *n_recs = n;
+        if (rc != TMK_OK) return rc;
+    }
     if (hc[0] > rec_cap) return tmk_fail(e, TMK_E_CAPACITY, "tmk_ask_decode_batch: record buffer too small");
     if (hc[0]) {
         CK(cudaMemcpyAsync(recs, e->d_ask_recs.p, hc[0] * sizeof(tmk_ask_rec), cudaMemcpyDeviceToHost, e->stream));

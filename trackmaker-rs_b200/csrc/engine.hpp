@@ -41,6 +41,9 @@ struct tmk_engine {
     DevBuf d_tile_dir, d_patterns, d_streams, d_blk_info, d_cand, d_recs_tmp, d_rec_ord, d_recs, d_payload, d_cnt, d_base,
         d_counters, d_samples, d_misc, d_misc2, d_next, d_cblk, d_blk_ptr, d_entries, d_spec, d_pool, d_link, d_pcm, d_frag;
     DevBuf d_ask_tab, d_ask_bits, d_ask_l2, d_ask_recs, d_ask_recs2;  // chirp+BPSK path (ask.cu)
+    DevBuf d_mcm_tab, d_mcm_recs, d_mcm_off;  // multi-carrier modem (mcm.cu): tables, device records, stream offsets
+    bool mcm_ready = false;
+    float mcm_demod_ms = 0.0f;
     DevBuf d_tile_desc;  // per-tile descriptors of the tensor-core scan (scan_tc.cu)
     DevBuf d_comm, d_wav, d_wavdesc;  // staging of the counter all-reduce (comm.cu); raw WAV bytes + descriptors (wav.cu)
     float* scan_dbg_dot = nullptr;    // set around tmk_scan_probe by tmk_scan_dot_probe (diagnostic)
@@ -82,3 +85,8 @@ inline bool tmk_is_device_ptr(const void* p) {
     }
     return a.type == cudaMemoryTypeDevice || a.type == cudaMemoryTypeManaged;
 }
+
+// ask.cu, shared with mcm.cu (the multi-carrier frames use the chirp preamble and the frame envelope of examples/ask.rs)
+int tmk_ask_ensure_tables(tmk_engine* e);
+int tmk_ask_sync_device(tmk_engine* e, const float* samples, uint64_t total_samples, const tmk_stream* streams, uint32_t n_streams,
+                        const float** dx_out, uint64_t* n_recs, uint64_t* dev_cap_out);

@@ -239,6 +239,63 @@ class Engine:
         self._check(self._lib.tmk_ask_last_stage_ms(self._h, ms))
         return {"scan": ms[0], "walk": ms[1]}
 
+    # ---- multi-carrier modem (build-defined FSK / OFDM spec on the batched FFT; parity unpinned by the reference)
+    def mcm_modulate(self, mode, payloads, seqs, gap1, gap2):
+        """payloads: list of bytes (<= 25 FSK / <= 100 OFDM each) -> float32 track"""
+        off = np.zeros(len(payloads) + 1, np.uint32)
+        off[1:] = np.cumsum([len(p) for p in payloads])
+        blob = np.frombuffer(b"".join(payloads) + b"\0", np.uint8).copy()
+        sq = np.ascontiguousarray(seqs, dtype=np.uint8)
+        g1 = np.ascontiguousarray(gap1, dtype=np.uint32)
+        g2 = np.ascontiguousarray(gap2, dtype=np.uint32)
+        n = int(self._lib.tmk_mcm_modulated_len(len(payloads), _ptr(g1), _ptr(g2)))
+        out = np.zeros(max(n, 1), np.float32)
+        ln = C.c_uint64(0)
+        self._check(self._lib.tmk_mcm_modulate(self._h, int(mode), _ptr(blob), _ptr(off), _ptr(sq), len(payloads), _ptr(g1),
+                                               _ptr(g2), _ptr(out), n, C.byref(ln)))
+        return out[:int(ln.value)]
+
+    def mcm_decode_batch(self, mode, samples, streams, rec_cap=None, total_samples=None):
+        """-> (ndarray[MCM_REC_DTYPE] sorted by (stream, start_index), payload bytes)"""
+        st = np.ascontiguousarray(streams, dtype=STREAM_DTYPE)
+        if isinstance(samples, np.ndarray):
+            s = np.ascontiguousarray(samples, dtype=np.float32)
+            sp, total = _ptr(s), s.size
+        else:
+            sp, total = C.c_void_p(int(samples)), int(total_samples)
+        tot = int(st["n_samples"].sum()) if len(st) else 0
+        rec_cap = int(rec_cap) if rec_cap is not None else max(64, tot // 4096 + 2 * len(st))
+        recs = np.zeros(rec_cap, _abi.MCM_REC_DTYPE)
+        pay = np.zeros(rec_cap * _abi.MCM_MAX_PAYLOAD.get(int(mode), 100) + 16, np.uint8)
+        n, pl = C.c_uint64(0), C.c_uint64(0)
+        self._check(self._lib.tmk_mcm_decode_batch(self._h, int(mode), sp, total, _ptr(st), len(st), _ptr(recs), rec_cap,
+                                                   C.byref(n), _ptr(pay), len(pay), C.byref(pl)))
+        return recs[:int(n.value)].copy(), pay[:int(pl.value)].copy()
+
+    def mcm_synth_batch(self, mode, seed, n_streams, n_per_stream, snr_db, multipath=False, device_ptr=None):
+        """-> (samples or None when device_ptr is given, frames planted)"""
+        nf = C.c_uint64(0)
+        if device_ptr is None:
+            out = np.zeros(n_streams * n_per_stream, np.float32)
+            sp = _ptr(out)
+        else:
+            out, sp = None, C.c_void_p(device_ptr)
+        self._check(self._lib.tmk_mcm_synth_batch(self._h, int(mode), seed, n_streams, n_per_stream, C.c_float(snr_db),
+                                                  1 if multipath else 0, sp, C.byref(nf)))
+        return out, int(nf.value)
+
+    def mcm_fft(self, rows):
+        """rows: (n_ffts, 64 | 256) real f32 -> complex64 spectra (the kernel's own FFT; parity probe)"""
+        r = np.ascontiguousarray(rows, dtype=np.float32)
+        out = np.zeros(r.shape + (2,), np.float32)
+        self._check(self._lib.tmk_mcm_fft_probe(self._h, r.shape[1], _ptr(r), r.shape[0], _ptr(out)))
+        return out.view(np.complex64)[..., 0]
+
+    def mcm_last_stage_ms(self):
+        ms = (C.c_float * 3)()
+        self._check(self._lib.tmk_mcm_last_stage_ms(self._h, ms))
+        return {"filter": ms[0], "walk": ms[1], "demod": ms[2]}
+
     # ---- the path
     def modulate(self, cfg, frames, gap=INTER_FRAME_GAP_SAMPLES, out_device_ptr=None):
         """PhyEncoder::encode_frames. frames: list of Frame. Returns float32 samples (host)."""

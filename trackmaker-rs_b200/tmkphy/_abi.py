@@ -78,6 +78,11 @@ PKT_OK, PKT_E_SHORT, PKT_E_IHL, PKT_E_TOO_MANY, PKT_E_MTU = range(5)
 MAX_FRAGMENTS = 512
 assert STREAM_DTYPE.itemsize == 48 and REC_DTYPE.itemsize == 48 and DESC_DTYPE.itemsize == 16
 assert ASK_REC_DTYPE.itemsize == 40
+MCM_REC_DTYPE = np.dtype([("stream", "<u4"), ("status", "<u4"), ("start_index", "<u8"), ("payload_off", "<u8"),
+                          ("sync_power", "<f4"), ("seq", "u1"), ("len", "u1"), ("crc", "u1"), ("mode", "u1")])
+assert MCM_REC_DTYPE.itemsize == 32
+MCM_FSK, MCM_OFDM = 0, 1
+MCM_MAX_PAYLOAD = {MCM_FSK: 25, MCM_OFDM: 100}
 
 _vp, _u64, _u32, _i32 = C.c_void_p, C.c_uint64, C.c_uint32, C.c_int32
 _pu64 = C.POINTER(C.c_uint64)
@@ -129,6 +134,12 @@ SYMBOLS = {
     "tmk_ask_modulate": (C.c_int, [_vp, _vp, _u32, _vp, _vp, _vp, _u64, _pu64]),
     "tmk_ask_decode_batch": (C.c_int, [_vp, _vp, _u64, _vp, _u32, _vp, _u64, _pu64]),
     "tmk_ask_last_stage_ms": (C.c_int, [_vp, C.POINTER(C.c_float)]),
+    "tmk_mcm_modulated_len": (_u64, [_u32, _vp, _vp]),
+    "tmk_mcm_modulate": (C.c_int, [_vp, _i32, _vp, _vp, _vp, _u32, _vp, _vp, _vp, _u64, _pu64]),
+    "tmk_mcm_decode_batch": (C.c_int, [_vp, _i32, _vp, _u64, _vp, _u32, _vp, _u64, _pu64, _vp, _u64, _pu64]),
+    "tmk_mcm_synth_batch": (C.c_int, [_vp, _i32, _u64, _u32, _u64, C.c_float, _i32, _vp, _pu64]),
+    "tmk_mcm_fft_probe": (C.c_int, [_vp, _u32, _vp, _u32, _vp]),
+    "tmk_mcm_last_stage_ms": (C.c_int, [_vp, C.POINTER(C.c_float)]),
     "tmk_pcm16_encode": (C.c_int, [_vp, _vp, _u64, _vp]),
     "tmk_pcm16_to_f32": (C.c_int, [_vp, _vp, _u64, _vp]),
     "tmk_decode_batch_pcm16": (C.c_int, [_vp, _vp, _u64, _vp, _u32, _vp, _u64, _pu64, _vp, _u64, _pu64]),
