@@ -40,7 +40,7 @@ struct AskStream {
     uint64_t offset, n;
     uint64_t word_base;  // first flag bit of this stream (one bit per 32 samples)
     uint32_t tile_base;  // first scan tile
-    uint32_t pad_;
+    uint32_t seg_base;   // first segment of the exact power chain (kSeg samples each)
 };
 
 // ---------------------------------------------------------------- TX
@@ -451,7 +451,115 @@ ask_scan_fft_kernel(const float* __restrict__ samples, const AskStream* __restri
     }
 }
 
+// ---------------------------------------------------------------- exact power chain, in parallel
+// `power` (ask.rs:696-697) is one serial chain per capture: p <- rn(rn(p c) + q), c = 63/64, q = rn(rn(x x) / 64) >= 0.
+// The step is MONOTONE in p (every rounding is), and it contracts: two chains fed with the same samples, one started
+// BELOW the reference's value and one ABOVE it, keep the reference's chain between them and approach each other by 63/64
+// per step until they land on the same float — from there on both ARE the reference's chain, bit for bit. So a thread
+// owns a segment of kSeg samples, starts kWarm samples before it from 0 and from 1.001 xmax^2 + 1e-30 (xmax = the largest
+// |x| of the whole capture: the exact chain never exceeds xmax^2 (1 + 130 u)), and stores the power at every 32-sample
+// word boundary of its segment once the two have met (-1 = not known: digital silence, where 0 and the decayed upper
+// chain sit on different subnormal fixed points, the first ~1500 samples after it, NaN / inf captures — the walk then
+// runs the chain literally from its last exact position, as before). The walk reads the checkpoints instead of chaining
+// through every sample of every capture with 32 lanes computing one scalar.
+constexpr int kSeg = 4096, kWarm = 2048;
+__device__ __forceinline__ uint32_t seg_stream(const AskStream* __restrict__ streams, uint32_t n_streams, uint32_t seg) {
+    uint32_t lo = 0, hi = n_streams - 1;
+    while (lo < hi) {
+        const uint32_t mid = (lo + hi + 1) >> 1;
+        if (streams[mid].seg_base <= seg) lo = mid; else hi = mid - 1;
+    }
+    return lo;
+}
+
+// largest |x| of every capture, as the bit pattern of the float (NaN > inf > finite): one warp per segment
+__global__ void __launch_bounds__(256)
+ask_xmax_kernel(const float* __restrict__ samples, const AskStream* __restrict__ streams, uint32_t n_streams, uint32_t n_segs,
+                uint32_t* __restrict__ xmax_bits) {
+    const uint32_t seg = blockIdx.x * 8 + (threadIdx.x >> 5);
+    if (seg >= n_segs) return;
+    const int lane = threadIdx.x & 31;
+    const uint32_t si = seg_stream(streams, n_streams, seg);
+    const AskStream sd = streams[si];
+    const int64_t lo = int64_t(seg - sd.seg_base) * kSeg, hi = min(lo + int64_t(kSeg), int64_t(sd.n));
+    const float* __restrict__ x = samples + sd.offset;
+    uint32_t m = 0;
+    for (int64_t i = lo + 4 * lane; i < hi; i += 128) {
+        if (i + 4 <= hi) {
+            const float4 v = *reinterpret_cast<const float4*>(x + i);
+            m = max(max(m, __float_as_uint(v.x) & 0x7fffffffu), max(__float_as_uint(v.y) & 0x7fffffffu,
+                    max(__float_as_uint(v.z) & 0x7fffffffu, __float_as_uint(v.w) & 0x7fffffffu)));
+        } else {
+            for (int64_t k = i; k < hi; ++k) m = max(m, __float_as_uint(x[k]) & 0x7fffffffu);
+        }
+    }
+    m = __reduce_max_sync(kFull, m);
+    if (lane == 0 && m) atomicMax(xmax_bits + si, m);
+}
+
+__global__ void __launch_bounds__(128)
+ask_power_kernel(const float* __restrict__ samples, const AskStream* __restrict__ streams, uint32_t n_streams, uint32_t n_segs,
+                 const uint32_t* __restrict__ xmax_bits, float* __restrict__ pchk) {
+    const uint32_t seg = blockIdx.x * blockDim.x + threadIdx.x;
+    if (seg >= n_segs) return;
+    const uint32_t si = seg_stream(streams, n_streams, seg);
+    const AskStream sd = streams[si];
+    const int64_t n = int64_t(sd.n);
+    const int64_t s0 = int64_t(seg - sd.seg_base) * kSeg, s1 = min(s0 + int64_t(kSeg), n);
+    const float* __restrict__ x = samples + sd.offset;
+    float* __restrict__ chk = pchk + sd.word_base;  // chk[w] = power BEFORE sample 32 w
+    int64_t pos = s0 - kWarm;
+    float pl = 0.0f, pu;
+    bool merged;
+    if (pos <= 0) {  // the chain's own start: exact
+        pos = 0;
+        pu = 0.0f;
+        merged = true;
+    } else {
+        const float xm = __uint_as_float(xmax_bits[si]);
+        pu = __fmaf_rn(1.001f, __fmul_rn(xm, xm), 1e-30f);  // inf / NaN captures never merge
+        merged = false;
+    }
+    // a word (32 samples) per round: eight 16-byte loads, then the chain(s) over them; pos, s0 are multiples of 32
+    while (pos < s1) {
+        if (!merged) merged = pl == pu;
+        if (pos >= s0) chk[pos >> 5] = merged ? pl : -1.0f;
+        if (pos + 32 > n) break;  // the partial last word of the capture: nobody reads behind its checkpoint
+        float4 v[8];
+#pragma unroll
+        for (int k = 0; k < 8; ++k) v[k] = __ldg(reinterpret_cast<const float4*>(x + pos) + k);
+        if (merged) {
+#pragma unroll
+            for (int k = 0; k < 8; ++k) {
+                pl = __fadd_rn(__fmul_rn(pl, kC), __fmul_rn(__fmul_rn(v[k].x, v[k].x), kInv64));
+                pl = __fadd_rn(__fmul_rn(pl, kC), __fmul_rn(__fmul_rn(v[k].y, v[k].y), kInv64));
+                pl = __fadd_rn(__fmul_rn(pl, kC), __fmul_rn(__fmul_rn(v[k].z, v[k].z), kInv64));
+                pl = __fadd_rn(__fmul_rn(pl, kC), __fmul_rn(__fmul_rn(v[k].w, v[k].w), kInv64));
+            }
+        } else {
+#pragma unroll
+            for (int k = 0; k < 8; ++k) {
+                const float q0 = __fmul_rn(__fmul_rn(v[k].x, v[k].x), kInv64), q1 = __fmul_rn(__fmul_rn(v[k].y, v[k].y), kInv64);
+                const float q2 = __fmul_rn(__fmul_rn(v[k].z, v[k].z), kInv64), q3 = __fmul_rn(__fmul_rn(v[k].w, v[k].w), kInv64);
+                pl = __fadd_rn(__fmul_rn(pl, kC), q0);
+                pu = __fadd_rn(__fmul_rn(pu, kC), q0);
+                pl = __fadd_rn(__fmul_rn(pl, kC), q1);
+                pu = __fadd_rn(__fmul_rn(pu, kC), q1);
+                pl = __fadd_rn(__fmul_rn(pl, kC), q2);
+                pu = __fadd_rn(__fmul_rn(pu, kC), q2);
+                pl = __fadd_rn(__fmul_rn(pl, kC), q3);
+                pu = __fadd_rn(__fmul_rn(pu, kC), q3);
+            }
+        }
+        pos += 32;
+    }
+}
+
 // ---------------------------------------------------------------- walk
+// scratch of the walk kernel at namespace scope: every access compiles to LDS / STS with immediate offsets (through the
+// generic pointers of AskCtx the taps of the exact dot were LD.E with 64-bit address arithmetic, ~6 instructions per tap)
+__shared__ __align__(16) float g_wpre[kPre];       // the chirp
+__shared__ __align__(16) float g_wxs[4][kPre + 40];  // the samples under the 32 windows of one word, per warp
 __device__ __forceinline__ float fadd(float a, float b) { return __fadd_rn(a, b); }
 __device__ __forceinline__ float fmul(float a, float b) { return __fmul_rn(a, b); }
 
@@ -465,11 +573,29 @@ struct AskCtx {
     int64_t cpos;
     float p;
     float* stage;  // 128 floats of shared memory per warp
+    const float* chk;  // exact power before sample 32 w per word of this capture, or -1 (ask_power_kernel); may be null
 };
 
 // advance the EMA chain to `target` (power after sample target - 1)            ask.rs:696-697
 __device__ __noinline__ void chain_to(AskCtx& c, int64_t target) {
     const float* __restrict__ x = c.x;
+    // the nearest checkpoint at or before the target (64 words back at most) replaces the chain up to it
+    if (c.chk != nullptr && (target & 31) == 0 && target > c.cpos) {
+        const int64_t wt = target >> 5;
+#pragma unroll 1
+        for (int rnd = 0; rnd < 2; ++rnd) {
+            const int64_t w = wt - 32 * rnd - c.lane;
+            const float v = (w >= 0 && w * 32 > c.cpos) ? c.chk[w] : -1.0f;
+            const uint32_t ok = __ballot_sync(kFull, !(v < 0.0f));  // -1 = unknown; a NaN power is a known value
+            if (ok) {
+                const int l = __ffs(ok) - 1;
+                c.p = __shfl_sync(kFull, v, l);
+                c.cpos = (wt - 32 * rnd - l) * 32;
+                break;
+            }
+        }
+        if (c.cpos == target) return;
+    }
     float p = c.p;
     int64_t pos = c.cpos;
     while (pos < target) {
@@ -547,38 +673,35 @@ __device__ __noinline__ void eval_word(AskCtx& c, int64_t w, int64_t r, float* s
             c.cpos = c.n;
         }
     }
-    float sum = 0.0f;
-    const int64_t first = i - (kPre - 1);  // sample index of tap 0
+    // the 471 samples under the 32 windows of the word, staged once (coalesced); samples before r read as the zeroed FIFO
+    // (a tap on the zeroed FIFO adds +-0.0 to a sum that starts at +0.0 — no effect — so no tap needs a mask; whole groups
+    // of 8 that are zero for every lane are skipped: right after a frame most of the window is still empty)
+    const int warp = threadIdx.x >> 5;
+    float* __restrict__ xs = g_wxs[warp];
+    const int64_t base = w * 32 - (kPre - 1);  // sample index of xs[0]
     const float* __restrict__ x = c.x;
-    // taps below k_lo read the zeroed FIFO (samples before r >= 0): they add +-0.0 to a sum that starts at +0.0, which
-    // leaves it unchanged, so they are skipped — whole groups of 8 when no lane of the warp needs them (right after a
-    // frame most of the window is still empty)
-    int k_lo = first < r ? int(r - first < int64_t(kPre) ? r - first : int64_t(kPre)) : 0;
-    if (i >= c.n) k_lo = kPre;
-    const int k0 = __reduce_min_sync(kFull, k_lo) & ~7;
-    const int k_hi = __reduce_max_sync(kFull, k_lo);  // from here on every lane of the warp reads real samples
-    const float* __restrict__ xp = x + first;          // dereferenced only at taps >= k_lo, i.e. at samples >= r >= 0
-    int k = k0;
-#pragma unroll 1
-    for (; k < kPre && k < k_hi; k += 8) {
-        const float4 pa = *reinterpret_cast<const float4*>(c.pre + k), pb = *reinterpret_cast<const float4*>(c.pre + k + 4);
-        const float pk[8] = {pa.x, pa.y, pa.z, pa.w, pb.x, pb.y, pb.z, pb.w};
-        float xv[8];
+    __syncwarp();
 #pragma unroll
-        for (int j = 0; j < 8; ++j) xv[j] = k + j >= k_lo ? xp[k + j] : 0.0f;
-#pragma unroll
-        for (int j = 0; j < 8; ++j)
-            if (k + j >= k_lo) sum = fadd(sum, fmul(xv[j], pk[j]));
+    for (int t = c.lane; t < kPre + 31; t += 32) {
+        const int64_t idx = base + t;
+        xs[t] = (idx >= r && idx < c.n) ? __ldg(x + idx) : 0.0f;
     }
-#pragma unroll 4
-    for (; k < kPre; k += 8) {  // no lane needs a mask: load, multiply, add (unrolled: 32 loads in flight above the add chain)
-        const float4 pa = *reinterpret_cast<const float4*>(c.pre + k), pb = *reinterpret_cast<const float4*>(c.pre + k + 4);
-        const float pk[8] = {pa.x, pa.y, pa.z, pa.w, pb.x, pb.y, pb.z, pb.w};
-        float xv[8];
-#pragma unroll
-        for (int j = 0; j < 8; ++j) xv[j] = xp[k + j];
-#pragma unroll
-        for (int j = 0; j < 8; ++j) sum = fadd(sum, fmul(xv[j], pk[j]));
+    __syncwarp();
+    const int64_t zeros = r - base;  // taps below this read zeros for lane 0; lane l reads tap k at xs[l + k]
+    const int k0 = zeros > 31 ? int(min(zeros - 31, int64_t(kPre))) & ~7 : 0;
+    const float* __restrict__ xl = xs + c.lane;
+    float sum = 0.0f;
+#pragma unroll 5
+    for (int k = k0; k < kPre; k += 8) {
+        const float4 pa = *reinterpret_cast<const float4*>(g_wpre + k), pb = *reinterpret_cast<const float4*>(g_wpre + k + 4);
+        sum = fadd(sum, fmul(xl[k + 0], pa.x));
+        sum = fadd(sum, fmul(xl[k + 1], pa.y));
+        sum = fadd(sum, fmul(xl[k + 2], pa.z));
+        sum = fadd(sum, fmul(xl[k + 3], pa.w));
+        sum = fadd(sum, fmul(xl[k + 4], pb.x));
+        sum = fadd(sum, fmul(xl[k + 5], pb.y));
+        sum = fadd(sum, fmul(xl[k + 6], pb.z));
+        sum = fadd(sum, fmul(xl[k + 7], pb.w));
     }
     *sp_out = __fdiv_rn(sum, 200.0f);
 }
@@ -586,20 +709,27 @@ __device__ __noinline__ void eval_word(AskCtx& c, int64_t w, int64_t r, float* s
 // carrier mixing, 11-tap moving average, integrate and dump of the 108 bits      ask.rs:733-761
 __device__ __noinline__ void decode_frame(const AskCtx& c, int64_t s, uint8_t* bits14, uint32_t* id_out) {
     uint32_t words[4];
+    const float* __restrict__ x = c.x + s + 1;
+    const float* __restrict__ car = c.car;
     for (int rnd = 0; rnd < 4; ++rnd) {
         const int j = rnd * 32 + c.lane;
         bool bit = false;
         if (j < kBits) {
+            // the 30 products under the bit's 20 averaging windows, each rounded once (the reference forms every product
+            // anew in each of the 11 windows that hold it: same value), then the 11-term sums in the reference's order
+            float pr[30];
+#pragma unroll
+            for (int t = 0; t < 30; ++t) {
+                const int k = 5 + j * TMK_ASK_SAMPLES_PER_BIT + t;
+                // decode_fifo[k]: rx[s+1 .. s+201) then rx[s+202 ..)  (the sample at s+201 is dropped)
+                pr[t] = fmul(__ldg(x + k + (k >= 200 ? 1 : 0)), __ldg(car + k));
+            }
             float tot = 0.0f;
+#pragma unroll
             for (int t = 0; t < 20; ++t) {
-                const int idx = 10 + j * TMK_ASK_SAMPLES_PER_BIT + t;
                 float sm = 0.0f;
 #pragma unroll
-                for (int k = idx - 5; k < idx + 6; ++k) {
-                    // decode_fifo[k]: rx[s+1 .. s+201) then rx[s+202 ..)  (the sample at s+201 is dropped)
-                    const float f = c.x[s + 1 + k + (k >= 200 ? 1 : 0)];
-                    sm = fadd(sm, fmul(f, c.car[k]));
-                }
+                for (int u = 0; u < 11; ++u) sm = fadd(sm, pr[t + u]);
                 tot = fadd(tot, __fdiv_rn(sm, 11.0f));
             }
             bit = tot > 0.0f;
@@ -612,11 +742,10 @@ __device__ __noinline__ void decode_frame(const AskCtx& c, int64_t s, uint8_t* b
 
 __global__ void __launch_bounds__(128)
 ask_walk_kernel(const float* __restrict__ samples, const AskStream* __restrict__ streams, uint32_t n_streams,
-                const float* __restrict__ tab, const uint32_t* __restrict__ wflag, tmk_ask_rec* __restrict__ recs,
-                uint64_t rec_cap, unsigned long long* __restrict__ counters) {
-    __shared__ __align__(16) float pre_s[kPre];
+                const float* __restrict__ tab, const uint32_t* __restrict__ wflag, const float* __restrict__ pchk,
+                tmk_ask_rec* __restrict__ recs, uint64_t rec_cap, unsigned long long* __restrict__ counters) {
     __shared__ __align__(16) float stage_s[4][128];
-    for (int i = threadIdx.x; i < kPre; i += blockDim.x) pre_s[i] = tab[i];
+    for (int i = threadIdx.x; i < kPre; i += blockDim.x) g_wpre[i] = tab[i];
     __syncthreads();
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     for (;;) {
@@ -628,12 +757,13 @@ ask_walk_kernel(const float* __restrict__ samples, const AskStream* __restrict__
         AskCtx c;
         c.x = samples + sd.offset;
         c.n = int64_t(sd.n);
-        c.pre = pre_s;
+        c.pre = g_wpre;
         c.car = tab + kPre;
         c.lane = lane;
         c.cpos = 0;
         c.p = 0.0f;
         c.stage = stage_s[warp];
+        c.chk = pchk != nullptr ? pchk + sd.word_base : nullptr;
         const int64_t nwords = (c.n + 31) / 32;
         int64_t r = 0, cur = 0, start = 0;
         float local_max = 0.0f;
@@ -858,7 +988,7 @@ int tmk_ask_sync_device(tmk_engine* e, const float* samples, uint64_t total_samp
     static const bool direct = getenv("TMK_ASK_DIRECT") != nullptr;
     const uint64_t tile_len = direct ? kT : kT2;
     std::vector<AskStream> sd(n_streams);
-    uint64_t words = 0, tiles = 0;
+    uint64_t words = 0, tiles = 0, segs = 0;
     for (uint32_t s = 0; s < n_streams; ++s) {
         if (streams[s].offset % 4 != 0) return tmk_fail(e, TMK_E_INVALID, "stream offset must be a multiple of 4 samples");
         if (streams[s].offset > total_samples || streams[s].n_samples > total_samples - streams[s].offset)
@@ -867,7 +997,9 @@ int tmk_ask_sync_device(tmk_engine* e, const float* samples, uint64_t total_samp
         sd[s].n = streams[s].n_samples;
         sd[s].word_base = words;
         sd[s].tile_base = uint32_t(tiles);
-        sd[s].pad_ = 0;
+        sd[s].seg_base = uint32_t(segs);
+        segs += (streams[s].n_samples + kSeg - 1) / kSeg;
+        if (segs > 0x7fffffffull) return tmk_fail(e, TMK_E_INVALID, "batch too large (segment count)");
         words += (streams[s].n_samples + 31) / 32;
         tiles += (streams[s].n_samples + tile_len - 1) / tile_len;
         if (tiles > 0x7fffffffull) return tmk_fail(e, TMK_E_INVALID, "batch too large (tile count)");
@@ -914,6 +1046,19 @@ int tmk_ask_sync_device(tmk_engine* e, const float* samples, uint64_t total_samp
     }
     CK(cudaGetLastError());
     CK(cudaEventRecord(e->ev[1], e->stream));
+    // exact power checkpoints for the walk (TMK_ASK_NO_CHK=1: the walk chains through every sample itself, for A/B)
+    static const bool no_chk = getenv("TMK_ASK_NO_CHK") != nullptr;
+    float* pchk = nullptr;
+    if (!no_chk && segs) {
+        CK(e->d_ask_chk.reserve((words + 2) * sizeof(float) + sizeof(uint32_t) * n_streams));
+        pchk = static_cast<float*>(e->d_ask_chk.p);
+        uint32_t* xmax = reinterpret_cast<uint32_t*>(pchk + words + 2);
+        CK(cudaMemsetAsync(xmax, 0, sizeof(uint32_t) * n_streams, e->stream));
+        ask_xmax_kernel<<<uint32_t((segs + 7) / 8), 256, 0, e->stream>>>(dx, ds, n_streams, uint32_t(segs), xmax);
+        ask_power_kernel<<<uint32_t((segs + 127) / 128), 128, 0, e->stream>>>(dx, ds, n_streams, uint32_t(segs), xmax, pchk);
+        e->launches += 2;
+        CK(cudaGetLastError());
+    }
     static int walk_ctas = 0;
     if (walk_ctas == 0) {
         int sms = 0, per_sm = 0;
@@ -922,7 +1067,7 @@ int tmk_ask_sync_device(tmk_engine* e, const float* samples, uint64_t total_samp
         walk_ctas = sms * (per_sm > 0 ? per_sm : 1);
     }
     const uint32_t grid = std::min<uint32_t>((n_streams + 3) / 4, uint32_t(walk_ctas));
-    ask_walk_kernel<<<grid, 128, 0, e->stream>>>(dx, ds, n_streams, tab, static_cast<const uint32_t*>(e->d_ask_bits.p),
+    ask_walk_kernel<<<grid, 128, 0, e->stream>>>(dx, ds, n_streams, tab, static_cast<const uint32_t*>(e->d_ask_bits.p), pchk,
                                                  static_cast<tmk_ask_rec*>(e->d_ask_recs.p), dev_cap,
                                                  static_cast<unsigned long long*>(e->d_ask_l2.p));
     e->launches += 1;
