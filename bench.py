@@ -743,7 +743,7 @@ def main():
             st4, tot4 = tmkphy.make_streams([per4] * n4, cfgs4)
             configs["C4_hour_captures"] = phy_leg(
                 eng, orc, tmkphy, "C4: 8 captures x 172.8 M samples (1 h @ 48 kHz), one frame per ~0.5 s, +-100 ppm clock drift, "
-                "amplitude U[0.3, 1], AWGN 10 dB; one warp walks one capture", d4, st4, tot4, 3, 2, hbm, 2, threads,
+                "amplitude U[0.3, 1], AWGN 10 dB; each capture walked by ~440 warps at once (segmented walk)", d4, st4, tot4, 3, 2, hbm, 2, threads,
                 {"frames_planted": pl4})
             eng.device_free(d4)
     if run_cfgs and "c5" in want_cfg:

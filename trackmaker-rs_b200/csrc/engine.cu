@@ -203,7 +203,7 @@ void tmk_engine_destroy(tmk_engine* e) {
                       &e->d_recs, &e->d_payload, &e->d_cnt, &e->d_base, &e->d_counters, &e->d_samples,
                       &e->d_misc, &e->d_misc2, &e->d_next, &e->d_cblk, &e->d_blk_ptr, &e->d_entries, &e->d_spec, &e->d_pool, &e->d_link, &e->d_pcm, &e->d_frag,
                       &e->d_ask_tab, &e->d_ask_bits, &e->d_ask_l2,
-                      &e->d_ask_recs, &e->d_ask_recs2, &e->d_ask_chk, &e->d_mcm_tab, &e->d_mcm_recs, &e->d_mcm_off};
+                      &e->d_ask_recs, &e->d_ask_recs2, &e->d_ask_chk, &e->d_seg, &e->d_mcm_tab, &e->d_mcm_recs, &e->d_mcm_off};
     for (DevBuf* b : bufs) b->release();
     for (int i = 0; i < 6; ++i)
         if (e->ev[i]) cudaEventDestroy(e->ev[i]);
@@ -388,9 +388,63 @@ static int decode_batch_impl(tmk_engine* e, const void* samples_v, bool pcm16, u
     }
     CK(e->d_blk_info.reserve(sizeof(float4) * std::max<uint64_t>(1, b.n_blocks)));
     CK(e->d_cand.reserve(sizeof(uint32_t) * TMK_BLK_WORDS * std::max<uint64_t>(1, b.n_blocks)));
-    CK(e->d_cnt.reserve(sizeof(uint32_t) * n_streams));
-    CK(e->d_base.reserve(sizeof(uint64_t) * (n_streams + 1)));
-    CK(e->d_next.reserve(sizeof(unsigned int) * (chunks.size() + 1)));
+    // Segmented walk (tmk_internal.cuh): when the batch has too few captures to fill the GPU with one warp per capture, long
+    // one-shot captures are cut into segments walked at once (BASELINE config 4: an hour-long capture is 172.8 M samples)
+    std::vector<TmkSegItem> items;
+    std::vector<uint32_t> item_base(n_streams + 1, 0);
+    bool seg_mode = false;
+    {
+        uint64_t target_walkers = 148ull * 24, seg_min = 131072;
+        if (const char* ev = getenv("TMK_WALK_SEGMENTS")) target_walkers = strtoull(ev, nullptr, 10);  // 0 / 1: off
+        if (const char* ev = getenv("TMK_WALK_SEG_MIN")) seg_min = std::max<uint64_t>(1024, strtoull(ev, nullptr, 10));
+        if (!link_init && !link_final && total_samples && uint64_t(n_streams) * 2 <= target_walkers) {
+            items.reserve(size_t(target_walkers) + n_streams);
+            for (uint32_t s = 0; s < n_streams; ++s) {
+                item_base[s] = uint32_t(items.size());
+                const TmkStreamDev& d = b.sd[s];
+                const uint32_t P = e->patterns[d.pattern].P;
+                const uint64_t nwin = d.n_samples >= P ? d.n_samples - P + 1 : 0;
+                uint64_t nseg = 1;
+                const bool one_shot = d.chunk == 0 || d.chunk >= d.n_samples;
+                if (one_shot && nwin > 2 * seg_min) {
+                    const uint64_t share = (target_walkers * d.n_samples + total_samples - 1) / total_samples;
+                    nseg = std::max<uint64_t>(1, std::min<uint64_t>(std::min<uint64_t>(share, nwin / seg_min), 60000));
+                }
+                const uint64_t unit = uint64_t(TMK_BLK) * 32;  // a walker reads block summaries 32 at a time
+                uint64_t seg_len = nseg > 1 ? ((nwin + nseg - 1) / nseg + unit - 1) / unit * unit : std::max<uint64_t>(nwin, 1);
+                nseg = nseg > 1 ? (nwin + seg_len - 1) / seg_len : 1;
+                for (uint64_t k = 0; k < nseg; ++k) {
+                    TmkSegItem it;
+                    it.stream = s;
+                    it.seg = uint32_t(k);
+                    it.first_item = item_base[s];
+                    it.n_seg = uint32_t(nseg);
+                    it.q0 = k == 0 ? d.init_q : k * seg_len;
+                    it.q1 = k + 1 < nseg ? (k + 1) * seg_len : ~0ull;
+                    it.seg_len = seg_len;
+                    items.push_back(it);
+                }
+            }
+            item_base[n_streams] = uint32_t(items.size());
+            seg_mode = items.size() > n_streams;
+        }
+    }
+    const uint32_t n_items = seg_mode ? uint32_t(items.size()) : n_streams;
+    TmkSegItem* d_items = nullptr;
+    TmkSegState* d_segst = nullptr;
+    uint32_t* d_first_valid = nullptr;
+    if (seg_mode) {
+        const size_t ib = sizeof(TmkSegItem) * n_items, sb = sizeof(TmkSegState) * n_items;
+        CK(e->d_seg.reserve(ib + sb + sizeof(uint32_t) * n_items + 64));
+        d_items = static_cast<TmkSegItem*>(e->d_seg.p);
+        d_segst = reinterpret_cast<TmkSegState*>(static_cast<char*>(e->d_seg.p) + ib);
+        d_first_valid = reinterpret_cast<uint32_t*>(static_cast<char*>(e->d_seg.p) + ib + sb);
+        CK(cudaMemcpyAsync(d_items, items.data(), ib, cudaMemcpyHostToDevice, e->stream));
+        CK(cudaMemsetAsync(d_segst, 0, sb, e->stream));
+    }
+    CK(e->d_cnt.reserve(sizeof(uint32_t) * n_items * (seg_mode ? 2 : 1)));
+    CK(e->d_base.reserve(sizeof(uint64_t) * (n_items + 1)));
+    CK(e->d_next.reserve(sizeof(unsigned int) * (2 * chunks.size() + 1)));
     // cluster pass (walk.cu): candidate entries + speculative verdicts, per chunk its own list region / counter
     const bool use_fast = b.n_blocks > 0 && b.n_blocks < (1ull << 31) && !getenv("TMK_NO_CLUSTER");
     // (the walk of a chunk follows its cluster pass: running them side by side — the walk waiting for blocks the
@@ -453,7 +507,7 @@ static int decode_batch_impl(tmk_engine* e, const void* samples_v, bool pcm16, u
     CK(cudaMemsetAsync(dcb, 0, sizeof(uint32_t) * TMK_BLK_WORDS * b.n_blocks, e->stream));  // (the CUDA-core scan ORs its bits in)
 #endif
     CK(cudaMemsetAsync(dc, 0, sizeof(TmkCounters), e->stream));
-    CK(cudaMemsetAsync(dnext, 0, sizeof(unsigned int) * (chunks.size() + 1), e->stream));
+    CK(cudaMemsetAsync(dnext, 0, sizeof(unsigned int) * (2 * chunks.size() + 1), e->stream));
     if (use_fast) {
         CK(cudaMemsetAsync(e->d_pool.p, 0, sizeof(unsigned int) * (2 + 2 * chunks.size()), e->stream));
     }
@@ -499,9 +553,17 @@ static int decode_batch_impl(tmk_engine* e, const void* samples_v, bool pcm16, u
                 CK(cudaStreamWaitEvent(ws, e->wev[0], 0));
             }
         }
+        if (seg_mode) {  // pass 1: every walker over its segment; pass 2: on to the meeting point with the next walkers
+            for (uint32_t pass = 1; pass <= 2; ++pass)
+                e->launches += tmk_launch_walk(dx, ds, item_base[ch.s0], item_base[ch.s1], dnext + (pass == 1 ? g : chunks.size() + 1 + g),
+                                               fast, dp, dbi, dcb, static_cast<tmk_frame_rec*>(e->d_recs_tmp.p),
+                                               static_cast<uint4*>(e->d_rec_ord.p), dev_rec_cap, dpay, dev_pay_cap,
+                                               static_cast<uint32_t*>(e->d_cnt.p), dc, nullptr, ws, TmkSeg{d_items, d_segst, pass, 0});
+        } else {
         e->launches += tmk_launch_walk(dx, ds, ch.s0, ch.s1, dnext + g, fast, dp, dbi, dcb,
                                        static_cast<tmk_frame_rec*>(e->d_recs_tmp.p), static_cast<uint4*>(e->d_rec_ord.p),
                                        dev_rec_cap, dpay, dev_pay_cap, static_cast<uint32_t*>(e->d_cnt.p), dc, d_link, ws);
+        }
         CK(cudaGetLastError());
     }
     if (chunks.size() != 1) CK(cudaEventRecord(e->ev[2], e->stream));  // end of the last scan
@@ -511,15 +573,31 @@ static int decode_batch_impl(tmk_engine* e, const void* samples_v, bool pcm16, u
     }
     TmkCounters hc;
     uint64_t n_exact = 0;  // records = sum of the per-stream counts
+    if (seg_mode) {
+        // which records of which walker count (meeting points), their verdict tallies, then the counts per walker
+        uint32_t* d_nvalid = static_cast<uint32_t*>(e->d_cnt.p) + n_items;
+        e->launches += tmk_launch_seg_resolve(d_items, d_segst, n_items, d_first_valid, d_nvalid,
+                                              static_cast<const tmk_frame_rec*>(e->d_recs_tmp.p), static_cast<const uint4*>(e->d_rec_ord.p),
+                                              dev_rec_cap, dev_rec_cap, use_fast ? static_cast<const tmk_frame_rec*>(e->d_spec.p) : nullptr,
+                                              dc, e->stream);
+        e->launches += tmk_launch_excl_scan(d_nvalid, static_cast<uint64_t*>(e->d_base.p), n_items, e->stream);
+        CK(cudaMemcpyAsync(&n_exact, static_cast<uint64_t*>(e->d_base.p) + n_items, sizeof n_exact, cudaMemcpyDeviceToHost, e->stream));
+    } else {
     e->launches += tmk_launch_excl_scan(static_cast<const uint32_t*>(e->d_cnt.p), static_cast<uint64_t*>(e->d_base.p), n_streams, e->stream);
     CK(cudaMemcpyAsync(&n_exact, static_cast<uint64_t*>(e->d_base.p) + n_streams, sizeof n_exact, cudaMemcpyDeviceToHost, e->stream));
+    }
     CK(cudaMemcpyAsync(&hc, dc, sizeof hc, cudaMemcpyDeviceToHost, e->stream));
     CK(cudaStreamSynchronize(e->stream));
     for (int attempt = 0; attempt < 2; ++attempt) {
-        const bool rec_short = hc.n_recs > dev_rec_cap && dev_rec_cap < rec_cap + kSlotSlack;
-        const bool pay_short = hc.n_payload > dev_pay_cap && dev_pay_cap < payload_cap;
+        // (the counters of the first pass include what is dropped later: payload bytes of speculative decodes that no
+        //  walk linked, records and bytes of segment walkers before their meeting point — before a caller's exactly
+        //  sized buffer is called too small, the plain walk counts again)
+        const bool dead = attempt == 0 && (seg_mode || use_fast);
+        const bool rec_short = hc.n_recs > dev_rec_cap && (dev_rec_cap < rec_cap + kSlotSlack || (dead && seg_mode));
+        const bool pay_short = hc.n_payload > dev_pay_cap && (dev_pay_cap < payload_cap || dead);
         if (!rec_short && !pay_short) break;
         // the guess was too small: grow the scratch and walk every stream again (everything is resident now)
+        seg_mode = false;  // (one walker per capture in this rare second pass)
         if (rec_short) dev_rec_cap = std::min<uint64_t>(rec_cap, hc.n_recs) + kSlotSlack;
         if (pay_short) dev_pay_cap = std::min<uint64_t>(payload_cap, hc.n_payload);
         CK(e->d_recs_tmp.reserve(sizeof(tmk_frame_rec) * std::max<uint64_t>(1, dev_rec_cap)));
@@ -559,6 +637,13 @@ static int decode_batch_impl(tmk_engine* e, const void* samples_v, bool pcm16, u
             CK(e->d_recs.reserve(sizeof(tmk_frame_rec) * n_exact));
             dout = static_cast<tmk_frame_rec*>(e->d_recs.p);
         }
+        if (seg_mode)
+            e->launches += tmk_launch_seg_order(static_cast<const tmk_frame_rec*>(e->d_recs_tmp.p),
+                                                static_cast<const uint4*>(e->d_rec_ord.p), hc.n_recs,
+                                                static_cast<const uint64_t*>(e->d_base.p),
+                                                use_fast ? static_cast<const tmk_frame_rec*>(e->d_spec.p) : nullptr, d_items, d_first_valid,
+                                                dout, e->stream);
+        else
         e->launches += tmk_launch_order(static_cast<const tmk_frame_rec*>(e->d_recs_tmp.p),
                                         static_cast<const uint4*>(e->d_rec_ord.p), hc.n_recs,
                                         static_cast<const uint32_t*>(e->d_cnt.p), static_cast<uint64_t*>(e->d_base.p),

@@ -44,6 +44,7 @@ struct tmk_engine {
     DevBuf d_mcm_tab, d_mcm_recs, d_mcm_off;  // multi-carrier modem (mcm.cu): tables, device records, stream offsets
     bool mcm_ready = false;
     float mcm_demod_ms = 0.0f;
+    DevBuf d_seg;  // segmented walk: items, walker states, first valid record per walker
     DevBuf d_tile_desc;  // per-tile descriptors of the tensor-core scan (scan_tc.cu)
     DevBuf d_comm, d_wav, d_wavdesc;  // staging of the counter all-reduce (comm.cu); raw WAV bytes + descriptors (wav.cu)
     float* scan_dbg_dot = nullptr;    // set around tmk_scan_probe by tmk_scan_dot_probe (diagnostic)

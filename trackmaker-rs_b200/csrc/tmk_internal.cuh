@@ -111,6 +111,38 @@ struct TmkFast {
     unsigned int* item_next;         // work counter of the cluster pass (one per chunk)
 };
 
+// ---- segmented walk (walk.cu): a long one-shot capture is walked by several warps at once. Walker j starts a search
+// at the first window of segment j as if the decoder were Searching there; the state of the reference's decoder at a
+// search entry is its position alone (one-shot feeding: every sample is buffered, the rolling energy is re-seeded at the
+// entry), so from the first search entry that a walker shares with the walk coming from the segments before it, its
+// records ARE that walk's. Pass 1: every walker runs to its first search entry at or behind the end of its segment.
+// Pass 2: it goes on from there until its search entry is one of the first entries of the walker that owns the position
+// (or the capture ends). Resolve: from walker 0 (exact by definition) along those meeting points; the records of a
+// walker before its meeting point and of walkers that were skipped are dropped.
+struct TmkSegItem {
+    uint32_t stream;      // the capture
+    uint32_t seg;         // segment index inside it
+    uint32_t first_item;  // item of the capture's segment 0
+    uint32_t n_seg;       // segments of the capture
+    uint64_t q0, q1;      // first search entry; pause at the first search entry >= q1 (the last segment: never)
+    uint64_t seg_len;     // windows per segment
+};
+#define TMK_SEG_HEADS 8
+struct TmkSegState {
+    uint64_t q;           // search entry at which the walker paused (pass 1) / met another walker (pass 2)
+    uint32_t ord;         // records emitted so far
+    uint32_t state;       // 0 ended (capture exhausted), 1 paused, 2 met walker sync_item at its entry sync_ord
+    uint32_t sync_item, sync_ord;
+    uint32_t n_head, pad_;
+    uint64_t head[TMK_SEG_HEADS];  // search entry after record 0, 1, ... of pass 1
+};
+struct TmkSeg {
+    const TmkSegItem* items;  // nullptr: one walker per capture (the plain walk)
+    TmkSegState* st;
+    uint32_t pass;
+    uint32_t pad_;
+};
+
 __host__ __device__ inline uint64_t tmk_sfb(int line_code, uint32_t spl, uint64_t nbits) {
     // LineCode::samples_for_bits  line_coding.rs:125-127 (Manchester), :295-300 (4B5B)
     return line_code == TMK_LINE_MANCHESTER ? nbits * spl * 2 : ((nbits + 3) / 4) * 5 * spl;
@@ -175,7 +207,15 @@ int tmk_launch_walk(const float* samples, const TmkStreamDev* streams, uint32_t 
                     const TmkPattern* patterns, const float4* blk_info, const uint32_t* cand_bits,
                     tmk_frame_rec* recs, uint4* rec_ord, uint64_t rec_cap, uint8_t* payload,
                     uint64_t payload_cap, uint32_t* stream_cnt, TmkCounters* counters, TmkLinkState* link_out,
-                    cudaStream_t st);
+                    cudaStream_t st, TmkSeg seg = TmkSeg{nullptr, nullptr, 0, 0});
+// segmented walk: valid record range per walker (first_valid / n_valid), verdict tallies of the valid records, and the
+// ordering of the valid records into (capture, time) order
+int tmk_launch_seg_resolve(const TmkSegItem* items, const TmkSegState* st, uint32_t n_items, uint32_t* first_valid,
+                           uint32_t* n_valid, const tmk_frame_rec* recs, const uint4* rec_ord, uint64_t n_slots, uint64_t rec_cap,
+                           const tmk_frame_rec* spec, TmkCounters* counters, cudaStream_t stream);
+int tmk_launch_seg_order(const tmk_frame_rec* recs_in, const uint4* rec_ord, uint64_t n_slots, const uint64_t* base,
+                         const tmk_frame_rec* spec, const TmkSegItem* items, const uint32_t* first_valid,
+                         tmk_frame_rec* recs_out, cudaStream_t stream);
 int tmk_launch_replay_probe(const float* samples, const TmkStreamDev* streams, const TmkPattern* patterns, uint64_t seed,
                             const uint64_t* ws, uint32_t n, float* out, unsigned long long* counts, cudaStream_t st);
 int tmk_launch_order(const tmk_frame_rec* recs_in, const uint4* rec_ord, uint64_t n_recs,

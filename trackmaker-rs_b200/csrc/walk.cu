@@ -1743,14 +1743,16 @@ cluster_kernel(const float* __restrict__ samples, const TmkStreamDev* __restrict
 // of warps that sit in different stages of 136 KB of code, spills below 168 registers).
 #define TMK_WALK_CTAS 3
 #endif
+template <bool SEG>  // SEG: the work items are segments of captures (segmented walk); the plain walk carries none of its state
 __global__ void __launch_bounds__(kWarpsPerCta * 32, TMK_WALK_CTAS)
 walk_kernel(const float* __restrict__ samples, const TmkStreamDev* __restrict__ streams, uint32_t s0, uint32_t s1,
             unsigned int* __restrict__ next, TmkFast fast,
             const TmkPattern* __restrict__ patterns, const float4* __restrict__ blk_info,
             const uint32_t* __restrict__ cand_bits, tmk_frame_rec* recs, uint4* rec_ord, uint64_t rec_cap,
             uint8_t* payload, uint64_t payload_cap, uint32_t* stream_cnt, TmkCounters* counters,
-            TmkLinkState* link_out) {
+            TmkLinkState* link_out, TmkSeg seg) {
     const uint32_t warp = threadIdx.x >> 5;
+    constexpr bool segm = SEG;  // (tmk_internal.cuh: segmented walk)
     const int lane_id = threadIdx.x & 31;
     Emit em{recs, rec_ord, rec_cap, payload, payload_cap, counters, 0, 0, 0ull, 0ull};
     // persistent warps: streams differ a lot in cost (idle noise vs dense traffic), so every warp
@@ -1764,17 +1766,31 @@ walk_kernel(const float* __restrict__ samples, const TmkStreamDev* __restrict__ 
             if (sl < rec_cap) rec_ord[sl].y = kNoRecord;
         return;
     }
-    const TmkStreamDev sd = streams[sidx];
+    uint32_t real = sidx, ord0 = 0;
+    uint64_t q1 = ~0ull;  // pass 1 of a segmented walk: pause at the first search entry at or behind this window
+    if (segm) {
+        real = seg.items[sidx].stream;
+        if (seg.pass == 1) {
+            q1 = seg.items[sidx].q1;
+        } else {  // pass 2: only walkers that paused at the end of their segment go on
+            const TmkSegState* ps = seg.st + sidx;
+            if (ps->state != 1) continue;
+            ord0 = ps->ord;
+        }
+    }
+    const TmkStreamDev sd = streams[real];
     Ctx c;
     init_ctx(c, samples, sd, patterns, blk_info, cand_bits, fast, lane_id, warp);
     em.stream = sidx;
-    em.ord = 0;
+    em.ord = ord0;
     uint32_t n_ok = 0, n_crc = 0, n_hdr = 0, n_nfu = 0;
+    uint32_t seg_exit = 0, sync_item = 0, sync_ord = 0;
 
     const int lc = c.pat->line_code;
     const uint32_t spl = c.pat->spl;
     const uint32_t hs = c.pat->hdr_samples;
     uint64_t q = sd.init_q;                   // buffer_offset (absolute)
+    if (segm) q = seg.pass == 1 ? seg.items[sidx].q0 : seg.st[sidx].q;
     uint64_t avail = c.C ? c.C : c.N;         // samples fed so far
     bool resume = sd.init_fs != TMK_NO_FRAME;  // the previous process_samples call ended in Decoding(frame_start)
     TmkLinkState fin;
@@ -1785,6 +1801,33 @@ walk_kernel(const float* __restrict__ samples, const TmkStreamDev* __restrict__ 
     Detection d;
     for (;;) {
         uint64_t fs;
+        if (segm) {  // q is a search entry
+            if (seg.pass == 1) {
+                if (em.ord >= 1 && em.ord <= TMK_SEG_HEADS && lane_id == 0) seg.st[sidx].head[em.ord - 1] = q;
+                if (q >= q1) {
+                    seg_exit = 1;
+                    break;
+                }
+            } else {
+                // has the walker that owns this position been here? (its first search entries, written by pass 1)
+                const TmkSegItem it = seg.items[sidx];
+                uint64_t k = q / it.seg_len;
+                if (k >= it.n_seg) k = it.n_seg - 1;
+                const uint32_t owner = it.first_item + uint32_t(k);
+                const TmkSegState* os = seg.st + owner;
+                const uint32_t nh = os->n_head;
+                bool hit = false;
+                if (lane_id == 0) hit = seg.items[owner].q0 == q;
+                else if (uint32_t(lane_id) <= nh) hit = os->head[lane_id - 1] == q;
+                const uint32_t hm = __ballot_sync(kFull, hit);
+                if (hm && owner != sidx) {
+                    sync_item = owner;
+                    sync_ord = uint32_t(__ffs(hm) - 1);
+                    seg_exit = 2;
+                    break;
+                }
+            }
+        }
         if (resume) {
             resume = false;
             d.c = sd.init_q;
@@ -1917,12 +1960,23 @@ walk_kernel(const float* __restrict__ samples, const TmkStreamDev* __restrict__ 
     if (c.lane == 0) {
         if (link_out) link_out[sidx] = fin;
         stream_cnt[sidx] = em.ord;
+        if (segm) {  // the verdict tallies come from the records that survive the resolve step
+            TmkSegState* ps = seg.st + sidx;
+            ps->q = q;
+            ps->ord = em.ord;
+            ps->state = seg_exit;
+            ps->sync_item = sync_item;
+            ps->sync_ord = sync_ord;
+            if (seg.pass == 1) ps->n_head = em.ord < TMK_SEG_HEADS ? em.ord : TMK_SEG_HEADS;
+            if (seg.pass == 1 && seg.items[sidx].seg == 0) atomicAdd(&counters->stats[TMK_STAT_SAMPLES], (unsigned long long)c.N);
+        } else {
         atomicAdd(&counters->stats[TMK_STAT_SAMPLES], (unsigned long long)c.N);
         atomicAdd(&counters->stats[TMK_STAT_DETECTIONS], (unsigned long long)c.n_det);
         atomicAdd(&counters->stats[TMK_STAT_FRAMES_OK], (unsigned long long)n_ok);
         atomicAdd(&counters->stats[TMK_STAT_CRC_FAIL], (unsigned long long)n_crc);
         atomicAdd(&counters->stats[TMK_STAT_HDR_FAIL], (unsigned long long)n_hdr);
         atomicAdd(&counters->stats[TMK_STAT_NOT_FOR_US], (unsigned long long)n_nfu);
+        }
         atomicAdd(&counters->stats[TMK_STAT_EXACT_REPLAYS], (unsigned long long)c.n_replays);
         atomicAdd(&counters->stats[TMK_STAT_CANDIDATES], (unsigned long long)c.n_cands);
         for (int i = 0; i < 4; ++i) atomicAdd(&counters->dbg[i], c.dbg[i]);
@@ -1982,6 +2036,72 @@ __global__ void order_kernel(const tmk_frame_rec* __restrict__ in, const uint4* 
     r.stream = ln.z;
     r.corr = __uint_as_float(ln.w);
     out[base[ln.z] + ln.y] = r;
+}
+
+// ---- segmented walk: which records count
+constexpr uint32_t kSegInvalid = 0xffffffffu;
+// one thread per capture: from its walker 0 along the meeting points
+__global__ void seg_chain_kernel(const TmkSegItem* __restrict__ items, const TmkSegState* __restrict__ st, uint32_t n_items,
+                                 uint32_t* __restrict__ first_valid, uint32_t* __restrict__ n_valid) {
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n_items) return;
+    const TmkSegItem it = items[i];
+    if (it.seg != 0) return;
+    for (uint32_t k = 0; k < it.n_seg; ++k) {
+        first_valid[i + k] = kSegInvalid;
+        n_valid[i + k] = 0;
+    }
+    uint32_t cur = i, start = 0;
+    for (uint32_t guard = 0; guard <= it.n_seg; ++guard) {
+        const TmkSegState s = st[cur];
+        first_valid[cur] = start;
+        n_valid[cur] = s.ord >= start ? s.ord - start : 0;
+        if (s.state != 2 || s.sync_item <= cur || s.sync_item >= i + it.n_seg) break;
+        start = s.sync_ord;
+        cur = s.sync_item;
+    }
+}
+// verdict tallies of the records that count (the walkers of a segmented walk do not tally: part of their records is dropped)
+__global__ void seg_tally_kernel(const tmk_frame_rec* __restrict__ in, const uint4* __restrict__ ord, uint64_t rec_cap,
+                                 const tmk_frame_rec* __restrict__ spec, const uint32_t* __restrict__ first_valid,
+                                 TmkCounters* counters) {
+    const uint64_t i = uint64_t(blockIdx.x) * blockDim.x + threadIdx.x;
+    const uint64_t n = counters->n_recs;  // slots the walkers reserved (the host does not know the number yet)
+    uint32_t status = 0xffu;
+    if (i < n && i < rec_cap) {
+        const uint4 ln = ord[i];
+        if (ln.y != kNoRecord) {
+            const uint32_t f = first_valid[ln.z];
+            if (f != kSegInvalid && ln.y >= f) status = ln.x != TMK_ENT_INVALID ? spec[ln.x].status : in[i].status;
+        }
+    }
+    const uint32_t any = __ballot_sync(kFull, status != 0xffu);
+    if (!any) return;
+    const uint32_t ok = __ballot_sync(kFull, status == TMK_FRAME_OK), crc = __ballot_sync(kFull, status == TMK_FRAME_CRC_FAIL);
+    const uint32_t nfu = __ballot_sync(kFull, status == TMK_FRAME_NOT_FOR_US), tr = __ballot_sync(kFull, status == TMK_FRAME_TRUNCATED);
+    if ((threadIdx.x & 31) == 0) {
+        atomicAdd(&counters->stats[TMK_STAT_DETECTIONS], (unsigned long long)__popc(any));
+        if (ok) atomicAdd(&counters->stats[TMK_STAT_FRAMES_OK], (unsigned long long)__popc(ok));
+        if (crc) atomicAdd(&counters->stats[TMK_STAT_CRC_FAIL], (unsigned long long)__popc(crc));
+        if (nfu) atomicAdd(&counters->stats[TMK_STAT_NOT_FOR_US], (unsigned long long)__popc(nfu));
+        const uint32_t hdr = any & ~(ok | crc | nfu | tr);
+        if (hdr) atomicAdd(&counters->stats[TMK_STAT_HDR_FAIL], (unsigned long long)__popc(hdr));
+    }
+}
+__global__ void seg_order_kernel(const tmk_frame_rec* __restrict__ in, const uint4* __restrict__ ord, uint64_t n,
+                                 const uint64_t* __restrict__ base, const tmk_frame_rec* __restrict__ spec,
+                                 const TmkSegItem* __restrict__ items, const uint32_t* __restrict__ first_valid,
+                                 tmk_frame_rec* __restrict__ out) {
+    const uint64_t i = uint64_t(blockIdx.x) * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const uint4 ln = ord[i];
+    if (ln.y == kNoRecord) return;
+    const uint32_t f = first_valid[ln.z];
+    if (f == kSegInvalid || ln.y < f) return;  // before the walker's meeting point, or a walker that was passed over
+    tmk_frame_rec r = ln.x != TMK_ENT_INVALID ? spec[ln.x] : in[i];
+    r.stream = items[ln.z].stream;
+    r.corr = __uint_as_float(ln.w);
+    out[base[ln.z] + (ln.y - f)] = r;
 }
 
 }  // namespace
@@ -2054,7 +2174,7 @@ int tmk_launch_walk(const float* samples, const TmkStreamDev* streams, uint32_t 
                     const TmkPattern* patterns, const float4* blk_info, const uint32_t* cand_bits,
                     tmk_frame_rec* recs, uint4* rec_ord, uint64_t rec_cap, uint8_t* payload,
                     uint64_t payload_cap, uint32_t* stream_cnt, TmkCounters* counters, TmkLinkState* link_out,
-                    cudaStream_t st) {
+                    cudaStream_t st, TmkSeg seg) {
     if (s1 <= s0) return 0;
     const uint32_t n_streams = s1 - s0;
     static int max_ctas = 0;
@@ -2062,13 +2182,35 @@ int tmk_launch_walk(const float* samples, const TmkStreamDev* streams, uint32_t 
         int dev = 0, sms = 0, per_sm = 0;
         cudaGetDevice(&dev);
         cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
-        cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, walk_kernel, kWarpsPerCta * 32, 0);
+        cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, walk_kernel<false>, kWarpsPerCta * 32, 0);
         max_ctas = sms * (per_sm > 0 ? per_sm : 1);
     }
     uint32_t grid = (n_streams + kWarpsPerCta - 1) / kWarpsPerCta;
     if (grid > uint32_t(max_ctas)) grid = uint32_t(max_ctas);
-    walk_kernel<<<grid, kWarpsPerCta * 32, 0, st>>>(samples, streams, s0, s1, next, fast, patterns, blk_info, cand_bits, recs,
-                                                    rec_ord, rec_cap, payload, payload_cap, stream_cnt, counters, link_out);
+    if (seg.items != nullptr)
+        walk_kernel<true><<<grid, kWarpsPerCta * 32, 0, st>>>(samples, streams, s0, s1, next, fast, patterns, blk_info, cand_bits, recs,
+                                                              rec_ord, rec_cap, payload, payload_cap, stream_cnt, counters, link_out, seg);
+    else
+        walk_kernel<false><<<grid, kWarpsPerCta * 32, 0, st>>>(samples, streams, s0, s1, next, fast, patterns, blk_info, cand_bits, recs,
+                                                               rec_ord, rec_cap, payload, payload_cap, stream_cnt, counters, link_out, seg);
+    return 1;
+}
+
+int tmk_launch_seg_resolve(const TmkSegItem* items, const TmkSegState* st, uint32_t n_items, uint32_t* first_valid,
+                           uint32_t* n_valid, const tmk_frame_rec* recs, const uint4* rec_ord, uint64_t n_slots, uint64_t rec_cap,
+                           const tmk_frame_rec* spec, TmkCounters* counters, cudaStream_t stream) {
+    seg_chain_kernel<<<(n_items + 127) / 128, 128, 0, stream>>>(items, st, n_items, first_valid, n_valid);
+    if (n_slots == 0) return 1;
+    seg_tally_kernel<<<uint32_t((n_slots + 255) / 256), 256, 0, stream>>>(recs, rec_ord, rec_cap, spec, first_valid, counters);
+    return 2;
+}
+
+int tmk_launch_seg_order(const tmk_frame_rec* recs_in, const uint4* rec_ord, uint64_t n_slots, const uint64_t* base,
+                         const tmk_frame_rec* spec, const TmkSegItem* items, const uint32_t* first_valid,
+                         tmk_frame_rec* recs_out, cudaStream_t stream) {
+    if (n_slots == 0) return 0;
+    seg_order_kernel<<<uint32_t((n_slots + 255) / 256), 256, 0, stream>>>(recs_in, rec_ord, n_slots, base, spec, items, first_valid,
+                                                                        recs_out);
     return 1;
 }
 
