@@ -1,0 +1,108 @@
+"""Two independent restatements of the reference's decoder against each other: the C++ oracle
+(oracle/phy_decoder.hpp) and a numpy-f32 one written from the Rust (oracle/second_restatement.py) decode the same random
+captures — one-shot and fed in random chunks — and must agree on every verdict, offset, header byte and payload byte.
+Plus the reference's other stored fixture (ref/checkutils/proj2/INPUT.bin, 6250 B) as a loopback through every modem, and
+the frame-length literal of docs/proj/report.md:166-169. None of this pins parity against the Rust binary itself (no
+rustc here or on the GPU box); it removes single-reader error from the restatement."""
+import os
+
+import numpy as np
+import pytest
+
+import helpers
+
+GOLDEN = os.path.join(os.path.dirname(__file__), "golden")
+FB, MAN = 1, 0
+
+
+def events_of(orc_recs, orc_pl):
+    out = []
+    for r in orc_recs:
+        pay = bytes(orc_pl[int(r["payload_off"]):int(r["payload_off"]) + int(r["len"])]) if r["status"] in (0, 4, 5) else b""
+        hdr = ([int(r["len"]) >> 8, int(r["len"]) & 255, int(r["crc"]), int(r["type"]), int(r["seq"]), int(r["src"]), int(r["dst"])]
+               if r["hdr_valid"] else None)
+        out.append((int(r["status"]), int(r["preamble_start"]), int(r["frame_start"]), int(r["consumed"]), hdr, pay))
+    return out
+
+
+@pytest.mark.parametrize("kind", [FB, MAN])
+def test_two_restatements_agree(orc, kind):
+    import tmkphy
+    from oracle.second_restatement import PhyDecoderPy
+    rng = np.random.default_rng(77 + kind)
+    cfg = tmkphy.make_config(kind, local_addr=1)
+    n_caps, n_events, statuses = 300, 0, set()
+    for k in range(n_caps):
+        snr = [None, 20.0, 10.0, 7.0, 6.0, 5.0, 3.0][k % 7]
+        c = helpers.make_capture(orc, cfg, rng, n_frames=int(rng.integers(1, 4)), snr_db=snr, multipath=(k % 5 == 4),
+                                 gap_range=(48, 400), tail=int(rng.integers(0, 300)), max_len=20,
+                                 amplitude=float(rng.uniform(0.2, 1.0)))
+        if k % 3 == 0 and len(c) > 600:  # flipped / zeroed stretches: every verdict and consume rule
+            a = int(rng.integers(0, len(c) - 300))
+            c[a:a + int(rng.integers(10, 300))] *= np.float32(-1.0 if k % 2 else 0.0)
+        if k % 4 == 0:
+            feeds = [len(c)]
+        else:
+            feeds, left = [], len(c)
+            while left:
+                f = min(left, int(rng.choice([1, 7, 48, 257, 1200, 3000])))
+                feeds.append(f)
+                left -= f
+        recs, pl, _ = orc.decode_feeds(cfg, c, feeds)
+        want = [e for e in events_of(recs, pl) if e[0] != 6]  # a frame still being gathered is state, not an event
+        dec = PhyDecoderPy(kind, local_addr=1)
+        pos = 0
+        for f in feeds:
+            dec.process_samples(c[pos:pos + f])
+            pos += f
+        got = [(s, p, fs, cons, (list(h) if h is not None else None), d) for s, p, fs, cons, h, d in dec.events]
+        assert got == want, f"capture {k} (snr {snr}, feeds {feeds[:6]}...): {got} != {want}"
+        n_events += len(want)
+        statuses |= {e[0] for e in want}
+    assert n_events > 300 and {0, 1, 5} <= statuses, (n_events, statuses)
+
+
+def test_input_bin_loopback_all_modems(orc):
+    """ref/checkutils/proj2/INPUT.bin (= OUTPUT.bin there): 6250 bytes through src/phy at both line codes, the chirp + BPSK
+    modem and the build-defined FSK / OFDM modem, decoded back to the same bytes"""
+    import tmkphy
+    data = open(os.path.join(GOLDEN, "INPUT.bin"), "rb").read()
+    assert len(data) == 6250
+    chunks = [data[i:i + 128] for i in range(0, len(data), 128)]
+    assert len(chunks) == 49 and len(chunks[-1]) == 106
+    for kind in (FB, MAN):
+        cfg = tmkphy.make_config(kind, local_addr=2)
+        x = orc.modulate(cfg, [(1, i & 255, 1, 2, c) for i, c in enumerate(chunks)], 48)
+        recs, pl = orc.decode_stream(cfg, x)
+        assert len(recs) == 49 and (recs["status"] == 0).all() and bytes(pl) == data
+        assert list(recs["len"]) == [128] * 48 + [106] and list(recs["seq"]) == list(range(49))
+    bits = np.unpackbits(np.frombuffer(data, np.uint8))
+    n_fr = (len(bits) + 91) // 92
+    fr = np.zeros((n_fr, 100), np.uint8)
+    for i in range(n_fr):
+        fr[i, :8] = [((i % 100 + 1) >> (7 - j)) & 1 for j in range(8)]
+        seg = bits[92 * i:92 * (i + 1)]
+        fr[i, 8:8 + len(seg)] = seg
+    x = np.concatenate([orc.ask_modulate(fr, [60] * n_fr, [60] * n_fr), np.zeros(400, np.float32)])
+    recs = orc.ask_demodulate(x)
+    assert len(recs) == n_fr and recs["accepted"].all()
+    got = np.concatenate([np.unpackbits(r["bits"])[8:100] for r in recs])[:len(bits)]
+    assert np.array_equal(got, bits)
+    for mode, cap in ((0, 25), (1, 100)):
+        pays = [data[i:i + cap] for i in range(0, len(data), cap)]
+        x = np.concatenate([orc.mcm_modulate(mode, pays, np.arange(len(pays)) & 255, [80] * len(pays), [80] * len(pays)),
+                            np.zeros(400, np.float32)])
+        recs, pl = orc.mcm_demodulate(mode, x)
+        assert len(recs) == len(pays) and (recs["status"] == 0).all() and bytes(pl) == data
+
+
+def test_report_frame_length_literal(orc):
+    """docs/proj/report.md:166-169: 64 B payload + 7 B header = 568 bits; Manchester at 3 samples per level = 3408 samples"""
+    import ctypes as C
+    import tmkphy
+    from tmkphy import _abi
+    assert orc.samples_for_bits(MAN, 3, (64 + 7) * 8) == 3408
+    cfg = tmkphy.make_config(MAN)
+    assert _abi.load_library().tmk_samples_for_bits(C.byref(cfg), 568) == 3408
+    x = orc.modulate(tmkphy.make_config(MAN, local_addr=2), [(1, 0, 1, 2, bytes(64))], 0)
+    assert len(x) == 96 + 3408
