@@ -73,7 +73,7 @@ def test_audio_data_json():
 
 # ---------------------------------------------------------------- ABI struct layouts, checked mechanically
 STRUCTS = ["tmk_phy_config", "tmk_stream", "tmk_frame_rec", "tmk_frame_desc", "tmk_ask_rec", "tmk_packet_rec",
-           "tmk_synth_params", "tmk_wav_info"]
+           "tmk_synth_params", "tmk_wav_info", "tmk_mcm_rec"]
 
 
 def c_layouts(tmp_path):
@@ -151,7 +151,8 @@ def test_abi_struct_layouts(tmp_path):
         for f in fields[name]:
             assert getattr(cls, f).offset == cl[f"{name}.{f}"], (name, f)
     for name, dt in (("tmk_frame_rec", _abi.REC_DTYPE), ("tmk_stream", _abi.STREAM_DTYPE), ("tmk_frame_desc", _abi.DESC_DTYPE),
-                     ("tmk_ask_rec", _abi.ASK_REC_DTYPE), ("tmk_packet_rec", _abi.PKT_DTYPE)):
+                     ("tmk_ask_rec", _abi.ASK_REC_DTYPE), ("tmk_packet_rec", _abi.PKT_DTYPE),
+                     ("tmk_mcm_rec", _abi.MCM_REC_DTYPE)):
         assert dt.itemsize == cl[name], name
         for f in fields[name]:
             assert dt.fields[f][1] == cl[f"{name}.{f}"], (name, f)

@@ -1022,6 +1022,32 @@ int tmk_ask_sync_device(tmk_engine* e, const float* samples, uint64_t total_samp
     const AskStream* ds = static_cast<const AskStream*>(e->d_streams.p);
     const float* tab = static_cast<const float*>(e->d_ask_tab.p);
     CK(cudaEventRecord(e->ev[0], e->stream));
+    // exact power checkpoints for the walk (TMK_ASK_NO_CHK=1: the walk chains through every sample itself, for A/B)
+    static const bool no_chk = getenv("TMK_ASK_NO_CHK") != nullptr;
+    float* pchk = nullptr;
+    if (!no_chk && segs) {
+        CK(e->d_ask_chk.reserve((words + 2) * sizeof(float) + sizeof(uint32_t) * n_streams));
+        pchk = static_cast<float*>(e->d_ask_chk.p);
+        uint32_t* xmax = reinterpret_cast<uint32_t*>(pchk + words + 2);
+        CK(cudaMemsetAsync(xmax, 0, sizeof(uint32_t) * n_streams, e->stream));
+        ask_xmax_kernel<<<uint32_t((segs + 7) / 8), 256, 0, e->stream>>>(dx, ds, n_streams, uint32_t(segs), xmax);
+        ask_power_kernel<<<uint32_t((segs + 127) / 128), 128, 0, e->stream>>>(dx, ds, n_streams, uint32_t(segs), xmax, pchk);
+        e->launches += 2;
+        CK(cudaGetLastError());
+    }
+    // the filter: tensor-core Toeplitz GEMM (ask_tc.cu) | TMK_ASK_FFT=1: FFT fast correlation | TMK_ASK_DIRECT=1: direct form
+    static const bool use_fft = getenv("TMK_ASK_FFT") != nullptr;
+    if (pchk != nullptr && !use_fft && !direct) {
+        std::vector<uint64_t> so(n_streams), sn(n_streams), sw(n_streams);
+        for (uint32_t s = 0; s < n_streams; ++s) {
+            so[s] = sd[s].offset;
+            sn[s] = sd[s].n;
+            sw[s] = sd[s].word_base;
+        }
+        rc = tmk_ask_tc_filter(e, dx, total_samples, so.data(), sn.data(), sw.data(), n_streams, tab, pchk,
+                               static_cast<uint32_t*>(e->d_ask_bits.p));
+        if (rc != TMK_OK) return rc;
+    } else
     if (tiles) {
         if (direct) {
             ask_scan_kernel<<<uint32_t(tiles), kThreads, 0, e->stream>>>(dx, ds, n_streams, tab, static_cast<uint32_t*>(e->d_ask_bits.p));
@@ -1046,19 +1072,6 @@ int tmk_ask_sync_device(tmk_engine* e, const float* samples, uint64_t total_samp
     }
     CK(cudaGetLastError());
     CK(cudaEventRecord(e->ev[1], e->stream));
-    // exact power checkpoints for the walk (TMK_ASK_NO_CHK=1: the walk chains through every sample itself, for A/B)
-    static const bool no_chk = getenv("TMK_ASK_NO_CHK") != nullptr;
-    float* pchk = nullptr;
-    if (!no_chk && segs) {
-        CK(e->d_ask_chk.reserve((words + 2) * sizeof(float) + sizeof(uint32_t) * n_streams));
-        pchk = static_cast<float*>(e->d_ask_chk.p);
-        uint32_t* xmax = reinterpret_cast<uint32_t*>(pchk + words + 2);
-        CK(cudaMemsetAsync(xmax, 0, sizeof(uint32_t) * n_streams, e->stream));
-        ask_xmax_kernel<<<uint32_t((segs + 7) / 8), 256, 0, e->stream>>>(dx, ds, n_streams, uint32_t(segs), xmax);
-        ask_power_kernel<<<uint32_t((segs + 127) / 128), 128, 0, e->stream>>>(dx, ds, n_streams, uint32_t(segs), xmax, pchk);
-        e->launches += 2;
-        CK(cudaGetLastError());
-    }
     static int walk_ctas = 0;
     if (walk_ctas == 0) {
         int sms = 0, per_sm = 0;

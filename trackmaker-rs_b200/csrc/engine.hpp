@@ -40,7 +40,7 @@ struct tmk_engine {
     std::vector<TmkPattern> patterns;  // host mirror of the device pattern table
     DevBuf d_tile_dir, d_patterns, d_streams, d_blk_info, d_cand, d_recs_tmp, d_rec_ord, d_recs, d_payload, d_cnt, d_base,
         d_counters, d_samples, d_misc, d_misc2, d_next, d_cblk, d_blk_ptr, d_entries, d_spec, d_pool, d_link, d_pcm, d_frag;
-    DevBuf d_ask_tab, d_ask_bits, d_ask_l2, d_ask_recs, d_ask_recs2, d_ask_chk;  // chirp+BPSK path (ask.cu)
+    DevBuf d_ask_tab, d_ask_bits, d_ask_l2, d_ask_recs, d_ask_recs2, d_ask_chk, d_ask_tc;  // chirp+BPSK path (ask.cu)
     DevBuf d_mcm_tab, d_mcm_recs, d_mcm_off;  // multi-carrier modem (mcm.cu): tables, device records, stream offsets
     bool mcm_ready = false;
     float mcm_demod_ms = 0.0f;
@@ -91,3 +91,6 @@ inline bool tmk_is_device_ptr(const void* p) {
 int tmk_ask_ensure_tables(tmk_engine* e);
 int tmk_ask_sync_device(tmk_engine* e, const float* samples, uint64_t total_samples, const tmk_stream* streams, uint32_t n_streams,
                         const float** dx_out, uint64_t* n_recs, uint64_t* dev_cap_out);
+// ask_tc.cu: the chirp filter on the tensor cores (marks candidate words in wflag)
+int tmk_ask_tc_filter(tmk_engine* e, const float* dx, uint64_t total_samples, const uint64_t* s_off, const uint64_t* s_n,
+                      const uint64_t* s_word, uint32_t n_streams, const float* chirp, const float* pchk, uint32_t* wflag);
