@@ -502,6 +502,22 @@ int tmk_fragment_batch(tmk_engine* e, const uint8_t* data, const uint64_t* pkt_o
                        uint16_t first_identification, tmk_packet_rec* frags, uint64_t frag_cap, uint64_t* n_frags,
                        uint8_t* bytes, uint64_t byte_cap, uint64_t* n_bytes, uint16_t* next_identification);
 
+/* The reassembler of a link kept across calls: AcousticInterface owns ONE IpReassembler for all its receive polls
+ * (src/mac/acoustic_interface.rs:316-378), so the fragments of a datagram may arrive in different process_samples calls.
+ * tmk_reasm_push takes the records of one decode call (tmk_decode_batch / tmk_links_process_samples: grouped by link,
+ * record.stream = link), puts the fragments still pending from earlier calls in front of them and returns the packets
+ * that complete now (same records and rules as tmk_reassemble_batch; `frame` = index of the completing record in THIS
+ * call). On an error nothing is consumed. tmk_reasm_pending: fragments / bytes the link still holds. */
+typedef struct tmk_reasm tmk_reasm;
+int tmk_reasm_create(tmk_engine* e, uint32_t n_links, tmk_reasm** out);
+void tmk_reasm_destroy(tmk_reasm* r);
+int tmk_reasm_push(tmk_reasm* r, const tmk_frame_rec* recs, uint64_t n_recs, const uint8_t* payload, uint64_t payload_len,
+                   tmk_packet_rec* pkts, uint64_t pkt_cap, uint64_t* n_pkts, uint8_t* bytes, uint64_t byte_cap,
+                   uint64_t* n_bytes);
+int tmk_reasm_pending(const tmk_reasm* r, uint32_t link, uint32_t* n_fragments, uint64_t* n_bytes);
+/* link == UINT32_MAX forgets every link's fragments */
+int tmk_reasm_reset(tmk_reasm* r, uint32_t link);
+
 #ifdef __cplusplus
 }
 #endif

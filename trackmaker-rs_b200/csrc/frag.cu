@@ -441,4 +441,131 @@ int tmk_fragment_batch(tmk_engine* e, const uint8_t* data, const uint64_t* pkt_o
     return TMK_OK;
 }
 
+// ---------------------------------------------------------------- reassembler state carried across calls
+// AcousticInterface keeps ONE IpReassembler for all its receive polls (src/mac/acoustic_interface.rs:316-378: the
+// `reassembler` field outlives every process_samples call), so a datagram whose fragments arrive in different polls
+// still completes. tmk_reasm_* carries that state per link: the fragments of unfinished datagrams (their frame records and
+// bytes) are kept on the host, put in front of the next call's frames of the link, and the batch kernels run over both.
+// A fragment stays pending exactly while the reassembler's maps would still hold it: it is a fragment (not a whole
+// packet, not an error) and no arrival at or behind it completed (or overflowed) its (identification, source) key.
+struct tmk_reasm {
+    tmk_engine* e;
+    uint32_t n_links;
+    std::vector<std::vector<tmk_frame_rec>> recs;   // per link, arrival order; payload_off indexes bytes[link]
+    std::vector<std::vector<uint8_t>> bytes;
+};
+
+int tmk_reasm_create(tmk_engine* e, uint32_t n_links, tmk_reasm** out) {
+    if (!e || !out || n_links == 0) return fail(e, TMK_E_INVALID, "tmk_reasm_create: bad argument");
+    tmk_reasm* r = new tmk_reasm;
+    r->e = e;
+    r->n_links = n_links;
+    r->recs.resize(n_links);
+    r->bytes.resize(n_links);
+    *out = r;
+    return TMK_OK;
+}
+
+void tmk_reasm_destroy(tmk_reasm* r) { delete r; }
+
+int tmk_reasm_reset(tmk_reasm* r, uint32_t link) {
+    if (!r || (link != 0xffffffffu && link >= r->n_links)) return TMK_E_INVALID;
+    for (uint32_t l = 0; l < r->n_links; ++l)
+        if (link == 0xffffffffu || l == link) {
+            r->recs[l].clear();
+            r->bytes[l].clear();
+        }
+    return TMK_OK;
+}
+
+int tmk_reasm_pending(const tmk_reasm* r, uint32_t link, uint32_t* n_fragments, uint64_t* n_bytes) {
+    if (!r || link >= r->n_links) return TMK_E_INVALID;
+    if (n_fragments) *n_fragments = uint32_t(r->recs[link].size());
+    if (n_bytes) *n_bytes = r->bytes[link].size();
+    return TMK_OK;
+}
+
+int tmk_reasm_push(tmk_reasm* r, const tmk_frame_rec* recs, uint64_t n_recs, const uint8_t* payload, uint64_t payload_len,
+                   tmk_packet_rec* pkts, uint64_t pkt_cap, uint64_t* n_pkts, uint8_t* bytes, uint64_t byte_cap, uint64_t* n_bytes) {
+    if (!r) return TMK_E_INVALID;
+    tmk_engine* e = r->e;
+    if ((!recs && n_recs) || (!payload && payload_len) || !n_pkts || !n_bytes || (!pkts && pkt_cap) || (!bytes && byte_cap))
+        return fail(e, TMK_E_INVALID, "tmk_reasm_push: null argument");
+    *n_pkts = 0;
+    *n_bytes = 0;
+    CK(cudaSetDevice(e->device));
+    // the call's records and bytes on the host (they may live on the device)
+    std::vector<tmk_frame_rec> hr(n_recs);
+    std::vector<uint8_t> hp(payload_len);
+    if (n_recs) CK(cudaMemcpy(hr.data(), recs, sizeof(tmk_frame_rec) * n_recs, cudaMemcpyDefault));
+    if (payload_len) CK(cudaMemcpy(hp.data(), payload, payload_len, cudaMemcpyDefault));
+    // carried fragments ++ the new frames, link by link; `origin` = index in this call's recs, or -1 for a carried one
+    std::vector<tmk_frame_rec> all;
+    std::vector<uint8_t> blob;
+    std::vector<int64_t> origin;
+    std::vector<uint64_t> first_new(r->n_links + 1, 0);
+    for (uint64_t i = 0; i < n_recs; ++i) {
+        if (hr[i].stream >= r->n_links) return fail(e, TMK_E_INVALID, "tmk_reasm_push: record of a link the reassembler does not have");
+        if (i && hr[i].stream < hr[i - 1].stream) return fail(e, TMK_E_INVALID, "tmk_reasm_push: records must be grouped by link, ascending");
+        const bool has_bytes = hr[i].status == TMK_FRAME_OK || hr[i].status == TMK_FRAME_NOT_FOR_US || hr[i].status == TMK_FRAME_CRC_FAIL;
+        if (has_bytes && (hr[i].payload_off > payload_len || hr[i].len > payload_len - hr[i].payload_off))
+            return fail(e, TMK_E_INVALID, "tmk_reasm_push: record payload outside the payload buffer");
+        first_new[hr[i].stream + 1] = i + 1;
+    }
+    for (uint32_t l = 0; l < r->n_links; ++l) first_new[l + 1] = std::max(first_new[l + 1], first_new[l]);
+    auto append = [&](const tmk_frame_rec& src, const uint8_t* data, int64_t org) {
+        tmk_frame_rec t = src;
+        t.payload_off = blob.size();
+        const bool has_bytes = t.status == TMK_FRAME_OK || t.status == TMK_FRAME_NOT_FOR_US || t.status == TMK_FRAME_CRC_FAIL;
+        if (has_bytes) blob.insert(blob.end(), data, data + t.len);
+        all.push_back(t);
+        origin.push_back(org);
+    };
+    for (uint32_t l = 0; l < r->n_links; ++l) {
+        for (const tmk_frame_rec& c : r->recs[l]) append(c, r->bytes[l].data() + c.payload_off, -1);
+        for (uint64_t i = first_new[l]; i < first_new[l + 1]; ++i) append(hr[i], hp.data() + hr[i].payload_off, int64_t(i));
+    }
+    if (all.empty()) return TMK_OK;
+    blob.push_back(0);
+    int rc = tmk_reassemble_batch(e, all.data(), all.size(), blob.data(), blob.size(), r->n_links, pkts, pkt_cap, n_pkts, bytes,
+                                  byte_cap, n_bytes);
+    if (rc != TMK_OK) return rc;  // (nothing was consumed: the call may be repeated with larger buffers)
+    // `frame` of a packet record: the arrival that completed it, always one of this call's frames
+    if (tmk_is_device_ptr(pkts)) {
+        // device-resident packet records keep the batch numbering (carried fragments first); host callers get the call's own
+    } else {
+        for (uint64_t k = 0; k < *n_pkts; ++k) pkts[k].frame = origin[pkts[k].frame] >= 0 ? uint32_t(origin[pkts[k].frame]) : 0xffffffffu;
+    }
+    // what the reassembler still holds: fragments with no completion of their key at or behind them
+    std::vector<FragDesc> hd(all.size());
+    CK(cudaMemcpy(hd.data(), e->d_frag.p, sizeof(FragDesc) * all.size(), cudaMemcpyDeviceToHost));
+    std::vector<std::vector<tmk_frame_rec>> nrecs(r->n_links);
+    std::vector<std::vector<uint8_t>> nbytes(r->n_links);
+    uint64_t hi = all.size();
+    for (uint32_t l = r->n_links; l-- > 0;) {
+        uint64_t lo = hi;
+        while (lo > 0 && all[lo - 1].stream == l) --lo;
+        std::vector<std::pair<uint32_t, uint16_t>> done;  // keys completed later in the link
+        std::vector<uint64_t> keep;
+        for (uint64_t j = hi; j-- > lo;) {
+            const FragDesc& d = hd[j];
+            if (d.kind != K_FRAG) continue;
+            const std::pair<uint32_t, uint16_t> key(d.src_ip, d.ident);
+            if (d.emit != 0) done.push_back(key);
+            if (std::find(done.begin(), done.end(), key) == done.end()) keep.push_back(j);
+        }
+        for (auto it = keep.rbegin(); it != keep.rend(); ++it) {
+            tmk_frame_rec t = all[*it];
+            const uint8_t* data = blob.data() + t.payload_off;
+            t.payload_off = nbytes[l].size();
+            nbytes[l].insert(nbytes[l].end(), data, data + t.len);
+            nrecs[l].push_back(t);
+        }
+        hi = lo;
+    }
+    r->recs.swap(nrecs);
+    r->bytes.swap(nbytes);
+    return TMK_OK;
+}
+
 }  // extern "C"

@@ -569,6 +569,42 @@ class Engine:
         self._check(self._lib.tmk_comm_destroy(self._h))
 
 
+class IpReassembler:
+    """IpReassembler kept across receive polls (src/mac/acoustic_interface.rs:316-378), for `n_links` links at once:
+    push(records, payload) of each decode call -> the packets that complete now."""
+
+    def __init__(self, engine, n_links=1):
+        self._eng = engine
+        h = C.c_void_p()
+        engine._check(engine._lib.tmk_reasm_create(engine._h, int(n_links), C.byref(h)))
+        self._r = h
+
+    def push(self, recs, payload, pkt_cap=None, byte_cap=None):
+        r = np.ascontiguousarray(recs, dtype=REC_DTYPE)
+        pl = np.ascontiguousarray(payload, dtype=np.uint8)
+        pkt_cap = int(pkt_cap) if pkt_cap is not None else max(16, len(r) + 16)
+        byte_cap = int(byte_cap) if byte_cap is not None else max(1 << 18, 4 * pl.size + 64 * len(r))
+        pk = np.zeros(pkt_cap, _abi.PKT_DTYPE)
+        by = np.zeros(byte_cap, np.uint8)
+        n, nb = C.c_uint64(0), C.c_uint64(0)
+        self._eng._check(self._eng._lib.tmk_reasm_push(self._r, _ptr(r), len(r), _ptr(pl), pl.size, _ptr(pk), pkt_cap, C.byref(n),
+                                                       _ptr(by), byte_cap, C.byref(nb)))
+        return pk[:n.value].copy(), by[:nb.value].copy()
+
+    def pending(self, link=0):
+        nf, nb = C.c_uint32(0), C.c_uint64(0)
+        self._eng._check(self._eng._lib.tmk_reasm_pending(self._r, int(link), C.byref(nf), C.byref(nb)))
+        return int(nf.value), int(nb.value)
+
+    def reset(self, link=0xFFFFFFFF):
+        self._eng._check(self._eng._lib.tmk_reasm_reset(self._r, int(link)))
+
+    def close(self):
+        if self._r:
+            self._eng._lib.tmk_reasm_destroy(self._r)
+            self._r = None
+
+
 def comm_unique_id():
     """ncclGetUniqueId through the library (rank 0 calls it and hands the 128 bytes to the other ranks)"""
     buf = C.create_string_buffer(128)

@@ -146,6 +146,11 @@ SYMBOLS = {
     "tmk_reassemble_batch": (C.c_int, [_vp, _vp, _u64, _vp, _u64, _u32, _vp, _u64, _pu64, _vp, _u64, _pu64]),
     "tmk_fragment_batch": (C.c_int, [_vp, _vp, _vp, _u32, _u32, C.c_uint16, _vp, _u64, _pu64, _vp, _u64, _pu64,
                                      C.POINTER(C.c_uint16)]),
+    "tmk_reasm_create": (C.c_int, [_vp, _u32, C.POINTER(_vp)]),
+    "tmk_reasm_destroy": (None, [_vp]),
+    "tmk_reasm_push": (C.c_int, [_vp, _vp, _u64, _vp, _u64, _vp, _u64, _pu64, _vp, _u64, _pu64]),
+    "tmk_reasm_pending": (C.c_int, [_vp, _u32, C.POINTER(_u32), _pu64]),
+    "tmk_reasm_reset": (C.c_int, [_vp, _u32]),
     "tmk_synth_batch": (C.c_int, [_vp, _pcfg, _u64, _u32, _u64, C.c_float, C.c_float, _vp, _vp, _u64, _pu64]),
     "tmk_synth_batch_ex": (C.c_int, [_vp, _pcfg, _u64, _u32, _u64, C.POINTER(SynthParams), _vp, _vp, _u64, _pu64]),
     "tmk_ask_synth_batch": (C.c_int, [_vp, _u64, _u32, _u64, C.c_float, _vp, _pu64]),
