@@ -520,14 +520,24 @@ ask_power_kernel(const float* __restrict__ samples, const AskStream* __restrict_
         pu = __fmaf_rn(1.001f, __fmul_rn(xm, xm), 1e-30f);  // inf / NaN captures never merge
         merged = false;
     }
-    // a word (32 samples) per round: eight 16-byte loads, then the chain(s) over them; pos, s0 are multiples of 32
+    // a word (32 samples) per round: eight 16-byte loads, then the chain(s) over them; pos, s0 are multiples of 32. The next
+    // word's loads are issued before the chain of the current one runs (the kernel is bound by the latency of its strided loads)
+    float4 nx[8];
+    auto fetch = [&](int64_t at) {
+        if (at < s1 && at + 32 <= n) {
+#pragma unroll
+            for (int k = 0; k < 8; ++k) nx[k] = __ldg(reinterpret_cast<const float4*>(x + at) + k);
+        }
+    };
+    fetch(pos);
     while (pos < s1) {
         if (!merged) merged = pl == pu;
         if (pos >= s0) chk[pos >> 5] = merged ? pl : -1.0f;
         if (pos + 32 > n) break;  // the partial last word of the capture: nobody reads behind its checkpoint
         float4 v[8];
 #pragma unroll
-        for (int k = 0; k < 8; ++k) v[k] = __ldg(reinterpret_cast<const float4*>(x + pos) + k);
+        for (int k = 0; k < 8; ++k) v[k] = nx[k];
+        fetch(pos + 32);
         if (merged) {
 #pragma unroll
             for (int k = 0; k < 8; ++k) {
@@ -743,7 +753,8 @@ __device__ __noinline__ void decode_frame(const AskCtx& c, int64_t s, uint8_t* b
 __global__ void __launch_bounds__(128)
 ask_walk_kernel(const float* __restrict__ samples, const AskStream* __restrict__ streams, uint32_t n_streams,
                 const float* __restrict__ tab, const uint32_t* __restrict__ wflag, const float* __restrict__ pchk,
-                tmk_ask_rec* __restrict__ recs, uint64_t rec_cap, unsigned long long* __restrict__ counters) {
+                tmk_ask_rec* __restrict__ recs, uint32_t* __restrict__ rec_ord, uint32_t* __restrict__ stream_cnt, uint64_t rec_cap,
+                unsigned long long* __restrict__ counters) {
     __shared__ __align__(16) float stage_s[4][128];
     for (int i = threadIdx.x; i < kPre; i += blockDim.x) g_wpre[i] = tab[i];
     __syncthreads();
@@ -768,6 +779,7 @@ ask_walk_kernel(const float* __restrict__ samples, const AskStream* __restrict__
         int64_t r = 0, cur = 0, start = 0;
         float local_max = 0.0f;
         bool done = false;
+        uint32_t n_emitted = 0;  // records of this capture, in time order: its position in the ordered output
         while (!done) {
             // ---- next word to evaluate: everything inside the first 439 positions after the FIFO was zeroed
             //      (partial windows are not covered by the filter), afterwards the flagged words only
@@ -846,7 +858,9 @@ ask_walk_kernel(const float* __restrict__ samples, const AskStream* __restrict__
                 rec.id = uint8_t(id);
                 for (int b = 0; b < 14; ++b) rec.bits[b] = bits_s[warp][b];
                 recs[slot] = rec;
+                rec_ord[slot] = n_emitted;
             }
+            ++n_emitted;
             __syncwarp();
             r = s + 2 + kFrame;  // first sample examined in state 0 again
             cur = r;
@@ -854,7 +868,18 @@ ask_walk_kernel(const float* __restrict__ samples, const AskStream* __restrict__
             local_max = 0.0f;
             if (cur >= c.n) done = true;
         }
+        if (lane == 0) stream_cnt[sidx] = n_emitted;
     }
+}
+
+// records in (capture, time) order: the walk's warps emit through an atomic slot counter; base = exclusive scan of the
+// captures' record counts
+__global__ void ask_order_kernel(const tmk_ask_rec* __restrict__ in, const uint32_t* __restrict__ rec_ord, uint64_t n,
+                                 const uint64_t* __restrict__ base, tmk_ask_rec* __restrict__ out) {
+    const uint64_t i = uint64_t(blockIdx.x) * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const tmk_ask_rec r = in[i];
+    out[base[r.stream] + rec_ord[i]] = r;
 }
 
 void host_tables(std::vector<float>& tab, size_t n_carrier) {
@@ -1016,6 +1041,12 @@ int tmk_ask_sync_device(tmk_engine* e, const float* samples, uint64_t total_samp
     CK(e->d_ask_l2.reserve(4 * sizeof(unsigned long long)));
     uint64_t dev_cap = std::max<uint64_t>(1024, total_samples / 4096 + 2ull * n_streams);
     CK(e->d_ask_recs.reserve(dev_cap * sizeof(tmk_ask_rec)));
+    // unordered records + their ordinals | per-capture counts and bases (the ordered records land in d_ask_recs)
+    CK(e->d_ask_recs2.reserve(dev_cap * (sizeof(tmk_ask_rec) + sizeof(uint32_t)) + 64 + sizeof(uint32_t) * n_streams + sizeof(uint64_t) * (n_streams + 1) + 64));
+    tmk_ask_rec* raw_recs = static_cast<tmk_ask_rec*>(e->d_ask_recs2.p);
+    uint32_t* raw_ord = reinterpret_cast<uint32_t*>(raw_recs + dev_cap);
+    uint64_t* rec_base = reinterpret_cast<uint64_t*>(static_cast<char*>(e->d_ask_recs2.p) + (dev_cap * (sizeof(tmk_ask_rec) + sizeof(uint32_t)) + 63) / 64 * 64);
+    uint32_t* rec_cnt = reinterpret_cast<uint32_t*>(rec_base + n_streams + 1);
     CK(cudaMemcpyAsync(e->d_streams.p, sd.data(), sizeof(AskStream) * n_streams, cudaMemcpyHostToDevice, e->stream));
     CK(cudaMemsetAsync(e->d_ask_bits.p, 0, flag_words * sizeof(uint32_t), e->stream));
     CK(cudaMemsetAsync(e->d_ask_l2.p, 0, 4 * sizeof(unsigned long long), e->stream));
@@ -1081,7 +1112,7 @@ int tmk_ask_sync_device(tmk_engine* e, const float* samples, uint64_t total_samp
     }
     const uint32_t grid = std::min<uint32_t>((n_streams + 3) / 4, uint32_t(walk_ctas));
     ask_walk_kernel<<<grid, 128, 0, e->stream>>>(dx, ds, n_streams, tab, static_cast<const uint32_t*>(e->d_ask_bits.p), pchk,
-                                                 static_cast<tmk_ask_rec*>(e->d_ask_recs.p), dev_cap,
+                                                 raw_recs, raw_ord, rec_cnt, dev_cap,
                                                  static_cast<unsigned long long*>(e->d_ask_l2.p));
     e->launches += 1;
     CK(cudaGetLastError());
@@ -1095,6 +1126,13 @@ int tmk_ask_sync_device(tmk_engine* e, const float* samples, uint64_t total_samp
     *dx_out = dx;
     *dev_cap_out = dev_cap;
     if (hc[0] > dev_cap) return tmk_fail(e, TMK_E_CAPACITY, "chirp synchroniser: internal record scratch too small");
+    if (hc[0]) {  // (capture, time) order on the device
+        e->launches += tmk_launch_excl_scan(rec_cnt, rec_base, n_streams, e->stream);
+        ask_order_kernel<<<uint32_t((hc[0] + 255) / 256), 256, 0, e->stream>>>(raw_recs, raw_ord, hc[0], rec_base,
+                                                                              static_cast<tmk_ask_rec*>(e->d_ask_recs.p));
+        e->launches += 1;
+        CK(cudaGetLastError());
+    }
     return TMK_OK;
 }
 
@@ -1120,10 +1158,7 @@ int tmk_ask_decode_batch(tmk_engine* e, const float* samples, uint64_t total_sam
     if (hc[0]) {
         CK(cudaMemcpyAsync(recs, e->d_ask_recs.p, hc[0] * sizeof(tmk_ask_rec), cudaMemcpyDeviceToHost, e->stream));
         CK(cudaStreamSynchronize(e->stream));
-        // reference order: per capture, in time (the warps emit through an atomic slot counter)
-        std::sort(recs, recs + hc[0], [](const tmk_ask_rec& a, const tmk_ask_rec& b) {
-            return a.stream != b.stream ? a.stream < b.stream : a.start_index < b.start_index;
-        });
+        // (already in reference order — per capture, in time: ask_order_kernel)
     }
     return TMK_OK;
 }

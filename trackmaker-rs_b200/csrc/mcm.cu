@@ -549,9 +549,7 @@ int tmk_mcm_decode_batch(tmk_engine* e, int32_t mode, const float* samples, uint
         CK(cudaMemcpyAsync(payload, e->d_payload.p, hc.n_payload, cudaMemcpyDeviceToHost, e->stream));
         CK(cudaStreamSynchronize(e->stream));
     }
-    std::sort(recs, recs + n, [](const tmk_mcm_rec& a, const tmk_mcm_rec& b) {
-        return a.stream != b.stream ? a.stream < b.stream : a.start_index < b.start_index;
-    });
+    // (the synchroniser's records are in (capture, time) order already, and record i here is its record i)
     return TMK_OK;
 }
 
