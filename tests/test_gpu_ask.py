@@ -147,3 +147,50 @@ def test_ask_marginal_detection_many_streams(engine, orc, seed):
     got = engine.ask_decode_batch(buf, st)
     assert_ask_equal(got, want, f"marginal seed={seed}")
     assert 300 < len(want) < 256 * 8 and (want["accepted"] == 1).sum() > 200
+
+
+@pytest.mark.parametrize("seg_min", [8192, 20000, 65536])
+def test_ask_segmented_walk(engine, orc, seg_min):
+    """captures cut into segments walked at once (ask.cu: segmented walk): whatever the segment length — frames that
+    straddle a cut, peaks pending at a cut, marginal locks, bursts, silence — the records are the serial receiver's"""
+    import os
+    import tmkphy
+    rng = np.random.default_rng(4000 + seg_min)
+    caps = []
+    for s in range(12):
+        nf = int(rng.integers(25, 60))
+        fr = rng.integers(0, 2, (nf, 100)).astype(np.uint8)
+        for i in range(nf):
+            fr[i, :8] = [((i % 100 + 1) >> (7 - j)) & 1 for j in range(8)]
+        x = orc.ask_modulate(fr, rng.integers(0, 900 if s % 3 else 100, nf), rng.integers(0, 300, nf))
+        a = float(rng.uniform(0.3, 1.2))
+        if s % 4 == 0:   # marginal locks: 1.1 a ~ 2 (a^2 / 2 + sigma^2)
+            s2 = max(1.1 * a / (2 * (1 + float(rng.uniform(-0.05, 0.05)))) - a * a / 2, 1e-6)
+            x = x * np.float32(a) + rng.normal(0, np.sqrt(s2), len(x)).astype(np.float32)
+        else:
+            x = impaired(rng, x, float(rng.choice([30, 15, 11])), amp=a, multipath=(s % 4 == 1))
+        if s % 5 == 2:
+            p = int(rng.integers(0, len(x) - 5000))
+            x[p:p + 3000] = 0.0
+        caps.append(x.astype(np.float32))
+    caps += [np.zeros(100000, np.float32), rng.normal(0, 0.3, 150000).astype(np.float32)]
+    st, total = tmkphy.make_streams([len(c) for c in caps], tmkphy.make_config(1))
+    buf = np.zeros(total, np.float32)
+    for c, t in zip(caps, st):
+        buf[int(t["offset"]):int(t["offset"]) + len(c)] = c
+    want = oracle_batch(orc, buf, st)
+    saved = {k: os.environ.get(k) for k in ("TMK_ASK_SEG_MIN", "TMK_ASK_SEGMENTS")}
+    try:
+        os.environ["TMK_ASK_SEG_MIN"] = str(seg_min)
+        os.environ["TMK_ASK_SEGMENTS"] = "20000"
+        got = engine.ask_decode_batch(buf, st)
+        assert_ask_equal(got, want, f"segmented seg_min={seg_min}")
+        os.environ["TMK_ASK_SEGMENTS"] = "0"
+        assert_ask_equal(engine.ask_decode_batch(buf, st), want, "one walker per capture")
+    finally:
+        for k, v in saved.items():
+            if v is None:
+                os.environ.pop(k, None)
+            else:
+                os.environ[k] = v
+    assert len(want) > 250

@@ -754,7 +754,12 @@ __global__ void __launch_bounds__(128)
 ask_walk_kernel(const float* __restrict__ samples, const AskStream* __restrict__ streams, uint32_t n_streams,
                 const float* __restrict__ tab, const uint32_t* __restrict__ wflag, const float* __restrict__ pchk,
                 tmk_ask_rec* __restrict__ recs, uint32_t* __restrict__ rec_ord, uint32_t* __restrict__ stream_cnt, uint64_t rec_cap,
-                unsigned long long* __restrict__ counters) {
+                unsigned long long* __restrict__ counters, TmkSeg seg, uint32_t* __restrict__ rec_item) {
+    // seg.items != nullptr: the work items are SEGMENTS of captures (the segmented walk of tmk_internal.cuh, for this
+    // receiver: its state right after a frame is the position r where the FIFO was zeroed — power is a function of the
+    // samples alone — so a walker that starts mid-capture as "searching, nothing pending" is the true receiver from the
+    // first frame end it shares with the walker coming from the segments before it)
+    const bool segm = seg.items != nullptr;
     __shared__ __align__(16) float stage_s[4][128];
     for (int i = threadIdx.x; i < kPre; i += blockDim.x) g_wpre[i] = tab[i];
     __syncthreads();
@@ -764,7 +769,24 @@ ask_walk_kernel(const float* __restrict__ samples, const AskStream* __restrict__
         if (lane == 0) sidx = uint32_t(atomicAdd(&counters[1], 1ull));
         sidx = __shfl_sync(kFull, sidx, 0);
         if (sidx >= n_streams) return;
-        const AskStream sd = streams[sidx];
+        uint32_t real = sidx, ord0 = 0;
+        int64_t q0 = 0, q1 = int64_t(0x7fffffffffffffffll);
+        bool resumed = false;
+        if (segm) {
+            const TmkSegItem it = seg.items[sidx];
+            real = it.stream;
+            if (seg.pass == 1) {
+                q0 = int64_t(it.q0);
+                q1 = it.q1 == ~0ull ? q1 : int64_t(it.q1);
+            } else {
+                const TmkSegState* ps = seg.st + sidx;
+                if (ps->state != 1) continue;  // only walkers that paused at the end of their segment go on
+                q0 = int64_t(ps->q);
+                ord0 = ps->ord;
+                resumed = true;
+            }
+        }
+        const AskStream sd = streams[real];
         AskCtx c;
         c.x = samples + sd.offset;
         c.n = int64_t(sd.n);
@@ -776,11 +798,39 @@ ask_walk_kernel(const float* __restrict__ samples, const AskStream* __restrict__
         c.stage = stage_s[warp];
         c.chk = pchk != nullptr ? pchk + sd.word_base : nullptr;
         const int64_t nwords = (c.n + 31) / 32;
-        int64_t r = 0, cur = 0, start = 0;
+        // a walker that resumes (pass 2) stands right behind a frame: FIFO zeroed at q0; one that starts a segment searches
+        // with a full FIFO (r = 0) from q0 on
+        int64_t r = resumed ? q0 : 0, cur = q0, start = 0;
         float local_max = 0.0f;
         bool done = false;
-        uint32_t n_emitted = 0;  // records of this capture, in time order: its position in the ordered output
+        uint32_t n_emitted = ord0;  // records of this walker, in time order: its position in the ordered output
+        uint32_t seg_exit = 0, sync_item = 0, sync_ord = 0;
+        bool at_entry = resumed;    // standing at a frame end (a state the position alone determines)
         while (!done) {
+            if (segm && at_entry) {
+                at_entry = false;
+                if (seg.pass == 1) {
+                    if (n_emitted >= 1 && n_emitted <= TMK_SEG_HEADS && lane == 0) seg.st[sidx].head[n_emitted - 1] = uint64_t(r);
+                    if (r >= q1) {
+                        seg_exit = 1;
+                        break;
+                    }
+                } else {
+                    const TmkSegItem it = seg.items[sidx];
+                    uint64_t k = uint64_t(r) / it.seg_len;
+                    if (k >= it.n_seg) k = it.n_seg - 1;
+                    const uint32_t owner = it.first_item + uint32_t(k);
+                    const TmkSegState* os = seg.st + owner;
+                    const bool hit = uint32_t(lane) < os->n_head && os->head[lane] == uint64_t(r);
+                    const uint32_t hm = __ballot_sync(kFull, hit);
+                    if (hm && owner != sidx) {
+                        sync_item = owner;
+                        sync_ord = uint32_t(__ffs(hm));  // head[i] is the frame end behind the owner's record i: valid from i + 1
+                        seg_exit = 2;
+                        break;
+                    }
+                }
+            }
             // ---- next word to evaluate: everything inside the first 439 positions after the FIFO was zeroed
             //      (partial windows are not covered by the filter), afterwards the flagged words only
             int64_t w = cur >> 5;
@@ -851,7 +901,7 @@ ask_walk_kernel(const float* __restrict__ samples, const AskStream* __restrict__
             if (lane == 0 && slot < rec_cap) {
                 tmk_ask_rec rec;
                 memset(&rec, 0, sizeof rec);
-                rec.stream = sidx;
+                rec.stream = real;
                 rec.accepted = (id > 0 && id <= 100) ? 1u : 0u;
                 rec.start_index = uint64_t(s);
                 rec.sync_power = local_max;
@@ -859,6 +909,7 @@ ask_walk_kernel(const float* __restrict__ samples, const AskStream* __restrict__
                 for (int b = 0; b < 14; ++b) rec.bits[b] = bits_s[warp][b];
                 recs[slot] = rec;
                 rec_ord[slot] = n_emitted;
+                if (rec_item != nullptr) rec_item[slot] = sidx;
             }
             ++n_emitted;
             __syncwarp();
@@ -866,10 +917,33 @@ ask_walk_kernel(const float* __restrict__ samples, const AskStream* __restrict__
             cur = r;
             start = 0;
             local_max = 0.0f;
+            at_entry = true;
             if (cur >= c.n) done = true;
         }
-        if (lane == 0) stream_cnt[sidx] = n_emitted;
+        if (lane == 0) {
+            stream_cnt[sidx] = n_emitted;
+            if (segm) {
+                TmkSegState* ps = seg.st + sidx;
+                ps->q = uint64_t(r);
+                ps->ord = n_emitted;
+                ps->state = seg_exit;
+                ps->sync_item = sync_item;
+                ps->sync_ord = sync_ord;
+                if (seg.pass == 1) ps->n_head = n_emitted < TMK_SEG_HEADS ? n_emitted : TMK_SEG_HEADS;
+            }
+        }
     }
+}
+
+// the ordered scatter of a segmented walk: only the records of walkers on the chain, from their first valid one on
+__global__ void ask_seg_order_kernel(const tmk_ask_rec* __restrict__ in, const uint32_t* __restrict__ rec_ord,
+                                     const uint32_t* __restrict__ rec_item, uint64_t n, const uint64_t* __restrict__ base,
+                                     const uint32_t* __restrict__ first_valid, tmk_ask_rec* __restrict__ out) {
+    const uint64_t i = uint64_t(blockIdx.x) * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const uint32_t item = rec_item[i], f = first_valid[item], o = rec_ord[i];
+    if (f == 0xffffffffu || o < f) return;
+    out[base[item] + (o - f)] = in[i];
 }
 
 // records in (capture, time) order: the walk's warps emit through an atomic slot counter; base = exclusive scan of the
@@ -1110,11 +1184,67 @@ int tmk_ask_sync_device(tmk_engine* e, const float* samples, uint64_t total_samp
         cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, ask_walk_kernel, 128, 0);
         walk_ctas = sms * (per_sm > 0 ? per_sm : 1);
     }
-    const uint32_t grid = std::min<uint32_t>((n_streams + 3) / 4, uint32_t(walk_ctas));
-    ask_walk_kernel<<<grid, 128, 0, e->stream>>>(dx, ds, n_streams, tab, static_cast<const uint32_t*>(e->d_ask_bits.p), pchk,
-                                                 raw_recs, raw_ord, rec_cnt, dev_cap,
-                                                 static_cast<unsigned long long*>(e->d_ask_l2.p));
-    e->launches += 1;
+    // Segmented walk: only the captures that lock have work, and a capture is one serial chain of frames — with few or long
+    // captures half of the SMs' warp slots stay empty (C2: 14 busy warps per SM). Captures are cut into segments walked at
+    // once and stitched exactly (tmk_internal.cuh; this receiver's state behind a frame is its position).
+    std::vector<TmkSegItem> items;
+    {
+        uint64_t target = 148ull * 28 * 3 / 2, seg_min = 65536;
+        if (const char* ev = getenv("TMK_ASK_SEGMENTS")) target = strtoull(ev, nullptr, 10);  // 0 / 1: off
+        if (const char* ev = getenv("TMK_ASK_SEG_MIN")) seg_min = std::max<uint64_t>(8192, strtoull(ev, nullptr, 10));
+        if (total_samples && uint64_t(n_streams) < target && pchk != nullptr) {
+            for (uint32_t s = 0; s < n_streams; ++s) {
+                const uint64_t n = sd[s].n;
+                const uint64_t share = (target * n + total_samples - 1) / total_samples;
+                uint64_t nseg = std::max<uint64_t>(1, std::min<uint64_t>(std::min<uint64_t>(share, n / seg_min), 60000));
+                const uint64_t seg_len = nseg > 1 ? ((n + nseg - 1) / nseg + 31) / 32 * 32 : std::max<uint64_t>(n, 1);
+                nseg = nseg > 1 ? (n + seg_len - 1) / seg_len : 1;
+                const uint32_t first = uint32_t(items.size());
+                for (uint64_t k = 0; k < nseg; ++k) {
+                    TmkSegItem it;
+                    it.stream = s;
+                    it.seg = uint32_t(k);
+                    it.first_item = first;
+                    it.n_seg = uint32_t(nseg);
+                    it.q0 = k * seg_len;
+                    it.q1 = k + 1 < nseg ? (k + 1) * seg_len : ~0ull;
+                    it.seg_len = seg_len;
+                    items.push_back(it);
+                }
+            }
+            if (items.size() == n_streams) items.clear();
+        }
+    }
+    const bool seg_mode = !items.empty();
+    const uint32_t n_items = seg_mode ? uint32_t(items.size()) : n_streams;
+    TmkSeg seg{nullptr, nullptr, 0, 0};
+    uint32_t *raw_item = nullptr, *first_valid = nullptr, *n_valid = nullptr;
+    if (seg_mode) {
+        const size_t ib = sizeof(TmkSegItem) * n_items, sb = sizeof(TmkSegState) * n_items;
+        const size_t o_item = (ib + sb + 63) / 64 * 64, o_fv = o_item + (sizeof(uint32_t) * dev_cap + 63) / 64 * 64;
+        const size_t o_nv = o_fv + (sizeof(uint32_t) * n_items + 63) / 64 * 64, o_cnt = o_nv + (sizeof(uint32_t) * n_items + 63) / 64 * 64;
+        const size_t o_base = o_cnt + (sizeof(uint32_t) * n_items + 63) / 64 * 64;
+        CK(e->d_ask_seg.reserve(o_base + sizeof(uint64_t) * (n_items + 1) + 64));
+        char* b = static_cast<char*>(e->d_ask_seg.p);
+        seg.items = reinterpret_cast<const TmkSegItem*>(b);
+        seg.st = reinterpret_cast<TmkSegState*>(b + ib);
+        raw_item = reinterpret_cast<uint32_t*>(b + o_item);
+        first_valid = reinterpret_cast<uint32_t*>(b + o_fv);
+        n_valid = reinterpret_cast<uint32_t*>(b + o_nv);
+        rec_cnt = reinterpret_cast<uint32_t*>(b + o_cnt);   // per walker
+        rec_base = reinterpret_cast<uint64_t*>(b + o_base);
+        CK(cudaMemcpyAsync(b, items.data(), ib, cudaMemcpyHostToDevice, e->stream));
+        CK(cudaMemsetAsync(b + ib, 0, sb, e->stream));
+    }
+    const uint32_t grid = std::min<uint32_t>((n_items + 3) / 4, uint32_t(walk_ctas));
+    unsigned long long* ctr = static_cast<unsigned long long*>(e->d_ask_l2.p);
+    for (uint32_t pass = 1; pass <= (seg_mode ? 2u : 1u); ++pass) {
+        seg.pass = pass;
+        if (pass == 2) CK(cudaMemsetAsync(ctr + 1, 0, sizeof(unsigned long long), e->stream));  // the work counter
+        ask_walk_kernel<<<grid, 128, 0, e->stream>>>(dx, ds, n_items, tab, static_cast<const uint32_t*>(e->d_ask_bits.p), pchk,
+                                                     raw_recs, raw_ord, rec_cnt, dev_cap, ctr, seg, raw_item);
+        e->launches += 1;
+    }
     CK(cudaGetLastError());
     CK(cudaEventRecord(e->ev[2], e->stream));
     unsigned long long hc[2] = {0, 0};
@@ -1126,6 +1256,22 @@ int tmk_ask_sync_device(tmk_engine* e, const float* samples, uint64_t total_samp
     *dx_out = dx;
     *dev_cap_out = dev_cap;
     if (hc[0] > dev_cap) return tmk_fail(e, TMK_E_CAPACITY, "chirp synchroniser: internal record scratch too small");
+    if (seg_mode) {
+        // which records count: from walker 0 of every capture along the meeting points; then (capture, time) order
+        e->launches += tmk_launch_seg_chain(seg.items, seg.st, n_items, first_valid, n_valid, e->stream);
+        e->launches += tmk_launch_excl_scan(n_valid, rec_base, n_items, e->stream);
+        uint64_t n_exact = 0;
+        CK(cudaMemcpyAsync(&n_exact, rec_base + n_items, sizeof n_exact, cudaMemcpyDeviceToHost, e->stream));
+        if (hc[0]) {
+            ask_seg_order_kernel<<<uint32_t((hc[0] + 255) / 256), 256, 0, e->stream>>>(raw_recs, raw_ord, raw_item, hc[0], rec_base,
+                                                                                      first_valid, static_cast<tmk_ask_rec*>(e->d_ask_recs.p));
+            e->launches += 1;
+        }
+        CK(cudaGetLastError());
+        CK(cudaStreamSynchronize(e->stream));
+        *n_recs = n_exact;
+        return TMK_OK;
+    }
     if (hc[0]) {  // (capture, time) order on the device
         e->launches += tmk_launch_excl_scan(rec_cnt, rec_base, n_streams, e->stream);
         ask_order_kernel<<<uint32_t((hc[0] + 255) / 256), 256, 0, e->stream>>>(raw_recs, raw_ord, hc[0], rec_base,

@@ -203,7 +203,7 @@ void tmk_engine_destroy(tmk_engine* e) {
                       &e->d_recs, &e->d_payload, &e->d_cnt, &e->d_base, &e->d_counters, &e->d_samples,
                       &e->d_misc, &e->d_misc2, &e->d_next, &e->d_cblk, &e->d_blk_ptr, &e->d_entries, &e->d_spec, &e->d_pool, &e->d_link, &e->d_pcm, &e->d_frag,
                       &e->d_ask_tab, &e->d_ask_bits, &e->d_ask_l2,
-                      &e->d_ask_recs, &e->d_ask_recs2, &e->d_ask_chk, &e->d_ask_tc, &e->d_seg, &e->d_mcm_tab, &e->d_mcm_recs, &e->d_mcm_off};
+                      &e->d_ask_recs, &e->d_ask_recs2, &e->d_ask_chk, &e->d_ask_tc, &e->d_ask_seg, &e->d_seg, &e->d_mcm_tab, &e->d_mcm_recs, &e->d_mcm_off};
     for (DevBuf* b : bufs) b->release();
     for (int i = 0; i < 6; ++i)
         if (e->ev[i]) cudaEventDestroy(e->ev[i]);

@@ -40,7 +40,7 @@ struct tmk_engine {
     std::vector<TmkPattern> patterns;  // host mirror of the device pattern table
     DevBuf d_tile_dir, d_patterns, d_streams, d_blk_info, d_cand, d_recs_tmp, d_rec_ord, d_recs, d_payload, d_cnt, d_base,
         d_counters, d_samples, d_misc, d_misc2, d_next, d_cblk, d_blk_ptr, d_entries, d_spec, d_pool, d_link, d_pcm, d_frag;
-    DevBuf d_ask_tab, d_ask_bits, d_ask_l2, d_ask_recs, d_ask_recs2, d_ask_chk, d_ask_tc;  // chirp+BPSK path (ask.cu)
+    DevBuf d_ask_tab, d_ask_bits, d_ask_l2, d_ask_recs, d_ask_recs2, d_ask_chk, d_ask_tc, d_ask_seg;  // chirp+BPSK path (ask.cu)
     DevBuf d_mcm_tab, d_mcm_recs, d_mcm_off;  // multi-carrier modem (mcm.cu): tables, device records, stream offsets
     bool mcm_ready = false;
     float mcm_demod_ms = 0.0f;

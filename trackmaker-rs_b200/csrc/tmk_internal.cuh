@@ -213,6 +213,8 @@ int tmk_launch_walk(const float* samples, const TmkStreamDev* streams, uint32_t 
 int tmk_launch_seg_resolve(const TmkSegItem* items, const TmkSegState* st, uint32_t n_items, uint32_t* first_valid,
                            uint32_t* n_valid, const tmk_frame_rec* recs, const uint4* rec_ord, uint64_t n_slots, uint64_t rec_cap,
                            const tmk_frame_rec* spec, TmkCounters* counters, cudaStream_t stream);
+int tmk_launch_seg_chain(const TmkSegItem* items, const TmkSegState* st, uint32_t n_items, uint32_t* first_valid, uint32_t* n_valid,
+                         cudaStream_t stream);
 int tmk_launch_seg_order(const tmk_frame_rec* recs_in, const uint4* rec_ord, uint64_t n_slots, const uint64_t* base,
                          const tmk_frame_rec* spec, const TmkSegItem* items, const uint32_t* first_valid,
                          tmk_frame_rec* recs_out, cudaStream_t stream);

@@ -2205,6 +2205,13 @@ int tmk_launch_seg_resolve(const TmkSegItem* items, const TmkSegState* st, uint3
     return 2;
 }
 
+// the chain of meeting points alone (the chirp receiver's segmented walk, ask.cu, tallies nothing)
+int tmk_launch_seg_chain(const TmkSegItem* items, const TmkSegState* st, uint32_t n_items, uint32_t* first_valid, uint32_t* n_valid,
+                         cudaStream_t stream) {
+    seg_chain_kernel<<<(n_items + 127) / 128, 128, 0, stream>>>(items, st, n_items, first_valid, n_valid);
+    return 1;
+}
+
 int tmk_launch_seg_order(const tmk_frame_rec* recs_in, const uint4* rec_ord, uint64_t n_slots, const uint64_t* base,
                          const tmk_frame_rec* spec, const TmkSegItem* items, const uint32_t* first_valid,
                          tmk_frame_rec* recs_out, cudaStream_t stream) {
