@@ -462,7 +462,7 @@ ask_scan_fft_kernel(const float* __restrict__ samples, const AskStream* __restri
 // chain sit on different subnormal fixed points, the first ~1500 samples after it, NaN / inf captures — the walk then
 // runs the chain literally from its last exact position, as before). The walk reads the checkpoints instead of chaining
 // through every sample of every capture with 32 lanes computing one scalar.
-constexpr int kSeg = 4096, kWarm = 2048;
+constexpr int kSeg = 8192, kWarm = 2048;
 __device__ __forceinline__ uint32_t seg_stream(const AskStream* __restrict__ streams, uint32_t n_streams, uint32_t seg) {
     uint32_t lo = 0, hi = n_streams - 1;
     while (lo < hi) {
@@ -1189,7 +1189,7 @@ int tmk_ask_sync_device(tmk_engine* e, const float* samples, uint64_t total_samp
     // once and stitched exactly (tmk_internal.cuh; this receiver's state behind a frame is its position).
     std::vector<TmkSegItem> items;
     {
-        uint64_t target = 148ull * 28 * 3 / 2, seg_min = 65536;
+        uint64_t target = 148ull * 28 * 3, seg_min = 65536;  // measured at C2 (walk ms): 6216 walkers 8.1, 12 500 7.1, 25 000 6.7
         if (const char* ev = getenv("TMK_ASK_SEGMENTS")) target = strtoull(ev, nullptr, 10);  // 0 / 1: off
         if (const char* ev = getenv("TMK_ASK_SEG_MIN")) seg_min = std::max<uint64_t>(8192, strtoull(ev, nullptr, 10));
         if (total_samples && uint64_t(n_streams) < target && pchk != nullptr) {
