@@ -1192,7 +1192,9 @@ int tmk_ask_sync_device(tmk_engine* e, const float* samples, uint64_t total_samp
         uint64_t target = 148ull * 28 * 3, seg_min = 65536;  // measured at C2 (walk ms): 6216 walkers 8.1, 12 500 7.1, 25 000 6.7
         if (const char* ev = getenv("TMK_ASK_SEGMENTS")) target = strtoull(ev, nullptr, 10);  // 0 / 1: off
         if (const char* ev = getenv("TMK_ASK_SEG_MIN")) seg_min = std::max<uint64_t>(8192, strtoull(ev, nullptr, 10));
-        if (total_samples && uint64_t(n_streams) < target && pchk != nullptr) {
+        // (only while the captures alone cannot fill the warp slots — 148 SMs x 28 warps: at 8192 busy captures the
+        //  duplicated frames and the second pass cost more than the segments gain: C3 FSK walk 51.8 -> 59.0 ms)
+        if (total_samples && uint64_t(n_streams) * 3 <= target && pchk != nullptr) {
             for (uint32_t s = 0; s < n_streams; ++s) {
                 const uint64_t n = sd[s].n;
                 const uint64_t share = (target * n + total_samples - 1) / total_samples;
