@@ -100,7 +100,9 @@ typedef struct tmk_frame_rec {
     uint64_t frame_start;    /* first header sample after sync-word refinement */
     uint64_t payload_off;    /* byte offset into the payload buffer (status OK / CRC_FAIL /
                                 NOT_FOR_US: `len` decoded payload bytes are stored there) */
-    float corr;              /* correlation of the detecting window */
+    float corr;              /* correlation of the detecting window, computed with the accurately summed window energy:
+                                within 1e-5 relative of the reference's value (which uses its drifting rolling energy);
+                                not part of the bit-exact contract — tmk_correlate is the bit-exact probe */
     uint32_t consumed;       /* samples consumed from preamble_start */
     uint16_t len;            /* header fields (zero when fewer than 7 header bytes decoded) */
     uint8_t crc;

@@ -331,3 +331,51 @@ def test_scan_filter_contract(engine, orc, kind, spl, pb):
             if e.min() >= 1e-3 * e.max():
                 assert rmax <= want_r * (1 + 2e-3) + 1e-6, (i, b, rmax, want_r)
             assert ncand == got_bits[b * B:(b + 1) * B].sum()
+
+
+def test_exactly_sized_caller_buffers(engine, orc):
+    """record and payload buffers sized to what the oracle returns must be enough: the first pass counts bytes of
+    speculative decodes no walk links (false preambles inside frame bodies) and of segment walkers before their meeting
+    point; the engine recounts with the plain walk before it calls a buffer too small"""
+    import os
+    import tmkphy
+    rng = np.random.default_rng(2025)
+    for kind in (FB, MAN):
+        cfg = tmkphy.make_config(kind, local_addr=1)
+        caps = [helpers.make_capture(orc, cfg, rng, n_frames=40, snr_db=s, gap_range=(48, 300)) for s in (None, 15, 8, 6, 4)]
+        for c in caps:  # flipped stretches: in-body false preambles, header failures
+            for _ in range(6):
+                a = int(rng.integers(0, len(c) - 500))
+                c[a:a + int(rng.integers(30, 400))] *= -1.0
+        s, st = helpers.pack(caps, cfg, tmkphy)
+        want, wpl = [], []
+        base = 0
+        for i, c in enumerate(caps):
+            r, p = orc.decode_stream(cfg, c, stream_id=i)
+            r["payload_off"] += base
+            base += len(p)
+            want.append(r)
+            wpl.append(p)
+        want, wpl = np.concatenate(want), np.concatenate(wpl)
+        saved = os.environ.get("TMK_WALK_SEG_MIN")
+        try:
+            for seg_min in (None, "8192"):
+                if seg_min:
+                    os.environ["TMK_WALK_SEG_MIN"] = seg_min
+                got, gpl = engine.decode_batch(s, st, rec_cap=len(want), payload_cap=max(1, len(wpl)))
+                helpers.assert_records_equal(got, gpl, want, wpl, f"exact caps kind={kind} seg_min={seg_min}")
+                if len(want) > 1:  # one record short: refused, with the exact count (the Python wrapper would grow and retry)
+                    import ctypes as C
+                    from tmkphy import _abi
+                    recs = np.zeros(len(want) - 1, _abi.REC_DTYPE)
+                    pl = np.zeros(len(wpl), np.uint8)
+                    nr, npl = C.c_uint64(0), C.c_uint64(0)
+                    rc = engine._lib.tmk_decode_batch(engine._h, s.ctypes.data_as(C.c_void_p), s.size, st.ctypes.data_as(C.c_void_p),
+                                                      len(st), recs.ctypes.data_as(C.c_void_p), len(recs), C.byref(nr),
+                                                      pl.ctypes.data_as(C.c_void_p), len(pl), C.byref(npl))
+                    assert rc == _abi.E_CAPACITY and nr.value == len(want) and npl.value == len(wpl)
+        finally:
+            if saved is None:
+                os.environ.pop("TMK_WALK_SEG_MIN", None)
+            else:
+                os.environ["TMK_WALK_SEG_MIN"] = saved
