@@ -540,15 +540,20 @@ static int decode_batch_impl(tmk_engine* e, const void* samples_v, bool pcm16, u
         // streams). Within a chunk the walk follows the cluster pass; they CAN run side by side (the cluster
         // pass publishes every block with a release store, a walk that reaches a block first waits for it,
         // bounded, or evaluates the block itself), but that measured slower (see serial_cluster above).
-        cudaStream_t cs = e->walk_streams[(2 * g) % 4], ws = e->walk_streams[(2 * g + 1) % 4];
-        cudaEvent_t se = e->cev[3 + (g & 1)];
-        CK(cudaEventRecord(se, e->stream));
-        CK(cudaStreamWaitEvent(cs, se, 0));
-        CK(cudaStreamWaitEvent(ws, se, 0));
+        // (one chunk — device-resident batches, the links' polls: everything in order on the engine's stream, no hand-overs
+        //  between streams; a poll of 256 links is ~110 us of kernels and was ~170 us of API calls and stream hops)
+        const bool one = chunks.size() == 1;
+        cudaStream_t cs = one ? e->stream : e->walk_streams[(2 * g) % 4], ws = one ? e->stream : e->walk_streams[(2 * g + 1) % 4];
+        if (!one) {
+            cudaEvent_t se = e->cev[3 + (g & 1)];
+            CK(cudaEventRecord(se, e->stream));
+            CK(cudaStreamWaitEvent(cs, se, 0));
+            CK(cudaStreamWaitEvent(ws, se, 0));
+        }
         if (use_fast) {
             e->launches += tmk_launch_cluster(dx, ds, dtd, dp, dbi, dcb, fast, dpay, dev_pay_cap, dc, !serial_cluster, cs);
-            if (chunks.size() == 1) CK(cudaEventRecord(e->ev[5], cs));
-            if (serial_cluster) {
+            if (one) CK(cudaEventRecord(e->ev[5], cs));
+            if (serial_cluster && !one) {
                 CK(cudaEventRecord(e->wev[0], cs));
                 CK(cudaStreamWaitEvent(ws, e->wev[0], 0));
             }
@@ -567,10 +572,11 @@ static int decode_batch_impl(tmk_engine* e, const void* samples_v, bool pcm16, u
         CK(cudaGetLastError());
     }
     if (chunks.size() != 1) CK(cudaEventRecord(e->ev[2], e->stream));  // end of the last scan
-    for (int i = 0; i < 4; ++i) {
-        CK(cudaEventRecord(e->wev[i], e->walk_streams[i]));
-        CK(cudaStreamWaitEvent(e->stream, e->wev[i], 0));
-    }
+    if (chunks.size() != 1)
+        for (int i = 0; i < 4; ++i) {
+            CK(cudaEventRecord(e->wev[i], e->walk_streams[i]));
+            CK(cudaStreamWaitEvent(e->stream, e->wev[i], 0));
+        }
     TmkCounters hc;
     uint64_t n_exact = 0;  // records = sum of the per-stream counts
     if (seg_mode) {

@@ -184,7 +184,8 @@ int tmk_links_process_samples(tmk_links* l, const float* samples, uint64_t total
                                                  static_cast<float*>(l->d_work.p));
     CK(cudaGetLastError());
     e->launches += 1;
-    CK(cudaStreamSynchronize(e->stream));  // `desc` is reused below; the decode enqueues on the same stream
+    // (no synchronisation: the descriptors were copied out of pageable memory, which cudaMemcpyAsync stages before it
+    //  returns, and the decode enqueues on the same stream)
 
     // 3. decode with the carried state
     std::vector<TmkLinkState> fin(n);
