@@ -19,7 +19,8 @@ samples each, 7.86 GB of fp32), src/phy 4B5B frames at random offsets, AWGN SNR 
                C4 (8 hour-long captures with clock drift), C5 (131 072 mixed-modulation streams x 2^18, sharded
                over the ranks: the strong-scaling leg)
 
---impl reference times the CPU implementation alone (the reference is Rust; there is no rustc here or on the GPU
+--impl reference times the CPU implementation alone, on a bounded sample of the SAME captures (the GPU arm's generator restated
+on the host, oracle/synth_host.py) (the reference is Rust; there is no rustc here or on the GPU
 box — probed, gpurun_out/r2_probe.txt — so oracle/_ref cannot exist: kind = "port").
 No torch anywhere: under torchrun the ranks find each other through RANK / WORLD_SIZE / LOCAL_RANK and exchange
 the NCCL id through a file; the reduction is tmk_comm_* of the C ABI.
@@ -447,18 +448,17 @@ def run_reference(args):
     orc.build()
     threads = host_threads()
     cfg = tmkphy.make_config(tmkphy.LINE_4B5B, local_addr=1)
-    # a bounded sample of the same workload: captures come from the oracle's own modulator here,
-    # so this arm needs no GPU and none of the product's kernels
-    sys.path.insert(0, os.path.join(ROOT, "tests"))
-    import helpers
-    n_s = max(256, 32 * threads)
+    # a bounded sample of the SAME workload: the captures of the GPU arm's generator (tmk_synth_batch, seeds 0x7A4D + group),
+    # restated on the host (oracle/synth_host.py: same frames, offsets and bytes; noise equal up to the rounding of the
+    # device's fast log / sin — checked in tests/test_gpu_ingest.py), so this arm needs no GPU and none of the product's kernels
+    from oracle import synth_host
+    n_s = max(256, 32 * threads) // len(SNRS) * len(SNRS)
     n_per = N_PER_STREAM  # whole 10 s streams, 1/8 of the captures of the workload per step on a 16-core host
+    per_g = n_s // len(SNRS)
     caps = []
-    base = [helpers.make_capture(orc, cfg, np.random.default_rng(100 + i), n_frames=150, snr_db=SNRS[i % len(SNRS)],
-                                 gap_range=(48, 4800)) for i in range(16)]
-    for i in range(n_s):
-        b = base[i % 16]
-        caps.append(np.resize(b, n_per) if len(b) < n_per else b[:n_per])
+    for g, snr in enumerate(SNRS):  # GPU stream g * 512 + s  <->  call seed 0x7A4D + g, local stream s
+        for sidx in range(per_g):
+            caps.append(synth_host.capture(orc, cfg, 0x7A4D + g, sidx, n_per, snr, 0.7)[0])
     samples = np.concatenate(caps).astype(np.float32)
     st, total = tmkphy.make_streams([n_per] * n_s, cfg)
     secs = []
@@ -468,12 +468,14 @@ def run_reference(args):
             secs.append(sec)
     t = float(np.sum(secs))
     v = total * args.steps / t / 1e6
-    sample = f"{n_s} streams x {n_per} samples per step (oracle-modulated 4B5B frames, AWGN sweep)"
+    sample = (f"{n_s} of the {N_STREAMS} captures of the workload per step (streams 0..{per_g - 1} of each of the 8 SNR groups, "
+              f"the GPU arm's generator restated on the host), {n_per} samples each")
     print(json.dumps({
         "impl": "reference", "metric": METRIC, "value": v, "unit": "Msamples/s", "n_gpus": args.gpus,
         "steps": args.steps, "warmup": args.warmup, "ms_per_step": t / args.steps * 1e3, "higher_is_better": True,
         "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-        "config": {"workload": WORKLOAD, "sample": sample},
+        "config": {"workload": WORKLOAD, "streams_per_gpu": N_STREAMS, "samples_per_stream": N_PER_STREAM, "line_code": "4b5b",
+                   "chunk": 0, "sample": sample},
         "cpu_baseline": {"value": v, "unit": "Msamples/s", "cores": threads, "kind": "port", "sample": sample},
         "e2e": {"value": v, "unit": "Msamples/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}))
 

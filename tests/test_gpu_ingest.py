@@ -133,3 +133,30 @@ def test_comm_single_rank_and_errors(engine):
         engine.comm_destroy()
     with pytest.raises(tmkphy.TmkError):
         engine.comm_init(uid, 2, 2)
+
+
+@pytest.mark.parametrize("kind", [1, 0])
+def test_host_generator_matches_device(engine, orc, kind):
+    """oracle/synth_host.py (what `bench.py --impl reference` decodes) against tmk_synth_batch: the same frames at the same
+    offsets with the same bytes, the noise equal up to the rounding of the device's fast log / sin / cos"""
+    import tmkphy
+    from oracle import synth_host
+    cfg = tmkphy.make_config(kind, local_addr=1)
+    seed, n_s, n_per = 0x7A4D + 3, 6, 48000
+    for snr in (10.0, 0.0, 100.0):
+        x, truth = engine.synth_batch(cfg, seed, n_s, n_per, snr, 0.7)
+        x = x.reshape(n_s, n_per)
+        for s in (0, 3, 5):
+            h, frames = synth_host.capture(orc, cfg, seed, s, n_per, snr, 0.7)
+            t = truth[truth["stream"] == s]
+            assert [int(v) for v in t["preamble_start"]] == [f[0] for f in frames] and len(frames) > 3
+            assert [(int(r["type"]), int(r["seq"]), int(r["src"]), int(r["dst"]), int(r["len"])) for r in t] == [f[1:] for f in frames]
+            sigma = 0.0 if snr >= 100 else 0.7 * 10 ** (-snr / 20)
+            assert np.abs(h - x[s]).max() <= 1e-5 * max(1.0, 8 * sigma), (snr, s, np.abs(h - x[s]).max())
+            if snr >= 100:
+                assert np.array_equal(h, x[s])  # no noise: the frames alone, exactly
+            # and the decoder sees the same frames in both
+            a, pa = orc.decode_stream(cfg, h)
+            b, pb = orc.decode_stream(cfg, x[s])
+            if snr >= 10:
+                assert np.array_equal(a["frame_start"], b["frame_start"]) and bytes(pa) == bytes(pb)
