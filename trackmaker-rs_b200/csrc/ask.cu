@@ -474,9 +474,9 @@ __device__ __forceinline__ uint32_t seg_stream(const AskStream* __restrict__ str
 
 // largest |x| of every capture, as the bit pattern of the float (NaN > inf > finite): one warp per segment
 __global__ void __launch_bounds__(256)
-ask_xmax_kernel(const float* __restrict__ samples, const AskStream* __restrict__ streams, uint32_t n_streams, uint32_t n_segs,
+ask_xmax_kernel(const float* __restrict__ samples, const AskStream* __restrict__ streams, uint32_t n_streams, uint32_t seg0, uint32_t n_segs,
                 uint32_t* __restrict__ xmax_bits) {
-    const uint32_t seg = blockIdx.x * 8 + (threadIdx.x >> 5);
+    const uint32_t seg = seg0 + blockIdx.x * 8 + (threadIdx.x >> 5);  // segments [seg0, n_segs) of the batch
     if (seg >= n_segs) return;
     const int lane = threadIdx.x & 31;
     const uint32_t si = seg_stream(streams, n_streams, seg);
@@ -498,9 +498,9 @@ ask_xmax_kernel(const float* __restrict__ samples, const AskStream* __restrict__
 }
 
 __global__ void __launch_bounds__(128)
-ask_power_kernel(const float* __restrict__ samples, const AskStream* __restrict__ streams, uint32_t n_streams, uint32_t n_segs,
+ask_power_kernel(const float* __restrict__ samples, const AskStream* __restrict__ streams, uint32_t n_streams, uint32_t seg0, uint32_t n_segs,
                  const uint32_t* __restrict__ xmax_bits, float* __restrict__ pchk) {
-    const uint32_t seg = blockIdx.x * blockDim.x + threadIdx.x;
+    const uint32_t seg = seg0 + blockIdx.x * blockDim.x + threadIdx.x;
     if (seg >= n_segs) return;
     const uint32_t si = seg_stream(streams, n_streams, seg);
     const AskStream sd = streams[si];
@@ -751,10 +751,13 @@ __device__ __noinline__ void decode_frame(const AskCtx& c, int64_t s, uint8_t* b
 }
 
 __global__ void __launch_bounds__(128)
-ask_walk_kernel(const float* __restrict__ samples, const AskStream* __restrict__ streams, uint32_t n_streams,
+ask_walk_kernel(const float* __restrict__ samples, const AskStream* __restrict__ streams, uint32_t item0, uint32_t n_streams,
                 const float* __restrict__ tab, const uint32_t* __restrict__ wflag, const float* __restrict__ pchk,
                 tmk_ask_rec* __restrict__ recs, uint32_t* __restrict__ rec_ord, uint32_t* __restrict__ stream_cnt, uint64_t rec_cap,
-                unsigned long long* __restrict__ counters, TmkSeg seg, uint32_t* __restrict__ rec_item) {
+                unsigned long long* __restrict__ counters, unsigned long long* __restrict__ work_ctr, TmkSeg seg,
+                uint32_t* __restrict__ rec_item) {
+    // work items [item0, n_streams): a chunk of the batch (the chunks of a batch run on different CUDA streams, so that
+    // the power chain / filter / walk of neighbouring chunks overlap); work_ctr: this launch's own zeroed counter
     // seg.items != nullptr: the work items are SEGMENTS of captures (the segmented walk of tmk_internal.cuh, for this
     // receiver: its state right after a frame is the position r where the FIFO was zeroed — power is a function of the
     // samples alone — so a walker that starts mid-capture as "searching, nothing pending" is the true receiver from the
@@ -766,7 +769,7 @@ ask_walk_kernel(const float* __restrict__ samples, const AskStream* __restrict__
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     for (;;) {
         uint32_t sidx = 0;
-        if (lane == 0) sidx = uint32_t(atomicAdd(&counters[1], 1ull));
+        if (lane == 0) sidx = item0 + uint32_t(atomicAdd(work_ctr, 1ull));
         sidx = __shfl_sync(kFull, sidx, 0);
         if (sidx >= n_streams) return;
         uint32_t real = sidx, ord0 = 0;
@@ -1112,7 +1115,7 @@ int tmk_ask_sync_device(tmk_engine* e, const float* samples, uint64_t total_samp
     const size_t flag_words = size_t(words / 32 + 2);
     CK(e->d_streams.reserve(sizeof(AskStream) * n_streams));
     CK(e->d_ask_bits.reserve(flag_words * sizeof(uint32_t)));
-    CK(e->d_ask_l2.reserve(4 * sizeof(unsigned long long)));
+    CK(e->d_ask_l2.reserve(16 * sizeof(unsigned long long)));
     uint64_t dev_cap = std::max<uint64_t>(1024, total_samples / 4096 + 2ull * n_streams);
     CK(e->d_ask_recs.reserve(dev_cap * sizeof(tmk_ask_rec)));
     // unordered records + their ordinals | per-capture counts and bases (the ordered records land in d_ask_recs)
@@ -1123,60 +1126,34 @@ int tmk_ask_sync_device(tmk_engine* e, const float* samples, uint64_t total_samp
     uint32_t* rec_cnt = reinterpret_cast<uint32_t*>(rec_base + n_streams + 1);
     CK(cudaMemcpyAsync(e->d_streams.p, sd.data(), sizeof(AskStream) * n_streams, cudaMemcpyHostToDevice, e->stream));
     CK(cudaMemsetAsync(e->d_ask_bits.p, 0, flag_words * sizeof(uint32_t), e->stream));
-    CK(cudaMemsetAsync(e->d_ask_l2.p, 0, 4 * sizeof(unsigned long long), e->stream));
+    CK(cudaMemsetAsync(e->d_ask_l2.p, 0, 16 * sizeof(unsigned long long), e->stream));
     const AskStream* ds = static_cast<const AskStream*>(e->d_streams.p);
     const float* tab = static_cast<const float*>(e->d_ask_tab.p);
     CK(cudaEventRecord(e->ev[0], e->stream));
     // exact power checkpoints for the walk (TMK_ASK_NO_CHK=1: the walk chains through every sample itself, for A/B)
     static const bool no_chk = getenv("TMK_ASK_NO_CHK") != nullptr;
+    // the filter: tensor-core Toeplitz GEMM (ask_tc.cu) | TMK_ASK_FFT=1: FFT fast correlation | TMK_ASK_DIRECT=1: direct form
+    static const bool use_fft = getenv("TMK_ASK_FFT") != nullptr;
     float* pchk = nullptr;
+    uint32_t* xmax = nullptr;
     if (!no_chk && segs) {
         CK(e->d_ask_chk.reserve((words + 2) * sizeof(float) + sizeof(uint32_t) * n_streams));
         pchk = static_cast<float*>(e->d_ask_chk.p);
-        uint32_t* xmax = reinterpret_cast<uint32_t*>(pchk + words + 2);
+        xmax = reinterpret_cast<uint32_t*>(pchk + words + 2);
         CK(cudaMemsetAsync(xmax, 0, sizeof(uint32_t) * n_streams, e->stream));
-        ask_xmax_kernel<<<uint32_t((segs + 7) / 8), 256, 0, e->stream>>>(dx, ds, n_streams, uint32_t(segs), xmax);
-        ask_power_kernel<<<uint32_t((segs + 127) / 128), 128, 0, e->stream>>>(dx, ds, n_streams, uint32_t(segs), xmax, pchk);
-        e->launches += 2;
-        CK(cudaGetLastError());
     }
-    // the filter: tensor-core Toeplitz GEMM (ask_tc.cu) | TMK_ASK_FFT=1: FFT fast correlation | TMK_ASK_DIRECT=1: direct form
-    static const bool use_fft = getenv("TMK_ASK_FFT") != nullptr;
-    if (pchk != nullptr && !use_fft && !direct) {
+    const bool tc = pchk != nullptr && !use_fft && !direct;
+    std::vector<uint32_t> tc_base(size_t(n_streams) + 1, 0);
+    if (tc) {
         std::vector<uint64_t> so(n_streams), sn(n_streams), sw(n_streams);
         for (uint32_t s = 0; s < n_streams; ++s) {
             so[s] = sd[s].offset;
             sn[s] = sd[s].n;
             sw[s] = sd[s].word_base;
         }
-        rc = tmk_ask_tc_filter(e, dx, total_samples, so.data(), sn.data(), sw.data(), n_streams, tab, pchk,
-                               static_cast<uint32_t*>(e->d_ask_bits.p));
+        rc = tmk_ask_tc_prepare(e, so.data(), sn.data(), sw.data(), n_streams, tc_base.data());
         if (rc != TMK_OK) return rc;
-    } else
-    if (tiles) {
-        if (direct) {
-            ask_scan_kernel<<<uint32_t(tiles), kThreads, 0, e->stream>>>(dx, ds, n_streams, tab, static_cast<uint32_t*>(e->d_ask_bits.p));
-        } else {
-            static bool attr = false;
-            if (!attr) {
-                CK(cudaFuncSetAttribute(ask_scan_fft_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, int(sizeof(FftSmem))));
-                attr = true;
-            }
-            const float2* twg = reinterpret_cast<const float2*>(tab + kTabFft);
-            static int fft_ctas = 0;
-            if (fft_ctas == 0) {
-                int sms = 0, per_sm = 0;
-                cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, e->device);
-                cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, ask_scan_fft_kernel, kFT, sizeof(FftSmem));
-                fft_ctas = sms * (per_sm > 0 ? per_sm : 1);
-            }
-            ask_scan_fft_kernel<<<uint32_t(std::min<uint64_t>((tiles + 1) / 2, uint64_t(fft_ctas))), kFT, sizeof(FftSmem), e->stream>>>(
-                dx, ds, n_streams, uint32_t(tiles), twg, twg + kN, e->ask_hscale, static_cast<uint32_t*>(e->d_ask_bits.p));
-        }
-        e->launches += 1;
     }
-    CK(cudaGetLastError());
-    CK(cudaEventRecord(e->ev[1], e->stream));
     static int walk_ctas = 0;
     if (walk_ctas == 0) {
         int sms = 0, per_sm = 0;
@@ -1188,6 +1165,7 @@ int tmk_ask_sync_device(tmk_engine* e, const float* samples, uint64_t total_samp
     // captures half of the SMs' warp slots stay empty (C2: 14 busy warps per SM). Captures are cut into segments walked at
     // once and stitched exactly (tmk_internal.cuh; this receiver's state behind a frame is its position).
     std::vector<TmkSegItem> items;
+    std::vector<uint32_t> item_of(size_t(n_streams) + 1, 0);  // first walker of every capture
     {
         uint64_t target = 148ull * 28 * 3, seg_min = 65536;  // measured at C2 (walk ms): 6216 walkers 8.1, 12 500 7.1, 25 000 6.7
         if (const char* ev = getenv("TMK_ASK_SEGMENTS")) target = strtoull(ev, nullptr, 10);  // 0 / 1: off
@@ -1202,6 +1180,7 @@ int tmk_ask_sync_device(tmk_engine* e, const float* samples, uint64_t total_samp
                 const uint64_t seg_len = nseg > 1 ? ((n + nseg - 1) / nseg + 31) / 32 * 32 : std::max<uint64_t>(n, 1);
                 nseg = nseg > 1 ? (n + seg_len - 1) / seg_len : 1;
                 const uint32_t first = uint32_t(items.size());
+                item_of[s] = first;
                 for (uint64_t k = 0; k < nseg; ++k) {
                     TmkSegItem it;
                     it.stream = s;
@@ -1214,6 +1193,7 @@ int tmk_ask_sync_device(tmk_engine* e, const float* samples, uint64_t total_samp
                     items.push_back(it);
                 }
             }
+            item_of[n_streams] = uint32_t(items.size());
             if (items.size() == n_streams) items.clear();
         }
     }
@@ -1238,16 +1218,87 @@ int tmk_ask_sync_device(tmk_engine* e, const float* samples, uint64_t total_samp
         CK(cudaMemcpyAsync(b, items.data(), ib, cudaMemcpyHostToDevice, e->stream));
         CK(cudaMemsetAsync(b + ib, 0, sb, e->stream));
     }
-    const uint32_t grid = std::min<uint32_t>((n_items + 3) / 4, uint32_t(walk_ctas));
-    unsigned long long* ctr = static_cast<unsigned long long*>(e->d_ask_l2.p);
-    for (uint32_t pass = 1; pass <= (seg_mode ? 2u : 1u); ++pass) {
-        seg.pass = pass;
-        if (pass == 2) CK(cudaMemsetAsync(ctr + 1, 0, sizeof(unsigned long long), e->stream));  // the work counter
-        ask_walk_kernel<<<grid, 128, 0, e->stream>>>(dx, ds, n_items, tab, static_cast<const uint32_t*>(e->d_ask_bits.p), pchk,
-                                                     raw_recs, raw_ord, rec_cnt, dev_cap, ctr, seg, raw_item);
-        e->launches += 1;
+    if (!seg_mode)
+        for (uint32_t s = 0; s <= n_streams; ++s) item_of[s] = s;
+    // Chunks of whole captures, each on its own CUDA stream (xmax -> power chain -> filter -> walk of a chunk in order,
+    // neighbouring chunks free to overlap), only on request (TMK_ASK_CHUNKS): MEASURED AND NOT SHIPPED — the stages load
+    // different units (DRAM, DRAM latency, tensor pipe, issue slots of a few busy warps), but the filter's 227 KB of shared
+    // memory per SM keeps it from sharing an SM with the walk's CTAs, and a chunk's walk has fewer captures to fill the
+    // warp slots with: C2 at 1 / 2 / 4 chunks 128 / 129 / 114 G samples/s, C3 FSK walk 59 -> 72 ms at 4 chunks.
+    constexpr uint32_t kMaxChunks = 4;
+    uint32_t n_chunks = 1;
+    if (tc) {
+        if (const char* ev = getenv("TMK_ASK_CHUNKS")) n_chunks = uint32_t(std::min<uint64_t>(kMaxChunks, std::max<uint64_t>(1, strtoull(ev, nullptr, 10))));
+        n_chunks = std::min(n_chunks, n_streams);
     }
-    CK(cudaGetLastError());
+    uint32_t cut[kMaxChunks + 1];
+    cut[0] = 0;
+    {
+        uint64_t acc = 0;
+        uint32_t g = 1;
+        for (uint32_t s = 0; s < n_streams && g < n_chunks; ++s) {
+            acc += sd[s].n;
+            if (acc * n_chunks >= uint64_t(g) * total_samples && s + 1 < n_streams) cut[g++] = s + 1;
+        }
+        while (g <= n_chunks) cut[g++] = n_streams;
+    }
+    unsigned long long* ctr = static_cast<unsigned long long*>(e->d_ask_l2.p);  // [0] record slots, [2 + 2 g + pass - 1] work counters
+    if (n_chunks > 1) CK(cudaEventRecord(e->cev[0], e->stream));
+    for (uint32_t g = 0; g < n_chunks; ++g) {
+        const uint32_t s0 = cut[g], s1 = cut[g + 1];
+        if (s1 <= s0) continue;
+        cudaStream_t st = n_chunks > 1 ? e->walk_streams[g % 4] : e->stream;
+        if (n_chunks > 1) CK(cudaStreamWaitEvent(st, e->cev[0], 0));
+        if (pchk != nullptr) {
+            const uint32_t g0 = sd[s0].seg_base, g1 = s1 < n_streams ? sd[s1].seg_base : uint32_t(segs);
+            if (g1 > g0) {
+                ask_xmax_kernel<<<(g1 - g0 + 7) / 8, 256, 0, st>>>(dx, ds, n_streams, g0, g1, xmax);
+                ask_power_kernel<<<(g1 - g0 + 127) / 128, 128, 0, st>>>(dx, ds, n_streams, g0, g1, xmax, pchk);
+                e->launches += 2;
+            }
+        }
+        if (tc) {
+            rc = tmk_ask_tc_filter(e, dx, total_samples, n_streams, tc_base[s0], tc_base[s1], tab, pchk,
+                                   static_cast<uint32_t*>(e->d_ask_bits.p), st);
+            if (rc != TMK_OK) return rc;
+        } else if (tiles) {
+            if (direct) {
+                ask_scan_kernel<<<uint32_t(tiles), kThreads, 0, st>>>(dx, ds, n_streams, tab, static_cast<uint32_t*>(e->d_ask_bits.p));
+            } else {
+                static bool attr = false;
+                if (!attr) {
+                    CK(cudaFuncSetAttribute(ask_scan_fft_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, int(sizeof(FftSmem))));
+                    attr = true;
+                }
+                const float2* twg = reinterpret_cast<const float2*>(tab + kTabFft);
+                static int fft_ctas = 0;
+                if (fft_ctas == 0) {
+                    int sms = 0, per_sm = 0;
+                    cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, e->device);
+                    cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, ask_scan_fft_kernel, kFT, sizeof(FftSmem));
+                    fft_ctas = sms * (per_sm > 0 ? per_sm : 1);
+                }
+                ask_scan_fft_kernel<<<uint32_t(std::min<uint64_t>((tiles + 1) / 2, uint64_t(fft_ctas))), kFT, sizeof(FftSmem), st>>>(
+                    dx, ds, n_streams, uint32_t(tiles), twg, twg + kN, e->ask_hscale, static_cast<uint32_t*>(e->d_ask_bits.p));
+            }
+            e->launches += 1;
+        }
+        CK(cudaGetLastError());
+        if (g + 1 == n_chunks) CK(cudaEventRecord(e->ev[1], st));  // the last filter is done: "filter" / "walk" split of the stage times
+        const uint32_t i0 = item_of[s0], i1c = item_of[s1];
+        const uint32_t grid = std::min<uint32_t>((i1c - i0 + 3) / 4, uint32_t(walk_ctas));
+        for (uint32_t pass = 1; pass <= (seg_mode ? 2u : 1u) && i1c > i0; ++pass) {
+            seg.pass = pass;
+            ask_walk_kernel<<<grid, 128, 0, st>>>(dx, ds, i0, i1c, tab, static_cast<const uint32_t*>(e->d_ask_bits.p), pchk, raw_recs,
+                                                  raw_ord, rec_cnt, dev_cap, ctr, ctr + 2 + 2 * g + (pass - 1), seg, raw_item);
+            e->launches += 1;
+        }
+        CK(cudaGetLastError());
+        if (n_chunks > 1) {
+            CK(cudaEventRecord(e->wev[g % 4], st));
+            CK(cudaStreamWaitEvent(e->stream, e->wev[g % 4], 0));
+        }
+    }
     CK(cudaEventRecord(e->ev[2], e->stream));
     unsigned long long hc[2] = {0, 0};
     CK(cudaMemcpyAsync(hc, e->d_ask_l2.p, sizeof hc, cudaMemcpyDeviceToHost, e->stream));

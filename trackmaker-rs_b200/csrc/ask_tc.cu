@@ -395,18 +395,17 @@ bool make_map(CUtensorMap* map, const float* base, uint64_t n_samples) {
 
 }  // namespace
 
-// Marks the candidate words of every stream in wflag (zeroed by the caller). s_off / s_n / s_word: per-stream sample offset,
-// length and first flag word (host arrays); pchk: the exact power checkpoints (ask_power_kernel) indexed by global word.
-int tmk_ask_tc_filter(tmk_engine* e, const float* dx, uint64_t total_samples, const uint64_t* s_off, const uint64_t* s_n,
-                      const uint64_t* s_word, uint32_t n_streams, const float* chirp, const float* pchk, uint32_t* wflag) {
-    std::vector<uint32_t> base(n_streams + 1, 0);
+// Tile descriptors of the whole batch (on e->stream), then one launch per range of streams. s_off / s_n / s_word: per-stream
+// sample offset, length and first flag word (host arrays); tile_base_out[s] = first tile of stream s (n_streams + 1 entries).
+int tmk_ask_tc_prepare(tmk_engine* e, const uint64_t* s_off, const uint64_t* s_n, const uint64_t* s_word, uint32_t n_streams,
+                       uint32_t* tile_base_out) {
     uint64_t tiles = 0;
     for (uint32_t s = 0; s < n_streams; ++s) {
-        base[s] = uint32_t(tiles);
+        tile_base_out[s] = uint32_t(tiles);
         if (s_n[s] >= uint64_t(kPre)) tiles += (s_n[s] - (kPre - 1) + kTile - 1) / kTile;
         if (tiles > 0x7fffffffull) return tmk_fail(e, TMK_E_INVALID, "batch too large (tile count)");
     }
-    base[n_streams] = uint32_t(tiles);
+    tile_base_out[n_streams] = uint32_t(tiles);
     if (tiles == 0) return TMK_OK;
     const size_t arr = sizeof(uint64_t) * n_streams;
     CK(e->d_ask_tc.reserve(3 * arr + sizeof(uint32_t) * (n_streams + 1) + 64 + sizeof(TileDescA) * tiles));
@@ -414,11 +413,24 @@ int tmk_ask_tc_filter(tmk_engine* e, const float* dx, uint64_t total_samples, co
     CK(cudaMemcpyAsync(d, s_off, arr, cudaMemcpyHostToDevice, e->stream));
     CK(cudaMemcpyAsync(d + arr, s_n, arr, cudaMemcpyHostToDevice, e->stream));
     CK(cudaMemcpyAsync(d + 2 * arr, s_word, arr, cudaMemcpyHostToDevice, e->stream));
-    CK(cudaMemcpyAsync(d + 3 * arr, base.data(), sizeof(uint32_t) * (n_streams + 1), cudaMemcpyHostToDevice, e->stream));
+    CK(cudaMemcpyAsync(d + 3 * arr, tile_base_out, sizeof(uint32_t) * (n_streams + 1), cudaMemcpyHostToDevice, e->stream));
     TileDescA* td = reinterpret_cast<TileDescA*>(d + (3 * arr + sizeof(uint32_t) * (n_streams + 1) + 31) / 32 * 32);
     ask_tile_desc_kernel<<<uint32_t((tiles + 255) / 256), 256, 0, e->stream>>>(
         reinterpret_cast<const uint64_t*>(d), reinterpret_cast<const uint64_t*>(d + arr), reinterpret_cast<const uint64_t*>(d + 2 * arr),
         reinterpret_cast<const uint32_t*>(d + 3 * arr), n_streams, uint32_t(tiles), td);
+    e->launches += 1;
+    CK(cudaGetLastError());
+    return TMK_OK;
+}
+
+// Marks the candidate words of the tiles [tile0, tile1) in wflag (zeroed by the caller), on `st`. pchk: the exact power
+// checkpoints (ask_power_kernel) indexed by global word.
+int tmk_ask_tc_filter(tmk_engine* e, const float* dx, uint64_t total_samples, uint32_t n_streams, uint32_t tile0, uint32_t tile1,
+                      const float* chirp, const float* pchk, uint32_t* wflag, cudaStream_t st) {
+    if (tile1 <= tile0) return TMK_OK;
+    const size_t arr = sizeof(uint64_t) * n_streams;
+    const TileDescA* td = reinterpret_cast<const TileDescA*>(static_cast<char*>(e->d_ask_tc.p) +
+                                                             (3 * arr + sizeof(uint32_t) * (n_streams + 1) + 31) / 32 * 32);
     static int sms = 0;
     const size_t smem = size_t(kStages) * kStageBytes + size_t(kHalves) * kTBytes + sizeof(Smem) + 1024;
     if (sms == 0) {
@@ -434,9 +446,10 @@ int tmk_ask_tc_filter(tmk_engine* e, const float* dx, uint64_t total_samples, co
         if (!make_map(&maps.m[n_maps], dx + b0, len)) break;
         ++n_maps;
     }
+    const uint32_t tiles = tile1 - tile0;
     const uint32_t grid = uint32_t(std::min<uint64_t>(tiles, uint64_t(sms)));
-    ask_tc_kernel<<<grid, kThreads, smem, e->stream>>>(maps, n_maps, dx, total_samples, td, uint32_t(tiles), chirp, pchk, wflag);
-    e->launches += 2;
+    ask_tc_kernel<<<grid, kThreads, smem, st>>>(maps, n_maps, dx, total_samples, td + tile0, tiles, chirp, pchk, wflag);
+    e->launches += 1;
     CK(cudaGetLastError());
     return TMK_OK;
 }

@@ -92,5 +92,7 @@ int tmk_ask_ensure_tables(tmk_engine* e);
 int tmk_ask_sync_device(tmk_engine* e, const float* samples, uint64_t total_samples, const tmk_stream* streams, uint32_t n_streams,
                         const float** dx_out, uint64_t* n_recs, uint64_t* dev_cap_out);
 // ask_tc.cu: the chirp filter on the tensor cores (marks candidate words in wflag)
-int tmk_ask_tc_filter(tmk_engine* e, const float* dx, uint64_t total_samples, const uint64_t* s_off, const uint64_t* s_n,
-                      const uint64_t* s_word, uint32_t n_streams, const float* chirp, const float* pchk, uint32_t* wflag);
+int tmk_ask_tc_prepare(tmk_engine* e, const uint64_t* s_off, const uint64_t* s_n, const uint64_t* s_word, uint32_t n_streams,
+                       uint32_t* tile_base_out);
+int tmk_ask_tc_filter(tmk_engine* e, const float* dx, uint64_t total_samples, uint32_t n_streams, uint32_t tile0, uint32_t tile1,
+                      const float* chirp, const float* pchk, uint32_t* wflag, cudaStream_t st);
