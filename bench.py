@@ -410,13 +410,15 @@ def c5_leg(eng, orc, tmkphy, rank, world, hbm, steps, warmup, n_total, n_per, th
     ms_all = eng.allreduce_max([ms])[0]
     rank_ms = eng.allreduce_max([ms, -ms])
     counts = eng.allreduce_sum([int(dec.nr.value), len(arecs), planted, n_loc])
+    per_rank = eng.allgather([int(ms / steps * 1000), int(dec.nr.value) + len(arecs)])  # ncclAllGather: step time (us), records
     res = {"workload": f"C5: {n_total} mixed streams x {n_per} samples (stream_id % 3 -> 4B5B / Manchester / chirp+BPSK, "
                        f"AWGN sweep), sharded over {world} rank(s) in contiguous id ranges",
            "scaling": "strong", "msamples_per_s": n_total * n_per * steps / (ms_all * 1e-3) / 1e6,
            "ms_per_step": ms_all / steps, "rank_ms_per_step_max_min": [rank_ms[0] / steps, -rank_ms[1] / steps],
            "frac_hbm": 4.0 * n_total * n_per / world / (ms_all / steps * 1e-3) / 1e9 / hbm,
            "stage_ms_rank0": {"src_phy": round(phy_ms, 3), "chirp_filter": round(am["scan"], 3), "chirp_walk": round(am["walk"], 3)},
-           "streams": counts[3], "frames_planted": counts[2], "records_src_phy": counts[0], "records_chirp": counts[1]}
+           "streams": counts[3], "frames_planted": counts[2], "records_src_phy": counts[0], "records_chirp": counts[1],
+           "per_rank_ms": [r[0] / 1000.0 for r in per_rank], "per_rank_records": [r[1] for r in per_rank]}
     dec.free()
     if orc is not None and rank == 0:
         ok = True

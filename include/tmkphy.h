@@ -448,6 +448,8 @@ int tmk_comm_size(const tmk_engine* e);
 int tmk_stats_allreduce(tmk_engine* e, uint64_t counters[TMK_STAT_COUNT]);
 int tmk_comm_allreduce_sum_u64(tmk_engine* e, uint64_t* counters, uint32_t n);
 int tmk_comm_allreduce_max_f64(tmk_engine* e, double* values, uint32_t n);
+/* all[r * n + i] = rank r's mine[i] (n <= 8): per-GPU record counts / step times after a batch (ncclAllGather) */
+int tmk_comm_allgather_u64(tmk_engine* e, const uint64_t* mine, uint32_t n, uint64_t* all);
 int tmk_comm_barrier(tmk_engine* e);
 int tmk_comm_destroy(tmk_engine* e);
 

@@ -117,6 +117,7 @@ def test_comm_single_rank_and_errors(engine):
     import tmkphy
     assert engine.comm_size() == 1
     assert engine.allreduce_sum([1, 2, 3]) == [1, 2, 3] and engine.allreduce_max([2.5]) == [2.5]
+    assert engine.allgather([7, 1 << 50]) == [[7, 1 << 50]]
     uid = tmkphy.comm_unique_id()
     assert len(uid) == 128 and any(uid)
     engine.comm_init(uid, 0, 1)
@@ -124,6 +125,7 @@ def test_comm_single_rank_and_errors(engine):
         assert engine.comm_size() == 1
         assert engine.allreduce_sum([5, 1 << 40]) == [5, 1 << 40]
         assert engine.allreduce_max([-1.0, 3.25]) == [-1.0, 3.25]
+        assert engine.allgather([9, 8, 7]) == [[9, 8, 7]]  # ncclAllGather over one rank
         st = engine.stats_allreduce()
         assert st == engine.stats()
         engine.comm_barrier()

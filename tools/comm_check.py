@@ -20,6 +20,8 @@ assert m == [float(world - 1), 0.0], m
 from tmkphy import sharding  # noqa: E402
 tot, ms = sharding.reduce_stats({"a": rank, "b": 3}, 5.0 + rank, eng)
 assert tot == {"a": world * (world - 1) // 2, "b": 3 * world} and ms == 4.0 + world
+g = eng.allgather([rank * 10 + 1, 1 << 41])
+assert g == [[r * 10 + 1, 1 << 41] for r in range(world)], g
 eng.comm_barrier()
 if rank == 0:
     print(f"comm ok: {world} ranks")

@@ -27,6 +27,7 @@ struct NcclApi {
     int (*GetUniqueId)(NcclId*) = nullptr;
     int (*CommInitRank)(NcclComm*, int, NcclId, int) = nullptr;
     int (*AllReduce)(const void*, void*, size_t, int, int, NcclComm, cudaStream_t) = nullptr;
+    int (*AllGather)(const void*, void*, size_t, int, NcclComm, cudaStream_t) = nullptr;
     int (*CommDestroy)(NcclComm) = nullptr;
     const char* (*GetErrorString)(int) = nullptr;
     std::string err;
@@ -51,9 +52,10 @@ bool load_nccl() {
     a.GetUniqueId = reinterpret_cast<decltype(a.GetUniqueId)>(dlsym(a.lib, "ncclGetUniqueId"));
     a.CommInitRank = reinterpret_cast<decltype(a.CommInitRank)>(dlsym(a.lib, "ncclCommInitRank"));
     a.AllReduce = reinterpret_cast<decltype(a.AllReduce)>(dlsym(a.lib, "ncclAllReduce"));
+    a.AllGather = reinterpret_cast<decltype(a.AllGather)>(dlsym(a.lib, "ncclAllGather"));
     a.CommDestroy = reinterpret_cast<decltype(a.CommDestroy)>(dlsym(a.lib, "ncclCommDestroy"));
     a.GetErrorString = reinterpret_cast<decltype(a.GetErrorString)>(dlsym(a.lib, "ncclGetErrorString"));
-    if (!a.GetUniqueId || !a.CommInitRank || !a.AllReduce || !a.CommDestroy || !a.GetErrorString) {
+    if (!a.GetUniqueId || !a.CommInitRank || !a.AllReduce || !a.AllGather || !a.CommDestroy || !a.GetErrorString) {
         a.err = "libnccl lacks a required symbol";
         dlclose(a.lib);
         a.lib = nullptr;
@@ -92,7 +94,7 @@ int tmk_comm_init(tmk_engine* e, const void* unique_id128, int rank, int world) 
     e->comm = comm;
     e->comm_rank = rank;
     e->comm_world = world;
-    CK(e->d_comm.reserve(64 * sizeof(uint64_t)));
+    CK(e->d_comm.reserve(sizeof(uint64_t) * (64 + 8 + 8 * 64)));
     return TMK_OK;
 }
 
@@ -122,6 +124,27 @@ int tmk_comm_allreduce_max_f64(tmk_engine* e, double* values, uint32_t n) {
     const int rc = api().AllReduce(d, d, n, kNcclFloat64, kNcclMax, e->comm, e->stream);
     if (rc != 0) return nccl_fail(e, "ncclAllReduce", rc);
     CK(cudaMemcpyAsync(values, d, n * sizeof(double), cudaMemcpyDeviceToHost, e->stream));
+    CK(cudaStreamSynchronize(e->stream));
+    return TMK_OK;
+}
+
+// all[r * n .. r * n + n) = rank r's mine[0..n) (n <= 8; SURVEY §8e: per-GPU record counts after a batch). Without a
+// communicator all = mine.
+int tmk_comm_allgather_u64(tmk_engine* e, const uint64_t* mine, uint32_t n, uint64_t* all) {
+    if (!e || !mine || !all || n == 0 || n > 8) return tmk_fail(e, TMK_E_INVALID, "tmk_comm_allgather_u64: bad argument");
+    if (!e->comm) {
+        for (uint32_t i = 0; i < n; ++i) all[i] = mine[i];
+        return TMK_OK;
+    }
+    if (e->comm_world > 64) return tmk_fail(e, TMK_E_INVALID, "tmk_comm_allgather_u64: more than 64 ranks");
+    CK(cudaSetDevice(e->device));
+    CK(e->d_comm.reserve(sizeof(uint64_t) * (64 + 8 + 8 * 64)));
+    uint64_t* src = static_cast<uint64_t*>(e->d_comm.p) + 64;
+    uint64_t* dst = src + 8;
+    CK(cudaMemcpyAsync(src, mine, n * sizeof(uint64_t), cudaMemcpyHostToDevice, e->stream));
+    const int rc = api().AllGather(src, dst, n, kNcclUint64, e->comm, e->stream);
+    if (rc != 0) return nccl_fail(e, "ncclAllGather", rc);
+    CK(cudaMemcpyAsync(all, dst, size_t(n) * e->comm_world * sizeof(uint64_t), cudaMemcpyDeviceToHost, e->stream));
     CK(cudaStreamSynchronize(e->stream));
     return TMK_OK;
 }

@@ -562,6 +562,14 @@ class Engine:
         self._check(self._lib.tmk_comm_allreduce_max_f64(self._h, c, len(values)))
         return [float(v) for v in c]
 
+    def allgather(self, values):
+        """-> list (one per rank) of lists: every rank's values (tmk_comm_allgather_u64; at most 8 values)"""
+        n, world = len(values), self._lib.tmk_comm_size(self._h)
+        mine = (C.c_uint64 * n)(*[int(v) for v in values])
+        out = (C.c_uint64 * (n * world))()
+        self._check(self._lib.tmk_comm_allgather_u64(self._h, mine, n, out))
+        return [[int(out[r * n + i]) for i in range(n)] for r in range(world)]
+
     def comm_barrier(self):
         self._check(self._lib.tmk_comm_barrier(self._h))
 

@@ -163,6 +163,7 @@ SYMBOLS = {
     "tmk_stats_allreduce": (C.c_int, [_vp, _pu64]),
     "tmk_comm_allreduce_sum_u64": (C.c_int, [_vp, _pu64, _u32]),
     "tmk_comm_allreduce_max_f64": (C.c_int, [_vp, C.POINTER(C.c_double), _u32]),
+    "tmk_comm_allgather_u64": (C.c_int, [_vp, _pu64, _u32, _pu64]),
     "tmk_comm_barrier": (C.c_int, [_vp]),
     "tmk_comm_destroy": (C.c_int, [_vp]),
 }
