@@ -755,7 +755,8 @@ ask_walk_kernel(const float* __restrict__ samples, const AskStream* __restrict__
                 const float* __restrict__ tab, const uint32_t* __restrict__ wflag, const float* __restrict__ pchk,
                 tmk_ask_rec* __restrict__ recs, uint32_t* __restrict__ rec_ord, uint32_t* __restrict__ stream_cnt, uint64_t rec_cap,
                 unsigned long long* __restrict__ counters, unsigned long long* __restrict__ work_ctr, TmkSeg seg,
-                uint32_t* __restrict__ rec_item) {
+                uint32_t* __restrict__ rec_item, uint32_t want_bits) {
+    // want_bits == 0: the caller only needs the synchroniser (mcm.cu demodulates the bodies itself): no BPSK demodulation
     // work items [item0, n_streams): a chunk of the batch (the chunks of a batch run on different CUDA streams, so that
     // the power chain / filter / walk of neighbouring chunks overlap); work_ctr: this launch's own zeroed counter
     // seg.items != nullptr: the work items are SEGMENTS of captures (the segmented walk of tmk_internal.cuh, for this
@@ -899,7 +900,11 @@ ask_walk_kernel(const float* __restrict__ samples, const AskStream* __restrict__
             if (lane == 0) slot = atomicAdd(&counters[0], 1ull);
             slot = __shfl_sync(kFull, slot, 0);
             __shared__ uint8_t bits_s[4][16];
-            decode_frame(c, s, bits_s[warp], &id);
+            if (want_bits) {
+                decode_frame(c, s, bits_s[warp], &id);
+            } else if (lane < 14) {
+                bits_s[warp][lane] = 0;
+            }
             __syncwarp();
             if (lane == 0 && slot < rec_cap) {
                 tmk_ask_rec rec;
@@ -1081,7 +1086,7 @@ int tmk_ask_ensure_tables(tmk_engine* e) { return ensure_tables(e); }
 // an atomic slot counter), *dx_out is where the samples live on the device. Shared with mcm.cu, whose frames use the
 // same chirp preamble and frame envelope.
 int tmk_ask_sync_device(tmk_engine* e, const float* samples, uint64_t total_samples, const tmk_stream* streams, uint32_t n_streams,
-                        const float** dx_out, uint64_t* n_recs, uint64_t* dev_cap_out) {
+                        const float** dx_out, uint64_t* n_recs, uint64_t* dev_cap_out, bool want_bits) {
     *n_recs = 0;
     CK(cudaSetDevice(e->device));
     int rc = ensure_tables(e);
@@ -1290,7 +1295,8 @@ int tmk_ask_sync_device(tmk_engine* e, const float* samples, uint64_t total_samp
         for (uint32_t pass = 1; pass <= (seg_mode ? 2u : 1u) && i1c > i0; ++pass) {
             seg.pass = pass;
             ask_walk_kernel<<<grid, 128, 0, st>>>(dx, ds, i0, i1c, tab, static_cast<const uint32_t*>(e->d_ask_bits.p), pchk, raw_recs,
-                                                  raw_ord, rec_cnt, dev_cap, ctr, ctr + 2 + 2 * g + (pass - 1), seg, raw_item);
+                                                  raw_ord, rec_cnt, dev_cap, ctr, ctr + 2 + 2 * g + (pass - 1), seg, raw_item,
+                                                  want_bits ? 1u : 0u);
             e->launches += 1;
         }
         CK(cudaGetLastError());

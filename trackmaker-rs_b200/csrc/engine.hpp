@@ -90,7 +90,7 @@ inline bool tmk_is_device_ptr(const void* p) {
 // ask.cu, shared with mcm.cu (the multi-carrier frames use the chirp preamble and the frame envelope of examples/ask.rs)
 int tmk_ask_ensure_tables(tmk_engine* e);
 int tmk_ask_sync_device(tmk_engine* e, const float* samples, uint64_t total_samples, const tmk_stream* streams, uint32_t n_streams,
-                        const float** dx_out, uint64_t* n_recs, uint64_t* dev_cap_out);
+                        const float** dx_out, uint64_t* n_recs, uint64_t* dev_cap_out, bool want_bits = true);
 // ask_tc.cu: the chirp filter on the tensor cores (marks candidate words in wflag)
 int tmk_ask_tc_prepare(tmk_engine* e, const uint64_t* s_off, const uint64_t* s_n, const uint64_t* s_word, uint32_t n_streams,
                        uint32_t* tile_base_out);

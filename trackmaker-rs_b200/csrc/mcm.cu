@@ -507,7 +507,7 @@ int tmk_mcm_decode_batch(tmk_engine* e, int32_t mode, const float* samples, uint
     // the chirp synchroniser of examples/ask.rs finds the frames (records stay on the device)
     const float* dx = nullptr;
     uint64_t n = 0, dev_cap = 0;
-    rc = tmk_ask_sync_device(e, samples, total_samples, streams, n_streams, &dx, &n, &dev_cap);
+    rc = tmk_ask_sync_device(e, samples, total_samples, streams, n_streams, &dx, &n, &dev_cap, false);  // no BPSK demodulation
     *n_recs = n;
     if (rc != TMK_OK) return rc;
     if (n > rec_cap) return tmk_fail(e, TMK_E_CAPACITY, "tmk_mcm_decode_batch: record buffer too small");
