@@ -24,7 +24,7 @@ def main():
             rows.append((int(d["# Samples"]), int(d["Instructions Executed"]), fname, int(x[0]), x[1].strip(), stalls))
     ts, ti = sum(r[0] for r in rows) or 1, sum(r[1] for r in rows) or 1
     print(f"kernel {kern}: {ts} samples, {ti} warp instructions")
-    for s, i, f, ln, src, st in sorted(rows, reverse=True)[:top]:
+    for s, i, f, ln, src, st in sorted(rows, key=lambda r: (r[0], r[1]), reverse=True)[:top]:
         tops = ",".join(f"{k}:{v}" for k, v in sorted(st.items(), key=lambda kv: -kv[1])[:3])
         print(f"{s / ts * 100:5.1f}% smp {i / ti * 100:5.1f}% ins {f}:{ln:<4} {src[:90]}  [{tops}]")
 

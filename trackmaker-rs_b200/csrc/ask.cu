@@ -569,7 +569,8 @@ ask_power_kernel(const float* __restrict__ samples, const AskStream* __restrict_
 // scratch of the walk kernel at namespace scope: every access compiles to LDS / STS with immediate offsets (through the
 // generic pointers of AskCtx the taps of the exact dot were LD.E with 64-bit address arithmetic, ~6 instructions per tap)
 __shared__ __align__(16) float g_wpre[kPre];       // the chirp
-__shared__ __align__(16) float g_wxs[4][kPre + 40];  // the samples under the 32 windows of one word, per warp
+constexpr int kStageMax = 1024;
+__shared__ __align__(16) float g_wxs[4][kStageMax];  // the samples under the windows of a run of words, per warp
 __device__ __forceinline__ float fadd(float a, float b) { return __fadd_rn(a, b); }
 __device__ __forceinline__ float fmul(float a, float b) { return __fmul_rn(a, b); }
 
@@ -584,6 +585,7 @@ struct AskCtx {
     float p;
     float* stage;  // 128 floats of shared memory per warp
     const float* chk;  // exact power before sample 32 w per word of this capture, or -1 (ask_power_kernel); may be null
+    int64_t st_lo, st_hi, st_r;  // samples [st_lo, st_hi) are staged in g_wxs (zeros before st_r); st_hi == st_lo: nothing
 };
 
 // advance the EMA chain to `target` (power after sample target - 1)            ask.rs:696-697
@@ -690,16 +692,22 @@ __device__ __noinline__ void eval_word(AskCtx& c, int64_t w, int64_t r, float* s
     float* __restrict__ xs = g_wxs[warp];
     const int64_t base = w * 32 - (kPre - 1);  // sample index of xs[0]
     const float* __restrict__ x = c.x;
-    __syncwarp();
-#pragma unroll
-    for (int t = c.lane; t < kPre + 31; t += 32) {
-        const int64_t idx = base + t;
-        xs[t] = (idx >= r && idx < c.n) ? __ldg(x + idx) : 0.0f;
+    // (the words right behind a frame come one after the other and share 439 of their 471 samples: the whole run — at
+    //  most 14 words, 919 samples — is staged when its first word is looked at)
+    if (!(c.st_r == r && base >= c.st_lo && base + (kPre + 31) <= c.st_hi)) {
+        int64_t hi = base + (kPre + 31);
+        const int64_t pf_last = r + (kPre - 2);  // last position whose window is still partial
+        if (w * 32 <= pf_last) hi = max(hi, min((pf_last >> 5) * 32 + 32, base + int64_t(kStageMax)));
+        __syncwarp();
+        for (int64_t idx = base + c.lane; idx < hi; idx += 32) xs[idx - base] = (idx >= r && idx < c.n) ? __ldg(x + idx) : 0.0f;
+        __syncwarp();
+        c.st_lo = base;
+        c.st_hi = hi;
+        c.st_r = r;
     }
-    __syncwarp();
-    const int64_t zeros = r - base;  // taps below this read zeros for lane 0; lane l reads tap k at xs[l + k]
+    const int64_t zeros = r - base;  // taps below this read zeros for lane 0; lane l reads tap k at xs[(base - st_lo) + l + k]
     const int k0 = zeros > 31 ? int(min(zeros - 31, int64_t(kPre))) & ~7 : 0;
-    const float* __restrict__ xl = xs + c.lane;
+    const float* __restrict__ xl = xs + (base - c.st_lo) + c.lane;
     float sum = 0.0f;
 #pragma unroll 5
     for (int k = k0; k < kPre; k += 8) {
@@ -801,6 +809,7 @@ ask_walk_kernel(const float* __restrict__ samples, const AskStream* __restrict__
         c.p = 0.0f;
         c.stage = stage_s[warp];
         c.chk = pchk != nullptr ? pchk + sd.word_base : nullptr;
+        c.st_lo = c.st_hi = c.st_r = 0;
         const int64_t nwords = (c.n + 31) / 32;
         // a walker that resumes (pass 2) stands right behind a frame: FIFO zeroed at q0; one that starts a segment searches
         // with a full FIFO (r = 0) from q0 on
