@@ -70,3 +70,34 @@ def test_segmented_walk_matches_oracle(engine, orc, seg_env, seg_min):
     os.environ["TMK_WALK_SEGMENTS"] = "0"
     recs0, pl0 = engine.decode_batch(s, st)
     helpers.assert_records_equal(recs0, pl0, want, wpl, "plain walk")
+
+
+def test_segmented_walk_with_chunked_host_staging(engine, orc, seg_env):
+    """host-resident captures staged in chunks (copy of chunk g + 1 under the kernels of chunk g) AND segmented walks: every
+    chunk walks its own range of segment walkers in two passes"""
+    import tmkphy
+    saved = os.environ.get("TMK_CHUNK_MSAMPLES")
+    os.environ["TMK_WALK_SEG_MIN"] = "16384"
+    os.environ["TMK_CHUNK_MSAMPLES"] = "1"  # chunks of about one capture
+    try:
+        rng = np.random.default_rng(77)
+        cf, cm = tmkphy.make_config(FB, local_addr=1), tmkphy.make_config(MAN, local_addr=1)
+        caps = [long_capture(orc, cf, rng, 230, 10.0, gap_range=(48, 900)), long_capture(orc, cm, rng, 150, 7.0, gap_range=(48, 2000)),
+                long_capture(orc, cf, rng, 200, 5.0, corrupt=0.1, gap_range=(48, 700)), long_capture(orc, cm, rng, 5, 20.0)]
+        cfgs = [cf, cm, cf, cm]
+        s, st = helpers.pack(caps, cfgs, tmkphy)
+        assert len(s) > (3 << 20)
+        recs, pl = engine.decode_batch(s, st)
+        want, wpl, base = [], [], 0
+        for i, (c, cfg) in enumerate(zip(caps, cfgs)):
+            r, p = orc.decode_stream(cfg, c, stream_id=i)
+            r["payload_off"] += base
+            base += len(p)
+            want.append(r)
+            wpl.append(p)
+        helpers.assert_records_equal(recs, pl, np.concatenate(want), np.concatenate(wpl), "chunked host staging + segments")
+    finally:
+        if saved is None:
+            os.environ.pop("TMK_CHUNK_MSAMPLES", None)
+        else:
+            os.environ["TMK_CHUNK_MSAMPLES"] = saved
