@@ -86,7 +86,7 @@ def test_segmented_walk_with_chunked_host_staging(engine, orc, seg_env):
                 long_capture(orc, cf, rng, 200, 5.0, corrupt=0.1, gap_range=(48, 700)), long_capture(orc, cm, rng, 5, 20.0)]
         cfgs = [cf, cm, cf, cm]
         s, st = helpers.pack(caps, cfgs, tmkphy)
-        assert len(s) > (3 << 20)
+        assert len(s) > (3 << 19)  # more than one chunk of 2^20 samples
         recs, pl = engine.decode_batch(s, st)
         want, wpl, base = [], [], 0
         for i, (c, cfg) in enumerate(zip(caps, cfgs)):

@@ -1,0 +1,1 @@
+timeout 600 python -m pytest tests/test_gpu_segwalk.py -m gpu -x -q 2>&1 | grep -v Warning | tail -8
