@@ -388,11 +388,18 @@ def c5_leg(eng, orc, tmkphy, rank, world, hbm, steps, warmup, n_total, n_per, th
     dec = Decode(eng, d_x, tot_phy, st_phy, rec_cap=tot_phy // 1024 + 4 * n_phy + 1024, pay_cap=tot_phy // 48 + 65536)
     ask_cap = max(64, tot_ask // 4096 + 2 * n_ask)
 
+    # the chirp records come back to the host: one pinned buffer for all steps (a pageable one allocated per step cost ~15 ms)
+    h_arecs = eng.pinned_array((ask_cap,), tmkphy._abi.ASK_REC_DTYPE) if n_ask else None
+    n_arecs = C.c_uint64(0)
+    stp_ask = st_ask.ctypes.data_as(C.c_void_p)
+
     def step():
         if n_phy:
             dec.step()
         if n_ask:
-            return eng.ask_decode_batch(d_ask, st_ask, rec_cap=ask_cap, total_samples=tot_ask)
+            eng._check(eng._lib.tmk_ask_decode_batch(eng._h, C.c_void_p(d_ask), tot_ask, stp_ask, n_ask,
+                                                     h_arecs.ctypes.data_as(C.c_void_p), ask_cap, C.byref(n_arecs)))
+            return h_arecs[:int(n_arecs.value)]
         return np.zeros(0, tmkphy._abi.ASK_REC_DTYPE)
 
     for _ in range(warmup):
@@ -437,6 +444,8 @@ def c5_leg(eng, orc, tmkphy, rank, world, hbm, steps, warmup, n_total, n_per, th
                 n_chk += 1
         res["parity"] = "bit-exact" if ok else "MISMATCH"
         res["parity_sample"] = f"rank 0: {min(48, n_phy)} src/phy captures + {n_chk} chirp captures against the oracle"
+    if h_arecs is not None:
+        eng.pinned_free(h_arecs.ctypes.data)
     eng.device_free(d_x)
     return res
 

@@ -194,3 +194,19 @@ def test_ask_segmented_walk(engine, orc, seg_min):
             else:
                 os.environ[k] = v
     assert len(want) > 250
+
+
+def test_ask_misaligned_device_buffer_is_refused(engine):
+    """the filter and the power chain read 16 bytes at a time: a device pointer that is not 16-byte aligned is an argument
+    error, not a misaligned access"""
+    import tmkphy
+    d = engine.device_alloc(4 * 20000)
+    try:
+        st, total = tmkphy.make_streams([8000], tmkphy.make_config(1))
+        with pytest.raises(tmkphy.TmkError) as ei:
+            engine.ask_decode_batch(d + 4, st, total_samples=total)
+        assert ei.value.code == tmkphy._abi.E_INVALID
+        with pytest.raises(tmkphy.TmkError):
+            engine.mcm_decode_batch(1, d + 8, st, total_samples=total)
+    finally:
+        engine.device_free(d)

@@ -1126,6 +1126,7 @@ int tmk_ask_sync_device(tmk_engine* e, const float* samples, uint64_t total_samp
         CK(cudaMemcpyAsync(e->d_samples.p, samples, total_samples * sizeof(float), cudaMemcpyHostToDevice, e->stream));
         dx = static_cast<const float*>(e->d_samples.p);
     }
+    if (reinterpret_cast<uintptr_t>(dx) % 16 != 0) return tmk_fail(e, TMK_E_INVALID, "sample buffer must be 16-byte aligned");
     const size_t flag_words = size_t(words / 32 + 2);
     CK(e->d_streams.reserve(sizeof(AskStream) * n_streams));
     CK(e->d_ask_bits.reserve(flag_words * sizeof(uint32_t)));
