@@ -379,3 +379,27 @@ def test_exactly_sized_caller_buffers(engine, orc):
                 os.environ.pop("TMK_WALK_SEG_MIN", None)
             else:
                 os.environ["TMK_WALK_SEG_MIN"] = saved
+
+
+@pytest.mark.parametrize("kind", [FB, MAN])
+def test_frame_length_limits(engine, orc, kind):
+    """payload lengths on the limits of the length rule (decoder.rs:277-286): ACK with 0, DATA with 0 (refused), 1, 128
+    (what the encoder's callers send at most), 255, 256 (max_frame_bytes: still accepted), 257 and 300 (refused: consume 1
+    sample, the body is then searched for preambles), and a decoder configured with a smaller max_frame_bytes"""
+    import tmkphy
+    rng = np.random.default_rng(31 + kind)
+    lens = [(2, 0), (1, 0), (1, 1), (1, 128), (1, 255), (1, 256), (1, 257), (1, 300), (1, 7), (2, 5)]
+    frames = [(t, i, 9, 1, bytes(rng.integers(0, 256, n, dtype=np.uint8))) for i, (t, n) in enumerate(lens)]
+    for max_bytes, chunk in ((256, 0), (256, 1200), (64, 0), (300, 0)):
+        cfg = tmkphy.make_config(kind, local_addr=1, chunk=chunk)
+        cfg.max_frame_bytes = max_bytes
+        parts = [np.zeros(300, np.float32)]
+        for f in frames:
+            parts += [orc.modulate(cfg, [f], 0), np.zeros(int(rng.integers(60, 400)), np.float32)]
+        x = np.concatenate(parts)
+        caps = [x, (x + rng.normal(0, 0.15, len(x))).astype(np.float32)]
+        want = check_batch(engine, orc, caps, cfg, f"length limits kind={kind} max={max_bytes} chunk={chunk}")
+        ok = set(int(v) for v in want[(want["status"] == 0) & (want["stream"] == 0)]["len"])
+        assert {0, 1, 7, 5} <= ok and (128 in ok) == (max_bytes >= 128) and (256 in ok) == (max_bytes >= 256)
+        assert (300 in ok) == (max_bytes >= 300) and (257 in ok) == (max_bytes >= 257)
+        assert (want["status"] == 2).sum() >= (1 if max_bytes >= 300 else 3)  # BAD_LEN: DATA with len 0, frames beyond max_frame_bytes
