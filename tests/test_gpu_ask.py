@@ -210,3 +210,44 @@ def test_ask_misaligned_device_buffer_is_refused(engine):
             engine.mcm_decode_batch(1, d + 8, st, total_samples=total)
     finally:
         engine.device_free(d)
+
+
+def test_ask_power_brackets_withdrawn(engine, orc):
+    """the exact power chain is computed in parallel from brackets that start at a LOCAL bound (ask_power_kernel) and are
+    verified afterwards: captures built to break the local bound — a burst hundreds of times louder than what follows, a
+    NaN, an inf, a sample whose square overflows, long silence — must still give the serial receiver's records"""
+    import tmkphy
+    rng = np.random.default_rng(77)
+    fr = rng.integers(0, 2, (9, 100)).astype(np.uint8)
+    fr[:, :8] = [[((k + 1) >> (7 - j)) & 1 for j in range(8)] for k in range(9)]
+    base = orc.ask_modulate(fr, rng.integers(0, 600, 9), rng.integers(0, 600, 9))
+    noisy = impaired(rng, base, 20)
+    caps = []
+    for kind in range(8):
+        x = noisy.copy()
+        if kind == 0:
+            x[3000:3400] += rng.normal(0, 300.0, 400).astype(np.float32)      # a burst 300 x louder than the rest
+        elif kind == 1:
+            x = np.concatenate([rng.normal(0, 50.0, 9000).astype(np.float32), noisy * np.float32(0.02)])
+        elif kind == 2:
+            x[100] = np.nan
+        elif kind == 3:
+            x[20000] = np.inf
+        elif kind == 4:
+            x[7000] = np.float32(3e19)                                       # finite, its square is not
+        elif kind == 5:
+            x = np.concatenate([noisy, np.zeros(30000, np.float32), noisy])    # digital silence between two bursts of frames
+        elif kind == 6:
+            x[9000] = np.float32(-2e19)
+            x = np.concatenate([x, noisy])
+        caps.append(x.astype(np.float32))
+    st, total = tmkphy.make_streams([len(c) for c in caps], tmkphy.make_config(1))
+    buf = np.zeros(total, np.float32)
+    for c, t in zip(caps, st):
+        buf[int(t["offset"]):int(t["offset"]) + len(c)] = c
+    with np.errstate(all="ignore"):
+        want = oracle_batch(orc, buf, st)
+    got = engine.ask_decode_batch(buf, st)
+    assert_ask_equal(got, want, "withdrawn brackets")
+    per = [int((want["stream"] == i).sum()) for i in range(8)]
+    assert per[7] == 9 and per[5] == 18 and per[2] == 0 and per[0] >= 5, per

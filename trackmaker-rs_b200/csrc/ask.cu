@@ -456,8 +456,8 @@ ask_scan_fft_kernel(const float* __restrict__ samples, const AskStream* __restri
 // The step is MONOTONE in p (every rounding is), and it contracts: two chains fed with the same samples, one started
 // BELOW the reference's value and one ABOVE it, keep the reference's chain between them and approach each other by 63/64
 // per step until they land on the same float — from there on both ARE the reference's chain, bit for bit. So a thread
-// owns a segment of kSeg samples, starts kWarm samples before it from 0 and from 1.001 xmax^2 + 1e-30 (xmax = the largest
-// |x| of the whole capture: the exact chain never exceeds xmax^2 (1 + 130 u)), and stores the power at every 32-sample
+// owns a segment of kSeg samples, starts kWarm samples before it from 0 and from a value that is not below the reference's
+// power there (see ask_power_kernel), and stores the power at every 32-sample
 // word boundary of its segment once the two have met (-1 = not known: digital silence, where 0 and the decayed upper
 // chain sit on different subnormal fixed points, the first ~1500 samples after it, NaN / inf captures — the walk then
 // runs the chain literally from its last exact position, as before). The walk reads the checkpoints instead of chaining
@@ -472,34 +472,23 @@ __device__ __forceinline__ uint32_t seg_stream(const AskStream* __restrict__ str
     return lo;
 }
 
-// largest |x| of every capture, as the bit pattern of the float (NaN > inf > finite): one warp per segment
-__global__ void __launch_bounds__(256)
-ask_xmax_kernel(const float* __restrict__ samples, const AskStream* __restrict__ streams, uint32_t n_streams, uint32_t seg0, uint32_t n_segs,
-                uint32_t* __restrict__ xmax_bits) {
-    const uint32_t seg = seg0 + blockIdx.x * 8 + (threadIdx.x >> 5);  // segments [seg0, n_segs) of the batch
-    if (seg >= n_segs) return;
-    const int lane = threadIdx.x & 31;
-    const uint32_t si = seg_stream(streams, n_streams, seg);
-    const AskStream sd = streams[si];
-    const int64_t lo = int64_t(seg - sd.seg_base) * kSeg, hi = min(lo + int64_t(kSeg), int64_t(sd.n));
-    const float* __restrict__ x = samples + sd.offset;
-    uint32_t m = 0;
-    for (int64_t i = lo + 4 * lane; i < hi; i += 128) {
-        if (i + 4 <= hi) {
-            const float4 v = *reinterpret_cast<const float4*>(x + i);
-            m = max(max(m, __float_as_uint(v.x) & 0x7fffffffu), max(__float_as_uint(v.y) & 0x7fffffffu,
-                    max(__float_as_uint(v.z) & 0x7fffffffu, __float_as_uint(v.w) & 0x7fffffffu)));
-        } else {
-            for (int64_t k = i; k < hi; ++k) m = max(m, __float_as_uint(x[k]) & 0x7fffffffu);
-        }
-    }
-    m = __reduce_max_sync(kFull, m);
-    if (lane == 0 && m) atomicMax(xmax_bits + si, m);
-}
+// The upper chain needs a value that is certainly not below the reference's power where it starts. The power is a convex
+// combination of the squares of ALL earlier samples (p = sum_j w_j x_j^2, sum w_j <= 1; with roundings: <= (1 + 130 u) max),
+// so max x^2 over everything before would do — but that is one more pass over the samples (round 2 first had it:
+// ask_xmax_kernel, 1.2 ms at C2, 7.9 GB). Instead the thread looks at the kBound samples in front of its bracket, starts the
+// upper chain from kHead x their largest square, and ask_power_check_kernel verifies the assumption afterwards from the
+// segments' own maxima (which the threads record as they go): the power at the bracket's start is at most
+//   1.0002 (M_{k-1} + c^6144 M_{k-2} + c^14336 max_{j <= k-3} M_j),   M_j = the largest square in segment j, c = 63/64,
+// (segment k-1 holds the bracket; c^6144 = 6.2e-43; the last term is below 1e-58 for finite samples) — if that exceeds the
+// start value, or any earlier segment holds a NaN / inf (the reference's power is then NaN / inf for good), the segment's
+// checkpoints are withdrawn (-1: the walk chains literally there, the filter reads 0). A segment whose surroundings are more
+// than sqrt(kHead) = 8 x louder than the 512 samples in front of its bracket is the only one that pays.
+constexpr int kBound = 512;        // samples in front of the bracket whose maximum gives the start value of the upper chain
+constexpr float kHead = 64.0f;     // head room of that start value (64 x: ~260 more steps until the chains meet)
 
 __global__ void __launch_bounds__(128)
 ask_power_kernel(const float* __restrict__ samples, const AskStream* __restrict__ streams, uint32_t n_streams, uint32_t seg0, uint32_t n_segs,
-                 const uint32_t* __restrict__ xmax_bits, float* __restrict__ pchk) {
+                 float* __restrict__ pchk, uint32_t* __restrict__ seg_max, float* __restrict__ seg_u0, uint32_t* __restrict__ first_bad) {
     const uint32_t seg = seg0 + blockIdx.x * blockDim.x + threadIdx.x;
     if (seg >= n_segs) return;
     const uint32_t si = seg_stream(streams, n_streams, seg);
@@ -511,15 +500,26 @@ ask_power_kernel(const float* __restrict__ samples, const AskStream* __restrict_
     int64_t pos = s0 - kWarm;
     float pl = 0.0f, pu;
     bool merged;
-    if (pos <= 0) {  // the chain's own start: exact
+    if (pos - kBound <= 0) {  // the chain's own start: exact
         pos = 0;
         pu = 0.0f;
         merged = true;
+        seg_u0[seg] = -1.0f;  // nothing to verify
     } else {
-        const float xm = __uint_as_float(xmax_bits[si]);
-        pu = __fmaf_rn(1.001f, __fmul_rn(xm, xm), 1e-30f);  // inf / NaN captures never merge
+        uint32_t mb = 0;
+        const float4* __restrict__ xb = reinterpret_cast<const float4*>(x + pos - kBound);
+#pragma unroll 8
+        for (int k = 0; k < kBound / 4; ++k) {
+            const float4 v = __ldg(xb + k);
+            mb = max(max(mb, __float_as_uint(v.x) & 0x7fffffffu), max(__float_as_uint(v.y) & 0x7fffffffu,
+                     max(__float_as_uint(v.z) & 0x7fffffffu, __float_as_uint(v.w) & 0x7fffffffu)));
+        }
+        const float xm = __uint_as_float(mb);
+        pu = __fmaf_rn(kHead * 1.001f, __fmul_rn(xm, xm), 1e-30f);  // (inf / NaN: the chains never meet)
         merged = false;
+        seg_u0[seg] = pu;
     }
+    uint32_t smax = 0;  // largest |x| of the segment's own samples, as float bits (NaN > inf > finite)
     // a word (32 samples) per round: eight 16-byte loads, then the chain(s) over them; pos, s0 are multiples of 32. The next
     // word's loads are issued before the chain of the current one runs (the kernel is bound by the latency of its strided loads)
     float4 nx[8];
@@ -538,6 +538,12 @@ ask_power_kernel(const float* __restrict__ samples, const AskStream* __restrict_
 #pragma unroll
         for (int k = 0; k < 8; ++k) v[k] = nx[k];
         fetch(pos + 32);
+        if (pos >= s0) {
+#pragma unroll
+            for (int k = 0; k < 8; ++k)
+                smax = max(max(smax, __float_as_uint(v[k].x) & 0x7fffffffu), max(__float_as_uint(v[k].y) & 0x7fffffffu,
+                           max(__float_as_uint(v[k].z) & 0x7fffffffu, __float_as_uint(v[k].w) & 0x7fffffffu)));
+        }
         if (merged) {
 #pragma unroll
             for (int k = 0; k < 8; ++k) {
@@ -563,6 +569,35 @@ ask_power_kernel(const float* __restrict__ samples, const AskStream* __restrict_
         }
         pos += 32;
     }
+    for (int64_t i = max(pos, s0); i < s1; ++i) smax = max(smax, __float_as_uint(x[i]) & 0x7fffffffu);  // the capture's partial last word
+    seg_max[seg] = smax;
+    // NaN / inf, or a sample whose square overflows (the reference's power is inf from there on): nothing behind it can be bracketed
+    if (smax >= 0x5d5e0b6bu /* 1e18f */) atomicMin(first_bad + si, seg - sd.seg_base);
+}
+
+// see above: withdraws the checkpoints of the segments whose upper chain may have started too low
+__global__ void __launch_bounds__(128)
+ask_power_check_kernel(const AskStream* __restrict__ streams, uint32_t n_streams, uint32_t seg0, uint32_t n_segs,
+                       const uint32_t* __restrict__ seg_max, const float* __restrict__ seg_u0, const uint32_t* __restrict__ first_bad,
+                       float* __restrict__ pchk) {
+    const uint32_t seg = seg0 + blockIdx.x * blockDim.x + threadIdx.x;
+    if (seg >= n_segs) return;
+    const float u0 = seg_u0[seg];
+    if (u0 < 0.0f) return;  // started at the capture's first sample
+    const uint32_t si = seg_stream(streams, n_streams, seg);
+    const AskStream sd = streams[si];
+    const uint32_t k = seg - sd.seg_base;  // >= 1 here
+    bool ok = first_bad[si] >= k;          // no NaN / inf / overflowing square in the segments before this one
+    if (ok) {
+        const double m1 = double(__uint_as_float(seg_max[seg - 1]));
+        const double m2 = k >= 2 ? double(__uint_as_float(seg_max[seg - 2])) : 0.0;
+        const double bound = 1.0002 * (m1 * m1 + 6.3e-43 * m2 * m2) + 1e-40;  // (older segments: below 1e-58 for finite samples)
+        ok = bound <= double(u0);
+    }
+    if (ok) return;
+    const int64_t s0 = int64_t(k) * kSeg, s1 = min(s0 + int64_t(kSeg), int64_t(sd.n));
+    float* __restrict__ chk = pchk + sd.word_base;
+    for (int64_t w = s0 >> 5; w * 32 < s1; ++w) chk[w] = -1.0f;
 }
 
 // ---------------------------------------------------------------- walk
@@ -1150,12 +1185,15 @@ int tmk_ask_sync_device(tmk_engine* e, const float* samples, uint64_t total_samp
     // the filter: tensor-core Toeplitz GEMM (ask_tc.cu) | TMK_ASK_FFT=1: FFT fast correlation | TMK_ASK_DIRECT=1: direct form
     static const bool use_fft = getenv("TMK_ASK_FFT") != nullptr;
     float* pchk = nullptr;
-    uint32_t* xmax = nullptr;
+    uint32_t *seg_max = nullptr, *first_bad = nullptr;
+    float* seg_u0 = nullptr;
     if (!no_chk && segs) {
-        CK(e->d_ask_chk.reserve((words + 2) * sizeof(float) + sizeof(uint32_t) * n_streams));
+        CK(e->d_ask_chk.reserve((words + 2) * sizeof(float) + sizeof(uint32_t) * (2 * segs + n_streams)));
         pchk = static_cast<float*>(e->d_ask_chk.p);
-        xmax = reinterpret_cast<uint32_t*>(pchk + words + 2);
-        CK(cudaMemsetAsync(xmax, 0, sizeof(uint32_t) * n_streams, e->stream));
+        seg_max = reinterpret_cast<uint32_t*>(pchk + words + 2);
+        seg_u0 = reinterpret_cast<float*>(seg_max + segs);
+        first_bad = reinterpret_cast<uint32_t*>(seg_u0 + segs);
+        CK(cudaMemsetAsync(first_bad, 0xff, sizeof(uint32_t) * n_streams, e->stream));
     }
     const bool tc = pchk != nullptr && !use_fft && !direct;
     std::vector<uint32_t> tc_base(size_t(n_streams) + 1, 0);
@@ -1267,8 +1305,8 @@ int tmk_ask_sync_device(tmk_engine* e, const float* samples, uint64_t total_samp
         if (pchk != nullptr) {
             const uint32_t g0 = sd[s0].seg_base, g1 = s1 < n_streams ? sd[s1].seg_base : uint32_t(segs);
             if (g1 > g0) {
-                ask_xmax_kernel<<<(g1 - g0 + 7) / 8, 256, 0, st>>>(dx, ds, n_streams, g0, g1, xmax);
-                ask_power_kernel<<<(g1 - g0 + 127) / 128, 128, 0, st>>>(dx, ds, n_streams, g0, g1, xmax, pchk);
+                ask_power_kernel<<<(g1 - g0 + 127) / 128, 128, 0, st>>>(dx, ds, n_streams, g0, g1, pchk, seg_max, seg_u0, first_bad);
+                ask_power_check_kernel<<<(g1 - g0 + 127) / 128, 128, 0, st>>>(ds, n_streams, g0, g1, seg_max, seg_u0, first_bad, pchk);
                 e->launches += 2;
             }
         }
