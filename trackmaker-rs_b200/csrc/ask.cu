@@ -462,7 +462,10 @@ ask_scan_fft_kernel(const float* __restrict__ samples, const AskStream* __restri
 // chain sit on different subnormal fixed points, the first ~1500 samples after it, NaN / inf captures — the walk then
 // runs the chain literally from its last exact position, as before). The walk reads the checkpoints instead of chaining
 // through every sample of every capture with 32 lanes computing one scalar.
-constexpr int kSeg = 8192, kWarm = 2048;
+#ifndef TMK_PW_SEG
+#define TMK_PW_SEG 8192
+#endif
+constexpr int kSeg = TMK_PW_SEG, kWarm = 2048;
 __device__ __forceinline__ uint32_t seg_stream(const AskStream* __restrict__ streams, uint32_t n_streams, uint32_t seg) {
     uint32_t lo = 0, hi = n_streams - 1;
     while (lo < hi) {
@@ -486,93 +489,161 @@ __device__ __forceinline__ uint32_t seg_stream(const AskStream* __restrict__ str
 constexpr int kBound = 512;        // samples in front of the bracket whose maximum gives the start value of the upper chain
 constexpr float kHead = 64.0f;     // head room of that start value (64 x: ~260 more steps until the chains meet)
 
-__global__ void __launch_bounds__(128)
+// Staging: a lane owns a segment, so the lanes of a warp read 32 KB apart — as plain loads that is 32 cache lines per request
+// (2.9 ms at C2: bound by the L1 tag rate of fully divergent requests, DRAM at 52 %). Instead every lane moves ITS OWN next
+// 512 bytes into shared memory with one bulk copy (cp.async.bulk, completion on the warp's mbarrier of that stage; rows
+// 528 bytes apart so that the lanes' 16-byte reads fall on different bank groups) while the warp runs the chains over the
+// previous stage: no register staging, no L1, a lane never touches another lane's row.
+#ifndef TMK_PW_CHUNK
+#define TMK_PW_CHUNK 128
+#define TMK_PW_STAGES 2
+#define TMK_PW_WARPS 2
+#endif
+constexpr int kPwChunk = TMK_PW_CHUNK;            // samples per lane and stage
+constexpr int kPwPitch = kPwChunk * 4 + 16;       // bytes between the rows of two lanes
+constexpr int kPwStages = TMK_PW_STAGES;
+constexpr int kPwWarps = TMK_PW_WARPS;
+constexpr int kPwRounds = (kBound + kWarm + kSeg) / kPwChunk;
+constexpr int kPwSmem = kPwWarps * kPwStages * 32 * kPwPitch;
+static_assert((kBound + kWarm) % kPwChunk == 0 && kSeg % kPwChunk == 0, "rounds are whole chunks");
+
+__device__ __forceinline__ uint32_t pw_smem_u32(const void* p) { return uint32_t(__cvta_generic_to_shared(p)); }
+
+__global__ void __launch_bounds__(kPwWarps * 32)
 ask_power_kernel(const float* __restrict__ samples, const AskStream* __restrict__ streams, uint32_t n_streams, uint32_t seg0, uint32_t n_segs,
                  float* __restrict__ pchk, uint32_t* __restrict__ seg_max, float* __restrict__ seg_u0, uint32_t* __restrict__ first_bad) {
-    const uint32_t seg = seg0 + blockIdx.x * blockDim.x + threadIdx.x;
-    if (seg >= n_segs) return;
-    const uint32_t si = seg_stream(streams, n_streams, seg);
-    const AskStream sd = streams[si];
-    const int64_t n = int64_t(sd.n);
-    const int64_t s0 = int64_t(seg - sd.seg_base) * kSeg, s1 = min(s0 + int64_t(kSeg), n);
-    const float* __restrict__ x = samples + sd.offset;
-    float* __restrict__ chk = pchk + sd.word_base;  // chk[w] = power BEFORE sample 32 w
-    int64_t pos = s0 - kWarm;
-    float pl = 0.0f, pu;
-    bool merged;
-    if (pos - kBound <= 0) {  // the chain's own start: exact
-        pos = 0;
-        pu = 0.0f;
-        merged = true;
-        seg_u0[seg] = -1.0f;  // nothing to verify
-    } else {
-        uint32_t mb = 0;
-        const float4* __restrict__ xb = reinterpret_cast<const float4*>(x + pos - kBound);
-#pragma unroll 8
-        for (int k = 0; k < kBound / 4; ++k) {
-            const float4 v = __ldg(xb + k);
-            mb = max(max(mb, __float_as_uint(v.x) & 0x7fffffffu), max(__float_as_uint(v.y) & 0x7fffffffu,
-                     max(__float_as_uint(v.z) & 0x7fffffffu, __float_as_uint(v.w) & 0x7fffffffu)));
-        }
-        const float xm = __uint_as_float(mb);
-        pu = __fmaf_rn(kHead * 1.001f, __fmul_rn(xm, xm), 1e-30f);  // (inf / NaN: the chains never meet)
-        merged = false;
-        seg_u0[seg] = pu;
+    extern __shared__ __align__(128) unsigned char pw_rows[];
+    __shared__ __align__(8) uint64_t pw_bar[kPwWarps][kPwStages];
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    if (lane == 0) {
+        for (int s = 0; s < kPwStages; ++s)
+            asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(pw_smem_u32(&pw_bar[warp][s])), "r"(32) : "memory");
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
-    uint32_t smax = 0;  // largest |x| of the segment's own samples, as float bits (NaN > inf > finite)
-    // a word (32 samples) per round: eight 16-byte loads, then the chain(s) over them; pos, s0 are multiples of 32. The next
-    // word's loads are issued before the chain of the current one runs (the kernel is bound by the latency of its strided loads)
-    float4 nx[8];
-    auto fetch = [&](int64_t at) {
-        if (at < s1 && at + 32 <= n) {
-#pragma unroll
-            for (int k = 0; k < 8; ++k) nx[k] = __ldg(reinterpret_cast<const float4*>(x + at) + k);
-        }
+    __syncthreads();
+    const uint32_t seg = seg0 + (blockIdx.x * kPwWarps + warp) * 32 + lane;
+    const bool live = seg < n_segs;
+    uint32_t si = 0;
+    int64_t n = 0, s0 = 0, s1 = 0, e = 0;
+    const float* __restrict__ x = samples;
+    float* __restrict__ chk = pchk;
+    uint32_t seg_in = 0;
+    if (live) {
+        si = seg_stream(streams, n_streams, seg);
+        const AskStream sd = streams[si];
+        n = int64_t(sd.n);
+        seg_in = seg - sd.seg_base;
+        s0 = int64_t(seg_in) * kSeg;
+        s1 = min(s0 + int64_t(kSeg), n);
+        e = min(s0 + int64_t(kSeg), n & ~int64_t(31));  // end of the whole words: the chain runs over [.., e)
+        x = samples + sd.offset;
+        chk = pchk + sd.word_base;  // chk[w] = power BEFORE sample 32 w
+    }
+    const int64_t base = s0 - (kWarm + kBound);  // first sample of round 0
+    const bool first = base <= 0;                // the chain's own start: exact from sample 0, nothing in front of it
+    unsigned char* const my_rows = pw_rows + size_t(warp) * (kPwStages * 32 * kPwPitch) + size_t(lane) * kPwPitch;
+    auto issue = [&](int r) {
+        const int st = r % kPwStages;
+        const int64_t a = base + int64_t(r) * kPwChunk;
+        int64_t cnt = min(int64_t(kPwChunk), e - a);
+        if (!live || a < 0 || cnt < 0) cnt = 0;
+        const uint32_t bytes = uint32_t(cnt) * 4u, bar = pw_smem_u32(&pw_bar[warp][st]);
+        asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
+        if (bytes)
+            asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(
+                             pw_smem_u32(my_rows + size_t(st) * (32 * kPwPitch))),
+                         "l"(x + a), "r"(bytes), "r"(bar)
+                         : "memory");
+        return int(cnt >> 5);  // whole words of this round
     };
-    fetch(pos);
-    while (pos < s1) {
-        if (!merged) merged = pl == pu;
-        if (pos >= s0) chk[pos >> 5] = merged ? pl : -1.0f;
-        if (pos + 32 > n) break;  // the partial last word of the capture: nobody reads behind its checkpoint
-        float4 v[8];
+    float pl = 0.0f, pu = 0.0f;
+    bool merged = first;
+    uint32_t mb = 0;    // largest |x| of the kBound samples in front of the bracket
+    uint32_t smax = 0;  // largest |x| of the segment's own samples, as float bits (NaN > inf > finite)
+    if (live && first) seg_u0[seg] = -1.0f;  // nothing to verify
+    int words[kPwStages];
 #pragma unroll
-        for (int k = 0; k < 8; ++k) v[k] = nx[k];
-        fetch(pos + 32);
-        if (pos >= s0) {
+    for (int r = 0; r < kPwStages - 1; ++r) words[r] = issue(r);
+#pragma unroll 1
+    for (int r0 = 0; r0 < kPwRounds; r0 += kPwStages) {
 #pragma unroll
-            for (int k = 0; k < 8; ++k)
-                smax = max(max(smax, __float_as_uint(v[k].x) & 0x7fffffffu), max(__float_as_uint(v[k].y) & 0x7fffffffu,
-                           max(__float_as_uint(v[k].z) & 0x7fffffffu, __float_as_uint(v[k].w) & 0x7fffffffu)));
-        }
-        if (merged) {
-#pragma unroll
-            for (int k = 0; k < 8; ++k) {
-                pl = __fadd_rn(__fmul_rn(pl, kC), __fmul_rn(__fmul_rn(v[k].x, v[k].x), kInv64));
-                pl = __fadd_rn(__fmul_rn(pl, kC), __fmul_rn(__fmul_rn(v[k].y, v[k].y), kInv64));
-                pl = __fadd_rn(__fmul_rn(pl, kC), __fmul_rn(__fmul_rn(v[k].z, v[k].z), kInv64));
-                pl = __fadd_rn(__fmul_rn(pl, kC), __fmul_rn(__fmul_rn(v[k].w, v[k].w), kInv64));
+        for (int k = 0; k < kPwStages; ++k) {
+            const int r = r0 + k;
+            if (r >= kPwRounds) break;
+            if (r + kPwStages - 1 < kPwRounds) words[(k + kPwStages - 1) % kPwStages] = issue(r + kPwStages - 1);
+            {
+                const uint32_t bar = pw_smem_u32(&pw_bar[warp][k]), parity = uint32_t(r0 / kPwStages) & 1u;
+                asm volatile(
+                    "{\n.reg .pred p;\nWAIT_%=:\nmbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n@p bra DONE_%=;\nbra WAIT_%=;\nDONE_%=:\n}\n" ::"r"(bar),
+                    "r"(parity)
+                    : "memory");
             }
-        } else {
+            const int64_t a = base + int64_t(r) * kPwChunk;
+            const float4* __restrict__ row = reinterpret_cast<const float4*>(my_rows + size_t(k) * (32 * kPwPitch));
+            const int nw = words[k];
+            const bool both = !__all_sync(0xffffffffu, merged || nw == 0);
+            for (int w = 0; w < nw; ++w) {
+                const int64_t pos = a + 32 * w;
+                float4 v[8];
 #pragma unroll
-            for (int k = 0; k < 8; ++k) {
-                const float q0 = __fmul_rn(__fmul_rn(v[k].x, v[k].x), kInv64), q1 = __fmul_rn(__fmul_rn(v[k].y, v[k].y), kInv64);
-                const float q2 = __fmul_rn(__fmul_rn(v[k].z, v[k].z), kInv64), q3 = __fmul_rn(__fmul_rn(v[k].w, v[k].w), kInv64);
-                pl = __fadd_rn(__fmul_rn(pl, kC), q0);
-                pu = __fadd_rn(__fmul_rn(pu, kC), q0);
-                pl = __fadd_rn(__fmul_rn(pl, kC), q1);
-                pu = __fadd_rn(__fmul_rn(pu, kC), q1);
-                pl = __fadd_rn(__fmul_rn(pl, kC), q2);
-                pu = __fadd_rn(__fmul_rn(pu, kC), q2);
-                pl = __fadd_rn(__fmul_rn(pl, kC), q3);
-                pu = __fadd_rn(__fmul_rn(pu, kC), q3);
+                for (int j = 0; j < 8; ++j) v[j] = row[w * 8 + j];
+                if (!first && pos < base + kBound) {  // in front of the bracket: only the maximum
+#pragma unroll
+                    for (int j = 0; j < 8; ++j)
+                        mb = max(max(mb, __float_as_uint(v[j].x) & 0x7fffffffu), max(__float_as_uint(v[j].y) & 0x7fffffffu,
+                                 max(__float_as_uint(v[j].z) & 0x7fffffffu, __float_as_uint(v[j].w) & 0x7fffffffu)));
+                    continue;
+                }
+                if (!first && pos == base + kBound) {  // the bracket opens
+                    const float xm = __uint_as_float(mb);
+                    pu = __fmaf_rn(kHead * 1.001f, __fmul_rn(xm, xm), 1e-30f);  // (inf / NaN: the chains never meet)
+                    seg_u0[seg] = pu;
+                }
+                if (!merged) merged = pl == pu;
+                if (pos >= s0) {
+                    chk[pos >> 5] = merged ? pl : -1.0f;
+#pragma unroll
+                    for (int j = 0; j < 8; ++j)
+                        smax = max(max(smax, __float_as_uint(v[j].x) & 0x7fffffffu), max(__float_as_uint(v[j].y) & 0x7fffffffu,
+                                   max(__float_as_uint(v[j].z) & 0x7fffffffu, __float_as_uint(v[j].w) & 0x7fffffffu)));
+                }
+                if (!both) {
+#pragma unroll
+                    for (int j = 0; j < 8; ++j) {
+                        pl = __fadd_rn(__fmul_rn(pl, kC), __fmul_rn(__fmul_rn(v[j].x, v[j].x), kInv64));
+                        pl = __fadd_rn(__fmul_rn(pl, kC), __fmul_rn(__fmul_rn(v[j].y, v[j].y), kInv64));
+                        pl = __fadd_rn(__fmul_rn(pl, kC), __fmul_rn(__fmul_rn(v[j].z, v[j].z), kInv64));
+                        pl = __fadd_rn(__fmul_rn(pl, kC), __fmul_rn(__fmul_rn(v[j].w, v[j].w), kInv64));
+                    }
+                    pu = pl;  // (all lanes of the warp have met)
+                } else {
+#pragma unroll
+                    for (int j = 0; j < 8; ++j) {
+                        const float q0 = __fmul_rn(__fmul_rn(v[j].x, v[j].x), kInv64), q1 = __fmul_rn(__fmul_rn(v[j].y, v[j].y), kInv64);
+                        const float q2 = __fmul_rn(__fmul_rn(v[j].z, v[j].z), kInv64), q3 = __fmul_rn(__fmul_rn(v[j].w, v[j].w), kInv64);
+                        pl = __fadd_rn(__fmul_rn(pl, kC), q0);
+                        pu = __fadd_rn(__fmul_rn(pu, kC), q0);
+                        pl = __fadd_rn(__fmul_rn(pl, kC), q1);
+                        pu = __fadd_rn(__fmul_rn(pu, kC), q1);
+                        pl = __fadd_rn(__fmul_rn(pl, kC), q2);
+                        pu = __fadd_rn(__fmul_rn(pu, kC), q2);
+                        pl = __fadd_rn(__fmul_rn(pl, kC), q3);
+                        pu = __fadd_rn(__fmul_rn(pu, kC), q3);
+                    }
+                }
             }
+            __syncwarp();
         }
-        pos += 32;
     }
-    for (int64_t i = max(pos, s0); i < s1; ++i) smax = max(smax, __float_as_uint(x[i]) & 0x7fffffffu);  // the capture's partial last word
+    if (!live) return;
+    if (e < s1) {  // the capture's partial last word: its checkpoint, and its samples for the maximum
+        if (!merged) merged = pl == pu;
+        chk[e >> 5] = merged ? pl : -1.0f;
+        for (int64_t i = e; i < s1; ++i) smax = max(smax, __float_as_uint(x[i]) & 0x7fffffffu);
+    }
     seg_max[seg] = smax;
     // NaN / inf, or a sample whose square overflows (the reference's power is inf from there on): nothing behind it can be bracketed
-    if (smax >= 0x5d5e0b6bu /* 1e18f */) atomicMin(first_bad + si, seg - sd.seg_base);
+    if (smax >= 0x5d5e0b6bu /* 1e18f */) atomicMin(first_bad + si, seg_in);
 }
 
 // see above: withdraws the checkpoints of the segments whose upper chain may have started too low
@@ -1305,7 +1376,8 @@ int tmk_ask_sync_device(tmk_engine* e, const float* samples, uint64_t total_samp
         if (pchk != nullptr) {
             const uint32_t g0 = sd[s0].seg_base, g1 = s1 < n_streams ? sd[s1].seg_base : uint32_t(segs);
             if (g1 > g0) {
-                ask_power_kernel<<<(g1 - g0 + 127) / 128, 128, 0, st>>>(dx, ds, n_streams, g0, g1, pchk, seg_max, seg_u0, first_bad);
+                CK(cudaFuncSetAttribute(ask_power_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kPwSmem));  // (per device: no static flag)
+                ask_power_kernel<<<(g1 - g0 + kPwWarps * 32 - 1) / (kPwWarps * 32), kPwWarps * 32, kPwSmem, st>>>(dx, ds, n_streams, g0, g1, pchk, seg_max, seg_u0, first_bad);
                 ask_power_check_kernel<<<(g1 - g0 + 127) / 128, 128, 0, st>>>(ds, n_streams, g0, g1, seg_max, seg_u0, first_bad, pchk);
                 e->launches += 2;
             }
