@@ -205,6 +205,9 @@ void tmk_engine_destroy(tmk_engine* e) {
                       &e->d_ask_tab, &e->d_ask_bits, &e->d_ask_l2,
                       &e->d_ask_recs, &e->d_ask_recs2, &e->d_ask_chk, &e->d_ask_tc, &e->d_ask_seg, &e->d_seg, &e->d_mcm_tab, &e->d_mcm_recs, &e->d_mcm_off};
     for (DevBuf* b : bufs) b->release();
+    e->d_small.release();
+    if (e->h_small) cudaFreeHost(e->h_small);
+    e->h_small = nullptr;
     for (int i = 0; i < 6; ++i)
         if (e->ev[i]) cudaEventDestroy(e->ev[i]);
     for (int i = 0; i < 2; ++i)
@@ -464,6 +467,7 @@ static int decode_batch_impl(tmk_engine* e, const void* samples_v, bool pcm16, u
     uint32_t* dcb = static_cast<uint32_t*>(e->d_cand.p);
     TmkCounters* dc = static_cast<TmkCounters*>(e->d_counters.p);
     unsigned int* dnext = static_cast<unsigned int*>(e->d_next.p);
+    unsigned int* dpool = use_fast ? static_cast<unsigned int*>(e->d_pool.p) : nullptr;
 
     if (reinterpret_cast<uintptr_t>(dx) % 16 != 0) return fail(e, TMK_E_INVALID, "sample buffer must be 16-byte aligned");
     CK(e->d_tile_dir.reserve(sizeof(uint32_t) * std::max<uint64_t>(1, b.n_tiles)));
@@ -481,14 +485,50 @@ static int decode_batch_impl(tmk_engine* e, const void* samples_v, bool pcm16, u
     uint64_t dev_pay_cap = pay_dev ? payload_cap : std::min<uint64_t>(payload_cap, std::max<uint64_t>(65536, total_samples / 24));
     CK(e->d_recs_tmp.reserve(sizeof(tmk_frame_rec) * std::max<uint64_t>(1, dev_rec_cap)));
     CK(e->d_rec_ord.reserve(sizeof(uint4) * std::max<uint64_t>(1, dev_rec_cap)));
-    if (!pay_dev) CK(e->d_payload.reserve(std::max<uint64_t>(1, dev_pay_cap)));
+    // Small batches (the links' polls, single captures): counters, exit states, ordered records and payload are gathered in ONE
+    // device block and reach pinned host memory with ONE copy before ONE synchronisation. The general path below needs the
+    // counts on the host before it can size its copies: two synchronisations and five copies into pageable memory, each of
+    // which the host waits for — ~100 us of a 260 us poll of 256 links.
+    struct SmallHdr {
+        TmkCounters hc;
+        uint64_t n_exact;
+        unsigned int next[4];
+        unsigned int pool[4];
+    };
+    const uint64_t r_spec = dev_rec_cap - kSlotSlack;  // records the block has room for (= the caller's capacity, or the guess)
+    const bool small = chunks.size() == 1 && !seg_mode && !recs_dev && !pay_dev && r_spec <= 8192 && dev_pay_cap <= (512u << 10) &&
+                       n_streams <= 16384 && !getenv("TMK_NO_SMALL_PATH");
+    const size_t sm_link = (sizeof(SmallHdr) + 15) & ~size_t(15);
+    const size_t sm_recs = (sm_link + (link_final ? sizeof(TmkLinkState) * n_streams : 0) + 15) & ~size_t(15);
+    const size_t sm_pay = (sm_recs + sizeof(tmk_frame_rec) * r_spec + 15) & ~size_t(15);
+    const size_t sm_bytes = sm_pay + dev_pay_cap;
+    char* sm = nullptr;
+    if (small) {
+        CK(e->d_small.reserve(sm_bytes));
+        if (e->h_small_cap < sm_bytes) {
+            if (e->h_small) cudaFreeHost(e->h_small);
+            e->h_small = nullptr;
+            e->h_small_cap = 0;
+            CK(cudaHostAlloc(&e->h_small, sm_bytes + sm_bytes / 4, cudaHostAllocDefault));
+            e->h_small_cap = sm_bytes + sm_bytes / 4;
+        }
+        sm = static_cast<char*>(e->d_small.p);
+        SmallHdr* hdr = reinterpret_cast<SmallHdr*>(sm);
+        dc = &hdr->hc;
+        dnext = hdr->next;
+        if (use_fast) dpool = hdr->pool;
+        if (link_final) d_link = reinterpret_cast<TmkLinkState*>(sm + sm_link);
+    } else if (!pay_dev) {
+        CK(e->d_payload.reserve(std::max<uint64_t>(1, dev_pay_cap)));
+    }
+    uint8_t* dpay_cur = pay_dev ? payload : small ? reinterpret_cast<uint8_t*>(sm + sm_pay) : static_cast<uint8_t*>(e->d_payload.p);
     uint64_t spec_cap = std::min<uint64_t>(0x7fffffffull, 2 * dev_rec_cap + 1024);
     if (use_fast) CK(e->d_spec.reserve(sizeof(tmk_frame_rec) * spec_cap));
     auto fast_of = [&](size_t g, const Chunk& ch) {
         TmkFast f;
         std::memset(&f, 0, sizeof f);
         if (!use_fast) return f;
-        unsigned int* pool = static_cast<unsigned int*>(e->d_pool.p);
+        unsigned int* pool = dpool;
         f.cblk_list = static_cast<uint32_t*>(e->d_cblk.p) + uint64_t(ch.t0) * TMK_TILE_BLKS;
         f.cblk_count = pool + 2 + g;
         f.item_next = pool + 2 + chunks.size() + g;
@@ -506,10 +546,12 @@ static int decode_batch_impl(tmk_engine* e, const void* samples_v, bool pcm16, u
 #ifdef TMK_SCAN_ARM_A
     CK(cudaMemsetAsync(dcb, 0, sizeof(uint32_t) * TMK_BLK_WORDS * b.n_blocks, e->stream));  // (the CUDA-core scan ORs its bits in)
 #endif
-    CK(cudaMemsetAsync(dc, 0, sizeof(TmkCounters), e->stream));
-    CK(cudaMemsetAsync(dnext, 0, sizeof(unsigned int) * (2 * chunks.size() + 1), e->stream));
-    if (use_fast) {
-        CK(cudaMemsetAsync(e->d_pool.p, 0, sizeof(unsigned int) * (2 + 2 * chunks.size()), e->stream));
+    if (small) {
+        CK(cudaMemsetAsync(sm, 0, sizeof(SmallHdr), e->stream));  // counters, work counters and list heads in one go
+    } else {
+        CK(cudaMemsetAsync(dc, 0, sizeof(TmkCounters), e->stream));
+        CK(cudaMemsetAsync(dnext, 0, sizeof(unsigned int) * (2 * chunks.size() + 1), e->stream));
+        if (use_fast) CK(cudaMemsetAsync(dpool, 0, sizeof(unsigned int) * (2 + 2 * chunks.size()), e->stream));
     }
     if (host_samples) {
         // the copy stream may only overwrite the staging buffer once earlier work on it is done
@@ -535,7 +577,7 @@ static int decode_batch_impl(tmk_engine* e, const void* samples_v, bool pcm16, u
                                        const_cast<uint32_t*>(fast.cblk_list), fast.cblk_count, e->stream,
                                        static_cast<char*>(e->d_tile_desc.p) + tmk_scan_tile_desc_bytes(ch.t0) * (ch.t0 ? 1 : 0));
         if (chunks.size() == 1) CK(cudaEventRecord(e->ev[2], e->stream));
-        uint8_t* dpay = pay_dev ? payload : static_cast<uint8_t*>(e->d_payload.p);
+        uint8_t* dpay = dpay_cur;
         // The walks / cluster passes of different chunks overlap each other and the later scans (high-priority
         // streams). Within a chunk the walk follows the cluster pass; they CAN run side by side (the cluster
         // pass publishes every block with a release store, a walk that reaches a block first waits for it,
@@ -579,7 +621,44 @@ static int decode_batch_impl(tmk_engine* e, const void* samples_v, bool pcm16, u
         }
     TmkCounters hc;
     uint64_t n_exact = 0;  // records = sum of the per-stream counts
-    if (seg_mode) {
+    bool small_tried = false;
+    if (small) {
+        CK(cudaEventRecord(e->ev[3], e->stream));
+        e->launches += tmk_launch_excl_scan(static_cast<const uint32_t*>(e->d_cnt.p), static_cast<uint64_t*>(e->d_base.p), n_streams, e->stream);
+        SmallHdr* hdr = reinterpret_cast<SmallHdr*>(sm);
+        e->launches += tmk_launch_order_small(static_cast<const tmk_frame_rec*>(e->d_recs_tmp.p), static_cast<const uint4*>(e->d_rec_ord.p), dc,
+                                              dev_rec_cap, static_cast<const uint64_t*>(e->d_base.p), n_streams,
+                                              use_fast ? static_cast<const tmk_frame_rec*>(e->d_spec.p) : nullptr,
+                                              reinterpret_cast<tmk_frame_rec*>(sm + sm_recs), r_spec, &hdr->n_exact, e->stream);
+        CK(cudaGetLastError());
+        CK(cudaEventRecord(e->ev[4], e->stream));
+        CK(cudaMemcpyAsync(e->h_small, sm, sm_bytes, cudaMemcpyDeviceToHost, e->stream));
+        CK(cudaStreamSynchronize(e->stream));
+        const char* hs = static_cast<const char*>(e->h_small);
+        const SmallHdr* hh = reinterpret_cast<const SmallHdr*>(hs);
+        hc = hh->hc;
+        n_exact = hh->n_exact;
+        small_tried = true;
+        if (hc.n_recs <= dev_rec_cap && hc.n_payload <= dev_pay_cap && n_exact <= r_spec) {  // (r_spec <= rec_cap, dev_pay_cap <= payload_cap)
+            if (n_exact) std::memcpy(recs, hs + sm_recs, sizeof(tmk_frame_rec) * n_exact);
+            if (hc.n_payload) std::memcpy(payload, hs + sm_pay, hc.n_payload);
+            if (link_final) std::memcpy(link_final, hs + sm_link, sizeof(TmkLinkState) * n_streams);
+            *n_recs = n_exact;
+            *payload_len = hc.n_payload;
+            for (int i = 0; i < TMK_STAT_COUNT; ++i) e->stats[i] += hc.stats[i];
+            for (int i = 0; i < 8; ++i) e->dbg[i] = hc.dbg[i];
+            float cms = 0.f;
+            if (cudaEventElapsedTime(&cms, e->ev[2], e->ev[5]) == cudaSuccess) e->dbg[4] = uint64_t(cms * 1000.f);
+            cudaEventElapsedTime(&e->stage_ms[3], e->ev[0], e->ev[1]);
+            cudaEventElapsedTime(&e->stage_ms[0], e->ev[1], e->ev[2]);
+            cudaEventElapsedTime(&e->stage_ms[1], e->ev[2], e->ev[3]);
+            cudaEventElapsedTime(&e->stage_ms[2], e->ev[3], e->ev[4]);
+            return TMK_OK;
+        }
+        // the guesses were too small: the general path takes over with the counts it now has
+    }
+    if (small_tried) {
+    } else if (seg_mode) {
         // which records of which walker count (meeting points), their verdict tallies, then the counts per walker
         uint32_t* d_nvalid = static_cast<uint32_t*>(e->d_cnt.p) + n_items;
         e->launches += tmk_launch_seg_resolve(d_items, d_segst, n_items, d_first_valid, d_nvalid,
@@ -592,8 +671,10 @@ static int decode_batch_impl(tmk_engine* e, const void* samples_v, bool pcm16, u
     e->launches += tmk_launch_excl_scan(static_cast<const uint32_t*>(e->d_cnt.p), static_cast<uint64_t*>(e->d_base.p), n_streams, e->stream);
     CK(cudaMemcpyAsync(&n_exact, static_cast<uint64_t*>(e->d_base.p) + n_streams, sizeof n_exact, cudaMemcpyDeviceToHost, e->stream));
     }
-    CK(cudaMemcpyAsync(&hc, dc, sizeof hc, cudaMemcpyDeviceToHost, e->stream));
-    CK(cudaStreamSynchronize(e->stream));
+    if (!small_tried) {
+        CK(cudaMemcpyAsync(&hc, dc, sizeof hc, cudaMemcpyDeviceToHost, e->stream));
+        CK(cudaStreamSynchronize(e->stream));
+    }
     for (int attempt = 0; attempt < 2; ++attempt) {
         // (the counters of the first pass include what is dropped later: payload bytes of speculative decodes that no
         //  walk linked, records and bytes of segment walkers before their meeting point — before a caller's exactly
@@ -608,8 +689,11 @@ static int decode_batch_impl(tmk_engine* e, const void* samples_v, bool pcm16, u
         if (pay_short) dev_pay_cap = std::min<uint64_t>(payload_cap, hc.n_payload);
         CK(e->d_recs_tmp.reserve(sizeof(tmk_frame_rec) * std::max<uint64_t>(1, dev_rec_cap)));
         CK(e->d_rec_ord.reserve(sizeof(uint4) * std::max<uint64_t>(1, dev_rec_cap)));
-        if (!pay_dev) CK(e->d_payload.reserve(std::max<uint64_t>(1, dev_pay_cap)));
-        uint8_t* dpay = pay_dev ? payload : static_cast<uint8_t*>(e->d_payload.p);
+        if (!pay_dev) {
+            CK(e->d_payload.reserve(std::max<uint64_t>(1, dev_pay_cap)));
+            dpay_cur = static_cast<uint8_t*>(e->d_payload.p);
+        }
+        uint8_t* dpay = dpay_cur;
         CK(cudaMemsetAsync(dc, 0, sizeof(TmkCounters), e->stream));
         CK(cudaMemsetAsync(dnext + chunks.size(), 0, sizeof(unsigned int), e->stream));
         // the speculative verdicts of the cluster pass point into the payload scratch that was just re-sized:
@@ -659,7 +743,7 @@ static int decode_batch_impl(tmk_engine* e, const void* samples_v, bool pcm16, u
         if (!recs_dev)
             CK(cudaMemcpyAsync(recs, dout, sizeof(tmk_frame_rec) * n_exact, cudaMemcpyDeviceToHost, e->stream));
         if (!pay_dev && hc.n_payload)
-            CK(cudaMemcpyAsync(payload, e->d_payload.p, hc.n_payload, cudaMemcpyDeviceToHost, e->stream));
+            CK(cudaMemcpyAsync(payload, dpay_cur, hc.n_payload, cudaMemcpyDeviceToHost, e->stream));
     } else {
         CK(cudaEventRecord(e->ev[4], e->stream));
     }

@@ -45,6 +45,9 @@ struct tmk_engine {
     bool mcm_ready = false;
     float mcm_demod_ms = 0.0f;
     DevBuf d_seg;  // segmented walk: items, walker states, first valid record per walker
+    DevBuf d_small;             // small batches: counters + exit states + ordered records + payload in one block (engine.cu)
+    void* h_small = nullptr;    // its pinned host mirror
+    size_t h_small_cap = 0;
     DevBuf d_tile_desc;  // per-tile descriptors of the tensor-core scan (scan_tc.cu)
     DevBuf d_comm, d_wav, d_wavdesc;  // staging of the counter all-reduce (comm.cu); raw WAV bytes + descriptors (wav.cu)
     float* scan_dbg_dot = nullptr;    // set around tmk_scan_probe by tmk_scan_dot_probe (diagnostic)

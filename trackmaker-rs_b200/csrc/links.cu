@@ -10,7 +10,8 @@
 //   1. assemble_kernel: working buffer of every link = its retained tail ++ its new samples (HBM to HBM);
 //   2. tmk_decode_batch over the working buffers (scan, cluster pass, walk) with the entry state of every
 //      link (TmkStreamDev::init_q / init_fs) and the exit state written by the walk (TmkLinkState);
-//   3. the drain rule (:90-109) applied per link, tails copied to the retained buffer (keep_kernel).
+//   3. the drain rule (:90-109) applied per link: the retained tail STAYS where it is in the working buffer (two working
+//      buffers take turns), the next call assembles from there — no second copy, no second synchronisation.
 // Records carry positions counted from the first sample ever fed to the link; a frame still being
 // gathered (TRUNCATED in the offline engine) is state, not a record.
 #include <algorithm>
@@ -24,11 +25,11 @@ struct tmk_links {
     uint32_t n = 0;
     std::vector<tmk_phy_config> cfg;
     std::vector<uint64_t> P;         // preamble samples per link
-    std::vector<uint64_t> tail_off;  // retained samples of link i: d_tail[cur] + tail_off[i] .. + tail_len[i]
+    std::vector<uint64_t> tail_off;  // retained samples of link i: d_work[cur] + tail_off[i] .. + tail_len[i]
     std::vector<uint64_t> tail_len;
     std::vector<uint64_t> drained;   // samples removed from the front of the link's buffer so far
     std::vector<TmkLinkState> state; // buffer_offset (relative to the retained buffer), Decoding(frame_start)
-    DevBuf d_tail[2], d_work, d_new, d_desc;
+    DevBuf d_work[2], d_new, d_desc;
     int cur = 0;
     uint64_t calls = 0;
 };
@@ -96,9 +97,8 @@ void tmk_links_destroy(tmk_links* l) {
         cudaSetDevice(l->e->device);
         cudaStreamSynchronize(l->e->stream);
     }
-    l->d_tail[0].release();
-    l->d_tail[1].release();
-    l->d_work.release();
+    l->d_work[0].release();
+    l->d_work[1].release();
     l->d_new.release();
     l->d_desc.release();
     delete l;
@@ -175,13 +175,13 @@ int tmk_links_process_samples(tmk_links* l, const float* samples, uint64_t total
         streams[i].cfg = l->cfg[i];
         total_work = (total_work + streams[i].n_samples + 3) & ~3ull;
     }
-    CK(l->d_work.reserve((total_work + 4) * sizeof(float)));
+    DevBuf& work = l->d_work[1 - l->cur];  // (the retained tails live in d_work[cur])
+    CK(work.reserve((total_work + 4) * sizeof(float)));
     CK(l->d_desc.reserve(sizeof(CopyDesc) * n));
     CK(cudaMemcpyAsync(l->d_desc.p, desc.data(), sizeof(CopyDesc) * n, cudaMemcpyHostToDevice, e->stream));
     const uint32_t grid = std::min<uint32_t>(n, 148u * 8u);
     assemble_kernel<<<grid, 256, 0, e->stream>>>(static_cast<const CopyDesc*>(l->d_desc.p), n,
-                                                 static_cast<const float*>(l->d_tail[l->cur].p), d_new,
-                                                 static_cast<float*>(l->d_work.p));
+                                                 static_cast<const float*>(l->d_work[l->cur].p), d_new, static_cast<float*>(work.p));
     CK(cudaGetLastError());
     e->launches += 1;
     // (no synchronisation: the descriptors were copied out of pageable memory, which cudaMemcpyAsync stages before it
@@ -192,7 +192,7 @@ int tmk_links_process_samples(tmk_links* l, const float* samples, uint64_t total
     e->link_init = l->state.data();
     e->link_final = fin.data();
     uint64_t nr = 0, np = 0;
-    const int rc = tmk_decode_batch(e, static_cast<const float*>(l->d_work.p), total_work, streams.data(), n, recs, rec_cap,
+    const int rc = tmk_decode_batch(e, static_cast<const float*>(work.p), total_work, streams.data(), n, recs, rec_cap,
                                     &nr, payload, payload_cap, &np);
     e->link_init = nullptr;
     e->link_final = nullptr;
@@ -212,36 +212,19 @@ int tmk_links_process_samples(tmk_links* l, const float* samples, uint64_t total
     }
     *n_recs = w;
     *payload_len = np;
-    // 5. drain rule (decoder.rs:90-109): keep P-1 samples before buffer_offset
-    uint64_t total_tail = 0;
+    // 5. drain rule (decoder.rs:90-109): keep P-1 samples before buffer_offset — in place, in the working buffer
     for (uint32_t i = 0; i < n; ++i) {
         const uint64_t work_len = streams[i].n_samples;
         const uint64_t off = std::min<uint64_t>(fin[i].off, work_len);
         const uint64_t keep = l->P[i] - 1;
         const uint64_t drain_end = off > keep ? off - keep : 0;
-        CopyDesc& d = desc[i];
-        d.dst = total_tail;
-        d.a = streams[i].offset + drain_end;
-        d.a_len = work_len - drain_end;
-        d.b = 0;
-        d.b_len = 0;
-        l->tail_off[i] = total_tail;
-        l->tail_len[i] = d.a_len;
-        total_tail += d.a_len;
+        l->tail_off[i] = streams[i].offset + drain_end;
+        l->tail_len[i] = work_len - drain_end;
         l->drained[i] += drain_end;
         l->state[i].off = off - drain_end;
         l->state[i].fs = fin[i].fs == TMK_NO_FRAME ? TMK_NO_FRAME : (fin[i].fs > drain_end ? fin[i].fs - drain_end : 0);
         l->state[i].corr = fin[i].corr;
     }
-    DevBuf& nt = l->d_tail[1 - l->cur];
-    CK(nt.reserve((total_tail + 4) * sizeof(float)));
-    CK(cudaMemcpyAsync(l->d_desc.p, desc.data(), sizeof(CopyDesc) * n, cudaMemcpyHostToDevice, e->stream));
-    assemble_kernel<<<grid, 256, 0, e->stream>>>(static_cast<const CopyDesc*>(l->d_desc.p), n,
-                                                 static_cast<const float*>(l->d_work.p), nullptr,
-                                                 static_cast<float*>(nt.p));
-    CK(cudaGetLastError());
-    e->launches += 1;
-    CK(cudaStreamSynchronize(e->stream));
     l->cur = 1 - l->cur;
     l->calls++;
     return TMK_OK;

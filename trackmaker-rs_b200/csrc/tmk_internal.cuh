@@ -220,6 +220,9 @@ int tmk_launch_seg_order(const tmk_frame_rec* recs_in, const uint4* rec_ord, uin
                          tmk_frame_rec* recs_out, cudaStream_t stream);
 int tmk_launch_replay_probe(const float* samples, const TmkStreamDev* streams, const TmkPattern* patterns, uint64_t seed,
                             const uint64_t* ws, uint32_t n, float* out, unsigned long long* counts, cudaStream_t st);
+int tmk_launch_order_small(const tmk_frame_rec* recs_in, const uint4* rec_ord, const TmkCounters* counters, uint64_t slot_cap,
+                           const uint64_t* stream_base, uint32_t n_streams, const tmk_frame_rec* spec, tmk_frame_rec* recs_out,
+                           uint64_t out_cap, uint64_t* n_exact, cudaStream_t st);
 int tmk_launch_order(const tmk_frame_rec* recs_in, const uint4* rec_ord, uint64_t n_recs,
                      const uint32_t* stream_cnt, uint64_t* stream_base, uint32_t n_streams,
                      const tmk_frame_rec* spec, tmk_frame_rec* recs_out, cudaStream_t st);

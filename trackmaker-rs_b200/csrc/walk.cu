@@ -2038,6 +2038,26 @@ __global__ void order_kernel(const tmk_frame_rec* __restrict__ in, const uint4* 
     out[base[ln.z] + ln.y] = r;
 }
 
+// the same with the number of reserved slots read on the device (small batches, engine.cu: nothing is known on the host yet);
+// records beyond `out_cap` are left out (the host sees the exact count and takes the general path then)
+__global__ void order_small_kernel(const tmk_frame_rec* __restrict__ in, const uint4* __restrict__ ord, const TmkCounters* __restrict__ counters,
+                                   uint64_t slot_cap, const uint64_t* __restrict__ base, uint32_t n_streams,
+                                   const tmk_frame_rec* __restrict__ spec, tmk_frame_rec* __restrict__ out, uint64_t out_cap,
+                                   uint64_t* __restrict__ n_exact) {
+    const uint64_t i = uint64_t(blockIdx.x) * blockDim.x + threadIdx.x;
+    if (i == 0) *n_exact = base[n_streams];
+    const uint64_t n = min(uint64_t(counters->n_recs), slot_cap);
+    if (i >= n) return;
+    const uint4 ln = ord[i];
+    if (ln.y == kNoRecord) return;
+    const uint64_t pos = base[ln.z] + ln.y;
+    if (pos >= out_cap) return;
+    tmk_frame_rec r = ln.x != TMK_ENT_INVALID ? spec[ln.x] : in[i];
+    r.stream = ln.z;
+    r.corr = __uint_as_float(ln.w);
+    out[pos] = r;
+}
+
 // ---- segmented walk: which records count
 constexpr uint32_t kSegInvalid = 0xffffffffu;
 // one thread per capture: from its walker 0 along the meeting points
@@ -2224,6 +2244,14 @@ int tmk_launch_seg_order(const tmk_frame_rec* recs_in, const uint4* rec_ord, uin
 int tmk_launch_replay_probe(const float* samples, const TmkStreamDev* streams, const TmkPattern* patterns, uint64_t seed,
                             const uint64_t* ws, uint32_t n, float* out, unsigned long long* counts, cudaStream_t st) {
     replay_probe_kernel<<<1, 32, 0, st>>>(samples, streams, patterns, seed, ws, n, out, counts);
+    return 1;
+}
+
+int tmk_launch_order_small(const tmk_frame_rec* recs_in, const uint4* rec_ord, const TmkCounters* counters, uint64_t slot_cap,
+                           const uint64_t* stream_base, uint32_t n_streams, const tmk_frame_rec* spec, tmk_frame_rec* recs_out,
+                           uint64_t out_cap, uint64_t* n_exact, cudaStream_t st) {
+    const uint32_t grid = uint32_t((std::max<uint64_t>(slot_cap, 1) + 255) / 256);
+    order_small_kernel<<<grid, 256, 0, st>>>(recs_in, rec_ord, counters, slot_cap, stream_base, n_streams, spec, recs_out, out_cap, n_exact);
     return 1;
 }
 
