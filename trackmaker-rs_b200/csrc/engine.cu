@@ -496,8 +496,10 @@ static int decode_batch_impl(tmk_engine* e, const void* samples_v, bool pcm16, u
         unsigned int pool[4];
     };
     const uint64_t r_spec = dev_rec_cap - kSlotSlack;  // records the block has room for (= the caller's capacity, or the guess)
-    const bool small = chunks.size() == 1 && !seg_mode && !recs_dev && !pay_dev && r_spec <= 8192 && dev_pay_cap <= (512u << 10) &&
+    const bool small = chunks.size() == 1 && !seg_mode && !recs_dev && !pay_dev && r_spec <= 65536 && dev_pay_cap <= (4u << 20) &&
                        n_streams <= 16384 && !getenv("TMK_NO_SMALL_PATH");
+    // what the first copy brings over: the header, the exit states, and as many records / payload bytes as a poll usually has
+    const uint64_t c_recs = std::min<uint64_t>(r_spec, 512 + n_streams / 2), c_pay = std::min<uint64_t>(dev_pay_cap, 32768 + 40ull * n_streams);
     const size_t sm_link = (sizeof(SmallHdr) + 15) & ~size_t(15);
     const size_t sm_recs = (sm_link + (link_final ? sizeof(TmkLinkState) * n_streams : 0) + 15) & ~size_t(15);
     const size_t sm_pay = (sm_recs + sizeof(tmk_frame_rec) * r_spec + 15) & ~size_t(15);
@@ -542,7 +544,12 @@ static int decode_batch_impl(tmk_engine* e, const void* samples_v, bool pcm16, u
     };
 
     CK(cudaEventRecord(e->ev[1], e->stream));
-    e->launches += tmk_launch_tile_dir(ds, n_streams, uint32_t(b.n_tiles), dtd, e->stream);
+#ifdef TMK_SCAN_ARM_A
+    const bool fuse_dir = false;
+#else
+    const bool fuse_dir = chunks.size() == 1 && (b.kinds & 3u) != 0 && b.n_tiles > 0;  // the scan's descriptor kernel writes the directory too
+#endif
+    if (!fuse_dir) e->launches += tmk_launch_tile_dir(ds, n_streams, uint32_t(b.n_tiles), dtd, e->stream);
 #ifdef TMK_SCAN_ARM_A
     CK(cudaMemsetAsync(dcb, 0, sizeof(uint32_t) * TMK_BLK_WORDS * b.n_blocks, e->stream));  // (the CUDA-core scan ORs its bits in)
 #endif
@@ -575,7 +582,7 @@ static int decode_batch_impl(tmk_engine* e, const void* samples_v, bool pcm16, u
         const TmkFast fast = fast_of(g, ch);
         e->launches += tmk_launch_scan(dx, total_samples, ds, n_streams, dtd, ch.t0, ch.t1 - ch.t0, dp, b.kinds, dbi, dcb,
                                        const_cast<uint32_t*>(fast.cblk_list), fast.cblk_count, e->stream,
-                                       static_cast<char*>(e->d_tile_desc.p) + tmk_scan_tile_desc_bytes(ch.t0) * (ch.t0 ? 1 : 0));
+                                       static_cast<char*>(e->d_tile_desc.p) + tmk_scan_tile_desc_bytes(ch.t0) * (ch.t0 ? 1 : 0), nullptr, fuse_dir);
         if (chunks.size() == 1) CK(cudaEventRecord(e->ev[2], e->stream));
         uint8_t* dpay = dpay_cur;
         // The walks / cluster passes of different chunks overlap each other and the later scans (high-priority
@@ -624,22 +631,30 @@ static int decode_batch_impl(tmk_engine* e, const void* samples_v, bool pcm16, u
     bool small_tried = false;
     if (small) {
         CK(cudaEventRecord(e->ev[3], e->stream));
-        e->launches += tmk_launch_excl_scan(static_cast<const uint32_t*>(e->d_cnt.p), static_cast<uint64_t*>(e->d_base.p), n_streams, e->stream);
         SmallHdr* hdr = reinterpret_cast<SmallHdr*>(sm);
-        e->launches += tmk_launch_order_small(static_cast<const tmk_frame_rec*>(e->d_recs_tmp.p), static_cast<const uint4*>(e->d_rec_ord.p), dc,
-                                              dev_rec_cap, static_cast<const uint64_t*>(e->d_base.p), n_streams,
-                                              use_fast ? static_cast<const tmk_frame_rec*>(e->d_spec.p) : nullptr,
+        e->launches += tmk_launch_order_small(static_cast<const uint32_t*>(e->d_cnt.p), static_cast<uint64_t*>(e->d_base.p), n_streams,
+                                              static_cast<const tmk_frame_rec*>(e->d_recs_tmp.p), static_cast<const uint4*>(e->d_rec_ord.p), dc,
+                                              dev_rec_cap, use_fast ? static_cast<const tmk_frame_rec*>(e->d_spec.p) : nullptr,
                                               reinterpret_cast<tmk_frame_rec*>(sm + sm_recs), r_spec, &hdr->n_exact, e->stream);
         CK(cudaGetLastError());
         CK(cudaEventRecord(e->ev[4], e->stream));
-        CK(cudaMemcpyAsync(e->h_small, sm, sm_bytes, cudaMemcpyDeviceToHost, e->stream));
+        char* hs = static_cast<char*>(e->h_small);
+        CK(cudaMemcpyAsync(hs, sm, sm_recs + sizeof(tmk_frame_rec) * c_recs, cudaMemcpyDeviceToHost, e->stream));
+        if (c_pay) CK(cudaMemcpyAsync(hs + sm_pay, sm + sm_pay, c_pay, cudaMemcpyDeviceToHost, e->stream));
         CK(cudaStreamSynchronize(e->stream));
-        const char* hs = static_cast<const char*>(e->h_small);
         const SmallHdr* hh = reinterpret_cast<const SmallHdr*>(hs);
         hc = hh->hc;
         n_exact = hh->n_exact;
         small_tried = true;
         if (hc.n_recs <= dev_rec_cap && hc.n_payload <= dev_pay_cap && n_exact <= r_spec) {  // (r_spec <= rec_cap, dev_pay_cap <= payload_cap)
+            if (n_exact > c_recs || hc.n_payload > c_pay) {  // a busy poll: the rest, now that the counts are known
+                if (n_exact > c_recs)
+                    CK(cudaMemcpyAsync(hs + sm_recs + sizeof(tmk_frame_rec) * c_recs, sm + sm_recs + sizeof(tmk_frame_rec) * c_recs,
+                                       sizeof(tmk_frame_rec) * (n_exact - c_recs), cudaMemcpyDeviceToHost, e->stream));
+                if (hc.n_payload > c_pay)
+                    CK(cudaMemcpyAsync(hs + sm_pay + c_pay, sm + sm_pay + c_pay, hc.n_payload - c_pay, cudaMemcpyDeviceToHost, e->stream));
+                CK(cudaStreamSynchronize(e->stream));
+            }
             if (n_exact) std::memcpy(recs, hs + sm_recs, sizeof(tmk_frame_rec) * n_exact);
             if (hc.n_payload) std::memcpy(payload, hs + sm_pay, hc.n_payload);
             if (link_final) std::memcpy(link_final, hs + sm_link, sizeof(TmkLinkState) * n_streams);

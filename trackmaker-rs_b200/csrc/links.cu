@@ -40,20 +40,27 @@ struct CopyDesc {  // dst[0 .. a_len) = a[0 .. a_len), dst[a_len .. a_len + b_le
     uint64_t dst, a, a_len, b, b_len;
 };
 
-// one CTA per link (grid-stride over links): two contiguous copies
+// four CTAs per link, each a quarter of the two contiguous copies; the CTAs behind them zero `pad_len` samples at `pad_at`
+// (the tensor-core scan loads a tile with one TMA box that reaches 8640 samples past the tile's first sample: with the
+// working buffer padded, the boxes of the last links stay inside it and no tile takes the scan's slow manual staging)
+constexpr uint32_t kAsmParts = 4, kAsmPadCtas = 8;
 __global__ void __launch_bounds__(256)
 assemble_kernel(const CopyDesc* __restrict__ desc, uint32_t n, const float* __restrict__ src_a,
-                const float* __restrict__ src_b, float* __restrict__ dst) {
-    for (uint32_t i = blockIdx.x; i < n; i += gridDim.x) {
-        const CopyDesc d = desc[i];
-        float* o = dst + d.dst;
-        const float* a = src_a + d.a;
-        for (uint64_t k = threadIdx.x; k < d.a_len; k += blockDim.x) o[k] = a[k];
-        if (d.b_len) {
-            const float* b = src_b + d.b;
-            o += d.a_len;
-            for (uint64_t k = threadIdx.x; k < d.b_len; k += blockDim.x) o[k] = b[k];
-        }
+                const float* __restrict__ src_b, float* __restrict__ dst, uint64_t pad_at, uint32_t pad_len) {
+    const uint32_t link = blockIdx.x / kAsmParts, part = blockIdx.x % kAsmParts;
+    if (link >= n) {
+        for (uint32_t k = (blockIdx.x - n * kAsmParts) * 256 + threadIdx.x; k < pad_len; k += kAsmPadCtas * 256) dst[pad_at + k] = 0.0f;
+        return;
+    }
+    const CopyDesc d = desc[link];
+    float* o = dst + d.dst;
+    const float* a = src_a + d.a;
+    const uint32_t k0 = part * 256 + threadIdx.x, step = kAsmParts * 256;
+    for (uint64_t k = k0; k < d.a_len; k += step) o[k] = a[k];
+    if (d.b_len) {
+        const float* b = src_b + d.b;
+        o += d.a_len;
+        for (uint64_t k = k0; k < d.b_len; k += step) o[k] = b[k];
     }
 }
 
@@ -175,13 +182,14 @@ int tmk_links_process_samples(tmk_links* l, const float* samples, uint64_t total
         streams[i].cfg = l->cfg[i];
         total_work = (total_work + streams[i].n_samples + 3) & ~3ull;
     }
+    constexpr uint32_t kPad = 16384;       // zeroed samples behind the last link (see assemble_kernel)
     DevBuf& work = l->d_work[1 - l->cur];  // (the retained tails live in d_work[cur])
-    CK(work.reserve((total_work + 4) * sizeof(float)));
+    CK(work.reserve((total_work + kPad + 4) * sizeof(float)));
     CK(l->d_desc.reserve(sizeof(CopyDesc) * n));
     CK(cudaMemcpyAsync(l->d_desc.p, desc.data(), sizeof(CopyDesc) * n, cudaMemcpyHostToDevice, e->stream));
-    const uint32_t grid = std::min<uint32_t>(n, 148u * 8u);
-    assemble_kernel<<<grid, 256, 0, e->stream>>>(static_cast<const CopyDesc*>(l->d_desc.p), n,
-                                                 static_cast<const float*>(l->d_work[l->cur].p), d_new, static_cast<float*>(work.p));
+    assemble_kernel<<<n * kAsmParts + kAsmPadCtas, 256, 0, e->stream>>>(static_cast<const CopyDesc*>(l->d_desc.p), n,
+                                                                        static_cast<const float*>(l->d_work[l->cur].p), d_new,
+                                                                        static_cast<float*>(work.p), total_work, kPad);
     CK(cudaGetLastError());
     e->launches += 1;
     // (no synchronisation: the descriptors were copied out of pageable memory, which cudaMemcpyAsync stages before it
@@ -192,7 +200,7 @@ int tmk_links_process_samples(tmk_links* l, const float* samples, uint64_t total
     e->link_init = l->state.data();
     e->link_final = fin.data();
     uint64_t nr = 0, np = 0;
-    const int rc = tmk_decode_batch(e, static_cast<const float*>(work.p), total_work, streams.data(), n, recs, rec_cap,
+    const int rc = tmk_decode_batch(e, static_cast<const float*>(work.p), total_work + kPad, streams.data(), n, recs, rec_cap,
                                     &nr, payload, payload_cap, &np);
     e->link_init = nullptr;
     e->link_final = nullptr;

@@ -387,8 +387,9 @@ void launch_fast(const float* samples, uint64_t total_samples, const TmkStreamDe
 int tmk_launch_scan(const float* samples, uint64_t total_samples, const TmkStreamDev* streams, uint32_t n_streams,
                     const uint32_t* tile_stream, uint32_t tile0, uint32_t n_tiles, const TmkPattern* patterns,
                     uint32_t kinds, float4* blk_info, uint32_t* cand_bits, uint32_t* cblk_list, unsigned int* cblk_count,
-                    cudaStream_t st, void* tile_desc, float* dbg_dot) {
+                    cudaStream_t st, void* tile_desc, float* dbg_dot, bool build_dir) {
     (void)dbg_dot;
+    (void)build_dir;
     (void)tile_desc;
     (void)n_streams;
     if (n_tiles == 0) return 0;

@@ -84,13 +84,27 @@ struct alignas(16) TileDesc {
 };
 static_assert(sizeof(TileDesc) == 32, "tile descriptor");
 
-__global__ void tile_desc_kernel(const TmkStreamDev* __restrict__ streams, const uint32_t* __restrict__ tile_stream,
-                                 const TmkPattern* __restrict__ patterns, uint32_t tile0, uint32_t n_tiles,
-                                 TileDesc* __restrict__ out) {
+// dir_out (nullable): the kernel also finds the stream that owns each tile (what tile_dir_kernel does: streams are sorted by
+// tile_base) and writes the directory — one launch less in front of the scan of a one-chunk batch
+__global__ void tile_desc_kernel(const TmkStreamDev* __restrict__ streams, uint32_t n_streams, const uint32_t* __restrict__ tile_stream,
+                                 uint32_t* __restrict__ dir_out, const TmkPattern* __restrict__ patterns, uint32_t tile0,
+                                 uint32_t n_tiles, TileDesc* __restrict__ out) {
     const uint32_t tl = blockIdx.x * blockDim.x + threadIdx.x;
     if (tl >= n_tiles) return;
     const uint32_t tile = tile0 + tl;
-    const TmkStreamDev sd = streams[tile_stream[tile]];
+    uint32_t owner;
+    if (dir_out != nullptr) {
+        uint32_t lo = 0, hi = n_streams - 1;
+        while (lo < hi) {
+            const uint32_t mid = (lo + hi + 1) >> 1;
+            if (streams[mid].tile_base <= tile) lo = mid; else hi = mid - 1;
+        }
+        owner = lo;
+        dir_out[tile] = lo;
+    } else {
+        owner = tile_stream[tile];
+    }
+    const TmkStreamDev sd = streams[owner];
     const TmkPattern* pat = patterns + sd.pattern;
     const uint64_t w0 = uint64_t(tile - sd.tile_base) * TMK_TILE;
     TileDesc d;
@@ -541,13 +555,14 @@ size_t tmk_scan_tile_desc_bytes(uint32_t n_tiles) { return sizeof(TileDesc) * si
 int tmk_launch_scan(const float* samples, uint64_t total_samples, const TmkStreamDev* streams, uint32_t n_streams,
                     const uint32_t* tile_stream, uint32_t tile0, uint32_t n_tiles, const TmkPattern* patterns,
                     uint32_t kinds, float4* blk_info, uint32_t* cand_bits, uint32_t* cblk_list, unsigned int* cblk_count,
-                    cudaStream_t st, void* tile_desc, float* dbg_dot) {
-    (void)n_streams;
+                    cudaStream_t st, void* tile_desc, float* dbg_dot, bool build_dir) {
     if (n_tiles == 0) return 0;
     int launches = 0;
     TileDesc* td = static_cast<TileDesc*>(tile_desc);
     if (kinds & 3u) {
-        tile_desc_kernel<<<(n_tiles + 255) / 256, 256, 0, st>>>(streams, tile_stream, patterns, tile0, n_tiles, td);
+        tile_desc_kernel<<<(n_tiles + 127) / 128, 128, 0, st>>>(streams, n_streams, tile_stream,
+                                                                build_dir && tile0 == 0 ? const_cast<uint32_t*>(tile_stream) : nullptr, patterns,
+                                                                tile0, n_tiles, td);
         ++launches;
     }
     if (kinds & 1u)

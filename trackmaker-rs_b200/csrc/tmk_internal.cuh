@@ -190,7 +190,8 @@ int tmk_launch_tile_dir(const TmkStreamDev* streams, uint32_t n_streams, uint32_
 int tmk_launch_scan(const float* samples, uint64_t total_samples, const TmkStreamDev* streams, uint32_t n_streams,
                     const uint32_t* tile_stream, uint32_t tile0, uint32_t n_tiles, const TmkPattern* patterns,
                     uint32_t kinds, float4* blk_info, uint32_t* cand_bits, uint32_t* cblk_list, unsigned int* cblk_count,
-                    cudaStream_t st, void* tile_desc, float* dbg_dot = nullptr);
+                    cudaStream_t st, void* tile_desc, float* dbg_dot = nullptr, bool build_dir = false);
+// build_dir: the descriptor kernel also fills tile_stream (tile0 == 0, all tiles): tmk_launch_tile_dir is not needed then
 // cblk_list / cblk_count (nullable): global ids of the blocks with candidates; tile_desc: device scratch of
 // tmk_scan_tile_desc_bytes(n_tiles) bytes; dbg_dot (nullable): the filter's correlation numerators per window
 size_t tmk_scan_tile_desc_bytes(uint32_t n_tiles);
@@ -220,9 +221,9 @@ int tmk_launch_seg_order(const tmk_frame_rec* recs_in, const uint4* rec_ord, uin
                          tmk_frame_rec* recs_out, cudaStream_t stream);
 int tmk_launch_replay_probe(const float* samples, const TmkStreamDev* streams, const TmkPattern* patterns, uint64_t seed,
                             const uint64_t* ws, uint32_t n, float* out, unsigned long long* counts, cudaStream_t st);
-int tmk_launch_order_small(const tmk_frame_rec* recs_in, const uint4* rec_ord, const TmkCounters* counters, uint64_t slot_cap,
-                           const uint64_t* stream_base, uint32_t n_streams, const tmk_frame_rec* spec, tmk_frame_rec* recs_out,
-                           uint64_t out_cap, uint64_t* n_exact, cudaStream_t st);
+int tmk_launch_order_small(const uint32_t* stream_cnt, uint64_t* stream_base, uint32_t n_streams, const tmk_frame_rec* recs_in,
+                           const uint4* rec_ord, const TmkCounters* counters, uint64_t slot_cap, const tmk_frame_rec* spec,
+                           tmk_frame_rec* recs_out, uint64_t out_cap, uint64_t* n_exact, cudaStream_t st);
 int tmk_launch_order(const tmk_frame_rec* recs_in, const uint4* rec_ord, uint64_t n_recs,
                      const uint32_t* stream_cnt, uint64_t* stream_base, uint32_t n_streams,
                      const tmk_frame_rec* spec, tmk_frame_rec* recs_out, cudaStream_t st);

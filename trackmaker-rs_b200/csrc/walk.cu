@@ -2038,24 +2038,62 @@ __global__ void order_kernel(const tmk_frame_rec* __restrict__ in, const uint4* 
     out[base[ln.z] + ln.y] = r;
 }
 
-// the same with the number of reserved slots read on the device (small batches, engine.cu: nothing is known on the host yet);
-// records beyond `out_cap` are left out (the host sees the exact count and takes the general path then)
-__global__ void order_small_kernel(const tmk_frame_rec* __restrict__ in, const uint4* __restrict__ ord, const TmkCounters* __restrict__ counters,
-                                   uint64_t slot_cap, const uint64_t* __restrict__ base, uint32_t n_streams,
-                                   const tmk_frame_rec* __restrict__ spec, tmk_frame_rec* __restrict__ out, uint64_t out_cap,
-                                   uint64_t* __restrict__ n_exact) {
-    const uint64_t i = uint64_t(blockIdx.x) * blockDim.x + threadIdx.x;
-    if (i == 0) *n_exact = base[n_streams];
+// Small batches (engine.cu: nothing is known on the host yet): exclusive scan of the per-stream counts AND the scatter in one
+// CTA, the number of reserved slots read on the device; records beyond `out_cap` are left out (the host sees the exact
+// count and takes the general path then)
+__global__ void __launch_bounds__(1024)
+count_order_small_kernel(const uint32_t* __restrict__ cnt, uint64_t* __restrict__ base, uint32_t n_streams,
+                         const tmk_frame_rec* __restrict__ in, const uint4* __restrict__ ord, const TmkCounters* __restrict__ counters,
+                         uint64_t slot_cap, const tmk_frame_rec* __restrict__ spec, tmk_frame_rec* __restrict__ out, uint64_t out_cap,
+                         uint64_t* __restrict__ n_exact) {
+    __shared__ uint64_t warp_tot[32];
+    __shared__ uint64_t carry_s;
+    if (threadIdx.x == 0) carry_s = 0;
+    __syncthreads();
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    for (uint32_t b0 = 0; b0 < n_streams; b0 += 1024) {
+        const uint32_t i = b0 + threadIdx.x;
+        const uint64_t v = i < n_streams ? cnt[i] : 0;
+        uint64_t s = v;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            uint64_t t = __shfl_up_sync(kFull, s, o);
+            if (lane >= o) s += t;
+        }
+        if (lane == 31) warp_tot[warp] = s;
+        __syncthreads();
+        if (warp == 0) {
+            uint64_t w = warp_tot[lane], ws = w;
+#pragma unroll
+            for (int o = 1; o < 32; o <<= 1) {
+                uint64_t t = __shfl_up_sync(kFull, ws, o);
+                if (lane >= o) ws += t;
+            }
+            warp_tot[lane] = ws - w;  // exclusive
+        }
+        __syncthreads();
+        const uint64_t c0 = carry_s;
+        if (i < n_streams) base[i] = c0 + warp_tot[warp] + s - v;
+        __syncthreads();
+        if (threadIdx.x == 1023) carry_s = c0 + warp_tot[31] + s;
+        __syncthreads();
+    }
+    if (threadIdx.x == 0) {
+        base[n_streams] = carry_s;
+        *n_exact = carry_s;
+    }
+    __syncthreads();  // (the bases written above are read below by other threads of this CTA)
     const uint64_t n = min(uint64_t(counters->n_recs), slot_cap);
-    if (i >= n) return;
-    const uint4 ln = ord[i];
-    if (ln.y == kNoRecord) return;
-    const uint64_t pos = base[ln.z] + ln.y;
-    if (pos >= out_cap) return;
-    tmk_frame_rec r = ln.x != TMK_ENT_INVALID ? spec[ln.x] : in[i];
-    r.stream = ln.z;
-    r.corr = __uint_as_float(ln.w);
-    out[pos] = r;
+    for (uint64_t i = threadIdx.x; i < n; i += 1024) {
+        const uint4 ln = ord[i];
+        if (ln.y == kNoRecord) continue;
+        const uint64_t pos = base[ln.z] + ln.y;
+        if (pos >= out_cap) continue;
+        tmk_frame_rec r = ln.x != TMK_ENT_INVALID ? spec[ln.x] : in[i];
+        r.stream = ln.z;
+        r.corr = __uint_as_float(ln.w);
+        out[pos] = r;
+    }
 }
 
 // ---- segmented walk: which records count
@@ -2247,11 +2285,11 @@ int tmk_launch_replay_probe(const float* samples, const TmkStreamDev* streams, c
     return 1;
 }
 
-int tmk_launch_order_small(const tmk_frame_rec* recs_in, const uint4* rec_ord, const TmkCounters* counters, uint64_t slot_cap,
-                           const uint64_t* stream_base, uint32_t n_streams, const tmk_frame_rec* spec, tmk_frame_rec* recs_out,
-                           uint64_t out_cap, uint64_t* n_exact, cudaStream_t st) {
-    const uint32_t grid = uint32_t((std::max<uint64_t>(slot_cap, 1) + 255) / 256);
-    order_small_kernel<<<grid, 256, 0, st>>>(recs_in, rec_ord, counters, slot_cap, stream_base, n_streams, spec, recs_out, out_cap, n_exact);
+int tmk_launch_order_small(const uint32_t* stream_cnt, uint64_t* stream_base, uint32_t n_streams, const tmk_frame_rec* recs_in,
+                           const uint4* rec_ord, const TmkCounters* counters, uint64_t slot_cap, const tmk_frame_rec* spec,
+                           tmk_frame_rec* recs_out, uint64_t out_cap, uint64_t* n_exact, cudaStream_t st) {
+    count_order_small_kernel<<<1, 1024, 0, st>>>(stream_cnt, stream_base, n_streams, recs_in, rec_ord, counters, slot_cap, spec, recs_out,
+                                                 out_cap, n_exact);
     return 1;
 }
 
