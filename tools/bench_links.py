@@ -30,12 +30,13 @@ lens = np.full(n_links, poll, np.uint64)
 base = np.arange(n_links, dtype=np.uint64) * np.uint64(n_per)
 frames = 0
 times = []
+p_x, p_lens, p_recs, p_pl = C.c_void_p(d_x), C.c_void_p(lens.ctypes.data), C.c_void_p(recs.ctypes.data), C.c_void_p(pl.ctypes.data)
+r_nr, r_npl = C.byref(nr), C.byref(npl)
 for k in range(n_polls):
     offs = base + np.uint64(k * poll)
+    p_offs = C.c_void_p(offs.ctypes.data)  # (the pointer objects are made outside the timed call: a Rust caller has none of this)
     t0 = time.perf_counter()
-    rc = lib.tmk_links_process_samples(h, C.c_void_p(d_x), n_links * n_per, offs.ctypes.data_as(C.c_void_p),
-                                       lens.ctypes.data_as(C.c_void_p), recs.ctypes.data_as(C.c_void_p), rec_cap,
-                                       C.byref(nr), pl.ctypes.data_as(C.c_void_p), pay_cap, C.byref(npl))
+    rc = lib.tmk_links_process_samples(h, p_x, n_links * n_per, p_offs, p_lens, p_recs, rec_cap, r_nr, p_pl, pay_cap, r_npl)
     times.append(time.perf_counter() - t0)
     eng._check(rc)
     frames += int((recs[:nr.value]["status"] == 0).sum())

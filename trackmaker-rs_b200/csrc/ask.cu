@@ -1250,6 +1250,7 @@ int tmk_ask_sync_device(tmk_engine* e, const float* samples, uint64_t total_samp
     CK(cudaMemsetAsync(e->d_ask_l2.p, 0, 16 * sizeof(unsigned long long), e->stream));
     const AskStream* ds = static_cast<const AskStream*>(e->d_streams.p);
     const float* tab = static_cast<const float*>(e->d_ask_tab.p);
+    tmk_flush_stage_ms(e);
     CK(cudaEventRecord(e->ev[0], e->stream));
     // exact power checkpoints for the walk (TMK_ASK_NO_CHK=1: the walk chains through every sample itself, for A/B)
     static const bool no_chk = getenv("TMK_ASK_NO_CHK") != nullptr;

@@ -2,6 +2,7 @@
 // scan / walk kernels. No CPU implementation of any PHY stage lives here: every entry point that
 // computes launches CUDA kernels, and fails with TMK_E_CUDA when no sm_100 device is usable.
 #include <algorithm>
+#include <chrono>
 #include <cmath>
 #include <cstdio>
 #include <cstdlib>
@@ -154,6 +155,18 @@ int stage_in(tmk_engine* e, DevBuf& buf, const void* src, size_t bytes, const vo
 }
 
 }  // namespace
+
+void tmk_flush_stage_ms(tmk_engine* e) {
+    if (!e || !e->stage_pending) return;
+    e->stage_pending = false;
+    float cms = 0.f;
+    if (cudaEventElapsedTime(&cms, e->ev[2], e->ev[5]) == cudaSuccess) e->dbg[4] = uint64_t(cms * 1000.f);
+    cudaEventElapsedTime(&e->stage_ms[3], e->ev[0], e->ev[1]);
+    cudaEventElapsedTime(&e->stage_ms[0], e->ev[1], e->ev[2]);
+    cudaEventElapsedTime(&e->stage_ms[1], e->ev[2], e->ev[3]);
+    cudaEventElapsedTime(&e->stage_ms[2], e->ev[3], e->ev[4]);
+    cudaGetLastError();
+}
 
 extern "C" {
 
@@ -315,7 +328,14 @@ static int decode_batch_impl(tmk_engine* e, const void* samples_v, bool pcm16, u
     *n_recs = 0;
     *payload_len = 0;
     if (n_streams == 0) return TMK_OK;
+    static const bool trace = getenv("TMK_TRACE_HOST") != nullptr;  // host-side time line of a small batch on stderr (us)
+    const auto t_in = std::chrono::steady_clock::now();
+    auto us_since = [&](std::chrono::steady_clock::time_point t) {
+        return std::chrono::duration<double, std::micro>(std::chrono::steady_clock::now() - t).count();
+    };
     CK(cudaSetDevice(e->device));
+    tmk_flush_stage_ms(e);
+    e->stage_pending = false;
     Batch b;
     int rc = prepare_batch(e, total_samples, streams, n_streams, &b);
     if (rc != TMK_OK) return rc;
@@ -641,7 +661,9 @@ static int decode_batch_impl(tmk_engine* e, const void* samples_v, bool pcm16, u
         char* hs = static_cast<char*>(e->h_small);
         CK(cudaMemcpyAsync(hs, sm, sm_recs + sizeof(tmk_frame_rec) * c_recs, cudaMemcpyDeviceToHost, e->stream));
         if (c_pay) CK(cudaMemcpyAsync(hs + sm_pay, sm + sm_pay, c_pay, cudaMemcpyDeviceToHost, e->stream));
+        const double t_enq = trace ? us_since(t_in) : 0.0;
         CK(cudaStreamSynchronize(e->stream));
+        if (trace) fprintf(stderr, "tmk small batch: enqueued after %.1f us, synchronised after %.1f us\n", t_enq, us_since(t_in));
         const SmallHdr* hh = reinterpret_cast<const SmallHdr*>(hs);
         hc = hh->hc;
         n_exact = hh->n_exact;
@@ -662,12 +684,7 @@ static int decode_batch_impl(tmk_engine* e, const void* samples_v, bool pcm16, u
             *payload_len = hc.n_payload;
             for (int i = 0; i < TMK_STAT_COUNT; ++i) e->stats[i] += hc.stats[i];
             for (int i = 0; i < 8; ++i) e->dbg[i] = hc.dbg[i];
-            float cms = 0.f;
-            if (cudaEventElapsedTime(&cms, e->ev[2], e->ev[5]) == cudaSuccess) e->dbg[4] = uint64_t(cms * 1000.f);
-            cudaEventElapsedTime(&e->stage_ms[3], e->ev[0], e->ev[1]);
-            cudaEventElapsedTime(&e->stage_ms[0], e->ev[1], e->ev[2]);
-            cudaEventElapsedTime(&e->stage_ms[1], e->ev[2], e->ev[3]);
-            cudaEventElapsedTime(&e->stage_ms[2], e->ev[3], e->ev[4]);
+            e->stage_pending = true;  // (stage times: on demand, tmk_flush_stage_ms)
             return TMK_OK;
         }
         // the guesses were too small: the general path takes over with the counts it now has
@@ -1009,6 +1026,8 @@ int tmk_stats(tmk_engine* e, uint64_t counters[TMK_STAT_COUNT]) {
 
 int tmk_debug_counters(tmk_engine* e, uint64_t out[8]) {
     if (!e || !out) return TMK_E_INVALID;
+    cudaSetDevice(e->device);
+    tmk_flush_stage_ms(e);
     for (int i = 0; i < 8; ++i) out[i] = e->dbg[i];
     return TMK_OK;
 }
@@ -1073,12 +1092,16 @@ void* tmk_engine_stream(tmk_engine* e) { return e ? static_cast<void*>(e->stream
 
 int tmk_last_kernel_ms(tmk_engine* e, float* ms) {
     if (!e || !ms) return TMK_E_INVALID;
+    cudaSetDevice(e->device);
+    tmk_flush_stage_ms(e);
     *ms = e->stage_ms[0] + e->stage_ms[1] + e->stage_ms[2];
     return TMK_OK;
 }
 
 int tmk_last_stage_ms(tmk_engine* e, float ms[4]) {
     if (!e || !ms) return TMK_E_INVALID;
+    cudaSetDevice(e->device);
+    tmk_flush_stage_ms(e);
     for (int i = 0; i < 4; ++i) ms[i] = e->stage_ms[i];
     return TMK_OK;
 }

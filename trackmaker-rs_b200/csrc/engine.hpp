@@ -59,6 +59,7 @@ struct tmk_engine {
     cudaEvent_t tev[2] = {};
     cudaEvent_t cev[6] = {};  // copy/compute hand-over of the chunked staging
     float stage_ms[4] = {0, 0, 0, 0};
+    bool stage_pending = false;  // small batches leave the event arithmetic to whoever asks (tmk_flush_stage_ms)
     float ask_ms[2] = {0, 0};  // last tmk_ask_decode_batch: scan, walk
     uint64_t launches = 0;
     uint64_t stats[TMK_STAT_COUNT] = {};
@@ -90,6 +91,8 @@ inline bool tmk_is_device_ptr(const void* p) {
     return a.type == cudaMemoryTypeDevice || a.type == cudaMemoryTypeManaged;
 }
 
+// engine.cu: stage times of the last decode out of its events, if nobody has asked yet — before e->ev[] are recorded again
+void tmk_flush_stage_ms(tmk_engine* e);
 // ask.cu, shared with mcm.cu (the multi-carrier frames use the chirp preamble and the frame envelope of examples/ask.rs)
 int tmk_ask_ensure_tables(tmk_engine* e);
 int tmk_ask_sync_device(tmk_engine* e, const float* samples, uint64_t total_samples, const tmk_stream* streams, uint32_t n_streams,
