@@ -277,6 +277,57 @@ def ask_leg(eng, tmkphy, orc, d_x, n_s, n_per, hbm, check_streams=8):
     return res
 
 
+def links_leg(eng, orc, tmkphy, n_links=256, n_polls=100, poll=1200, check_links=8):
+    """Carried-state streaming decode (SURVEY §8 f1: PhyDecoder::process_samples, decoder.rs:68-112, at the cadence of
+    csma.rs:446 — 25 ms polls of 1200 samples): n_links decoders fed poll by poll out of captures resident in HBM through
+    tmk_links_process_samples; a poll is one call, timed on the host from call to return (records and payload in host
+    memory). Parity: every record of `check_links` links, poll by poll, against the oracle's decoder fed with the same calls."""
+    import ctypes as C
+    n_per = poll * n_polls
+    cfg = tmkphy.make_config(tmkphy.LINE_4B5B, local_addr=1)
+    d_x = eng.device_alloc(n_links * n_per * 4)
+    eng.synth_batch(cfg, 4242, n_links, n_per, 15.0, 0.7, device_ptr=d_x, want_truth=False)
+    bank = tmkphy.PhyDecoderBank(eng, [cfg] * n_links)
+    lib, h = eng._lib, bank._h
+    rec_cap, pay_cap = 8 * n_links + 1024, 300 * n_links + 65536
+    recs = np.zeros(rec_cap, tmkphy.REC_DTYPE)
+    pl = np.zeros(pay_cap, np.uint8)
+    nr, npl = C.c_uint64(0), C.c_uint64(0)
+    lens = np.full(n_links, poll, np.uint64)
+    base = np.arange(n_links, dtype=np.uint64) * np.uint64(n_per)
+    p_x, p_lens, p_recs, p_pl = C.c_void_p(d_x), C.c_void_p(lens.ctypes.data), C.c_void_p(recs.ctypes.data), C.c_void_p(pl.ctypes.data)
+    times, got = [], []
+    for k in range(n_polls):
+        offs = base + np.uint64(k * poll)
+        p_offs = C.c_void_p(offs.ctypes.data)
+        t0 = time.perf_counter()
+        rc = lib.tmk_links_process_samples(h, p_x, n_links * n_per, p_offs, p_lens, p_recs, rec_cap, C.byref(nr), p_pl, pay_cap, C.byref(npl))
+        times.append(time.perf_counter() - t0)
+        eng._check(rc)
+        got.append((recs[:nr.value].copy(), pl[:npl.value].copy()))
+    ms = np.array(times[5:]) * 1e3
+    res = {"workload": f"{n_links} links x {n_polls} polls of {poll} samples (25 ms at 48 kHz), 4B5B frames, AWGN 15 dB, captures resident in HBM",
+           "ms_per_poll": float(np.median(ms)), "ms_per_poll_p99": float(np.percentile(ms, 99)),
+           "realtime_factor": 25.0 / float(np.median(ms)), "Msamples_per_s": n_links * poll / float(np.median(ms)) / 1e3,
+           "frames_ok": int(sum(int((r["status"] == 0).sum()) for r, _ in got))}
+    if orc is not None:
+        same, n_cmp = True, 0
+        for i in np.unique(np.linspace(0, n_links - 1, check_links).astype(np.int64)):
+            x = np.zeros(n_per, np.float32)
+            eng.d2h(x, d_x + int(i) * n_per * 4)
+            want, wpl, feed = orc.decode_feeds(cfg, x, [poll] * n_polls, stream_id=int(i))
+            for k in range(n_polls):
+                r, p = got[k]
+                g, w = r[r["stream"] == i], want[feed == k]
+                n_cmp += len(w)
+                same = same and records_equal(g, p, w, wpl)
+        res["parity"] = "bit-exact" if same else "MISMATCH"
+        res["parity_sample"] = f"{check_links} links, {n_cmp} records, poll by poll"
+    bank.close()
+    eng.device_free(d_x)
+    return res
+
+
 def mcm_leg(eng, orc, tmkphy, hbm, n_s, n_per, check_streams=4):
     """BASELINE config 3 as worded: FSK / OFDM demodulation with the batched FFT over n_s captures x n_per samples
     (half FSK, half OFDM), 3-tap multipath + AWGN sweep. Build-defined specification (the reference has no FSK / OFDM /
@@ -505,6 +556,7 @@ def main():
     ap.add_argument("--cpu-max-captures", type=int, default=0, help="bound the cpu_baseline sample (0: by time)")
     ap.add_argument("--no-numa-bind", action="store_true", help="do not bind the rank to the GPU's NUMA node")
     ap.add_argument("--no-ask", action="store_true", help="skip the chirp+BPSK (examples/ask.rs) leg")
+    ap.add_argument("--no-links", action="store_true", help="skip the carried-state streaming (links) leg")
     ap.add_argument("--no-pcm16", action="store_true", help="skip the 16-bit PCM end-to-end leg")
     ap.add_argument("--no-cpu", action="store_true")
     ap.add_argument("--no-configs", action="store_true", help="skip the C2-Manchester / chunk / C3 / C4 / C5 legs")
@@ -721,6 +773,8 @@ def main():
         out["chirp_bpsk"] = ask_leg(eng, tmkphy, orc, d_x, n_s, n_per, hbm)
     dec.free()
     eng.device_free(d_x)
+    if rank == 0 and world == 1 and not args.no_links:
+        out["links"] = links_leg(eng, orc, tmkphy)
     if run_cfgs and world == 1:
         if "c3" in want_cfg:
             # C3: 16 384 captures x 2^20 samples (68.7 GB resident), 3-tap multipath + AWGN sweep; half 4B5B, half Manchester
