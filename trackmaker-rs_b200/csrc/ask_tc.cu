@@ -38,10 +38,12 @@ constexpr int kRowLen = 64, kRows = 128;
 constexpr int kTile = kRows * kRowLen;         // 8192 window starts per tile
 constexpr int kHalves = 8;                     // taps reach sample offset 63 + 439 = 502 < 8 x 64
 constexpr int kGroups = 16 + kHalves - 1;      // row groups a per stage
-constexpr int kTeams = 2, kStages = kTeams, kAccStages = kTeams;
+constexpr int kTeams = 2, kStages = 4, kAccStages = 4;  // tile j of a CTA: team j % 2, shared-memory stage and TMEM stage j % 4
+constexpr int kSlices = (kPre + 63 + 7) / 8;            // K slices of 8 taps that reach a tap: 63
+constexpr int kWBlocks = kSlices + 7;                   // blocks of the Toeplitz strip (see the kernel): 70 x 256 B
 constexpr int kEpiWarps = 4 * kTeams;
 constexpr int kThreads = 32 * (2 + kEpiWarps);
-constexpr uint32_t kGroupBytes = 2048, kAtomBytes = 1024, kTBytes = 16384;
+constexpr uint32_t kGroupBytes = 2048, kAtomBytes = 1024, kWBytes = kWBlocks * 256;
 constexpr uint32_t kStageBytes = kGroups * kGroupBytes;
 constexpr uint32_t kIdesc = (1u << 4) | (2u << 7) | (2u << 10) | (uint32_t(kRowLen >> 3) << 17) | (uint32_t(kRows >> 4) << 24);
 constexpr float kC = 0.984375f, kInv64 = 0.015625f;
@@ -110,6 +112,11 @@ __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
 __device__ __forceinline__ uint64_t umma_desc(uint32_t saddr, uint32_t sbo) {
     return uint64_t((saddr >> 4) & 0x3fffu) | (1ull << 16) | (uint64_t((sbo >> 4) & 0x3fffu) << 32) | (1ull << 46) | (2ull << 61);
 }
+// K-major, no swizzle: core matrices of 8 rows x 16 B; LBO = bytes between the two core matrices of an instruction's K = 8,
+// SBO = bytes between 8-row groups
+__device__ __forceinline__ uint64_t umma_desc_ns(uint32_t saddr, uint32_t lbo, uint32_t sbo) {
+    return uint64_t((saddr >> 4) & 0x3fffu) | (uint64_t((lbo >> 4) & 0x3fffu) << 16) | (uint64_t((sbo >> 4) & 0x3fffu) << 32) | (1ull << 46);
+}
 __device__ __forceinline__ void umma_tf32(uint32_t tmem_d, uint64_t adesc, uint64_t bdesc, uint32_t idesc, uint32_t accumulate) {
     asm volatile(
         "{\n"
@@ -117,6 +124,31 @@ __device__ __forceinline__ void umma_tf32(uint32_t tmem_d, uint64_t adesc, uint6
         "setp.ne.b32 p, %4, 0;\n"
         "tcgen05.mma.cta_group::1.kind::tf32 [%0], %1, %2, %3, p;\n"
         "}\n" ::"r"(tmem_d), "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate) : "memory");
+}
+// the same with the descriptors as (low word, high word): per instruction only the low words change, by a constant — one add
+// each, where the 64-bit form recomputed shift, mask and merge (13 SASS instructions and ~49 cycles per MMA in the one
+// issuing thread: the filter was bound by the ISSUE of its 63 MMAs per tile, not by the tensor pipe)
+__device__ __forceinline__ void umma_tf32_lohi(uint32_t tmem_d, uint32_t alo, uint32_t ahi, uint32_t blo, uint32_t bhi, uint32_t idesc,
+                                               uint32_t accumulate) {
+    asm volatile(
+        "{\n"
+        ".reg .pred p;\n"
+        ".reg .b64 da, db;\n"
+        "mov.b64 da, {%1, %2};\n"
+        "mov.b64 db, {%3, %4};\n"
+        "setp.ne.b32 p, %6, 0;\n"
+        "tcgen05.mma.cta_group::1.kind::tf32 [%0], da, db, %5, p;\n"
+        "}\n" ::"r"(tmem_d), "r"(alo), "r"(ahi), "r"(blo), "r"(bhi), "r"(idesc), "r"(accumulate) : "memory");
+}
+__device__ __forceinline__ uint32_t elect_one() {
+    uint32_t pred;
+    asm volatile(
+        "{\n"
+        ".reg .pred P;\n"
+        "elect.sync _|P, 0xffffffff;\n"
+        "selp.b32 %0, 1, 0, P;\n"
+        "}\n" : "=r"(pred));
+    return pred;
 }
 __device__ __forceinline__ void umma_commit(uint64_t* bar) {
     asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_u32(bar)) : "memory");
@@ -145,7 +177,7 @@ ask_tc_kernel(const __grid_constant__ TcMaps maps, int n_maps, const float* __re
     uint8_t* smem_raw = smem_dyn + ((1024u - (smem_u32(smem_dyn) & 1023u)) & 1023u);
     uint8_t* stage0 = smem_raw;
     uint8_t* tmat = smem_raw + kStages * kStageBytes;
-    Smem& sm = *reinterpret_cast<Smem*>(tmat + kHalves * kTBytes);
+    Smem& sm = *reinterpret_cast<Smem*>(tmat + ((kWBytes + 127u) & ~127u));
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
 
     if (threadIdx.x == 0) {
@@ -164,13 +196,19 @@ ask_tc_kernel(const __grid_constant__ TcMaps maps, int n_maps, const float* __re
                      "n"(kAccStages * kRowLen) : "memory");
         asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
     }
-    // the Toeplitz operands T_h[n][k] = chirp[64 h + k - n]
-    for (uint32_t i = threadIdx.x; i < uint32_t(kHalves) * 64 * 64; i += kThreads) {
-        const uint32_t h = i >> 12, n = (i >> 6) & 63, k = i & 63;
-        const int t = int(64 * h + k) - int(n);
-        const float v = (t >= 0 && t < kPre) ? __ldg(chirp + t) : 0.0f;
-        const uint32_t c = k >> 5, kc = (k >> 2) & 7;
-        *reinterpret_cast<float*>(tmat + h * kTBytes + c * 8192 + (n >> 3) * kAtomBytes + (n & 7) * 128 + ((kc ^ (n & 7)) << 4) + (k & 3) * 4) = v;
+    // The Toeplitz operand of K slice s (taps 8 s .. 8 s + 7): B_s[n][kk] = chirp[8 s + kk - n], n = 8 u + v
+    //   = chirp[8 (s - u) + kk - v]: a function of w = s - u and (v, kk) only. So ONE strip of 8 x 8 blocks
+    //   W_w[v][kk] = chirp[8 w + kk - v], w = 62 .. -7 (stored in that order: block j holds w = 62 - j), serves every slice:
+    //   B_s is the eight consecutive blocks j = 62 - s + u, u = 0 .. 7 — the operand descriptor of slice s points at block 62 - s
+    //   with a stride of one block between the 8-row groups. 70 blocks x 256 B = 17.5 KB instead of 8 x 16 KB of explicit
+    //   T_h, which leaves room for FOUR stages of samples (the kernel was bound by its two-stage pipeline: 4.0 ms at C2
+    //   with 2.5 ms of MMA). Layout of a block: tcgen05's K-major layout without swizzle, two core matrices (taps 0-3, 4-7)
+    //   of 8 rows x 16 B.
+    for (uint32_t i = threadIdx.x; i < uint32_t(kWBlocks) * 64; i += kThreads) {
+        const uint32_t j = i >> 6, v = (i >> 3) & 7, kk = i & 7;
+        const int t = 8 * (kSlices - 1 - int(j)) + int(kk) - int(v);
+        const float val = (t >= 0 && t < kPre) ? __ldg(chirp + t) : 0.0f;
+        *reinterpret_cast<float*>(tmat + j * 256 + (kk >> 2) * 128 + v * 16 + (kk & 3) * 4) = val;
     }
     asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
     asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
@@ -195,9 +233,11 @@ ask_tc_kernel(const __grid_constant__ TcMaps maps, int n_maps, const float* __re
     if (warp == 0) {
         // ================================================================ producer
         uint32_t j = 0;
+        TileDescA nxt = load_desc(blockIdx.x);  // (the descriptor of the next tile is in flight while this one is staged)
         for (uint32_t tl = blockIdx.x; tl < n_tiles; tl += gridDim.x, ++j) {
-            const TileDescA td = load_desc(tl);
-            const uint32_t s = j % kTeams, ph = (j / kTeams) & 1u;
+            const TileDescA td = nxt;
+            nxt = load_desc(tl + gridDim.x);
+            const uint32_t s = j % kStages, ph = (j / kStages) & 1u;
             mbar_wait(&sm.empty[s], ph ^ 1u);
             uint8_t* dst = stage0 + s * kStageBytes;
             const uint64_t start = td.start;
@@ -237,22 +277,25 @@ ask_tc_kernel(const __grid_constant__ TcMaps maps, int n_maps, const float* __re
         // ================================================================ MMA issuer
         uint32_t j = 0;
         for (uint32_t tl = blockIdx.x; tl < n_tiles; tl += gridDim.x, ++j) {
-            const uint32_t s = j % kTeams, ph = (j / kTeams) & 1u;
+            const uint32_t s = j % kStages, ph = (j / kStages) & 1u;  // (kAccStages == kStages: the same index and phase)
             mbar_wait(&sm.full[s], ph);
             mbar_wait(&sm.tempty[s], ph ^ 1u);
             asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
-            if (lane == 0) {
-                const uint32_t a0 = smem_u32(stage0 + s * kStageBytes), b0 = smem_u32(tmat);
+            if (elect_one()) {
+                const uint64_t ad = umma_desc(smem_u32(stage0 + s * kStageBytes), kGroupBytes), bd = umma_desc_ns(smem_u32(tmat), 128, 256);
+                const uint32_t alo = uint32_t(ad), ahi = uint32_t(ad >> 32), blo = uint32_t(bd), bhi = uint32_t(bd >> 32);
                 const uint32_t d = tmem_base + s * kRowLen;
                 uint32_t acc = 0;
+                // (the start-address field holds address >> 4 in 14 bits; shared memory ends below 2^18, so adding a byte
+                //  offset >> 4 to the low word never carries out of the field)
 #pragma unroll
                 for (int h = 0; h < kHalves; ++h) {
                     const int left = kPre + 63 - 64 * h;  // taps reach k < left in this half
                     const int ksteps = left >= 64 ? 8 : (left + 7) / 8;
 #pragma unroll
                     for (int kk = 0; kk < ksteps; ++kk) {
-                        umma_tf32(d, umma_desc(a0 + h * kGroupBytes + (kk >> 2) * kAtomBytes + (kk & 3) * 32, kGroupBytes),
-                                  umma_desc(b0 + h * kTBytes + (kk >> 2) * 8192 + (kk & 3) * 32, kAtomBytes), kIdesc, acc);
+                        umma_tf32_lohi(d, alo + ((h * kGroupBytes + (kk >> 2) * kAtomBytes + (kk & 3) * 32) >> 4), ahi,
+                                       blo + ((uint32_t(kSlices - 1 - (8 * h + kk)) * 256u) >> 4), bhi, kIdesc, acc);
                         acc = 1;
                     }
                 }
@@ -267,17 +310,30 @@ ask_tc_kernel(const __grid_constant__ TcMaps maps, int n_maps, const float* __re
         const int m = 32 * q + lane;   // MMA row = TMEM lane
         const int a = m >> 3, b = m & 7;
         const int rho = 16 * b + a;    // capture row of the tile
-        const uint32_t s = team;
         uint32_t cnt = 0;
         float* rs = sm.rowsum[team];
-        for (uint32_t tl = blockIdx.x + team * gridDim.x; tl < n_tiles; tl += kTeams * gridDim.x) {
-            const TileDescA td = load_desc(tl);
-            const uint32_t ph = cnt++ & 1u;
-            const uint64_t wrow = uint64_t(rho) * kRowLen;
-            const int nvalid = wrow >= td.nwin ? 0 : (td.nwin - wrow < uint64_t(kRowLen) ? int(td.nwin - wrow) : kRowLen);
-            // the exact power before the first sample of the word that holds this row's first position (issued early)
+        // The descriptor of a tile and, behind it, the power checkpoint of the row are two dependent trips to L2 / HBM: both are
+        // fetched one and two tiles ahead (47 % of the kernel's samples sat on the first use of the checkpoint before)
+        const uint64_t wrow = uint64_t(rho) * kRowLen;
+        auto valid_of = [&](const TileDescA& d) -> int {
+            return wrow >= d.nwin ? 0 : (d.nwin - wrow < uint64_t(kRowLen) ? int(d.nwin - wrow) : kRowLen);
+        };
+        // the exact power before the first sample of the word that holds the row's first position
+        auto chk_of = [&](const TileDescA& d) -> float { return valid_of(d) > 0 ? __ldg(pchk + ((d.pos0 + wrow) >> 5)) : 0.0f; };
+        const uint32_t step = kTeams * gridDim.x;
+        uint32_t tl = blockIdx.x + team * gridDim.x;
+        TileDescA td_cur = load_desc(tl), td_nxt = load_desc(tl + step);
+        float p_cur = chk_of(td_cur);
+        for (; tl < n_tiles; tl += step) {
+            const TileDescA td = td_cur;
+            float p = p_cur;
+            td_cur = td_nxt;
+            p_cur = chk_of(td_cur);
+            td_nxt = load_desc(tl + 2 * step);
+            const uint32_t j = team + kTeams * cnt++;  // this CTA's tile counter
+            const uint32_t s = j % kStages, ph = (j / kStages) & 1u;
+            const int nvalid = valid_of(td);
             const uint64_t bit0 = td.pos0 + wrow;  // 32 x global word + sample in the word, of the row's first position (bit0 % 32 == 23)
-            float p = nvalid > 0 ? __ldg(pchk + (bit0 >> 5)) : 0.0f;
             mbar_wait(&sm.full[s], ph);
             const uint8_t* stage = stage0 + s * kStageBytes;
             const uint8_t* row = stage + a * kGroupBytes + b * 128;
@@ -432,7 +488,7 @@ int tmk_ask_tc_filter(tmk_engine* e, const float* dx, uint64_t total_samples, ui
     const TileDescA* td = reinterpret_cast<const TileDescA*>(static_cast<char*>(e->d_ask_tc.p) +
                                                              (3 * arr + sizeof(uint32_t) * (n_streams + 1) + 31) / 32 * 32);
     static int sms = 0;
-    const size_t smem = size_t(kStages) * kStageBytes + size_t(kHalves) * kTBytes + sizeof(Smem) + 1024;
+    const size_t smem = size_t(kStages) * kStageBytes + ((kWBytes + 127u) & ~127u) + sizeof(Smem) + 1024;
     if (sms == 0) {
         cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, e->device);
         CK(cudaFuncSetAttribute(ask_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, int(smem)));
