@@ -1,0 +1,2 @@
+ncu --set full --import-source on --clock-control none -k regex:scan_tc_kernel -c 1 -o gpurun_out/scantc55 python bench.py --no-configs --no-links --no-ask --e2e-steps 0 --no-cpu --steps 1 --warmup 1 > /dev/null 2>&1
+ls -la gpurun_out/scantc55.ncu-rep

@@ -173,6 +173,30 @@ __device__ __forceinline__ void umma_tf32(uint32_t tmem_d, uint64_t adesc, uint6
         "tcgen05.mma.cta_group::1.kind::tf32 [%0], %1, %2, %3, p;\n"
         "}\n" ::"r"(tmem_d), "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate) : "memory");
 }
+// the same with the descriptors as (low word, high word): per instruction only the low words change, by a constant
+// (see ask_tc.cu: 6 SASS instructions per MMA in the one issuing thread instead of 13 and a branch)
+__device__ __forceinline__ void umma_tf32_lohi(uint32_t tmem_d, uint32_t alo, uint32_t ahi, uint32_t blo, uint32_t bhi, uint32_t idesc,
+                                               uint32_t accumulate) {
+    asm volatile(
+        "{\n"
+        ".reg .pred p;\n"
+        ".reg .b64 da, db;\n"
+        "mov.b64 da, {%1, %2};\n"
+        "mov.b64 db, {%3, %4};\n"
+        "setp.ne.b32 p, %6, 0;\n"
+        "tcgen05.mma.cta_group::1.kind::tf32 [%0], da, db, %5, p;\n"
+        "}\n" ::"r"(tmem_d), "r"(alo), "r"(ahi), "r"(blo), "r"(bhi), "r"(idesc), "r"(accumulate) : "memory");
+}
+__device__ __forceinline__ uint32_t elect_one() {
+    uint32_t pred;
+    asm volatile(
+        "{\n"
+        ".reg .pred P;\n"
+        "elect.sync _|P, 0xffffffff;\n"
+        "selp.b32 %0, 1, 0, P;\n"
+        "}\n" : "=r"(pred));
+    return pred;
+}
 __device__ __forceinline__ void umma_commit(uint64_t* bar) {
     asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_u32(bar)) : "memory");
 }
@@ -220,7 +244,8 @@ __device__ __forceinline__ bool tc_window(float Dv, float e, float kap, bool val
 // staged samples, candidate mask and row statistics. `row`: the thread's row in the stage (un-swizzle with b).
 template <int P, bool FULL>
 __device__ __forceinline__ void epi_row(const uint8_t* __restrict__ row, int b, uint32_t taddr, float kap, int nvalid,
-                                        uint64_t* tempty, int lane, float* __restrict__ dbg, RowStat& o, uint32_t (&mask)[2]) {
+                                        uint64_t* tfull, uint32_t tphase, uint64_t* tempty, int lane, float* __restrict__ dbg,
+                                        RowStat& o, uint32_t (&mask)[2]) {
     auto chunk = [&](int c) -> float4 {  // samples 4 c .. 4 c + 3 counted from the row start
         return *reinterpret_cast<const float4*>(row + (c >> 4) * kGroupBytes + ((c >> 3) & 1) * kAtomBytes + (((c & 7) ^ b) << 4));
     };
@@ -233,6 +258,10 @@ __device__ __forceinline__ void epi_row(const uint8_t* __restrict__ row, int b, 
         e = fmaf(v.z, v.z, e);
         e = fmaf(v.w, v.w, e);
     }
+    // (the seed energy needs the samples only: it runs while the tile's MMAs are still in flight — a fresh profile had 38 % of
+    //  the kernel's samples on this wait when it stood in front of the seed sum)
+    mbar_wait(tfull, tphase);  // the dot products are in TMEM
+    asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
 #pragma unroll
     for (int half = 0; half < 2; ++half) {
         float D[32];
@@ -405,17 +434,19 @@ scan_tc_kernel(const __grid_constant__ TcMaps maps, int n_maps, const float* __r
             mbar_wait(&sm.full[s], ph);
             mbar_wait(&sm.tempty[s], ph ^ 1u);
             asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
-            if (lane == 0) {
-                const uint32_t a0 = smem_u32(stage0 + s * kStageBytes), b0 = smem_u32(tmat);
+            if (elect_one()) {
+                const uint64_t ad = umma_desc(smem_u32(stage0 + s * kStageBytes), kGroupBytes), bd = umma_desc(smem_u32(tmat), kAtomBytes);
+                const uint32_t alo = uint32_t(ad), ahi = uint32_t(ad >> 32), blo = uint32_t(bd), bhi = uint32_t(bd >> 32);
                 const uint32_t d = tmem_base + s * kRowLen;
                 uint32_t acc = 0;
+                // (the start-address field holds address >> 4 in 14 bits; shared memory ends below 2^18: no carry out of it)
 #pragma unroll
                 for (int h = 0; h < S::kHalves; ++h) {
                     const int ksteps = (P + 63 - 64 * h) >= 64 ? 8 : (P + 63 - 64 * h + 7) / 8;  // taps reach k < P + 63
 #pragma unroll
                     for (int kk = 0; kk < ksteps; ++kk) {  // K = 8 samples per instruction: column block kk / 4, 32 B further per step
-                        umma_tf32(d, umma_desc(a0 + h * kGroupBytes + (kk >> 2) * kAtomBytes + (kk & 3) * 32, kGroupBytes),
-                                  umma_desc(b0 + h * kTBytes + (kk >> 2) * 8192 + (kk & 3) * 32, kAtomBytes), kIdesc, acc);
+                        umma_tf32_lohi(d, alo + ((h * kGroupBytes + (kk >> 2) * kAtomBytes + (kk & 3) * 32) >> 4), ahi,
+                                       blo + ((h * kTBytes + (kk >> 2) * 8192 + (kk & 3) * 32) >> 4), bhi, kIdesc, acc);
                         acc = 1;
                     }
                 }
@@ -445,15 +476,13 @@ scan_tc_kernel(const __grid_constant__ TcMaps maps, int n_maps, const float* __r
             const int nvalid = wrow >= nwin ? 0 : (nwin - wrow < uint64_t(kRowLen) ? int(nwin - wrow) : kRowLen);
             const bool full = nwin >= uint64_t(TMK_TILE);
             mbar_wait(&sm.full[s], ph);    // the samples are visible to this thread
-            mbar_wait(&sm.tfull[s], ph);   // the dot products are in TMEM
-            asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
             const uint8_t* row = stage0 + s * kStageBytes + a * kGroupBytes + b * 128;  // the row (and, + kGroupBytes, the rows behind it)
             const uint32_t taddr = tmem_base + (uint32_t(32 * q) << 16) + s * kRowLen;
             RowStat o{__int_as_float(0x7f800000), 0.0f, 0.0f, 0u};
             uint32_t mask[2];
             float* dbg = dbg_dot != nullptr ? dbg_dot + td.start + wrow : nullptr;
-            if (full) epi_row<P, true>(row, b, taddr, kap, kRowLen, &sm.tempty[s], lane, dbg, o, mask);
-            else epi_row<P, false>(row, b, taddr, kap, nvalid, &sm.tempty[s], lane, dbg, o, mask);
+            if (full) epi_row<P, true>(row, b, taddr, kap, kRowLen, &sm.tfull[s], ph, &sm.tempty[s], lane, dbg, o, mask);
+            else epi_row<P, false>(row, b, taddr, kap, nvalid, &sm.tfull[s], ph, &sm.tempty[s], lane, dbg, o, mask);
             // ---- the staged samples are no longer needed
             __syncwarp();
             if (lane == 0) mbar_arrive(&sm.empty[s]);
