@@ -1377,7 +1377,11 @@ int tmk_ask_sync_device(tmk_engine* e, const float* samples, uint64_t total_samp
         if (pchk != nullptr) {
             const uint32_t g0 = sd[s0].seg_base, g1 = s1 < n_streams ? sd[s1].seg_base : uint32_t(segs);
             if (g1 > g0) {
-                CK(cudaFuncSetAttribute(ask_power_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kPwSmem));  // (per device: no static flag)
+                static TmkPerDevice pw_attr;
+                if (!pw_attr.done(e->device)) {
+                    CK(cudaFuncSetAttribute(ask_power_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kPwSmem));
+                    pw_attr.set(e->device);
+                }
                 ask_power_kernel<<<(g1 - g0 + kPwWarps * 32 - 1) / (kPwWarps * 32), kPwWarps * 32, kPwSmem, st>>>(dx, ds, n_streams, g0, g1, pchk, seg_max, seg_u0, first_bad);
                 ask_power_check_kernel<<<(g1 - g0 + 127) / 128, 128, 0, st>>>(ds, n_streams, g0, g1, seg_max, seg_u0, first_bad, pchk);
                 e->launches += 2;
@@ -1391,10 +1395,10 @@ int tmk_ask_sync_device(tmk_engine* e, const float* samples, uint64_t total_samp
             if (direct) {
                 ask_scan_kernel<<<uint32_t(tiles), kThreads, 0, st>>>(dx, ds, n_streams, tab, static_cast<uint32_t*>(e->d_ask_bits.p));
             } else {
-                static bool attr = false;
-                if (!attr) {
+                static TmkPerDevice fft_attr;
+                if (!fft_attr.done(e->device)) {
                     CK(cudaFuncSetAttribute(ask_scan_fft_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, int(sizeof(FftSmem))));
-                    attr = true;
+                    fft_attr.set(e->device);
                 }
                 const float2* twg = reinterpret_cast<const float2*>(tab + kTabFft);
                 static int fft_ctas = 0;

@@ -487,11 +487,13 @@ int tmk_ask_tc_filter(tmk_engine* e, const float* dx, uint64_t total_samples, ui
     const size_t arr = sizeof(uint64_t) * n_streams;
     const TileDescA* td = reinterpret_cast<const TileDescA*>(static_cast<char*>(e->d_ask_tc.p) +
                                                              (3 * arr + sizeof(uint32_t) * (n_streams + 1) + 31) / 32 * 32);
-    static int sms = 0;
     const size_t smem = size_t(kStages) * kStageBytes + ((kWBytes + 127u) & ~127u) + sizeof(Smem) + 1024;
-    if (sms == 0) {
-        cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, e->device);
+    static TmkPerDevice attr;
+    int sms = 0;
+    CK(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, e->device));
+    if (!attr.done(e->device)) {
         CK(cudaFuncSetAttribute(ask_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, int(smem)));
+        attr.set(e->device);
     }
     TcMaps maps;
     std::memset(&maps, 0, sizeof maps);

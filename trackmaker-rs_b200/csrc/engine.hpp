@@ -1,6 +1,7 @@
 // engine.hpp — the engine object behind the C ABI and the small host helpers shared by the
 // translation units that implement entry points (engine.cu, ask.cu).
 #pragma once
+#include <atomic>
 #include <string>
 #include <vector>
 

@@ -559,13 +559,14 @@ template <int LC>
 int launch_tc(const float* samples, uint64_t total_samples, const TileDesc* tdesc, uint32_t n_tiles, float4* blk_info,
               uint32_t* cand_bits, uint32_t* cblk_list, unsigned int* cblk_count, float* dbg_dot, cudaStream_t st) {
     using S = Tc<LC>;
-    static int sms = 0;
     const size_t smem = size_t(kStages) * S::kGroups * kGroupBytes + size_t(S::kHalves) * 16384 + sizeof(Smem) + 1024;
-    if (sms == 0) {
-        int dev = 0;
-        cudaGetDevice(&dev);
-        cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+    static TmkPerDevice attr;  // (one per instantiation)
+    int sms = 0, dev = 0;
+    cudaGetDevice(&dev);
+    cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+    if (!attr.done(dev)) {
         cudaFuncSetAttribute(scan_tc_kernel<LC>, cudaFuncAttributeMaxDynamicSharedMemorySize, int(smem));
+        attr.set(dev);
     }
     // one tensor map per window of kMapWin samples (the box coordinate is a signed 32-bit sample index); a tile is
     // loaded through the map of the window its first sample lies in, which therefore reaches one tile past the window

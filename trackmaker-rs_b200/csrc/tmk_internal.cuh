@@ -14,7 +14,17 @@
 #include <cuda_runtime.h>
 #include <stdint.h>
 
+#include <atomic>
+
 #include "../../include/tmkphy.h"
+
+// cudaFuncSetAttribute is per DEVICE and costs ~25 us: a call site does it once per device (an engine may sit on any of them)
+struct TmkPerDevice {
+    std::atomic<uint64_t> mask{0};
+    bool done(int dev) const { return (mask.load(std::memory_order_acquire) >> (dev & 63)) & 1ull; }
+    void set(int dev) { mask.fetch_or(1ull << (dev & 63), std::memory_order_release); }
+};
+
 
 #ifdef TMK_SCAN_ARM_A        // build of the round-1 CUDA-core scan (scan_fast.cu), kept for the A/B of DESIGN.md §3.1
 #define TMK_BLK 480          // windows per block (candidate bitmap / energy summary granularity):
