@@ -334,8 +334,7 @@ static int decode_batch_impl(tmk_engine* e, const void* samples_v, bool pcm16, u
         return std::chrono::duration<double, std::micro>(std::chrono::steady_clock::now() - t).count();
     };
     CK(cudaSetDevice(e->device));
-    tmk_flush_stage_ms(e);
-    e->stage_pending = false;
+    e->stage_pending = false;  // (this call records the events again: stage times nobody asked for are dropped, not computed)
     Batch b;
     int rc = prepare_batch(e, total_samples, streams, n_streams, &b);
     if (rc != TMK_OK) return rc;
