@@ -221,6 +221,8 @@ void tmk_engine_destroy(tmk_engine* e) {
     e->d_small.release();
     if (e->h_small) cudaFreeHost(e->h_small);
     e->h_small = nullptr;
+    if (e->h_streams) cudaFreeHost(e->h_streams);
+    e->h_streams = nullptr;
     for (int i = 0; i < 6; ++i)
         if (e->ev[i]) cudaEventDestroy(e->ev[i]);
     for (int i = 0; i < 2; ++i)
@@ -330,6 +332,7 @@ static int decode_batch_impl(tmk_engine* e, const void* samples_v, bool pcm16, u
     if (n_streams == 0) return TMK_OK;
     static const bool trace = getenv("TMK_TRACE_HOST") != nullptr;  // host-side time line of a small batch on stderr (us)
     const auto t_in = std::chrono::steady_clock::now();
+    double tr[8] = {0, 0, 0, 0, 0, 0, 0, 0};  // trace stamps: [0] batch prepared, [1] buffers reserved, [2] scan, [3] cluster, [4] walk enqueued
     auto us_since = [&](std::chrono::steady_clock::time_point t) {
         return std::chrono::duration<double, std::micro>(std::chrono::steady_clock::now() - t).count();
     };
@@ -338,6 +341,7 @@ static int decode_batch_impl(tmk_engine* e, const void* samples_v, bool pcm16, u
     Batch b;
     int rc = prepare_batch(e, total_samples, streams, n_streams, &b);
     if (rc != TMK_OK) return rc;
+    if (trace) tr[0] = us_since(t_in);
     // carried PhyDecoder state of the links module (links.cu): entry state in, exit state out
     const TmkLinkState* link_init = e->link_init;
     TmkLinkState* link_final = e->link_final;
@@ -356,7 +360,25 @@ static int decode_batch_impl(tmk_engine* e, const void* samples_v, bool pcm16, u
     }
 
     CK(e->d_streams.reserve(sizeof(TmkStreamDev) * n_streams));
-    CK(cudaMemcpyAsync(e->d_streams.p, b.sd.data(), sizeof(TmkStreamDev) * n_streams, cudaMemcpyHostToDevice, e->stream));
+    {
+        // (every call ends with a synchronisation of e->stream, so the staging buffer is free again here)
+        const size_t sb = sizeof(TmkStreamDev) * n_streams;
+        const void* src = b.sd.data();
+        if (sb <= (8u << 20)) {
+            if (e->h_streams_cap < sb) {
+                if (e->h_streams) cudaFreeHost(e->h_streams);
+                e->h_streams = nullptr;
+                e->h_streams_cap = 0;
+                if (cudaHostAlloc(&e->h_streams, sb + sb / 2 + 4096, cudaHostAllocDefault) == cudaSuccess) e->h_streams_cap = sb + sb / 2 + 4096;
+                else cudaGetLastError();
+            }
+            if (e->h_streams_cap >= sb) {
+                std::memcpy(e->h_streams, b.sd.data(), sb);
+                src = e->h_streams;
+            }
+        }
+        CK(cudaMemcpyAsync(e->d_streams.p, src, sb, cudaMemcpyHostToDevice, e->stream));
+    }
     CK(cudaEventRecord(e->ev[0], e->stream));
     // Host-resident captures are staged in chunks of whole streams: the copy of chunk g+1 (copy stream)
     // overlaps the scan + walk of chunk g (compute stream). Device-resident captures are one chunk.
@@ -562,6 +584,7 @@ static int decode_batch_impl(tmk_engine* e, const void* samples_v, bool pcm16, u
         return f;
     };
 
+    if (trace) tr[1] = us_since(t_in);
     CK(cudaEventRecord(e->ev[1], e->stream));
 #ifdef TMK_SCAN_ARM_A
     const bool fuse_dir = false;
@@ -603,6 +626,7 @@ static int decode_batch_impl(tmk_engine* e, const void* samples_v, bool pcm16, u
                                        const_cast<uint32_t*>(fast.cblk_list), fast.cblk_count, e->stream,
                                        static_cast<char*>(e->d_tile_desc.p) + tmk_scan_tile_desc_bytes(ch.t0) * (ch.t0 ? 1 : 0), nullptr, fuse_dir);
         if (chunks.size() == 1) CK(cudaEventRecord(e->ev[2], e->stream));
+        if (trace) tr[2] = us_since(t_in);
         uint8_t* dpay = dpay_cur;
         // The walks / cluster passes of different chunks overlap each other and the later scans (high-priority
         // streams). Within a chunk the walk follows the cluster pass; they CAN run side by side (the cluster
@@ -621,6 +645,7 @@ static int decode_batch_impl(tmk_engine* e, const void* samples_v, bool pcm16, u
         if (use_fast) {
             e->launches += tmk_launch_cluster(dx, ds, dtd, dp, dbi, dcb, fast, dpay, dev_pay_cap, dc, !serial_cluster, cs);
             if (one) CK(cudaEventRecord(e->ev[5], cs));
+            if (trace) tr[3] = us_since(t_in);
             if (serial_cluster && !one) {
                 CK(cudaEventRecord(e->wev[0], cs));
                 CK(cudaStreamWaitEvent(ws, e->wev[0], 0));
@@ -638,6 +663,7 @@ static int decode_batch_impl(tmk_engine* e, const void* samples_v, bool pcm16, u
                                        dev_rec_cap, dpay, dev_pay_cap, static_cast<uint32_t*>(e->d_cnt.p), dc, d_link, ws);
         }
         CK(cudaGetLastError());
+        if (trace) tr[4] = us_since(t_in);
     }
     if (chunks.size() != 1) CK(cudaEventRecord(e->ev[2], e->stream));  // end of the last scan
     if (chunks.size() != 1)
@@ -662,7 +688,9 @@ static int decode_batch_impl(tmk_engine* e, const void* samples_v, bool pcm16, u
         if (c_pay) CK(cudaMemcpyAsync(hs + sm_pay, sm + sm_pay, c_pay, cudaMemcpyDeviceToHost, e->stream));
         const double t_enq = trace ? us_since(t_in) : 0.0;
         CK(cudaStreamSynchronize(e->stream));
-        if (trace) fprintf(stderr, "tmk small batch: enqueued after %.1f us, synchronised after %.1f us\n", t_enq, us_since(t_in));
+        if (trace)
+            fprintf(stderr, "tmk small batch (us from entry): prepared %.1f, reserved %.1f, scan %.1f, cluster %.1f, walk %.1f, all enqueued %.1f, synchronised %.1f\n",
+                    tr[0], tr[1], tr[2], tr[3], tr[4], t_enq, us_since(t_in));
         const SmallHdr* hh = reinterpret_cast<const SmallHdr*>(hs);
         hc = hh->hc;
         n_exact = hh->n_exact;

@@ -49,6 +49,8 @@ struct tmk_engine {
     DevBuf d_small;             // small batches: counters + exit states + ordered records + payload in one block (engine.cu)
     void* h_small = nullptr;    // its pinned host mirror
     size_t h_small_cap = 0;
+    void* h_streams = nullptr;  // pinned staging of the stream descriptors (a copy out of pageable memory is staged by the runtime: ~8 us for 256 links)
+    size_t h_streams_cap = 0;
     DevBuf d_tile_desc;  // per-tile descriptors of the tensor-core scan (scan_tc.cu)
     DevBuf d_comm, d_wav, d_wavdesc;  // staging of the counter all-reduce (comm.cu); raw WAV bytes + descriptors (wav.cu)
     float* scan_dbg_dot = nullptr;    // set around tmk_scan_probe by tmk_scan_dot_probe (diagnostic)

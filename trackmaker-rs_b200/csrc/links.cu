@@ -30,6 +30,8 @@ struct tmk_links {
     std::vector<uint64_t> drained;   // samples removed from the front of the link's buffer so far
     std::vector<TmkLinkState> state; // buffer_offset (relative to the retained buffer), Decoding(frame_start)
     DevBuf d_work[2], d_new, d_desc;
+    void* h_desc = nullptr;  // pinned staging of the copy descriptors
+    size_t h_desc_cap = 0;
     int cur = 0;
     uint64_t calls = 0;
 };
@@ -108,6 +110,7 @@ void tmk_links_destroy(tmk_links* l) {
     l->d_work[1].release();
     l->d_new.release();
     l->d_desc.release();
+    if (l->h_desc) cudaFreeHost(l->h_desc);
     delete l;
 }
 
@@ -186,7 +189,24 @@ int tmk_links_process_samples(tmk_links* l, const float* samples, uint64_t total
     DevBuf& work = l->d_work[1 - l->cur];  // (the retained tails live in d_work[cur])
     CK(work.reserve((total_work + kPad + 4) * sizeof(float)));
     CK(l->d_desc.reserve(sizeof(CopyDesc) * n));
-    CK(cudaMemcpyAsync(l->d_desc.p, desc.data(), sizeof(CopyDesc) * n, cudaMemcpyHostToDevice, e->stream));
+    {
+        // (through pinned memory: the runtime stages a copy out of pageable memory itself, which costs more than this memcpy;
+        //  the decode below ends with a synchronisation of the stream, so the buffer is free again at the next call)
+        const size_t db = sizeof(CopyDesc) * n;
+        const void* src = desc.data();
+        if (l->h_desc_cap < db) {
+            if (l->h_desc) cudaFreeHost(l->h_desc);
+            l->h_desc = nullptr;
+            l->h_desc_cap = 0;
+            if (cudaHostAlloc(&l->h_desc, db + db / 2 + 4096, cudaHostAllocDefault) == cudaSuccess) l->h_desc_cap = db + db / 2 + 4096;
+            else cudaGetLastError();
+        }
+        if (l->h_desc_cap >= db) {
+            std::memcpy(l->h_desc, desc.data(), db);
+            src = l->h_desc;
+        }
+        CK(cudaMemcpyAsync(l->d_desc.p, src, db, cudaMemcpyHostToDevice, e->stream));
+    }
     assemble_kernel<<<n * kAsmParts + kAsmPadCtas, 256, 0, e->stream>>>(static_cast<const CopyDesc*>(l->d_desc.p), n,
                                                                         static_cast<const float*>(l->d_work[l->cur].p), d_new,
                                                                         static_cast<float*>(work.p), total_work, kPad);
