@@ -543,8 +543,10 @@ static int decode_batch_impl(tmk_engine* e, const void* samples_v, bool pcm16, u
     const uint64_t c_recs = std::min<uint64_t>(r_spec, 512 + n_streams / 2), c_pay = std::min<uint64_t>(dev_pay_cap, 32768 + 40ull * n_streams);
     const size_t sm_link = (sizeof(SmallHdr) + 15) & ~size_t(15);
     const size_t sm_recs = (sm_link + (link_final ? sizeof(TmkLinkState) * n_streams : 0) + 15) & ~size_t(15);
-    const size_t sm_pay = (sm_recs + sizeof(tmk_frame_rec) * r_spec + 15) & ~size_t(15);
-    const size_t sm_bytes = sm_pay + dev_pay_cap;
+    // block: [header | exit states | first c_recs records | payload | the other records] — header .. first payload bytes is ONE copy
+    const size_t sm_pay = (sm_recs + sizeof(tmk_frame_rec) * c_recs + 15) & ~size_t(15);
+    const size_t sm_rest = (sm_pay + dev_pay_cap + 15) & ~size_t(15);
+    const size_t sm_bytes = sm_rest + sizeof(tmk_frame_rec) * (r_spec - c_recs);
     char* sm = nullptr;
     if (small) {
         CK(e->d_small.reserve(sm_bytes));
@@ -680,14 +682,14 @@ static int decode_batch_impl(tmk_engine* e, const void* samples_v, bool pcm16, u
         e->launches += tmk_launch_order_small(static_cast<const uint32_t*>(e->d_cnt.p), static_cast<uint64_t*>(e->d_base.p), n_streams,
                                               static_cast<const tmk_frame_rec*>(e->d_recs_tmp.p), static_cast<const uint4*>(e->d_rec_ord.p), dc,
                                               dev_rec_cap, use_fast ? static_cast<const tmk_frame_rec*>(e->d_spec.p) : nullptr,
-                                              reinterpret_cast<tmk_frame_rec*>(sm + sm_recs), r_spec, &hdr->n_exact, e->stream);
+                                              reinterpret_cast<tmk_frame_rec*>(sm + sm_recs), c_recs, reinterpret_cast<tmk_frame_rec*>(sm + sm_rest),
+                                              r_spec, &hdr->n_exact, e->stream);
         CK(cudaGetLastError());
         CK(cudaEventRecord(e->ev[4], e->stream));
         char* hs = static_cast<char*>(e->h_small);
-        CK(cudaMemcpyAsync(hs, sm, sm_recs + sizeof(tmk_frame_rec) * c_recs, cudaMemcpyDeviceToHost, e->stream));
-        if (c_pay) CK(cudaMemcpyAsync(hs + sm_pay, sm + sm_pay, c_pay, cudaMemcpyDeviceToHost, e->stream));
+        CK(cudaMemcpyAsync(hs, sm, sm_pay + c_pay, cudaMemcpyDeviceToHost, e->stream));
         const double t_enq = trace ? us_since(t_in) : 0.0;
-        CK(cudaStreamSynchronize(e->stream));
+        CK(cudaStreamSynchronize(e->stream));  // (polling cudaStreamQuery instead measured the same: the runtime spins already)
         if (trace)
             fprintf(stderr, "tmk small batch (us from entry): prepared %.1f, reserved %.1f, scan %.1f, cluster %.1f, walk %.1f, all enqueued %.1f, synchronised %.1f\n",
                     tr[0], tr[1], tr[2], tr[3], tr[4], t_enq, us_since(t_in));
@@ -698,13 +700,13 @@ static int decode_batch_impl(tmk_engine* e, const void* samples_v, bool pcm16, u
         if (hc.n_recs <= dev_rec_cap && hc.n_payload <= dev_pay_cap && n_exact <= r_spec) {  // (r_spec <= rec_cap, dev_pay_cap <= payload_cap)
             if (n_exact > c_recs || hc.n_payload > c_pay) {  // a busy poll: the rest, now that the counts are known
                 if (n_exact > c_recs)
-                    CK(cudaMemcpyAsync(hs + sm_recs + sizeof(tmk_frame_rec) * c_recs, sm + sm_recs + sizeof(tmk_frame_rec) * c_recs,
-                                       sizeof(tmk_frame_rec) * (n_exact - c_recs), cudaMemcpyDeviceToHost, e->stream));
+                    CK(cudaMemcpyAsync(hs + sm_rest, sm + sm_rest, sizeof(tmk_frame_rec) * (n_exact - c_recs), cudaMemcpyDeviceToHost, e->stream));
                 if (hc.n_payload > c_pay)
                     CK(cudaMemcpyAsync(hs + sm_pay + c_pay, sm + sm_pay + c_pay, hc.n_payload - c_pay, cudaMemcpyDeviceToHost, e->stream));
                 CK(cudaStreamSynchronize(e->stream));
             }
-            if (n_exact) std::memcpy(recs, hs + sm_recs, sizeof(tmk_frame_rec) * n_exact);
+            if (n_exact) std::memcpy(recs, hs + sm_recs, sizeof(tmk_frame_rec) * std::min<uint64_t>(n_exact, c_recs));
+            if (n_exact > c_recs) std::memcpy(recs + c_recs, hs + sm_rest, sizeof(tmk_frame_rec) * (n_exact - c_recs));
             if (hc.n_payload) std::memcpy(payload, hs + sm_pay, hc.n_payload);
             if (link_final) std::memcpy(link_final, hs + sm_link, sizeof(TmkLinkState) * n_streams);
             *n_recs = n_exact;

@@ -233,7 +233,8 @@ int tmk_launch_replay_probe(const float* samples, const TmkStreamDev* streams, c
                             const uint64_t* ws, uint32_t n, float* out, unsigned long long* counts, cudaStream_t st);
 int tmk_launch_order_small(const uint32_t* stream_cnt, uint64_t* stream_base, uint32_t n_streams, const tmk_frame_rec* recs_in,
                            const uint4* rec_ord, const TmkCounters* counters, uint64_t slot_cap, const tmk_frame_rec* spec,
-                           tmk_frame_rec* recs_out, uint64_t out_cap, uint64_t* n_exact, cudaStream_t st);
+                           tmk_frame_rec* recs_out, uint64_t first_cap, tmk_frame_rec* recs_out_rest, uint64_t out_cap, uint64_t* n_exact,
+                           cudaStream_t st);
 int tmk_launch_order(const tmk_frame_rec* recs_in, const uint4* rec_ord, uint64_t n_recs,
                      const uint32_t* stream_cnt, uint64_t* stream_base, uint32_t n_streams,
                      const tmk_frame_rec* spec, tmk_frame_rec* recs_out, cudaStream_t st);

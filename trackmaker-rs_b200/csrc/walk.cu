@@ -2044,8 +2044,8 @@ __global__ void order_kernel(const tmk_frame_rec* __restrict__ in, const uint4* 
 __global__ void __launch_bounds__(1024)
 count_order_small_kernel(const uint32_t* __restrict__ cnt, uint64_t* __restrict__ base, uint32_t n_streams,
                          const tmk_frame_rec* __restrict__ in, const uint4* __restrict__ ord, const TmkCounters* __restrict__ counters,
-                         uint64_t slot_cap, const tmk_frame_rec* __restrict__ spec, tmk_frame_rec* __restrict__ out, uint64_t out_cap,
-                         uint64_t* __restrict__ n_exact) {
+                         uint64_t slot_cap, const tmk_frame_rec* __restrict__ spec, tmk_frame_rec* __restrict__ out, uint64_t first_cap,
+                         tmk_frame_rec* __restrict__ out_rest, uint64_t out_cap, uint64_t* __restrict__ n_exact) {
     __shared__ uint64_t warp_tot[32];
     __shared__ uint64_t carry_s;
     if (threadIdx.x == 0) carry_s = 0;
@@ -2092,7 +2092,8 @@ count_order_small_kernel(const uint32_t* __restrict__ cnt, uint64_t* __restrict_
         tmk_frame_rec r = ln.x != TMK_ENT_INVALID ? spec[ln.x] : in[i];
         r.stream = ln.z;
         r.corr = __uint_as_float(ln.w);
-        out[pos] = r;
+        if (pos < first_cap) out[pos] = r;  // (the first records sit next to the header and the payload: one copy brings a usual poll over)
+        else out_rest[pos - first_cap] = r;
     }
 }
 
@@ -2287,9 +2288,10 @@ int tmk_launch_replay_probe(const float* samples, const TmkStreamDev* streams, c
 
 int tmk_launch_order_small(const uint32_t* stream_cnt, uint64_t* stream_base, uint32_t n_streams, const tmk_frame_rec* recs_in,
                            const uint4* rec_ord, const TmkCounters* counters, uint64_t slot_cap, const tmk_frame_rec* spec,
-                           tmk_frame_rec* recs_out, uint64_t out_cap, uint64_t* n_exact, cudaStream_t st) {
+                           tmk_frame_rec* recs_out, uint64_t first_cap, tmk_frame_rec* recs_out_rest, uint64_t out_cap, uint64_t* n_exact,
+                           cudaStream_t st) {
     count_order_small_kernel<<<1, 1024, 0, st>>>(stream_cnt, stream_base, n_streams, recs_in, rec_ord, counters, slot_cap, spec, recs_out,
-                                                 out_cap, n_exact);
+                                                 first_cap, recs_out_rest, out_cap, n_exact);
     return 1;
 }
 
