@@ -87,3 +87,38 @@ def test_small_batch_buffers_on_the_limit(engine, orc, path_env):
     rc, recs, pl = call(len(want) + 7, len(wpl) + 100)
     assert rc == 0
     helpers.assert_records_equal(recs, pl, want, wpl, "roomy buffers")
+
+
+@pytest.mark.parametrize("small", [True, False])
+def test_fresh_engine_without_cluster_pass(orc, path_env, small):
+    """a NEW engine whose first decode runs without the cluster pass (TMK_NO_CLUSTER): the event that times the cluster pass
+    has never been recorded, and asking for its elapsed time used to leave a CUDA error behind for the next call"""
+    import tmkphy
+    saved = os.environ.get("TMK_NO_CLUSTER")
+    os.environ["TMK_NO_CLUSTER"] = "1"
+    if small:
+        os.environ.pop("TMK_NO_SMALL_PATH", None)
+    else:
+        os.environ["TMK_NO_SMALL_PATH"] = "1"
+    eng = tmkphy.Engine(0)
+    try:
+        rng = np.random.default_rng(79)
+        cf = tmkphy.make_config(FB, local_addr=1)
+        caps = [helpers.make_capture(orc, cf, rng, n_frames=12, snr_db=15.0)]
+        s, st = helpers.pack(caps, [cf], tmkphy)
+        want, wpl = oracle_records(orc, caps, [cf])
+        for _ in range(2):
+            recs, pl = eng.decode_batch(s, st)
+            helpers.assert_records_equal(recs, pl, want, wpl, "no cluster pass")
+            eng.last_stage_ms()
+            eng.debug_counters()
+        bank = tmkphy.PhyDecoderBank(eng, [cf])
+        got = bank.process_samples([caps[0][:5000]])
+        bank.close()
+        assert len(got[0]) >= 0
+    finally:
+        eng.close()
+        if saved is None:
+            os.environ.pop("TMK_NO_CLUSTER", None)
+        else:
+            os.environ["TMK_NO_CLUSTER"] = saved

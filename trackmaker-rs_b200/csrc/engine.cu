@@ -160,7 +160,7 @@ void tmk_flush_stage_ms(tmk_engine* e) {
     if (!e || !e->stage_pending) return;
     e->stage_pending = false;
     float cms = 0.f;
-    if (cudaEventElapsedTime(&cms, e->ev[2], e->ev[5]) == cudaSuccess) e->dbg[4] = uint64_t(cms * 1000.f);
+    if (e->ev5_valid && cudaEventElapsedTime(&cms, e->ev[2], e->ev[5]) == cudaSuccess) e->dbg[4] = uint64_t(cms * 1000.f);
     cudaEventElapsedTime(&e->stage_ms[3], e->ev[0], e->ev[1]);
     cudaEventElapsedTime(&e->stage_ms[0], e->ev[1], e->ev[2]);
     cudaEventElapsedTime(&e->stage_ms[1], e->ev[2], e->ev[3]);
@@ -337,6 +337,7 @@ static int decode_batch_impl(tmk_engine* e, const void* samples_v, bool pcm16, u
         return std::chrono::duration<double, std::micro>(std::chrono::steady_clock::now() - t).count();
     };
     CK(cudaSetDevice(e->device));
+    e->ev5_valid = false;
     e->stage_pending = false;  // (this call records the events again: stage times nobody asked for are dropped, not computed)
     Batch b;
     int rc = prepare_batch(e, total_samples, streams, n_streams, &b);
@@ -490,7 +491,12 @@ static int decode_batch_impl(tmk_engine* e, const void* samples_v, bool pcm16, u
     CK(e->d_base.reserve(sizeof(uint64_t) * (n_items + 1)));
     CK(e->d_next.reserve(sizeof(unsigned int) * (2 * chunks.size() + 1)));
     // cluster pass (walk.cu): candidate entries + speculative verdicts, per chunk its own list region / counter
-    const bool use_fast = b.n_blocks > 0 && b.n_blocks < (1ull << 31) && !getenv("TMK_NO_CLUSTER");
+    // (short polls of carried-state links walk faster without it: the cluster pass and the walk of a poll are two dependent
+    //  ~20 us single-warp frame decodes, one of which goes away — 256 links 0.131 -> 0.118 ms, one link 0.091 -> 0.075 ms)
+    uint64_t stream_samples = 0;  // (not total_samples: the links pad their working buffer)
+    for (uint32_t s = 0; s < n_streams; ++s) stream_samples += streams[s].n_samples;
+    const bool short_polls = link_init != nullptr && stream_samples < 16384ull * n_streams;
+    const bool use_fast = b.n_blocks > 0 && b.n_blocks < (1ull << 31) && !short_polls && !getenv("TMK_NO_CLUSTER");
     // (the walk of a chunk follows its cluster pass: running them side by side — the walk waiting for blocks the
     //  cluster pass had not reached — measured slower in round 1, 16.2 ms against 12.0 per step, and was removed)
     const bool serial_cluster = true;
@@ -646,7 +652,10 @@ static int decode_batch_impl(tmk_engine* e, const void* samples_v, bool pcm16, u
         }
         if (use_fast) {
             e->launches += tmk_launch_cluster(dx, ds, dtd, dp, dbi, dcb, fast, dpay, dev_pay_cap, dc, !serial_cluster, cs);
-            if (one) CK(cudaEventRecord(e->ev[5], cs));
+            if (one) {
+                CK(cudaEventRecord(e->ev[5], cs));
+                e->ev5_valid = true;
+            }
             if (trace) tr[3] = us_since(t_in);
             if (serial_cluster && !one) {
                 CK(cudaEventRecord(e->wev[0], cs));
@@ -779,7 +788,8 @@ static int decode_batch_impl(tmk_engine* e, const void* samples_v, bool pcm16, u
     for (int i = 0; i < 8; ++i) e->dbg[i] = hc.dbg[i];
     if (chunks.size() == 1) {  // [4]: device time of the cluster pass in microseconds (part of stage [1])
         float cms = 0.f;
-        if (cudaEventElapsedTime(&cms, e->ev[2], e->ev[5]) == cudaSuccess) e->dbg[4] = uint64_t(cms * 1000.f);
+        if (e->ev5_valid && cudaEventElapsedTime(&cms, e->ev[2], e->ev[5]) == cudaSuccess) e->dbg[4] = uint64_t(cms * 1000.f);
+        cudaGetLastError();  // (an event that was never recorded must not leave an error behind)
     }
     const bool overflow = n_exact > rec_cap || hc.n_recs > dev_rec_cap || hc.n_payload > payload_cap;
     if (!overflow && n_exact) {

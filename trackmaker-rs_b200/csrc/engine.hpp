@@ -62,6 +62,7 @@ struct tmk_engine {
     cudaEvent_t tev[2] = {};
     cudaEvent_t cev[6] = {};  // copy/compute hand-over of the chunked staging
     float stage_ms[4] = {0, 0, 0, 0};
+    bool ev5_valid = false;      // ev[5] (end of the cluster pass) was recorded by the last decode
     bool stage_pending = false;  // small batches leave the event arithmetic to whoever asks (tmk_flush_stage_ms)
     float ask_ms[2] = {0, 0};  // last tmk_ask_decode_batch: scan, walk
     uint64_t launches = 0;
