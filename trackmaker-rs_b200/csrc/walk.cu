@@ -1738,13 +1738,17 @@ cluster_kernel(const float* __restrict__ samples, const TmkStreamDev* __restrict
 }
 
 #ifndef TMK_WALK_CTAS
-// measured at C2 (walk kernel, ms): 2 CTAs/SM 3.72, 3 -> 3.71, 4 -> 3.99, 5 -> 4.21, 6 -> 4.44. The kernel is the sum of
+// measured at C2 (walk kernel, ms), round 1: 2 CTAs/SM 3.72, 3 -> 3.71, 4 -> 3.99, 5 -> 4.21, 6 -> 4.44. The kernel is the sum of
 // the streams' serial latencies; beyond 12 warps per SM every warp slows the others down (instruction-cache misses
 // of warps that sit in different stages of 136 KB of code, spills below 168 registers).
-#define TMK_WALK_CTAS 3
+// End of round 2 (the cluster pass has taken most of the work): 2 -> 2.92, 3 -> 3.05, 4 -> 3.37 at C2; with 2 CTAs per SM
+// (up to 255 registers) Manchester 2.55 -> 2.41, C4 2.69 -> 2.58, C3 (16 384 long captures: throughput, not latency) 36.1 -> 37.0.
+#define TMK_WALK_CTAS 2
 #endif
-template <bool SEG>  // SEG: the work items are segments of captures (segmented walk); the plain walk carries none of its state
-__global__ void __launch_bounds__(kWarpsPerCta * 32, TMK_WALK_CTAS)
+// CTAS: 2 for batches whose time is the serial latency of their slowest captures, 3 (168 registers) for batches of many long
+// captures, where throughput counts (C3 / C5: 12 288 work items and more)
+template <bool SEG, int CTAS>  // SEG: the work items are segments of captures (segmented walk); the plain walk carries none of its state
+__global__ void __launch_bounds__(kWarpsPerCta * 32, CTAS)
 walk_kernel(const float* __restrict__ samples, const TmkStreamDev* __restrict__ streams, uint32_t s0, uint32_t s1,
             unsigned int* __restrict__ next, TmkFast fast,
             const TmkPattern* __restrict__ patterns, const float4* __restrict__ blk_info,
@@ -2236,22 +2240,30 @@ int tmk_launch_walk(const float* samples, const TmkStreamDev* streams, uint32_t 
                     cudaStream_t st, TmkSeg seg) {
     if (s1 <= s0) return 0;
     const uint32_t n_streams = s1 - s0;
-    static int max_ctas = 0;
-    if (max_ctas == 0) {
+    static int max_ctas[2] = {0, 0};  // [0]: TMK_WALK_CTAS per SM, [1]: 3 per SM
+    if (max_ctas[0] == 0) {
         int dev = 0, sms = 0, per_sm = 0;
         cudaGetDevice(&dev);
         cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
-        cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, walk_kernel<false>, kWarpsPerCta * 32, 0);
-        max_ctas = sms * (per_sm > 0 ? per_sm : 1);
+        cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, walk_kernel<false, TMK_WALK_CTAS>, kWarpsPerCta * 32, 0);
+        max_ctas[0] = sms * (per_sm > 0 ? per_sm : 1);
+        cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, walk_kernel<false, 3>, kWarpsPerCta * 32, 0);
+        max_ctas[1] = sms * (per_sm > 0 ? per_sm : 1);
     }
+    const bool many = seg.items == nullptr && n_streams >= 12288;
     uint32_t grid = (n_streams + kWarpsPerCta - 1) / kWarpsPerCta;
-    if (grid > uint32_t(max_ctas)) grid = uint32_t(max_ctas);
+    if (grid > uint32_t(max_ctas[many ? 1 : 0])) grid = uint32_t(max_ctas[many ? 1 : 0]);
     if (seg.items != nullptr)
-        walk_kernel<true><<<grid, kWarpsPerCta * 32, 0, st>>>(samples, streams, s0, s1, next, fast, patterns, blk_info, cand_bits, recs,
-                                                              rec_ord, rec_cap, payload, payload_cap, stream_cnt, counters, link_out, seg);
+        walk_kernel<true, TMK_WALK_CTAS><<<grid, kWarpsPerCta * 32, 0, st>>>(samples, streams, s0, s1, next, fast, patterns, blk_info, cand_bits,
+                                                                             recs, rec_ord, rec_cap, payload, payload_cap, stream_cnt, counters,
+                                                                             link_out, seg);
+    else if (many)
+        walk_kernel<false, 3><<<grid, kWarpsPerCta * 32, 0, st>>>(samples, streams, s0, s1, next, fast, patterns, blk_info, cand_bits, recs,
+                                                                  rec_ord, rec_cap, payload, payload_cap, stream_cnt, counters, link_out, seg);
     else
-        walk_kernel<false><<<grid, kWarpsPerCta * 32, 0, st>>>(samples, streams, s0, s1, next, fast, patterns, blk_info, cand_bits, recs,
-                                                               rec_ord, rec_cap, payload, payload_cap, stream_cnt, counters, link_out, seg);
+        walk_kernel<false, TMK_WALK_CTAS><<<grid, kWarpsPerCta * 32, 0, st>>>(samples, streams, s0, s1, next, fast, patterns, blk_info, cand_bits,
+                                                                              recs, rec_ord, rec_cap, payload, payload_cap, stream_cnt, counters,
+                                                                              link_out, seg);
     return 1;
 }
 
