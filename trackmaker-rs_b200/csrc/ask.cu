@@ -864,7 +864,10 @@ __device__ __noinline__ void decode_frame(const AskCtx& c, int64_t s, uint8_t* b
     *id_out = words[0] >> 24;
 }
 
-__global__ void __launch_bounds__(128)
+#ifndef TMK_ASK_WALK_CTAS
+#define TMK_ASK_WALK_CTAS 5  // measured at C2 (walk, ms): 3 -> 6.82, 4 -> 6.80, 5 -> 6.38, 6 -> 6.50 (spills), 8 -> 6.88
+#endif
+__global__ void __launch_bounds__(128, TMK_ASK_WALK_CTAS)
 ask_walk_kernel(const float* __restrict__ samples, const AskStream* __restrict__ streams, uint32_t item0, uint32_t n_streams,
                 const float* __restrict__ tab, const uint32_t* __restrict__ wflag, const float* __restrict__ pchk,
                 tmk_ask_rec* __restrict__ recs, uint32_t* __restrict__ rec_ord, uint32_t* __restrict__ stream_cnt, uint64_t rec_cap,
