@@ -106,3 +106,64 @@ def test_report_frame_length_literal(orc):
     assert _abi.load_library().tmk_samples_for_bits(C.byref(cfg), 568) == 3408
     x = orc.modulate(tmkphy.make_config(MAN, local_addr=2), [(1, 0, 1, 2, bytes(64))], 0)
     assert len(x) == 96 + 3408
+
+
+def test_two_restatements_agree_chirp_modem(orc):
+    """Rows a14-a16 (examples/ask.rs:574-796): the C++ oracle (oracle/ask_modem.hpp) against the numpy-f32 restatement
+    written from the Rust (oracle/second_restatement_ask.py). Transmitter sample for sample; receiver record for record
+    (lock position, the bits of the locking sync power, id, verdict, the 108 decided bits) on noisy, scaled, clipped,
+    truncated and frame-free captures. The sine tables agree within one ulp: glibc's sinf, which the oracle (and the
+    Rust binary on linux-gnu) calls, is not correctly rounded, the second restatement's sine is — the receivers are
+    compared on the oracle's tables, and once more each on its own tables through a clean loopback."""
+    from oracle import second_restatement_ask as sra
+    pre2, car2 = sra.tables(4752)
+    pre, car = orc.ask_tables(4752)
+    for mine, theirs in ((pre2, pre), (car2, car)):
+        ulp = np.abs(mine.view(np.int32).astype(np.int64) - theirs.view(np.int32).astype(np.int64))
+        assert ulp.max() <= 1 and (ulp != 0).mean() < 0.03, (int(ulp.max()), float((ulp != 0).mean()))
+    assert pre2[0] == 0.0 and pre[0] == 0.0
+
+    rng = np.random.default_rng(2026)
+    n_recs = n_acc = n_rej = 0
+    for k in range(48):
+        nf = int(rng.integers(0, 5))
+        bits = rng.integers(0, 2, (nf, 100)).astype(np.uint8)
+        for f in range(nf):  # ids inside and outside 1..=100 (ask.rs:771)
+            ident = int(rng.integers(1, 101)) if rng.random() < 0.7 else int(rng.choice([0, 101, 200, 255]))
+            bits[f, :8] = [(ident >> (7 - j)) & 1 for j in range(8)]
+        g1 = rng.integers(0, 100, nf) if k % 3 else rng.integers(0, 3000, nf)
+        g2 = rng.integers(0, 100, nf)
+        x = orc.ask_modulate(bits, g1, g2) if nf else np.zeros(int(rng.integers(1, 5000)), np.float32)
+        assert np.array_equal(x, sra.modulate(bits, g1, g2, pre, car)) or nf == 0
+        x = x * np.float32(rng.uniform(0.05, 1.0))
+        snr = [None, 30.0, 15.0, 8.0, 3.0, 0.0, -3.0][k % 7]
+        if snr is not None:
+            sigma = np.sqrt(np.mean(x.astype(np.float64) ** 2) + 1e-12) * 10 ** (-snr / 20) if nf else 0.3
+            x = (x + rng.normal(0, sigma, len(x))).astype(np.float32)
+        if k % 5 == 1 and len(x) > 3000:   # capture ends inside a frame: the decode never completes
+            x = x[:len(x) - int(rng.integers(1, 3000))]
+        if k % 5 == 2 and len(x) > 3000:   # a zeroed / flipped stretch: lost locks, wrong ids
+            a = int(rng.integers(0, len(x) - 2000))
+            x[a:a + int(rng.integers(50, 2000))] *= np.float32(0.0 if k % 2 else -1.0)
+        if k % 5 == 3:                     # clipping
+            x = np.clip(x, -0.3, 0.3)
+        want = orc.ask_demodulate(x)
+        got = sra.demodulate(x, pre, car)
+        assert len(got) == len(want), (k, len(got), len(want))
+        for g, w in zip(got, want):
+            assert g[0] == int(w["start_index"]) and np.float32(g[1]).view(np.uint32) == w["sync_power"].view(np.uint32), (k, g[:2], w)
+            assert g[2] == int(w["id"]) and bool(g[3]) == bool(w["accepted"]), (k, g[2:4], w)
+            assert np.array_equal(np.unpackbits(w["bits"])[:108], g[4].astype(np.uint8)), k
+        n_recs += len(want)
+        n_acc += int(sum(bool(w["accepted"]) for w in want))
+        n_rej += int(sum(not bool(w["accepted"]) for w in want))
+    assert n_recs > 60 and n_acc > 30 and n_rej > 5, (n_recs, n_acc, n_rej)
+
+    # each restatement end to end on ITS OWN tables: a clean loopback returns the frames it was given
+    bits = rng.integers(0, 2, (6, 100)).astype(np.uint8)
+    for f in range(6):
+        bits[f, :8] = [((f + 1) >> (7 - j)) & 1 for j in range(8)]
+    g1, g2 = rng.integers(1, 100, 6), rng.integers(0, 100, 6)
+    got = sra.demodulate(sra.modulate(bits, g1, g2, pre2, car2), pre2, car2)
+    assert [g[2] for g in got] == [1, 2, 3, 4, 5, 6] and all(g[3] for g in got)
+    assert all(np.array_equal(g[4][:100].astype(np.uint8), bits[f]) and not g[4][100:].any() for f, g in enumerate(got))
