@@ -1542,7 +1542,7 @@ __device__ __forceinline__ void publish_blk(uint2* p, uint32_t v, float gain) {
 // detect. All of it is independent of the rest of the capture, so it runs at full occupancy; the per-stream
 // walk then only decides (the drift bound depends on where ITS search started) and links the results.
 #ifndef TMK_CLUSTER_CTAS
-#define TMK_CLUSTER_CTAS 5  // measured at C2: 4 -> 3.66 ms, 5 -> 3.53, 6 -> 3.50
+#define TMK_CLUSTER_CTAS 5  // measured at C2, round 1: 4 -> 3.66 ms, 5 -> 3.53, 6 -> 3.50; final kernel: 4 -> 2.447, 5 -> 2.408, 6 -> 2.538 (7+ do not fit: 34 KB smem)
 #endif
 __global__ void __launch_bounds__(kWarpsPerCta * 32, TMK_CLUSTER_CTAS)
 cluster_kernel(const float* __restrict__ samples, const TmkStreamDev* __restrict__ streams,
