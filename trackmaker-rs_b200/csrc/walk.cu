@@ -309,12 +309,17 @@ __device__ __noinline__ float roll_literal(Ctx& c, float e, uint64_t pos, uint64
 // smallest ulp, one ulp held back for the rounded vs real intermediate), negative / zero / subnormal / NaN /
 // inf values, a clamp, or chains 0 and 3 in different binades make the segment "in doubt": it is rolled
 // literally (roll_literal) from the exact start value that is known by then.
-constexpr uint32_t kParMinSeg = 128;  // steps per lane below which a parallel round is not worth it
+#ifndef TMK_PAR_MIN
+#define TMK_PAR_MIN 128
+#endif
+constexpr uint32_t kParMinSeg = TMK_PAR_MIN;  // steps per lane below which a parallel round is not worth it
 #ifndef TMK_PAR_SEG
 #define TMK_PAR_SEG 512
 #endif
 constexpr uint32_t kParMaxSeg = TMK_PAR_SEG;  // steps per lane and round: the chance that a segment is in doubt and the cost of
                                               // rolling it literally both grow with it (2048: 42 % of the segments at C2)
+                                              // (final kernel, walk at C2, ms: 256 -> 2.956, 384 -> 2.924, 512 -> 2.916, 768 -> 3.002,
+                                              //  1024 -> 3.064; TMK_PAR_MIN 64 -> 2.912, 128 -> 2.916, 256 -> 2.979)
 
 __device__ __noinline__ float roll_parallel(Ctx& c, float e, uint64_t* pos_io, uint64_t w) {
     const float* __restrict__ x = c.x;
