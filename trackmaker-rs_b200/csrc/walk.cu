@@ -309,6 +309,10 @@ __device__ __noinline__ float roll_literal(Ctx& c, float e, uint64_t pos, uint64
 // smallest ulp, one ulp held back for the rounded vs real intermediate), negative / zero / subnormal / NaN /
 // inf values, a clamp, or chains 0 and 3 in different binades make the segment "in doubt": it is rolled
 // literally (roll_literal) from the exact start value that is known by then.
+#ifndef TMK_PAR_DEPTH
+#define TMK_PAR_DEPTH 1  // iterations (of 8 steps) the sample loads of the lane-parallel replay run ahead of the chain
+                         // (2 measured on the final kernel: walk 2.92 -> 2.95 ms at C2, 1.43 -> 1.41 ms on 16 384 x 120 000: no gain)
+#endif
 #ifndef TMK_PAR_MIN
 #define TMK_PAR_MIN 128
 #endif
@@ -363,7 +367,25 @@ __device__ __noinline__ float roll_parallel(Ctx& c, float e, uint64_t* pos_io, u
         const float4* __restrict__ xa = reinterpret_cast<const float4*>(xp);
         const float4* __restrict__ xb = reinterpret_cast<const float4*>(xp + P);
         float4 a0 = xa[0], a1 = xa[1], b0 = xb[0], b1 = xb[1];
+#if TMK_PAR_DEPTH == 2
+        float4 pa0 = a0, pa1 = a1, pb0 = b0, pb1 = b1;  // the samples of the next iteration: loads run two iterations ahead
+        if (L > 8) {
+            pa0 = xa[2];
+            pa1 = xa[3];
+            pb0 = xb[2];
+            pb1 = xb[3];
+        }
+#endif
         for (uint32_t k = 0; k < L; k += 8) {
+#if TMK_PAR_DEPTH == 2
+            float4 an0 = pa0, an1 = pa1, bn0 = pb0, bn1 = pb1;
+            if (k + 16 < L) {
+                pa0 = xa[k / 4 + 4];
+                pa1 = xa[k / 4 + 5];
+                pb0 = xb[k / 4 + 4];
+                pb1 = xb[k / 4 + 5];
+            }
+#else
             float4 an0 = a0, an1 = a1, bn0 = b0, bn1 = b1;
             if (k + 8 < L) {
                 an0 = xa[k / 4 + 2];
@@ -371,6 +393,7 @@ __device__ __noinline__ float roll_parallel(Ctx& c, float e, uint64_t* pos_io, u
                 bn0 = xb[k / 4 + 2];
                 bn1 = xb[k / 4 + 3];
             }
+#endif
             const float a[8] = {a0.x, a0.y, a0.z, a0.w, a1.x, a1.y, a1.z, a1.w};
             const float b[8] = {b0.x, b0.y, b0.z, b0.w, b1.x, b1.y, b1.z, b1.w};
 #pragma unroll
