@@ -279,7 +279,7 @@ int tmk_modulate(tmk_engine* e, const tmk_phy_config* cfg, const tmk_frame_desc*
     std::vector<uint64_t> off(n_frames + 1, 0);
     const uint64_t P = tmk_preamble_len(cfg);
     for (uint32_t i = 0; i < n_frames; ++i) {
-        if (frames[i].len > 65535u || frames[i].payload_off + frames[i].len > payload_len)
+        if (frames[i].len > 65535u || frames[i].payload_off > payload_len || frames[i].len > payload_len - frames[i].payload_off)
             return fail(e, TMK_E_INVALID, "tmk_modulate: frame " + std::to_string(i) + " payload out of range");
         uint64_t flen = P + tmk_sfb(cfg->line_code, cfg->spl, 8ull * (TMK_PHY_HEADER_BYTES + frames[i].len));
         off[i + 1] = off[i] + flen + (i + 1 < n_frames ? gap_samples : 0);
