@@ -227,3 +227,21 @@ class PhyDecoderPy:
                 if self.state is not None:
                     self.state = max(0, self.state - drain)
         return self.frames[n0:]
+
+
+def frame_bits(ftype, seq, src, dst, data):
+    """frame.rs:74-107 (`to_bytes` + `to_bits`): [len_hi, len_lo, crc8(data), type, seq, src, dst, data...], MSB first."""
+    by = [(len(data) >> 8) & 255, len(data) & 255, crc8(data), ftype, seq, src, dst] + list(data)
+    return [(b >> (7 - j)) & 1 for b in by for j in range(8)]
+
+
+def encode_frames(kind, frames, gap, spl=3, preamble_bytes=2):
+    """encoder.rs:41-85: per frame the preamble followed by the line-coded frame bits; `gap` zeros BETWEEN frames only."""
+    lc = LineCode(kind, spl)
+    pre = lc.preamble(preamble_bytes)
+    out = []
+    for i, f in enumerate(frames):
+        out += [pre, lc.encode(frame_bits(*f))]
+        if i + 1 < len(frames):
+            out.append(np.zeros(gap, F))
+    return np.concatenate(out) if out else np.zeros(0, F)

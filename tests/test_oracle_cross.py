@@ -167,3 +167,23 @@ def test_two_restatements_agree_chirp_modem(orc):
     got = sra.demodulate(sra.modulate(bits, g1, g2, pre2, car2), pre2, car2)
     assert [g[2] for g in got] == [1, 2, 3, 4, 5, 6] and all(g[3] for g in got)
     assert all(np.array_equal(g[4][:100].astype(np.uint8), bits[f]) and not g[4][100:].any() for f, g in enumerate(got))
+
+
+@pytest.mark.parametrize("kind", [FB, MAN])
+def test_two_restatements_agree_transmitter(orc, kind):
+    """Rows a9 / a10 (encoder.rs:41-85, frame.rs:74-107): the C++ oracle's modulate against the numpy restatement's, sample
+    for sample, over data / ack frames of 0..300 bytes, several shapes and gaps; plus the reference's own encoder test
+    (encoder.rs:106-128: 4B5B, 2 samples per level, 2 preamble bytes, 3 payload bytes -> 40 + 200 samples)."""
+    import tmkphy
+    from oracle.second_restatement import encode_frames
+    rng = np.random.default_rng(5 + kind)
+    for spl, pb, gap in ((3, 2, 48), (2, 2, 0), (1, 1, 7), (5, 3, 100)):
+        frames = helpers.random_frames(rng, 7, max_len=300) + [(1, 9, 8, 7, b""), (2, 255, 0, 255, bytes(range(256)))]
+        cfg = tmkphy.make_config(kind, spl=spl, preamble_bytes=pb)
+        want = orc.modulate(cfg, frames, gap)
+        got = encode_frames(kind, frames, gap, spl, pb)
+        assert got.dtype == np.float32 and np.array_equal(got, want), (spl, pb, gap)
+    assert len(encode_frames(kind, [], 48)) == 0 and len(orc.modulate(tmkphy.make_config(kind), [], 48)) == 0
+    if kind == FB:
+        x = encode_frames(FB, [(1, 1, 0, 1, bytes([0x12, 0x34, 0x56]))], 0, spl=2, preamble_bytes=2)
+        assert len(x) == 40 + 200  # 16 preamble bits and 80 frame bits: 5 levels per 4 bits, 2 samples per level
