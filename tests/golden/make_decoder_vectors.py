@@ -41,7 +41,7 @@ def main():
     orc.build()
     rng = np.random.default_rng(20261105)
 
-    # ---- src/phy decoder (decoder.rs:68-356): 16 captures, both line codes, clean .. 3 dB, multipath, damage, chunked feeds
+    # ---- src/phy decoder (decoder.rs:68-356): 16 captures, both line codes, clean .. 6.5 dB, multipath, damage, chunked feeds
     pcm, cap_len, cap_kind, cap_chunk = [], [], [], []
     recs_all, pl_all = [], []
     pl_off = 0
